@@ -1,0 +1,406 @@
+// Persistent warp-specialised tcgen05 GEMM for sm_100a with fused epilogues.
+//
+//   D[b] = epilogue(alpha * op(A[b]) * op(B[b])^T)      A: M x K, B: N x K (each K-major or MN-major), D: M x N
+//
+// Design (B200-first, no library GEMM on this path):
+//   * one CTA per SM, static round-robin tile schedule with grouped rasterisation (L2 reuse of B tiles)
+//   * warp 0 lane 0 : TMA producer (cp.async.bulk.tensor, 128-byte swizzle) into a multi-stage smem ring
+//   * warp 1 lane 0 : issues tcgen05.mma (UMMA 128 x BN x 16, fp32 accumulate in TMEM) and tcgen05.commit
+//   * warp 2        : TMEM allocator (2 accumulator stages so epilogue(i) overlaps mainloop(i+1))
+//   * warps 4..7    : epilogue; tcgen05.ld -> registers -> fused math -> swizzled smem -> TMA store
+//   * operands may be K-major ([rows, K] row-major) or MN-major ([K, rows] row-major), which is what the
+//     forward (NT), dgrad (NN) and wgrad (TN) products of a Linear layer need without any transposed copy.
+//
+// Replaces the reference's cublasGemmEx / cublasGemmStridedBatchedEx call sites and the SIMT epilogue kernels
+// that followed them (reference: csrc/transformer/cublas_wrappers.cu:16-164, gelu_kernels.cu:61-128,
+// dropout_kernels.cu:386-465, general_kernels.cu:89-182).
+#include "../common/ptx.cuh"
+#include "../../include/dsb200.h"
+#include <stdio.h>
+#include <type_traits>
+
+namespace dsb {
+
+constexpr int BM = 128;
+constexpr int BK = 64;           // 64 x 16-bit = one 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int EPI_COLS = 64;     // epilogue chunk width (one 128-byte swizzled row of D)
+constexpr int NUM_THREADS = 256;
+
+struct GemmParams {
+    int M, N, K, batch;
+    int a_mn, b_mn;
+    int epilogue;
+    float alpha;
+    const void* bias;
+    const void* aux;
+    long ldaux, stride_aux;
+    void* aux_out;
+    long ldaux_out, stride_aux_out;
+};
+
+template <int BN> struct GemmCfg {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES = (BN == 256) ? 4 : 6;
+    static constexpr int EPI_BYTES = 4 /*warps*/ * 2 /*bufs*/ * 32 * 128;
+    static constexpr int BAR_BYTES = 256;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BAR_BYTES + 1024 /*align slack*/;
+    static constexpr int TMEM_COLS = 2 * BN;  // 512 or 256, power of two
+};
+
+template <typename T, int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+    using Cfg = GemmCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_epi = smem + Cfg::STAGES * Cfg::STAGE_BYTES;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_epi + Cfg::EPI_BYTES);
+    uint64_t* full_bar = bars;                      // [STAGES]
+    uint64_t* empty_bar = bars + Cfg::STAGES;       // [STAGES]
+    uint64_t* tfull_bar = bars + 2 * Cfg::STAGES;   // [2]
+    uint64_t* tempty_bar = tfull_bar + 2;           // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    const int m_blocks = (p.M + BM - 1) / BM;
+    const int n_blocks = (p.N + BN - 1) / BN;
+    const int tiles_per_batch = m_blocks * n_blocks;
+    const int num_tiles = tiles_per_batch * p.batch;
+    const int k_blocks = (p.K + BK - 1) / BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmD);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < Cfg::STAGES; ++i) {
+            mbar_init(&full_bar[i], 1);
+            mbar_init(&empty_bar[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tfull_bar[i], 1);
+            mbar_init(&tempty_bar[i], 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<Cfg::TMEM_COLS>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // tile -> (batch, m_blk, n_blk) with groups of 8 M-blocks sweeping N (keeps a B panel hot in L2)
+    auto decode = [&](int tile, int& b, int& mb, int& nb) {
+        b = tile / tiles_per_batch;
+        int t = tile - b * tiles_per_batch;
+        const int GROUP = 8;
+        int per_group = GROUP * n_blocks;
+        int g = t / per_group;
+        int first_m = g * GROUP;
+        int gsz = min(m_blocks - first_m, GROUP);
+        int r = t - g * per_group;
+        mb = first_m + (r % gsz);
+        nb = r / gsz;
+    };
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                int b, mb, nb;
+                decode(tile, b, mb, nb);
+                const int m0 = mb * BM, n0 = nb * BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1);
+                    uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+                    uint8_t* sb = sa + Cfg::A_BYTES;
+                    mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+                    if (!p.a_mn) {
+                        tma_load_3d(sa, &tmA, &full_bar[stage], kb * BK, m0, b);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / 64; ++j)
+                            tma_load_3d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * BK, b);
+                    }
+                    if (!p.b_mn) {
+                        tma_load_3d(sb, &tmB, &full_bar[stage], kb * BK, n0, b);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_3d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * BK, b);
+                    }
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer (single thread)
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_f16(BM, BN, sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value,
+                                                  p.a_mn, p.b_mn);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(&tempty_bar[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < k_blocks; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+                    const uint32_t sb = sa + Cfg::A_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k) {
+                        // K-major: advance 16 elements (32 B) inside the swizzled 128-B row.
+                        // MN-major: advance 16 k-rows (2 atoms of 8 rows x 128 B).
+                        const uint64_t da = p.a_mn ? make_smem_desc_sw128(sa + k * 2048, BK * 128, 1024)
+                                                   : make_smem_desc_sw128(sa + k * 32, 16, 1024);
+                        const uint64_t db = p.b_mn ? make_smem_desc_sw128(sb + k * 2048, BK * 128, 1024)
+                                                   : make_smem_desc_sw128(sb + k * 32, 16, 1024);
+                        umma_f16(d_tmem, da, db, idesc, (kb | k) != 0);
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(&tfull_bar[as]);
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ epilogue (4 warps, 32 rows each)
+        const int q = warp & 3;  // TMEM lane quarter this warp may touch
+        uint8_t* my_epi = smem_epi + q * (2 * 32 * 128);
+        int it = 0;
+        int buf = 0;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            int b, mb, nb;
+            decode(tile, b, mb, nb);
+            const int m0 = mb * BM, n0 = nb * BN;
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            mbar_wait(&tfull_bar[as], aphase);
+            tc_fence_after();
+            const int row = m0 + q * 32 + lane;
+            const bool row_ok = row < p.M;
+#pragma unroll 1
+            for (int c = 0; c < BN / EPI_COLS; ++c) {
+                uint32_t r0[32], r1[32];
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN + c * EPI_COLS;
+                tmem_ld_32x32b_x32(taddr, r0);
+                tmem_ld_32x32b_x32(taddr + 32, r1);
+                tmem_ld_wait();
+                if (c == BN / EPI_COLS - 1) {
+                    // accumulator stage fully read -> hand it back to the MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[as]);
+                }
+                const int col0 = n0 + c * EPI_COLS;
+                if (col0 >= p.N || m0 + q * 32 >= p.M) continue;  // whole box out of range (warp-uniform)
+
+                float v[64];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    v[i] = __uint_as_float(r0[i]) * p.alpha;
+                    v[32 + i] = __uint_as_float(r1[i]) * p.alpha;
+                }
+                const int epi = p.epilogue;
+                if (p.bias != nullptr && epi != DSB_EPI_DGELU) {
+                    const T* bp = reinterpret_cast<const T*>(p.bias) + col0;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (col0 + j * 8 < p.N) {
+                            uint4 u = __ldg(reinterpret_cast<const uint4*>(bp) + j);
+                            const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                            for (int t = 0; t < 4; ++t) {
+                                float2 f = Cvt<T>::unpack2(w[t]);
+                                v[j * 8 + t * 2] += f.x;
+                                v[j * 8 + t * 2 + 1] += f.y;
+                            }
+                        }
+                    }
+                }
+                if (epi == DSB_EPI_BIAS_GELU) {
+                    if (p.aux_out != nullptr && row_ok) {
+                        T* op = reinterpret_cast<T*>(p.aux_out) + b * p.stride_aux_out + (long)row * p.ldaux_out + col0;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (col0 + j * 8 < p.N) {
+                                uint4 u;
+                                u.x = Cvt<T>::pack2(v[j * 8 + 0], v[j * 8 + 1]);
+                                u.y = Cvt<T>::pack2(v[j * 8 + 2], v[j * 8 + 3]);
+                                u.z = Cvt<T>::pack2(v[j * 8 + 4], v[j * 8 + 5]);
+                                u.w = Cvt<T>::pack2(v[j * 8 + 6], v[j * 8 + 7]);
+                                *(reinterpret_cast<uint4*>(op) + j) = u;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < 64; ++i) v[i] = gelu_tanh(v[i]);
+                } else if (epi == DSB_EPI_BIAS_RESIDUAL || epi == DSB_EPI_DGELU) {
+                    if (row_ok) {
+                        const T* ap = reinterpret_cast<const T*>(p.aux) + b * p.stride_aux + (long)row * p.ldaux + col0;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (col0 + j * 8 < p.N) {
+                                uint4 u = *(reinterpret_cast<const uint4*>(ap) + j);
+                                const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                                for (int t = 0; t < 4; ++t) {
+                                    float2 f = Cvt<T>::unpack2(w[t]);
+                                    if (epi == DSB_EPI_DGELU) {
+                                        v[j * 8 + t * 2] *= gelu_tanh_grad(f.x);
+                                        v[j * 8 + t * 2 + 1] *= gelu_tanh_grad(f.y);
+                                    } else {
+                                        v[j * 8 + t * 2] += f.x;
+                                        v[j * 8 + t * 2 + 1] += f.y;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                // stage the 32 x 64 chunk in swizzled smem, then one TMA store per warp
+                uint8_t* sbuf = my_epi + buf * (32 * 128);
+                if (lane == 0) tma_store_wait_read<1>();
+                __syncwarp();
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    uint4 u;
+                    u.x = Cvt<T>::pack2(v[j * 8 + 0], v[j * 8 + 1]);
+                    u.y = Cvt<T>::pack2(v[j * 8 + 2], v[j * 8 + 3]);
+                    u.z = Cvt<T>::pack2(v[j * 8 + 4], v[j * 8 + 5]);
+                    u.w = Cvt<T>::pack2(v[j * 8 + 6], v[j * 8 + 7]);
+                    *reinterpret_cast<uint4*>(sbuf + lane * 128 + ((j ^ (lane & 7)) << 4)) = u;
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                    tma_store_3d(&tmD, sbuf, col0, m0 + q * 32, b);
+                    tma_store_commit();
+                }
+                buf ^= 1;
+            }
+        }
+        if (lane == 0) tma_store_wait<0>();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            return nullptr;
+        fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+static int make_map(CUtensorMap* m, int is_bf16, const void* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t s1,
+                    uint64_t s2, uint32_t b0, uint32_t b1) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return -1;
+    cuuint64_t dims[3] = {d0, d1, d2};
+    cuuint64_t strides[2] = {s1 * 2, s2 * 2};
+    cuuint32_t box[3] = {b0, b1, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3,
+                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
+}
+
+template <typename T, int BN>
+static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const GemmParams& p, int sms,
+                  cudaStream_t stream) {
+    using Cfg = GemmCfg<BN>;
+    static bool attr_set = false;
+    auto kern = gemm_tcgen05_kernel<T, BN>;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+        if (e != cudaSuccess) return -(int)e;
+        attr_set = true;
+    }
+    const int m_blocks = (p.M + BM - 1) / BM, n_blocks = (p.N + BN - 1) / BN;
+    const long tiles = (long)m_blocks * n_blocks * p.batch;
+    const int grid = (int)(tiles < sms ? tiles : sms);
+    kern<<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, b, d, p);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+}  // namespace dsb
+
+extern "C" int dsb_gemm(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb,
+                        long ldd, long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major, int dtype,
+                        int epilogue, float alpha, const void* bias, const void* aux, long ldaux, long stride_aux,
+                        void* aux_out, long ldaux_out, long stride_aux_out, void* stream_) {
+    using namespace dsb;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (M <= 0 || N <= 0 || K <= 0 || batch <= 0) return 0;
+    if ((lda % 8) || (ldb % 8) || (ldd % 8) || (N % 8)) return DSB_ERR_ALIGN;
+    if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(D)) & 15)
+        return DSB_ERR_ALIGN;
+    if (batch > 1 && ((strideA % 8) || (strideB % 8) || (strideD % 8))) return DSB_ERR_ALIGN;
+    if ((epilogue == DSB_EPI_BIAS_RESIDUAL || epilogue == DSB_EPI_DGELU) && (!aux || (ldaux % 8))) return DSB_ERR_ARG;
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int bn = (N > 128) ? 256 : 128;
+    const int bf = dtype == DSB_DTYPE_BF16;
+    if (batch == 1) {
+        strideA = (long)(a_mn_major ? K : M) * lda;
+        strideB = (long)(b_mn_major ? K : N) * ldb;
+        strideD = (long)M * ldd;
+    }
+    CUtensorMap ta, tb, td;
+    int rc;
+    if (!a_mn_major) rc = make_map(&ta, bf, A, K, M, batch, lda, strideA, BK, BM);
+    else rc = make_map(&ta, bf, A, M, K, batch, lda, strideA, 64, BK);
+    if (rc) return rc;
+    if (!b_mn_major) rc = make_map(&tb, bf, B, K, N, batch, ldb, strideB, BK, bn);
+    else rc = make_map(&tb, bf, B, N, K, batch, ldb, strideB, 64, BK);
+    if (rc) return rc;
+    rc = make_map(&td, bf, D, N, M, batch, ldd, strideD, EPI_COLS, 32);
+    if (rc) return rc;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.batch = batch;
+    p.a_mn = a_mn_major; p.b_mn = b_mn_major;
+    p.epilogue = epilogue; p.alpha = alpha;
+    p.bias = bias; p.aux = aux; p.ldaux = ldaux; p.stride_aux = stride_aux;
+    p.aux_out = aux_out; p.ldaux_out = ldaux_out; p.stride_aux_out = stride_aux_out;
+    if (bf) {
+        return bn == 256 ? launch<__nv_bfloat16, 256>(ta, tb, td, p, sms, stream)
+                         : launch<__nv_bfloat16, 128>(ta, tb, td, p, sms, stream);
+    }
+    return bn == 256 ? launch<__half, 256>(ta, tb, td, p, sms, stream)
+                     : launch<__half, 128>(ta, tb, td, p, sms, stream);
+}

@@ -1,0 +1,130 @@
+/* dsb200.h — C ABI of the deeperspeed_b200 native kernel library (libdsb200.so, sm_100a).
+ *
+ * Every entry point takes raw device pointers plus an opaque `stream` (a cudaStream_t cast to void*; NULL is the
+ * legacy default stream) and returns 0 on success or a negative DSB_ERR_* / -cudaError code. Nothing here
+ * synchronises the device. Python binds these through ctypes (deeperspeed_b200/ops/native.py).
+ *
+ * Citations name the reference implementation (MLRichter/DeeperSpeed) whose behaviour each entry point covers.
+ */
+#ifndef DSB200_H
+#define DSB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSB_OK 0
+#define DSB_ERR_ALIGN (-2001)  /* pointer / leading dimension not 16-byte aligned */
+#define DSB_ERR_ARG (-2002)    /* inconsistent arguments */
+#define DSB_ERR_SIZE (-2003)   /* problem size outside what the entry point supports */
+#define DSB_ERR_DTYPE (-2004)
+
+#define DSB_DTYPE_F16 0
+#define DSB_DTYPE_BF16 1
+#define DSB_DTYPE_F32 2
+
+/* ---- tcgen05 GEMM with fused epilogues (csrc/gemm/gemm_tcgen05.cu) --------------------------------------------
+ * D[b] = epi(alpha * A[b] * B[b]^T), A: M x K, B: N x K. a_mn_major / b_mn_major = 1 means the operand is stored
+ * [K, rows] row-major (i.e. "transposed" in BLAS terms). Replaces cublasGemmEx/cublasGemmStridedBatchedEx
+ * (reference csrc/transformer/cublas_wrappers.cu:16-164) plus the SIMT epilogues that followed them. */
+#define DSB_EPI_NONE 0
+#define DSB_EPI_BIAS 1          /* + bias[n] */
+#define DSB_EPI_BIAS_GELU 2     /* gelu(acc + bias); optional aux_out receives the pre-activation */
+#define DSB_EPI_BIAS_RESIDUAL 3 /* acc (+ bias) + aux[m, n]; aux may alias D (accumulate) */
+#define DSB_EPI_DGELU 4         /* acc * gelu'(aux[m, n]) */
+int dsb_gemm(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb, long ldd,
+             long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major, int dtype, int epilogue,
+             float alpha, const void* bias, const void* aux, long ldaux, long stride_aux, void* aux_out,
+             long ldaux_out, long stride_aux_out, void* stream);
+
+/* ---- optimizers (csrc/optim) -------------------------------------------------------------------------------- */
+/* Flat-arena Adam/AdamW: fp32 master/m/v, grads in g_dtype, optional low-precision copy of the updated params.
+ * inv_scale_dev (optional, device float) multiplies the gradient (1 / combined loss scale); skip_dev (optional,
+ * device int) != 0 turns the launch into a no-op (overflow skip without a host sync).
+ * Reference: csrc/adam/multi_tensor_adam.cu:28-121. */
+int dsb_adam_flat(float* p, float* m, float* v, const void* g, int g_dtype, void* p_lp, int lp_dtype, long n,
+                  float lr, float beta1, float beta2, float eps, float weight_decay, int adamw_mode,
+                  int bias_correction, int step, float inv_scale, const float* inv_scale_dev, const int* skip_dev,
+                  void* stream);
+/* Multi-tensor Adam over a host table of device pointers (params updated in their own dtype, fp32 math).
+ * Reference: csrc/adam/multi_tensor_apply.cuh:43-127. */
+int dsb_adam_multi(int ntensors, void* const* p, void* const* g, void* const* m, void* const* v, const long* numel,
+                   int p_dtype, int g_dtype, int state_dtype, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int adamw_mode, int bias_correction, int step, float inv_scale, void* stream);
+/* LAMB for one tensor; `scratch` needs dsb_lamb_scratch_bytes(n) bytes. coeff_out (device float) gets the trust
+ * ratio. Reference: csrc/lamb/fused_lamb_cuda_kernel.cu:186-310. */
+long dsb_lamb_scratch_bytes(long n);
+int dsb_lamb_step(void* p, int p_dtype, void* p_copy, int copy_dtype, const void* g, int g_dtype, float* m, float* v,
+                  long n, float lr, float beta1, float beta2, float eps, float weight_decay, float max_coeff,
+                  float min_coeff, int eps_inside_sqrt, int bias_correction, int step, float grad_scale,
+                  float* coeff_out, void* scratch, void* stream);
+/* dtype cast (fp32 -> fp16/bf16 param write-back; reference csrc/adam/custom_cuda_kernel.cu:5-20). */
+int dsb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, long n, void* stream);
+/* sum of squares + inf/nan flag of a flat buffer, no host sync. `scratch` needs dsb_sumsq_scratch_bytes() bytes.
+ * out[0] += sumsq (or = if !accumulate), flag_out |= non-finite seen. Replaces the per-tensor host-synchronising
+ * overflow checks (reference deepspeed/runtime/utils.py:157-175, zero/stage2.py:1600-1618). */
+long dsb_sumsq_scratch_bytes(void);
+int dsb_sumsq(const void* x, int dtype, long n, float* out, int* flag_out, int accumulate, void* scratch,
+              void* stream);
+/* x *= scale (device or host scalar), in place. */
+int dsb_scale(void* x, int dtype, long n, float scale, const float* scale_dev, void* stream);
+
+/* ---- transformer building blocks (csrc/transformer) --------------------------------------------------------- */
+/* y = LN(x (+ residual)) * gamma + beta; optionally writes sum_out = x + residual, mean/rstd for backward.
+ * Reference: csrc/transformer/normalize_kernels.cu:16-600. */
+int dsb_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, void* y,
+                      void* sum_out, float* mean, float* rstd, long rows, int hidden, float eps, int dtype,
+                      void* stream);
+/* dx = LN'(dy) (+ dres); dgamma/dbeta via per-CTA partials in `scratch` (dsb_layernorm_bwd_scratch_bytes).
+ * Reference: csrc/transformer/normalize_kernels.cu:607-2103. */
+long dsb_layernorm_bwd_scratch_bytes(int hidden);
+int dsb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
+                      const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden, int dtype,
+                      void* scratch, void* stream);
+/* y = softmax(x * scale + mask) over the last dim. x: [batch, heads, q_len, k_len]; mask: additive [batch, k_len]
+ * or NULL; causal != 0 masks k > q + (k_len - q_len). In place allowed.
+ * Reference: csrc/transformer/softmax_kernels.cu:8-431. */
+int dsb_softmax_fwd(const void* x, const void* mask, void* y, int batch, int heads, int q_len, int k_len,
+                    float scale, int causal, int dtype, void* stream);
+/* dx = y * (dy - sum(dy * y)) * scale. Reference: softmax_kernels.cu:433-577. */
+int dsb_softmax_bwd(const void* dy, const void* y, void* dx, long rows, int k_len, float scale, int dtype,
+                    void* stream);
+/* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */
+int dsb_bias_gelu_fwd(const void* x, const void* bias, void* y, long rows, int cols, int dtype, void* stream);
+int dsb_bias_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, long rows, int cols, int dtype,
+                      void* stream);
+/* out = dropout(x + bias) + residual with a Philox mask (uint8 per element); ratio = drop probability.
+ * Reference: csrc/transformer/dropout_kernels.cu:5-721. */
+int dsb_dropout_fwd(const void* x, const void* bias, const void* residual, void* out, unsigned char* mask, long rows,
+                    int cols, float ratio, unsigned long long seed, unsigned long long offset, int dtype,
+                    void* stream);
+int dsb_dropout_bwd(const void* dy, const unsigned char* mask, void* dx, long n, float ratio, int dtype,
+                    void* stream);
+/* [B, S, 3, H, D] (+ bias[3*H*D]) -> q, k, v each [B, H, S, D]; and [B, H, S, D] -> [B, S, H*D].
+ * Reference: csrc/transformer/transform_kernels.cu:56-575. */
+int dsb_qkv_bias_split_transpose(const void* qkv, const void* bias, void* q, void* k, void* v, int B, int S, int H,
+                                 int D, int dtype, void* stream);
+int dsb_transpose_0213(const void* x, void* y, int B, int d1, int d2, int D, int dtype, void* stream);
+/* out[cols] = sum over rows of x[rows, cols] (bias gradient); `scratch` = cols floats of fp32 accumulators.
+ * Reference: general_kernels.cu:6-48. */
+int dsb_column_sum(const void* x, void* out, long rows, int cols, int dtype, int accumulate, float* scratch,
+                   void* stream);
+/* out = a + b (+ c (+ d)). Reference: general_kernels.cu:89-323. */
+int dsb_fused_add(const void* a, const void* b, const void* c, const void* d, void* out, long n, int dtype,
+                  void* stream);
+/* Token-level softmax cross entropy: loss[t] = lse(logits[t]) - logits[t, target[t]] (0 for ignore_index);
+ * backward overwrites logits with (softmax - onehot) * grad_scale. */
+int dsb_cross_entropy_fwd(const void* logits, const long* targets, float* loss, float* lse, long tokens, int vocab,
+                          long ld, long ignore_index, int dtype, void* stream);
+int dsb_cross_entropy_bwd(void* logits, const long* targets, const float* lse, const float* grad_scale_dev,
+                          float grad_scale, long tokens, int vocab, long ld, long ignore_index, int dtype,
+                          void* stream);
+/* Rotary embedding applied in place to q and k laid out [tokens_b, seq, heads, dim] (first rot_dim dims rotate,
+ * GPT-NeoX half-split convention); inverse != 0 applies the transpose rotation (backward). */
+int dsb_rotary(void* q, void* k, int B, int S, int H, int D, int rot_dim, long stride_b, long stride_s, long stride_h,
+               float base, int inverse, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSB200_H */

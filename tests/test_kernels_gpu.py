@@ -1,0 +1,213 @@
+"""Numerics of every sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import pytest
+import torch
+
+from deeperspeed_b200.ops import kernels as K
+from deeperspeed_b200.ops import native as N
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).abs().max() / (b.abs().max() + 1e-6)).item()
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(128, 256, 64), (256, 512, 128), (1000, 264, 200), (4096, 2048, 2048), (384, 128, 320),
+                                   (77, 64, 72)])
+@pytest.mark.parametrize("ta,tb", [(False, True), (False, False), (True, False), (True, True)])
+def test_gemm_layouts(dtype, shape, ta, tb):
+    M, Nn, Kk = shape
+    torch.manual_seed(0)
+    a = torch.randn((Kk, M) if ta else (M, Kk), device=DEV, dtype=dtype)
+    b = torch.randn((Nn, Kk) if tb else (Kk, Nn), device=DEV, dtype=dtype)
+    if (M % 8 and ta) or (Nn % 8):
+        pytest.skip("leading dims must be multiples of 8")
+    out = K.gemm(a, b, trans_a=ta, trans_b=tb)
+    ref = (a.float().t() if ta else a.float()) @ (b.float().t() if tb else b.float())
+    assert _rel(out, ref) < (2e-3 if dtype == torch.float16 else 1.5e-2)
+
+
+@pytest.mark.parametrize("epi", ["bias", "bias_gelu", "residual", "dgelu", "accum"])
+def test_gemm_epilogues(epi):
+    torch.manual_seed(1)
+    M, Nn, Kk = 520, 1032, 512
+    dt = torch.float16
+    a = torch.randn(M, Kk, device=DEV, dtype=dt) * 0.1
+    b = torch.randn(Nn, Kk, device=DEV, dtype=dt) * 0.1
+    bias = torch.randn(Nn, device=DEV, dtype=dt)
+    aux = torch.randn(M, Nn, device=DEV, dtype=dt)
+    acc = a.float() @ b.float().t()
+    if epi == "bias":
+        out = K.gemm(a, b, epilogue=N.EPI_BIAS, bias=bias)
+        ref = acc + bias.float()
+    elif epi == "bias_gelu":
+        pre = torch.empty(M, Nn, device=DEV, dtype=dt)
+        out = K.gemm(a, b, epilogue=N.EPI_BIAS_GELU, bias=bias, aux_out=pre)
+        ref = K.gelu_tanh(acc + bias.float())
+        assert _rel(pre, acc + bias.float()) < 2e-3
+    elif epi == "residual":
+        out = K.gemm(a, b, epilogue=N.EPI_BIAS_RESIDUAL, bias=bias, aux=aux)
+        ref = acc + bias.float() + aux.float()
+    elif epi == "dgelu":
+        out = K.gemm(a, b, epilogue=N.EPI_DGELU, aux=aux)
+        ref = acc * K.gelu_tanh_grad(aux.float())
+    else:
+        out = aux.clone()
+        K.gemm(a, b, epilogue=N.EPI_BIAS_RESIDUAL, aux=out, out=out)
+        ref = acc + aux.float()
+    assert _rel(out, ref) < 3e-3
+
+
+def test_gemm_batched_alpha():
+    torch.manual_seed(2)
+    B, S, D = 12, 256, 64
+    q = torch.randn(B, S, D, device=DEV, dtype=torch.float16)
+    k = torch.randn(B, S, D, device=DEV, dtype=torch.float16)
+    v = torch.randn(B, S, D, device=DEV, dtype=torch.float16)
+    sc = K.gemm(q, k, trans_b=True, alpha=0.125)
+    assert _rel(sc, torch.matmul(q.float(), k.float().transpose(1, 2)) * 0.125) < 2e-3
+    ctx = K.gemm(sc, v, trans_b=False)
+    assert _rel(ctx, torch.matmul(sc.float(), v.float())) < 2e-3
+
+
+def test_linear_autograd():
+    torch.manual_seed(3)
+    x = torch.randn(4, 96, 256, device=DEV, dtype=torch.float16, requires_grad=True)
+    w = (torch.randn(512, 256, device=DEV, dtype=torch.float16) * 0.05).requires_grad_()
+    b = torch.randn(512, device=DEV, dtype=torch.float16, requires_grad=True)
+    y = K.linear_gelu(x, w, b)
+    g = torch.randn_like(y)
+    y.backward(g)
+    xf, wf, bf = (t.detach().float().requires_grad_() for t in (x, w, b))
+    yr = K.gelu_tanh(torch.nn.functional.linear(xf, wf, bf))
+    yr.backward(g.float())
+    assert _rel(y, yr) < 3e-3
+    assert _rel(x.grad, xf.grad) < 5e-3
+    assert _rel(w.grad, wf.grad) < 5e-3
+    assert _rel(b.grad, bf.grad) < 5e-3
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("hidden", [160, 1024, 2048, 4096, 8192])
+def test_layernorm(dtype, hidden):
+    torch.manual_seed(4)
+    rows = 333
+    x = torch.randn(rows, hidden, device=DEV, dtype=dtype, requires_grad=True)
+    r = torch.randn(rows, hidden, device=DEV, dtype=dtype, requires_grad=True)
+    g = (1 + 0.1 * torch.randn(hidden, device=DEV, dtype=dtype)).requires_grad_()
+    b = (0.1 * torch.randn(hidden, device=DEV, dtype=dtype)).requires_grad_()
+    y, s = K.layer_norm(x, g, b, 1e-5, residual=r)
+    gy, gs = torch.randn_like(y), torch.randn_like(s)
+    (y * gy).sum().backward(retain_graph=True)
+    (s * gs).sum().backward()
+    xf, rf, gf, bf = (t.detach().float().requires_grad_() for t in (x, r, g, b))
+    sf = (xf + rf)
+    yf = torch.nn.functional.layer_norm(sf, (hidden,), gf, bf, 1e-5)
+    ((yf * gy.float()).sum() + (sf * gs.float()).sum()).backward()
+    tol = 4e-3 if dtype == torch.float16 else 3e-2
+    assert _rel(y, yf) < tol and _rel(s, sf) < tol
+    assert _rel(x.grad, xf.grad) < tol and _rel(r.grad, rf.grad) < tol
+    assert _rel(g.grad, gf.grad) < tol and _rel(b.grad, bf.grad) < tol
+
+
+@pytest.mark.parametrize("sk", [64, 128, 512, 2048, 8192])
+@pytest.mark.parametrize("causal", [False, True])
+def test_softmax(sk, causal):
+    torch.manual_seed(5)
+    B, H, Sq = 2, 3, min(sk, 128)
+    x = torch.randn(B, H, Sq, sk, device=DEV, dtype=torch.float16)
+    mask = torch.zeros(B, sk, device=DEV, dtype=torch.float16)
+    mask[:, -5:] = -10000.0
+    y = K.softmax_fwd(x, mask, scale=0.3, causal=causal)
+    ref = K.softmax_fwd(x.cpu(), mask.cpu(), scale=0.3, causal=causal).to(DEV)
+    assert _rel(y, ref) < 2e-3
+    dy = torch.randn_like(y)
+    dx = K.softmax_bwd(dy, y, scale=0.3)
+    assert _rel(dx, K.softmax_bwd(dy.cpu(), y.cpu(), scale=0.3).to(DEV)) < 3e-3
+
+
+def test_bias_gelu_dropout_transforms():
+    torch.manual_seed(6)
+    x = torch.randn(300, 1024, device=DEV, dtype=torch.float16)
+    bias = torch.randn(1024, device=DEV, dtype=torch.float16)
+    assert _rel(K.bias_gelu_fwd(x, bias), K.gelu_tanh(x.float() + bias.float())) < 2e-3
+    dy = torch.randn_like(x)
+    assert _rel(K.bias_gelu_bwd(dy, x, bias), dy.float() * K.gelu_tanh_grad(x.float() + bias.float())) < 3e-3
+    res = torch.randn_like(x)
+    out, mask = K.dropout_fwd(x, 0.25, seed=1234, offset=7, bias=bias, residual=res)
+    keep = mask.float()
+    assert abs(keep.mean().item() - 0.75) < 0.01
+    ref = (x.float() + bias.float()) * keep / 0.75 + res.float()
+    assert _rel(out, ref) < 2e-3
+    out2, mask2 = K.dropout_fwd(x, 0.25, seed=1234, offset=7, bias=bias, residual=res)
+    assert torch.equal(mask, mask2)
+    assert _rel(K.dropout_bwd(dy, mask, 0.25), dy.float() * keep / 0.75) < 2e-3
+    B, S, H, D = 2, 50, 4, 64
+    qkv = torch.randn(B, S, 3 * H * D, device=DEV, dtype=torch.float16)
+    qb = torch.randn(3 * H * D, device=DEV, dtype=torch.float16)
+    q, k, v = K.qkv_bias_split_transpose(qkv, qb, B, S, H, D)
+    qr, kr, vr = K.qkv_bias_split_transpose(qkv.cpu(), qb.cpu(), B, S, H, D)
+    assert _rel(q, qr.to(DEV)) < 1e-3 and _rel(k, kr.to(DEV)) < 1e-3 and _rel(v, vr.to(DEV)) < 1e-3
+    assert torch.equal(K.transpose_0213(q), q.permute(0, 2, 1, 3).contiguous())
+    assert _rel(K.column_sum(x), x.float().sum(0)) < 3e-3
+    assert _rel(K.fused_add(x, res, dy), x.float() + res.float() + dy.float()) < 2e-3
+
+
+@pytest.mark.parametrize("vocab", [1000, 50432, 50257])
+def test_cross_entropy(vocab):
+    torch.manual_seed(7)
+    T = 257
+    ld = (vocab + 7) // 8 * 8
+    buf = torch.randn(T, ld, device=DEV, dtype=torch.float16) * 2
+    logits = buf[:, :vocab].detach().requires_grad_()
+    tg = torch.randint(0, vocab, (T,), device=DEV)
+    tg[5] = -100
+    ref_in = logits.detach().float().requires_grad_()
+    ref = torch.nn.functional.cross_entropy(ref_in, tg, ignore_index=-100)
+    (ref * 3.0).backward()
+    loss = K.cross_entropy(logits, tg)
+    (loss * 3.0).backward()
+    assert abs(loss.item() - ref.item()) < 2e-3 * abs(ref.item())
+    assert _rel(logits.grad, ref_in.grad) < 5e-3
+
+
+def test_rotary():
+    torch.manual_seed(8)
+    B, S, H, D = 2, 128, 4, 128
+    qkv = torch.randn(B, S, 3, H, D, device=DEV, dtype=torch.float16, requires_grad=True)
+    q, k = K.rotary(qkv[:, :, 0], qkv[:, :, 1], rot_dim=32)
+    qr, kr = K._rotary_ref(qkv[:, :, 0].detach().cpu(), qkv[:, :, 1].detach().cpu(), 32, 10000.0, False)
+    assert _rel(q, qr.to(DEV)) < 2e-3 and _rel(k, kr.to(DEV)) < 2e-3
+    (q.float().sum() + 2 * k.float().sum()).backward()
+    assert torch.isfinite(qkv.grad).all()
+
+
+@pytest.mark.parametrize("gdt", [torch.float16, torch.bfloat16, torch.float32])
+def test_adam_flat_and_sumsq(gdt):
+    torch.manual_seed(9)
+    n = 1_000_003
+    p = torch.randn(n, device=DEV)
+    m = torch.zeros(n, device=DEV)
+    v = torch.zeros(n, device=DEV)
+    g = (torch.randn(n, device=DEV) * 4).to(gdt)
+    lp = torch.empty(n, device=DEV, dtype=torch.float16)
+    pr, mr, vr = p.cpu().clone(), m.cpu().clone(), v.cpu().clone()
+    for step in (1, 2):
+        K.adam_flat(p, m, v, g, lp=lp, lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, step=step,
+                    inv_scale=0.25)
+        K.adam_flat(pr, mr, vr, g.cpu(), lr=1e-2, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.01, step=step,
+                    inv_scale=0.25)
+    assert _rel(p, pr.to(DEV)) < 1e-5 and _rel(lp, pr.to(DEV)) < 1e-3
+    skip = torch.ones(1, dtype=torch.int32, device=DEV)
+    before = p.clone()
+    K.adam_flat(p, m, v, g, lr=1.0, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, step=3, skip_dev=skip)
+    assert torch.equal(p, before)
+    flag = torch.zeros(1, dtype=torch.int32, device=DEV)
+    s = K.sumsq(g, flag=flag)
+    assert abs(s.item() - (g.float() ** 2).sum().item()) < 1e-3 * s.item() and flag.item() == 0
+    g[12345] = float("inf")
+    K.sumsq(g, flag=flag)
+    assert flag.item() == 1
