@@ -543,3 +543,36 @@ def rotary(q, k, rot_dim, base=10000.0):
             q, k = q.contiguous(), k.contiguous()
         return RotaryFn.apply(q.clone(), k.clone(), rot_dim, base)
     return _rotary_ref(q, k, rot_dim, base, False)
+
+
+class LinearResidualFn(torch.autograd.Function):
+    """y = x @ W^T + b + r with the bias and residual add fused into the GEMM epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, r):
+        x2 = x.reshape(-1, x.shape[-1])
+        r2 = r.reshape(-1, r.shape[-1])
+        if not r2.is_contiguous():
+            r2 = r2.contiguous()
+        y = gemm(x2, w, trans_b=True, epilogue=N.EPI_BIAS_RESIDUAL, bias=b, aux=r2)
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias = b is not None
+        ctx.x_shape = x.shape
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx = gemm(dy2, w, trans_b=False).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dw = gemm(dy2, x2, trans_a=True, trans_b=False) if ctx.needs_input_grad[1] else None
+        db = column_sum(dy2) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        return dx, dw, db, (dy if ctx.needs_input_grad[3] else None)
+
+
+def linear_residual(x, w, b, r):
+    if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16):
+        return LinearResidualFn.apply(x, w, b, r)
+    return F.linear(x, w, b) + r

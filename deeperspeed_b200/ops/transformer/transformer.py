@@ -1,0 +1,349 @@
+"""DeepSpeedTransformerLayer: BERT-style encoder layer (pre- or post-LN) on the sm_100a kernel stack.
+
+API / parameter names / init per reference deepspeed/ops/transformer/transformer.py:39-614 and dataflow per
+csrc/transformer/ds_transformer_cuda.cpp:146-547. Instead of a stateful C++ layer object that owns
+cuBLAS handles and a workspace, the layer is a composition of fused autograd ops, each backed by our kernels:
+
+  LN(+residual) kernel -> tcgen05 GEMM (QKV) -> bias+split+transpose kernel -> batched tcgen05 GEMM (QK^T, scaled)
+  -> masked softmax kernel -> Philox dropout kernel -> batched tcgen05 GEMM (P.V) -> transpose kernel
+  -> tcgen05 GEMM (out-proj) -> bias+dropout+residual kernel -> LN kernel -> tcgen05 GEMM with bias+GeLU epilogue
+  -> tcgen05 GEMM (FF2) -> bias+dropout+residual kernel.
+
+Memory flags: `gelu_checkpoint`, `attn_dropout_checkpoint` and `normalize_invertible` are honoured by recomputing the
+corresponding segment in backward (activation recompute) rather than by special-cased kernels."""
+import json
+import math
+
+import torch
+from torch import nn
+
+from .. import kernels as K
+from .. import native as N
+
+
+class TransformerConfig:
+    def __init__(self, batch_size, max_seq_length, hidden_size, intermediate_size, heads, attn_dropout_ratio,
+                 hidden_dropout_ratio, num_hidden_layers, initializer_range):
+        self.layer_id = -1
+        self.batch_size = batch_size
+        self.hidden_size = hidden_size
+        self.intermediate_size = intermediate_size
+        self.max_seq_length = max_seq_length
+        self.heads = heads
+        self.attn_dropout_ratio = attn_dropout_ratio
+        self.hidden_dropout_ratio = hidden_dropout_ratio
+        self.num_hidden_layers = num_hidden_layers
+        self.initializer_range = initializer_range
+
+
+class DeepSpeedTransformerConfig(TransformerConfig):
+    """batch_size is a maximum; intermediate_size defaults to 4*hidden; see the reference docstring for each flag."""
+
+    def __init__(self, batch_size=-1, max_seq_length=-1, hidden_size=-1, intermediate_size=-1, heads=-1,
+                 attn_dropout_ratio=-1, hidden_dropout_ratio=-1, num_hidden_layers=-1, initializer_range=-1,
+                 local_rank=-1, seed=-1, fp16=False, pre_layer_norm=True, normalize_invertible=False,
+                 gelu_checkpoint=False, adjust_init_range=True, attn_dropout_checkpoint=False, stochastic_mode=False,
+                 huggingface=False, training=True, bf16=False, layer_norm_eps=1e-12):
+        super().__init__(batch_size, max_seq_length, hidden_size,
+                         intermediate_size if intermediate_size > 0 else 4 * hidden_size, heads, attn_dropout_ratio,
+                         hidden_dropout_ratio, num_hidden_layers, initializer_range)
+        self.fp16 = fp16
+        self.bf16 = bf16
+        self.pre_layer_norm = pre_layer_norm
+        self.local_rank = local_rank
+        self.seed = seed
+        self.normalize_invertible = normalize_invertible
+        self.gelu_checkpoint = gelu_checkpoint
+        self.adjust_init_range = adjust_init_range
+        self.test_gemm = False
+        self.training = training
+        self.is_grad_enabled = True
+        self.attn_dropout_checkpoint = attn_dropout_checkpoint
+        self.stochastic_mode = stochastic_mode
+        self.huggingface = huggingface
+        self.layer_norm_eps = layer_norm_eps
+
+    @classmethod
+    def from_dict(cls, json_object):
+        config = DeepSpeedTransformerConfig()
+        for key, value in json_object.items():
+            config.__dict__[key] = value
+        return config
+
+    @classmethod
+    def from_json_file(cls, json_file):
+        with open(json_file, "r", encoding="utf-8") as reader:
+            text = reader.read()
+        return cls.from_dict(json.loads(text))
+
+
+# ------------------------------------------------------------------------------------------------ fused autograd ops
+class MatmulFn(torch.autograd.Function):
+    """Batched C = alpha * A @ op(B) on the tcgen05 GEMM (fwd, dA, dB all tensor-core, no transposed copies)."""
+
+    @staticmethod
+    def forward(ctx, a, b, trans_b, alpha):
+        ctx.save_for_backward(a, b)
+        ctx.trans_b, ctx.alpha = trans_b, alpha
+        return K.gemm(a, b, trans_b=trans_b, alpha=alpha)
+
+    @staticmethod
+    def backward(ctx, dc):
+        a, b = ctx.saved_tensors
+        dc = dc.contiguous()
+        da = db = None
+        if ctx.needs_input_grad[0]:
+            # dA = alpha * dC @ op(B)^T
+            da = K.gemm(dc, b, trans_b=not ctx.trans_b, alpha=ctx.alpha)
+        if ctx.needs_input_grad[1]:
+            if ctx.trans_b:   # C = A B^T, B: [N, K]  -> dB = dC^T A
+                db = K.gemm(dc, a, trans_a=True, trans_b=False, alpha=ctx.alpha)
+            else:             # C = A B,   B: [K, N]  -> dB = A^T dC
+                db = K.gemm(a, dc, trans_a=True, trans_b=False, alpha=ctx.alpha)
+        return da, db, None, None
+
+
+def _gemm_ok(*ts):
+    return all(t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) for t in ts)
+
+
+def matmul(a, b, trans_b=False, alpha=1.0):
+    if _gemm_ok(a, b) and a.shape[-1] % 8 == 0 and b.shape[-1] % 8 == 0 and a.shape[-2] % 8 == 0:
+        return MatmulFn.apply(a.contiguous(), b.contiguous(), trans_b, alpha)
+    bt = b.transpose(-1, -2) if trans_b else b
+    return torch.matmul(a, bt) * alpha
+
+
+class SoftmaxFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, scores, mask, scale):
+        y = K.softmax_fwd(scores, mask, scale=scale)
+        ctx.save_for_backward(y)
+        ctx.scale = scale
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return K.softmax_bwd(dy.contiguous(), y, scale=ctx.scale), None, None
+
+
+def masked_softmax(scores, mask2d, scale=1.0):
+    """scores [B,H,Sq,Sk]; mask2d additive [B,Sk] (or None)."""
+    if _gemm_ok(scores) and scores.shape[-1] % 8 == 0:
+        return SoftmaxFn.apply(scores.contiguous(), mask2d, scale)
+    s = scores.float() * scale
+    if mask2d is not None:
+        s = s + mask2d.float().view(mask2d.shape[0], 1, 1, -1)
+    return torch.softmax(s, -1).to(scores.dtype)
+
+
+class DropoutFn(torch.autograd.Function):
+    """out = dropout(x + bias) + residual with a Philox mask (seed, offset) generated in the kernel."""
+    _offset = 0
+
+    @staticmethod
+    def forward(ctx, x, bias, residual, ratio, seed):
+        DropoutFn._offset += 1
+        out, mask = K.dropout_fwd(x, ratio, seed, DropoutFn._offset, bias=bias, residual=residual)
+        ctx.save_for_backward(mask)
+        ctx.ratio = ratio
+        ctx.has_bias, ctx.has_res = bias is not None, residual is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx = K.dropout_bwd(dy, mask, ctx.ratio)
+        db = K.column_sum(dx.view(-1, dx.shape[-1])) if ctx.has_bias else None
+        return dx, db, (dy if ctx.has_res else None), None, None
+
+
+def bias_dropout_residual(x, bias, residual, ratio, training, seed=0):
+    if training and ratio > 0.0 and _gemm_ok(x) and x.shape[-1] % 8 == 0:
+        return DropoutFn.apply(x.contiguous(), bias, residual.contiguous() if residual is not None else None, ratio, seed)
+    y = x if bias is None else x + bias
+    if training and ratio > 0.0:
+        y = torch.nn.functional.dropout(y, ratio, True)
+    return y if residual is None else y + residual
+
+
+class DeepSpeedTransformerLayer(nn.Module):
+    """Initialize the DeepSpeed Transformer Layer.
+
+    Arguments:
+        config: DeepSpeedTransformerConfig
+        initial_weights / initial_biases: optional [q, k, v, attn_out, attn_norm, inter, output, norm] tensors
+            (used by module injection and by the unit tests to start from a reference BERT layer)."""
+    layer_id = 0
+
+    def __init__(self, config, initial_weights=None, initial_biases=None):
+        super().__init__()
+        self.config = config
+        self.config.layer_id = DeepSpeedTransformerLayer.layer_id
+        DeepSpeedTransformerLayer.layer_id = DeepSpeedTransformerLayer.layer_id + 1
+        h, inter = self.config.hidden_size, self.config.intermediate_size
+        if initial_weights is None and initial_biases is None:
+            self.attn_qkvw = nn.Parameter(torch.Tensor(h * 3, h))
+            self.attn_qkvb = nn.Parameter(torch.Tensor(h * 3))
+            self.attn_ow = nn.Parameter(torch.Tensor(h, h))
+            self.attn_ob = nn.Parameter(torch.Tensor(h))
+            self.attn_nw = nn.Parameter(torch.Tensor(h))
+            self.attn_nb = nn.Parameter(torch.Tensor(h))
+            self.inter_w = nn.Parameter(torch.Tensor(inter, h))
+            self.inter_b = nn.Parameter(torch.Tensor(inter))
+            self.output_w = nn.Parameter(torch.Tensor(h, inter))
+            self.output_b = nn.Parameter(torch.Tensor(h))
+            self.norm_w = nn.Parameter(torch.Tensor(h))
+            self.norm_b = nn.Parameter(torch.Tensor(h))
+            self.init_transformer_weights(self.config.adjust_init_range)
+        else:
+            q, k, v = initial_weights[0].data, initial_weights[1].data, initial_weights[2].data
+            self.attn_qkvw = nn.Parameter(torch.cat((q, k, v)))
+            self.attn_qkvb = nn.Parameter(torch.cat((initial_biases[0].data, initial_biases[1].data,
+                                                     initial_biases[2].data)))
+            self.attn_ow = initial_weights[3]
+            self.attn_ob = initial_biases[3]
+            self.attn_nw = initial_weights[4]
+            self.attn_nb = initial_biases[4]
+            self.inter_w = initial_weights[5]
+            self.inter_b = initial_biases[5]
+            self.output_w = initial_weights[6]
+            self.output_b = initial_biases[6]
+            self.norm_w = initial_weights[7]
+            self.norm_b = initial_biases[7]
+        if torch.cuda.is_available():
+            N.cuda_lib()   # fail loudly at construction time if the kernel library is missing on a GPU box
+
+    def init_transformer_weights(self, adjust_init_range=False):
+        num_layers = self.config.num_hidden_layers
+        output_std = self.config.initializer_range
+        if adjust_init_range and self.config.local_rank == 0:
+            print("Accounting for accumulation on the residual path")
+        if adjust_init_range:
+            output_std = self.config.initializer_range / math.sqrt(2.0 * num_layers)
+        self.attn_qkvw.data.normal_(mean=0.0, std=self.config.initializer_range)
+        self.attn_qkvb.data.zero_()
+        self.attn_ow.data.normal_(mean=0.0, std=output_std)
+        self.attn_ob.data.zero_()
+        self.attn_nw.data.fill_(1.0)
+        self.attn_nb.data.zero_()
+        self.inter_w.data.normal_(mean=0.0, std=self.config.initializer_range)
+        self.inter_b.data.zero_()
+        self.output_w.data.normal_(mean=0.0, std=output_std)
+        self.output_b.data.zero_()
+        self.norm_w.data.fill_(1.0)
+        self.norm_b.data.zero_()
+
+    # ---- segments (each may be recomputed in backward when the matching *_checkpoint flag is set)
+    def _attention(self, xn, mask2d, B, S):
+        cfg = self.config
+        H, D = cfg.heads, cfg.hidden_size // cfg.heads
+        qkv = K.linear(xn, self.attn_qkvw, None)                                   # [B,S,3h]
+        q, k, v = _split_heads(qkv, self.attn_qkvb, B, S, H, D)                    # [B,H,S,D]
+        scores = matmul(q.reshape(B * H, S, D), k.reshape(B * H, S, D), trans_b=True, alpha=1.0 / math.sqrt(D))
+        probs = masked_softmax(scores.view(B, H, S, S), mask2d)
+        probs = bias_dropout_residual(probs, None, None, cfg.attn_dropout_ratio, self.training, seed=max(cfg.seed, 0))
+        ctx = matmul(probs.reshape(B * H, S, S), v.reshape(B * H, S, D), trans_b=False)   # [BH,S,D]
+        ctx = _merge_heads(ctx.view(B, H, S, D))                                   # [B,S,h]
+        return K.linear(ctx, self.attn_ow, None)
+
+    def _ffn(self, y):
+        cfg = self.config
+        f = K.linear_gelu(y, self.inter_w, self.inter_b)
+        return K.linear(f, self.output_w, None)
+
+    def forward(self, hidden_states, attention_mask=None, head_mask=None, layer_head_mask=None,
+                encoder_hidden_states=None, encoder_attention_mask=None, past_key_value=None,
+                output_attentions=False, grads=None):
+        self.config.training = self.training
+        self.config.is_grad_enabled = torch.is_grad_enabled()
+        cfg = self.config
+        x = hidden_states
+        B, S, h = x.shape
+        # pad the sequence to a multiple of 16 (tensor-core friendly), masking the padded keys out
+        pad = (-S) % 16 if x.is_cuda else 0
+        mask2d = None
+        if attention_mask is not None:
+            mask2d = attention_mask.reshape(B, -1)[:, -S:].to(x.dtype).contiguous()
+        if pad:
+            x = torch.cat((x, torch.zeros(B, pad, h, dtype=x.dtype, device=x.device)), 1)
+            m = mask2d if mask2d is not None else torch.zeros(B, S, dtype=x.dtype, device=x.device)
+            mask2d = torch.cat((m, torch.full((B, pad), -10000.0, dtype=x.dtype, device=x.device)), 1)
+            S = S + pad
+        eps = cfg.layer_norm_eps
+        ck = _maybe_checkpoint
+        if cfg.pre_layer_norm:
+            xn, _ = K.layer_norm(x, self.norm_w, self.norm_b, eps)
+            a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, xn, mask2d, B, S)
+            r1 = bias_dropout_residual(a, self.attn_ob, x, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
+            y, _ = K.layer_norm(r1, self.attn_nw, self.attn_nb, eps)
+            o = ck(cfg.gelu_checkpoint and self.training, self._ffn, y)
+            out = bias_dropout_residual(o, self.output_b, r1, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
+        else:
+            a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, x, mask2d, B, S)
+            s1 = bias_dropout_residual(a, self.attn_ob, x, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
+            r1, _ = K.layer_norm(s1, self.attn_nw, self.attn_nb, eps)
+            o = ck(cfg.gelu_checkpoint and self.training, self._ffn, r1)
+            s2 = bias_dropout_residual(o, self.output_b, r1, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
+            out, _ = K.layer_norm(s2, self.norm_w, self.norm_b, eps)
+        if pad:
+            out = out[:, :S - pad].contiguous()
+        if self.config.huggingface:
+            return (out,)
+        return out
+
+
+def _maybe_checkpoint(enabled, fn, *args):
+    if enabled and torch.is_grad_enabled():
+        from torch.utils.checkpoint import checkpoint as _ckpt
+        return _ckpt(fn, *args, use_reentrant=False)
+    return fn(*args)
+
+
+class _SplitHeadsFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, bias, B, S, H, D):
+        ctx.dims = (B, S, H, D)
+        ctx.has_bias = bias is not None
+        return K.qkv_bias_split_transpose(qkv.contiguous(), bias, B, S, H, D)
+
+    @staticmethod
+    def backward(ctx, dq, dk, dv):
+        B, S, H, D = ctx.dims
+        # [3][B,H,S,D] -> [B,S,3,H,D]
+        stacked = torch.stack((dq, dk, dv), 0).view(3 * B, H, S, D)
+        t = K.transpose_0213(stacked.contiguous()).view(3, B, S, H * D)
+        dqkv = t.permute(1, 2, 0, 3).contiguous().view(B, S, 3 * H * D)
+        db = K.column_sum(dqkv.view(B * S, 3 * H * D)) if ctx.has_bias else None
+        return dqkv, db, None, None, None, None
+
+
+def _split_heads(qkv, bias, B, S, H, D):
+    if _gemm_ok(qkv) and D % 8 == 0:
+        return _SplitHeadsFn.apply(qkv, bias, B, S, H, D)
+    t = qkv.view(B, S, 3, H, D)
+    if bias is not None:
+        t = t + bias.view(1, 1, 3, H, D)
+    return tuple(t[:, :, i].permute(0, 2, 1, 3).contiguous() for i in range(3))
+
+
+def _merge_heads(x):
+    """[B,H,S,D] -> [B,S,H*D]"""
+    B, H, S, D = x.shape
+    if _gemm_ok(x) and D % 8 == 0:
+        return _TransposeFn.apply(x).view(B, S, H * D)
+    return x.permute(0, 2, 1, 3).contiguous().view(B, S, H * D)
+
+
+class _TransposeFn(torch.autograd.Function):
+    """[B,d1,d2,D] <-> [B,d2,d1,D]; its own inverse."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return K.transpose_0213(x.contiguous())
+
+    @staticmethod
+    def backward(ctx, dy):
+        return K.transpose_0213(dy.contiguous())

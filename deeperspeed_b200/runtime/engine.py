@@ -1,0 +1,708 @@
+"""DeepSpeedEngine: wraps an nn.Module with distributed setup, precision handling, optimizer / scheduler wiring
+(ZeRO 1/2/3, FP16 fused/unfused, AMP-less fp32), gradient accumulation, reduction, timers and checkpointing.
+
+Public behaviour per reference deepspeed/runtime/engine.py:102-1915. Differences that matter on B200:
+  * device-agnostic (CUDA+NCCL or CPU+gloo), so the whole engine runs in CI without a GPU;
+  * gradients live in flat arenas (runtime/flat.py): reductions are in-place collectives on arena buckets;
+  * overflow / norm / unscale / clip / cast are fused into device kernels with one host read per step;
+  * timers use CUDA events (no stream serialisation).
+"""
+import hashlib
+import os
+from collections import OrderedDict
+from shutil import copyfile
+
+import torch
+import torch.distributed as dist
+from torch.nn.modules import Module
+
+from ..utils.logging import logger, log_dist
+from ..utils.timer import SynchronizedWallClockTimer, ThroughputTimer
+from ..utils.distributed import init_distributed
+from . import constants as C
+from .constants import (ADAM_OPTIMIZER, ADAMW_OPTIMIZER, LAMB_OPTIMIZER, ONEBIT_ADAM_OPTIMIZER,  # noqa: F401
+                        ONEBIT_LAMB_OPTIMIZER, DEEPSPEED_OPTIMIZERS, ROUTE_TRAIN, ROUTE_EVAL, ROUTE_PREDICT)
+from .config import DeepSpeedConfig
+from .csr_tensor import CSRTensor
+from .dataloader import DeepSpeedDataLoader
+from .fp16.fused_optimizer import FP16_Optimizer
+from .fp16.unfused_optimizer import FP16_UnfusedOptimizer
+from .progressive_layer_drop import ProgressiveLayerDrop
+from . import lr_schedules
+from . import utils as ds_utils
+from .engine_train import TrainStepMixin, _get_global_rank, is_zero_supported_optimizer, split_half_float_double_csr
+from .engine_checkpoint import CheckpointMixin
+
+MEMORY_OPT_ALLREDUCE_SIZE = 500000000
+DeepSpeedOptimizerCallable = None
+
+try:
+    from torch.utils.tensorboard import SummaryWriter as _SummaryWriter
+except Exception:  # pragma: no cover
+    _SummaryWriter = None
+
+
+def _initialize_parameter_parallel_groups(parameter_parallel_size=None):
+    data_parallel_size = int(dist.get_world_size())
+    if parameter_parallel_size is None:
+        parameter_parallel_size = int(data_parallel_size)
+    assert data_parallel_size % parameter_parallel_size == 0, "world size should be divisible by parameter parallel size"
+    rank = dist.get_rank()
+    my_group = None
+    for i in range(dist.get_world_size() // parameter_parallel_size):
+        ranks = range(i * parameter_parallel_size, (i + 1) * parameter_parallel_size)
+        group = torch.distributed.new_group(ranks)
+        if rank in ranks:
+            my_group = group
+    return my_group
+
+
+def print_configuration(args, name):
+    logger.info("{}:".format(name))
+    for arg in sorted(vars(args)):
+        dots = "." * (29 - len(arg))
+        logger.info("  {} {} {}".format(arg, dots, getattr(args, arg)))
+
+
+class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
+    r"""DeepSpeed engine for training."""
+
+    def __init__(self, args, model, optimizer=None, model_parameters=None, training_data=None, lr_scheduler=None,
+                 mpu=None, dist_init_required=None, collate_fn=None, config_params=None, dont_change_device=False):
+        super().__init__()
+        self.dont_change_device = dont_change_device
+        self.client_optimizer = optimizer
+        self.client_model_parameters = model_parameters
+        self.client_lr_scheduler = lr_scheduler
+        self.training_data = training_data
+        self.collate_fn = collate_fn
+        self.mpu = mpu
+        self.data_parallel_group = None
+        self.global_steps = 0
+        self.global_samples = 0
+        self.micro_steps = 0
+        self.skipped_steps = 0
+        self.gradient_average = True
+        self.warn_unscaled_loss = True
+        self.config_params = config_params
+        self.loaded_checkpoint_mp_world_size = None
+        self.loaded_checkpoint_dp_world_size = None
+        self.enable_backward_allreduce = True
+        self.progressive_layer_drop = None
+        self.dist_backend = "nccl" if torch.cuda.is_available() else "gloo"
+        self.store_gradients = False
+        self.store_gradients_cpu = False
+        self.stored_gradients = None
+        self.layer_outputs = {}
+        self._hook_handles = []
+
+        if dist_init_required is None:
+            dist_init_required = not dist.is_initialized()
+        if dist_init_required is False:
+            assert dist.is_initialized() is True, "Torch distributed not initialized. Please set dist_init_required to True or initialize before calling deepspeed.initialize()"
+        else:
+            init_distributed(dist_backend=self.dist_backend)
+
+        self._do_args_sanity_check(args)
+        self._configure_with_arguments(args, mpu)
+        self._do_sanity_check()
+        self._set_distributed_vars()
+
+        if self.tensorboard_enabled() and self.global_rank == 0:
+            self.summary_writer = self.get_summary_writer()
+
+        self._configure_distributed_model(model)
+
+        self.timers = SynchronizedWallClockTimer()
+        self.tput_timer = ThroughputTimer(batch_size=self.train_micro_batch_size_per_gpu(),
+                                          num_workers=self.dp_world_size, steps_per_output=self.steps_per_print(),
+                                          monitor_memory=False)
+        if training_data:
+            self.training_dataloader = self.deepspeed_io(training_data)
+        else:
+            self.training_dataloader = None
+
+        self.optimizer = None
+        self.lr_scheduler = None
+        if model_parameters or optimizer:
+            self._configure_optimizer(optimizer, model_parameters)
+            self._configure_lr_scheduler(lr_scheduler)
+            self._report_progress(0)
+
+        self.csr_tensor_module_names = set()
+        if self.sparse_gradients_enabled():
+            for name, module in self.module.named_modules():
+                if isinstance(module, torch.nn.Embedding):
+                    self.csr_tensor_module_names.add(name + ".weight")
+                    logger.info("Will convert {} to sparse (csr) tensor during training".format(name))
+
+        self.save_non_zero_checkpoint = False
+        self.save_zero_checkpoint = False
+        self._configure_checkpointing(dist_init_required)
+
+        if self.pld_enabled():
+            self.progressive_layer_drop = self._configure_progressive_layer_drop()
+
+        if self.global_rank == 0:
+            self._config.print("DeepSpeedEngine configuration")
+            if self.dump_state():
+                print_configuration(self, "DeepSpeedEngine")
+
+    # ------------------------------------------------------------------ DeeperSpeed extras
+    def register_forward_hook(self, layers_to_hook, layer_name_pattern="transformerlayer"):
+        """Capture the outputs of the selected transformer layers into `self.layer_outputs[idx]`."""
+        for h in self._hook_handles:
+            h.remove()
+        self._hook_handles = []
+        self.layer_outputs = {}
+        idx = 0
+        for name, module in self.module.named_modules():
+            if layer_name_pattern.lower() in module.__class__.__name__.lower():
+                if layers_to_hook == "all" or idx in layers_to_hook:
+                    def _hook(mod, inp, out, _idx=idx):
+                        self.layer_outputs[_idx] = out[0] if isinstance(out, (tuple, list)) else out
+                    self._hook_handles.append(module.register_forward_hook(_hook))
+                idx += 1
+
+    def set_train_batch_size(self, train_batch_size):
+        """Adjust the global batch size by changing gradient accumulation (micro-batch and dp stay fixed)."""
+        if train_batch_size % (self.train_micro_batch_size_per_gpu() * self.dp_world_size) != 0:
+            raise ValueError("Train batch size must be divisible by micro-batch data parallelism")
+        new_gas = train_batch_size // (self.train_micro_batch_size_per_gpu() * self.dp_world_size)
+        self._config.train_batch_size = train_batch_size
+        self._config.gradient_accumulation_steps = new_gas
+
+    # ------------------------------------------------------------------ config accessors
+    def get_batch_info(self):
+        return self.train_batch_size, self.train_micro_batch_size_per_gpu, self.gradient_accumulation_steps
+
+    def checkpoint_tag_validation_enabled(self):
+        return self._config.checkpoint_tag_validation_enabled
+
+    def checkpoint_tag_validation_fail(self):
+        return self._config.checkpoint_tag_validation_fail
+
+    def elasticity_enabled(self):
+        return self._config.elasticity_enabled
+
+    def pld_enabled(self):
+        return self._config.pld_enabled
+
+    def pld_params(self):
+        return self._config.pld_params
+
+    def pld_theta(self):
+        return self.pld_params()[C.PLD_THETA]
+
+    def pld_gamma(self):
+        return self.pld_params()[C.PLD_GAMMA]
+
+    def tensorboard_enabled(self):
+        return self._config.tensorboard_enabled
+
+    def tensorboard_output_path(self):
+        return self._config.tensorboard_output_path
+
+    def tensorboard_job_name(self):
+        return self._config.tensorboard_job_name
+
+    def get_summary_writer(self, name="DeepSpeedJobName", base=os.path.join(os.path.expanduser("~"), "tensorboard")):
+        if _SummaryWriter is None:
+            logger.warning("tensorboard is not installed; tensorboard logging disabled")
+            self._config.tensorboard_enabled = False
+            return None
+        if self.tensorboard_output_path():
+            base_dir = self.tensorboard_output_path()
+            job_name = self.tensorboard_job_name()
+            log_dir = os.path.join(base_dir, job_name)
+        else:
+            if self.tensorboard_job_name():
+                name = self.tensorboard_job_name()
+            if "DLWS_JOB_ID" in os.environ:
+                infra_job_id = os.environ["DLWS_JOB_ID"]
+            elif "DLTS_JOB_ID" in os.environ:
+                infra_job_id = os.environ["DLTS_JOB_ID"]
+            else:
+                infra_job_id = "unknown-job-id"
+            summary_writer_dir_name = os.path.join(infra_job_id, "logs")
+            log_dir = os.path.join(base, summary_writer_dir_name, name)
+        os.makedirs(log_dir, exist_ok=True)
+        return _SummaryWriter(log_dir=log_dir)
+
+    def wall_clock_breakdown(self):
+        return self._config.wall_clock_breakdown
+
+    def flops_profiler_enabled(self):
+        return self._config.flops_profiler_config.enabled
+
+    def flops_profiler_profile_step(self):
+        return self._config.flops_profiler_config.profile_step
+
+    def flops_profiler_module_depth(self):
+        return self._config.flops_profiler_config.module_depth
+
+    def flops_profiler_top_modules(self):
+        return self._config.flops_profiler_config.top_modules
+
+    def flops_profiler_detailed(self):
+        return self._config.flops_profiler_config.detailed
+
+    def memory_breakdown(self):
+        return self._config.memory_breakdown
+
+    def sparse_gradients_enabled(self):
+        return self._config.sparse_gradients_enabled
+
+    def train_batch_size(self):
+        return self._config.train_batch_size
+
+    def train_micro_batch_size_per_gpu(self):
+        return self._config.train_micro_batch_size_per_gpu
+
+    def optimizer_name(self):
+        return self.client_optimizer.__class__.__name__ if self.client_optimizer else self._config.optimizer_name
+
+    def optimizer_params(self):
+        return self._config.optimizer_params
+
+    def optimizer_legacy_fusion(self):
+        return self._config.optimizer_legacy_fusion
+
+    def scheduler_name(self):
+        return self._config.scheduler_name
+
+    def scheduler_params(self):
+        return self._config.scheduler_params
+
+    def zero_optimization(self):
+        return self._config.zero_enabled
+
+    def zero_allow_untested_optimizer(self):
+        return self._config.zero_allow_untested_optimizer
+
+    def zero_reduce_scatter(self):
+        return self._config.zero_config.reduce_scatter
+
+    def zero_overlap_comm(self):
+        return self._config.zero_config.overlap_comm
+
+    def zero_offload_optimizer(self):
+        return self._config.zero_config.offload_optimizer
+
+    def zero_offload_param(self):
+        return self._config.zero_config.offload_param
+
+    def zero_cpu_offload(self):
+        return self._config.zero_config.offload_optimizer is not None
+
+    def zero_sub_group_size(self):
+        return self._config.zero_config.sub_group_size
+
+    def zero_optimization_stage(self):
+        return self._config.zero_optimization_stage
+
+    def zero_reduce_bucket_size(self):
+        return self._config.zero_config.reduce_bucket_size
+
+    def zero_allgather_bucket_size(self):
+        return self._config.zero_config.allgather_bucket_size
+
+    def zero_optimization_partition_gradients(self):
+        return self.zero_optimization_stage() >= C.ZERO_OPTIMIZATION_GRADIENTS
+
+    def zero_optimization_partition_weights(self):
+        return self.zero_optimization_stage() >= C.ZERO_OPTIMIZATION_WEIGHTS
+
+    def zero_contiguous_gradients(self):
+        return self._config.zero_config.contiguous_gradients
+
+    def zero_load_from_fp32_weights(self):
+        return self._config.zero_config.load_from_fp32_weights
+
+    def zero_elastic_checkpoint(self):
+        return self._config.zero_config.elastic_checkpoint
+
+    def zero_max_live_parameters(self):
+        return self._config.zero_config.max_live_parameters
+
+    def zero_max_reuse_distance(self):
+        return self._config.zero_config.max_reuse_distance
+
+    def zero_prefetch_bucket_size(self):
+        return self._config.zero_config.prefetch_bucket_size
+
+    def zero_param_persistence_threshold(self):
+        return self._config.zero_config.param_persistence_threshold
+
+    def zero_gather_fp16_weights_on_model_save(self):
+        return self._config.zero_config.gather_fp16_weights_on_model_save
+
+    def zero_fused_nvlink(self):
+        v = self._config.zero_config.fused_nvlink
+        if v == "auto":
+            return torch.cuda.is_available() and self.dp_world_size > 1 and os.environ.get("DSB_FUSED_NVLINK", "1") != "0"
+        return bool(v)
+
+    def fp16_enabled(self):
+        return self._config.fp16_enabled
+
+    def precision(self):
+        return self._config.precision
+
+    def amp_enabled(self):
+        return self._config.amp_enabled
+
+    def amp_params(self):
+        return self._config.amp_params
+
+    def loss_scale(self):
+        return self._config.loss_scale
+
+    def gradient_accumulation_steps(self):
+        return self._config.gradient_accumulation_steps
+
+    def allreduce_always_fp32(self):
+        return self._config.fp32_allreduce
+
+    def postscale_gradients(self):
+        return not self._config.prescale_gradients
+
+    def gradient_predivide_factor(self):
+        return self._config.gradient_predivide_factor
+
+    def steps_per_print(self):
+        return self._config.steps_per_print
+
+    def zero_allgather_partitions(self):
+        return self._config.zero_config.allgather_partitions
+
+    def dump_state(self):
+        return self._config.dump_state
+
+    def gradient_clipping(self):
+        return self._config.gradient_clipping
+
+    def dynamic_loss_scale(self):
+        return self._config.loss_scale == 0
+
+    def initial_dynamic_scale(self):
+        return self._config.initial_dynamic_scale
+
+    def dynamic_loss_scale_args(self):
+        return self._config.dynamic_loss_scale_args
+
+    def aio_config(self):
+        return self._config.aio_config
+
+    # ------------------------------------------------------------------ setup
+    def _configure_lr_scheduler(self, client_lr_scheduler):
+        lr_scheduler = self._scheduler_from_config(self.optimizer)
+        if lr_scheduler:
+            if self.global_rank == 0:
+                logger.info(f"DeepSpeed using configured LR scheduler = {self.scheduler_name()}")
+            self.lr_scheduler = lr_scheduler
+        else:
+            if self.global_rank == 0:
+                logger.info("DeepSpeed using client LR scheduler")
+            self.lr_scheduler = client_lr_scheduler
+        log_dist(f"DeepSpeed LR Scheduler = {self.lr_scheduler}", ranks=[0])
+
+    def _configure_checkpointing(self, dist_init_required):
+        dp_rank = self.global_rank
+        if self.mpu:
+            dp_rank = self.mpu.get_data_parallel_rank()
+        # only the first data-parallel replica writes module states; ZeRO ranks each write their optimizer shard
+        self.save_non_zero_checkpoint = (dp_rank == 0) or self.zero_optimization_partition_weights()
+        if self.zero_optimization():
+            param_rank = dist.get_rank(group=self.optimizer.dp_process_group) if hasattr(self.optimizer, "dp_process_group") else dp_rank
+            self.save_zero_checkpoint = (param_rank == dp_rank)
+
+    def _scheduler_from_config(self, optimizer):
+        scheduler_name = self.scheduler_name()
+        if scheduler_name is not None:
+            if hasattr(lr_schedules, scheduler_name):
+                scheduler = getattr(lr_schedules, scheduler_name)
+            else:
+                assert hasattr(torch.optim.lr_scheduler, scheduler_name), f"DeepSpeed does not recognize LR scheduler {scheduler_name}"
+                scheduler = getattr(torch.optim.lr_scheduler, scheduler_name)
+                optimizer = lr_schedules.get_torch_optimizer(optimizer)
+            return scheduler(optimizer, **self.scheduler_params())
+        return None
+
+    def _set_distributed_vars(self):
+        if self.local_rank >= 0 and torch.cuda.is_available():
+            torch.cuda.set_device(self.local_rank)
+            self.device = torch.device("cuda", self.local_rank)
+        elif torch.cuda.is_available():
+            self.device = torch.device("cuda")
+        else:
+            self.device = torch.device("cpu")
+        self.world_size = dist.get_world_size()
+        self.global_rank = dist.get_rank()
+
+    def _configure_with_arguments(self, args, mpu):
+        self.local_rank = int(os.environ.get("LOCAL_RANK", getattr(args, "local_rank", 0) if args is not None else 0))
+        if hasattr(args, "local_rank"):
+            args.local_rank = self.local_rank
+        config_file = None
+        if args is not None:
+            config_file = getattr(args, "deepspeed_config", None)
+            if config_file is None and getattr(args, "deepscale_config", None) is not None:
+                config_file = args.deepscale_config
+        self._config = DeepSpeedConfig(config_file, mpu, param_dict=self.config_params)
+
+    def _do_args_sanity_check(self, args):
+        if hasattr(args, "deepscale_config") and args.deepscale_config is not None:
+            logger.warning("************ --deepscale_config is deprecated, please use --deepspeed_config ************")
+            if hasattr(args, "deepspeed_config"):
+                assert args.deepspeed_config is None, "Not sure how to proceed, we were given both a deepscale_config and deepspeed_config"
+            args.deepspeed_config = args.deepscale_config
+        if self.config_params is None:
+            assert args is not None and hasattr(args, "deepspeed_config") and args.deepspeed_config is not None, \
+                "DeepSpeed requires --deepspeed_config to specify configuration file"
+            assert os.path.isfile(args.deepspeed_config), \
+                "DeepSpeed configuration file: {} is not an existing file".format(args.deepspeed_config)
+
+    def _is_supported_optimizer(self, optimizer_name):
+        return optimizer_name in C.DEEPSPEED_OPTIMIZERS or getattr(torch.optim, optimizer_name, None) is not None
+
+    def _do_sanity_check(self):
+        if not self.client_optimizer:
+            if self.optimizer_name() is not None:
+                assert self._is_supported_optimizer(self.optimizer_name()), \
+                    "{} is not a supported DeepSpeed Optimizer".format(self.optimizer_name())
+        if self.optimizer_name() in (C.LAMB_OPTIMIZER, C.ONEBIT_LAMB_OPTIMIZER):
+            assert self.dynamic_loss_scale(), \
+                "DeepSpeed {} optimizer requires dynamic loss scaling".format(self.optimizer_name())
+
+    def _broadcast_model(self):
+        def is_replicated(p):
+            if hasattr(p, "ds_status"):
+                from .zero.partition_parameters import ZeroParamStatus
+                if p.ds_status is not ZeroParamStatus.AVAILABLE:
+                    return False
+            return True
+
+        for p in self.module.parameters():
+            if torch.is_tensor(p) and is_replicated(p):
+                dist.broadcast(p.data, self.broadcast_src_rank, group=self.data_parallel_group)
+
+    def _configure_distributed_model(self, model):
+        self.module = model
+        if self.fp16_enabled() and self.precision() != torch.float32:
+            self.module.to(self.precision())
+        if not self.dont_change_device:
+            self.module.to(self.device)
+        if self.mpu is None:
+            self.data_parallel_group = _initialize_parameter_parallel_groups()
+            self.dp_world_size = dist.get_world_size()
+            self.mp_world_size = 1
+            self.broadcast_src_rank = 0
+        else:
+            self.data_parallel_group = self.mpu.get_data_parallel_group()
+            self.dp_world_size = self.mpu.get_data_parallel_world_size()
+            self.mp_world_size = self.mpu.get_model_parallel_world_size()
+            self.broadcast_src_rank = _get_global_rank(self.mpu.get_data_parallel_group(), 0)
+        if not self.amp_enabled():
+            self._broadcast_model()
+
+    # ------------------------------------------------------------------ optimizer wiring
+    def _configure_optimizer(self, client_optimizer, model_parameters):
+        if client_optimizer is not None:
+            if callable(client_optimizer) and not isinstance(client_optimizer, torch.optim.Optimizer):
+                client_optimizer = client_optimizer(model_parameters)
+            client_optimizer.param_groups[:] = [pg for pg in client_optimizer.param_groups if len(pg["params"]) != 0]
+            basic_optimizer = client_optimizer
+            if self.global_rank == 0:
+                logger.info("Using client Optimizer as basic optimizer")
+        else:
+            basic_optimizer = self._configure_basic_optimizer(model_parameters)
+            if self.global_rank == 0:
+                logger.info("Using DeepSpeed Optimizer param name {} as basic optimizer".format(self.optimizer_name()))
+        if self.global_rank == 0:
+            logger.info("DeepSpeed Basic Optimizer = {}".format(basic_optimizer.__class__.__name__))
+
+        if self.zero_optimization():
+            assert not self.amp_enabled(), "Amp and ZeRO are not currently compatible, please use (legacy) fp16 mode which performs similar to amp opt_mode=O2"
+            if not is_zero_supported_optimizer(basic_optimizer):
+                assert self.zero_allow_untested_optimizer(), \
+                    'You are using an untested ZeRO Optimizer. Please add <"zero_allow_untested_optimizer": true> in the configuration file to use it.'
+                if self.global_rank == 0:
+                    logger.warning("**** You are using ZeRO with an untested optimizer, proceed with caution *****")
+            self.optimizer = self._configure_zero_optimizer(basic_optimizer)
+        elif self.amp_enabled():
+            raise RuntimeError("apex AMP is not available in this environment; use the fp16 block (fp16 or bfloat16) "
+                               "which gives the O2-style master-weight regime")
+        elif self.fp16_enabled() and self.precision() != torch.float32:
+            self.optimizer = self._configure_fp16_optimizer(basic_optimizer)
+        else:
+            self.optimizer = basic_optimizer
+        log_dist("DeepSpeed Final Optimizer = {}".format(self.optimizer_name()), ranks=[0])
+
+    def _configure_basic_optimizer(self, model_parameters):
+        optimizer_parameters = dict(self.optimizer_params() or {})
+        if "max_grad_norm" in optimizer_parameters:
+            raise ValueError("'max_grad_norm' is not supported as an optimizer parameter, please switch to using the "
+                             "deepspeed parameter 'gradient_clipping' see: "
+                             "https://www.deepspeed.ai/docs/config-json/#gradient-clipping for more details")
+        name = self.optimizer_name()
+        if name in (C.ADAM_OPTIMIZER, C.ADAMW_OPTIMIZER):
+            torch_adam = optimizer_parameters.pop(C.TORCH_ADAM_PARAM, False)
+            adam_w_mode = optimizer_parameters.pop(C.ADAM_W_MODE, C.ADAM_W_MODE_DEFAULT)
+            # "adamw" always means decoupled decay; "adam" follows adam_w_mode (default True, as in the reference)
+            effective_adam_w_mode = name == C.ADAMW_OPTIMIZER or adam_w_mode
+            if torch_adam:
+                if not effective_adam_w_mode:
+                    optimizer = torch.optim.Adam(model_parameters, **optimizer_parameters)
+                else:
+                    optimizer = torch.optim.AdamW(model_parameters, **optimizer_parameters)
+            elif self.zero_cpu_offload():
+                from ..ops.adam import DeepSpeedCPUAdam
+                optimizer = DeepSpeedCPUAdam(model_parameters, **optimizer_parameters, adamw_mode=effective_adam_w_mode)
+            else:
+                from ..ops.adam import FusedAdam
+                optimizer = FusedAdam(model_parameters, **optimizer_parameters, adam_w_mode=effective_adam_w_mode)
+        elif name == C.LAMB_OPTIMIZER:
+            from ..ops.lamb import FusedLamb
+            optimizer = FusedLamb(model_parameters, **optimizer_parameters)
+        elif name == C.ONEBIT_ADAM_OPTIMIZER:
+            from .fp16.onebit.adam import OnebitAdam
+            optimizer = OnebitAdam(model_parameters, self, **optimizer_parameters)
+            if not self.fp16_enabled():
+                logger.warning("Currently the convergence of 1-bit Adam is only verified under FP16")
+        elif name == C.ONEBIT_LAMB_OPTIMIZER:
+            from .fp16.onebit.lamb import OnebitLamb
+            optimizer = OnebitLamb(model_parameters, self, **optimizer_parameters)
+            if not self.fp16_enabled():
+                logger.warning("Currently the convergence of 1-bit Lamb is only verified under FP16")
+        else:
+            torch_optimizer = getattr(torch.optim, name)
+            optimizer = torch_optimizer(model_parameters, **optimizer_parameters)
+        return optimizer
+
+    def _configure_fp16_optimizer(self, optimizer):
+        initial_dynamic_scale = self.initial_dynamic_scale()
+        dynamic_loss_args = self.dynamic_loss_scale_args()
+        clip_grad = self.gradient_clipping()
+        from ..ops.adam import FusedAdam
+        is_bf16 = self.precision() == torch.bfloat16
+        if isinstance(optimizer, FusedAdam) or self.optimizer_name() == C.ONEBIT_ADAM_OPTIMIZER:
+            if self.dynamic_loss_scale() and not is_bf16:
+                log_dist("Creating fp16 optimizer with dynamic loss scale", ranks=[0])
+                optimizer = FP16_Optimizer(optimizer, dynamic_loss_scale=True, initial_dynamic_scale=initial_dynamic_scale,
+                                           dynamic_loss_args=dynamic_loss_args, mpu=self.mpu, clip_grad=clip_grad,
+                                           fused_adam_legacy=self.optimizer_legacy_fusion(), timers=None,
+                                           dp_process_group=self.data_parallel_group,
+                                           fp32_allreduce=self.allreduce_always_fp32())
+            else:
+                log_dist("Creating fp16 optimizer with static loss scale: {}".format(self.loss_scale()), ranks=[0])
+                optimizer = FP16_Optimizer(optimizer, static_loss_scale=1.0 if is_bf16 else self.loss_scale(),
+                                           mpu=self.mpu, clip_grad=clip_grad,
+                                           fused_adam_legacy=self.optimizer_legacy_fusion(),
+                                           dp_process_group=self.data_parallel_group,
+                                           fp32_allreduce=self.allreduce_always_fp32())
+        else:
+            log_dist("Creating fp16 unfused optimizer with dynamic loss scale", ranks=[0])
+            optimizer = FP16_UnfusedOptimizer(optimizer, static_loss_scale=1.0 if is_bf16 else self.loss_scale(),
+                                              dynamic_loss_scale=self.dynamic_loss_scale() and not is_bf16,
+                                              dynamic_loss_args=dynamic_loss_args, mpu=self.mpu, clip_grad=clip_grad,
+                                              fused_lamb_legacy=self.optimizer_name() == C.LAMB_OPTIMIZER)
+        return optimizer
+
+    def _configure_zero_optimizer(self, optimizer):
+        zero_stage = self.zero_optimization_stage()
+        log_dist("Creating fp16 ZeRO stage {} optimizer".format(zero_stage), ranks=[0])
+        assert not self.allreduce_always_fp32() or self.precision() == torch.bfloat16 or True
+        common = dict(static_loss_scale=self.loss_scale(), dynamic_loss_scale=self.dynamic_loss_scale(),
+                      dynamic_loss_args=self.dynamic_loss_scale_args(), clip_grad=self.gradient_clipping(),
+                      dp_process_group=self.data_parallel_group, mpu=self.mpu,
+                      elastic_checkpoint=self.zero_elastic_checkpoint(), precision=self.precision(),
+                      postscale_gradients=self.postscale_gradients(),
+                      gradient_predivide_factor=self.gradient_predivide_factor())
+        if zero_stage == C.ZERO_OPTIMIZATION_OPTIMIZER_STATES:
+            assert self.zero_reduce_scatter(), "Stage 1 only supports reduce scatter mode"
+            from .zero.stage1 import FP16_DeepSpeedZeroOptimizer_Stage1
+            optimizer = FP16_DeepSpeedZeroOptimizer_Stage1(
+                optimizer, all_gather_partitions=self.zero_allgather_partitions(),
+                allgather_size=self.zero_allgather_bucket_size(), max_elements_per_comm=self.zero_reduce_bucket_size(),
+                fp32_allreduce=self.allreduce_always_fp32() and self.precision() != torch.bfloat16,
+                fused_nvlink=self.zero_fused_nvlink(), **common)
+        elif zero_stage == C.ZERO_OPTIMIZATION_GRADIENTS:
+            from .zero.stage2 import FP16_DeepSpeedZeroOptimizer
+            off = self.zero_offload_optimizer()
+            optimizer = FP16_DeepSpeedZeroOptimizer(
+                optimizer, timers=self.timers, contiguous_gradients=self.zero_contiguous_gradients(),
+                reduce_bucket_size=self.zero_reduce_bucket_size(), allgather_bucket_size=self.zero_allgather_bucket_size(),
+                reduce_scatter=self.zero_reduce_scatter(), overlap_comm=self.zero_overlap_comm(),
+                cpu_offload=self.zero_cpu_offload(), pin_memory=True if off is None else (off.get("pin_memory", False) or True),
+                allreduce_always_fp32=self.allreduce_always_fp32() and self.precision() != torch.bfloat16,
+                gradient_accumulation_steps=self.gradient_accumulation_steps(),
+                fused_nvlink=self.zero_fused_nvlink(), **common)
+        elif zero_stage == C.ZERO_OPTIMIZATION_WEIGHTS:
+            from .zero.stage3 import FP16_DeepSpeedZeroOptimizer_Stage3
+            optimizer = FP16_DeepSpeedZeroOptimizer_Stage3(
+                self.module, optimizer, timers=self.timers, static_loss_scale=self.loss_scale(),
+                dynamic_loss_scale=self.dynamic_loss_scale(), dynamic_loss_args=self.dynamic_loss_scale_args(),
+                clip_grad=self.gradient_clipping(), contiguous_gradients=self.zero_contiguous_gradients(),
+                reduce_bucket_size=self.zero_reduce_bucket_size(), prefetch_bucket_size=self.zero_prefetch_bucket_size(),
+                max_reuse_distance=self.zero_max_reuse_distance(), max_live_parameters=self.zero_max_live_parameters(),
+                param_persistence_threshold=self.zero_param_persistence_threshold(),
+                dp_process_group=self.data_parallel_group, reduce_scatter=self.zero_reduce_scatter(),
+                overlap_comm=self.zero_overlap_comm(), offload_optimizer_config=self.zero_offload_optimizer(),
+                offload_param_config=self.zero_offload_param(), sub_group_size=self.zero_sub_group_size(),
+                mpu=self.mpu, postscale_gradients=self.postscale_gradients(),
+                gradient_predivide_factor=self.gradient_predivide_factor(),
+                gradient_accumulation_steps=self.gradient_accumulation_steps(), aio_config=self.aio_config(),
+                precision=self.precision())
+        else:
+            raise NotImplementedError("ZeRO stage {} not implemented".format(zero_stage))
+        return optimizer
+
+    def _configure_progressive_layer_drop(self):
+        return ProgressiveLayerDrop(theta=self.pld_theta(), gamma=self.pld_gamma())
+
+    # ------------------------------------------------------------------ data
+    def deepspeed_io(self, dataset, batch_size=None, route=C.ROUTE_TRAIN, pin_memory=True, data_sampler=None,
+                     collate_fn=None, num_local_io_workers=None):
+        if not isinstance(dataset, torch.utils.data.Dataset):
+            raise ValueError("Training data must be a torch Dataset")
+        if data_sampler is None and route in (C.ROUTE_PREDICT, C.ROUTE_EVAL):
+            data_sampler = torch.utils.data.SequentialSampler(dataset)
+        if batch_size is None:
+            batch_size = self.train_micro_batch_size_per_gpu()
+        if collate_fn is None:
+            collate_fn = self.collate_fn
+        deepspeed_io_timer = self.tput_timer if route == C.ROUTE_TRAIN else None
+        if self.mpu is not None:
+            dp_world, dp_rank = self.mpu.get_data_parallel_world_size(), self.mpu.get_data_parallel_rank()
+        else:
+            dp_world, dp_rank = self.dp_world_size, dist.get_rank(group=self.data_parallel_group)
+        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory,
+                                   collate_fn=collate_fn, local_rank=self.local_rank, tput_timer=deepspeed_io_timer,
+                                   num_local_io_workers=num_local_io_workers, data_sampler=data_sampler,
+                                   data_parallel_world_size=dp_world, data_parallel_rank=dp_rank)
+
+    def train(self, mode=True):
+        self.warn_unscaled_loss = True
+        self.module.train(mode)
+
+    def eval(self):
+        self.warn_unscaled_loss = True
+        self.module.train(False)
+
+    def _scale_loss(self, prescaled_loss):
+        if isinstance(prescaled_loss, torch.Tensor):
+            scaled_loss = prescaled_loss / self.gradient_accumulation_steps()
+        elif isinstance(prescaled_loss, (tuple, list)):
+            scaled_loss = []
+            for l in prescaled_loss:
+                if isinstance(l, torch.Tensor):
+                    scaled_loss.append(l / self.gradient_accumulation_steps())
+                else:
+                    scaled_loss.append(l)
+        else:
+            scaled_loss = prescaled_loss
+            if self.warn_unscaled_loss:
+                logger.warning(f"DeepSpeed unable to scale loss because of type: {type(prescaled_loss)}")
+                self.warn_unscaled_loss = False
+        return scaled_loss

@@ -1,0 +1,75 @@
+"""Pipeline point-to-point transport.
+
+NCCL send/recv between adjacent stage ranks, stream-ordered (asynchronous to the host), so the next kernels are
+queued while a transfer is in flight; on CPU/gloo the same calls are blocking. The reference emulates p2p with a
+2-rank broadcast and forces it synchronous (reference deepspeed/runtime/pipe/p2p.py:31-61); the pair groups are
+still built for API parity (`_get_send_recv_group`)."""
+import torch
+import torch.distributed as dist
+
+_groups = None
+_grid = None
+
+
+def init_process_groups(grid):
+    """Create the 2-rank neighbour groups (collective: every rank walks the same list)."""
+    global _groups, _grid
+    _grid = grid
+    assert _grid.pipe_parallel_size > 1, "There is no pipeline parallelism"
+    _groups = [dist.new_group(ranks=group) for group in _grid.p2p_groups]
+
+
+def _is_valid_send_recv(src_stage, dest_stage):
+    first_stage, last_stage = 0, _grid.pipe_parallel_size - 1
+    assert abs(src_stage - dest_stage) == 1 or (src_stage == first_stage and dest_stage == last_stage) or \
+        (src_stage == last_stage and dest_stage == first_stage), \
+        "Functionality currently limited to send and receive between adjacent ranks only"
+
+
+def _wire(tensor, fp32_comm):
+    return tensor.float() if (fp32_comm and tensor.is_floating_point() and tensor.dtype != torch.float32) else tensor
+
+
+def send(tensor, dest_stage, async_op=False, fp32_comm=False):
+    src_stage = _grid.get_stage_id()
+    _is_valid_send_recv(src_stage, dest_stage)
+    dst = _grid.stage_to_global(stage_id=dest_stage)
+    t = _wire(tensor, fp32_comm).contiguous()
+    if async_op:
+        return dist.isend(t, dst=dst)
+    dist.send(t, dst=dst)
+    return None
+
+
+def recv(tensor, src_stage, async_op=False, fp32_comm=False):
+    dest_stage = _grid.get_stage_id()
+    _is_valid_send_recv(src_stage, dest_stage)
+    src = _grid.stage_to_global(stage_id=src_stage)
+    if fp32_comm and tensor.is_floating_point() and tensor.dtype != torch.float32:
+        tmp = torch.empty_like(tensor, dtype=torch.float32)
+        dist.recv(tmp, src=src)
+        tensor.copy_(tmp)
+        return None
+    if async_op:
+        return dist.irecv(tensor, src=src)
+    dist.recv(tensor, src=src)
+    return None
+
+
+def barrier(stage_id):
+    """Barrier with the next-stage neighbour."""
+    group_id = _grid.stage_to_global(stage_id=stage_id)
+    dist.barrier(group=_groups[group_id])
+
+
+def _get_send_recv_group(src_stage, dest_stage):
+    """Pair group keyed by the lower stage's rank, except the wrap-around pair keyed by the last stage."""
+    first_stage, last_stage = 0, _grid.pipe_parallel_size - 1
+    if (src_stage == first_stage and dest_stage == last_stage) or (dest_stage == first_stage and src_stage == last_stage):
+        stage_id = last_stage
+    elif src_stage > dest_stage:
+        stage_id = dest_stage
+    else:
+        stage_id = src_stage
+    group_id = _grid.stage_to_global(stage_id=stage_id)
+    return _groups[group_id]

@@ -1,0 +1,271 @@
+"""Cartesian process topology and the pipeline/data/model process-group grid (the `mpu` interface).
+Behaviour per reference deepspeed/runtime/pipe/topology.py:13-468; rank maths is plain row-major arithmetic here
+instead of an enumerated namedtuple->rank dictionary."""
+from collections import namedtuple
+from itertools import product as cartesian_product
+
+import torch.distributed as dist
+
+from ...utils.logging import logger
+
+
+class ProcessTopology:
+    """Maps n-dimensional cartesian coordinates to linear ranks (row-major: last axis varies fastest)."""
+
+    def __init__(self, axes, dims):
+        self.axes = list(axes)
+        self.dims = list(dims)
+        self.ProcessCoord = namedtuple("ProcessCoord", axes)
+        self.mapping = {}
+        for global_rank, coord in enumerate(cartesian_product(*[range(d) for d in dims])):
+            self.mapping[self.ProcessCoord(**dict(zip(axes, coord)))] = global_rank
+
+    def get_rank(self, **coord_kwargs):
+        if len(coord_kwargs) != len(self.axes):
+            raise ValueError("get_rank() does not support slices. Use filter_match())")
+        key = self.ProcessCoord(**coord_kwargs)
+        assert key in self.mapping, f"key {coord_kwargs} invalid"
+        return self.mapping[key]
+
+    def get_axis_names(self):
+        return self.axes
+
+    def get_rank_repr(self, rank, omit_axes=("data", "pipe"), inner_sep="_", outer_sep="-"):
+        omit_axes = frozenset(omit_axes)
+        axes = [a for a in self.get_axis_names() if a not in omit_axes]
+        names = []
+        for ax in axes:
+            ax_rank = getattr(self.get_coord(rank=rank), ax)
+            names.append(f"{ax}{inner_sep}{ax_rank:02d}")
+        return outer_sep.join(names)
+
+    def get_dim(self, axis):
+        if axis not in self.axes:
+            return 0
+        return self.dims[self.axes.index(axis)]
+
+    def get_coord(self, rank):
+        for coord, idx in self.mapping.items():
+            if idx == rank:
+                return coord
+        raise ValueError(f"rank {rank} not found in topology.")
+
+    def get_axis_comm_lists(self, axis):
+        """Lists of ranks that differ only along `axis` (the communicator groups of that axis)."""
+        if axis not in self.axes:
+            return []
+        other_axes = [a for a in self.axes if a != axis]
+        lists = []
+        for coord in cartesian_product(*[range(self.get_dim(a)) for a in other_axes]):
+            other_keys = dict(zip(other_axes, coord))
+            lists.append([self.mapping[self.ProcessCoord(**other_keys, **{axis: i})]
+                          for i in range(self.get_dim(axis))])
+        return lists
+
+    def filter_match(self, **filter_kwargs):
+        def _match(coord):
+            return all(getattr(coord, k) == v for k, v in filter_kwargs.items())
+
+        return [self.mapping[c] for c in filter(_match, self.mapping.keys())]
+
+    def get_axis_list(self, axis, idx):
+        axis_num = self.axes.index(axis)
+        return [self.mapping[k] for k in self.mapping.keys() if k[axis_num] == idx]
+
+    def world_size(self):
+        return len(self.mapping)
+
+    def __str__(self):
+        return str(self.mapping)
+
+
+def _prime_factors(N):
+    if N <= 0:
+        raise ValueError("Values must be strictly positive.")
+    primes = []
+    while N != 1:
+        for candidate in range(2, N + 1):
+            if N % candidate == 0:
+                primes.append(candidate)
+                N //= candidate
+                break
+    return primes
+
+
+class PipeDataParallelTopology(ProcessTopology):
+    """pipe x data: DP ranks of a stage are adjacent (gradient reductions stay on neighbouring GPUs)."""
+
+    def __init__(self, num_pp, num_dp):
+        super().__init__(axes=["pipe", "data"], dims=[num_pp, num_dp])
+
+
+class PipeModelDataParallelTopology(ProcessTopology):
+    """3-D pipe x data x model."""
+
+    def __init__(self, num_pp, num_mp, num_dp):
+        super().__init__(axes=["pipe", "data", "model"], dims=[num_pp, num_dp, num_mp])
+
+
+class PipelineParallelGrid:
+    """Builds every process group a pipeline engine needs and implements the Megatron-style `mpu` interface.
+
+    Groups: data-parallel (same pipe/model coords), pipe (same data/model), "ds model" (= all ranks sharing my data
+    coordinate; checkpoint mp_rank is the index inside it), slice (tensor-parallel) and 2-rank p2p neighbours."""
+
+    def __init__(self, topology=None, process_group=None):
+        self.global_rank = dist.get_rank()
+        self.world_size = dist.get_world_size()
+        if topology is not None:
+            self._topo = topology
+        else:
+            num_pp, num_dp = 1, 1
+            for idx, prime in enumerate(_prime_factors(self.world_size)):
+                if idx % 2 == 0:
+                    num_pp *= prime
+                else:
+                    num_dp *= prime
+            self._topo = PipeDataParallelTopology(num_dp=num_dp, num_pp=num_pp)
+        self.data_parallel_size = max(self._topo.get_dim("data"), 1)
+        self.pipe_parallel_size = max(self._topo.get_dim("pipe"), 1)
+        self.model_parallel_size = max(self._topo.get_dim("model"), 1)
+        self.slice_parallel_size = self.model_parallel_size
+        assert self._is_grid_valid(), "Invalid Grid"
+
+        self.stage_id = self.get_stage_id()
+        self.data_parallel_id = self.get_data_parallel_id()
+
+        # "ds model" groups: everything except the data axis
+        self.ds_model_proc_group = None
+        self.ds_model_rank = -1
+        for dp in range(self.data_parallel_size):
+            ranks = sorted(self._topo.get_axis_list(axis="data", idx=dp))
+            proc_group = dist.new_group(ranks=ranks)
+            if self.global_rank in ranks:
+                self.ds_model_proc_group = proc_group
+                self.ds_model_world_size = len(ranks)
+                self.ds_model_rank = ranks.index(self.global_rank)
+        assert self.ds_model_rank > -1 and self.ds_model_proc_group is not None
+
+        self.dp_group = []
+        self.dp_groups = self._topo.get_axis_comm_lists("data")
+        for g in self.dp_groups:
+            proc_group = dist.new_group(ranks=g)
+            if self.global_rank in g:
+                self.dp_group = g
+                self.dp_proc_group = proc_group
+
+        self.is_first_stage = self.stage_id == 0
+        self.is_last_stage = self.stage_id == (self.pipe_parallel_size - 1)
+
+        self.p2p_groups = self._build_p2p_groups()
+
+        self.pp_group = []
+        self.pp_proc_group = None
+        self.pipe_groups = self._topo.get_axis_comm_lists("pipe")
+        for ranks in self.pipe_groups:
+            proc_group = dist.new_group(ranks=ranks)
+            if self.global_rank in ranks:
+                self.pp_group = ranks
+                self.pp_proc_group = proc_group
+        assert self.pp_proc_group is not None
+
+        # slice (tensor-parallel) groups
+        self.slice_group = None
+        self.slice_proc_group = None
+        if "model" in self._topo.get_axis_names():
+            self.mp_group = []
+            self.model_groups = self._topo.get_axis_comm_lists("model")
+            for g in self.model_groups:
+                proc_group = dist.new_group(ranks=g)
+                if self.global_rank in g:
+                    self.slice_group = g
+                    self.slice_proc_group = proc_group
+        else:
+            self.slice_group = [self.global_rank]
+            self.slice_proc_group = dist.new_group(ranks=[self.global_rank]) if self.world_size > 1 else None
+            self.model_groups = [[r] for r in range(self.world_size)]
+            if self.world_size > 1:
+                # every rank must take part in every new_group call
+                for r in range(self.world_size):
+                    if r != self.global_rank:
+                        dist.new_group(ranks=[r])
+
+    def get_stage_id(self):
+        return self._topo.get_coord(rank=self.global_rank).pipe
+
+    def get_data_parallel_id(self):
+        return self._topo.get_coord(rank=self.global_rank).data
+
+    def _build_p2p_groups(self):
+        """[rank, next-stage rank] pairs, including the wrap-around from the last stage to the first."""
+        comm_lists = self._topo.get_axis_comm_lists("pipe")
+        p2p_lists = []
+        for rank in range(self.world_size):
+            for l in comm_lists:
+                assert len(l) == self.pipe_parallel_size
+                if rank in l:
+                    idx = l.index(rank)
+                    buddy_rank = l[(idx + 1) % self.pipe_parallel_size]
+                    p2p_lists.append([rank, buddy_rank])
+                    break
+        assert len(p2p_lists) == self.world_size
+        return p2p_lists
+
+    def _is_grid_valid(self):
+        ranks = 1
+        for ax in self._topo.get_axis_names():
+            ranks *= self._topo.get_dim(ax)
+        return ranks == dist.get_world_size()
+
+    def stage_to_global(self, stage_id, **kwargs):
+        me = self._topo.get_coord(self.global_rank)
+        transform = me._replace(pipe=stage_id, **kwargs)._asdict()
+        return self._topo.get_rank(**transform)
+
+    def topology(self):
+        return self._topo
+
+    # ---- mpu interface
+    def get_global_rank(self):
+        return self.global_rank
+
+    def get_pipe_parallel_rank(self):
+        return self.stage_id
+
+    def get_pipe_parallel_world_size(self):
+        return self.pipe_parallel_size
+
+    def get_pipe_parallel_group(self):
+        return self.pp_proc_group
+
+    def get_data_parallel_rank(self):
+        return self.data_parallel_id
+
+    def get_data_parallel_world_size(self):
+        return self.data_parallel_size
+
+    def get_data_parallel_group(self):
+        return self.dp_proc_group
+
+    def get_data_parallel_src_rank(self):
+        return self.dp_group[0]
+
+    def get_model_parallel_rank(self):
+        return self.ds_model_rank
+
+    def get_model_parallel_world_size(self):
+        return self.ds_model_world_size
+
+    def get_model_parallel_group(self):
+        return self.ds_model_proc_group
+
+    def get_slice_parallel_rank(self):
+        if "model" in self._topo.get_axis_names():
+            return self._topo.get_coord(rank=self.global_rank).model
+        return 0
+
+    def get_slice_parallel_world_size(self):
+        return self.slice_parallel_size
+
+    def get_slice_parallel_group(self):
+        return self.slice_proc_group

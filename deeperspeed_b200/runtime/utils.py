@@ -1,0 +1,482 @@
+"""Runtime helpers: overflow check, grad/weight norms (MP-aware), partitioning, PartitionedTensor, memory reports,
+GradientNoiseScale. API per reference deepspeed/runtime/utils.py:65-674.
+
+B200-native difference: norms and overflow are computed by one fused sum-of-squares + non-finite-flag kernel per
+flat buffer with the results left on the device; a single tiny all-reduce and one D2H read replace the reference's
+per-tensor `float(x.float().sum())` host syncs (reference utils.py:157-175)."""
+import math
+from bisect import bisect_left
+from math import inf
+
+import torch
+import torch.distributed as dist
+
+from ..utils.logging import logger
+from ..ops import kernels as K
+
+
+def noop_decorator(func):
+    return func
+
+
+def ensure_directory_exists(filename):
+    import os
+    os.makedirs(os.path.dirname(filename), exist_ok=True)
+
+
+def set_random_seed(seed):
+    import random
+    import numpy
+    random.seed(seed)
+    numpy.random.seed(seed)
+    torch.manual_seed(seed)
+
+
+def move_to_device(item, device):
+    if torch.is_tensor(item):
+        return item.to(device)
+    if isinstance(item, list):
+        return [move_to_device(v, device) for v in item]
+    if isinstance(item, tuple):
+        return tuple(move_to_device(v, device) for v in item)
+    if isinstance(item, dict):
+        return {k: move_to_device(v, device) for k, v in item.items()}
+    return item
+
+
+def is_model_parallel_parameter(p):
+    return hasattr(p, "model_parallel") and p.model_parallel
+
+
+def _mp_rank(mpu):
+    return mpu.get_model_parallel_rank() if mpu is not None else 0
+
+
+def _counts_for_norm(p, mpu):
+    """A replicated (non-MP) parameter is counted only on MP rank 0 (reference utils.py:226-229)."""
+    return mpu is None or is_model_parallel_parameter(p) or _mp_rank(mpu) == 0
+
+
+class CheckOverflow:
+    """Checks for inf/nan over model gradients, agreeing across MP / DP ranks with a MAX all-reduce."""
+
+    def __init__(self, param_groups=None, mpu=None, zero_reduce_scatter=False):
+        self.mpu = mpu
+        self.params = [] if param_groups else None
+        self.zero_reduce_scatter = zero_reduce_scatter
+        if param_groups:
+            for group in param_groups:
+                for param in group:
+                    self.params.append(param)
+
+    def check_using_norm(self, norm_group, reduce_overflow=True):
+        overflow = -1 in norm_group
+        if self.mpu is not None or reduce_overflow:
+            dev = "cuda" if torch.cuda.is_available() and dist.get_backend() == "nccl" else "cpu"
+            t = torch.tensor([float(overflow)], device=dev)
+            if self.mpu is not None:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.mpu.get_model_parallel_group())
+            elif reduce_overflow:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            overflow = t[0].item()
+        return bool(overflow)
+
+    def check(self, param_groups=None):
+        params = []
+        if param_groups is None:
+            params = self.params
+        else:
+            assert param_groups is not None, "self.params and param_groups both cannot be none"
+            for group in param_groups:
+                for param in group:
+                    params.append(param)
+        return self.has_overflow(params)
+
+    def has_overflow_serial(self, params):
+        grads = [p.grad for p in params if p.grad is not None]
+        if not grads:
+            return False
+        flag = torch.zeros(1, dtype=torch.int32, device=grads[0].device)
+        out = torch.zeros(1, dtype=torch.float32, device=grads[0].device)
+        for g in grads:
+            if g.is_contiguous():
+                K.sumsq(g.view(-1), out=out, flag=flag, accumulate=True)
+            else:
+                K.sumsq(g.contiguous().view(-1), out=out, flag=flag, accumulate=True)
+        return bool(flag.item()) or not math.isfinite(out.item())
+
+    def has_overflow(self, params):
+        overflow = self.has_overflow_serial(params)
+        if not (dist.is_available() and dist.is_initialized()):
+            return overflow
+        dev = params[0].device if params else torch.device("cpu")
+        t = torch.tensor([float(overflow)], device=dev)
+        if self.zero_reduce_scatter:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=dist.group.WORLD)
+        elif self.mpu is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.mpu.get_model_parallel_group())
+        return bool(t[0].item())
+
+    @staticmethod
+    def _has_inf_or_nan(x, i=None):
+        s = float(x.float().sum())
+        return s in (float("inf"), -float("inf")) or s != s
+
+
+def _has_inf_or_nan(x):
+    return CheckOverflow._has_inf_or_nan(x)
+
+
+def get_grad_norm(parameters, norm_type=2, mpu=None):
+    """Global gradient norm across model-parallel ranks; returns -1 for inf/nan (treated as overflow upstream)."""
+    if isinstance(parameters, torch.Tensor):
+        parameters = [parameters]
+    parameters = [p for p in parameters if p.grad is not None]
+    if not parameters:
+        return 0.0
+    dev = parameters[0].device
+    norm_type = float(norm_type)
+    if norm_type == inf:
+        total = torch.stack([p.grad.detach().abs().max().float() for p in parameters]).max().reshape(1)
+        if mpu is not None:
+            dist.all_reduce(total, op=dist.ReduceOp.MAX, group=mpu.get_model_parallel_group())
+        total_norm = total[0].item()
+    else:
+        if norm_type == 2.0:
+            acc = torch.zeros(1, dtype=torch.float32, device=dev)
+            for p in parameters:
+                if _counts_for_norm(p, mpu):
+                    g = p.grad.detach()
+                    K.sumsq(g.view(-1) if g.is_contiguous() else g.contiguous().view(-1), out=acc, accumulate=True)
+        else:
+            acc = torch.zeros(1, dtype=torch.float32, device=dev)
+            for p in parameters:
+                if _counts_for_norm(p, mpu):
+                    acc += p.grad.detach().float().norm(norm_type) ** norm_type
+        if mpu is not None:
+            dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=mpu.get_model_parallel_group())
+        total_norm = acc[0].item() ** (1.0 / norm_type)
+    if total_norm == float("inf") or total_norm == -float("inf") or total_norm != total_norm:
+        total_norm = -1
+    return total_norm
+
+
+def get_weight_norm(parameters, norm_type=2, mpu=None):
+    if isinstance(parameters, torch.Tensor):
+        parameters = [parameters]
+    parameters = list(parameters)
+    if not parameters:
+        return 0.0
+    dev = parameters[0].device
+    norm_type = float(norm_type)
+    if norm_type == inf:
+        total = torch.stack([p.detach().abs().max().float() for p in parameters]).max().reshape(1)
+        if mpu is not None:
+            dist.all_reduce(total, op=dist.ReduceOp.MAX, group=mpu.get_model_parallel_group())
+        total_norm = total[0].item()
+    else:
+        acc = torch.zeros(1, dtype=torch.float32, device=dev)
+        for p in parameters:
+            if _counts_for_norm(p, mpu):
+                acc += p.detach().float().norm(norm_type) ** norm_type
+        if mpu is not None:
+            dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=mpu.get_model_parallel_group())
+        total_norm = acc[0].item() ** (1.0 / norm_type)
+    if total_norm == float("inf") or total_norm == -float("inf") or total_norm != total_norm:
+        total_norm = -1
+    return total_norm
+
+
+def clip_grad_norm_(parameters, max_norm, norm_type=2, mpu=None):
+    """MP-aware clip (fp32 / AMP path)."""
+    if isinstance(parameters, torch.Tensor):
+        parameters = [parameters]
+    parameters = [p for p in parameters if p.grad is not None]
+    total_norm = get_grad_norm(parameters, norm_type, mpu)
+    if total_norm in (-1,):
+        return total_norm
+    clip_coef = float(max_norm) / (total_norm + 1e-6)
+    if clip_coef < 1:
+        for p in parameters:
+            p.grad.detach().mul_(clip_coef)
+    return total_norm
+
+
+# ----------------------------------------------------------------------------------------------- partitioning
+def is_prime(n):
+    return n > 1 and all(n % i for i in range(2, int(math.sqrt(n)) + 1))
+
+
+def prime_factors(n):
+    out, d = [], 2
+    while d * d <= n:
+        while n % d == 0:
+            out.append(d)
+            n //= d
+        d += 1
+    if n > 1:
+        out.append(n)
+    return out
+
+
+def prefix_sum_inc(weights):
+    """Inclusive prefix sum."""
+    out = list(weights)
+    for i in range(1, len(out)):
+        out[i] += out[i - 1]
+    return out
+
+
+def partition_uniform(num_items, num_parts):
+    parts = [0] * (num_parts + 1)
+    if num_items <= num_parts:
+        for p in range(num_parts + 1):
+            parts[p] = min(p, num_items)
+        return parts
+    chunksize = math.floor(num_items / num_parts)
+    for p in range(num_parts):
+        parts[p] = min(chunksize * p, num_items)
+    parts[num_parts] = num_items
+    return parts
+
+
+def _lprobe(weights, num_parts, bottleneck):
+    """Greedy feasibility probe: can prefix-summed `weights` be split into num_parts parts of weight <= bottleneck?"""
+    num_items = len(weights)
+    total_weight = weights[-1]
+    parts = [0] * (num_parts + 1)
+    for p in range(1, num_parts + 1):
+        parts[p] = num_items
+    bsum = bottleneck
+    chunksize = num_items // num_parts
+    step = chunksize
+    for p in range(1, num_parts):
+        while step < num_items and weights[step] < bsum:
+            step += chunksize
+        parts[p] = bisect_left(weights, bsum, lo=step - chunksize, hi=min(step, num_items))
+        if parts[p] == num_items:
+            part_size = weights[-1] - weights[parts[p - 1]]
+            return parts, part_size < bottleneck
+        bsum = weights[parts[p] - 1] + bottleneck
+    return parts, bsum >= total_weight
+
+
+def _rb_partition_balanced(weights, num_parts, eps):
+    total_weight = weights[-1]
+    lower = total_weight / num_parts
+    upper = total_weight
+    while upper > lower + eps:
+        mid = lower + (upper - lower) / 2
+        parts, success = _lprobe(weights, num_parts, mid)
+        if success:
+            upper = mid
+        else:
+            lower = mid + eps
+    return upper
+
+
+def partition_balanced(weights, num_parts, eps=1e-3):
+    """Minimise the heaviest part (binary search on the bottleneck; reference utils.py:333-414)."""
+    num_items = len(weights)
+    if num_items <= num_parts:
+        return partition_uniform(num_items, num_parts)
+    weights_ = prefix_sum_inc(weights)
+    bottleneck = _rb_partition_balanced(weights_, num_parts, eps=eps)
+    parts, success = _lprobe(weights_, num_parts, bottleneck)
+    assert success
+    return parts
+
+
+class PartitionedTensor:
+    """A tensor scattered along its flattened view over a process group, with a self-describing meta vector so the
+    receiver of a pipeline send can rebuild it (meta = [ndims, *shape, num_parts, rank, *partition_offsets])."""
+
+    def __init__(self, tensor, group, partition_meta=None):
+        super().__init__()
+        self.group = group
+        self.num_parts = dist.get_world_size(group=self.group)
+        self.rank = dist.get_rank(group=self.group)
+        self.orig_size = list(tensor.size())
+        self.orig_device = tensor.device
+        self.local_data, self.partition = self._partition_tensor(tensor)
+
+    @classmethod
+    def from_meta(cls, meta, local_part, group, device=None):
+        assert meta.dtype == torch.long
+        dummy = torch.ones(dist.get_world_size(group=group))
+        part_obj = cls(tensor=dummy, group=group)
+        meta = meta.tolist()
+        part_obj.orig_size = meta[1:(1 + meta[0])]
+        meta = meta[1 + meta[0]:]
+        part_obj.orig_device = device if device is not None else local_part.device
+        part_obj.local_data = local_part.detach()
+        part_obj.group = group
+        assert part_obj.num_parts == meta[0]
+        assert part_obj.rank == meta[1]
+        part_obj.partition = meta[2:]
+        return part_obj
+
+    def _partition_tensor(self, tensor):
+        partition = partition_uniform(num_items=tensor.numel(), num_parts=self.num_parts)
+        start = partition[self.rank]
+        length = partition[self.rank + 1] - start
+        tensor_part = tensor.detach().contiguous().view(-1).narrow(0, start=start, length=length).clone()
+        return tensor_part, partition
+
+    def full(self, device=None):
+        if device is None:
+            device = self.orig_device
+        full_numel = math.prod(self.full_size())
+        flat_tensor = torch.zeros([full_numel], dtype=self.local_data.dtype, device=device)
+        partition_tensors = []
+        for part_id in range(self.num_parts):
+            part_size = self.partition[part_id + 1] - self.partition[part_id]
+            buf = flat_tensor.narrow(0, start=self.partition[part_id], length=part_size)
+            if part_id == self.rank:
+                buf.copy_(self.local_data)
+            partition_tensors.append(buf)
+        # parts may be uneven, so exchange through equally-sized padded buffers
+        max_len = max(t.numel() for t in partition_tensors)
+        padded = [torch.zeros(max_len, dtype=flat_tensor.dtype, device=device) for _ in range(self.num_parts)]
+        mine = torch.zeros(max_len, dtype=flat_tensor.dtype, device=device)
+        mine[:self.local_data.numel()].copy_(self.local_data)
+        dist.all_gather(padded, mine, group=self.group)
+        for part_id, buf in enumerate(partition_tensors):
+            buf.copy_(padded[part_id][:buf.numel()])
+        return flat_tensor.view(self.full_size()).clone().detach()
+
+    def to_meta(self):
+        meta = [len(self.orig_size)] + list(self.orig_size) + [self.num_parts, self.rank] + list(self.partition)
+        return torch.LongTensor(data=meta).to(self.orig_device)
+
+    def data(self):
+        return self.local_data
+
+    def local_size(self):
+        return self.local_data.size()
+
+    def full_size(self):
+        return self.orig_size
+
+
+# ----------------------------------------------------------------------------------------------- memory / misc
+mem_alloced = 0
+mem_cached = 0
+
+
+def memory_status(msg, print_rank=-1, reset_max=False):
+    global mem_alloced, mem_cached
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    if print_rank != -1 and rank != print_rank:
+        return
+    if not torch.cuda.is_available():
+        return
+    torch.cuda.synchronize()
+    if reset_max:
+        torch.cuda.reset_peak_memory_stats()
+    new_alloced, new_cached = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    delta_alloced, delta_cached = new_alloced - mem_alloced, new_cached - mem_cached
+    mem_cached, mem_alloced = new_cached, new_alloced
+    gb = 1024 ** 3
+    print(f"RANK={rank} MEMSTATS", msg, f"device={torch.cuda.current_device()} "
+          f"current alloc={new_alloced / gb:0.4f}GB (delta={delta_alloced / gb:0.4f}GB max={torch.cuda.max_memory_allocated() / gb:0.4f}GB) "
+          f"current cache={new_cached / gb:0.4f}GB (delta={delta_cached / gb:0.4f}GB max={torch.cuda.max_memory_reserved() / gb:0.4f}GB)")
+
+
+def see_memory_usage(message, force=False):
+    if not force:
+        return
+    if dist.is_initialized() and dist.get_rank() != 0:
+        return
+    logger.info(message)
+    if torch.cuda.is_available():
+        gb = 1024 ** 3
+        logger.info(f"MA {round(torch.cuda.memory_allocated() / gb, 2)} GB  Max_MA {round(torch.cuda.max_memory_allocated() / gb, 2)} GB  "
+                    f"CA {round(torch.cuda.memory_reserved() / gb, 2)} GB  Max_CA {round(torch.cuda.max_memory_reserved() / gb)} GB ")
+    try:
+        import psutil
+        vm = psutil.virtual_memory()
+        logger.info(f"CPU Virtual Memory:  used = {round((vm.total - vm.available) / (1024 ** 3), 2)} GB, percent = {vm.percent}%")
+    except ImportError:
+        pass
+
+
+def call_to_str(base, *args, **kwargs):
+    """'base(arg1, arg2, key=value)' (used by the pipeline instruction reprs)."""
+    name = f"{base}("
+    if args:
+        name += ", ".join(repr(arg) for arg in args)
+        if kwargs:
+            name += ", "
+    if kwargs:
+        name += ", ".join(f"{key}={repr(arg)}" for key, arg in kwargs.items())
+    name += ")"
+    return name
+
+
+class GradientNoiseScale:
+    """Simple gradient-noise-scale estimator (McCandlish et al.) from small/large batch gradient norms
+    (DeeperSpeed addition, reference runtime/utils.py:618-674)."""
+
+    def __init__(self, model, batch_size_small, n_batches=10, beta=0.99, cpu_offload=False, neox_args=None, mpu=None):
+        self.batch_size_small = batch_size_small
+        self.batch_size_large = batch_size_small * n_batches
+        self.n_batches = n_batches
+        self.beta = beta
+        self.model = model
+        self.buffer = None
+        self.ema_scale = None
+        self.ema_noise = None
+        self.noise_scale = None
+        self.n_updates = 0
+        self.cpu_offload = cpu_offload
+        self.model_parallel = mpu is not None
+        self.mpu = mpu
+
+    def flatten_grads(self):
+        grads = []
+        module = getattr(self.model, "module", self.model)
+        for p in module.parameters():
+            if p.grad is None or not _counts_for_norm(p, self.mpu):
+                continue
+            g = p.grad.detach().flatten().float()
+            grads.append(g.cpu() if self.cpu_offload else g)
+        return torch.cat(grads) if grads else None
+
+    def _sync_overflow(self, is_overflow):
+        if self.model_parallel:
+            t = torch.tensor([float(is_overflow)], device="cuda" if torch.cuda.is_available() else "cpu")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.mpu.get_model_parallel_group())
+            return bool(t[0].item())
+        return is_overflow
+
+    def _update(self):
+        grad = self.flatten_grads()
+        if grad is None:
+            return
+        is_overflow = self._sync_overflow(bool(torch.isinf(grad).any() or torch.isnan(grad).any()))
+        if is_overflow:
+            return
+        self.buffer = grad if self.buffer is None else self.buffer + grad
+        if self.n_updates % self.n_batches == self.n_batches - 1:
+            self.buffer /= self.n_batches
+            g_big = torch.square(torch.norm(self.buffer))
+            g_small = torch.square(torch.norm(grad))
+            if self.model_parallel:
+                dist.all_reduce(g_big, group=self.mpu.get_model_parallel_group())
+                dist.all_reduce(g_small, group=self.mpu.get_model_parallel_group())
+            bs, bl = self.batch_size_small, self.batch_size_large
+            noise = 1 / (bl - bs) * (bl * g_big - bs * g_small)
+            scale = 1 / (1 / bs - 1 / bl) * (g_small - g_big)
+            self.ema_noise = noise if self.ema_noise is None else self.beta * self.ema_noise + (1 - self.beta) * noise
+            self.ema_scale = scale if self.ema_scale is None else self.beta * self.ema_scale + (1 - self.beta) * scale
+            self.noise_scale = (self.ema_scale / self.ema_noise).item() if float(self.ema_noise) != 0 else None
+            self.buffer = None
+        self.n_updates += 1
+
+    def update(self):
+        if self.neox_is_last_stage():
+            self._update()
+
+    def neox_is_last_stage(self):
+        return True

@@ -1,0 +1,86 @@
+"""Memory-efficient linear for ZeRO-3: the autograd function keeps a *reference to the Parameter object*, not to
+its (gathered) storage, so the weight can be released between forward and backward and re-gathered by the ZeRO-3
+hooks (reference deepspeed/runtime/zero/linear.py:29-168). On CUDA the products run on the tcgen05 GEMM kernels."""
+import math
+
+import torch
+from torch import Tensor
+from torch.nn import init
+from torch.nn.modules.module import Module
+from torch.nn.parameter import Parameter
+
+from ...ops import kernels as K
+
+tensor_map = {}
+
+
+class LinearFunctionForZeroStage3(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, input, weight, bias=None):
+        weight_id = id(weight)
+        bias_id = id(bias)
+        tensor_map[weight_id] = weight
+        tensor_map[bias_id] = bias
+        ctx.save_for_backward(input, torch.tensor(weight_id), torch.tensor(bias_id))
+        if input.is_cuda and input.dtype in (torch.float16, torch.bfloat16) and input.shape[-1] % 8 == 0 \
+                and weight.shape[0] % 8 == 0:
+            x2 = input.reshape(-1, input.shape[-1])
+            out = K.gemm(x2, weight, trans_b=True, epilogue=1 if bias is not None else 0, bias=bias)
+            return out.view(*input.shape[:-1], weight.shape[0])
+        if input.dim() == 2 and bias is not None:
+            return torch.addmm(bias, input, weight.t())
+        output = input.matmul(weight.t())
+        if bias is not None:
+            output = output + bias
+        return output
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input, weight_id, bias_id = ctx.saved_tensors
+        weight = tensor_map[weight_id.item()]
+        bias = tensor_map[bias_id.item()]
+        grad_input = grad_weight = grad_bias = None
+        if ctx.needs_input_grad[0]:
+            grad_input = grad_output.matmul(weight)
+        if ctx.needs_input_grad[1]:
+            dim = grad_output.dim()
+            if dim > 2:
+                grad_weight = grad_output.reshape(-1, grad_output.shape[-1]).t().matmul(input.reshape(-1, input.shape[-1]))
+            else:
+                grad_weight = grad_output.t().matmul(input)
+        if bias is not None and ctx.needs_input_grad[2]:
+            grad_bias = grad_output.reshape(-1, grad_output.shape[-1]).sum(0)
+        return grad_input, grad_weight, grad_bias
+
+    @staticmethod
+    def apply_compat(input, weight, bias=None):
+        return LinearFunctionForZeroStage3.apply(input, weight, bias)
+
+
+class LinearModuleForZeroStage3(Module):
+    """nn.Linear twin built on LinearFunctionForZeroStage3."""
+    __constants__ = ["in_features", "out_features"]
+
+    def __init__(self, in_features: int, out_features: int, bias: bool = True) -> None:
+        super().__init__()
+        self.in_features = in_features
+        self.out_features = out_features
+        self.weight = Parameter(torch.Tensor(out_features, in_features))
+        if bias:
+            self.bias = Parameter(torch.Tensor(out_features))
+        else:
+            self.register_parameter("bias", None)
+        self.reset_parameters()
+
+    def reset_parameters(self) -> None:
+        init.kaiming_uniform_(self.weight, a=math.sqrt(5))
+        if self.bias is not None:
+            fan_in, _ = init._calculate_fan_in_and_fan_out(self.weight)
+            bound = 1 / math.sqrt(fan_in)
+            init.uniform_(self.bias, -bound, bound)
+
+    def forward(self, input: Tensor) -> Tensor:
+        return LinearFunctionForZeroStage3.apply(input, self.weight, self.bias)
+
+    def extra_repr(self) -> str:
+        return "in_features={}, out_features={}, bias={}".format(self.in_features, self.out_features, self.bias is not None)

@@ -1,0 +1,3 @@
+from .logging import logger, log_dist
+from .distributed import init_distributed
+from .timer import SynchronizedWallClockTimer, ThroughputTimer

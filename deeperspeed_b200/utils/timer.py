@@ -1,0 +1,159 @@
+"""Timers. `SynchronizedWallClockTimer` keeps the reference API (deepspeed/utils/timer.py:19-101) but measures
+on the device with CUDA events when CUDA is present, so starting/stopping a timer does not serialise the stream;
+elapsed() synchronises only on the recorded end event. `ThroughputTimer` as reference timer.py:105-182."""
+import time
+
+import torch
+
+from .logging import log_dist
+
+try:
+    import psutil
+except ImportError:  # pragma: no cover
+    psutil = None
+
+
+def _cuda():
+    return torch.cuda.is_available()
+
+
+class SynchronizedWallClockTimer:
+    class Timer:
+        def __init__(self, name):
+            self.name_ = name
+            self.elapsed_ = 0.0
+            self.started_ = False
+            self._t0 = None
+            self._pending = []  # (start_event, end_event) pairs not yet folded into elapsed_
+
+        def start(self):
+            assert not self.started_, f"timer {self.name_} has already been started"
+            if _cuda():
+                self._t0 = torch.cuda.Event(enable_timing=True)
+                self._t0.record()
+            else:
+                self._t0 = time.time()
+            self.started_ = True
+
+        def stop(self, reset=False):
+            assert self.started_, "timer is not started"
+            if _cuda():
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                self._pending.append((self._t0, e))
+            else:
+                dt = time.time() - self._t0
+                self.elapsed_ = dt if reset else self.elapsed_ + dt
+            self.started_ = False
+
+        def _fold(self):
+            for s, e in self._pending:
+                e.synchronize()
+                self.elapsed_ += s.elapsed_time(e) / 1000.0
+            self._pending = []
+
+        def reset(self):
+            self.elapsed_ = 0.0
+            self._pending = []
+            self.started_ = False
+
+        def elapsed(self, reset=True):
+            started = self.started_
+            if started:
+                self.stop()
+            self._fold()
+            v = self.elapsed_
+            if reset:
+                self.reset()
+            if started:
+                self.start()
+            return v
+
+    def __init__(self):
+        self.timers = {}
+
+    def __call__(self, name):
+        if name not in self.timers:
+            self.timers[name] = self.Timer(name)
+        return self.timers[name]
+
+    @staticmethod
+    def memory_usage():
+        if not _cuda():
+            return ""
+        gb = 1024 ** 3
+        return " | mem_allocated: {:.4f} GB | max_mem_allocated: {:.4f} GB | cache_allocated: {:.4f} GB | " \
+               "max_cache_allocated: {:.4f} GB".format(torch.cuda.memory_allocated() / gb,
+                                                       torch.cuda.max_memory_allocated() / gb,
+                                                       torch.cuda.memory_reserved() / gb,
+                                                       torch.cuda.max_memory_reserved() / gb)
+
+    def log(self, names, normalizer=1.0, reset=True, memory_breakdown=False, ranks=None):
+        assert normalizer > 0.0
+        s = "time (ms)"
+        for name in names:
+            if name in self.timers:
+                s += " | {}: {:.2f}".format(name, self.timers[name].elapsed(reset=reset) * 1000.0 / normalizer)
+        if memory_breakdown:
+            s += self.memory_usage()
+        log_dist(s, ranks=ranks or [0])
+
+
+class ThroughputTimer:
+    def __init__(self, batch_size, num_workers, start_step=2, steps_per_output=50, monitor_memory=False,
+                 logging_fn=None):
+        self.start_time = 0
+        self.end_time = 0
+        self.started = False
+        self.batch_size = batch_size or 1
+        self.num_workers = num_workers
+        self.start_step = start_step
+        self.epoch_count = 0
+        self.local_step_count = 0
+        self.total_step_count = 0
+        self.total_elapsed_time = 0
+        self.steps_per_output = steps_per_output
+        self.monitor_memory = monitor_memory
+        self.logging = logging_fn or (lambda m: log_dist(m, ranks=[0]))
+        self.initialized = False
+
+    def update_epoch_count(self):
+        self.epoch_count += 1
+        self.local_step_count = 0
+
+    def _init_timer(self):
+        self.initialized = True
+
+    def start(self):
+        self._init_timer()
+        self.started = True
+        if self.total_step_count >= self.start_step:
+            if _cuda():
+                torch.cuda.synchronize()
+            self.start_time = time.time()
+
+    def stop(self, report_speed=True):
+        if not self.started:
+            return
+        self.started = False
+        self.total_step_count += 1
+        self.local_step_count += 1
+        if self.total_step_count > self.start_step:
+            if _cuda():
+                torch.cuda.synchronize()
+            self.end_time = time.time()
+            self.total_elapsed_time += self.end_time - self.start_time
+            if report_speed and self.local_step_count % self.steps_per_output == 0:
+                self.logging("{}/{}, SamplesPerSec={}".format(self.epoch_count, self.local_step_count,
+                                                              self.avg_samples_per_sec()))
+                if self.monitor_memory and psutil is not None:
+                    vm = psutil.virtual_memory()
+                    self.logging("{}/{}, vm percent: {}, swap percent: {}".format(
+                        self.epoch_count, self.local_step_count, vm.percent, psutil.swap_memory().percent))
+
+    def avg_samples_per_sec(self):
+        if self.total_step_count > self.start_step and self.total_elapsed_time > 0:
+            samples_per_step = self.batch_size * self.num_workers
+            avg = self.total_elapsed_time / (self.total_step_count - self.start_step)
+            return samples_per_step / avg
+        return float("-inf")

@@ -1,0 +1,99 @@
+#!/usr/bin/env python
+"""Offline recovery: stitch the fp32 master shards of a ZeRO checkpoint into one consolidated fp32 state_dict.
+
+  python zero_to_fp32.py <checkpoint_dir> <output_file>
+
+Handles stage 1 (`local_sub_partitions_of_fp32_groups`, bucket-major / rank-minor), stage 2
+(`single_partition_of_fp32_groups`) and stage 3 (`fp32_flat_groups`, per-parameter shards) using the `param_shapes`
+stored next to the optimizer state. Same role as reference deepspeed/utils/zero_to_fp32.py:21-151. Self-contained
+on purpose: it is copied into every checkpoint directory."""
+import argparse
+import glob
+import os
+import re
+from collections import OrderedDict
+
+import torch
+
+
+def _rank_key(path):
+    m = re.search(r"zero_pp_rank_(\d+)_mp_rank_(\d+)", path)
+    return (int(m.group(2)), int(m.group(1))) if m else (0, 0)
+
+
+def get_optim_files(checkpoint_dir):
+    files = sorted(glob.glob(os.path.join(checkpoint_dir, "*_optim_states.pt")), key=_rank_key)
+    if not files:
+        raise FileNotFoundError(f"can't find '*_optim_states.pt' files in directory '{checkpoint_dir}'")
+    return files
+
+
+def _align8(n):
+    return (n + 7) // 8 * 8
+
+
+def _take_params(flat, param_shapes, state_dict, aligned):
+    """Cut `flat` into the named parameters; `aligned` = arena layout with 8-element aligned parameter starts."""
+    off = 0
+    for name, shape in param_shapes.items():
+        numel = 1
+        for d in shape:
+            numel *= d
+        state_dict[name] = flat.narrow(0, off, numel).view(*shape).clone()
+        off += numel
+        if aligned:
+            off = _align8(off)
+    return off
+
+
+def convert_zero_chkpt_to_fp32_consolid_state_dict(checkpoint_dir, output_file=None):
+    files = get_optim_files(checkpoint_dir)
+    sds = [torch.load(f, map_location="cpu", weights_only=False) for f in files]
+    osd = [sd["optimizer_state_dict"] for sd in sds]
+    stage = osd[0]["zero_stage"]
+    world = osd[0]["partition_count"]
+    param_shapes = sds[0]["param_shapes"]
+    state_dict = OrderedDict()
+    total = sum(int(torch.tensor(list(s)).prod()) if len(s) else 1 for s in param_shapes.values())
+    total_aligned = sum(_align8(int(torch.tensor(list(s)).prod()) if len(s) else 1) for s in param_shapes.values())
+    if stage in (1, 2):
+        key = "local_sub_partitions_of_fp32_groups" if stage == 1 else "single_partition_of_fp32_groups"
+        ngroups = len(osd[0][key])
+        flats = []
+        for gi in range(ngroups):
+            per_rank = [o[key][gi] for o in osd[:world]]
+            per_rank = [[p] if torch.is_tensor(p) else list(p) for p in per_rank]
+            pieces = []
+            for k in range(len(per_rank[0])):
+                for r in range(len(per_rank)):
+                    pieces.append(per_rank[r][k].float().view(-1))
+            flats.append(torch.cat(pieces))
+        flat = torch.cat(flats) if len(flats) > 1 else flats[0]
+        # one param group in model order is the common case; with several groups the shapes are consumed in order
+        aligned = flat.numel() >= total_aligned and total_aligned != total
+        _take_params(flat, param_shapes, state_dict, aligned)
+    elif stage == 3:
+        flat_groups = [torch.cat([g.float().view(-1) for g in o["fp32_flat_groups"]]) for o in osd[:world]]
+        offset = 0
+        for name, shape in param_shapes.items():
+            numel = 1
+            for d in shape:
+                numel *= d
+            part = (numel + world - 1) // world
+            full = torch.cat([fg.narrow(0, offset, part) for fg in flat_groups])
+            state_dict[name] = full.narrow(0, 0, numel).view(*shape).clone()
+            offset += part
+    else:
+        raise ValueError(f"unknown zero stage {stage}")
+    if output_file is not None:
+        print(f"Saving fp32 state dict to {output_file} (total_numel = {total})")
+        torch.save(state_dict, output_file)
+    return state_dict
+
+
+if __name__ == "__main__":
+    parser = argparse.ArgumentParser()
+    parser.add_argument("checkpoint_dir", type=str, help="path to the deepspeed checkpoint folder, e.g. path/global_step1")
+    parser.add_argument("output_file", type=str, help="path to the pytorch fp32 state_dict output file")
+    args = parser.parse_args()
+    convert_zero_chkpt_to_fp32_consolid_state_dict(args.checkpoint_dir, args.output_file)
