@@ -86,7 +86,8 @@ class FP16_DeepSpeedZeroOptimizer(ZeroShardedOptimizer):
             if self._dev.type == "cuda":
                 torch.cuda.current_stream().synchronize()
             from ...ops.adam import DeepSpeedCPUAdam
-            if isinstance(self.optimizer, DeepSpeedCPUAdam) and all(n == 1 for n in self.num_buckets):
+            lowp = all(a.dtype in (torch.float16, torch.bfloat16) for a in self.arenas)
+            if isinstance(self.optimizer, DeepSpeedCPUAdam) and lowp and all(n == 1 for n in self.num_buckets):
                 # fused copy-back: the CPU optimizer writes the low-precision slice straight to the GPU arena
                 self.optimizer.step(fp16_param_groups=[[self._slice(a.data, gi, 0)] for gi, a in enumerate(self.arenas)])
             else:

@@ -1,0 +1,260 @@
+"""Engine / ZeRO / pipeline / checkpoint plumbing on CPU with the gloo backend (world size 1-2).
+BASELINE config #1: SimpleModel, ZeRO-1, fp32, CPU/gloo, world 2."""
+import copy
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+
+import deeperspeed_b200 as deepspeed
+from common import distributed_test
+from simple_model import SimpleModel, LinearStack, LinearStackPipe, random_dataloader, args_from_dict, random_dataset
+
+HID = 16
+
+
+def _cfg(stage, **kw):
+    c = {"train_batch_size": 8, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+         "optimizer": {"type": "Adam", "params": {"lr": 0.01, "weight_decay": 0.01}},
+         "fp16": {"enabled": True, "type": "fp32"}}
+    if stage:
+        c["zero_optimization"] = {"stage": stage}
+    c.update(kw)
+    return c
+
+
+def _train(engine, steps, seed=0):
+    losses = []
+    dl = random_dataloader(engine, 64, HID, engine.device, seed=seed + dist.get_rank())
+    it = iter(dl)
+    for _ in range(steps * engine.gradient_accumulation_steps()):
+        x, y = next(it)
+        loss = engine(x, y)
+        engine.backward(loss)
+        engine.step()
+        losses.append(loss.item())
+    return losses
+
+
+def _reference_run(steps, world, gas):
+    """Plain torch AdamW on the concatenated global batch = what any DP/ZeRO variant must reproduce."""
+    torch.manual_seed(42)
+    model = SimpleModel(HID)
+    opt = torch.optim.AdamW(model.parameters(), lr=0.01, weight_decay=0.01)
+    its = [iter(torch.utils.data.DataLoader(random_dataset(64, HID, seed=r), batch_size=2)) for r in range(world)]
+    for _ in range(steps):
+        opt.zero_grad()
+        for _ in range(gas):
+            for it in its:
+                x, y = next(it)
+                (model(x, y) / (gas * world)).backward()
+        opt.step()
+    return [p.detach().clone() for p in model.parameters()]
+
+
+@pytest.mark.parametrize("stage", [0, 1, 2])
+def test_zero_matches_plain_adamw_world2(stage, tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(42)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(stage)), model=model,
+                                               model_parameters=model.parameters())
+        assert engine.gradient_accumulation_steps() == 2
+        _train(engine, 3)
+        ref = _reference_run(3, 2, 2)
+        for p, r in zip(engine.module.parameters(), ref):
+            assert torch.allclose(p.detach(), r, atol=2e-5), (p - r).abs().max()
+    run()
+
+
+def test_zero2_overlap_and_offload_world2(tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        for extra in ({"overlap_comm": True}, {"cpu_offload": True}):
+            torch.manual_seed(42)
+            model = SimpleModel(HID)
+            cfg = _cfg(2)
+            cfg["zero_optimization"].update(extra)
+            engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=model.parameters())
+            _train(engine, 3)
+            ref = _reference_run(3, 2, 2)
+            for p, r in zip(engine.module.parameters(), ref):
+                assert torch.allclose(p.detach(), r, atol=3e-5), (extra, (p - r).abs().max())
+    run()
+
+
+def test_unbalanced_gradients_zero(tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        for stage in (1, 2):
+            model = SimpleModel(HID, empty_grad=True, rank=dist.get_rank())
+            engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(stage)), model=model,
+                                                   model_parameters=model.parameters())
+            losses = _train(engine, 2)
+            assert all(l == l for l in losses)
+    run()
+
+
+@pytest.mark.parametrize("stage", [1, 2])
+def test_checkpoint_roundtrip_and_elastic_reload(stage, tmp_path):
+    @distributed_test(world_size=2)
+    def save():
+        torch.manual_seed(7)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(stage)), model=model,
+                                               model_parameters=model.parameters())
+        _train(engine, 2)
+        engine.save_checkpoint(str(tmp_path), client_state={"foo": 17})
+        # same world size: bitwise restore of master weights and Adam state
+        model2 = SimpleModel(HID)
+        e2, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(stage)), model=model2,
+                                           model_parameters=model2.parameters())
+        path, client = e2.load_checkpoint(str(tmp_path))
+        assert path is not None and client["foo"] == 17 and e2.global_steps == engine.global_steps
+        for a, b in zip(engine.module.parameters(), e2.module.parameters()):
+            assert torch.equal(a, b)
+        for ma, mb in zip(engine.optimizer.fp32_masters, e2.optimizer.fp32_masters):
+            assert torch.equal(ma, mb)
+            sa, sb = engine.optimizer.optimizer.state[ma], e2.optimizer.optimizer.state[mb]
+            assert torch.equal(sa["exp_avg"], sb["exp_avg"]) and torch.equal(sa["exp_avg_sq"], sb["exp_avg_sq"])
+        l1, l2 = _train(engine, 1, seed=5), _train(e2, 1, seed=5)
+        assert l1 == l2
+        if dist.get_rank() == 0:
+            torch.save([p.detach().clone() for p in engine.module.parameters()], os.path.join(str(tmp_path), "after.pt"))
+    save()
+
+    @distributed_test(world_size=1)
+    def reload_dp1():
+        cfg = _cfg(stage)
+        cfg["train_micro_batch_size_per_gpu"] = 4
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        path, _ = engine.load_checkpoint(str(tmp_path))
+        assert path is not None
+        full = torch.cat([m.data for m in engine.optimizer.fp32_masters])
+        flat = torch.cat([p.detach().view(-1) for p in engine.module.parameters()])
+        assert torch.allclose(full[:flat.numel()], flat)
+        st = engine.optimizer.optimizer.state[engine.optimizer.fp32_masters[0]]
+        assert st["exp_avg"].abs().sum() > 0
+    reload_dp1()
+
+
+def test_zero_to_fp32(tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(1)), model=model,
+                                               model_parameters=model.parameters())
+        _train(engine, 1)
+        engine.save_checkpoint(str(tmp_path), tag="t")
+        if dist.get_rank() == 0:
+            from deeperspeed_b200.utils.zero_to_fp32 import convert_zero_chkpt_to_fp32_consolid_state_dict
+            sd = convert_zero_chkpt_to_fp32_consolid_state_dict(os.path.join(str(tmp_path), "t"))
+            for name, p in engine.module.named_parameters():
+                assert torch.allclose(sd[name], p.detach().float(), atol=1e-6), name
+    run()
+
+
+def test_pipeline_matches_sequential_world2(tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        from deeperspeed_b200.runtime.pipe.topology import PipeDataParallelTopology
+        cfg = {"train_batch_size": 8, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.01}}, "fp16": {"enabled": True, "type": "fp32"},
+               "zero_optimization": {"stage": 1}}
+        torch.manual_seed(3)
+        full = LinearStack(HID, HID, HID, 2)
+        torch.manual_seed(3)
+        pipe = LinearStackPipe(HID, HID, HID, 2, topology=PipeDataParallelTopology(num_pp=2, num_dp=1),
+                               partition_method="uniform")
+        # same initial weights as the sequential model
+        seq_layers = [full.input_layer] + list(full.layers) + [full.output_layer]
+        mods = [m for m in pipe.forward_funcs if isinstance(m, torch.nn.Module)]
+        start = 0 if pipe.stage_id == 0 else len(seq_layers) - len(mods)
+        for m, ref in zip(mods, seq_layers[start:start + len(mods)]):
+            m.load_state_dict(ref.state_dict())
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=pipe,
+                                               model_parameters=[p for p in pipe.parameters()])
+        ds = random_dataset(64, HID, seed=11)
+        it = iter(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(ds, batch_size=2)))
+        opt = torch.optim.AdamW(full.parameters(), lr=0.01, weight_decay=0.0)
+        ref_it = iter(torch.utils.data.DataLoader(ds, batch_size=2))
+        for step in range(3):
+            loss = engine.train_batch(it)
+            opt.zero_grad()
+            tot = 0.0
+            for _ in range(4):
+                x, y = next(ref_it)
+                l = full(x, y) / 4
+                l.backward()
+                tot += l.item()
+            opt.step()
+            assert abs(float(loss) - tot) < 1e-4, (step, float(loss), tot)
+        for m, ref in zip(mods, seq_layers[start:start + len(mods)]):
+            for a, b in zip(m.parameters(), ref.parameters()):
+                assert torch.allclose(a.detach(), b.detach(), atol=1e-5)
+        # per-layer checkpoint files + reload
+        engine.save_checkpoint(str(tmp_path), tag="pp")
+        dist.barrier()
+        files = sorted(os.listdir(os.path.join(str(tmp_path), "pp")))
+        assert "layer_00-model_states.pt" in files and "mp_rank_00_model_states.pt" in files and "mp_rank_01_model_states.pt" in files
+        before = [p.detach().clone() for p in pipe.parameters()]
+        for p in pipe.parameters():
+            p.data.zero_()
+        engine.load_checkpoint(str(tmp_path), tag="pp")
+        for a, b in zip(before, pipe.parameters()):
+            assert torch.equal(a, b.detach())
+        ev = engine.eval_batch(it)
+        assert float(ev) == float(ev)
+    run()
+
+
+def test_fp16_optimizer_bf16_cpu(tmp_path):
+    @distributed_test(world_size=1)
+    def run():
+        cfg = {"train_batch_size": 4, "steps_per_print": 100, "optimizer": {"type": "Adam", "params": {"lr": 0.01}},
+               "fp16": {"enabled": True, "type": "bfloat16"}, "gradient_clipping": 1.0}
+        model = SimpleModel(HID)
+        engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                 model_parameters=model.parameters())
+        assert type(opt).__name__ == "FP16_Optimizer" and next(engine.module.parameters()).dtype == torch.bfloat16
+        dl = random_dataloader(engine, 32, HID, engine.device, dtype=torch.bfloat16)
+        first = last = None
+        for _ in range(4):
+            for x, y in dl:
+                loss = engine(x, y); engine.backward(loss); engine.step()
+                first = first if first is not None else loss.item()
+                last = loss.item()
+        assert last < first
+        sd = opt.state_dict()
+        assert set(["dynamic_loss_scale", "cur_scale", "cur_iter", "optimizer_state_dict", "fp32_groups_flat", "clip_grad"]) <= set(sd)
+    run()
+
+
+def test_dynamic_loss_scale_overflow_skips(tmp_path):
+    @distributed_test(world_size=1)
+    def run():
+        cfg = {"train_batch_size": 1, "steps_per_print": 100, "optimizer": {"type": "Adam", "params": {"lr": 0.001}},
+               "fp16": {"enabled": True, "type": "bfloat16"}}
+        model = SimpleModel(HID)
+        engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                 model_parameters=model.parameters())
+        # force the fp16-style dynamic scaler on a bf16 CPU model to exercise the overflow path
+        opt.dynamic_loss_scale, opt.cur_scale, opt.scale_window, opt.min_loss_scale = True, 2.0 ** 8, 2, 1
+        opt.last_overflow_iter, opt.scale_factor = -1, 2
+        before = [p.detach().clone() for p in model.parameters()]
+        x = torch.randn(1, HID, dtype=torch.bfloat16); y = torch.zeros(1, dtype=torch.long)
+        loss = engine(x, y); engine.backward(loss)
+        opt.arenas[0].grad[3] = float("inf")
+        engine.step()
+        assert opt.overflow and opt.cur_scale == 2.0 ** 7 and engine.skipped_steps == 1
+        for a, b in zip(before, model.parameters()):
+            assert torch.equal(a, b.detach())
+        for _ in range(3):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        assert not opt.overflow and opt.cur_scale == 2.0 ** 8
+    run()
