@@ -478,3 +478,49 @@ extern "C" int dsb_cross_entropy_bwd(void* logits, const long* targets, const fl
     DSB_DISPATCH_HALF(dtype, (ce_bwd_kernel<T><<<(unsigned)tokens, CE_THREADS, 0, s>>>((T*)logits, targets, lse, grad_scale_dev, grad_scale, vocab, ld, ignore_index)));
     DSB_RET();
 }
+
+// ------------------------------------------------------------------------------------------- allocation-free column sum
+// Same reduction as dsb_column_sum, for callers that cannot hand over (or obtain) scratch memory: a plug-in or host
+// callback that is not allowed to touch the CUDA allocation API, or a process whose HBM has been given wholesale to
+// another allocator so that cudaMalloc would fail. The fp32 accumulators live in a fixed file-scope device array
+// instead. Every GPU that loads this library carries that array (DSB_COLSUM_NOALLOC_MAX_COLS floats = 256 KiB)
+// until the process exits.
+//
+// The array's name is only a host-side handle; the device address is looked up with cudaGetSymbolAddress the first
+// time the entry point runs on a given device (with that device current) and cached per device. Make that first
+// call outside of any stream capture. All calls on one GPU share the array and it still holds the previous call's
+// sums, so each call zeroes the columns it uses first (stream-ordered); two calls that may run at the same time on
+// one GPU (different streams) would corrupt each other and must be serialised by the caller.
+namespace dsb {
+static __device__ __align__(256) float g_colsum_noalloc_scratch[DSB_COLSUM_NOALLOC_MAX_COLS];
+static float* g_colsum_noalloc_ptr[64] = {nullptr};
+}  // namespace dsb
+
+extern "C" int dsb_column_sum_noalloc(const void* x, void* out, long rows, int cols, int dtype, int accumulate,
+                                      void* stream) {
+    if (cols % 8) return DSB_ERR_SIZE;
+    if (cols > DSB_COLSUM_NOALLOC_MAX_COLS) return DSB_ERR_SIZE;  // beyond the built-in scratch: use dsb_column_sum
+    if (rows <= 0 || cols <= 0) return 0;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return -(int)e;
+    if (dev < 0 || dev >= 64) return DSB_ERR_ARG;
+    if (dsb::g_colsum_noalloc_ptr[dev] == nullptr) {
+        float* p = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), dsb::g_colsum_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) return e != cudaSuccess ? -(int)e : DSB_ERR_ARG;
+        dsb::g_colsum_noalloc_ptr[dev] = p;
+    }
+    float* acc = dsb::g_colsum_noalloc_ptr[dev];
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    e = cudaMemsetAsync(acc, 0, sizeof(float) * cols, s);
+    if (e != cudaSuccess) return -(int)e;
+    const int gx = (cols + 63) / 64;
+    long gy = (long)ew_sms() * 4 / gx;
+    if (gy < 1) gy = 1;
+    if (gy > (rows + 31) / 32) gy = (rows + 31) / 32;
+    dim3 grid(gx, (unsigned)gy);
+    DSB_DISPATCH_HALF(dtype, (column_sum_kernel<T><<<grid, 256, 0, s>>>((const T*)x, acc, rows, cols),
+                              colsum_finalize<T><<<(cols + 255) / 256, 256, 0, s>>>(acc, (T*)out, cols, accumulate)));
+    DSB_RET();
+}

@@ -109,6 +109,15 @@ int dsb_transpose_0213(const void* x, void* y, int B, int d1, int d2, int D, int
  * Reference: general_kernels.cu:6-48. */
 int dsb_column_sum(const void* x, void* out, long rows, int cols, int dtype, int accumulate, float* scratch,
                    void* stream);
+/* dsb_column_sum without a scratch argument, for callers that may not allocate device memory (code running where
+ * the CUDA allocation API is off limits, or in a process whose HBM is already owned by another allocator). The
+ * accumulators sit in a fixed device array inside the library: cols must be <= DSB_COLSUM_NOALLOC_MAX_COLS, larger
+ * requests return DSB_ERR_SIZE. The entry point itself allocates and frees nothing. Its first call on each device
+ * resolves the array's address (do that call outside stream capture); the array is shared by all calls on a GPU,
+ * is re-zeroed at the start of every call, and calls that can overlap on one GPU race and must be serialised.
+ * This entry point has no counterpart in the reference. */
+#define DSB_COLSUM_NOALLOC_MAX_COLS 65536
+int dsb_column_sum_noalloc(const void* x, void* out, long rows, int cols, int dtype, int accumulate, void* stream);
 /* out = a + b (+ c (+ d)). Reference: general_kernels.cu:89-323. */
 int dsb_fused_add(const void* a, const void* b, const void* c, const void* d, void* out, long n, int dtype,
                   void* stream);
