@@ -1,0 +1,135 @@
+"""Fused ZeRO step over NVLink peer memory: reduce-scatter + fp16->fp32 cast + average + norm/overflow in one kernel,
+Adam + cast + all-gather (peer stores) in a second one. See csrc/comm/fused_zero.cu."""
+import ctypes as C
+import os
+
+import torch
+import torch.distributed as dist
+
+from ..ops import kernels as K
+from ..ops import native as N
+from ..utils.logging import logger
+from .symm import SymmetricHeap
+
+_p, _i, _l, _f, _u = C.c_void_p, C.c_int, C.c_long, C.c_float, C.c_uint
+N.register_sigs({
+    "dsb_fused_rs_norm": [_p, _p, _i, _i, _l, _l, _i, _f, _p, _p, _p, _p, _u, _p],
+    "dsb_fused_adam_ag": [_p, _p, _p, _p, _p, _p, _i, _i, _l, _l, _i, _f, _f, _f, _f, _f, _i, _i, _i, _p, _p, _u, _p],
+})
+N.register_sigs({"dsb_fused_zero_scratch_bytes": []}, restype=_l)
+
+
+def _ptr_array(ptrs):
+    return (C.c_void_p * len(ptrs))(*ptrs)
+
+
+class FusedZeroStep:
+    """Owns the symmetric heap that backs the arenas of a ZeroShardedOptimizer and runs its step with the fused
+    kernels. Created through `maybe_create`, which returns None when the fused path cannot be used (CPU, dp == 1,
+    peers not on one NVLink domain, fp32 arenas)."""
+
+    @staticmethod
+    def heap_bytes_for(param_groups, dp):
+        total = 0
+        for g in param_groups:
+            n = sum((p.numel() + 7) // 8 * 8 for p in g["params"])
+            n = (n + dp * 8 - 1) // (dp * 8) * (dp * 8) + 4096
+            total += 2 * n * 2 + 1024
+        return total
+
+    @staticmethod
+    def make_allocator(param_groups, group):
+        """Returns (allocator, heap): arenas created with this allocator live in the symmetric heap."""
+        if not torch.cuda.is_available() or not dist.is_initialized() or dist.get_world_size(group=group) < 2:
+            return None, None
+        if any(p.dtype not in (torch.float16, torch.bfloat16) for g in param_groups for p in g["params"]):
+            return None, None
+        dp = dist.get_world_size(group=group)
+        heap = SymmetricHeap(FusedZeroStep.heap_bytes_for(param_groups, dp) + (1 << 20), group=group)
+        offsets = {}
+
+        def allocator(numel, dtype, device):
+            t, off = heap.alloc(numel, dtype)
+            offsets[t.data_ptr()] = off
+            return t
+
+        heap.offsets = offsets
+        return allocator, heap
+
+    @staticmethod
+    def maybe_create(opt):
+        heap = getattr(opt, "_symm_heap", None)
+        if heap is None:
+            return None
+        return FusedZeroStep(opt, heap)
+
+    def __init__(self, opt, heap):
+        self.opt = opt
+        self.heap = heap
+        self.lib = N.cuda_lib()
+        self.scratch = torch.zeros(self.lib.dsb_fused_zero_scratch_bytes(), dtype=torch.uint8, device=opt._dev)
+        self.red32 = [torch.empty(opt.sub_size[gi], dtype=torch.float32, device=opt._dev)
+                      for gi in range(len(opt.arenas))]
+        self.flag_ptrs = _ptr_array(heap.flag_ptrs())
+        self.grad_ptrs, self.param_ptrs = [], []
+        for a in opt.arenas:
+            self.grad_ptrs.append(_ptr_array(heap.peer_ptrs(heap.offsets[a.grad.data_ptr()])))
+            self.param_ptrs.append(_ptr_array(heap.peer_ptrs(heap.offsets[a.data.data_ptr()])))
+        logger.info(f"[fused-zero] rank {opt.dp_rank}/{opt.dp_world}: NVLink peer-memory ZeRO step enabled "
+                    f"({sum(a.numel for a in opt.arenas)} elements)")
+
+    def step(self):
+        o = self.opt
+        for a in o.arenas:
+            a.absorb_stray_grads()
+        R, me = o.dp_world, o.dp_rank
+        s = N.stream_ptr()
+        o._sumsq.zero_()
+        o._flag.zero_()
+        sumsq = o._sumsq.narrow(0, 0, 1)
+        # With several buckets the reduced slices are kept per bucket; the common case is one bucket per group.
+        reds = {}
+        for gi, arena in enumerate(o.arenas):
+            sub = o.sub_size[gi]
+            for k in range(o.num_buckets[gi]):
+                red = self.red32[gi] if k == 0 else torch.empty(sub, dtype=torch.float32, device=o._dev)
+                reds[(gi, k)] = red
+                off = (k * o.partition_count + me) * sub
+                N.check(self.lib.dsb_fused_rs_norm(self.grad_ptrs[gi], self.flag_ptrs, R, me, off, sub,
+                                                   N.dtype_code(arena.dtype), 1.0 / R, N.ptr(red), N.ptr(sumsq),
+                                                   N.ptr(o._flag), N.ptr(self.scratch), self.heap.next_epoch(), s),
+                        "dsb_fused_rs_norm")
+                K._count()
+        o._sumsq[1] = o._flag[0].float()
+        o._mp_owned_correction()
+        norm, bad = o._global_scalars()
+        for gi, arena in enumerate(o.arenas):
+            group = o.optimizer.param_groups[gi]
+            master = o.fp32_masters[gi]
+            st = o.optimizer.state[master]
+            group["step"] = group.get("step", 0) + 1
+            beta1, beta2 = group["betas"]
+            sub = o.sub_size[gi]
+            for k in range(o.num_buckets[gi]):
+                off = (k * o.partition_count + me) * sub
+                N.check(self.lib.dsb_fused_adam_ag(
+                    N.ptr(reds[(gi, k)]), N.ptr(o._master_slice(master.data, gi, k)),
+                    N.ptr(o._master_slice(st["exp_avg"], gi, k)), N.ptr(o._master_slice(st["exp_avg_sq"], gi, k)),
+                    self.param_ptrs[gi], self.flag_ptrs, R, me, off, sub, N.dtype_code(arena.dtype),
+                    float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), float(group["weight_decay"]),
+                    int(o.optimizer.adam_w_mode), int(group["bias_correction"]), int(group["step"]),
+                    N.ptr(o._inv_scale), N.ptr(o._skip), self.heap.next_epoch(), s), "dsb_fused_adam_ag")
+                K._count()
+        host = torch.stack([norm, bad.float()]).tolist()
+        overflow = bool(host[1])
+        o.overflow = overflow
+        o._global_grad_norm = -1 if overflow else host[0] / float(o._loss_scale())
+        prev = o._loss_scale()
+        o._on_step_result(overflow)
+        if overflow:
+            for group in o.optimizer.param_groups:
+                group["step"] = max(group.get("step", 1) - 1, 0)
+            logger.info("[deepspeed] OVERFLOW! Rank {} Skipping step. Attempted loss scale: {}, reducing to {}".format(
+                dist.get_rank(), prev, o._loss_scale()))
+        o.zero_grad()
+        return overflow

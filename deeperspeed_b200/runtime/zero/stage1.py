@@ -45,6 +45,15 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
         self.elastic_checkpoint = elastic_checkpoint
         self.precision = precision
         self.all_gather_partitions = all_gather_partitions
+        self._symm_heap = None
+        if fused_nvlink and allocator is None and getattr(init_optimizer, "supports_flat_fused", False):
+            # arenas go into a symmetric (peer-mapped) heap so the fused NVLink kernels can address every rank
+            from ...parallel.fused_zero import FusedZeroStep
+            try:
+                allocator, self._symm_heap = FusedZeroStep.make_allocator(init_optimizer.param_groups, dp_process_group)
+            except Exception as e:  # peer mapping unavailable (no P2P / IPC): stay on the NCCL path, loudly
+                logger.warning(f"[fused-zero] symmetric heap unavailable ({e!r}); using NCCL collectives")
+                allocator, self._symm_heap = None, None
         super().__init__(init_optimizer, dp_process_group=dp_process_group, shard=True, mpu=mpu, clip_grad=clip_grad,
                          max_elements_per_comm=max_elements_per_comm, fp32_allreduce=fp32_allreduce,
                          overlap_comm=overlap_comm, allocator=allocator,
