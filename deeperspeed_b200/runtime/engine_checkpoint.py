@@ -76,6 +76,10 @@ class CheckpointMixin:
         if isinstance(self, PipelineEngine):
             # pipeline parallelism keeps one file per layer next to the model-states file
             self._curr_ckpt_path = os.path.join(load_dir, tag)
+        if self.zero_optimization_partition_weights():
+            # the file holds shard placeholders: bring every parameter (also the persistent ones) to that state;
+            # the real values come from the fp32 shards in the optimizer checkpoint
+            self.optimizer.save_checkpoint_prologue()
         self.load_module_state_dict(state_dict=checkpoint["module"], strict=load_module_strict)
         if self.optimizer is not None and not self.zero_optimization():
             if self.fp16_enabled() and self.precision() != torch.float32:

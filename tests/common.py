@@ -71,3 +71,29 @@ def distributed_test(world_size=2, use_cuda=False):
         run.__name__ = fn.__name__
         return run
     return deco
+
+
+def run_distributed(fn, world_size=2, use_cuda=False, args=()):
+    """Run a MODULE-LEVEL function on `world_size` ranks (spawn-safe: needed once CUDA is initialised in the parent)."""
+    if use_cuda and torch.cuda.device_count() < world_size:
+        pytest.skip(f"needs {world_size} GPUs")
+    ctx = mp.get_context("spawn" if use_cuda else "fork")
+    errq = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world_size, port, fn, args, {}, errq, use_cuda)) for r in range(world_size)]
+    for p in procs:
+        p.start()
+    deadline = time.time() + DEEPSPEED_UNIT_WORKER_TIMEOUT
+    for p in procs:
+        p.join(max(0.0, deadline - time.time()))
+    hung = [p for p in procs if p.is_alive()]
+    for p in hung:
+        p.terminate()
+    if not errq.empty():
+        rank, tb = errq.get()
+        pytest.fail(f"worker {rank} failed:\n{tb}", pytrace=False)
+    if hung:
+        pytest.fail(f"{len(hung)} worker(s) hung", pytrace=False)
+    for p in procs:
+        if p.exitcode != 0:
+            pytest.fail(f"worker exited with code {p.exitcode}", pytrace=False)

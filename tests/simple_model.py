@@ -66,7 +66,7 @@ def random_dataloader(model, total_samples, hidden_dim, device, dtype=torch.floa
 
 
 def args_from_dict(tmpdir, config_dict):
-    config_path = os.path.join(str(tmpdir), "temp_config.json")
+    config_path = os.path.join(str(tmpdir), "temp_config_{}_{}.json".format(os.environ.get("RANK", 0), os.getpid()))
     with open(config_path, "w") as fd:
         json.dump(config_dict, fd)
     parser = argparse.ArgumentParser()

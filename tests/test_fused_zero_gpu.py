@@ -6,7 +6,7 @@ import torch
 import torch.distributed as dist
 
 import deeperspeed_b200 as deepspeed
-from common import distributed_test
+from common import run_distributed
 
 pytestmark = pytest.mark.gpu
 
@@ -40,21 +40,38 @@ def _run(fused, steps=4):
     return [p.detach().float().clone() for p in model.parameters()], opt
 
 
+def _fused_vs_nccl_worker():
+    global _ref_opt
+    ref, _ref_opt = _run(False)
+    got, opt = _run(True)
+    # Adam moves an element by ~lr per step whatever the gradient magnitude, so fp16-vs-fp32 reduction rounding of
+    # near-zero gradients may flip a sign: bound the drift by 2 * lr * steps and require the bulk to agree tightly
+    for a, b in zip(got, ref):
+        d = (a - b).abs()
+        assert d.max().item() <= 2 * 1e-3 * 4 + 1e-3, d.max().item()
+        assert (d > 2e-3).float().mean().item() < 0.02
+    # every rank sees identical parameters after the peer-store all-gather
+    flat = torch.cat([p.view(-1) for p in got])
+    other = flat.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(flat, other)
+    # exact check with injected gradients: both paths must produce the same update from the same (rank-dependent) grads
+    torch.manual_seed(77)
+    g = torch.randn(opt.arenas[0].numel, device="cuda") * 0.1 * (1 + dist.get_rank())
+    masters = []
+    for o in (opt, _ref_opt):
+        o.zero_grad()
+        o.arenas[0].grad.copy_(g.half())
+        before = o.fp32_masters[0].detach().clone()
+        o.step()
+        masters.append((o.fp32_masters[0].detach() - before))
+    torch.cuda.synchronize()
+    assert (masters[0] - masters[1]).abs().max().item() < 2e-5, (masters[0] - masters[1]).abs().max().item()
+    # overflow is skipped consistently through the device-side flag
+    opt.arenas[0].grad[7] = float("inf")
+    opt.step()
+    assert opt.overflow
+
+
 def test_fused_matches_nccl_path():
-    @distributed_test(world_size=2, use_cuda=True)
-    def run():
-        ref, _ = _run(False)
-        got, opt = _run(True)
-        for a, b in zip(got, ref):
-            assert (a - b).abs().max().item() < 2e-3, (a - b).abs().max().item()
-        # every rank sees identical parameters after the peer-store all-gather
-        flat = torch.cat([p.view(-1) for p in got])
-        other = flat.clone()
-        dist.broadcast(other, src=0)
-        assert torch.equal(flat, other)
-        # overflow is skipped consistently through the device-side flag
-        before = [p.clone() for p in got]
-        opt.arenas[0].grad[7] = float("inf")
-        opt.step()
-        assert opt.overflow
-    run()
+    run_distributed(_fused_vs_nccl_worker, world_size=2, use_cuda=True)
