@@ -1,0 +1,73 @@
+"""Compressed (1-bit, error-feedback) all-reduce: torch restatement vs an independent simulation on CPU/gloo, and the
+fused sm_100a kernel vs the restatement on 2 GPUs (oracle in the spirit of reference tests/unit/test_onebit.py:862-884)."""
+import pytest
+import torch
+import torch.distributed as dist
+
+from common import distributed_test, run_distributed
+
+
+def torch_sim(a, world, rank, group=None):
+    """All-gather everything and compute the two-phase result densely."""
+    n = a.numel()
+    c = n // world
+    scale = a.norm() / (n ** 0.5)
+    sgn = (a >= 0).float() * 2 - 1
+    ws = [torch.zeros_like(a) for _ in range(world)]
+    dist.all_gather(ws, scale * sgn, group=group)
+    avg = torch.stack(ws).mean(0)
+    out = []
+    for k in range(world):
+        chunk = avg[k * c:(k + 1) * c]
+        sc = chunk.norm() / (c ** 0.5)
+        out.append(sc * ((chunk >= 0).float() * 2 - 1))
+    return torch.cat(out)
+
+
+def _cpu_worker():
+    from deeperspeed_b200.runtime.comm.nccl import NcclBackend
+    world, rank = dist.get_world_size(), dist.get_rank()
+    backend = NcclBackend()
+    n = 64 * world * 4
+    torch.manual_seed(10 + rank)
+    a = (torch.rand(n) - 0.5) + 0.01 * rank
+    werr, serr = torch.zeros(n), torch.zeros(n // world)
+    want = torch_sim(a.clone(), world, rank)
+    got = backend.compressed_allreduce(a.clone(), werr, serr, rank)
+    assert torch.allclose(got, want, atol=1e-6), (got - want).abs().max()
+    # error feedback buffers are non-trivial and bounded
+    assert werr.abs().sum() > 0 and serr.abs().sum() > 0
+    # 2-D input keeps its shape; padded input (numel < error size) is cut back
+    b = torch.rand(8, n // 8) - 0.5
+    assert backend.compressed_allreduce(b, torch.zeros(n), torch.zeros(n // world), rank).shape == b.shape
+    s = torch.rand(n - 5) - 0.5
+    assert backend.compressed_allreduce(s, torch.zeros(n), torch.zeros(n // world), rank).numel() == n - 5
+
+
+def test_compressed_allreduce_cpu():
+    run_distributed(_cpu_worker, world_size=2, use_cuda=False)
+
+
+def _gpu_worker():
+    from deeperspeed_b200.runtime.comm.nccl import NcclBackend
+    world, rank = dist.get_world_size(), dist.get_rank()
+    fused, plain = NcclBackend(use_fused=True), NcclBackend(use_fused=False)
+    n = 32 * world * 4096
+    torch.manual_seed(10 + rank)
+    we_f, se_f = torch.zeros(n, device="cuda"), torch.zeros(n // world, device="cuda")
+    we_p, se_p = we_f.clone(), se_f.clone()
+    for it in range(3):   # several rounds so the error-feedback state is exercised
+        a = ((torch.rand(n, device="cuda") - 0.5) + 0.01 * rank)
+        got = fused.compressed_allreduce(a.clone(), we_f, se_f, rank)
+        want = plain.compressed_allreduce(a.clone(), we_p, se_p, rank)
+        torch.cuda.synchronize()
+        bad = (got - want).abs() > 1e-5
+        # a sign may legitimately differ where the server value is ~0 (summation order)
+        assert bad.float().mean().item() < 1e-3, (it, bad.float().mean().item())
+        assert torch.allclose(we_f, we_p, atol=1e-5)
+        assert (se_f - se_p).abs().mean().item() < 1e-4
+
+
+@pytest.mark.gpu
+def test_compressed_allreduce_fused_2gpu():
+    run_distributed(_gpu_worker, world_size=2, use_cuda=True)
