@@ -472,7 +472,7 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
                 assert self._is_supported_optimizer(self.optimizer_name()), \
                     "{} is not a supported DeepSpeed Optimizer".format(self.optimizer_name())
         if self.optimizer_name() in (C.LAMB_OPTIMIZER, C.ONEBIT_LAMB_OPTIMIZER):
-            assert self.dynamic_loss_scale(), \
+            assert self.dynamic_loss_scale() or self.precision() != torch.float16, \
                 "DeepSpeed {} optimizer requires dynamic loss scaling".format(self.optimizer_name())
 
     def _broadcast_model(self):

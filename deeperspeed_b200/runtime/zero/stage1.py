@@ -91,8 +91,23 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
     def _on_step_result(self, overflow):
         self.loss_scaler.update_scale(overflow)
 
+    def _use_fused(self):
+        return getattr(self, "fused", None) is not None and self.fused_inner
+
+    def reduce_gradients(self):
+        if self._use_fused():
+            # the fused step pulls the peers' raw gradients itself; an NCCL reduction here would double count
+            self._reduced = True
+            return
+        super().reduce_gradients()
+
+    def reduce_bucket(self, gi, k):
+        if self._use_fused():
+            return
+        super().reduce_bucket(gi, k)
+
     def step(self, closure=None):
-        if self.fused is not None and self.fused_inner:
+        if self._use_fused():
             return self.fused.step()
         return super().step(closure)
 

@@ -71,3 +71,38 @@ def _gpu_worker():
 @pytest.mark.gpu
 def test_compressed_allreduce_fused_2gpu():
     run_distributed(_gpu_worker, world_size=2, use_cuda=True)
+
+
+def _onebit_opt_worker(kind):
+    import deeperspeed_b200 as deepspeed
+    from simple_model import SimpleModel, random_dataset
+    cfg = {"train_batch_size": 4, "steps_per_print": 100,
+           "optimizer": {"type": kind, "params": {"lr": 0.01, "freeze_step": 3, "weight_decay": 0.0}},
+           "fp16": {"enabled": True, "type": "bfloat16"}}
+    torch.manual_seed(1)
+    model = SimpleModel(64)
+    engine, opt, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+    it = iter(torch.utils.data.DataLoader(random_dataset(256, 64, dtype=torch.bfloat16, seed=dist.get_rank()), batch_size=2))
+    losses = []
+    for step in range(8):
+        x, y = next(it)
+        loss = engine(x, y); engine.backward(loss); engine.step()
+        losses.append(loss.item())
+    inner = opt.optimizer
+    assert (inner.adam_freeze_key if kind == "OneBitAdam" else inner.lamb_freeze_key), "compression phase not entered"
+    assert engine.enable_backward_allreduce is False
+    assert all(l == l for l in losses)
+    # parameters stay identical across ranks: the compressed all-reduce returns the same momentum everywhere
+    flat = torch.cat([p.detach().float().view(-1) for p in model.parameters()])
+    ref = flat.clone()
+    dist.broadcast(ref, src=0)
+    assert torch.allclose(flat, ref, atol=1e-3), (flat - ref).abs().max()
+    # checkpoint: loading a compression-phase state re-enters compression and resets the error buffers
+    sd = inner.state_dict()
+    inner.load_state_dict(sd)
+    assert (inner.adam_freeze_key if kind == "OneBitAdam" else inner.lamb_freeze_key)
+
+
+@pytest.mark.parametrize("kind", ["OneBitAdam", "OneBitLamb"])
+def test_onebit_optimizers_cpu(kind):
+    run_distributed(_onebit_opt_worker, world_size=2, use_cuda=False, args=(kind,))
