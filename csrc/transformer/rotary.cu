@@ -1,0 +1,114 @@
+// Out-of-place, vectorised rotary embedding (GPT-NeoX half-split) with a precomputed cos/sin table.
+// Reads q/k straight out of the fused QKV activation (arbitrary batch/seq/head strides, unit last stride) and writes
+// rotated q/k into separately strided outputs (e.g. contiguous [B,S,H,D] buffers in forward, slices of the dQKV
+// buffer in backward), so no clone / slice-backward / zero-fill passes are needed around attention.
+#include "../common/ptx.cuh"
+#include "../../include/dsb200.h"
+
+namespace dsb {
+
+__global__ void rotary_table_kernel(float* __restrict__ cs, float* __restrict__ sn, int S, int half, float log2_base,
+                                    int rot) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S * half) return;
+    const int s = i / half, j = i % half;
+    const float inv_freq = exp2f(-log2_base * (2.f * j) / rot);
+    float a, b;
+    sincosf(s * inv_freq, &a, &b);
+    sn[i] = a;
+    cs[i] = b;
+}
+
+struct RotStrides {
+    long b, s, h;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) rotary_oop_kernel(const T* __restrict__ qi, const T* __restrict__ ki,
+                                                         T* __restrict__ qo, T* __restrict__ ko, int B, int S, int H,
+                                                         int D, int rot, RotStrides si, RotStrides so,
+                                                         const float* __restrict__ cs, const float* __restrict__ sn,
+                                                         float sign) {
+    const int half = rot >> 1;
+    const int hv = half >> 3;                  // 8-element vectors per rotated half
+    const int pv = (D - rot) >> 3;             // pass-through vectors
+    const int per_head = hv + pv;
+    const long total = (long)B * S * H * per_head;
+    const long stride = (long)gridDim.x * blockDim.x;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        long t = i;
+        const int v = t % per_head; t /= per_head;
+        const int h = t % H; t /= H;
+        const int s = t % S;
+        const int b = t / S;
+        const long oi = b * si.b + s * si.s + h * si.h;
+        const long oo = b * so.b + s * so.s + h * so.h;
+        if (v < hv) {
+            const int j = v * 8;
+            float c8[8], s8[8];
+            *reinterpret_cast<float4*>(c8) = __ldg(reinterpret_cast<const float4*>(cs + (long)s * half + j));
+            *reinterpret_cast<float4*>(c8 + 4) = __ldg(reinterpret_cast<const float4*>(cs + (long)s * half + j + 4));
+            *reinterpret_cast<float4*>(s8) = __ldg(reinterpret_cast<const float4*>(sn + (long)s * half + j));
+            *reinterpret_cast<float4*>(s8 + 4) = __ldg(reinterpret_cast<const float4*>(sn + (long)s * half + j + 4));
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                const T* in = w == 0 ? qi : ki;
+                T* out = w == 0 ? qo : ko;
+                float x0[8], x1[8], y0[8], y1[8];
+                unpack8<T>(*reinterpret_cast<const uint4*>(in + oi + j), x0);
+                unpack8<T>(*reinterpret_cast<const uint4*>(in + oi + j + half), x1);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const float sg = s8[e] * sign;
+                    y0[e] = x0[e] * c8[e] - x1[e] * sg;
+                    y1[e] = x1[e] * c8[e] + x0[e] * sg;
+                }
+                *reinterpret_cast<uint4*>(out + oo + j) = pack8<T>(y0);
+                *reinterpret_cast<uint4*>(out + oo + j + half) = pack8<T>(y1);
+            }
+        } else {
+            const int j = rot + (v - hv) * 8;
+            *reinterpret_cast<uint4*>(qo + oo + j) = *reinterpret_cast<const uint4*>(qi + oi + j);
+            *reinterpret_cast<uint4*>(ko + oo + j) = *reinterpret_cast<const uint4*>(ki + oi + j);
+        }
+    }
+}
+
+}  // namespace dsb
+
+using namespace dsb;
+
+extern "C" int dsb_rotary_table(float* cos_out, float* sin_out, int S, int rot_dim, float base, void* stream) {
+    const int half = rot_dim / 2;
+    const int n = S * half;
+    if (n <= 0) return 0;
+    rotary_table_kernel<<<(n + 255) / 256, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(cos_out, sin_out, S, half,
+                                                                                             log2f(base), rot_dim);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int dsb_rotary_oop(const void* q_in, const void* k_in, void* q_out, void* k_out, int B, int S, int H, int D,
+                              int rot_dim, long in_sb, long in_ss, long in_sh, long out_sb, long out_ss, long out_sh,
+                              const float* cos_tab, const float* sin_tab, int inverse, int dtype, void* stream) {
+    if (rot_dim % 16 || rot_dim > D || D % 8 || (in_sb | in_ss | in_sh | out_sb | out_ss | out_sh) % 8)
+        return DSB_ERR_SIZE;
+    const long total = (long)B * S * H * ((rot_dim / 2 + (D - rot_dim)) / 8);
+    if (total <= 0) return 0;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long blocks = (total + 255) / 256;
+    if (blocks > (long)sms * 16) blocks = (long)sms * 16;
+    RotStrides si{in_sb, in_ss, in_sh}, so{out_sb, out_ss, out_sh};
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const float sign = inverse ? -1.f : 1.f;
+    if (dtype == DSB_DTYPE_F16)
+        rotary_oop_kernel<__half><<<(unsigned)blocks, 256, 0, s>>>((const __half*)q_in, (const __half*)k_in, (__half*)q_out, (__half*)k_out, B, S, H, D, rot_dim, si, so, cos_tab, sin_tab, sign);
+    else if (dtype == DSB_DTYPE_BF16)
+        rotary_oop_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, s>>>((const __nv_bfloat16*)q_in, (const __nv_bfloat16*)k_in, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out, B, S, H, D, rot_dim, si, so, cos_tab, sin_tab, sign);
+    else
+        return DSB_ERR_DTYPE;
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}

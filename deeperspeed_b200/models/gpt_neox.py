@@ -11,6 +11,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from ..ops import kernels as K
+from ..ops.attention import causal_self_attention
 from ..runtime.pipe.module import LayerSpec, PipelineModule
 
 
@@ -78,12 +79,8 @@ class ParallelTransformerLayerPipe(nn.Module):
     def _attention(self, xn):
         B, S, h = xn.shape
         H, D = self.heads, self.head_dim
-        qkv = K.linear(xn, self.qkv_w, self.qkv_b).view(B, S, 3, H, D)
-        q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
-        if self.rot_dim > 0:
-            q, k = K.rotary(q, k, self.rot_dim, self.cfg.rotary_base)
-        ctx = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), is_causal=True)
-        return ctx.transpose(1, 2).reshape(B, S, h)
+        qkv = K.linear(xn, self.qkv_w, self.qkv_b)
+        return causal_self_attention(qkv, H, D, self.rot_dim, self.cfg.rotary_base)
 
     def forward(self, x):
         cfg = self.cfg

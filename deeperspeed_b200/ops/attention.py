@@ -1,0 +1,102 @@
+"""Causal self-attention block op for decoder models: fused-QKV in, context out.
+
+forward : rotary (our vectorised out-of-place kernel, reads q/k straight from the fused QKV activation) -> causal
+          flash attention (library SDPA) -> context [B, S, h]
+backward: attention backward -> inverse rotary written DIRECTLY into the dQKV buffer (no slice-backward zero fills,
+          no gradient-accumulation adds, no clones).
+"""
+import ctypes as C
+
+import torch
+import torch.nn.functional as F
+
+from . import kernels as K
+from . import native as N
+
+_p, _i, _l, _f = C.c_void_p, C.c_int, C.c_long, C.c_float
+N.register_sigs({
+    "dsb_rotary_table": [_p, _p, _i, _i, _f, _p],
+    "dsb_rotary_oop": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _p, _p, _i, _i, _p],
+})
+
+_tables = {}
+
+
+def rotary_table(S, rot_dim, base, device):
+    key = (S, rot_dim, float(base), device.index)
+    t = _tables.get(key)
+    if t is None:
+        half = rot_dim // 2
+        cs = torch.empty(S, half, dtype=torch.float32, device=device)
+        sn = torch.empty(S, half, dtype=torch.float32, device=device)
+        N.check(N.cuda_lib().dsb_rotary_table(N.ptr(cs), N.ptr(sn), S, rot_dim, float(base), N.stream_ptr()),
+                "dsb_rotary_table")
+        t = (cs, sn)
+        _tables[key] = t
+    return t
+
+
+def rotary_oop(q_in, k_in, q_out, k_out, rot_dim, base, inverse=False):
+    """q_in/k_in/q_out/k_out: [B, S, H, D] views with unit last stride (in and out may have different strides)."""
+    B, S, H, D = q_in.shape
+    assert q_in.stride() == k_in.stride() and q_out.stride() == k_out.stride()
+    cs, sn = rotary_table(S, rot_dim, base, q_in.device)
+    N.check(N.cuda_lib().dsb_rotary_oop(N.ptr(q_in), N.ptr(k_in), N.ptr(q_out), N.ptr(k_out), B, S, H, D, rot_dim,
+                                        q_in.stride(0), q_in.stride(1), q_in.stride(2), q_out.stride(0),
+                                        q_out.stride(1), q_out.stride(2), N.ptr(cs), N.ptr(sn), int(inverse),
+                                        N.dtype_code(q_in.dtype), N.stream_ptr()), "dsb_rotary_oop")
+    K._count()
+
+
+class CausalSelfAttentionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, H, D, rot_dim, base):
+        B, S = qkv.shape[0], qkv.shape[1]
+        qkv5 = qkv.view(B, S, 3, H, D)
+        q = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
+        k = torch.empty_like(q)
+        if rot_dim > 0:
+            rotary_oop(qkv5[:, :, 0], qkv5[:, :, 1], q, k, rot_dim, base)
+        else:
+            q.copy_(qkv5[:, :, 0])
+            k.copy_(qkv5[:, :, 1])
+        with torch.enable_grad():
+            ql, kl = q.requires_grad_(), k.requires_grad_()
+            vl = qkv5[:, :, 2].detach().requires_grad_()
+            out = F.scaled_dot_product_attention(ql.transpose(1, 2), kl.transpose(1, 2), vl.transpose(1, 2),
+                                                 is_causal=True)
+        ctx.graph = (ql, kl, vl, out)
+        ctx.meta = (B, S, H, D, rot_dim, base)
+        return out.detach().transpose(1, 2).reshape(B, S, H * D)
+
+    @staticmethod
+    def backward(ctx, dctx):
+        ql, kl, vl, out = ctx.graph
+        B, S, H, D, rot_dim, base = ctx.meta
+        dout = dctx.view(B, S, H, D).transpose(1, 2)
+        dq, dk, dv = torch.autograd.grad(out, (ql, kl, vl), dout)
+        ctx.graph = None
+        dqkv = torch.empty(B, S, 3, H, D, dtype=dctx.dtype, device=dctx.device)
+        if rot_dim > 0:
+            if dq.stride(-1) != 1 or dq.stride() != dk.stride():
+                dq, dk = dq.contiguous(), dk.contiguous()
+            rotary_oop(dq, dk, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
+        else:
+            dqkv[:, :, 0].copy_(dq)
+            dqkv[:, :, 1].copy_(dk)
+        dqkv[:, :, 2].copy_(dv)
+        return dqkv.view(B, S, 3 * H * D), None, None, None, None
+
+
+def causal_self_attention(qkv, H, D, rot_dim, base=10000.0):
+    """qkv: [B, S, 3*H*D] laid out (3, H, D). Returns the attention context [B, S, H*D]."""
+    if qkv.is_cuda and qkv.dtype in (torch.float16, torch.bfloat16) and D % 8 == 0 and (rot_dim % 16 == 0):
+        N.cuda_lib()
+        return CausalSelfAttentionFn.apply(qkv.contiguous(), H, D, rot_dim, base)
+    B, S = qkv.shape[0], qkv.shape[1]
+    t = qkv.view(B, S, 3, H, D)
+    q, k, v = t[:, :, 0], t[:, :, 1], t[:, :, 2]
+    if rot_dim > 0:
+        q, k = K._rotary_ref(q, k, rot_dim, base, False)
+    ctx = F.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), is_causal=True)
+    return ctx.transpose(1, 2).reshape(B, S, H * D)

@@ -99,6 +99,27 @@ def _gemm_ref(a, b, trans_a, trans_b, epilogue, alpha, bias, aux, aux_out, out):
     return res
 
 
+ACCUMULATE_INTO_GRAD = True   # wgrad GEMMs add straight into an existing .grad (arena view) via the epilogue
+
+
+def _wgrad(dy2, x2, w):
+    """dW = dy^T x. If the parameter already owns a gradient buffer (a view of the flat gradient arena), the GEMM
+    epilogue accumulates into it in place (no dW temporary, no separate add pass) and autograd gets None."""
+    g = w.grad
+    if ACCUMULATE_INTO_GRAD and g is not None and g.dtype == dy2.dtype and g.is_contiguous() and g.shape == w.shape:
+        gemm(dy2, x2, trans_a=True, trans_b=False, epilogue=N.EPI_BIAS_RESIDUAL, aux=g, out=g)
+        return None
+    return gemm(dy2, x2, trans_a=True, trans_b=False)
+
+
+def _bgrad(dy2, b):
+    g = b.grad
+    if ACCUMULATE_INTO_GRAD and g is not None and g.dtype == dy2.dtype and g.is_contiguous():
+        column_sum(dy2, out=g, accumulate=True)
+        return None
+    return column_sum(dy2)
+
+
 class LinearFn(torch.autograd.Function):
     """y = x @ W^T (+ b) with tcgen05 GEMMs for fwd / dgrad / wgrad; wgrad accumulates straight into `w.grad`
     storage when the engine has pre-allocated it in the flat gradient arena (no flatten/unflatten copies)."""
@@ -107,14 +128,14 @@ class LinearFn(torch.autograd.Function):
     def forward(ctx, x, w, b):
         x2 = x.reshape(-1, x.shape[-1])
         y = gemm(x2, w, trans_b=True, epilogue=N.EPI_BIAS if b is not None else N.EPI_NONE, bias=b)
-        ctx.save_for_backward(x2, w)
+        ctx.save_for_backward(x2, w, b)
         ctx.has_bias = b is not None
         ctx.x_shape = x.shape
         return y.view(*x.shape[:-1], w.shape[0])
 
     @staticmethod
     def backward(ctx, dy):
-        x2, w = ctx.saved_tensors
+        x2, w, b = ctx.saved_tensors
         dy2 = dy.reshape(-1, dy.shape[-1])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
@@ -122,9 +143,9 @@ class LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = gemm(dy2, w, trans_b=False).view(ctx.x_shape)
         if ctx.needs_input_grad[1]:
-            dw = gemm(dy2, x2, trans_a=True, trans_b=False)
+            dw = _wgrad(dy2, x2, w)
         if ctx.has_bias and ctx.needs_input_grad[2]:
-            db = column_sum(dy2)
+            db = _bgrad(dy2, b)
         return dx, dw, db
 
 
@@ -143,18 +164,18 @@ class LinearGeluFn(torch.autograd.Function):
         x2 = x.reshape(-1, x.shape[-1])
         pre = torch.empty((x2.shape[0], w.shape[0]), dtype=x.dtype, device=x.device)
         h = gemm(x2, w, trans_b=True, epilogue=N.EPI_BIAS_GELU, bias=b, aux_out=pre)
-        ctx.save_for_backward(x2, w, pre)
+        ctx.save_for_backward(x2, w, pre, b)
         ctx.x_shape = x.shape
         return h.view(*x.shape[:-1], w.shape[0])
 
     @staticmethod
     def backward(ctx, dh):
-        x2, w, pre = ctx.saved_tensors
+        x2, w, pre, b = ctx.saved_tensors
         dh2 = dh.reshape(-1, dh.shape[-1])
         dpre = bias_gelu_bwd(dh2.contiguous(), pre, None)
         dx = gemm(dpre, w, trans_b=False).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
-        dw = gemm(dpre, x2, trans_a=True, trans_b=False) if ctx.needs_input_grad[1] else None
-        db = column_sum(dpre) if ctx.needs_input_grad[2] else None
+        dw = _wgrad(dpre, x2, w) if ctx.needs_input_grad[1] else None
+        db = _bgrad(dpre, b) if ctx.needs_input_grad[2] else None
         return dx, dw, db
 
 
@@ -555,20 +576,20 @@ class LinearResidualFn(torch.autograd.Function):
         if not r2.is_contiguous():
             r2 = r2.contiguous()
         y = gemm(x2, w, trans_b=True, epilogue=N.EPI_BIAS_RESIDUAL, bias=b, aux=r2)
-        ctx.save_for_backward(x2, w)
+        ctx.save_for_backward(x2, w, b)
         ctx.has_bias = b is not None
         ctx.x_shape = x.shape
         return y.view(*x.shape[:-1], w.shape[0])
 
     @staticmethod
     def backward(ctx, dy):
-        x2, w = ctx.saved_tensors
+        x2, w, b = ctx.saved_tensors
         dy2 = dy.reshape(-1, dy.shape[-1])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         dx = gemm(dy2, w, trans_b=False).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
-        dw = gemm(dy2, x2, trans_a=True, trans_b=False) if ctx.needs_input_grad[1] else None
-        db = column_sum(dy2) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
+        dw = _wgrad(dy2, x2, w) if ctx.needs_input_grad[1] else None
+        db = _bgrad(dy2, b) if (ctx.has_bias and ctx.needs_input_grad[2]) else None
         return dx, dw, db, (dy if ctx.needs_input_grad[3] else None)
 
 

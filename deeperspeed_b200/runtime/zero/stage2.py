@@ -138,6 +138,8 @@ class FP16_DeepSpeedZeroOptimizer(ZeroShardedOptimizer):
 
     # ------------------------------------------------------------------ overlap of reduction with backward
     def _install_hooks(self):
+        # bucket readiness is driven by autograd's post-accumulate hooks, so gradients must flow through autograd
+        K.ACCUMULATE_INTO_GRAD = False
         for gi, arena in enumerate(self.arenas):
             span = self.partition_count * self.sub_size[gi]
             for s in arena.segments:

@@ -211,3 +211,38 @@ def test_adam_flat_and_sumsq(gdt):
     g[12345] = float("inf")
     K.sumsq(g, flag=flag)
     assert flag.item() == 1
+
+
+def test_wgrad_accumulates_into_existing_grad():
+    torch.manual_seed(11)
+    x = torch.randn(64, 256, device=DEV, dtype=torch.float16)
+    w = (torch.randn(512, 256, device=DEV, dtype=torch.float16) * 0.05).requires_grad_()
+    b = torch.zeros(512, device=DEV, dtype=torch.float16, requires_grad=True)
+    w.grad = torch.ones_like(w)
+    b.grad = torch.ones_like(b)
+    gptr = w.grad.data_ptr()
+    y = K.linear(x, w, b)
+    g = torch.randn_like(y)
+    y.backward(g)
+    assert w.grad.data_ptr() == gptr
+    assert _rel(w.grad, 1.0 + g.float().t() @ x.float()) < 3e-3
+    assert _rel(b.grad, 1.0 + g.float().sum(0)) < 3e-3
+
+
+def test_causal_self_attention_op():
+    from deeperspeed_b200.ops.attention import causal_self_attention
+    torch.manual_seed(12)
+    B, S, H, D = 2, 256, 4, 64
+    qkv = (torch.randn(B, S, 3 * H * D, device=DEV, dtype=torch.float16) * 0.5).requires_grad_()
+    out = causal_self_attention(qkv, H, D, rot_dim=D)
+    g = torch.randn_like(out)
+    out.backward(g)
+    ref_in = qkv.detach().float().cpu().requires_grad_()
+    t = ref_in.view(B, S, 3, H, D)
+    q, k = K._rotary_ref(t[:, :, 0], t[:, :, 1], D, 10000.0, False)
+    ctx = torch.nn.functional.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), t[:, :, 2].transpose(1, 2),
+                                                           is_causal=True)
+    ref = ctx.transpose(1, 2).reshape(B, S, H * D)
+    ref.backward(g.float().cpu())
+    assert _rel(out.cpu(), ref) < 5e-3
+    assert _rel(qkv.grad.cpu(), ref_in.grad) < 1e-2
