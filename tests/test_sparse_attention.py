@@ -1,0 +1,169 @@
+"""Block-sparse attention: layouts, matmul modes and softmax against dense-masked oracles
+(in the spirit of reference tests/unit/test_sparse_attention.py). CPU runs the emulation path; the GPU tests check
+the sm_100a kernels against the same oracle."""
+import pytest
+import torch
+
+from deeperspeed_b200.ops.sparse_attention import (MatMul, Softmax, SparseSelfAttention, FixedSparsityConfig,
+                                                   VariableSparsityConfig, BigBirdSparsityConfig,
+                                                   BSLongformerSparsityConfig, DenseSparsityConfig,
+                                                   LocalSlidingWindowSparsityConfig)
+from deeperspeed_b200.ops.sparse_attention.matmul import dense_to_sparse, sparse_to_dense, get_lut
+
+
+def _layout(H, nb, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    layout = (torch.rand(H, nb, nb, generator=g) < 0.4).long()
+    layout[:, torch.arange(nb), torch.arange(nb)] = 1
+    return layout
+
+
+def test_layouts():
+    f = FixedSparsityConfig(num_heads=4, block=16, num_local_blocks=4, num_global_blocks=1).make_layout(256)
+    assert f.shape == (4, 16, 16) and f[0, 0, :4].all() and f[0, 5, 3] == 1 and f[0, 0, 4] == 0
+    assert (f[0] == f[3]).all()
+    u = FixedSparsityConfig(num_heads=2, block=16, attention="unidirectional").make_layout(128)
+    assert torch.equal(u[0], torch.tril(u[0]))
+    assert DenseSparsityConfig(num_heads=2).make_layout(64).all()
+    v = VariableSparsityConfig(num_heads=2, num_random_blocks=1, local_window_blocks=[2, 4], global_block_indices=[0]).make_layout(256)
+    assert v[0, :, 0].all() and v[0, 0, 1] == 1
+    bb = BigBirdSparsityConfig(num_heads=2, num_random_blocks=1, num_sliding_window_blocks=3, num_global_blocks=1).make_layout(256)
+    assert bb[0, 0].all() and bb[0, :, 0].all() and bb[0, 5, 4] == 1 and bb[0, 5, 6] == 1
+    lf = BSLongformerSparsityConfig(num_heads=2, global_block_indices=[0, 5], global_block_end_indices=[1, 7]).make_layout(256)
+    assert lf[0, 5].all() and lf[0, :, 6].all()
+    sw = LocalSlidingWindowSparsityConfig(num_heads=2, num_sliding_window_blocks=3).make_layout(128)
+    assert sw[0, 3, 2] == 1 and sw[0, 3, 4] == 0
+    with pytest.raises(ValueError):
+        FixedSparsityConfig(num_heads=2).make_layout(100)
+
+
+def test_native_luts_and_segment():
+    layout = _layout(2, 8)
+    lut = get_lut(layout, 16)
+    assert lut.nnz == int(layout.sum())
+    nz = layout.nonzero()
+    assert torch.equal(lut.blocks[:, :3].long(), nz)
+    for hr in range(16):
+        cols = lut.row_idx[lut.row_ptr[hr]:lut.row_ptr[hr + 1], 0].long()
+        assert torch.equal(cols, layout.view(16, 8)[hr].nonzero().flatten())
+    ids, widths, counts = lut.sdd_segment(4)
+    assert ((ids >= 0) == (layout > 0)).all()
+    assert int((counts * torch.tensor([1, 4, 16])).sum()) == lut.nnz
+
+
+def _run_matmul_case(mode, trans_a, trans_b, device, dtype, block=16):
+    torch.manual_seed(0)
+    Bz, H, nb, D = 2, 2, 4, 32
+    S = nb * block
+    layout = _layout(H, nb, seed=3)
+
+    def dense(r, c):
+        return (torch.randn(Bz, H, r, c, device=device) * 0.5).to(dtype).requires_grad_()
+
+    if mode == "sdd":
+        a = dense(D, S) if trans_a else dense(S, D)
+        b = dense(S, D) if trans_b else dense(D, S)
+    elif mode == "dsd":
+        a = (torch.randn(Bz, int(layout.sum()), block, block, device=device) * 0.5).to(dtype).requires_grad_()
+        b = dense(D, S) if trans_b else dense(S, D)
+    else:
+        a = dense(S, D) if trans_a else dense(D, S)
+        b = (torch.randn(Bz, int(layout.sum()), block, block, device=device) * 0.5).to(dtype).requires_grad_()
+    op = MatMul(layout, block, mode, trans_a=trans_a, trans_b=trans_b)
+    c = op(a, b)
+    g = torch.randn_like(c)
+    c.backward(g)
+    # dense oracle
+    af = a.detach().float().cpu().requires_grad_()
+    bf = b.detach().float().cpu().requires_grad_()
+    A = sparse_to_dense(af, layout, block) if mode == "dsd" else af
+    Bm = sparse_to_dense(bf, layout, block) if mode == "dds" else bf
+    A = A.transpose(-1, -2) if trans_a else A
+    Bm = Bm.transpose(-1, -2) if trans_b else Bm
+    ref = A @ Bm
+    if mode == "sdd":
+        ref = dense_to_sparse(ref, layout, block)
+    ref.backward(g.float().cpu())
+    tol = 2e-2 if dtype != torch.float32 else 1e-4
+
+    def rel(x, y):
+        return ((x.float().cpu() - y).abs().max() / (y.abs().max() + 1e-6)).item()
+
+    assert rel(c.detach(), ref.detach()) < tol
+    assert rel(a.grad, af.grad) < tol and rel(b.grad, bf.grad) < tol
+
+
+@pytest.mark.parametrize("mode", ["sdd", "dsd", "dds"])
+@pytest.mark.parametrize("trans_a", [False, True])
+@pytest.mark.parametrize("trans_b", [False, True])
+def test_matmul_cpu(mode, trans_a, trans_b):
+    _run_matmul_case(mode, trans_a, trans_b, "cpu", torch.float32)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("block", [16, 32, 64])
+@pytest.mark.parametrize("mode,trans_a,trans_b", [("sdd", False, True), ("sdd", False, False), ("dsd", False, False),
+                                                  ("dsd", True, False), ("dds", False, False), ("dds", False, True)])
+def test_matmul_gpu(mode, trans_a, trans_b, block):
+    _run_matmul_case(mode, trans_a, trans_b, "cuda", torch.float16, block=block)
+
+
+def _run_softmax_case(device, dtype, block=16):
+    torch.manual_seed(1)
+    Bz, H, nb = 2, 2, 4
+    S = nb * block
+    layout = _layout(H, nb, seed=5)
+    x = (torch.randn(Bz, int(layout.sum()), block, block, device=device)).to(dtype).requires_grad_()
+    kpm = torch.zeros(Bz, S, device=device, dtype=dtype)
+    kpm[:, -3:] = -10000.0
+    am = torch.tril(torch.ones(S, S, device=device, dtype=dtype))
+    rpe = (torch.randn(H, S, S, device=device) * 0.1).to(dtype)
+    sm = Softmax(layout, block)
+    y = sm(x, scale=0.5, rpe=rpe, key_padding_mask=kpm, attn_mask=am, key_padding_mask_mode="add", attn_mask_mode="mul")
+    g = torch.randn_like(y)
+    y.backward(g)
+    xf = x.detach().float().cpu().requires_grad_()
+    d = sparse_to_dense(xf, layout, block, zero=float("-inf")) * 0.5 + rpe.float().cpu() + kpm.float().cpu()[:, None, None, :]
+    d = d.masked_fill(am.float().cpu()[None, None] == 0, float("-inf"))
+    p = torch.softmax(d, -1)
+    p = torch.where(torch.isnan(p), torch.zeros_like(p), p)
+    ref = dense_to_sparse(p, layout, block)
+    ref.backward(g.float().cpu())
+    tol = 2e-2 if dtype != torch.float32 else 1e-5
+    assert (y.detach().float().cpu() - ref.detach()).abs().max() < tol
+    assert (x.grad.float().cpu() - xf.grad).abs().max() < tol
+
+
+def test_softmax_cpu():
+    _run_softmax_case("cpu", torch.float32)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("block", [16, 32])
+def test_softmax_gpu(block):
+    _run_softmax_case("cuda", torch.float16, block)
+
+
+def _attn_case(device, dtype):
+    torch.manual_seed(2)
+    Bz, H, S, D = 2, 4, 128, 32
+    cfg = FixedSparsityConfig(num_heads=H, block=16, num_local_blocks=2, num_global_blocks=1)
+    attn = SparseSelfAttention(cfg, max_seq_length=S)
+    SparseSelfAttention.ops.clear()
+    q, k, v = ((torch.randn(Bz, H, S, D, device=device) * 0.5).to(dtype) for _ in range(3))
+    out = attn(q, k, v)
+    layout = cfg.make_layout(S)
+    mask = sparse_to_dense(torch.ones(1, int(layout.sum()), 16, 16), layout, 16)[0].bool()
+    sc = (q.float().cpu() @ k.float().cpu().transpose(-1, -2)) * D ** -0.5
+    sc = sc.masked_fill(~mask[None], float("-inf"))
+    ref = torch.softmax(sc, -1) @ v.float().cpu()
+    assert (out.float().cpu() - ref).abs().max() < (3e-2 if dtype != torch.float32 else 1e-4)
+
+
+def test_sparse_self_attention_cpu():
+    _attn_case("cpu", torch.float32)
+
+
+@pytest.mark.gpu
+def test_sparse_self_attention_gpu():
+    _attn_case("cuda", torch.float16)
