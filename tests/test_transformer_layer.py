@@ -1,0 +1,65 @@
+"""DeepSpeedTransformerLayer vs a plain-PyTorch BERT layer with identical weights (dropout 0): forward and
+per-parameter gradients (oracle strategy of reference tests/unit/test_cuda_forward.py / test_cuda_backward.py)."""
+import pytest
+import torch
+
+from deeperspeed_b200.models.bert import BertConfig, BertLayer, BertLayerPreLN
+from deeperspeed_b200.module_inject import replace_transformer_layer, revert_transformer_layer
+
+
+def _case(batch, hidden, seq, heads, preln, device, dtype, atol):
+    torch.manual_seed(0)
+    cfg = BertConfig(hidden_size=hidden, num_hidden_layers=2, num_attention_heads=heads, hidden_dropout_prob=0.0,
+                     attention_probs_dropout_prob=0.0)
+    cls = BertLayerPreLN if preln else BertLayer
+    ref = torch.nn.Sequential(cls(cfg)).to(device)
+    import copy
+    model = copy.deepcopy(ref).to(device, dtype)
+    model = replace_transformer_layer(cls, model, micro_batch_size=batch, bert_config=cfg, seed=1, max_seq_length=seq,
+                                      preln=preln, fp16=dtype == torch.float16)
+    ds_layer = model[0]
+    assert type(ds_layer).__name__ == "DeepSpeedTransformerLayer"
+    x = (torch.randn(batch, seq, hidden, device=device) * 0.5)
+    mask = torch.zeros(batch, 1, 1, seq, device=device)
+    mask[:, :, :, -3:] = -10000.0
+    xr = x.clone().requires_grad_()
+    xd = x.clone().to(dtype).requires_grad_()
+    ref.train(); ds_layer.train()
+    yr = ref[0](xr, mask)
+    yd = ds_layer(xd, mask.to(dtype))
+    assert (yd.float() - yr).abs().max().item() < atol, (yd.float() - yr).abs().max().item()
+    g = torch.randn_like(yr)
+    yr.backward(g)
+    yd.backward(g.to(dtype))
+
+    def close(a, b, name):
+        tol = atol * max(b.abs().mean().item(), 1e-3) * 8 + atol * 0.1
+        assert (a.float() - b).abs().max().item() < tol, (name, (a.float() - b).abs().max().item(), tol)
+
+    close(xd.grad, xr.grad, "dx")
+    r = ref[0]
+    qkv_w = torch.cat((r.attention.self.query.weight.grad, r.attention.self.key.weight.grad, r.attention.self.value.weight.grad))
+    close(ds_layer.attn_qkvw.grad, qkv_w, "qkv_w")
+    close(ds_layer.attn_ow.grad, r.attention.output.dense.weight.grad, "attn_ow")
+    inter = r.intermediate.dense_act if preln else r.intermediate.dense
+    close(ds_layer.inter_w.grad, inter.weight.grad, "inter_w")
+    close(ds_layer.inter_b.grad, inter.bias.grad, "inter_b")
+    close(ds_layer.output_w.grad, r.output.dense.weight.grad, "output_w")
+    ln = r.PreAttentionLayerNorm if preln else r.output.LayerNorm
+    close(ds_layer.norm_w.grad, ln.weight.grad, "norm_w")
+    # revert gives back an equivalent torch layer
+    back = revert_transformer_layer(cls, model, cfg, preln=preln)
+    assert type(back[0]).__name__ == cls.__name__
+
+
+@pytest.mark.parametrize("preln", [True, False])
+def test_layer_cpu(preln):
+    _case(2, 64, 24, 4, preln, "cpu", torch.float32, 2e-4)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,hidden,seq,heads,preln", [(8, 1024, 128, 16, True), (8, 1024, 128, 16, False),
+                                                         (3, 1024, 119, 16, True), (8, 1600, 128, 25, True),
+                                                         (8, 160, 128, 2, False), (2, 2048, 512, 16, True)])
+def test_layer_gpu(batch, hidden, seq, heads, preln):
+    _case(batch, hidden, seq, heads, preln, "cuda", torch.float16, 2e-2)
