@@ -1,0 +1,215 @@
+"""Smaller components: launcher parsing, CSR tensors, RepeatingLoader, PLD, flops profiler, activation checkpointing,
+optimizer selection matrix, argument parsing, deepspeed alias, batch-size scheduler, checkpoint tag validation."""
+import argparse
+import os
+import pickle
+
+import pytest
+import torch
+
+import deeperspeed_b200 as deepspeed
+from common import distributed_test
+from simple_model import SimpleModel, args_from_dict, random_dataloader
+
+
+def test_runner_filters_and_commands():
+    from deeperspeed_b200.launcher import runner as R
+    from deeperspeed_b200.launcher.multinode_runner import PDSHRunner, OpenMPIRunner, SlurmRunner
+    hosts = {"worker-0": [0, 1, 2, 3], "worker-1": [0, 1, 2, 3]}
+    assert R.parse_resource_filter(hosts, include_str="worker-1:0,2") == {"worker-1": [0, 2]}
+    assert R.parse_resource_filter(hosts, exclude_str="worker-0") == {"worker-1": [0, 1, 2, 3]}
+    with pytest.raises(ValueError):
+        R.parse_resource_filter(hosts, include_str="worker-1", exclude_str="worker-0")
+    with pytest.raises(ValueError):
+        R.parse_resource_filter(hosts, include_str="worker-9")
+    with pytest.raises(ValueError):
+        R.parse_resource_filter(hosts, include_str="worker-1:7")
+    args = R.parse_args(["--num_nodes", "1", "--num_gpus", "2", "--master_addr", "10.0.0.1", "train.py", "--foo", "bar"])
+    assert args.user_script == "train.py" and args.user_args == ["--foo", "bar"]
+    wi = R.encode_world_info(hosts)
+    cmd = PDSHRunner(args, wi).get_cmd({}, hosts)
+    assert cmd[0] == "pdsh" and "--node_rank=%n" in cmd and any("launcher.launch" in c for c in cmd)
+    args.hostfile = "/job/hostfile"
+    cmd = OpenMPIRunner(R.parse_args(["train.py"]), wi, {"a": 4, "b": 4}).get_cmd({}, hosts)
+    assert cmd[:3] == ["mpirun", "-n", "8"]
+    sargs = R.parse_args(["--launcher", "slurm", "--comment", "neox", "train.py"])
+    cmd = SlurmRunner(sargs, wi, {"a": 4, "b": 4}).get_cmd({}, hosts)
+    assert cmd[:3] == ["srun", "-n", "8"] and "--comment" in cmd and cmd[cmd.index("--comment") + 1] == "neox"
+
+
+def test_hostfile(tmp_path):
+    from deeperspeed_b200.launcher.runner import fetch_hostfile
+    f = tmp_path / "hostfile"
+    f.write_text("worker-0 slots=4\n# c\nworker-1 slots=2\n")
+    assert fetch_hostfile(str(f)) == {"worker-0": 4, "worker-1": 2}
+    f.write_text("worker-0 slots=4\nworker-0 slots=2\n")
+    with pytest.raises(ValueError):
+        fetch_hostfile(str(f))
+    assert fetch_hostfile(str(tmp_path / "nope")) is None
+
+
+def test_gpu_topology_parse():
+    from deeperspeed_b200.launcher.gpu_topology import detect_nvlink_pairs
+    text = ("\tGPU0\tGPU1\tGPU2\tGPU3\tCPU Affinity\n"
+            "GPU0\t X \tPIX\tNV2\tSYS\t0-15\nGPU1\tPIX\t X \tSYS\tNV2\t0-15\n"
+            "GPU2\tNV2\tSYS\t X \tPIX\t0-15\nGPU3\tSYS\tNV2\tPIX\t X \t0-15\n")
+    assert detect_nvlink_pairs(text) == [0, 2, 1, 3]
+
+
+def test_csr_and_repeating_loader_and_pld():
+    from deeperspeed_b200.runtime.csr_tensor import CSRTensor
+    from deeperspeed_b200.runtime.progressive_layer_drop import ProgressiveLayerDrop
+    import math
+    dense = torch.zeros(10, 4)
+    dense[3] = 1.0
+    dense[7] = 2.0
+    c = CSRTensor(dense)
+    assert c.indices.tolist() == [3, 7] and torch.equal(c.to_dense(), dense)
+    c.add(CSRTensor(dense))
+    assert torch.equal(c.to_dense(), 2 * dense)
+    loader = deepspeed.utils.RepeatingLoader([1, 2, 3])
+    assert [next(loader) for _ in range(7)] == [1, 2, 3, 1, 2, 3, 1]
+    pld = ProgressiveLayerDrop(theta=0.5, gamma=0.01)
+    pld.update_state(100)
+    assert abs(pld.get_theta() - (0.5 * math.exp(-1.0) + 0.5)) < 1e-9
+    assert pld.get_state() == {"progressive_layer_drop": True, "pld_theta": pld.get_theta()}
+
+
+def test_flops_profiler_lenet():
+    import torch.nn as nn
+    import torch.nn.functional as F
+    from deeperspeed_b200.profiling.flops_profiler import get_model_profile
+
+    class LeNet5(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.f = nn.Sequential(nn.Conv2d(1, 6, 5), nn.Tanh(), nn.AvgPool2d(2), nn.Conv2d(6, 16, 5), nn.Tanh(),
+                                   nn.AvgPool2d(2), nn.Conv2d(16, 120, 5), nn.Tanh())
+            self.c = nn.Sequential(nn.Linear(120, 84), nn.Tanh(), nn.Linear(84, 10))
+
+        def forward(self, x):
+            return F.softmax(self.c(torch.flatten(self.f(x), 1)), dim=1)
+
+    macs, params = get_model_profile(LeNet5(), (1024, 1, 32, 32), print_profile=False)
+    assert macs == "439.56 MMACs" and params == "61.71 k"
+
+
+def test_activation_checkpointing_matches_plain():
+    ckpt = deepspeed.checkpointing
+    torch.manual_seed(0)
+    lin = torch.nn.Sequential(torch.nn.Linear(16, 16), torch.nn.Dropout(0.3), torch.nn.Linear(16, 16))
+    x = torch.randn(4, 16, requires_grad=True)
+    mask = torch.ones(4, 16, dtype=torch.bool)
+
+    def fn(a, m, flag):
+        out = lin(a)
+        return out * m, (1 if flag else 0)
+
+    torch.manual_seed(5)
+    y_ref, _ = fn(x, mask, True)
+    y_ref.sum().backward()
+    gref = [p.grad.clone() for p in lin.parameters()]
+    xg = x.grad.clone()
+    for p in lin.parameters():
+        p.grad = None
+    x.grad = None
+    torch.manual_seed(5)
+    out = ckpt.checkpoint(fn, x, mask, True)
+    assert isinstance(out, tuple) and out[1] == 1
+    out[0].sum().backward()
+    assert torch.allclose(out[0], y_ref) and torch.allclose(x.grad, xg)
+    for p, g in zip(lin.parameters(), gref):
+        assert torch.allclose(p.grad, g)
+    ckpt.configure(None, partition_activations=False, profile=False)
+    assert ckpt.is_configured()
+    ckpt.get_cuda_rng_tracker().reset()
+    ckpt.model_parallel_cuda_manual_seed(123)
+    with ckpt.get_cuda_rng_tracker().fork():
+        a = torch.rand(3)
+    with ckpt.get_cuda_rng_tracker().fork():
+        b = torch.rand(3)
+    assert not torch.equal(a, b)
+
+
+def test_optimizer_selection_matrix(tmp_path):
+    @distributed_test(world_size=1)
+    def run():
+        from deeperspeed_b200.ops.adam import FusedAdam, DeepSpeedCPUAdam
+        cases = [("Adam", {}, False, FusedAdam, 1), ("AdamW", {}, False, FusedAdam, 1),
+                 ("Adam", {"adam_w_mode": False}, False, FusedAdam, 0),
+                 ("Adam", {"torch_adam": True}, False, torch.optim.AdamW, None),
+                 ("Adam", {"torch_adam": True, "adam_w_mode": False}, False, torch.optim.Adam, None),
+                 ("Adam", {}, True, DeepSpeedCPUAdam, True), ("Lamb", {}, False, None, None)]
+        for name, extra, offload, cls, wmode in cases:
+            cfg = {"train_batch_size": 2, "steps_per_print": 100,
+                   "optimizer": {"type": name, "params": dict({"lr": 0.001}, **extra)},
+                   "fp16": {"enabled": True, "type": "bfloat16"}}
+            if offload:
+                cfg["zero_optimization"] = {"stage": 2, "cpu_offload": True}
+            model = SimpleModel(8)
+            engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                     model_parameters=model.parameters())
+            inner = opt.optimizer
+            if cls is None:
+                assert type(opt).__name__ == "FP16_UnfusedOptimizer" and type(inner).__name__ == "FusedLamb"
+            else:
+                assert type(inner) is cls, (name, extra, type(inner))
+                if wmode is not None:
+                    assert inner.adam_w_mode == wmode
+    run()
+
+
+def test_add_config_arguments_and_alias():
+    parser = deepspeed.add_config_arguments(argparse.ArgumentParser())
+    args = parser.parse_args(["--deepspeed", "--deepspeed_config", "foo.json"])
+    assert args.deepspeed and args.deepspeed_config == "foo.json" and args.deepscale_config is None
+    deepspeed.install_deepspeed_alias()
+    import deepspeed as ds_alias
+    from deepspeed.runtime.fp16.loss_scaler import DynamicLossScaler
+    from deepspeed.runtime.pipe.schedule import TrainSchedule
+    from deepspeed.pipe import PipelineModule, LayerSpec
+    assert ds_alias.initialize is deepspeed.initialize
+    s = pickle.loads(pickle.dumps(DynamicLossScaler(init_scale=8)))
+    assert s.cur_scale == 8
+    import deepspeed.pt.loss_scaler as legacy
+    assert legacy.DynamicLossScaler is DynamicLossScaler
+
+
+def test_bs_scheduler_and_gns():
+    from deeperspeed_b200.runtime.bs_schedules import BatchSizeScheduler
+    s = BatchSizeScheduler(final_batch_size=64, start_batch_size=8, num_intervals=7, steps_per_interval=10,
+                           min_batch_size_multiplier=8)
+    seen = [s.step() for _ in range(75)]
+    assert seen[0] == 8 and seen[-1] == 64 and sorted(seen) == seen
+    from deeperspeed_b200.runtime.utils import GradientNoiseScale
+    m = torch.nn.Linear(4, 4)
+    gns = GradientNoiseScale(m, batch_size_small=2, n_batches=2)
+    for _ in range(6):
+        m.zero_grad()
+        m(torch.randn(2, 4)).sum().backward()
+        gns.update()
+    assert gns.n_updates == 6
+
+
+def test_engine_lr_scheduler_and_tag_validation(tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        import torch.distributed as dist
+        cfg = {"train_batch_size": 4, "steps_per_print": 100, "optimizer": {"type": "Adam", "params": {"lr": 0.01}},
+               "scheduler": {"type": "WarmupLR", "params": {"warmup_min_lr": 0, "warmup_max_lr": 0.01, "warmup_num_steps": 4}},
+               "checkpoint": {"tag_validation": "FAIL"}}
+        model = SimpleModel(8)
+        engine, _, _, sched = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=model.parameters())
+        assert type(sched).__name__ == "WarmupLR"
+        for x, y in random_dataloader(engine, 16, 8, engine.device):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        assert engine.get_lr()[0] == pytest.approx(0.01)
+        with pytest.raises(AssertionError):
+            engine.save_checkpoint(str(tmp_path), tag=f"rank{dist.get_rank()}")
+        engine.save_checkpoint(str(tmp_path), tag="same")
+        dist.barrier()   # rank 0 writes `latest` after the collective part of save_checkpoint
+        if dist.get_rank() == 0:
+            assert open(os.path.join(str(tmp_path), "latest")).read() == "same"
+        assert engine.load_checkpoint(str(tmp_path / "missing")) == (None, None)
+    run()
