@@ -37,6 +37,7 @@ struct GemmParams {
     long ldaux, stride_aux;
     void* aux_out;
     long ldaux_out, stride_aux_out;
+    int rows_per_rank;   // gather variant: rows of B owned by each rank
 };
 
 template <int BN> struct GemmCfg {
@@ -50,9 +51,16 @@ template <int BN> struct GemmCfg {
     static constexpr int TMEM_COLS = 2 * BN;  // 512 or 256, power of two
 };
 
-template <typename T, int BN>
+// NMAPS > 1: the B operand (K-major weight [N, K]) is row-sharded over NMAPS ranks; each rank's shard has its own
+// tensor map (peer-mapped memory), and the producer picks the map of the rank that owns the tile's rows. This is the
+// fused all-gather + GEMM of ZeRO-3: weight tiles travel over NVLink straight into shared memory, no gathered copy.
+template <int NMAPS> struct BMapSet {
+    CUtensorMap m[NMAPS];
+};
+
+template <typename T, int BN, int NMAPS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ BMapSet<NMAPS> tmBs,
                     const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
     using Cfg = GemmCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -76,7 +84,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
-        tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmBs.m[0]);
         tma_prefetch_desc(&tmD);
     }
     if (warp == 1 && lane == 0) {
@@ -132,11 +140,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             tma_load_3d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * BK, b);
                     }
                     if (!p.b_mn) {
-                        tma_load_3d(sb, &tmB, &full_bar[stage], kb * BK, n0, b);
+                        if (NMAPS == 1) {
+                            tma_load_3d(sb, &tmBs.m[0], &full_bar[stage], kb * BK, n0, b);
+                        } else {
+                            const int owner = n0 / p.rows_per_rank;
+                            tma_load_3d(sb, &tmBs.m[owner], &full_bar[stage], kb * BK, n0 - owner * p.rows_per_rank, b);
+                        }
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
-                            tma_load_3d(sb + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * BK, b);
+                            tma_load_3d(sb + j * (BK * 128), &tmBs.m[0], &full_bar[stage], n0 + j * 64, kb * BK, b);
                     }
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -335,12 +348,12 @@ static int make_map(CUtensorMap* m, int is_bf16, const void* base, uint64_t d0, 
     return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
 }
 
-template <typename T, int BN>
-static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const GemmParams& p, int sms,
+template <typename T, int BN, int NMAPS = 1>
+static int launch(const CUtensorMap& a, const BMapSet<NMAPS>& b, const CUtensorMap& d, const GemmParams& p, int sms,
                   cudaStream_t stream) {
     using Cfg = GemmCfg<BN>;
     static bool attr_set = false;
-    auto kern = gemm_tcgen05_kernel<T, BN>;
+    auto kern = gemm_tcgen05_kernel<T, BN, NMAPS>;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;
@@ -381,7 +394,9 @@ extern "C" int dsb_gemm(const void* A, const void* B, void* D, int M, int N, int
         strideB = (long)(b_mn_major ? K : N) * ldb;
         strideD = (long)M * ldd;
     }
-    CUtensorMap ta, tb, td;
+    CUtensorMap ta, td;
+    BMapSet<1> tbs;
+    CUtensorMap& tb = tbs.m[0];
     int rc;
     if (!a_mn_major) rc = make_map(&ta, bf, A, K, M, batch, lda, strideA, BK, BM);
     else rc = make_map(&ta, bf, A, M, K, batch, lda, strideA, 64, BK);
@@ -397,10 +412,53 @@ extern "C" int dsb_gemm(const void* A, const void* B, void* D, int M, int N, int
     p.epilogue = epilogue; p.alpha = alpha;
     p.bias = bias; p.aux = aux; p.ldaux = ldaux; p.stride_aux = stride_aux;
     p.aux_out = aux_out; p.ldaux_out = ldaux_out; p.stride_aux_out = stride_aux_out;
+    p.rows_per_rank = N;
     if (bf) {
-        return bn == 256 ? launch<__nv_bfloat16, 256>(ta, tb, td, p, sms, stream)
-                         : launch<__nv_bfloat16, 128>(ta, tb, td, p, sms, stream);
+        return bn == 256 ? launch<__nv_bfloat16, 256>(ta, tbs, td, p, sms, stream)
+                         : launch<__nv_bfloat16, 128>(ta, tbs, td, p, sms, stream);
     }
-    return bn == 256 ? launch<__half, 256>(ta, tb, td, p, sms, stream)
-                     : launch<__half, 128>(ta, tb, td, p, sms, stream);
+    return bn == 256 ? launch<__half, 256>(ta, tbs, td, p, sms, stream)
+                     : launch<__half, 128>(ta, tbs, td, p, sms, stream);
+}
+
+// Fused all-gather + GEMM (ZeRO-3): D = epi(A * W^T) where W [N, K] is row-sharded over `nranks` peers;
+// shard_ptrs[r] points at rank r's [N / nranks, K] slice (peer-mapped device memory, leading dimension ldb).
+extern "C" int dsb_gemm_gather_b(const void* A, void* const* shard_ptrs, int nranks, void* D, int M, int N, int K,
+                                 long lda, long ldb, long ldd, int dtype, int epilogue, float alpha, const void* bias,
+                                 const void* aux, long ldaux, void* stream_) {
+    using namespace dsb;
+    constexpr int MAXR = 8;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (M <= 0 || N <= 0 || K <= 0) return 0;
+    if (nranks < 1 || nranks > MAXR || (N % nranks)) return DSB_ERR_ARG;
+    const int rows = N / nranks;
+    if ((rows % 256) || (lda % 8) || (ldb % 8) || (ldd % 8)) return DSB_ERR_SIZE;
+    if ((epilogue == DSB_EPI_BIAS_RESIDUAL || epilogue == DSB_EPI_DGELU) && (!aux || (ldaux % 8))) return DSB_ERR_ARG;
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int bf = dtype == DSB_DTYPE_BF16;
+    CUtensorMap ta, td;
+    BMapSet<MAXR> tbs;
+    int rc = make_map(&ta, bf, A, K, M, 1, lda, (long)M * lda, BK, BM);
+    if (rc) return rc;
+    for (int r = 0; r < MAXR; ++r) {
+        const void* base = shard_ptrs[r < nranks ? r : 0];
+        rc = make_map(&tbs.m[r], bf, base, K, rows, 1, ldb, (long)rows * ldb, BK, 256);
+        if (rc) return rc;
+    }
+    rc = make_map(&td, bf, D, N, M, 1, ldd, (long)M * ldd, EPI_COLS, 32);
+    if (rc) return rc;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.batch = 1;
+    p.a_mn = 0; p.b_mn = 0;
+    p.epilogue = epilogue; p.alpha = alpha;
+    p.bias = bias; p.aux = aux; p.ldaux = ldaux; p.stride_aux = 0;
+    p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
+    p.rows_per_rank = rows;
+    if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);
+    return launch<__half, 256, MAXR>(ta, tbs, td, p, sms, stream);
 }

@@ -75,3 +75,25 @@ def _fused_vs_nccl_worker():
 
 def test_fused_matches_nccl_path():
     run_distributed(_fused_vs_nccl_worker, world_size=2, use_cuda=True)
+
+
+def _ag_gemm_worker():
+    from deeperspeed_b200.parallel.ag_gemm import ShardedWeight, ag_linear
+    torch.manual_seed(3)   # same full weight on every rank; each keeps only its rows
+    Nn, Kk, M = 2048, 1024, 512
+    w = (torch.randn(Nn, Kk, device="cuda") * 0.05).half()
+    b = torch.randn(Nn, device="cuda").half()
+    sw = ShardedWeight(w, group=None)
+    assert sw.supported()
+    torch.manual_seed(10 + dist.get_rank())
+    x = torch.randn(M, Kk, device="cuda").half()
+    y = ag_linear(x, sw, b)
+    torch.cuda.synchronize()
+    ref = x.float() @ w.float().t() + b.float()
+    rel = ((y.float() - ref).abs().max() / ref.abs().max()).item()
+    assert rel < 3e-3, rel
+    dist.barrier()
+
+
+def test_fused_allgather_gemm_2gpu():
+    run_distributed(_ag_gemm_worker, world_size=2, use_cuda=True)
