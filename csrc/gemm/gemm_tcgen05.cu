@@ -73,7 +73,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint64_t* tempty_bar = tfull_bar + 2;           // [2]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);   // provably warp-uniform role index
     const int lane = threadIdx.x & 31;
 
     const int m_blocks = (p.M + BM - 1) / BM;
@@ -120,7 +120,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
-        if (lane == 0) {
+        // elect.sync rather than lane == 0: ptxas then knows exactly one thread is active and emits UTMALDG / UTCHMMA
+        // directly instead of a per-active-lane serialisation loop around every one of them (137 -> ~50 SASS
+        // instructions per k-block in the MMA loop; the issuing thread was the bottleneck, profiles/gemm_ncu_v2.md).
+        if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -157,9 +160,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
     } else if (warp == 1) {
         // ------------------------------------------------------------------ MMA issuer (single thread)
-        if (lane == 0) {
+        if (elect_one()) {
             const uint32_t idesc = make_idesc_f16(BM, BN, sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value,
                                                   p.a_mn, p.b_mn);
+            // smem matrix descriptor = {hi: SBO 1024 B | version | SWIZZLE_128B, lo: address >> 4 | LBO >> 4 << 16};
+            // K-major: k-step = 16 elements (32 B) inside the swizzled 128-B row; MN-major: 16 k-rows (2048 B),
+            // LBO = next 64-element MN chunk. Stage and k-step advance only the address field.
+            constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t a_lo0 = ((smem_u32(smem) & 0x3FFFF) >> 4) | ((p.a_mn ? (BK * 128u) >> 4 : 1u) << 16);
+            const uint32_t b_lo0 =
+                (((smem_u32(smem) + Cfg::A_BYTES) & 0x3FFFF) >> 4) | ((p.b_mn ? (BK * 128u) >> 4 : 1u) << 16);
+            const uint32_t a_kstep = p.a_mn ? (2048u >> 4) : (32u >> 4);
+            const uint32_t b_kstep = p.b_mn ? (2048u >> 4) : (32u >> 4);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -172,18 +184,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-                    const uint32_t sb = sa + Cfg::A_BYTES;
+                    const uint32_t a_lo = a_lo0 + stage * (Cfg::STAGE_BYTES >> 4);
+                    const uint32_t b_lo = b_lo0 + stage * (Cfg::STAGE_BYTES >> 4);
 #pragma unroll
-                    for (int k = 0; k < BK / UMMA_K; ++k) {
-                        // K-major: advance 16 elements (32 B) inside the swizzled 128-B row.
-                        // MN-major: advance 16 k-rows (2 atoms of 8 rows x 128 B).
-                        const uint64_t da = p.a_mn ? make_smem_desc_sw128(sa + k * 2048, BK * 128, 1024)
-                                                   : make_smem_desc_sw128(sa + k * 32, 16, 1024);
-                        const uint64_t db = p.b_mn ? make_smem_desc_sw128(sb + k * 2048, BK * 128, 1024)
-                                                   : make_smem_desc_sw128(sb + k * 32, 16, 1024);
-                        umma_f16(d_tmem, da, db, idesc, (kb | k) != 0);
-                    }
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_f16_lohi(d_tmem, a_lo + k * a_kstep, b_lo + k * b_kstep, DESC_HI, idesc, (kb | k) != 0);
                     umma_commit(&empty_bar[stage]);
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }

@@ -5,6 +5,7 @@ PyTorch path so the engine/pipeline/ZeRO logic is testable without a GPU; the sa
 GPU numerics tests compare against.
 """
 import math
+import os
 
 import torch
 import torch.nn.functional as F
@@ -24,6 +25,19 @@ def _count(n=1):
 
 
 # ------------------------------------------------------------------------------------------------ GEMM
+# Tile policy: "auto" picks the CTA-pair (cta_group::2, 256 x 256) kernel for large outputs and the single-CTA kernel
+# (128 x 256 / 128 x 128 tiles) otherwise; "pair" / "single" force one (DSB_GEMM_KERNEL env, tools/bench_gemm.py).
+GEMM_KERNEL = os.environ.get("DSB_GEMM_KERNEL", "auto")
+
+
+def _use_pair(M, Nn, K, batch):
+    if GEMM_KERNEL == "pair":
+        return True
+    if GEMM_KERNEL == "single":
+        return False
+    return M >= 256 and Nn >= 128 and ((M + 255) // 256) * ((Nn + 127) // 128) * batch >= 64
+
+
 def gemm(a, b, *, trans_a=False, trans_b=True, epilogue=N.EPI_NONE, alpha=1.0, bias=None, aux=None, aux_out=None,
          out=None):
     """D = epi(alpha * op(a) @ op(b)).
@@ -57,10 +71,11 @@ def gemm(a, b, *, trans_a=False, trans_b=True, epilogue=N.EPI_NONE, alpha=1.0, b
         sb = 0
     s_aux = aux.stride(0) if (aux is not None and aux.dim() == 3) else 0
     s_auxo = aux_out.stride(0) if (aux_out is not None and aux_out.dim() == 3) else 0
-    rc = lib.dsb_gemm(N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, batch, a.stride(-2), b.stride(-2), out.stride(-2),
-                      sa, sb, sd, int(trans_a), int(not trans_b), N.dtype_code(a.dtype), epilogue, float(alpha),
-                      N.ptr(bias), N.ptr(aux), aux.stride(-2) if aux is not None else 0, s_aux, N.ptr(aux_out),
-                      aux_out.stride(-2) if aux_out is not None else 0, s_auxo, N.stream_ptr())
+    fn = lib.dsb_gemm_pair if _use_pair(M, Nn, K, batch) else lib.dsb_gemm
+    rc = fn(N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, batch, a.stride(-2), b.stride(-2), out.stride(-2),
+            sa, sb, sd, int(trans_a), int(not trans_b), N.dtype_code(a.dtype), epilogue, float(alpha),
+            N.ptr(bias), N.ptr(aux), aux.stride(-2) if aux is not None else 0, s_aux, N.ptr(aux_out),
+            aux_out.stride(-2) if aux_out is not None else 0, s_auxo, N.stream_ptr())
     N.check(rc, "dsb_gemm")
     _count()
     return out

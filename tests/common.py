@@ -28,7 +28,9 @@ def _worker(rank, world, port, fn, args, kwargs, errq, use_cuda):
         os.environ["WORLD_SIZE"] = str(world)
         if not use_cuda:
             os.environ["CUDA_VISIBLE_DEVICES"] = ""
-        torch.set_num_threads(2)
+        # forked children must not touch the parent's OpenMP pool (it does not survive fork once the parent has run a
+        # threaded op such as a conv): one thread => parallel regions run inline
+        torch.set_num_threads(2 if use_cuda else 1)
         import deeperspeed_b200 as deepspeed
         deepspeed.init_distributed(dist_backend="nccl" if use_cuda else "gloo", verbose=False)
         if use_cuda:

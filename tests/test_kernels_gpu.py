@@ -61,6 +61,65 @@ def test_gemm_epilogues(epi):
     assert _rel(out, ref) < 3e-3
 
 
+@pytest.fixture(params=[256, 128])
+def pair_kernel(monkeypatch, request):
+    """Force the CTA-pair kernel with 256- and 128-wide pair tiles."""
+    monkeypatch.setattr(K, "GEMM_KERNEL", "pair")
+    lib = N.cuda_lib()
+    assert lib.dsb_gemm_pair_force_bn(request.param) == 0
+    yield request.param
+    lib.dsb_gemm_pair_force_bn(0)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(256, 256, 64), (512, 768, 448), (1000, 264, 200), (4096, 2048, 2048),
+                                   (8192, 2048, 1024), (77, 64, 72)])
+@pytest.mark.parametrize("ta,tb", [(False, True), (False, False), (True, False), (True, True)])
+def test_gemm_pair_layouts(pair_kernel, dtype, shape, ta, tb):
+    """CTA-pair (cta_group::2) kernel, all four operand layouts incl. ragged edges."""
+    M, Nn, Kk = shape
+    if (M % 8 and ta) or (Nn % 8):
+        pytest.skip("leading dims must be multiples of 8")
+    torch.manual_seed(0)
+    a = torch.randn((Kk, M) if ta else (M, Kk), device=DEV, dtype=dtype)
+    b = torch.randn((Nn, Kk) if tb else (Kk, Nn), device=DEV, dtype=dtype)
+    out = K.gemm(a, b, trans_a=ta, trans_b=tb)
+    ref = (a.float().t() if ta else a.float()) @ (b.float().t() if tb else b.float())
+    assert _rel(out, ref) < (2e-3 if dtype == torch.float16 else 1.5e-2)
+
+
+@pytest.mark.parametrize("epi", ["bias_gelu", "residual", "dgelu"])
+def test_gemm_pair_epilogues(pair_kernel, epi):
+    torch.manual_seed(1)
+    M, Nn, Kk = 520, 1032, 512
+    dt = torch.float16
+    a = torch.randn(M, Kk, device=DEV, dtype=dt) * 0.1
+    b = torch.randn(Nn, Kk, device=DEV, dtype=dt) * 0.1
+    bias = torch.randn(Nn, device=DEV, dtype=dt)
+    aux = torch.randn(M, Nn, device=DEV, dtype=dt)
+    acc = a.float() @ b.float().t()
+    if epi == "bias_gelu":
+        pre = torch.empty(M, Nn, device=DEV, dtype=dt)
+        out = K.gemm(a, b, epilogue=N.EPI_BIAS_GELU, bias=bias, aux_out=pre)
+        ref = K.gelu_tanh(acc + bias.float())
+        assert _rel(pre, acc + bias.float()) < 2e-3
+    elif epi == "residual":
+        out = K.gemm(a, b, epilogue=N.EPI_BIAS_RESIDUAL, bias=bias, aux=aux)
+        ref = acc + bias.float() + aux.float()
+    else:
+        out = K.gemm(a, b, epilogue=N.EPI_DGELU, aux=aux)
+        ref = acc * K.gelu_tanh_grad(aux.float())
+    assert _rel(out, ref) < 3e-3
+
+
+def test_gemm_pair_batched(pair_kernel):
+    torch.manual_seed(2)
+    q = torch.randn(6, 512, 64, device=DEV, dtype=torch.float16)
+    k = torch.randn(6, 512, 64, device=DEV, dtype=torch.float16)
+    sc = K.gemm(q, k, trans_b=True, alpha=0.125)
+    assert _rel(sc, torch.matmul(q.float(), k.float().transpose(1, 2)) * 0.125) < 2e-3
+
+
 def test_gemm_batched_alpha():
     torch.manual_seed(2)
     B, S, D = 12, 256, 64

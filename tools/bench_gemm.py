@@ -30,13 +30,49 @@ for (M, N, Kk, ta, tb, tag) in [
     a = torch.randn((Kk, M) if ta else (M, Kk), device="cuda", dtype=dt)
     b = torch.randn((N, Kk) if tb else (Kk, N), device="cuda", dtype=dt)
     out = torch.empty(M, N, device="cuda", dtype=dt)
+    K.GEMM_KERNEL = "single"
     t_ours = timeit(lambda: K.gemm(a, b, trans_a=ta, trans_b=tb, out=out))
+    K.GEMM_KERNEL = "pair"
+    t_pair = timeit(lambda: K.gemm(a, b, trans_a=ta, trans_b=tb, out=out))
     at = a.t() if ta else a
     bt = b.t() if tb else b
     t_ref = timeit(lambda: torch.matmul(at, bt, out=out))
     fl = 2.0 * M * N * Kk
-    res.append(dict(tag=tag, M=M, N=N, K=Kk, ours_ms=round(t_ours, 4), cublas_ms=round(t_ref, 4),
-                    ours_tflops=round(fl / t_ours / 1e9, 1), cublas_tflops=round(fl / t_ref / 1e9, 1)))
+    res.append(dict(tag=tag, M=M, N=N, K=Kk, ours_ms=round(t_ours, 4), pair_ms=round(t_pair, 4), cublas_ms=round(t_ref, 4),
+                    ours_tflops=round(fl / t_ours / 1e9, 1), pair_tflops=round(fl / t_pair / 1e9, 1), cublas_tflops=round(fl / t_ref / 1e9, 1)))
     print(res[-1], flush=True)
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump(res, open("gpurun_out/bench_gemm.json", "w"), indent=1)
+
+# ---- sustained mode: 150 back-to-back launches per kernel (power-limited regime, how a training step runs them)
+def sustained(fn, iters=150):
+    for _ in range(10):
+        fn()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / iters
+
+sus = []
+for (M, N, Kk, tag) in [(8192, 6144, 2048, "qkv fwd"), (8192, 8192, 2048, "ff1 fwd"), (8192, 2048, 8192, "ff2 fwd"),
+                        (8192, 50432, 2048, "lm head")]:
+    a = torch.randn(M, Kk, device="cuda", dtype=dt)
+    b = torch.randn(N, Kk, device="cuda", dtype=dt)
+    out = torch.empty(M, N, device="cuda", dtype=dt)
+    r = dict(tag=tag, M=M, N=N, K=Kk)
+    fl = 2.0 * M * N * Kk
+    for rep in range(2):
+        for name in ("single", "pair", "cublas"):
+            if name == "cublas":
+                t = sustained(lambda: torch.matmul(a, b.t(), out=out))
+            else:
+                K.GEMM_KERNEL = name
+                t = sustained(lambda: K.gemm(a, b, out=out))
+            r[f"{name}_tflops_{rep}"] = round(fl / t / 1e9, 1)
+    sus.append(r)
+    print("sustained", r, flush=True)
+json.dump(dict(flushed=res, sustained=sus), open("gpurun_out/bench_gemm.json", "w"), indent=1)
