@@ -75,11 +75,10 @@ class GPT2Block(nn.Module):
 
     def forward(self, x):
         cfg = self.cfg
-        xn, _ = K.layer_norm(x, self.ln_1_w, self.ln_1_b, cfg.layer_norm_eps)
+        xn, xr = K.layer_norm(x, self.ln_1_w, self.ln_1_b, cfg.layer_norm_eps)   # xr aliases x (see K.layer_norm)
         a = K.linear(self._attention(xn), self.c_proj_w, self.c_proj_b)
-        yn, r1 = K.layer_norm(a, self.ln_2_w, self.ln_2_b, cfg.layer_norm_eps, residual=x)
-        f = K.linear_gelu(yn, self.c_fc_w, self.c_fc_b)
-        return K.linear_residual(f, self.mlp_proj_w, self.mlp_proj_b, r1)
+        yn, r1 = K.layer_norm(a, self.ln_2_w, self.ln_2_b, cfg.layer_norm_eps, residual=xr)
+        return K.mlp_residual(yn, self.c_fc_w, self.c_fc_b, self.mlp_proj_w, self.mlp_proj_b, r1)
 
 
 class GPT2Model(nn.Module):

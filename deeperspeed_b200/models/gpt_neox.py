@@ -84,19 +84,20 @@ class ParallelTransformerLayerPipe(nn.Module):
 
     def forward(self, x):
         cfg = self.cfg
-        xn, _ = K.layer_norm(x, self.input_layernorm_w, self.input_layernorm_b, cfg.layernorm_eps)
+        # `xr` aliases x: the residual stream is threaded through the LayerNorm ops so that its gradient is added
+        # inside their backward kernels (no stand-alone accumulation adds in autograd)
+        xn, xr = K.layer_norm(x, self.input_layernorm_w, self.input_layernorm_b, cfg.layernorm_eps)
         ctx = self._attention(xn)
         if cfg.parallel_residual:
-            yn, _ = K.layer_norm(x, self.post_attention_layernorm_w, self.post_attention_layernorm_b, cfg.layernorm_eps)
-            a = K.linear_residual(ctx, self.dense_w, self.dense_b, x)
-            f = K.linear_gelu(yn, self.h_to_4h_w, self.h_to_4h_b)
-            return K.linear_residual(f, self.four_h_to_h_w, self.four_h_to_h_b, a)
+            yn, xr = K.layer_norm(xr, self.post_attention_layernorm_w, self.post_attention_layernorm_b,
+                                  cfg.layernorm_eps)
+            a = K.linear_residual(ctx, self.dense_w, self.dense_b, xr)
+            return K.mlp_residual(yn, self.h_to_4h_w, self.h_to_4h_b, self.four_h_to_h_w, self.four_h_to_h_b, a)
         a = K.linear(ctx, self.dense_w, self.dense_b)
         # LN(x + a) and the new residual stream x + a come out of one kernel
         yn, r1 = K.layer_norm(a, self.post_attention_layernorm_w, self.post_attention_layernorm_b, cfg.layernorm_eps,
-                              residual=x)
-        f = K.linear_gelu(yn, self.h_to_4h_w, self.h_to_4h_b)
-        return K.linear_residual(f, self.four_h_to_h_w, self.four_h_to_h_b, r1)
+                              residual=xr)
+        return K.mlp_residual(yn, self.h_to_4h_w, self.h_to_4h_b, self.four_h_to_h_w, self.four_h_to_h_b, r1)
 
 
 class NormPipe(nn.Module):

@@ -315,7 +315,10 @@ def _ln_ref(x, res, gamma, beta, eps):
 
 
 class LayerNormFn(torch.autograd.Function):
-    """y = LN(x [+ residual]); returns (y, x + residual) so the residual stream is produced by the same pass."""
+    """y = LN(x [+ residual]); returns (y, s) with s = x + residual produced by the same pass. Without a residual, s
+    is an alias of x: routing the residual stream through it hands the stream's gradient to THIS backward, which
+    adds it inside the LN-backward kernel (`dres`) instead of leaving a separate accumulation add to autograd.
+    gamma/beta gradients are accumulated straight into existing `.grad` buffers by the finalize kernel."""
 
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, eps):
@@ -332,40 +335,52 @@ class LayerNormFn(torch.autograd.Function):
                                                rows, hidden, float(eps), N.dtype_code(x.dtype), N.stream_ptr()),
                 "dsb_layernorm_fwd")
         _count()
-        ctx.save_for_backward(ssum, mean, rstd, gamma)
+        ctx.save_for_backward(ssum, mean, rstd, gamma, beta)
         ctx.has_res = residual is not None
         ctx.shape = x.shape
+        ctx.set_materialize_grads(False)
         if residual is not None:
             return y.view(x.shape), ssum.view(x.shape)
-        return y.view(x.shape)
+        return y.view(x.shape), x.detach()
 
     @staticmethod
-    def backward(ctx, dy, dsum=None):
-        ssum, mean, rstd, gamma = ctx.saved_tensors
+    def backward(ctx, dy, dsum):
+        ssum, mean, rstd, gamma, beta = ctx.saved_tensors
         hidden = ssum.shape[-1]
         rows = ssum.shape[0]
+        if dy is None:   # only the pass-through stream was used downstream
+            return dsum, (dsum if ctx.has_res else None), None, None, None
         dy2 = dy.reshape(-1, hidden).contiguous()
         dres = dsum.reshape(-1, hidden).contiguous() if dsum is not None else None
         dx = torch.empty_like(ssum)
-        dgamma = torch.empty_like(gamma)
-        dbeta = torch.empty_like(gamma)
+        gg, gb = gamma.grad, beta.grad
+        acc = (ACCUMULATE_INTO_GRAD and gg is not None and gb is not None and gg.dtype == ssum.dtype
+               and gb.dtype == ssum.dtype and gg.is_contiguous() and gb.is_contiguous())
+        if acc:
+            dgamma, dbeta = gg, gb
+        else:
+            dgamma = torch.empty_like(gamma)
+            dbeta = torch.empty_like(gamma)
         lib = N.cuda_lib()
         sc = N.scratch(lib.dsb_layernorm_bwd_scratch_bytes(hidden), ssum.device, "ln_bwd")
-        N.check(lib.dsb_layernorm_bwd(N.ptr(dy2), N.ptr(ssum), N.ptr(mean), N.ptr(rstd), N.ptr(gamma), N.ptr(dres),
-                                      N.ptr(dx), N.ptr(dgamma), N.ptr(dbeta), rows, hidden,
-                                      N.dtype_code(ssum.dtype), N.ptr(sc), N.stream_ptr()), "dsb_layernorm_bwd")
+        N.check(lib.dsb_layernorm_bwd_acc(N.ptr(dy2), N.ptr(ssum), N.ptr(mean), N.ptr(rstd), N.ptr(gamma), N.ptr(dres),
+                                          N.ptr(dx), N.ptr(dgamma), N.ptr(dbeta), rows, hidden,
+                                          N.dtype_code(ssum.dtype), int(acc), N.ptr(sc), N.stream_ptr()),
+                "dsb_layernorm_bwd")
         _count(2)
         dx = dx.view(ctx.shape)
+        if acc:
+            dgamma = dbeta = None
         return dx, (dx if ctx.has_res else None), dgamma, dbeta, None
 
 
 def layer_norm(x, gamma, beta, eps=1e-5, residual=None):
-    """Returns (LN(x + residual), x + residual). With residual=None the second output is x itself."""
+    """Returns (LN(x + residual), x + residual). With residual=None the second output is an alias of x: use it (not
+    x) as the residual stream downstream so the stream's gradient is folded into the LN backward kernel."""
     if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16) and x.shape[-1] % 8 == 0 and x.shape[-1] <= 8192:
         N.cuda_lib()
-        if residual is not None:
-            return LayerNormFn.apply(x.contiguous(), residual.contiguous(), gamma, beta, eps)
-        return LayerNormFn.apply(x.contiguous(), None, gamma, beta, eps), x
+        return LayerNormFn.apply(x.contiguous(), residual.contiguous() if residual is not None else None, gamma,
+                                 beta, eps)
     s = x if residual is None else x + residual
     return F.layer_norm(s, (s.shape[-1],), gamma, beta, eps), s
 
@@ -612,3 +627,49 @@ def linear_residual(x, w, b, r):
     if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16):
         return LinearResidualFn.apply(x, w, b, r)
     return F.linear(x, w, b) + r
+
+
+class MlpResidualFn(torch.autograd.Function):
+    """y = gelu(x @ W1^T + b1) @ W2^T + b2 + r as four GEMMs with every elementwise step in an epilogue:
+    forward bias+GeLU (keeps the pre-activation) and bias+residual; backward gelu'(pre) is applied in the epilogue
+    of the FF2 dgrad GEMM, so the 4h-wide gradient is written once and never re-read by a separate kernel
+    (the reference runs d_gelu as its own pass, csrc/transformer/gelu_kernels.cu:187-330)."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, r):
+        x2 = x.reshape(-1, x.shape[-1])
+        r2 = r.reshape(-1, r.shape[-1])
+        if not r2.is_contiguous():
+            r2 = r2.contiguous()
+        pre = torch.empty((x2.shape[0], w1.shape[0]), dtype=x.dtype, device=x.device)
+        h = gemm(x2, w1, trans_b=True, epilogue=N.EPI_BIAS_GELU, bias=b1, aux_out=pre)
+        y = gemm(h, w2, trans_b=True, epilogue=N.EPI_BIAS_RESIDUAL, bias=b2, aux=r2)
+        ctx.save_for_backward(x2, w1, b1, w2, b2, pre, h)
+        ctx.x_shape = x.shape
+        return y.view(*x.shape[:-1], w2.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, b1, w2, b2, pre, h = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        need = ctx.needs_input_grad
+        dw2 = _wgrad(dy2, h, w2) if need[3] else None
+        db2 = _bgrad(dy2, b2) if (b2 is not None and need[4]) else None
+        dx = dw1 = db1 = None
+        if need[0] or need[1] or need[2]:
+            dpre = gemm(dy2, w2, trans_b=False, epilogue=N.EPI_DGELU, aux=pre)
+            if need[0]:
+                dx = gemm(dpre, w1, trans_b=False).view(ctx.x_shape)
+            if need[1]:
+                dw1 = _wgrad(dpre, x2, w1)
+            if b1 is not None and need[2]:
+                db1 = _bgrad(dpre, b1)
+        return dx, dw1, db1, dw2, db2, (dy if need[5] else None)
+
+
+def mlp_residual(x, w1, b1, w2, b2, r):
+    if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16):
+        return MlpResidualFn.apply(x, w1, b1, w2, b2, r)
+    return F.linear(gelu_tanh(F.linear(x, w1, b1)), w2, b2) + r

@@ -32,6 +32,7 @@ _CUDA_SIGS = {
     "dsb_scale": [_p, _i, _l, _f, _p, _p],
     "dsb_layernorm_fwd": [_p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _f, _i, _p],
     "dsb_layernorm_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _p, _p],
+    "dsb_layernorm_bwd_acc": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _i, _p, _p],
     "dsb_softmax_fwd": [_p, _p, _p, _i, _i, _i, _i, _f, _i, _i, _p],
     "dsb_softmax_bwd": [_p, _p, _p, _l, _i, _f, _i, _p],
     "dsb_bias_gelu_fwd": [_p, _p, _p, _l, _i, _i, _p],

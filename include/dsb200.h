@@ -81,6 +81,10 @@ long dsb_layernorm_bwd_scratch_bytes(int hidden);
 int dsb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
                       const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden, int dtype,
                       void* scratch, void* stream);
+/* Same; accumulate != 0 adds the gamma/beta gradients into dgamma/dbeta (the parameters' .grad storage). */
+int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
+                          const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden, int dtype,
+                          int accumulate, void* scratch, void* stream);
 /* y = softmax(x * scale + mask) over the last dim. x: [batch, heads, q_len, k_len]; mask: additive [batch, k_len]
  * or NULL; causal != 0 masks k > q + (k_len - q_len). In place allowed.
  * Reference: csrc/transformer/softmax_kernels.cu:8-431. */

@@ -27,7 +27,19 @@ def test_gemm_layouts(dtype, shape, ta, tb):
         pytest.skip("leading dims must be multiples of 8")
     out = K.gemm(a, b, trans_a=ta, trans_b=tb)
     ref = (a.float().t() if ta else a.float()) @ (b.float().t() if tb else b.float())
-    assert _rel(out, ref) < (2e-3 if dtype == torch.float16 else 1.5e-2)
+    tol = 2e-3 if dtype == torch.float16 else 1.5e-2
+    assert _rel(out, ref) < tol, _where(out, ref, tol)
+
+
+def _where(out, ref, tol):
+    """Failure message: where the mismatching elements sit (which tile / CTA half / epilogue chunk)."""
+    err = (out.float() - ref).abs()
+    bad = (err > tol * ref.abs().max()).nonzero()
+    if bad.numel() == 0:
+        return "no element above tolerance"
+    r, c = bad[:, -2], bad[:, -1]
+    return (f"{bad.shape[0]} bad elements, max err {err.max().item():.4f}, rows {r.min().item()}..{r.max().item()}, "
+            f"cols {c.min().item()}..{c.max().item()}, first {bad[:8].tolist()}")
 
 
 @pytest.mark.parametrize("epi", ["bias", "bias_gelu", "residual", "dgelu", "accum"])
@@ -147,6 +159,54 @@ def test_linear_autograd():
     assert _rel(x.grad, xf.grad) < 5e-3
     assert _rel(w.grad, wf.grad) < 5e-3
     assert _rel(b.grad, bf.grad) < 5e-3
+
+
+def test_layernorm_passthrough_and_grad_accumulate():
+    """Residual stream routed through the LN op (alias output) + gamma/beta gradients accumulated in place."""
+    torch.manual_seed(6)
+    rows, hidden = 130, 2048
+    x = torch.randn(rows, hidden, device=DEV, dtype=torch.float16, requires_grad=True)
+    g = (1 + 0.1 * torch.randn(hidden, device=DEV, dtype=torch.float16)).requires_grad_()
+    b = (0.1 * torch.randn(hidden, device=DEV, dtype=torch.float16)).requires_grad_()
+    g.grad = torch.ones_like(g)
+    b.grad = torch.full_like(b, 2.0)
+    gbuf, bbuf = g.grad, b.grad
+    y, xr = K.layer_norm(x, g, b, 1e-5)
+    assert xr.data_ptr() == x.data_ptr()
+    gy, gs = torch.randn_like(y), torch.randn_like(y)
+    ((y * gy).sum() + (xr * gs).sum()).backward()
+    xf, gf, bf = (t.detach().float().requires_grad_() for t in (x, g, b))
+    yf = torch.nn.functional.layer_norm(xf, (hidden,), gf, bf, 1e-5)
+    ((yf * gy.float()).sum() + (xf * gs.float()).sum()).backward()
+    assert _rel(y, yf) < 4e-3 and _rel(x.grad, xf.grad) < 4e-3
+    assert g.grad is gbuf and b.grad is bbuf          # accumulated in place, no new tensors
+    assert _rel(g.grad, gf.grad + 1.0) < 4e-3 and _rel(b.grad, bf.grad + 2.0) < 4e-3
+    # only the pass-through used
+    x2 = x.detach().clone().requires_grad_()
+    _, xr2 = K.layer_norm(x2, g, b, 1e-5)
+    (xr2 * gs).sum().backward()
+    assert torch.equal(x2.grad, gs)
+
+
+def test_mlp_residual_autograd():
+    """Fused MLP block (gelu' in the FF2 dgrad epilogue) against fp32 autograd."""
+    torch.manual_seed(5)
+    x = torch.randn(3, 128, 256, device=DEV, dtype=torch.float16, requires_grad=True)
+    r = torch.randn(3, 128, 256, device=DEV, dtype=torch.float16, requires_grad=True)
+    w1 = (torch.randn(1024, 256, device=DEV, dtype=torch.float16) * 0.05).requires_grad_()
+    b1 = (torch.randn(1024, device=DEV, dtype=torch.float16) * 0.1).requires_grad_()
+    w2 = (torch.randn(256, 1024, device=DEV, dtype=torch.float16) * 0.05).requires_grad_()
+    b2 = (torch.randn(256, device=DEV, dtype=torch.float16) * 0.1).requires_grad_()
+    y = K.mlp_residual(x, w1, b1, w2, b2, r)
+    g = torch.randn_like(y)
+    y.backward(g)
+    ref_in = [t.detach().float().requires_grad_() for t in (x, w1, b1, w2, b2, r)]
+    xf, w1f, b1f, w2f, b2f, rf = ref_in
+    yr = torch.nn.functional.linear(K.gelu_tanh(torch.nn.functional.linear(xf, w1f, b1f)), w2f, b2f) + rf
+    yr.backward(g.float())
+    assert _rel(y, yr) < 3e-3
+    for t, tf in zip((x, w1, b1, w2, b2, r), ref_in):
+        assert _rel(t.grad, tf.grad) < 6e-3
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
