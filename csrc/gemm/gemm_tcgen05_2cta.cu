@@ -38,11 +38,31 @@ struct Cfg {
     static constexpr int TMEM_COLS = 2 * BN;
 };
 
+// Work units. The first `full_tiles` units are whole output tiles. When the tile count leaves the last wave of CTA
+// pairs mostly idle (256 tiles on 74 pairs = 3.46 waves), the remaining `tail_tiles` tiles are each cut into `split`
+// K-slices of `kpp` k-blocks: slices 0..split-2 ("contributors") park their fp32 accumulators in a workspace and raise
+// a flag, the last slice ("owner") adds them in its epilogue and writes the tile. Units are numbered
+// [full tiles][all slices 0][all slices 1]...[owners] and every pair walks its units in increasing order, so each
+// contributor precedes every owner on every pair and never waits itself: no deadlock with all pairs resident.
 struct Params {
     EpiParams e;
     int K, batch;
     int a_mn, b_mn;
+    int full_tiles, tail_tiles, split, kpp;
+    float* ws;      // [tail_tiles][split - 1][2 CTAs][4 warps] regions of BN x 32 floats
+    int* flags;     // [tail_tiles][2][4], zero between launches
 };
+
+enum { ROLE_FULL = 0, ROLE_CONTRIB = 1, ROLE_OWNER = 2 };
+
+DSB_DEVICE void red_release_add(int* p, int v) {
+    asm volatile("red.release.gpu.global.add.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+DSB_DEVICE int ld_acquire_gpu(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 
 template <typename T, int BN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
@@ -111,6 +131,22 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         nb = r / gsz;
     };
 
+    const int num_units = p.full_tiles + p.tail_tiles * p.split;
+    (void)num_tiles;
+    auto unit_of = [&](int u, int& tile, int& kb0, int& kb1, int& role, int& tt, int& piece) {
+        if (u < p.full_tiles) {
+            tile = u; kb0 = 0; kb1 = k_blocks; role = ROLE_FULL; tt = 0; piece = 0;
+        } else {
+            const int v = u - p.full_tiles;
+            piece = v / p.tail_tiles;
+            tt = v - piece * p.tail_tiles;
+            tile = p.full_tiles + tt;
+            kb0 = piece * p.kpp;
+            kb1 = min(kb0 + p.kpp, k_blocks);
+            role = p.split == 1 ? ROLE_FULL : (piece == p.split - 1 ? ROLE_OWNER : ROLE_CONTRIB);
+        }
+    };
+
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer (both CTAs)
         // elect.sync (not lane == 0): ptxas then knows exactly one thread is active and emits the uniform-datapath
@@ -118,12 +154,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-                int b, mb, nb;
+            for (int u = cluster_id; u < num_units; u += num_clusters) {
+                int tile, kb0, kb1, role, tt, piece, b, mb, nb;
+                unit_of(u, tile, kb0, kb1, role, tt, piece);
                 decode(tile, b, mb, nb);
                 const int m0 = mb * 2 * BM + (int)cta * BM;      // this CTA's A rows
                 const int n0 = nb * BN + (int)cta * BNH;         // this CTA's half of B
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
@@ -160,13 +197,15 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
+            for (int u = cluster_id; u < num_units; u += num_clusters, ++it) {
+                int tile, kb0, kb1, role, tt, piece;
+                unit_of(u, tile, kb0, kb1, role, tt, piece);
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 mbar_wait(&tempty_bar[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_lo = a_lo0 + stage * (STAGE_BYTES >> 4);
@@ -174,7 +213,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
                         umma_f16_2sm_lohi(d_tmem, a_lo + k * a_kstep, b_lo + k * b_kstep, DESC_HI, idesc,
-                                          (kb | k) != 0);
+                                          ((kb - kb0) | k) != 0);
                     umma_commit_2sm(&empty_bar[stage], 0x3);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -187,8 +226,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint8_t* my_epi = smem_epi + q * (2 * 32 * 128);
         int it = 0;
         int buf = 0;
-        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++it) {
-            int b, mb, nb;
+        for (int u = cluster_id; u < num_units; u += num_clusters, ++it) {
+            int tile, kb0, kb1, role, tt, piece, b, mb, nb;
+            unit_of(u, tile, kb0, kb1, role, tt, piece);
             decode(tile, b, mb, nb);
             const int m0 = mb * 2 * BM + (int)cta * BM, n0 = nb * BN;
             const int as = it & 1;
@@ -197,6 +237,18 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             tc_fence_after();
             const int row = m0 + q * 32 + lane;
             const bool row_ok = row < M;
+            // split-K bookkeeping: one flag and (split - 1) workspace regions per (tail tile, CTA, epilogue warp)
+            int* flag = p.flags + ((tt * 2 + (int)cta) * 4 + q);
+            constexpr int REGION_F4 = BN * 8;   // BN x 32 floats as float4
+            float4* ws4 = reinterpret_cast<float4*>(p.ws) +
+                          (size_t)(((tt * (p.split - 1)) * 2 + (int)cta) * 4 + q) * REGION_F4 + lane;
+            const size_t piece_stride = (size_t)2 * 4 * REGION_F4;
+            if (role == ROLE_OWNER) {
+                if (lane == 0) {
+                    while (ld_acquire_gpu(flag) < p.split - 1) {}
+                }
+                __syncwarp();
+            }
 #pragma unroll 1
             for (int c = 0; c < BN / EPI_COLS; ++c) {
                 uint32_t r0[32], r1[32];
@@ -211,12 +263,36 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
                 const int col0 = n0 + c * EPI_COLS;
                 if (col0 >= N || m0 + q * 32 >= M) continue;
+                if (role == ROLE_CONTRIB) {
+                    // park the raw fp32 accumulators: [chunk][16 float4][lane] so a warp writes 512 contiguous bytes
+                    float4* dst = ws4 + piece * piece_stride + (size_t)c * 16 * 32;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        dst[j * 32] = make_float4(__uint_as_float(r0[4 * j]), __uint_as_float(r0[4 * j + 1]),
+                                                  __uint_as_float(r0[4 * j + 2]), __uint_as_float(r0[4 * j + 3]));
+                        dst[(8 + j) * 32] = make_float4(__uint_as_float(r1[4 * j]), __uint_as_float(r1[4 * j + 1]),
+                                                        __uint_as_float(r1[4 * j + 2]), __uint_as_float(r1[4 * j + 3]));
+                    }
+                    continue;
+                }
                 float v[64];
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
-                    v[i] = __uint_as_float(r0[i]) * p.e.alpha;
-                    v[32 + i] = __uint_as_float(r1[i]) * p.e.alpha;
+                    v[i] = __uint_as_float(r0[i]);
+                    v[32 + i] = __uint_as_float(r1[i]);
                 }
+                if (role == ROLE_OWNER) {
+                    for (int pc = 0; pc < p.split - 1; ++pc) {
+                        const float4* src = ws4 + pc * piece_stride + (size_t)c * 16 * 32;
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const float4 t = __ldcg(src + j * 32);
+                            v[4 * j] += t.x; v[4 * j + 1] += t.y; v[4 * j + 2] += t.z; v[4 * j + 3] += t.w;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int i = 0; i < 64; ++i) v[i] *= p.e.alpha;
                 epilogue_apply<T>(v, p.e, b, row, row_ok, col0);
                 uint8_t* sbuf = my_epi + buf * (32 * 128);
                 if (lane == 0) tma_store_wait_read<1>();
@@ -229,6 +305,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     tma_store_commit();
                 }
                 buf ^= 1;
+            }
+            if (role == ROLE_CONTRIB) {
+                __threadfence();
+                __syncwarp();
+                if (lane == 0) red_release_add(flag, 1);
+            } else if (role == ROLE_OWNER) {
+                __syncwarp();
+                if (lane == 0) *flag = 0;   // ready for the next launch (stream order separates the launches)
             }
         }
         if (lane == 0) tma_store_wait<0>();
@@ -281,9 +365,9 @@ static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap&
         if (e != cudaSuccess) return -(int)e;
         attr_set = true;
     }
-    const long tiles = (long)((p.e.M + 2 * BM - 1) / (2 * BM)) * ((p.e.N + BN - 1) / BN) * p.batch;
+    const long units = (long)p.full_tiles + (long)p.tail_tiles * p.split;
     long clusters = sms / 2;
-    if (tiles < clusters) clusters = tiles;
+    if (units < clusters) clusters = units;
     kern<<<(unsigned)(2 * clusters), NUM_THREADS, SMEM_BYTES, stream>>>(a, b, d, p);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
@@ -291,6 +375,52 @@ static int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap&
 
 }  // namespace g2
 }  // namespace dsb
+
+// ---- split-K workspace: one per stream that launches a split GEMM (launches on one stream are ordered, so a region
+// is never written by two launches at once), grown on demand.
+namespace {
+struct SplitWs {
+    cudaStream_t stream;
+    float* ws;
+    size_t ws_bytes;
+    int* flags;
+    int flag_count;
+};
+constexpr int MAX_WS = 8;
+SplitWs g_ws[MAX_WS];
+int g_ws_used = 0;
+int g_split_mode = -1;   // -1 = choose per shape, 1 = never split, 2..4 = force (test hook)
+
+SplitWs* get_ws(cudaStream_t stream, size_t bytes, int flag_count) {
+    SplitWs* w = nullptr;
+    for (int i = 0; i < g_ws_used; ++i)
+        if (g_ws[i].stream == stream) w = &g_ws[i];
+    if (!w) {
+        if (g_ws_used == MAX_WS) return nullptr;
+        w = &g_ws[g_ws_used++];
+        *w = SplitWs{stream, nullptr, 0, nullptr, 0};
+    }
+    if (w->ws_bytes < bytes) {
+        if (w->ws) { cudaStreamSynchronize(stream); cudaFree(w->ws); }
+        if (cudaMalloc(&w->ws, bytes) != cudaSuccess) { w->ws = nullptr; w->ws_bytes = 0; return nullptr; }
+        w->ws_bytes = bytes;
+    }
+    if (w->flag_count < flag_count) {
+        if (w->flags) { cudaStreamSynchronize(stream); cudaFree(w->flags); }
+        if (cudaMalloc(&w->flags, flag_count * sizeof(int)) != cudaSuccess) { w->flags = nullptr; w->flag_count = 0; return nullptr; }
+        cudaMemsetAsync(w->flags, 0, flag_count * sizeof(int), stream);
+        w->flag_count = flag_count;
+    }
+    return w;
+}
+}  // namespace
+
+// Test / tuning hook: -1 = choose the K split of the tail wave per shape, 1 = never split, 2..4 = force that split.
+extern "C" int dsb_gemm_pair_force_split(int split) {
+    if (split != -1 && (split < 1 || split > 4)) return DSB_ERR_ARG;
+    g_split_mode = split;
+    return 0;
+}
 
 static int g_force_bn = 0;
 // Test / tuning hook: 0 = choose per shape, 128 or 256 = force that pair-tile width.
@@ -345,6 +475,41 @@ extern "C" int dsb_gemm_pair(const void* A, const void* B, void* D, int M, int N
     p.e.bias = bias; p.e.aux = aux; p.e.ldaux = ldaux; p.e.stride_aux = stride_aux;
     p.e.aux_out = aux_out; p.e.ldaux_out = ldaux_out; p.e.stride_aux_out = stride_aux_out;
     p.K = K; p.batch = batch; p.a_mn = a_mn_major; p.b_mn = b_mn_major;
+    // tail-wave K split (see Params): pick the split that minimises the tail's duration in units of one whole tile
+    const int tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN) * batch;
+    const int k_blocks = (K + BK - 1) / BK;
+    const int pairs = sms / 2;
+    const int tail = tiles >= pairs ? tiles % pairs : tiles;
+    int split = 1;
+    if (tail > 0 && BN == 256) {
+        double best = 1.0;
+        for (int sp = 2; sp <= 4; ++sp) {
+            const int kpp = (k_blocks + sp - 1) / sp;
+            if (kpp < 8 || (sp - 1) * kpp >= k_blocks) continue;
+            const double cost = (double)((tail * sp + pairs - 1) / pairs) / sp + 0.03 * (sp - 1);
+            if (cost < best - 1e-9) { best = cost; split = sp; }
+        }
+        if (g_split_mode >= 1) {
+            split = g_split_mode;
+            const int kpp = (k_blocks + split - 1) / split;
+            if ((split - 1) * kpp >= k_blocks) split = 1;
+        }
+    }
+    p.split = split;
+    p.kpp = (k_blocks + split - 1) / split;
+    p.tail_tiles = split > 1 ? tail : 0;
+    p.full_tiles = tiles - p.tail_tiles;
+    p.ws = nullptr;
+    p.flags = nullptr;
+    if (split > 1) {
+        SplitWs* w = get_ws(stream, (size_t)tail * (split - 1) * 8 * BN * 32 * sizeof(float), tail * 8);
+        if (!w) {   // no workspace: fall back to whole tiles
+            p.split = 1; p.kpp = k_blocks; p.tail_tiles = 0; p.full_tiles = tiles;
+        } else {
+            p.ws = w->ws;
+            p.flags = w->flags;
+        }
+    }
     if (BN == 256) {
         if (bf) return launch<__nv_bfloat16, 256>(ta, tb, td, p, sms, stream);
         return launch<__half, 256>(ta, tb, td, p, sms, stream);

@@ -24,6 +24,7 @@ _CUDA_SIGS = {
     "dsb_gemm": [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _i, _i, _i, _i, _f, _p, _p, _l, _l, _p, _l, _l, _p],
     "dsb_gemm_pair": [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _i, _i, _i, _i, _f, _p, _p, _l, _l, _p, _l, _l, _p],
     "dsb_gemm_pair_force_bn": [_i],
+    "dsb_gemm_pair_force_split": [_i],
     "dsb_adam_flat": [_p, _p, _p, _p, _i, _p, _i, _l, _f, _f, _f, _f, _f, _i, _i, _i, _f, _p, _p, _p],
     "dsb_adam_multi": [_i, _p, _p, _p, _p, _p, _i, _i, _i, _f, _f, _f, _f, _f, _i, _i, _i, _f, _p],
     "dsb_lamb_step": [_p, _i, _p, _i, _p, _i, _p, _p, _l, _f, _f, _f, _f, _f, _f, _f, _i, _i, _i, _f, _p, _p, _p],

@@ -132,6 +132,30 @@ def test_gemm_pair_batched(pair_kernel):
     assert _rel(sc, torch.matmul(q.float(), k.float().transpose(1, 2)) * 0.125) < 2e-3
 
 
+@pytest.mark.parametrize("split", [2, 3, 4])
+@pytest.mark.parametrize("shape,ta,tb", [((4096, 2048, 2048), False, True), ((1000, 520, 4096), False, True),
+                                         ((2048, 2048, 8192), True, False), ((8192, 2048, 1024), False, False)])
+def test_gemm_pair_split_k(monkeypatch, split, shape, ta, tb):
+    """Tail-wave K split: contributors park fp32 partials, the owner slice adds them in its epilogue."""
+    monkeypatch.setattr(K, "GEMM_KERNEL", "pair")
+    lib = N.cuda_lib()
+    assert lib.dsb_gemm_pair_force_split(split) == 0
+    try:
+        M, Nn, Kk = shape
+        torch.manual_seed(7)
+        dt = torch.float16
+        a = torch.randn((Kk, M) if ta else (M, Kk), device=DEV, dtype=dt)
+        b = torch.randn((Nn, Kk) if tb else (Kk, Nn), device=DEV, dtype=dt)
+        bias = torch.randn(Nn, device=DEV, dtype=dt)
+        aux = torch.randn(M, Nn, device=DEV, dtype=dt)
+        ref = (a.float().t() if ta else a.float()) @ (b.float().t() if tb else b.float())
+        for _ in range(3):   # flags must be back to zero after every launch
+            out = K.gemm(a, b, trans_a=ta, trans_b=tb, epilogue=N.EPI_BIAS_RESIDUAL, bias=bias, aux=aux, alpha=0.5)
+            assert _rel(out, 0.5 * ref + bias.float() + aux.float()) < 2e-3, _where(out, 0.5 * ref + bias.float() + aux.float(), 2e-3)
+    finally:
+        lib.dsb_gemm_pair_force_split(-1)
+
+
 def test_gemm_batched_alpha():
     torch.manual_seed(2)
     B, S, D = 12, 256, 64
