@@ -123,3 +123,4 @@ def main(args, METRIC, SEQ, MICRO_BATCH, MB_PER_STAGE, topo_for, ds_config, Cloc
             "gpu_launches": 0,
         }), flush=True)
     dist.barrier()
+    dist.destroy_process_group()

@@ -16,6 +16,7 @@
 // dropout_kernels.cu:386-465, general_kernels.cu:89-182).
 #include "../common/ptx.cuh"
 #include "../../include/dsb200.h"
+#include "../common/host_ctx.h"
 #include <stdio.h>
 #include <type_traits>
 
@@ -379,6 +380,7 @@ extern "C" int dsb_gemm(const void* A, const void* B, void* D, int M, int N, int
                         int epilogue, float alpha, const void* bias, const void* aux, long ldaux, long stride_aux,
                         void* aux_out, long ldaux_out, long stride_aux_out, void* stream_) {
     using namespace dsb;
+    ensure_context_on_this_thread();
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     if (M <= 0 || N <= 0 || K <= 0 || batch <= 0) return 0;
     if ((lda % 8) || (ldb % 8) || (ldd % 8) || (N % 8)) return DSB_ERR_ALIGN;
@@ -432,6 +434,7 @@ extern "C" int dsb_gemm_gather_b(const void* A, void* const* shard_ptrs, int nra
                                  long lda, long ldb, long ldd, int dtype, int epilogue, float alpha, const void* bias,
                                  const void* aux, long ldaux, void* stream_) {
     using namespace dsb;
+    ensure_context_on_this_thread();
     constexpr int MAXR = 8;
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     if (M <= 0 || N <= 0 || K <= 0) return 0;

@@ -12,6 +12,7 @@
 //   warp 2 (both): pair TMEM allocation; warps 4..7 (both): epilogue of the CTA's own 128 rows
 #include "../common/ptx_2sm.cuh"
 #include "gemm_epilogue.cuh"
+#include "../common/host_ctx.h"
 #include <type_traits>
 
 namespace dsb {
@@ -431,12 +432,30 @@ extern "C" int dsb_gemm_pair_force_bn(int bn) {
 }
 
 // Same contract as dsb_gemm (include/dsb200.h); 256 x 256 (or 256 x 128) pair tiles. Best for M >= 256, N >= 128.
+extern "C" int dsb_gemm_pair_ex(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda,
+                                long ldb, long ldd, long strideA, long strideB, long strideD, int a_mn_major,
+                                int b_mn_major, int dtype, int epilogue, float alpha, const void* bias,
+                                const void* aux, long ldaux, long stride_aux, void* aux_out, long ldaux_out,
+                                long stride_aux_out, int split_mode, void* stream_);
+
 extern "C" int dsb_gemm_pair(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb,
                              long ldd, long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major,
                              int dtype, int epilogue, float alpha, const void* bias, const void* aux, long ldaux,
                              long stride_aux, void* aux_out, long ldaux_out, long stride_aux_out, void* stream_) {
+    return dsb_gemm_pair_ex(A, B, D, M, N, K, batch, lda, ldb, ldd, strideA, strideB, strideD, a_mn_major, b_mn_major,
+                            dtype, epilogue, alpha, bias, aux, ldaux, stride_aux, aux_out, ldaux_out, stride_aux_out,
+                            g_split_mode, stream_);
+}
+
+// split_mode: -1 = choose the tail-wave K split per shape, 1 = whole tiles only, 2..4 = that split (if K allows).
+extern "C" int dsb_gemm_pair_ex(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda,
+                                long ldb, long ldd, long strideA, long strideB, long strideD, int a_mn_major,
+                                int b_mn_major, int dtype, int epilogue, float alpha, const void* bias,
+                                const void* aux, long ldaux, long stride_aux, void* aux_out, long ldaux_out,
+                                long stride_aux_out, int split_mode, void* stream_) {
     using namespace dsb;
     using namespace dsb::g2;
+    ensure_context_on_this_thread();
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     if (M <= 0 || N <= 0 || K <= 0 || batch <= 0) return 0;
     if ((lda % 8) || (ldb % 8) || (ldd % 8) || (N % 8)) return DSB_ERR_ALIGN;
@@ -489,8 +508,8 @@ extern "C" int dsb_gemm_pair(const void* A, const void* B, void* D, int M, int N
             const double cost = (double)((tail * sp + pairs - 1) / pairs) / sp + 0.03 * (sp - 1);
             if (cost < best - 1e-9) { best = cost; split = sp; }
         }
-        if (g_split_mode >= 1) {
-            split = g_split_mode;
+        if (split_mode >= 1) {
+            split = split_mode;
             const int kpp = (k_blocks + split - 1) / split;
             if ((split - 1) * kpp >= k_blocks) split = 1;
         }

@@ -25,8 +25,9 @@ def _count(n=1):
 
 
 # ------------------------------------------------------------------------------------------------ GEMM
-# Tile policy: "auto" picks the CTA-pair (cta_group::2, 256 x 256) kernel for large outputs and the single-CTA kernel
-# (128 x 256 / 128 x 128 tiles) otherwise; "pair" / "single" force one (DSB_GEMM_KERNEL env, tools/bench_gemm.py).
+# Tile policy: "auto" lets the native dispatcher choose (autotuned variant if the problem was tuned, else CTA-pair
+# 256 x 256 tiles for large outputs and single-CTA 128 x 256 / 128 x 128 tiles otherwise); "pair" / "single" force
+# one (DSB_GEMM_KERNEL env, tools/bench_gemm.py).
 GEMM_KERNEL = os.environ.get("DSB_GEMM_KERNEL", "auto")
 
 
@@ -71,7 +72,10 @@ def gemm(a, b, *, trans_a=False, trans_b=True, epilogue=N.EPI_NONE, alpha=1.0, b
         sb = 0
     s_aux = aux.stride(0) if (aux is not None and aux.dim() == 3) else 0
     s_auxo = aux_out.stride(0) if (aux_out is not None and aux_out.dim() == 3) else 0
-    fn = lib.dsb_gemm_pair if _use_pair(M, Nn, K, batch) else lib.dsb_gemm
+    if GEMM_KERNEL == "auto":
+        fn = lib.dsb_gemm_auto      # tuned table (ops/gemm_autotune.py) first, static rule otherwise
+    else:
+        fn = lib.dsb_gemm_pair if _use_pair(M, Nn, K, batch) else lib.dsb_gemm
     rc = fn(N.ptr(a), N.ptr(b), N.ptr(out), M, Nn, K, batch, a.stride(-2), b.stride(-2), out.stride(-2),
             sa, sb, sd, int(trans_a), int(not trans_b), N.dtype_code(a.dtype), epilogue, float(alpha),
             N.ptr(bias), N.ptr(aux), aux.stride(-2) if aux is not None else 0, s_aux, N.ptr(aux_out),

@@ -23,6 +23,9 @@ _p, _i, _l, _f, _u64 = C.c_void_p, C.c_int, C.c_long, C.c_float, C.c_ulonglong
 _CUDA_SIGS = {
     "dsb_gemm": [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _i, _i, _i, _i, _f, _p, _p, _l, _l, _p, _l, _l, _p],
     "dsb_gemm_pair": [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _i, _i, _i, _i, _f, _p, _p, _l, _l, _p, _l, _l, _p],
+    "dsb_gemm_auto": [_p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _i, _i, _i, _i, _f, _p, _p, _l, _l, _p, _l, _l, _p],
+    "dsb_gemm_tune": [_i, _i, _i, _i, _i, _i, _i, _i, _p, _p],
+    "dsb_gemm_tuned_variant": [_i, _i, _i, _i, _i, _i, _i],
     "dsb_gemm_pair_force_bn": [_i],
     "dsb_gemm_pair_force_split": [_i],
     "dsb_adam_flat": [_p, _p, _p, _p, _i, _p, _i, _l, _f, _f, _f, _f, _f, _i, _i, _i, _f, _p, _p, _p],

@@ -164,6 +164,16 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
                     self._hook_handles.append(module.register_forward_hook(_hook))
                 idx += 1
 
+    def autotune_gemms(self, tokens_per_micro_batch, iters=7, verbose=False):
+        """Time every GEMM kernel variant (single-CTA / CTA-pair / tail-wave K split) for the linear layers of this
+        rank's module at `tokens_per_micro_batch` rows and let the native dispatcher use the winners. The reference
+        does the equivalent cuBLAS algorithm search when a transformer layer is created (gemm_test.h:27-293).
+        No-op without a GPU. Returns {(M, N, K, trans_a, trans_b): (variant, [ms])}."""
+        from ..ops import gemm_autotune
+        dtype = torch.bfloat16 if self.precision() == "bfloat16" else torch.float16
+        return gemm_autotune.tune_module(self.module, int(tokens_per_micro_batch), dtype=dtype, iters=iters,
+                                         verbose=verbose)
+
     def set_train_batch_size(self, train_batch_size):
         """Adjust the global batch size by changing gradient accumulation (micro-batch and dp stay fixed)."""
         if train_batch_size % (self.train_micro_batch_size_per_gpu() * self.dp_world_size) != 0:

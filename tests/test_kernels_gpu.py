@@ -156,6 +156,22 @@ def test_gemm_pair_split_k(monkeypatch, split, shape, ta, tb):
         lib.dsb_gemm_pair_force_split(-1)
 
 
+def test_gemm_autotune_dispatch():
+    """Native tuner records a variant per problem and dsb_gemm_auto uses it (results stay correct)."""
+    from deeperspeed_b200.ops import gemm_autotune as GA
+    best, ms = GA.tune(1024, 512, 2048, iters=3)
+    assert best in GA.VARIANTS and len(ms) == len(GA.VARIANTS) and min(x for x in ms if x > 0) > 0
+    assert GA.tuned_variant(1024, 512, 2048) == best
+    assert GA.tuned_variant(1024, 512, 2056) is None
+    torch.manual_seed(8)
+    a = torch.randn(1024, 2048, device=DEV, dtype=torch.float16)
+    b = torch.randn(512, 2048, device=DEV, dtype=torch.float16)
+    out = K.gemm(a, b)
+    assert _rel(out, a.float() @ b.float().t()) < 2e-3
+    rep = GA.tune_module(torch.nn.Linear(256, 384, bias=False).cuda().half(), 512, iters=2)
+    assert len(rep) == 3
+
+
 def test_gemm_batched_alpha():
     torch.manual_seed(2)
     B, S, D = 12, 256, 64
