@@ -28,11 +28,13 @@ __global__ void __launch_bounds__(256) rotary_oop_kernel(const T* __restrict__ q
                                                          T* __restrict__ qo, T* __restrict__ ko, int B, int S, int H,
                                                          int D, int rot, RotStrides si, RotStrides so,
                                                          const float* __restrict__ cs, const float* __restrict__ sn,
-                                                         float sign) {
+                                                         float sign, const T* __restrict__ vi, T* __restrict__ vo,
+                                                         RotStrides sv) {
     const int half = rot >> 1;
     const int hv = half >> 3;                  // 8-element vectors per rotated half
     const int pv = (D - rot) >> 3;             // pass-through vectors
-    const int per_head = hv + pv;
+    const int vv = vi != nullptr ? (D >> 3) : 0;   // optional third tensor copied verbatim (v / dv) in the same launch
+    const int per_head = hv + pv + vv;
     const long total = (long)B * S * H * per_head;
     const long stride = (long)gridDim.x * blockDim.x;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
@@ -66,10 +68,14 @@ __global__ void __launch_bounds__(256) rotary_oop_kernel(const T* __restrict__ q
                 *reinterpret_cast<uint4*>(out + oo + j) = pack8<T>(y0);
                 *reinterpret_cast<uint4*>(out + oo + j + half) = pack8<T>(y1);
             }
-        } else {
+        } else if (v < hv + pv) {
             const int j = rot + (v - hv) * 8;
             *reinterpret_cast<uint4*>(qo + oo + j) = *reinterpret_cast<const uint4*>(qi + oi + j);
             *reinterpret_cast<uint4*>(ko + oo + j) = *reinterpret_cast<const uint4*>(ki + oi + j);
+        } else {
+            const int j = (v - hv - pv) * 8;
+            *reinterpret_cast<uint4*>(vo + oo + j) =
+                *reinterpret_cast<const uint4*>(vi + b * sv.b + s * sv.s + h * sv.h + j);
         }
     }
 }
@@ -88,25 +94,41 @@ extern "C" int dsb_rotary_table(float* cos_out, float* sin_out, int S, int rot_d
     return e == cudaSuccess ? 0 : -(int)e;
 }
 
+extern "C" int dsb_rotary_oop_v(const void* q_in, const void* k_in, void* q_out, void* k_out, int B, int S, int H,
+                                int D, int rot_dim, long in_sb, long in_ss, long in_sh, long out_sb, long out_ss,
+                                long out_sh, const float* cos_tab, const float* sin_tab, int inverse, int dtype,
+                                const void* v_in, void* v_out, long v_sb, long v_ss, long v_sh, void* stream);
+
 extern "C" int dsb_rotary_oop(const void* q_in, const void* k_in, void* q_out, void* k_out, int B, int S, int H, int D,
                               int rot_dim, long in_sb, long in_ss, long in_sh, long out_sb, long out_ss, long out_sh,
                               const float* cos_tab, const float* sin_tab, int inverse, int dtype, void* stream) {
+    return dsb_rotary_oop_v(q_in, k_in, q_out, k_out, B, S, H, D, rot_dim, in_sb, in_ss, in_sh, out_sb, out_ss, out_sh,
+                            cos_tab, sin_tab, inverse, dtype, nullptr, nullptr, 0, 0, 0, stream);
+}
+
+// Same, plus an optional third tensor v_in [B,S,H,D] (strides v_s*) copied verbatim to v_out, which shares q_out's
+// batch/seq/head strides (forward: nothing; backward: dV into its slice of the dQKV buffer).
+extern "C" int dsb_rotary_oop_v(const void* q_in, const void* k_in, void* q_out, void* k_out, int B, int S, int H,
+                                int D, int rot_dim, long in_sb, long in_ss, long in_sh, long out_sb, long out_ss,
+                                long out_sh, const float* cos_tab, const float* sin_tab, int inverse, int dtype,
+                                const void* v_in, void* v_out, long v_sb, long v_ss, long v_sh, void* stream) {
     if (rot_dim % 16 || rot_dim > D || D % 8 || (in_sb | in_ss | in_sh | out_sb | out_ss | out_sh) % 8)
         return DSB_ERR_SIZE;
-    const long total = (long)B * S * H * ((rot_dim / 2 + (D - rot_dim)) / 8);
+    if (v_in && (!v_out || (v_sb | v_ss | v_sh) % 8)) return DSB_ERR_SIZE;
+    const long total = (long)B * S * H * ((rot_dim / 2 + (D - rot_dim) + (v_in ? D : 0)) / 8);
     if (total <= 0) return 0;
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     long blocks = (total + 255) / 256;
     if (blocks > (long)sms * 16) blocks = (long)sms * 16;
-    RotStrides si{in_sb, in_ss, in_sh}, so{out_sb, out_ss, out_sh};
+    RotStrides si{in_sb, in_ss, in_sh}, so{out_sb, out_ss, out_sh}, sv{v_sb, v_ss, v_sh};
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     const float sign = inverse ? -1.f : 1.f;
     if (dtype == DSB_DTYPE_F16)
-        rotary_oop_kernel<__half><<<(unsigned)blocks, 256, 0, s>>>((const __half*)q_in, (const __half*)k_in, (__half*)q_out, (__half*)k_out, B, S, H, D, rot_dim, si, so, cos_tab, sin_tab, sign);
+        rotary_oop_kernel<__half><<<(unsigned)blocks, 256, 0, s>>>((const __half*)q_in, (const __half*)k_in, (__half*)q_out, (__half*)k_out, B, S, H, D, rot_dim, si, so, cos_tab, sin_tab, sign, (const __half*)v_in, (__half*)v_out, sv);
     else if (dtype == DSB_DTYPE_BF16)
-        rotary_oop_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, s>>>((const __nv_bfloat16*)q_in, (const __nv_bfloat16*)k_in, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out, B, S, H, D, rot_dim, si, so, cos_tab, sin_tab, sign);
+        rotary_oop_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, s>>>((const __nv_bfloat16*)q_in, (const __nv_bfloat16*)k_in, (__nv_bfloat16*)q_out, (__nv_bfloat16*)k_out, B, S, H, D, rot_dim, si, so, cos_tab, sin_tab, sign, (const __nv_bfloat16*)v_in, (__nv_bfloat16*)v_out, sv);
     else
         return DSB_ERR_DTYPE;
     cudaError_t e = cudaGetLastError();

@@ -17,6 +17,8 @@ _p, _i, _l, _f = C.c_void_p, C.c_int, C.c_long, C.c_float
 N.register_sigs({
     "dsb_rotary_table": [_p, _p, _i, _i, _f, _p],
     "dsb_rotary_oop": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _p, _p, _i, _i, _p],
+    "dsb_rotary_oop_v": [_p, _p, _p, _p, _i, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _p, _p, _i, _i, _p, _p, _l, _l,
+                         _l, _p],
 })
 
 _tables = {}
@@ -36,15 +38,23 @@ def rotary_table(S, rot_dim, base, device):
     return t
 
 
-def rotary_oop(q_in, k_in, q_out, k_out, rot_dim, base, inverse=False):
-    """q_in/k_in/q_out/k_out: [B, S, H, D] views with unit last stride (in and out may have different strides)."""
+def rotary_oop(q_in, k_in, q_out, k_out, rot_dim, base, inverse=False, v_in=None, v_out=None):
+    """q_in/k_in/q_out/k_out: [B, S, H, D] views with unit last stride (in and out may have different strides).
+    v_in/v_out (optional): a third [B, S, H, D] tensor copied verbatim in the same launch; v_out must have q_out's
+    strides (it is the V slice of the same fused buffer)."""
     B, S, H, D = q_in.shape
     assert q_in.stride() == k_in.stride() and q_out.stride() == k_out.stride()
     cs, sn = rotary_table(S, rot_dim, base, q_in.device)
-    N.check(N.cuda_lib().dsb_rotary_oop(N.ptr(q_in), N.ptr(k_in), N.ptr(q_out), N.ptr(k_out), B, S, H, D, rot_dim,
-                                        q_in.stride(0), q_in.stride(1), q_in.stride(2), q_out.stride(0),
-                                        q_out.stride(1), q_out.stride(2), N.ptr(cs), N.ptr(sn), int(inverse),
-                                        N.dtype_code(q_in.dtype), N.stream_ptr()), "dsb_rotary_oop")
+    if v_in is not None:
+        assert v_out.stride() == q_out.stride() and v_in.stride(-1) == 1 and v_in.shape == q_in.shape
+    N.check(N.cuda_lib().dsb_rotary_oop_v(N.ptr(q_in), N.ptr(k_in), N.ptr(q_out), N.ptr(k_out), B, S, H, D, rot_dim,
+                                          q_in.stride(0), q_in.stride(1), q_in.stride(2), q_out.stride(0),
+                                          q_out.stride(1), q_out.stride(2), N.ptr(cs), N.ptr(sn), int(inverse),
+                                          N.dtype_code(q_in.dtype), N.ptr(v_in), N.ptr(v_out),
+                                          v_in.stride(0) if v_in is not None else 0,
+                                          v_in.stride(1) if v_in is not None else 0,
+                                          v_in.stride(2) if v_in is not None else 0, N.stream_ptr()),
+            "dsb_rotary_oop_v")
     K._count()
 
 
@@ -80,11 +90,17 @@ class CausalSelfAttentionFn(torch.autograd.Function):
         if rot_dim > 0:
             if dq.stride(-1) != 1 or dq.stride() != dk.stride():
                 dq, dk = dq.contiguous(), dk.contiguous()
-            rotary_oop(dq, dk, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
+            if dv.stride(-1) == 1 and all(st % 8 == 0 for st in dv.stride()[:3]):
+                # dV rides along in the same launch (its own vectorised strided copy was 1.4 % of the step)
+                rotary_oop(dq, dk, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True, v_in=dv,
+                           v_out=dqkv[:, :, 2])
+            else:
+                rotary_oop(dq, dk, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
+                dqkv[:, :, 2].copy_(dv)
         else:
             dqkv[:, :, 0].copy_(dq)
             dqkv[:, :, 1].copy_(dk)
-        dqkv[:, :, 2].copy_(dv)
+            dqkv[:, :, 2].copy_(dv)
         return dqkv.view(B, S, 3 * H * D), None, None, None, None
 
 
