@@ -246,22 +246,18 @@ int dsb_cpu_adam_step(int id, long step, float lr, float beta1, float beta2, flo
         if (it == g_opts.end()) return -1;
         st = &it->second;
     }
-    // incremental beta powers; recomputed when the step counter jumps (checkpoint reload)
-    if (step != st->step + 1 || beta1 != st->beta1 || beta2 != st->beta2) {
-        st->beta1_t = powf(beta1, (float)step);
-        st->beta2_t = powf(beta2, (float)step);
-    } else {
-        st->beta1_t *= beta1;
-        st->beta2_t *= beta2;
-    }
+    // beta powers in double, straight from the step counter: 1 - beta2^t cancels badly in float, and an incrementally
+    // multiplied power would make a run resumed from a checkpoint differ from the uninterrupted one
+    st->beta1_t = (float)pow((double)beta1, (double)step);
+    st->beta2_t = (float)pow((double)beta2, (double)step);
     st->step = step; st->lr = lr; st->beta1 = beta1; st->beta2 = beta2; st->eps = eps; st->wd = weight_decay;
     Coef c;
     c.beta1 = beta1; c.beta2 = beta2; c.omb1 = 1.f - beta1; c.omb2 = 1.f - beta2; c.eps = eps; c.wd = weight_decay;
     c.adamw = st->adamw;
     float bc1 = 1.f, bc2 = 1.f;
     if (bias_correction) {
-        bc1 = 1.f - st->beta1_t;
-        bc2 = 1.f / sqrtf(1.f - st->beta2_t);
+        bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+        bc2 = (float)(1.0 / sqrt(1.0 - pow((double)beta2, (double)step)));
     }
     c.step_size = -lr / bc1;
     c.bc2_rsqrt = bc2;

@@ -16,7 +16,7 @@ class ContiguousMemoryAllocator:
         self.total_size = size
         self.total_free = size
         self.largest_contiguous = size
-        self.max_allocated = 0
+        self._max_allocated = 0
         self.count = 0
 
     def allocate_tensor(self, size):
@@ -27,7 +27,7 @@ class ContiguousMemoryAllocator:
             self._reset_param_data()
         self.total_free -= size
         allocated = self.total_size - self.total_free
-        self.max_allocated = max(self.max_allocated, allocated)
+        self._max_allocated = max(self._max_allocated, allocated)
         tensor_address = self._get_new_tensor_address(size)
         ret_tensor = self._get_new_tensor(tensor_address, size)
         assert self.total_free + size == free_before, "Allocation bookkeeping error"
@@ -74,7 +74,7 @@ class ContiguousMemoryAllocator:
         print(s)
 
     def max_allocated(self):
-        return self.max_allocated
+        return self._max_allocated
 
     def _reset_param_data(self):
         for id_, tensor in self.tensor_map.items():
