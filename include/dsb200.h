@@ -9,6 +9,8 @@
 #ifndef DSB200_H
 #define DSB200_H
 
+#include <stdint.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -136,6 +138,119 @@ int dsb_cross_entropy_bwd(void* logits, const long* targets, const float* lse, c
  * GPT-NeoX half-split convention); inverse != 0 applies the transpose rotation (backward). */
 int dsb_rotary(void* q, void* k, int B, int S, int H, int D, int rot_dim, long stride_b, long stride_s, long stride_h,
                float base, int inverse, int dtype, void* stream);
+
+/* Out-of-place rotary through a cos/sin table [S, rot_dim/2] (dsb_rotary_table): q/k read with one set of
+ * (batch, seq, head) strides and written with another, e.g. out of the fused QKV activation / into the dQKV buffer.
+ * The _v form also copies a third tensor (v / dv) verbatim in the same launch. */
+int dsb_rotary_table(float* cos_out, float* sin_out, int S, int rot_dim, float base, void* stream);
+int dsb_rotary_oop(const void* q_in, const void* k_in, void* q_out, void* k_out, int B, int S, int H, int D,
+                   int rot_dim, long in_sb, long in_ss, long in_sh, long out_sb, long out_ss, long out_sh,
+                   const float* cos_tab, const float* sin_tab, int inverse, int dtype, void* stream);
+int dsb_rotary_oop_v(const void* q_in, const void* k_in, void* q_out, void* k_out, int B, int S, int H, int D,
+                     int rot_dim, long in_sb, long in_ss, long in_sh, long out_sb, long out_ss, long out_sh,
+                     const float* cos_tab, const float* sin_tab, int inverse, int dtype, const void* v_in, void* v_out,
+                     long v_sb, long v_ss, long v_sh, void* stream);
+
+/* ---- GEMM variants (csrc/gemm) ----------------------------------------------------------------------------- */
+/* CTA-pair (cta_group::2) kernel, same contract as dsb_gemm. _ex: split_mode -1 = choose the tail-wave K split,
+ * 1 = whole tiles, 2..4 = that split. force_* are test / tuning hooks for the plain entry point. */
+int dsb_gemm_pair(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb, long ldd,
+                  long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major, int dtype, int epilogue,
+                  float alpha, const void* bias, const void* aux, long ldaux, long stride_aux, void* aux_out,
+                  long ldaux_out, long stride_aux_out, void* stream);
+int dsb_gemm_pair_ex(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb,
+                     long ldd, long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major, int dtype,
+                     int epilogue, float alpha, const void* bias, const void* aux, long ldaux, long stride_aux,
+                     void* aux_out, long ldaux_out, long stride_aux_out, int split_mode, void* stream);
+int dsb_gemm_pair_force_bn(int bn);
+int dsb_gemm_pair_force_split(int split);
+/* Dispatcher (tuned table, else static rule) and the autotuner that fills the table: variant 0 = single-CTA,
+ * 1..4 = pair with that split, 5 = pair choosing its split. Reference: csrc/includes/gemm_test.h:27-293. */
+int dsb_gemm_auto(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb, long ldd,
+                  long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major, int dtype, int epilogue,
+                  float alpha, const void* bias, const void* aux, long ldaux, long stride_aux, void* aux_out,
+                  long ldaux_out, long stride_aux_out, void* stream);
+int dsb_gemm_tune(int M, int N, int K, int batch, int a_mn, int b_mn, int dtype, int iters, float* ms_out,
+                  void* stream);
+int dsb_gemm_tuned_variant(int M, int N, int K, int batch, int a_mn, int b_mn, int dtype);
+void dsb_gemm_tune_clear(void);
+/* Fused all-gather + GEMM: B [N, K] is row-sharded over `nranks` peers (shard_ptrs = peer-mapped device pointers,
+ * N / nranks rows each, a multiple of 256); TMA loads each B tile straight from its owner's memory over NVLink, so
+ * no gathered copy of the weight ever exists (ZeRO-3 linear). No reference counterpart. */
+int dsb_gemm_gather_b(const void* A, void* const* shard_ptrs, int nranks, void* D, int M, int N, int K, long lda,
+                      long ldb, long ldd, int dtype, int epilogue, float alpha, const void* bias, const void* aux,
+                      long ldaux, void* stream);
+
+/* ---- fused compute + collective kernels over peer memory (csrc/comm) ---------------------------------------- */
+/* Symmetric-heap plumbing: plain cudaMalloc + CUDA IPC handles (64 bytes) exchanged by the Python side. */
+int dsb_symm_alloc(long bytes, void** out);
+int dsb_symm_free(void* p);
+int dsb_ipc_get_handle(void* devptr, void* handle64);
+int dsb_ipc_open(const void* handle64, void** out);
+int dsb_ipc_close(void* p);
+/* ZeRO-1/2 step as two cooperative kernels. rs_norm: every rank pulls its slice of all peers' gradient arenas,
+ * reduces in fp32, unscales, accumulates sum-of-squares + non-finite flag. adam_ag: Adam on the owned slice and
+ * stores the new low-precision parameters into every peer's parameter arena. Replaces reduce_scatter + cast +
+ * optimizer + all_gather (reference stage1.py:629-773). */
+long dsb_fused_zero_scratch_bytes(void);
+int dsb_fused_rs_norm(void* const* grad_ptrs, void* const* flag_ptrs, int R, int me, long slice_off, long n,
+                      int dtype, float scale, float* red32, float* sumsq_out, int* flag_out, void* scratch,
+                      unsigned int epoch, void* stream);
+int dsb_fused_adam_ag(const float* red32, float* p32, float* m, float* v, void* const* param_ptrs,
+                      void* const* flag_ptrs, int R, int me, long slice_off, long n, int dtype, float lr, float beta1,
+                      float beta2, float eps, float weight_decay, int adamw_mode, int bias_correction, int step,
+                      const float* inv_scale_dev, const int* skip_dev, unsigned int epoch, void* stream);
+/* 1-bit (sign + scale, error feedback) allreduce as ONE cooperative kernel: compress, exchange packed signs through
+ * the peers' heaps, server-side average + recompress, gather. Reference: runtime/comm/nccl.py:47-186. */
+long dsb_onebit_heap_bytes(long n, int W);
+int dsb_onebit_allreduce(float* m, float* e_w, float* e_s, long n, int W, int me, void* const* heap_bases,
+                         long region_off, void* const* flag_bases, void* scratch, unsigned int epoch, void* stream);
+
+/* ---- block-sparse attention (csrc/sparse_attn) -------------------------------------------------------------- */
+/* Host LUT builders: layout [H, nb, nb] (0/1) -> block list (h, i, j), row CSR, column CSC; super-block packing. */
+long dsb_bs_count_nnz(const int64_t* layout, int H, int nb);
+int dsb_bs_build_luts(const int64_t* layout, int H, int nb, int32_t* blocks, int32_t* row_ptr, int32_t* row_idx,
+                      int32_t* col_ptr, int32_t* col_idx);
+int dsb_sdd_segment(const int64_t* layout, int H, int nb, int max_width, int32_t* out_id, int32_t* out_width,
+                    int64_t* counts);
+/* C[nnz blocks] = alpha * A B^T on the non-zero blocks; O = P_sparse X (or P^T X); in-place block-sparse softmax.
+ * Reference: ops/sparse_attention/trsrc/{matmul,softmax_fwd,softmax_bwd}.tr. */
+int dsb_bs_sdd(const void* A, const void* B, void* C, const int* blocks, int batch, int H, int S, int D, int block,
+               long nnz, float alpha, int dtype, void* stream);
+int dsb_bs_dsd(const void* P, const void* X, void* O, const int* ptr, const int* idx, int batch, int H, int S, int D,
+               int block, long nnz, int transposed, int dtype, void* stream);
+int dsb_bs_softmax_fwd(void* X, const int* ptr, const int* idx, int batch, int H, int S, int block, long nnz,
+                       float scale, const void* rpe, const void* kp_mask, int kp_mul, const void* attn_mask,
+                       int attn_mul, int dtype, void* stream);
+int dsb_bs_softmax_bwd(void* dY, const void* Y, const int* ptr, const int* idx, int batch, int H, int S, int block,
+                       long nnz, float scale, int dtype, void* stream);
+
+/* ---- host library (libdsb200_host.so, csrc/host) ------------------------------------------------------------ */
+/* CPU Adam: AVX-512 / AVX2 / scalar chosen at run time (simd_level 2 / 1 / 0), OpenMP over tiles; optional
+ * low-precision copy of the updated parameters to a host buffer or, through pinned double buffering, to the GPU.
+ * Reference: csrc/adam/cpu_adam.cpp:1-684. */
+int dsb_cpu_adam_simd_level(void);
+int dsb_cpu_adam_create(int id, float lr, float beta1, float beta2, float eps, float weight_decay, int adamw_mode);
+int dsb_cpu_adam_destroy(int id);
+int dsb_cpu_adam_step(int id, long step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                      int bias_correction, float* p, const float* g, float* m, float* v, long n, void* dev_lp,
+                      void* host_lp, int lp_bf16);
+int dsb_cpu_cast_lp(const float* src, void* dst, long n, int lp_bf16);
+/* Async file I/O: kernel AIO (io_submit / io_getevents by raw syscall) with O_DIRECT where alignment allows, thread
+ * pool per handle. Reference: csrc/aio/py_lib/deepspeed_py_aio_handle.cpp. */
+void* dsb_aio_handle_create(long block_size, int queue_depth, int single_submit, int overlap_events, int num_threads);
+void dsb_aio_handle_destroy(void* handle);
+int dsb_aio_submit(void* handle, int is_read, void* buf, long nbytes, const char* path);
+long dsb_aio_wait(void* handle);
+long dsb_aio_pending(void* handle);
+long dsb_aio_sync_rw(int is_read, void* buf, long nbytes, const char* path, long block_size, int queue_depth,
+                     int single_submit, int overlap_events);
+void* dsb_aio_alloc_aligned(long nbytes, int lock_pages);
+void dsb_aio_free_aligned(void* p, long nbytes, int locked);
+int dsb_parallel_memcpy(void* dst, const void* src, long nbytes);
+/* flatten / unflatten of n host or device-agnostic byte ranges. Reference: csrc/utils/flatten_unflatten.cpp. */
+int dsb_flatten_bytes(const void* const* ptrs, const long* bytes, int n, void* dst);
+int dsb_unflatten_bytes(const void* src, void* const* ptrs, const long* bytes, int n);
 
 #ifdef __cplusplus
 }
