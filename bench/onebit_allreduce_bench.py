@@ -31,6 +31,11 @@ for name, fused in (("fused", True), ("nccl_restatement", False)):
 if rank == 0:
     res["speedup"] = round(res["nccl_restatement"]["ms"] / res["fused"]["ms"], 2)
     res["world"], res["numel"] = world, n
+    # roofline: the kernel is HBM-bound (the wire carries n/8 bytes): phases A+B+E move 24 B/element, the server phases
+    # C+D 16 B per chunk element; copy bandwidth from MEASURED_PEAKS.json (6545 GB/s)
+    hbm_bytes = 24.0 * n + 16.0 * n / world
+    res["hbm_roofline_ms"] = round(hbm_bytes / 6545e6, 3)
+    res["fused_fraction_of_roofline"] = round(res["hbm_roofline_ms"] / res["fused"]["ms"], 3)
     print(json.dumps(res))
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(res, open(f"gpurun_out/onebit_bench_w{world}.json", "w"))

@@ -46,23 +46,55 @@ DSB_DEVICE float fold_partials(const float* partials, int nparts, float* sh) {
     return block_sum(t, sh);
 }
 
+// 4 sign bits per lane (elements 4q..4q+3 of a 32-element word, q = lane % 8) -> the 32-bit word, held by every lane
+// of the 8-lane group afterwards.
+DSB_DEVICE uint32_t pack_nibbles(uint32_t nib, int lane) {
+    uint32_t v = nib << ((lane & 7) * 4);
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    v |= __shfl_xor_sync(0xffffffffu, v, 4);
+    return v;
+}
+DSB_DEVICE float sgn_sel(uint32_t bits, int t, float s) { return ((bits >> t) & 1u) ? s : -s; }
+
+// All element loops run on float4 (16-byte accesses, two independent iterations in flight per thread in the pure
+// streaming phases): the first version used 4-byte accesses and reached ~1/6 of HBM bandwidth
+// (profiles/onebit_bench_w*.json history).
 __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict__ m, float* __restrict__ e_w,
                                                                float* __restrict__ e_s, long n, int W, int me,
                                                                ObPtrs P, float* __restrict__ partials, uint32_t epoch) {
     cg::grid_group grid = cg::this_grid();
     __shared__ float sh[33];
+    __shared__ float ssc[OB_MAX_RANKS];
     const long c = n / W;
     const long cwords = c >> 5;
+    const long n4 = n >> 2, c4 = c >> 2;
     const long gtid = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const long gstride = (long)gridDim.x * blockDim.x;
     const int lane = threadIdx.x & 31;
+    float4* m4 = reinterpret_cast<float4*>(m);
+    float4* ew4 = reinterpret_cast<float4*>(e_w);
+    float4* es4 = reinterpret_cast<float4*>(e_s);
 
     // ---- phase A: x = m + e_w (kept in m), partial sum of squares
     float acc = 0.f;
-    for (long i = gtid; i < n; i += gstride) {
-        const float x = m[i] + e_w[i];
-        m[i] = x;
-        acc += x * x;
+    {
+        long i = gtid;
+        for (; i + gstride < n4; i += 2 * gstride) {
+            float4 a0 = m4[i], b0 = ew4[i], a1 = m4[i + gstride], b1 = ew4[i + gstride];
+            a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+            a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
+            m4[i] = a0;
+            m4[i + gstride] = a1;
+            acc += a0.x * a0.x + a0.y * a0.y + a0.z * a0.z + a0.w * a0.w;
+            acc += a1.x * a1.x + a1.y * a1.y + a1.z * a1.z + a1.w * a1.w;
+        }
+        if (i < n4) {
+            float4 a0 = m4[i], b0 = ew4[i];
+            a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
+            m4[i] = a0;
+            acc += a0.x * a0.x + a0.y * a0.y + a0.z * a0.z + a0.w * a0.w;
+        }
     }
     acc = block_sum(acc, sh);
     if (threadIdx.x == 0) partials[blockIdx.x] = acc;
@@ -70,14 +102,22 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     const float s_w = sqrtf(fold_partials(partials, gridDim.x, sh) / (float)n);
     grid.sync();   // partials are reused below
 
-    // ---- phase B: worker error, sign packing (one ballot = 32 elements), scatter chunk r to rank r
-    for (long i = gtid; i < n; i += gstride) {   // n is a multiple of 32 * W: whole warps stay together
-        const float x = m[i];
-        const bool pos = x >= 0.f;
-        e_w[i] = x - (pos ? s_w : -s_w);
-        const uint32_t word = __ballot_sync(0xffffffffu, pos);
-        if (lane == 0) {
-            const long w = i >> 5;
+    // ---- phase B: worker error, sign packing, scatter chunk r to rank r (whole warps stay together: n % 32 == 0)
+    for (long base = gtid - lane; base < n4; base += gstride) {
+        const long i = base + lane;
+        const bool valid = i < n4;
+        uint32_t nib = 0;
+        if (valid) {
+            const float4 x = m4[i];
+            nib = (x.x >= 0.f ? 1u : 0u) | (x.y >= 0.f ? 2u : 0u) | (x.z >= 0.f ? 4u : 0u) | (x.w >= 0.f ? 8u : 0u);
+            float4 e;
+            e.x = x.x - sgn_sel(nib, 0, s_w); e.y = x.y - sgn_sel(nib, 1, s_w);
+            e.z = x.z - sgn_sel(nib, 2, s_w); e.w = x.w - sgn_sel(nib, 3, s_w);
+            ew4[i] = e;
+        }
+        const uint32_t word = pack_nibbles(nib, lane);
+        if (valid && (lane & 7) == 0) {
+            const long w = i >> 3;
             const int dst = (int)(w / cwords);
             P.recv_signs[dst][(long)me * cwords + (w - (long)dst * cwords)] = word;
         }
@@ -89,20 +129,25 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     grid.sync();
 
     // ---- phase C: server average of my chunk + server error feedback (y kept in m[me*c ..])
-    float* ybuf = m + (long)me * c;
+    float4* y4 = reinterpret_cast<float4*>(m + (long)me * c);
     const uint32_t* rs = P.recv_signs[me];
-    const float* rsc = P.recv_scales[me];
+    if (threadIdx.x < W) ssc[threadIdx.x] = __ldcg(P.recv_scales[me] + threadIdx.x);
+    __syncthreads();
+    const float inv_w = 1.f / (float)W;
     acc = 0.f;
-    for (long j = gtid; j < c; j += gstride) {
-        float y = 0.f;
+    for (long j = gtid; j < c4; j += gstride) {
+        float4 y = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int sh4 = (int)(j & 7) * 4;
         for (int w = 0; w < W; ++w) {
-            const uint32_t word = __ldcg(rs + (long)w * cwords + (j >> 5));
-            const float s = __ldcg(rsc + w);
-            y += ((word >> (j & 31)) & 1u) ? s : -s;
+            const uint32_t bits = __ldcg(rs + (long)w * cwords + (j >> 3)) >> sh4;
+            const float s = ssc[w];
+            y.x += sgn_sel(bits, 0, s); y.y += sgn_sel(bits, 1, s);
+            y.z += sgn_sel(bits, 2, s); y.w += sgn_sel(bits, 3, s);
         }
-        y = y / (float)W + e_s[j];
-        ybuf[j] = y;
-        acc += y * y;
+        const float4 e = es4[j];
+        y.x = y.x * inv_w + e.x; y.y = y.y * inv_w + e.y; y.z = y.z * inv_w + e.z; y.w = y.w * inv_w + e.w;
+        y4[j] = y;
+        acc += y.x * y.x + y.y * y.y + y.z * y.z + y.w * y.w;
     }
     acc = block_sum(acc, sh);
     if (threadIdx.x == 0) partials[blockIdx.x] = acc;
@@ -110,13 +155,21 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     const float s_s = sqrtf(fold_partials(partials, gridDim.x, sh) / (float)c);
 
     // ---- phase D: server error, pack, broadcast my chunk's signs + scale to every rank
-    for (long j = gtid; j < c; j += gstride) {
-        const float y = ybuf[j];
-        const bool pos = y >= 0.f;
-        e_s[j] = y - (pos ? s_s : -s_s);
-        const uint32_t word = __ballot_sync(0xffffffffu, pos);
-        if (lane == 0) {
-            const long w = (long)me * cwords + (j >> 5);
+    for (long base = gtid - lane; base < c4; base += gstride) {
+        const long j = base + lane;
+        const bool valid = j < c4;
+        uint32_t nib = 0;
+        if (valid) {
+            const float4 y = y4[j];
+            nib = (y.x >= 0.f ? 1u : 0u) | (y.y >= 0.f ? 2u : 0u) | (y.z >= 0.f ? 4u : 0u) | (y.w >= 0.f ? 8u : 0u);
+            float4 e;
+            e.x = y.x - sgn_sel(nib, 0, s_s); e.y = y.y - sgn_sel(nib, 1, s_s);
+            e.z = y.z - sgn_sel(nib, 2, s_s); e.w = y.w - sgn_sel(nib, 3, s_s);
+            es4[j] = e;
+        }
+        const uint32_t word = pack_nibbles(nib, lane);
+        if (valid && (lane & 7) == 0) {
+            const long w = (long)me * cwords + (j >> 3);
             for (int r = 0; r < W; ++r) P.gath_signs[(me + r) % W][w] = word;
         }
     }
@@ -128,11 +181,23 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
 
     // ---- phase E: decompress everything into m
     const uint32_t* gs = P.gath_signs[me];
-    const float* gsc = P.gath_scales[me];
-    for (long i = gtid; i < n; i += gstride) {
-        const uint32_t word = __ldcg(gs + (i >> 5));
-        const float s = __ldcg(gsc + (int)(i / c));
-        m[i] = ((word >> (i & 31)) & 1u) ? s : -s;
+    if (threadIdx.x < W) ssc[threadIdx.x] = __ldcg(P.gath_scales[me] + threadIdx.x);
+    __syncthreads();
+    {
+        long i = gtid;
+        for (; i + gstride < n4; i += 2 * gstride) {
+            const long i1 = i + gstride;
+            const uint32_t b0 = __ldcg(gs + (i >> 3)) >> ((int)(i & 7) * 4);
+            const uint32_t b1 = __ldcg(gs + (i1 >> 3)) >> ((int)(i1 & 7) * 4);
+            const float s0 = ssc[(int)(i / c4)], s1 = ssc[(int)(i1 / c4)];
+            m4[i] = make_float4(sgn_sel(b0, 0, s0), sgn_sel(b0, 1, s0), sgn_sel(b0, 2, s0), sgn_sel(b0, 3, s0));
+            m4[i1] = make_float4(sgn_sel(b1, 0, s1), sgn_sel(b1, 1, s1), sgn_sel(b1, 2, s1), sgn_sel(b1, 3, s1));
+        }
+        if (i < n4) {
+            const uint32_t b0 = __ldcg(gs + (i >> 3)) >> ((int)(i & 7) * 4);
+            const float s0 = ssc[(int)(i / c4)];
+            m4[i] = make_float4(sgn_sel(b0, 0, s0), sgn_sel(b0, 1, s0), sgn_sel(b0, 2, s0), sgn_sel(b0, 3, s0));
+        }
     }
 }
 
