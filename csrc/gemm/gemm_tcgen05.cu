@@ -39,6 +39,13 @@ struct GemmParams {
     void* aux_out;
     long ldaux_out, stride_aux_out;
     int rows_per_rank;   // gather variant: rows of B owned by each rank
+    // overlapped all-gather variant (ag_overlap != 0): warps 2-3 of every CTA copy the remote shards panel by panel
+    // (one panel = the BN rows of B one n-block needs) into `gathered`, the producer loads a remote panel from there
+    // once panel_ready[nb] shows that every CTA has delivered its share; own panels come straight from the own shard.
+    int ag_overlap, me, nranks;
+    const void* peer_shards[8];
+    void* gathered;
+    int* panel_ready;
 };
 
 template <int BN> struct GemmCfg {
@@ -107,6 +114,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     // tile -> (batch, m_blk, n_blk) with groups of 8 M-blocks sweeping N (keeps a B panel hot in L2)
     auto decode = [&](int tile, int& b, int& mb, int& nb) {
+        if constexpr (NMAPS > 1) {
+            if (p.ag_overlap) {
+                // panel-major order starting at the own shard: remote panels are needed as late as possible
+                b = 0;
+                const int seq = tile / m_blocks;
+                mb = tile - seq * m_blocks;
+                nb = (seq + p.me * (p.rows_per_rank / BN)) % n_blocks;
+                return;
+            }
+        }
         b = tile / tiles_per_batch;
         int t = tile - b * tiles_per_batch;
         const int GROUP = 8;
@@ -146,9 +163,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     if (!p.b_mn) {
                         if (NMAPS == 1) {
                             tma_load_3d(sb, &tmBs.m[0], &full_bar[stage], kb * BK, n0, b);
-                        } else {
+                        } else if (!p.ag_overlap) {
                             const int owner = n0 / p.rows_per_rank;
                             tma_load_3d(sb, &tmBs.m[owner], &full_bar[stage], kb * BK, n0 - owner * p.rows_per_rank, b);
+                        } else {
+                            const int owner = n0 / p.rows_per_rank;
+                            if (owner == p.me) {
+                                tma_load_3d(sb, &tmBs.m[1], &full_bar[stage], kb * BK, n0 - owner * p.rows_per_rank, b);
+                            } else {
+                                if (kb == 0) {   // the panel was written by generic-proxy stores of all CTAs
+                                    while (ld_acquire_gpu_s32(p.panel_ready + nb) < (int)gridDim.x) {}
+                                    fence_proxy_async_all();
+                                }
+                                tma_load_3d(sb, &tmBs.m[0], &full_bar[stage], kb * BK, n0, b);
+                            }
                         }
                     } else {
 #pragma unroll
@@ -314,6 +342,54 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
         }
         if (lane == 0) tma_store_wait<0>();
+    } else {
+        // ------------------------------------------------------------------ warps 2-3: all-gather copier (overlap mode)
+        if constexpr (NMAPS > 1) {
+            if (p.ag_overlap && p.nranks > 1) {
+                const int t = threadIdx.x - 64;                       // 0..63
+                const int ppr = p.rows_per_rank / BN;                 // panels per rank
+                const long panel_vecs = (long)BN * p.K / 8;           // 16-byte vectors per panel (shards are dense)
+                const long cta_stride = (long)gridDim.x * 64;
+                uint4* gath = reinterpret_cast<uint4*>(p.gathered);
+                // remote panels in the order the tiles will need them, two panels per round so that every thread keeps
+                // up to 16 independent 16-byte peer loads in flight (NVLink round trips are ~4 us: with 4 in flight the
+                // copy ran at ~100 GB/s and the W = 4 case stalled the tensor pipe)
+                constexpr int PG = 2, UNR = 16;
+                const int pv = (int)panel_vecs;
+                const int cstride = (int)cta_stride;
+                (void)gath;
+                for (int seq0 = ppr; seq0 < n_blocks; seq0 += PG) {
+                    const int np = min(PG, n_blocks - seq0);
+                    const int total = np * pv;
+                    for (int i0 = blockIdx.x * 64 + t; i0 < total; i0 += UNR * cstride) {
+                        uint4 v[UNR];
+#pragma unroll
+                        for (int u = 0; u < UNR; ++u) {
+                            const int i = i0 + u * cstride;
+                            if (i < total) {
+                                const int pi = i / pv, off = i - pi * pv;
+                                const int nb = (seq0 + pi + p.me * ppr) % n_blocks;
+                                const int owner = nb / ppr;
+                                v[u] = ld_na_v4(reinterpret_cast<const uint4*>(p.peer_shards[owner]) +
+                                                (long)(nb - owner * ppr) * panel_vecs + off);
+                            }
+                        }
+#pragma unroll
+                        for (int u = 0; u < UNR; ++u) {
+                            const int i = i0 + u * cstride;
+                            if (i < total) {
+                                const int pi = i / pv, off = i - pi * pv;
+                                const int nb = (seq0 + pi + p.me * ppr) % n_blocks;
+                                reinterpret_cast<uint4*>(p.gathered)[(long)nb * panel_vecs + off] = v[u];
+                            }
+                        }
+                    }
+                    __threadfence();
+                    named_bar_sync(1, 64);
+                    if (t < np) red_release_gpu_add_s32(p.panel_ready + (seq0 + t + p.me * ppr) % n_blocks, 1);
+                }
+            }
+        }
     }
 
     tc_fence_before();
@@ -467,6 +543,61 @@ extern "C" int dsb_gemm_gather_b(const void* A, void* const* shard_ptrs, int nra
     p.bias = bias; p.aux = aux; p.ldaux = ldaux; p.stride_aux = 0;
     p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
     p.rows_per_rank = rows;
+    p.ag_overlap = 0; p.me = 0; p.nranks = nranks; p.gathered = nullptr; p.panel_ready = nullptr;
+    for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = nullptr;
+    if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);
+    return launch<__half, 256, MAXR>(ta, tbs, td, p, sms, stream);
+}
+
+// Overlapped all-gather + GEMM: D = epi(alpha * A @ gather(B)^T) where B [N, K] is row-sharded (dense shards,
+// N / nranks rows each, a multiple of 256) over `nranks` peers. Inside ONE kernel, two warps of every CTA stream the
+// remote shards over NVLink into `gathered` ([N, K], local scratch) panel by panel while the tensor pipe works on the
+// panels that are already local (own shard first); a panel's tiles start as soon as its flag in `panel_flags`
+// (N / 256 ints, zeroed here) shows every CTA has delivered its share. Each weight byte crosses NVLink once
+// (dsb_gemm_gather_b re-reads remote tiles for every M block). Callers order the peers' shard writes before the launch.
+extern "C" int dsb_gemm_ag_overlap(const void* A, void* const* shard_ptrs, int nranks, int me, void* gathered,
+                                   int* panel_flags, void* D, int M, int N, int K, long lda, long ldd, int dtype,
+                                   int epilogue, float alpha, const void* bias, const void* aux, long ldaux,
+                                   void* stream_) {
+    using namespace dsb;
+    ensure_context_on_this_thread();
+    constexpr int MAXR = 8;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (M <= 0 || N <= 0 || K <= 0) return 0;
+    if (nranks < 1 || nranks > MAXR || me < 0 || me >= nranks || (N % nranks) || !gathered || !panel_flags)
+        return DSB_ERR_ARG;
+    const int rows = N / nranks;
+    if ((rows % 256) || (lda % 8) || (K % 8) || (ldd % 8)) return DSB_ERR_SIZE;
+    if ((epilogue == DSB_EPI_BIAS_RESIDUAL || epilogue == DSB_EPI_DGELU) && (!aux || (ldaux % 8))) return DSB_ERR_ARG;
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int bf = dtype == DSB_DTYPE_BF16;
+    CUtensorMap ta, td;
+    BMapSet<MAXR> tbs;
+    int rc = make_map(&ta, bf, A, K, M, 1, lda, (long)M * lda, BK, BM);
+    if (rc) return rc;
+    rc = make_map(&tbs.m[0], bf, gathered, K, N, 1, K, (long)N * K, BK, 256);
+    if (rc) return rc;
+    rc = make_map(&tbs.m[1], bf, shard_ptrs[me], K, rows, 1, K, (long)rows * K, BK, 256);
+    if (rc) return rc;
+    for (int r = 2; r < MAXR; ++r) tbs.m[r] = tbs.m[0];
+    rc = make_map(&td, bf, D, N, M, 1, ldd, (long)M * ldd, EPI_COLS, 32);
+    if (rc) return rc;
+    cudaError_t e = cudaMemsetAsync(panel_flags, 0, sizeof(int) * (N / 256), stream);
+    if (e != cudaSuccess) return -(int)e;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.batch = 1;
+    p.a_mn = 0; p.b_mn = 0;
+    p.epilogue = epilogue; p.alpha = alpha;
+    p.bias = bias; p.aux = aux; p.ldaux = ldaux; p.stride_aux = 0;
+    p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
+    p.rows_per_rank = rows;
+    p.ag_overlap = 1; p.me = me; p.nranks = nranks; p.gathered = gathered; p.panel_ready = panel_flags;
+    for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = shard_ptrs[r < nranks ? r : 0];
     if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);
     return launch<__half, 256, MAXR>(ta, tbs, td, p, sms, stream);
 }

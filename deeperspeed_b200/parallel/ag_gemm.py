@@ -13,7 +13,10 @@ from ..ops import native as N
 from .symm import SymmetricHeap
 
 _p, _i, _l, _f = C.c_void_p, C.c_int, C.c_long, C.c_float
-N.register_sigs({"dsb_gemm_gather_b": [_p, _p, _i, _p, _i, _i, _i, _l, _l, _l, _i, _i, _f, _p, _p, _l, _p]})
+N.register_sigs({
+    "dsb_gemm_gather_b": [_p, _p, _i, _p, _i, _i, _i, _l, _l, _l, _i, _i, _f, _p, _p, _l, _p],
+    "dsb_gemm_ag_overlap": [_p, _p, _i, _i, _p, _p, _p, _i, _i, _i, _l, _l, _i, _i, _f, _p, _p, _l, _p],
+})
 
 
 class ShardedWeight:
@@ -45,12 +48,27 @@ class ShardedWeight:
         return self.rows % 256 == 0 and self.K % 8 == 0 and self.world <= 8
 
 
-def ag_linear(x, sw, bias=None):
-    """x [.., K] @ gather(sw)^T (+ bias) with the gather fused into the GEMM's operand loads."""
+def ag_linear(x, sw, bias=None, direct=False):
+    """x [.., K] @ gather(sw)^T (+ bias) with the all-gather inside the GEMM kernel.
+
+    Default: two warps of every CTA stream the remote shards into a local scratch panel by panel while the tensor
+    pipe works on the panels already present (own shard first); every weight byte crosses NVLink once and the scratch
+    is shared by all layers (`dsb_gemm_ag_overlap`). direct=True keeps the first design (TMA loads every remote tile
+    straight from the peer; only sensible for a handful of rows since tiles are re-fetched per M block)."""
     x2 = x.reshape(-1, x.shape[-1]).contiguous()
     M = x2.shape[0]
     out = torch.empty(M, sw.N, dtype=x.dtype, device=x.device)
     ptrs = (C.c_void_p * sw.world)(*sw.peer_ptrs)
+    if not direct:
+        gathered = N.scratch(sw.N * sw.K * 2, x.device, "ag_gather")
+        flags = N.scratch(4 * (sw.N // 256), x.device, "ag_flags")
+        rc = N.cuda_lib().dsb_gemm_ag_overlap(N.ptr(x2), ptrs, sw.world, sw.rank, N.ptr(gathered), N.ptr(flags),
+                                              N.ptr(out), M, sw.N, sw.K, x2.stride(0), out.stride(0),
+                                              N.dtype_code(x.dtype), N.EPI_BIAS if bias is not None else 0, 1.0,
+                                              N.ptr(bias), None, 0, N.stream_ptr())
+        N.check(rc, "dsb_gemm_ag_overlap")
+        K._count()
+        return out.view(*x.shape[:-1], sw.N)
     rc = N.cuda_lib().dsb_gemm_gather_b(N.ptr(x2), ptrs, sw.world, N.ptr(out), M, sw.N, sw.K, x2.stride(0), sw.K,
                                         out.stride(0), N.dtype_code(x.dtype), N.EPI_BIAS if bias is not None else 0,
                                         1.0, N.ptr(bias), None, 0, N.stream_ptr())

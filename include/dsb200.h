@@ -181,6 +181,15 @@ int dsb_gemm_gather_b(const void* A, void* const* shard_ptrs, int nranks, void* 
                       long ldb, long ldd, int dtype, int epilogue, float alpha, const void* bias, const void* aux,
                       long ldaux, void* stream);
 
+/* Overlapped all-gather + GEMM (the ZeRO-3 linear the framework uses): dense shards of N / nranks rows; two warps of
+ * every CTA copy the remote shards into `gathered` [N, K] panel by panel (N / 256 flags in `panel_flags`, zeroed by
+ * the call) while the tensor pipe consumes the panels already present, own shard first. One launch; every weight
+ * byte crosses NVLink once. No reference counterpart (reference: all_gather then F.linear,
+ * runtime/zero/partition_parameters.py:746-855). */
+int dsb_gemm_ag_overlap(const void* A, void* const* shard_ptrs, int nranks, int me, void* gathered, int* panel_flags,
+                        void* D, int M, int N, int K, long lda, long ldd, int dtype, int epilogue, float alpha,
+                        const void* bias, const void* aux, long ldaux, void* stream);
+
 /* ---- fused compute + collective kernels over peer memory (csrc/comm) ---------------------------------------- */
 /* Symmetric-heap plumbing: plain cudaMalloc + CUDA IPC handles (64 bytes) exchanged by the Python side. */
 int dsb_symm_alloc(long bytes, void** out);

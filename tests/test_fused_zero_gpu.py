@@ -87,11 +87,20 @@ def _ag_gemm_worker():
     assert sw.supported()
     torch.manual_seed(10 + dist.get_rank())
     x = torch.randn(M, Kk, device="cuda").half()
-    y = ag_linear(x, sw, b)
-    torch.cuda.synchronize()
     ref = x.float() @ w.float().t() + b.float()
-    rel = ((y.float() - ref).abs().max() / ref.abs().max()).item()
-    assert rel < 3e-3, rel
+    # overlapped in-kernel all-gather (default, run twice: the panel flags are re-armed per launch) and the direct
+    # remote-TMA variant
+    for kwargs in ({}, {}, {"direct": True}):
+        y = ag_linear(x, sw, b, **kwargs)
+        torch.cuda.synchronize()
+        rel = ((y.float() - ref).abs().max() / ref.abs().max()).item()
+        assert rel < 3e-3, (kwargs, rel)
+        dist.barrier()
+    # a taller problem so that several waves of tiles wait on remote panels
+    x2 = torch.randn(4096, Kk, device="cuda").half()
+    y2 = ag_linear(x2, sw, None)
+    ref2 = x2.float() @ w.float().t()
+    assert ((y2.float() - ref2).abs().max() / ref2.abs().max()).item() < 3e-3
     dist.barrier()
 
 
