@@ -57,6 +57,53 @@ class LinearFunctionForZeroStage3(torch.autograd.Function):
         return LinearFunctionForZeroStage3.apply(input, weight, bias)
 
 
+class WeightHolder:
+    """Keeps a partitioned weight Parameter out of autograd's sight (it is a 1-element placeholder in forward, so
+    autograd would reduce its gradient to that shape) plus a dummy leaf that forces the backward to run."""
+
+    def __init__(self, param):
+        self.param = param
+        self.dummy = torch.zeros((), device=param.device, requires_grad=True)
+
+
+class FusedAGLinearFunction(torch.autograd.Function):
+    """ZeRO-3 linear whose forward gathers the weight INSIDE the GEMM kernel from the peers' shards
+    (parallel/ag_gemm.py). The weight is not an autograd input: backward computes its gradient from the copy the
+    ZeRO-3 pre-backward hook has gathered, stores it in `.grad` and runs the parameter's ZeRO gradient hook
+    (reduce-scatter + release) itself."""
+
+    @staticmethod
+    def forward(ctx, input, bias, dummy, holder):
+        from ...parallel.ag_gemm import ag_linear
+        ctx.holder = holder
+        ctx.save_for_backward(input, bias)
+        return ag_linear(input, holder.param.ds_sharded, bias)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input, bias = ctx.saved_tensors
+        w = ctx.holder.param
+        assert w.numel() == w.ds_numel, "ZeRO-3 pre-backward hook did not gather the weight"
+        go2 = grad_output.reshape(-1, grad_output.shape[-1])
+        if not go2.is_contiguous():
+            go2 = go2.contiguous()
+        x2 = input.reshape(-1, input.shape[-1])
+        fast = go2.shape[0] % 64 == 0 and go2.shape[1] % 8 == 0 and x2.shape[1] % 8 == 0
+        grad_input = grad_bias = None
+        if ctx.needs_input_grad[0]:
+            gi = K.gemm(go2, w.data, trans_b=False) if fast else go2.matmul(w.data)
+            grad_input = gi.view(input.shape)
+        if bias is not None and ctx.needs_input_grad[1]:
+            grad_bias = go2.float().sum(0).to(go2.dtype)
+        if w.requires_grad:
+            gw = K.gemm(go2, x2.contiguous(), trans_a=True, trans_b=False) if fast else go2.t().matmul(x2)
+            w.grad = gw if w.grad is None else w.grad + gw
+            hook = getattr(w, "ds_grad_hook", None)
+            if hook is not None:
+                hook(w)
+        return grad_input, grad_bias, None, None
+
+
 class LinearModuleForZeroStage3(Module):
     """nn.Linear twin built on LinearFunctionForZeroStage3."""
     __constants__ = ["in_features", "out_features"]

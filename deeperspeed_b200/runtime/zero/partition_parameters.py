@@ -93,6 +93,9 @@ class ZeROOrderedDict(dict):
             return param
         if hasattr(param, "ds_status") and param.ds_status == ZeroParamStatus.NOT_AVAILABLE:
             if self._parent_module._parameters._in_forward:
+                if getattr(param, "ds_fused_ag", False) and key == "weight" \
+                        and "forward" in self._parent_module.__dict__:
+                    return param   # its Linear gathers it inside the GEMM kernel (stage3: _fused_linear_forward)
                 register_external_parameter(FWD_MODULE_STACK[-1], param)
                 param.all_gather()
         return param
@@ -197,9 +200,12 @@ class Init(InsertPostInitMethodToModuleSubClasses):
     param_id = 0
 
     def __init__(self, module=None, data_parallel_group=None, mem_efficient_linear=True, remote_device=None,
-                 pin_memory=False, deepspeed_config=None, param_dict=None, enabled=True):
+                 pin_memory=False, deepspeed_config=None, param_dict=None, enabled=True, fused_allgather_gemm=None):
         """Partition parameters as they are constructed so models larger than one device can be built.
-        `remote_device`: None/"cuda" keeps shards on the GPU, "cpu" (optionally pinned) or "nvme" host them remotely."""
+        `remote_device`: None/"cuda" keeps shards on the GPU, "cpu" (optionally pinned) or "nvme" host them remotely.
+        `fused_allgather_gemm` (default: env DSB_ZERO3_FUSED_AG=1): shards of eligible 2-D weights live on a symmetric
+        (peer-mapped) heap and nn.Linear forwards run the all-gather INSIDE the GEMM kernel (`parallel/ag_gemm.py`)
+        instead of all_gather + linear; backward still gathers the weight the regular way."""
         super().__init__(enabled=enabled, mem_efficient_linear=mem_efficient_linear)
         if not dist.is_initialized():
             init_distributed()
@@ -226,6 +232,11 @@ class Init(InsertPostInitMethodToModuleSubClasses):
                 self.remote_device = off["device"]
                 self.pin_memory = off.get("pin_memory", False)
         self.param_swapper = None
+        if fused_allgather_gemm is None:
+            fused_allgather_gemm = os.environ.get("DSB_ZERO3_FUSED_AG", "0") == "1"
+        self.fused_allgather_gemm = bool(fused_allgather_gemm) and self.local_device.type == "cuda" \
+            and 1 < self.world_size <= 8 and self.remote_device == self.local_device
+        self._ag_heaps = []
         # already constructed module: convert in place
         if module is not None:
             assert isinstance(module, torch.nn.Module)
@@ -255,6 +266,7 @@ class Init(InsertPostInitMethodToModuleSubClasses):
         param.ds_tensor = None
         param.ds_active_sub_modules = 0
         param.ds_persist = False
+        param.ds_fused_ag = False
         param.ds_id = Init.param_id
         Init.param_id += 1
         param.ds_process_group = self.ds_process_group
@@ -304,6 +316,27 @@ class Init(InsertPostInitMethodToModuleSubClasses):
         param.aligned_size = aligned_size
         param.padding_size = padding_size
         param.partitioned_size = partitioned_size
+
+    # ---- symmetric-heap shards for the fused all-gather + GEMM forward
+    AG_HEAP_CHUNK_BYTES = 256 << 20
+
+    def _fused_ag_eligible(self, param):
+        if not self.fused_allgather_gemm or len(param.ds_shape) != 2:
+            return False
+        rows, cols = param.ds_shape
+        return (param.dtype in (torch.float16, torch.bfloat16) and rows % (256 * self.world_size) == 0
+                and cols % 8 == 0)
+
+    def _ag_alloc(self, numel, dtype):
+        """Carve a shard out of the peer-mapped heap (collective: every rank allocates the same sequence)."""
+        from ...parallel.symm import SymmetricHeap
+        nbytes = (numel * 2 + 255) // 256 * 256
+        heap = self._ag_heaps[-1] if self._ag_heaps else None
+        if heap is None or heap._cursor + nbytes > heap.nbytes:
+            heap = SymmetricHeap(max(self.AG_HEAP_CHUNK_BYTES, nbytes + 4096), group=self.ds_process_group)
+            self._ag_heaps.append(heap)
+        t, off = heap.alloc(numel, dtype)
+        return t, heap.peer_ptrs(off)
 
     # ---- size helpers (per-parameter: pad = (-numel) mod dp; reference partition_parameters.py:547-555)
     def _aligned_size(self, param):
@@ -368,6 +401,16 @@ class Init(InsertPostInitMethodToModuleSubClasses):
         part = self._partitioned_size(param)
         start = part * self.rank
         one_dim = param.data.contiguous().view(-1)
+        if param.ds_tensor is None and self._fused_ag_eligible(param):
+            import types
+            shard, ptrs = self._ag_alloc(part, param.dtype)
+            param.ds_tensor = shard
+            param.ds_tensor.requires_grad = False
+            param.ds_tensor.ds_numel = part
+            param.ds_fused_ag = True
+            param.ds_heap_shard = shard.view(-1)   # survives the optimizer re-homing ds_tensor.data into its flat buffer
+            param.ds_sharded = types.SimpleNamespace(world=self.world_size, rank=self.rank, N=param.ds_shape[0],
+                                                     K=param.ds_shape[1], peer_ptrs=ptrs)
         if param.ds_tensor is None:
             dev = self.local_device if not isinstance(self.remote_device, str) else torch.device("cpu")
             shard = torch.zeros(part, dtype=param.dtype, device=dev)

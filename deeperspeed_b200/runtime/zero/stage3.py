@@ -87,10 +87,18 @@ class PartitionedParameterCoordinator:
     def record_trace(self, sub_module):
         self.prefetch_coordinator.record_trace(sub_module)
 
-    def fetch_sub_module(self, sub_module):
-        """Gather the parameters of `sub_module` (waiting on any prefetch already in flight)."""
+    @staticmethod
+    def _fused_forward_weight(sub_module, p):
+        """True when `p` is the weight of a Linear whose forward gathers it inside the GEMM kernel."""
+        return (getattr(p, "ds_fused_ag", False) and type(sub_module) is torch.nn.Linear
+                and p is getattr(sub_module, "weight", None) and "forward" in sub_module.__dict__)
+
+    def fetch_sub_module(self, sub_module, forward=False):
+        """Gather the parameters of `sub_module` (waiting on any prefetch already in flight). In forward, weights
+        served by the fused all-gather + GEMM stay partitioned."""
         params = self._params_of(sub_module)
-        to_fetch = [p for p in params if p.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+        to_fetch = [p for p in params if p.ds_status == ZeroParamStatus.NOT_AVAILABLE
+                    and not (forward and self._fused_forward_weight(sub_module, p))]
         for p in params:
             p.ds_active_sub_modules += 1
         if to_fetch:
@@ -123,7 +131,8 @@ class PartitionedParameterCoordinator:
             mod = self.module_by_id.get(mid)
             if mod is None:
                 continue
-            params = [p for p in self._params_of(mod) if p.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+            params = [p for p in self._params_of(mod) if p.ds_status == ZeroParamStatus.NOT_AVAILABLE
+                      and not getattr(p, "ds_fused_ag", False)]
             cost = sum(p.ds_numel for p in params)
             if not params:
                 continue
@@ -234,6 +243,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 self._add_sub_group(cur, gid)
         self._rebuild_inner_param_groups()
         self._persist_small_params()
+        self._peer_shard_fence()
         if self.swap_optimizer:
             from ..swap_tensor.partitioned_optimizer_swapper import PartitionedOptimizerSwapper
             from ..swap_tensor.pipelined_optimizer_swapper import PipelinedOptimizerSwapper
@@ -300,6 +310,21 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
             self.param_coordinator.module_by_id[module.id] = module
             self._module_id += 1
             _init_external_params(module)
+            w = getattr(module, "weight", None)
+            if type(module) is torch.nn.Linear and getattr(w, "ds_fused_ag", False):
+                # route this Linear through the ZeRO-3 linear function, which runs the fused all-gather + GEMM while
+                # the weight is partitioned (F.linear would see the 1-element placeholder)
+                import types
+                from .linear import FusedAGLinearFunction, WeightHolder
+                module._ds_weight_holder = WeightHolder(w)
+
+                def _fused_linear_forward(mod, inp):
+                    wt = dict.__getitem__(mod._parameters, "weight")   # no auto-gather
+                    if wt.numel() != wt.ds_numel and inp.is_cuda:
+                        h = mod._ds_weight_holder
+                        return FusedAGLinearFunction.apply(inp, mod.bias, h.dummy, h)
+                    return torch.nn.functional.linear(inp, wt, mod.bias)
+                module.forward = types.MethodType(_fused_linear_forward, module)
             self.hook_handles.append(module.register_forward_pre_hook(self._pre_forward))
             self.hook_handles.append(module.register_forward_hook(self._post_forward))
             self.hook_handles.append(module.register_full_backward_pre_hook(self._pre_backward))
@@ -315,7 +340,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         if not pc.prefetch_coordinator.trace_completed() or len(pc.prefetch_coordinator.sub_module_trace) <= module.id:
             if module.id not in pc.prefetch_coordinator.sub_module_trace:
                 pc.record_trace(module)
-        pc.fetch_sub_module(module)
+        pc.fetch_sub_module(module, forward=True)
         pc.prefetch_next_sub_modules(module, numel=self.prefetch_elements)
 
     def _post_forward(self, module, inputs, output):
@@ -338,7 +363,9 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
     def _install_grad_hooks(self):
         for params in self.sub_groups:
             for p in params:
-                p.register_post_accumulate_grad_hook(self._make_grad_hook(p))
+                hook = self._make_grad_hook(p)
+                p.ds_grad_hook = hook   # also called directly by FusedAGLinearFunction.backward
+                p.register_post_accumulate_grad_hook(hook)
 
     def _make_grad_hook(self, param):
         init = Init.__new__(Init)   # size helpers only
@@ -487,7 +514,20 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 if p.ds_status == ZeroParamStatus.AVAILABLE:
                     p.ds_status = ZeroParamStatus.NOT_AVAILABLE
                 p.all_gather()
+        self._peer_shard_fence()
         return self.overflow
+
+    def _peer_shard_fence(self):
+        """Fused all-gather + GEMM forwards read the peers' shards directly: every rank's shard update must have
+        executed before anyone's next forward (NCCL all-gathers gave that ordering for free)."""
+        fused = [p for p in self.module.parameters() if getattr(p, "ds_fused_ag", False)]
+        if not fused:
+            return
+        for p in fused:   # the optimizer keeps the shard in its flat buffer: refresh the peer-visible copy
+            if p.ds_heap_shard.data_ptr() != p.ds_tensor.data_ptr():
+                p.ds_heap_shard.copy_(p.ds_tensor)
+        if _dist_ready():
+            dist.barrier(group=self.dp_process_group)
 
     def get_global_grad_norm(self):
         return self._global_grad_norm
@@ -543,6 +583,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
             if p.ds_persist:
                 p.ds_status = ZeroParamStatus.NOT_AVAILABLE
                 p.all_gather()
+        self._peer_shard_fence()
 
     def __repr__(self):
         return repr(self.optimizer)

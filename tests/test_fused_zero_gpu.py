@@ -106,3 +106,60 @@ def _ag_gemm_worker():
 
 def test_fused_allgather_gemm_2gpu():
     run_distributed(_ag_gemm_worker, world_size=2, use_cuda=True)
+
+
+def _zero3_fused_ag_worker(tmp):
+    """ZeRO-3 training with Linear forwards served by the fused all-gather + GEMM must match the regular path."""
+    import deeperspeed_b200 as deepspeed
+    from deeperspeed_b200.parallel import ag_gemm
+    calls = [0]
+    orig = ag_gemm.ag_linear
+
+    def counting(*a, **k):
+        calls[0] += 1
+        return orig(*a, **k)
+    ag_gemm.ag_linear = counting
+
+    class MLP(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.l1 = torch.nn.Linear(256, 1024)
+            self.l2 = torch.nn.Linear(1024, 512)
+            self.head = torch.nn.Linear(512, 16)      # 16 rows: not eligible, regular gather
+
+        def forward(self, x, y):
+            h = torch.nn.functional.gelu(self.l1(x))
+            return torch.nn.functional.cross_entropy(self.head(self.l2(h)).float(), y)
+
+    cfg = {"train_batch_size": 16, "train_micro_batch_size_per_gpu": 8, "steps_per_print": 100,
+           "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
+           "fp16": {"enabled": True, "loss_scale": 128},
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 10}}
+    results = []
+    for fused in (False, True):
+        torch.manual_seed(7)
+        with deepspeed.zero.Init(fused_allgather_gemm=fused):
+            model = MLP()
+        assert getattr(model.l1.weight, "ds_fused_ag", False) == fused and not model.head.weight.ds_fused_ag
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        g = torch.Generator().manual_seed(100 + dist.get_rank())
+        losses = []
+        for _ in range(4):
+            x = torch.randn(8, 256, generator=g).cuda().half()
+            y = torch.randint(0, 16, (8,), generator=g).cuda()
+            loss = engine(x, y)
+            engine.backward(loss)
+            engine.step()
+            losses.append(loss.item())
+        with deepspeed.zero.GatheredParameters(list(model.parameters())):
+            results.append((losses, [p.detach().float().clone() for p in model.parameters()]))
+    (l0, p0), (l1, p1) = results
+    assert calls[0] == 2 * 4, calls   # l1 and l2 forwards of the fused run, nothing else
+    assert all(abs(a - b) < 2e-2 for a, b in zip(l0, l1)), (l0, l1)
+    for a, b in zip(p0, p1):
+        assert (a - b).abs().max().item() < 5e-3
+    dist.barrier()
+
+
+def test_zero3_fused_allgather_gemm_2gpu(tmp_path):
+    run_distributed(_zero3_fused_ag_worker, world_size=2, use_cuda=True, args=(str(tmp_path),))
