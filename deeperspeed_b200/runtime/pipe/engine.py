@@ -309,6 +309,25 @@ class PipelineEngine(PipeExecMixin, DeepSpeedEngine):
 
     def _aggregate_total_loss(self):
         # scale loss, average among DP ranks, and bcast loss to the rest of my DP group
+        # a module without loss_fn "returns" its last-stage output: that is a whole tensor, not a scalar
+        # (reference tests/unit/test_pipe_module.py compares eval_batch() with the sequential forward)
+        src_rank = self.grid.stage_to_global(self.num_stages - 1)
+        flag = torch.zeros(1, dtype=torch.long, device=self.device)
+        if self.is_last_stage():
+            flag[0] = int(isinstance(self.total_loss, torch.Tensor) and self.total_loss.numel() > 1)
+        if self.is_pipe_parallel:
+            dist.broadcast(flag, src=src_rank, group=self.grid.get_pipe_parallel_group())
+        if int(flag.item()):
+            agg = None
+            if self.is_last_stage():
+                agg = self._scale_loss(self.total_loss).clone().detach()
+                self.dp_group_loss = agg.clone()
+                if self.is_data_parallel:
+                    dist.all_reduce(agg, group=self.mpu.get_data_parallel_group())
+                    agg /= self.dp_world_size
+            if self.is_pipe_parallel:
+                agg = self._bcast_tensor(agg, src_rank)
+            return agg
         if self.is_last_stage():
             loss = self._scale_loss(self.total_loss)
             self.dp_group_loss = loss.clone().detach()

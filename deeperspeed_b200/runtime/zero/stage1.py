@@ -124,6 +124,9 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
                 else:
                     ent[key] = val
             ent["__group_step__"] = self.optimizer.param_groups[gi].get("step", 0)
+            # lr / betas / weight decay ... as they were when saved (an LR scheduler may have moved them)
+            ent["__group_hparams__"] = {k: v for k, v in self.optimizer.param_groups[gi].items()
+                                        if k != "params" and not torch.is_tensor(v)}
             out.append(ent)
         return out
 
@@ -170,6 +173,8 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
             for key, val in ents[0].items():
                 if key == "__group_step__":
                     self.optimizer.param_groups[gi]["step"] = val
+                elif key == "__group_hparams__":
+                    self.optimizer.param_groups[gi].update(val)
                 elif isinstance(val, list) and len(val) > 0 and torch.is_tensor(val[0]):
                     merged = self._merge_and_take_mine(gi, [e[key] for e in ents]).to(master.device)
                     if key in st and torch.is_tensor(st[key]) and st[key].numel() == merged.numel():

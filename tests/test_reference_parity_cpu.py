@@ -1,0 +1,490 @@
+"""Behaviours the reference's unit tests pin down that are not covered elsewhere here: init/config
+corner cases, tuple-of-losses models, PLD kwargs injection, flops profiler inside the engine, call_to_str, dynamic loss
+scale through the optimizers, Sequential -> PipelineModule, GatheredParameters(modifier_rank), external parameters,
+activation checkpointing with None / non-tensor arguments, 1-bit Adam checkpoint phase handling."""
+import argparse
+import json
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+
+import deeperspeed_b200 as deepspeed
+from common import distributed_test
+from simple_model import SimpleModel, args_from_dict, random_dataloader
+
+HID = 10
+
+
+def _base_cfg(**extra):
+    cfg = {"train_batch_size": 2, "steps_per_print": 100, "optimizer": {"type": "Adam", "params": {"lr": 0.00015}}}
+    cfg.update(extra)
+    return cfg
+
+
+# ------------------------------------------------------------------------------------------------- init / config
+def test_init_variants(tmp_path):
+    """reference test_config.py: deprecated --deepscale_config, args=None + config_params, no optimizer, model=None."""
+    @distributed_test(world_size=1)
+    def run():
+        # deprecated flag
+        path = os.path.join(str(tmp_path), "c.json")
+        json.dump(_base_cfg(), open(path, "w"))
+        parser = deepspeed.add_config_arguments(argparse.ArgumentParser())
+        args = parser.parse_args(["--deepscale_config", path])
+        args.local_rank = 0
+        model = SimpleModel(HID)
+        engine, opt, _, _ = deepspeed.initialize(args=args, model=model, model_parameters=model.parameters())
+        assert engine.train_batch_size() == 2 and opt is not None
+        # args=None with config_params
+        model = SimpleModel(HID)
+        engine, opt, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(),
+                                                 config_params=_base_cfg())
+        for x, y in random_dataloader(engine, 6, HID, engine.device):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        # no optimizer in the config and none passed: forward works, backward / step assert (reference
+        # test_config.py::test_init_no_optimizer, engine.py:1045)
+        model = SimpleModel(HID)
+        cfg = {"train_batch_size": 2, "steps_per_print": 100}
+        engine, opt, _, _ = deepspeed.initialize(model=model, config_params=cfg)
+        assert opt is None
+        x, y = next(iter(random_dataloader(engine, 2, HID, engine.device)))
+        loss = engine(x, y)
+        with pytest.raises(AssertionError):
+            engine.backward(loss)
+        with pytest.raises(AssertionError):
+            engine.step()
+        # client optimizer object
+        model = SimpleModel(HID)
+        client = torch.optim.SGD(model.parameters(), lr=0.1)
+        engine, opt, _, _ = deepspeed.initialize(model=model, optimizer=client, config_params=cfg)
+        assert opt is client
+        with pytest.raises(AssertionError):
+            deepspeed.initialize(model=None, config_params=cfg)
+    run()
+
+
+def test_dist_init_required_false_uses_existing_group(tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(),
+                                               config_params=_base_cfg(train_batch_size=4), dist_init_required=False)
+        assert engine.world_size == 2 and engine.dp_world_size == 2
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- multi-output model
+class MultiOutputModel(torch.nn.Module):
+    def __init__(self, hidden_dim, weight_value):
+        super().__init__()
+        self.linear = torch.nn.Linear(hidden_dim, hidden_dim, bias=False)
+        self.linear.weight.data.fill_(weight_value)
+        self.cross_entropy_loss = torch.nn.CrossEntropyLoss()
+
+    def forward(self, inputs, targets):
+        return tuple(self.cross_entropy_loss(self.linear(x), y) for x, y in zip(inputs, targets))
+
+
+@pytest.mark.parametrize("n_outputs", [2, 3])
+def test_tuple_of_losses_with_grad_accumulation(tmp_path, n_outputs):
+    """reference test_multi_output_model.py: summed tuple loss, engine.backward returns the loss scaled by 1/gas."""
+    @distributed_test(world_size=1)
+    def run():
+        gas, micro = 2, 2
+        cfg = _base_cfg(train_micro_batch_size_per_gpu=micro, gradient_accumulation_steps=gas, train_batch_size=micro * gas)
+        weight_value = 0.1
+        model = MultiOutputModel(HID, weight_value)
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        inputs = [torch.full((micro, HID), float(i + 1)) for i in range(n_outputs)]
+        targets = [torch.full((micro,), i + 1, dtype=torch.long) for i in range(n_outputs)]
+        # uniform weights -> every logit equal -> each loss = log(HID)
+        expected = torch.log(torch.tensor(float(HID)))
+        for step in range(gas):
+            losses = engine(inputs, targets)
+            assert len(losses) == n_outputs
+            for l in losses:
+                assert l.item() == pytest.approx(expected.item(), rel=1e-5)
+            summed = sum(losses)
+            scaled = engine.backward(summed)
+            assert scaled.item() == pytest.approx(n_outputs * expected.item() / gas, rel=1e-5)
+            engine.step()
+        assert engine.global_steps == 1
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- PLD kwargs
+class PLDModel(SimpleModel):
+    def forward(self, x, y, **kwargs):
+        self.seen_kwargs = dict(kwargs)
+        return super().forward(x, y)
+
+
+@pytest.mark.parametrize("enabled", [True, False])
+def test_pld_kwargs_injected_only_when_enabled(tmp_path, enabled):
+    @distributed_test(world_size=1)
+    def run():
+        import math
+        theta, gamma = 0.5, 0.001
+        cfg = _base_cfg(train_batch_size=1)
+        if enabled:
+            cfg["progressive_layer_drop"] = {"enabled": True, "theta": theta, "gamma": gamma}
+        model = PLDModel(HID)
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        for i, (x, y) in enumerate(random_dataloader(engine, 5, HID, engine.device)):
+            loss = engine(x, y)
+            if enabled:
+                assert model.seen_kwargs["progressive_layer_drop"] is True and "pld_theta" in model.seen_kwargs
+            else:
+                assert model.seen_kwargs == {}
+            engine.backward(loss); engine.step()
+            if enabled:   # reference test_pld.py: theta after step i follows the schedule at t = i
+                assert engine.get_pld_theta() == pytest.approx((1 - theta) * math.exp(-gamma * i) + theta)
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- flops profiler in engine
+def test_flops_profiler_in_engine(tmp_path):
+    """reference test_flops_profiler.py:21-53: profile at profile_step, flops == 100 and params == 110 for Linear(10, 10)."""
+    @distributed_test(world_size=1)
+    def run():
+        cfg = _base_cfg(train_batch_size=1, flops_profiler={"enabled": True, "profile_step": 1, "module_depth": -1,
+                                                            "top_modules": 3, "detailed": True})
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        for n, (x, y) in enumerate(random_dataloader(engine, 4, HID, engine.device)):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+            if n == 3:
+                break
+        assert engine.flops_profiler.flops == 100
+        assert engine.flops_profiler.params == 110
+    run()
+
+
+def test_call_to_str():
+    from deeperspeed_b200.runtime.utils import call_to_str
+    c2s = call_to_str
+    assert c2s("int") == "int()"
+    assert c2s("int", 3) == "int(3)"
+    assert c2s("int", 3, "jeff") == "int(3, 'jeff')"
+    assert c2s("hello", val=3) == "hello(val=3)"
+    assert c2s("hello", 1138, val=3) == "hello(1138, val=3)"
+
+
+# ------------------------------------------------------------------------------------------------- dynamic loss scale
+@pytest.mark.parametrize("optimizer", ["Adam", "Lamb"])
+def test_dynamic_loss_scale_through_optimizer(tmp_path, optimizer):
+    """reference test_dynamic_loss_scale.py: growth every window without overflow, halving (to min) on overflow, for
+    the fused (Adam) and unfused (LAMB) fp16 wrappers."""
+    @distributed_test(world_size=1)
+    def run():
+        cfg = {"train_batch_size": 1, "steps_per_print": 100,
+               "optimizer": {"type": optimizer, "params": {"lr": 0.00015}},
+               "fp16": {"enabled": True, "type": "bfloat16" if False else "fp16", "loss_scale": 0,
+                        "initial_scale_power": 8, "loss_scale_window": 2, "min_loss_scale": 0.25}}
+        model = SimpleModel(HID)
+        engine, optim, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(),
+                                                   config_params=cfg)
+        expected = 2 ** 8
+        assert optim.dynamic_loss_scale and optim.cur_scale == expected
+
+        def run_step(value):
+            for p in model.parameters():
+                p.grad = torch.full_like(p, value)
+            optim.step()
+
+        # no overflow: doubles after every 2 clean steps (checked the reference's way: the expectation moves AFTER the
+        # assertion, reference test_dynamic_loss_scale.py:37-45)
+        for i in range(6):
+            run_step(0.5)
+            assert optim.cur_scale == expected and optim.cur_iter == i + 1
+            if optim.cur_iter % 2 == 0:
+                expected *= 2
+        # overflows: halves each time down to min_loss_scale
+        expected = optim.cur_scale
+        for value in (float("inf"), float("nan"), float("inf")):
+            run_step(value)
+            expected = max(expected / 2, 0.25)
+            assert optim.cur_scale == expected and optim.overflow
+        for _ in range(20):
+            run_step(float("inf"))
+        assert optim.cur_scale == 0.25
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- pipeline module
+def test_sequential_to_pipeline_module_world4(tmp_path):
+    """reference test_pipe_module.py:62-99: PipelineModule(layers=nn.Sequential, num_stages=4): per-stage parameter
+    counts add up to the sequential model's, eval_batch equals the plain sequential forward."""
+    @distributed_test(world_size=4)
+    def run():
+        from deeperspeed_b200.pipe import PipelineModule
+        dim = 32
+        torch.manual_seed(1234)
+        layers = []
+        for _ in range(8):
+            layers += [torch.nn.Linear(dim, dim), torch.nn.ReLU(), torch.nn.Linear(dim, dim, bias=False)]
+        seq = torch.nn.Sequential(*layers)
+        total_params = sum(p.numel() for p in seq.parameters())
+        import copy
+        plain = copy.deepcopy(seq)
+        pipe = PipelineModule(layers=seq, num_stages=4)
+        mine = torch.tensor([sum(p.numel() for p in pipe.parameters())])
+        dist.all_reduce(mine)
+        assert mine.item() == total_params
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 1, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-3}}}
+        engine, _, _, _ = deepspeed.initialize(model=pipe, model_parameters=[p for p in pipe.parameters()],
+                                               config_params=cfg)
+        torch.manual_seed(99)
+        x = torch.randn(1, dim)
+        data = iter(deepspeed.utils.RepeatingLoader([(x, 0)]))     # the label is meaningless without a loss_fn
+        out = engine.eval_batch(data)
+        # every rank of the pipe group gets the (micro-batch averaged) output of the last stage
+        assert torch.allclose(out.float().cpu(), plain(x), atol=1e-4)
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- zero context
+def test_gathered_parameters_modifier_rank_and_external_params(tmp_path):
+    """reference test_zero_context.py: scatter/gather, GatheredParameters(modifier_rank=0) broadcasts rank 0's update,
+    half-type scatter, external parameter registration through a returned parameter."""
+    @distributed_test(world_size=2)
+    def run():
+        from deeperspeed_b200.runtime.zero.partition_parameters import ZeroParamStatus
+        with deepspeed.zero.Init():
+            lin = torch.nn.Linear(6, 3)
+        assert lin.weight.ds_status == ZeroParamStatus.NOT_AVAILABLE and lin.weight.numel() == 1
+        assert lin.weight.ds_tensor.numel() == 9          # 18 elements over 2 ranks
+        with deepspeed.zero.GatheredParameters(lin.weight, modifier_rank=0):
+            assert lin.weight.shape == (3, 6) and lin.weight.ds_status == ZeroParamStatus.AVAILABLE
+            if dist.get_rank() == 0:
+                with torch.no_grad():
+                    lin.weight.fill_(3.25)
+        assert lin.weight.ds_status == ZeroParamStatus.NOT_AVAILABLE
+        with deepspeed.zero.GatheredParameters(lin.weight):
+            assert torch.all(lin.weight == 3.25)           # rank 1 sees rank 0's modification
+        # modification on a non-modifier rank without modifier_rank is dropped at exit
+        with deepspeed.zero.GatheredParameters(lin.bias):
+            with torch.no_grad():
+                lin.bias.add_(100.0 * (dist.get_rank() + 1))
+        with deepspeed.zero.GatheredParameters(lin.bias):
+            assert lin.bias.abs().max() < 50
+
+        # external parameter: a module returning its own parameter for another module to use
+        class Holder(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.w = torch.nn.Parameter(torch.ones(4, 4))
+
+            def forward(self, x):
+                return x, self.w
+
+        class User(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.holder = Holder()
+                self.lin = torch.nn.Linear(4, 4)
+
+            def forward(self, x, y):
+                h, w = self.holder(x)
+                return torch.nn.functional.cross_entropy((self.lin(h) @ w).float(), y)
+
+        with deepspeed.zero.Init():
+            model = User()
+        deepspeed.zero.register_external_parameter(model, model.holder.w)
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-2}},
+               "fp16": {"enabled": True, "type": "fp32"},
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+        engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        x = torch.randn(2, 4)
+        y = torch.randint(0, 4, (2,))
+        with deepspeed.zero.GatheredParameters(model.holder.w):
+            before = model.holder.w.detach().clone()
+        for _ in range(2):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        with deepspeed.zero.GatheredParameters(model.holder.w):
+            assert not torch.equal(model.holder.w.detach(), before)    # the externally used parameter trained
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- activation checkpointing
+def test_activation_checkpointing_none_and_non_tensor_args():
+    """reference test_activation_checkpointing.py: None inputs, non-tensor inputs/outputs, mixed output ordering."""
+    ckpt = deepspeed.checkpointing
+    lin = torch.nn.Linear(8, 8)
+
+    def fn(a, none_arg, scale, b):
+        assert none_arg is None
+        out = lin(a) * scale + b
+        return "tag", out, 7, out.sum(), None
+
+    a = torch.randn(3, 8, requires_grad=True)
+    b = torch.randn(3, 8, requires_grad=True)
+    ref = fn(a, None, 2.0, b)
+    ref[1].sum().backward()
+    ga, gb, gw = a.grad.clone(), b.grad.clone(), lin.weight.grad.clone()
+    a.grad = b.grad = None
+    lin.zero_grad()
+    out = ckpt.checkpoint(fn, a, None, 2.0, b)
+    assert out[0] == "tag" and out[2] == 7 and out[4] is None
+    assert torch.allclose(out[1], ref[1]) and torch.allclose(out[3], ref[3])
+    out[1].sum().backward()
+    assert torch.allclose(a.grad, ga) and torch.allclose(b.grad, gb) and torch.allclose(lin.weight.grad, gw)
+
+
+# ------------------------------------------------------------------------------------------------- 1-bit Adam checkpoint
+def test_onebit_adam_checkpoint_phases(tmp_path):
+    """reference test_onebit.py (checkpointing): loading a warm-up checkpoint into a run already in compression resets
+    the error-feedback buffers; exp_avg_mask keeps masked rows of the momentum at zero."""
+    @distributed_test(world_size=2)
+    def run():
+        def make(freeze_step):
+            cfg = {"train_batch_size": 2, "steps_per_print": 100,
+                   "optimizer": {"type": "OneBitAdam", "params": {"lr": 1e-3, "freeze_step": freeze_step,
+                                                                  "cuda_aware": False, "comm_backend_name": "nccl"}},
+                   "fp16": {"enabled": True, "type": "fp32"}}
+            torch.manual_seed(3)
+            model = SimpleModel(16)
+            mask = torch.ones(16, 16)
+            mask[:4] = 0
+            groups = [{"params": [model.linear.weight], "exp_avg_mask": mask}, {"params": [model.linear.bias]}]
+            engine, opt, _, _ = deepspeed.initialize(model=model, model_parameters=groups, config_params=cfg)
+            return model, engine, opt
+
+        model, engine, opt = make(freeze_step=2)
+        for n, (x, y) in enumerate(random_dataloader(engine, 10, 16, engine.device)):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+            if n == 0:
+                engine.save_checkpoint(str(tmp_path), tag="warm")      # still in warm-up
+        inner = getattr(opt, "optimizer", opt)
+        assert inner.adam_freeze_key is True                          # compression stage reached
+        st = inner.state[model.linear.weight]
+        assert torch.all(st["exp_avg"][:4] == 0) and st["exp_avg"][4:].abs().sum() > 0
+        assert st["worker_error"].abs().sum() > 0
+        engine.load_checkpoint(str(tmp_path), tag="warm")
+        inner = getattr(engine.optimizer, "optimizer", engine.optimizer)
+        assert inner.adam_freeze_key is False                         # back in warm-up
+        st = inner.state[model.linear.weight] if model.linear.weight in inner.state else None
+        if st is not None and "worker_error" in st:
+            assert st["worker_error"].abs().sum() == 0 and st["server_error"].abs().sum() == 0
+    run()
+
+
+# ------------------------------------------------------------------------------------------------- checkpoint matrix
+@pytest.mark.parametrize("zero_stage", [0, 2])
+def test_checkpoint_lr_scheduler_latest_and_hybrid_state(tmp_path, zero_stage):
+    """reference test_checkpointing.py: LR scheduler state saved/restored (or skipped with
+    load_lr_scheduler_states=False), `latest` drives tag-less loads, missing `latest` -> (None, None), non-tensor
+    optimizer state survives ZeRO."""
+    @distributed_test(world_size=2)
+    def run():
+        cfg = {"train_batch_size": 4, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.01}},
+               "scheduler": {"type": "WarmupLR", "params": {"warmup_min_lr": 0, "warmup_max_lr": 0.01,
+                                                            "warmup_num_steps": 50}},
+               "fp16": {"enabled": True, "type": "fp32"}, "zero_optimization": {"stage": zero_stage}}
+        torch.manual_seed(11)
+        model = SimpleModel(HID)
+        engine, _, _, sched = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=model.parameters())
+        for x, y in random_dataloader(engine, 12, HID, engine.device):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        lr_saved = engine.get_lr()[0]
+        assert 0 < lr_saved < 0.01
+        engine.save_checkpoint(str(tmp_path), tag="first")
+        for x, y in random_dataloader(engine, 4, HID, engine.device, seed=3):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        engine.save_checkpoint(str(tmp_path))            # default tag global_step<N>; `latest` now points at it
+        dist.barrier()
+        latest = open(os.path.join(str(tmp_path), "latest")).read().strip()
+        assert latest == f"global_step{engine.global_steps}"
+
+        def fresh():
+            m = SimpleModel(HID)
+            e, _, _, s = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=m, model_parameters=m.parameters())
+            return e, s
+
+        e2, s2 = fresh()
+        path, _ = e2.load_checkpoint(str(tmp_path))      # no tag -> latest
+        assert path is not None and latest in path and e2.global_steps == engine.global_steps
+        assert e2.get_lr()[0] == pytest.approx(engine.get_lr()[0])
+        e3, s3 = fresh()
+        path, _ = e3.load_checkpoint(str(tmp_path), tag="first", load_lr_scheduler_states=False)
+        assert path is not None and e3.global_steps == 6
+        # the scheduler was NOT restored: stepping it once gives the first warm-up value, not a continuation
+        x, y = next(iter(random_dataloader(e3, 2, HID, e3.device)))
+        loss = e3(x, y); e3.backward(loss); e3.step()
+        assert e3.get_lr()[0] < lr_saved
+        e4, _ = fresh()
+        path, _ = e4.load_checkpoint(str(tmp_path), tag="first")
+        loss = e4(x, y); e4.backward(loss); e4.step()
+        assert e4.get_lr()[0] > lr_saved                 # restored: continues the warm-up
+        # a directory without `latest`
+        assert e4.load_checkpoint(os.path.join(str(tmp_path), "nothing_here")) == (None, None)
+        # a tag that was never written: warning + (None, None), as the reference (engine.py:1589-1596)
+        assert e4.load_checkpoint(str(tmp_path), tag="no_such_tag") == (None, None)
+    run()
+
+
+def test_pipeline_checkpoint_and_repartition(tmp_path):
+    """reference test_checkpointing.py (pipeline): per-layer files let a 2-stage checkpoint load into a 1-stage run."""
+    from simple_model import LinearStackPipe
+
+    def cfg(micro):
+        return {"train_batch_size": 4, "train_micro_batch_size_per_gpu": micro, "steps_per_print": 100,
+                "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}}
+
+    @distributed_test(world_size=2)
+    def save_pp2():
+        from deeperspeed_b200.runtime.pipe.topology import PipeDataParallelTopology
+        torch.manual_seed(21)
+        model = LinearStackPipe(input_dim=16, hidden_dim=16, output_dim=16, num_layers=2,
+                                topology=PipeDataParallelTopology(num_pp=2, num_dp=1))
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg(2)), model=model,
+                                               model_parameters=[p for p in model.parameters()])
+        g = torch.Generator().manual_seed(5)
+        data = [(torch.randn(2, 16, generator=g), torch.randint(0, 16, (2,), generator=g)) for _ in range(8)]
+        it = iter(deepspeed.utils.RepeatingLoader(data))
+        for _ in range(2):
+            engine.train_batch(it)
+        engine.save_checkpoint(str(tmp_path), tag="pp2")
+        # same topology: restore and continue identically
+        torch.manual_seed(99)
+        model2 = LinearStackPipe(input_dim=16, hidden_dim=16, output_dim=16, num_layers=2,
+                                 topology=PipeDataParallelTopology(num_pp=2, num_dp=1))
+        e2, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg(2)), model=model2,
+                                           model_parameters=[p for p in model2.parameters()])
+        path, _ = e2.load_checkpoint(str(tmp_path), tag="pp2")
+        assert path is not None
+        for a, b in zip(engine.module.parameters(), e2.module.parameters()):
+            assert torch.equal(a, b)
+        it1, it2 = iter(deepspeed.utils.RepeatingLoader(data)), iter(deepspeed.utils.RepeatingLoader(data))
+        l1, l2 = engine.train_batch(it1), e2.train_batch(it2)
+        assert float(l1) == pytest.approx(float(l2), rel=1e-6)
+        names = sorted(os.listdir(os.path.join(str(tmp_path), "pp2")))
+        if dist.get_rank() == 0:
+            assert any(n.startswith("layer_") and n.endswith("-model_states.pt") for n in names), names
+            layer_w = {n: torch.load(os.path.join(str(tmp_path), "pp2", n), weights_only=False) for n in names
+                       if n.startswith("layer_")}
+            torch.save(layer_w, os.path.join(str(tmp_path), "layers.pt"))
+    save_pp2()
+
+    @distributed_test(world_size=1)
+    def load_pp1():
+        from deeperspeed_b200.runtime.pipe.topology import PipeDataParallelTopology
+        torch.manual_seed(1)
+        model = LinearStackPipe(input_dim=16, hidden_dim=16, output_dim=16, num_layers=2,
+                                topology=PipeDataParallelTopology(num_pp=1, num_dp=1))
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg(4)), model=model,
+                                               model_parameters=[p for p in model.parameters()])
+        path, _ = engine.load_checkpoint(str(tmp_path), tag="pp2", load_optimizer_states=False,
+                                         load_lr_scheduler_states=False)
+        assert path is not None
+        saved = torch.load(os.path.join(str(tmp_path), "layers.pt"), weights_only=False)
+        flat_saved = torch.cat([v.float().view(-1) for n in sorted(saved) for v in saved[n].values()])
+        flat_now = torch.cat([p.detach().float().view(-1) for p in model.parameters()])
+        assert flat_saved.numel() == flat_now.numel() and torch.allclose(flat_saved, flat_now)
+    load_pp1()
