@@ -488,3 +488,61 @@ def test_pipeline_checkpoint_and_repartition(tmp_path):
         flat_now = torch.cat([p.detach().float().view(-1) for p in model.parameters()])
         assert flat_saved.numel() == flat_now.numel() and torch.allclose(flat_saved, flat_now)
     load_pp1()
+
+
+# ------------------------------------------------------------------------------------------------- test_fp16.py items
+@pytest.mark.parametrize("zero_stage", [0, 1, 2, 3])
+def test_static_loss_scale_and_onecycle(tmp_path, zero_stage):
+    """reference test_fp16.py: static loss scale 138 reaches the optimizer wrapper; OneCycle drives lr/momentum."""
+    @distributed_test(world_size=2)
+    def run():
+        cfg = {"train_batch_size": 4, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.00015}},
+               "scheduler": {"type": "OneCycle", "params": {"cycle_first_step_size": 4, "cycle_first_stair_count": 2,
+                                                            "cycle_second_step_size": 4, "cycle_second_stair_count": 2,
+                                                            "decay_step_size": 4, "cycle_min_lr": 1e-4,
+                                                            "cycle_max_lr": 1e-3, "decay_lr_rate": 0.001,
+                                                            "cycle_min_mom": 0.85, "cycle_max_mom": 0.99,
+                                                            "decay_mom_rate": 0.0}},
+               "fp16": {"enabled": True, "loss_scale": 138.0},
+               "zero_optimization": {"stage": zero_stage}}
+        model = SimpleModel(HID)
+        engine, optim, _, sched = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                       model_parameters=model.parameters())
+        scale = optim.loss_scale if hasattr(optim, "loss_scale") else optim.cur_scale
+        assert float(scale() if callable(scale) else scale) == 138.0
+        assert getattr(optim, "dynamic_loss_scale", False) is False
+        lrs, moms = [], []
+        for x, y in random_dataloader(engine, 40, HID, engine.device, dtype=torch.float16):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+            lrs.append(engine.get_lr()[0])
+            moms.append(engine.get_mom()[0][0] if isinstance(engine.get_mom()[0], (tuple, list)) else engine.get_mom()[0])
+        assert max(lrs) == pytest.approx(1e-3, rel=0.05) and min(lrs) >= 1e-4 * 0.5
+        assert lrs.index(max(lrs)) in (2, 3, 4) and lrs[-1] < max(lrs)
+        assert min(moms) == pytest.approx(0.85, abs=0.02)
+    run()
+
+
+def test_deprecated_zero_flag_and_untested_optimizer(tmp_path):
+    """reference test_fp16.py: `zero_optimization: true` means stage 1; a client optimizer under ZeRO needs
+    `zero_allow_untested_optimizer`."""
+    @distributed_test(world_size=2)
+    def run():
+        base = {"train_batch_size": 4, "steps_per_print": 100, "fp16": {"enabled": True, "type": "bfloat16"}}
+        cfg = dict(base, optimizer={"type": "Adam", "params": {"lr": 1e-3}}, zero_optimization=True)
+        model = SimpleModel(HID)
+        engine, optim, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=model.parameters())
+        assert engine.zero_optimization_stage() == 1
+        cfg = dict(base, zero_optimization={"stage": 1})
+        model = SimpleModel(HID)
+        client = torch.optim.SGD(model.parameters(), lr=0.1)
+        with pytest.raises(AssertionError):
+            deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model, optimizer=client)
+        cfg["zero_allow_untested_optimizer"] = True
+        model = SimpleModel(HID)
+        client = torch.optim.SGD(model.parameters(), lr=0.1)
+        engine, optim, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model, optimizer=client)
+        for x, y in random_dataloader(engine, 4, HID, engine.device, dtype=torch.bfloat16):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+    run()
