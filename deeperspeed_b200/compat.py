@@ -10,6 +10,9 @@ _PKG = "deeperspeed_b200"
 # reference path prefix -> our path prefix (longest prefix wins)
 _REMAP = {
     "deepspeed.pt": _PKG + ".pt",
+    # attributes of the reference package that people also import as modules
+    "deepspeed.checkpointing": _PKG + ".runtime.activation_checkpointing.checkpointing",
+    "deepspeed.zero": _PKG + ".runtime.zero",
     "deepspeed.ops.op_builder": _PKG + ".ops.op_builder",
     "deepspeed": _PKG,
 }
