@@ -401,6 +401,15 @@ SplitWs* get_ws(cudaStream_t stream, size_t bytes, int flag_count) {
         w = &g_ws[g_ws_used++];
         *w = SplitWs{stream, nullptr, 0, nullptr, 0};
     }
+    if (w->ws_bytes < bytes || w->flag_count < flag_count) {
+        // growing means cudaMalloc / cudaFree / a stream sync: none of that is legal while the stream is being
+        // captured into a CUDA graph -> the caller falls back to whole tiles for this launch
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) {
+            cudaGetLastError();
+            return nullptr;
+        }
+    }
     if (w->ws_bytes < bytes) {
         if (w->ws) { cudaStreamSynchronize(stream); cudaFree(w->ws); }
         if (cudaMalloc(&w->ws, bytes) != cudaSuccess) { w->ws = nullptr; w->ws_bytes = 0; return nullptr; }

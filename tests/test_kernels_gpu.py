@@ -288,6 +288,18 @@ def test_softmax(sk, causal):
     assert _rel(dx, K.softmax_bwd(dy.cpu(), y.cpu(), scale=0.3).to(DEV)) < 3e-3
 
 
+@pytest.mark.parametrize("sk", [72, 256, 1024, 1536])
+def test_softmax_group_kernels_ragged_rows(sk):
+    """Short-row kernels (several rows per warp / CTA) with a row count that does not fill the last CTA."""
+    torch.manual_seed(6)
+    x = torch.randn(1, 3, 5, sk, device=DEV, dtype=torch.float16)
+    y = K.softmax_fwd(x, None, scale=0.7, causal=True)
+    ref = K.softmax_fwd(x.cpu(), None, scale=0.7, causal=True).to(DEV)
+    assert _rel(y, ref) < 2e-3
+    dy = torch.randn_like(y)
+    assert _rel(K.softmax_bwd(dy, y, scale=0.7), K.softmax_bwd(dy.cpu(), y.cpu(), scale=0.7).to(DEV)) < 3e-3
+
+
 def test_bias_gelu_dropout_transforms():
     torch.manual_seed(6)
     x = torch.randn(300, 1024, device=DEV, dtype=torch.float16)
