@@ -1,44 +1,43 @@
-"""Row-sparse (CSR-like) gradient container for nn.Embedding grads (reference deepspeed/runtime/csr_tensor.py:11-59)."""
+"""Row-sparse gradient container for embedding tables (`sparse_gradients: true`): the rows of a [rows, cols] gradient
+that are non-zero plus their indices. The engine exchanges (indices, values) with padded all-gathers instead of
+all-reducing the dense table (engine_train.py: csr_allreduce). API of reference deepspeed/runtime/csr_tensor.py:11-59
+(`indices`, `values`, `dense_size`, `to_dense`, `add`, `sparse_size`, `type`)."""
 import torch
 
 
 class CSRTensor:
     def __init__(self, dense_tensor=None):
         self.orig_dense_tensor = dense_tensor
+        self.indices = self.values = self.dense_size = None
         if dense_tensor is not None:
-            result = torch.sum(dense_tensor.abs(), dim=1)
-            self.indices = result.nonzero().flatten()
-            self.values = dense_tensor[self.indices]
-            self.dense_size = list(dense_tensor.size())
-        else:
-            self.indices = None
-            self.values = None
-            self.dense_size = None
+            touched = dense_tensor.ne(0).any(dim=1)          # rows with at least one non-zero entry
+            self.indices = touched.nonzero(as_tuple=False).reshape(-1)
+            self.values = dense_tensor.index_select(0, self.indices)
+            self.dense_size = list(dense_tensor.shape)
 
     @staticmethod
     def type():
         return "deepspeed.CSRTensor"
 
     def to_dense(self):
-        it = self.indices.unsqueeze(1)
-        full_indices = torch.cat([it for _ in range(self.dense_size[1])], dim=1)
-        return self.values.new_zeros(self.dense_size).scatter_add_(0, full_indices, self.values)
+        """Scatter the rows back; duplicate indices (after `add`) accumulate."""
+        dense = self.values.new_zeros(self.dense_size)
+        return dense.index_add_(0, self.indices, self.values)
+
+    def add(self, other):
+        """Concatenate another sparse gradient of the same dense shape (summation happens in `to_dense`)."""
+        assert self.dense_size == other.dense_size, "both operands must describe the same dense tensor"
+        self.indices = torch.cat((self.indices, other.indices))
+        self.values = torch.cat((self.values, other.values))
 
     def sparse_size(self):
-        index_size = list(self.indices.size())
-        value_size = list(self.values.size())
-        dense_size = self.dense_size
-        return index_size[0] + value_size[0] * value_size[1], dense_size[0] * dense_size[1]
-
-    def add(self, b):
-        assert self.dense_size == b.dense_size
-        self.indices = torch.cat([self.indices, b.indices])
-        self.values = torch.cat([self.values, b.values])
-
-    def __str__(self):
-        sparse_size, dense_size = self.sparse_size()
-        return "DeepSpeed.CSRTensor(indices_size={}, values_size={}, dense_size={}, device={}, reduction_factor={})".format(
-            self.indices.size(), self.values.size(), self.dense_size, self.indices.device, dense_size / sparse_size)
+        """(elements held: indices + values, elements of the dense tensor)."""
+        held = self.indices.numel() + self.values.numel()
+        return held, self.dense_size[0] * self.dense_size[1]
 
     def __repr__(self):
-        return self.__str__()
+        held, dense = self.sparse_size()
+        return (f"DeepSpeed.CSRTensor(indices_size={tuple(self.indices.shape)}, values_size={tuple(self.values.shape)}, "
+                f"dense_size={self.dense_size}, device={self.indices.device}, reduction_factor={dense / max(held, 1):.2f})")
+
+    __str__ = __repr__

@@ -1,152 +1,121 @@
-"""AsyncTensorSwapper: streams tensors (e.g. gradients) out to NVMe through rotating pinned buffers, overlapping the
-write of a full buffer with the filling of the next (reference deepspeed/runtime/swap_tensor/async_swapper.py:16-173)."""
+"""AsyncTensorSwapper: streams a sequence of tensors (e.g. gradient partitions) out to files through a small ring of
+pinned staging slabs, so that filling one slab overlaps the file writes of the previous ones.
+
+Same role and public surface as the reference class (deepspeed/runtime/swap_tensor/async_swapper.py:16-173:
+add_buffers / swap_out_tensors / release_buffers / has_buffers / get_timer_names); the mechanics here are a three-queue
+slab pipeline:
+
+    idle slabs  --fill-->  the slab being packed  --seal-->  in-flight slabs (writes submitted)  --drain-->  idle
+
+A slab is sealed when the next tensor does not fit; sealing submits one asynchronous write per packed tensor. A drain
+(`aio_handle.wait()`) happens only when no idle slab is left, or at `release_buffers()`."""
+from collections import deque
+
 import torch
 
 from ...utils.logging import logger
-from .utils import swap_out_tensors, SwapBuffer
+from .utils import SwapBuffer
 
-INVALID_BUFFER_INDEX = -1
 ASYNC_SWAPPER_WAIT_TIMER = "async_swap_gradient_wait"
 
 
 class AsyncTensorSwapper:
     def __init__(self, aio_handle, numel_alignment, timers):
-        self.free_buffer_index = []
-        self.swapping_buffer_index = []
-        self.ready_buffer_index = []
-        self.current_buffer_index = INVALID_BUFFER_INDEX
-        self.all_buffers = []
         self.aio_handle = aio_handle
-        self.numel_alignment = numel_alignment
-        self.max_numel = 0
-        self.num_pending_swaps = 0
+        self.numel_alignment = int(numel_alignment)
         self.timers = timers
-        self.timer_names = set()
-        self.num_elements_swapped = 0
-        self.dtype = None
+        self._slabs = []            # every SwapBuffer handed to us
+        self._idle = deque()        # slabs with nothing in them
+        self._packing = None        # the slab currently receiving tensors
+        self._in_flight = []        # sealed slabs whose writes have been submitted
+        self._writes_pending = 0
+        self._timer_names = set()
+        self._elements_out = 0
+        self._dtype = None
+        self._slab_capacity = 0
 
+    # ------------------------------------------------------------------ buffers
     def has_buffers(self):
-        return len(self.all_buffers) > 0
+        return bool(self._slabs)
 
     def add_buffers(self, buffer_list):
-        assert len(self.all_buffers) == 0
-        assert all([not b.is_cuda for b in buffer_list])
-        dtype = buffer_list[0].dtype
-        assert all([b.dtype == dtype for b in buffer_list])
-        self.dtype = dtype
-        self.all_buffers = [SwapBuffer(buffer) for buffer in buffer_list]
-        self.free_buffer_index += [i for i in range(len(self.all_buffers))]
-        self.max_numel = max([buffer.numel() for buffer in buffer_list])
-        self.timer_names = set()
-
-    def get_timer_names(self):
-        return list(self.timer_names)
+        assert not self._slabs, "buffers were already handed over; release_buffers() first"
+        assert buffer_list and all(not b.is_cuda for b in buffer_list), "staging buffers live in (pinned) host memory"
+        dtypes = {b.dtype for b in buffer_list}
+        assert len(dtypes) == 1, f"staging buffers must share one dtype, got {dtypes}"
+        self._dtype = dtypes.pop()
+        self._slabs = [SwapBuffer(b) for b in buffer_list]
+        self._idle = deque(self._slabs)
+        self._slab_capacity = max(b.numel() for b in buffer_list)
+        self._timer_names = set()
 
     def release_buffers(self):
-        self._report_statistics("Swapped out[Before flush]")
-        self._flush_buffers_until_complete()
-        self._report_statistics("Swapped out[After flush]")
-        pinned_buffers = [buf.buffer for buf in self.all_buffers]
-        self.all_buffers = []
-        self.free_buffer_index = []
-        self.current_buffer_index = INVALID_BUFFER_INDEX
-        self.num_elements_swapped = 0
-        self.dtype = None
-        return pinned_buffers
+        """Flush everything that is still staged, then hand the raw pinned buffers back to the caller."""
+        self._log_volume("swapped out (before final flush)")
+        self._seal()
+        self._drain()
+        assert len(self._idle) == len(self._slabs)
+        self._log_volume("swapped out (after final flush)")
+        raw = [slab.buffer for slab in self._slabs]
+        self._slabs, self._idle, self._packing = [], deque(), None
+        self._elements_out, self._dtype = 0, None
+        return raw
 
+    def get_timer_names(self):
+        return sorted(self._timer_names)
+
+    # ------------------------------------------------------------------ swapping
     def swap_out_tensors(self, tensor_list, path_list):
-        for tensor, swap_path in zip(tensor_list, path_list):
-            self._swap_out_tensor(tensor, swap_path)
+        assert self._slabs, "add_buffers() first"
+        for tensor, path in zip(tensor_list, path_list):
+            need = self._round_up(tensor.numel())
+            assert need <= self._slab_capacity, f"tensor of {tensor.numel()} elements exceeds the staging slab size"
+            if self._packing is not None and not self._packing.has_space(need):
+                self._seal()
+            if self._packing is None:
+                if not self._idle:
+                    self._drain()
+                self._packing = self._idle.popleft()
+            self._packing.insert_tensor(tensor, path, need)
 
-    def _report_statistics(self, message):
-        if torch.distributed.is_initialized() and torch.distributed.get_rank() == 0 and self.dtype is not None:
-            element_size = torch.tensor([], dtype=self.dtype).element_size()
-            swapped_GB = (self.num_elements_swapped * element_size) / (1024 ** 3)
-            logger.info(f"{message} num_elems = {self.num_elements_swapped}, {swapped_GB:5.2f} GB")
+    def _round_up(self, numel):
+        a = self.numel_alignment
+        return (numel + a - 1) // a * a
 
-    def _swap_out_tensor(self, tensor, swap_path):
-        assert len(self.all_buffers) > 0
-        aligned_numel = self._io_aligned_numel(tensor.numel())
-        assert aligned_numel <= self.max_numel
-        self._make_swap_space(aligned_numel)
-        assert self.current_buffer_index != INVALID_BUFFER_INDEX
-        swap_buffer = self._get_current_buffer()
-        swap_buffer.insert_tensor(tensor, swap_path, aligned_numel)
-
-    def _make_swap_space(self, numel):
-        if self.current_buffer_index == INVALID_BUFFER_INDEX:
-            self._allocate_buffer()
+    def _seal(self):
+        """Submit the writes of the slab being packed (if any) and move it to the in-flight list."""
+        slab, self._packing = self._packing, None
+        if slab is None:
             return
-        if not self._get_current_buffer().has_space(numel):
-            if len(self.free_buffer_index) > 0:
-                self._flush_ready_buffers()
-            else:
-                self._flush_buffers_until_complete()
-            self._allocate_buffer()
+        tensors, paths = slab.get_swap_tensors(), slab.get_swap_paths()
+        for t, p in zip(tensors, paths):
+            assert self.aio_handle.async_pwrite(t, p) == 0
+        self._writes_pending += len(tensors)
+        self._in_flight.append(slab)
 
-    def _io_aligned_numel(self, numel):
-        remainder = numel % self.numel_alignment
-        return numel if remainder == 0 else (numel + self.numel_alignment - remainder)
-
-    def _allocate_buffer(self):
-        assert self.current_buffer_index == INVALID_BUFFER_INDEX
-        assert len(self.all_buffers) > 0
-        assert len(self.free_buffer_index) > 0
-        self.current_buffer_index = self.free_buffer_index[-1]
-        self.free_buffer_index = self.free_buffer_index[:-1]
-
-    def _flush_ready_buffers(self):
-        if self.current_buffer_index != INVALID_BUFFER_INDEX:
-            self.ready_buffer_index.append(self.current_buffer_index)
-            self.current_buffer_index = INVALID_BUFFER_INDEX
-        self._swap_out_ready_buffers()
-
-    def _flush_buffers_until_complete(self):
-        self._flush_ready_buffers()
-        assert len(self.ready_buffer_index) == 0
-        self._wait_for_swap_complete()
-        assert len(self.swapping_buffer_index) == 0
-        assert len(self.free_buffer_index) == len(self.all_buffers)
-
-    def _swap_out_ready_buffers(self):
-        for buffer_index in self.ready_buffer_index:
-            buffer = self._get_buffer(buffer_index)
-            swap_tensors = buffer.get_swap_tensors()
-            swap_paths = buffer.get_swap_paths()
-            self.num_pending_swaps += len(swap_tensors)
-            swap_out_tensors(self.aio_handle, swap_tensors, swap_paths)
-        self.swapping_buffer_index += self.ready_buffer_index
-        self.ready_buffer_index = []
-
-    def _wait_for_swap_complete(self):
-        assert len(self.swapping_buffer_index) > 0
-        self._start_timer(ASYNC_SWAPPER_WAIT_TIMER)
-        assert self.aio_handle.wait() == self.num_pending_swaps
-        self._stop_timer(ASYNC_SWAPPER_WAIT_TIMER)
-        self.timer_names.add(ASYNC_SWAPPER_WAIT_TIMER)
-        self.num_pending_swaps = 0
-        for buffer_index in self.swapping_buffer_index:
-            buffer = self._get_buffer(buffer_index)
-            self.num_elements_swapped += buffer.get_num_elem()
-            buffer.reset()
-        self.free_buffer_index += self.swapping_buffer_index
-        assert len(self.free_buffer_index) <= len(self.all_buffers)
-        self.swapping_buffer_index = []
-
-    def _get_buffer(self, index):
-        assert index != INVALID_BUFFER_INDEX
-        return self.all_buffers[index]
-
-    def _get_current_buffer(self):
-        return self._get_buffer(self.current_buffer_index)
-
-    def _start_timer(self, name):
+    def _drain(self):
+        """Wait for every submitted write, recycle the slabs."""
+        if not self._in_flight:
+            return
         if self.timers:
-            self.timers(name).start()
-
-    def _stop_timer(self, name):
+            self.timers(ASYNC_SWAPPER_WAIT_TIMER).start()
+        done = self.aio_handle.wait()
         if self.timers:
-            self.timers(name).stop()
+            self.timers(ASYNC_SWAPPER_WAIT_TIMER).stop()
+            self._timer_names.add(ASYNC_SWAPPER_WAIT_TIMER)
+        assert done == self._writes_pending, f"expected {self._writes_pending} completed writes, got {done}"
+        self._writes_pending = 0
+        for slab in self._in_flight:
+            self._elements_out += slab.get_num_elem()
+            slab.reset()
+            self._idle.append(slab)
+        self._in_flight = []
+
+    def _log_volume(self, what):
+        if self._dtype is None or not torch.distributed.is_initialized() or torch.distributed.get_rank() != 0:
+            return
+        gib = self._elements_out * torch.empty((), dtype=self._dtype).element_size() / 2 ** 30
+        logger.info(f"{what}: {self._elements_out} elements, {gib:5.2f} GiB")
 
     def _log_timers(self, name_list, force=False):
         if self.timers and force:

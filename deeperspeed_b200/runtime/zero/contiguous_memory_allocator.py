@@ -1,182 +1,107 @@
-"""Contiguous memory allocator with defragmentation (API of reference
-deepspeed/runtime/zero/contiguous_memory_allocator.py:9-283): hands out views of one big buffer; when no free block is
-large enough but the total free space is, live tensors are compacted towards the start and their owners re-pointed."""
+"""Arena allocator with compaction: hands out views of one preallocated buffer and, when the free space is large
+enough but fragmented, slides the live blocks down to the start of the arena and re-points their owners.
+
+Same public surface as the reference allocator (deepspeed/runtime/zero/contiguous_memory_allocator.py:9-283:
+allocate_tensor / assign_to_param / release_tensor / release_tensor_with_id / print_allocation / max_allocated).
+Bookkeeping here is a single address-ordered list of live blocks; free extents are the gaps between them, so there is
+no separate free map to keep consistent and compaction is one ordered pass."""
+import bisect
+from dataclasses import dataclass, field
+from typing import List
+
 import torch
+
+
+@dataclass(eq=False)
+class _Block:
+    start: int
+    size: int
+    view: torch.Tensor                      # the tensor handed to the caller (its .data is re-pointed on compaction)
+    params: List[torch.nn.Parameter] = field(default_factory=list)
 
 
 class ContiguousMemoryAllocator:
     def __init__(self, size, dtype, device):
         self.buffer = torch.zeros(size, dtype=dtype, device=device)
-        self.contiguous_sizes = {0: size}      # free blocks: start -> length
-        self.tensor_addresses = {}             # tensor id -> start
-        self.tensor_sizes = {}                 # start -> length (allocated)
-        self.tensor_ids = {}                   # start -> tensor id
-        self.tensor_map = {}                   # tensor id -> tensor view
-        self.id_to_params = {}                 # tensor id -> [params whose .data alias the view]
         self.total_size = size
         self.total_free = size
-        self.largest_contiguous = size
-        self._max_allocated = 0
-        self.count = 0
+        self._blocks: List[_Block] = []     # sorted by start
+        self._by_id = {}                    # id(view) -> block
+        self._peak = 0
+        self.count = 0                      # allocations served so far
 
-    def allocate_tensor(self, size):
-        free_before = self.total_free
-        assert size <= self.total_free, "Not enough memory in buffer. Allocation failed"
-        if self.largest_contiguous < size:
-            self._defragment_memory()
-            self._reset_param_data()
-        self.total_free -= size
-        allocated = self.total_size - self.total_free
-        self._max_allocated = max(self._max_allocated, allocated)
-        tensor_address = self._get_new_tensor_address(size)
-        ret_tensor = self._get_new_tensor(tensor_address, size)
-        assert self.total_free + size == free_before, "Allocation bookkeeping error"
-        return ret_tensor
+    # ------------------------------------------------------------------ queries
+    def _gaps(self):
+        """Free extents (start, size) in address order."""
+        cursor = 0
+        for b in self._blocks:
+            if b.start > cursor:
+                yield cursor, b.start - cursor
+            cursor = b.start + b.size
+        if cursor < self.total_size:
+            yield cursor, self.total_size - cursor
 
-    def assign_to_param(self, tensor, param, numel, shape):
-        tensor_id = id(tensor)
-        assert tensor_id in self.tensor_map, "No such tensor allocated by the allocator."
-        assert tensor.numel() >= numel, "Assert tensor buffer does is not large enough"
-        assert tensor_id not in self.id_to_params, "This tensor has already been assigned to a param"
-        self.id_to_params[tensor_id] = [param]
-        replicated_tensor = tensor.narrow(0, 0, numel).view(shape)
-        param.data = replicated_tensor.data
-
-    def release_tensor(self, tensor):
-        free_before = self.total_free
-        tensor_id = id(tensor)
-        tensor_size = tensor.numel()
-        self._release_tensor(tensor_id)
-        self._unassign_params(tensor_id)
-        self.total_free += tensor_size
-        assert self.total_free - tensor_size == free_before, "Release bookkeeping error"
-
-    def release_tensor_with_id(self, tensor_id):
-        free_before = self.total_free
-        assert tensor_id in self.tensor_map, "Invalid tensor id"
-        tensor = self.tensor_map[tensor_id]
-        tensor_size = tensor.numel()
-        self._release_tensor(tensor_id)
-        self._unassign_params(tensor_id)
-        self.total_free += tensor_size
-        assert self.total_free - tensor_size == free_before, "Release bookkeeping error"
-
-    def print_allocation(self, resolution=200):
-        total_size = self.buffer.numel() * 1.0
-        empty = []
-        for addr, size in self.contiguous_sizes.items():
-            start = int(addr * resolution / total_size)
-            end = int((addr + size) * resolution / total_size)
-            empty.extend(range(start, end))
-        s = ""
-        for i in range(resolution):
-            s += "." if i in empty else "|"
-        print(s)
+    @property
+    def largest_contiguous(self):
+        return max((size for _, size in self._gaps()), default=0)
 
     def max_allocated(self):
-        return self._max_allocated
+        return self._peak
 
-    def _reset_param_data(self):
-        for id_, tensor in self.tensor_map.items():
-            for param in self.id_to_params.get(id_, []):
-                param.data = tensor.narrow(0, 0, param.numel()).view(param.data.shape).data
+    def print_allocation(self, resolution=200):
+        cells = ["|"] * resolution
+        for start, size in self._gaps():
+            lo = int(start * resolution / self.total_size)
+            hi = int((start + size) * resolution / self.total_size)
+            for i in range(lo, min(hi, resolution)):
+                cells[i] = "."
+        print("".join(cells))
 
-    def _unassign_params(self, tensor_id):
-        if tensor_id in self.id_to_params:
-            del self.id_to_params[tensor_id]
-
-    def _release_tensor(self, tensor_id):
-        assert tensor_id in self.tensor_addresses, f"Tensor id {tensor_id} not found"
-        address = self.tensor_addresses[tensor_id]
-        contiguous_size = self.tensor_map[tensor_id].numel()
-        del self.tensor_addresses[tensor_id]
-        del self.tensor_ids[address]
-        del self.tensor_map[tensor_id]
-        del self.tensor_sizes[address]
-        self._consolidate_address(address, contiguous_size)
-        self.largest_contiguous = self._largest_contiguous()
-
-    def _consolidate_address(self, address, contiguous_size):
-        # merge with the free block that starts right after
-        end_address = address + contiguous_size
-        if end_address in self.contiguous_sizes:
-            contiguous_size += self.contiguous_sizes[end_address]
-            del self.contiguous_sizes[end_address]
-        # merge with the free block that ends right before
-        for addr, size in list(self.contiguous_sizes.items()):
-            if addr + size == address:
-                del self.contiguous_sizes[addr]
-                contiguous_size += size
-                address = addr
-                break
-        self.contiguous_sizes[address] = contiguous_size
-
-    def _defragment_memory(self):
-        empty_addresses = sorted(self.contiguous_sizes.keys())
-        tensor_addresses = sorted(self.tensor_addresses.values())
-        tensor_index = 0
-        while tensor_index < len(tensor_addresses):
-            empty_addr = empty_addresses[0]
-            empty_size = self.contiguous_sizes[empty_addr]
-            tensor_addr = tensor_addresses[tensor_index]
-            tensor_size = self.tensor_sizes[tensor_addr]
-            tensor_id = self.tensor_ids[tensor_addr]
-            tensor = self.tensor_map[self.tensor_ids[tensor_addr]]
-            assert tensor_size == tensor.numel(), "Size mismatch"
-            if empty_addr < tensor_addr:
-                if empty_size >= tensor_size:
-                    dest_buffer = self.buffer.narrow(0, empty_addr, tensor_size)
-                    src_buffer = self.buffer.narrow(0, tensor_addr, tensor_size)
-                    dest_buffer.data.copy_(src_buffer.data)
-                else:
-                    src_buffer = self.buffer.narrow(0, tensor_addr, tensor_size)
-                    dest_buffer = self.buffer.narrow(0, empty_addr, tensor_size)
-                    dest_buffer.data.copy_(src_buffer.data.clone())
-                self._replace_old_address_with_new(tensor_id, empty_addr)
-                tensor_index += 1
-            else:
-                tensor_index += 1
-            empty_addresses = sorted(self.contiguous_sizes.keys())
-
-    def _replace_old_address_with_new(self, tensor_id, new_address):
-        tensor = self.tensor_map[tensor_id]
-        tensor_size = tensor.numel()
-        tensor.data = self.buffer.narrow(0, new_address, tensor_size).data
-        self._release_tensor(tensor_id)
-        self._mark_as_occupied(new_address, tensor_size)
-        self.tensor_ids[new_address] = tensor_id
-        self.tensor_map[tensor_id] = tensor
-        self.tensor_addresses[tensor_id] = new_address
-        self.tensor_sizes[new_address] = tensor_size
-
-    def _get_new_tensor_address(self, size):
-        tensor_address = None
-        for address, contiguous_size in self.contiguous_sizes.items():
-            if contiguous_size >= size and (tensor_address is None or contiguous_size < self.contiguous_sizes[tensor_address]):
-                tensor_address = address
-        assert tensor_address is not None, "address cannot be None"
-        return tensor_address
-
-    def _get_new_tensor(self, address, size):
-        available_contiguous_size = self.contiguous_sizes[address]
-        assert size <= available_contiguous_size, "Tensor numel {} is large than available contiguous size {}".format(
-            size, available_contiguous_size)
+    # ------------------------------------------------------------------ allocate / release
+    def allocate_tensor(self, size):
+        assert size <= self.total_free, "Not enough memory in buffer. Allocation failed"
+        if self.largest_contiguous < size:
+            self._compact()
+        # best fit: the smallest gap that holds the request
+        start = min((g for g in self._gaps() if g[1] >= size), key=lambda g: g[1])[0]
+        view = self.buffer.narrow(0, start, size)
+        block = _Block(start, size, view)
+        bisect.insort(self._blocks, block, key=lambda b: b.start)
+        self._by_id[id(view)] = block
+        self.total_free -= size
+        self._peak = max(self._peak, self.total_size - self.total_free)
         self.count += 1
-        new_tensor = self.buffer.narrow(0, address, size)
-        tensor_id = id(new_tensor)
-        self.tensor_addresses[tensor_id] = address
-        self.tensor_sizes[address] = size
-        self.tensor_ids[address] = tensor_id
-        self.tensor_map[tensor_id] = new_tensor
-        self._mark_as_occupied(address, size)
-        return new_tensor
+        return view
 
-    def _largest_contiguous(self):
-        return max(self.contiguous_sizes.values()) if len(self.contiguous_sizes) > 0 else 0
+    def assign_to_param(self, tensor, param, numel, shape):
+        block = self._by_id.get(id(tensor))
+        assert block is not None, "No such tensor allocated by the allocator."
+        assert tensor.numel() >= numel, "the allocation is smaller than the parameter"
+        assert not block.params, "This tensor has already been assigned to a param"
+        block.params.append(param)
+        param.data = tensor.narrow(0, 0, numel).view(shape).data
 
-    def _mark_as_occupied(self, address, size):
-        available_contiguous_size = self.contiguous_sizes[address]
-        del self.contiguous_sizes[address]
-        if available_contiguous_size != size:
-            self.contiguous_sizes[address + size] = available_contiguous_size - size
-        self.largest_contiguous = self._largest_contiguous()
+    def release_tensor(self, tensor):
+        self.release_tensor_with_id(id(tensor))
+
+    def release_tensor_with_id(self, tensor_id):
+        block = self._by_id.pop(tensor_id, None)
+        assert block is not None, "Invalid tensor id"
+        self._blocks.remove(block)
+        self.total_free += block.size
+
+    # ------------------------------------------------------------------ compaction
+    def _compact(self):
+        """Slide every live block down so that all free space ends up in one extent at the top."""
+        cursor = 0
+        for block in self._blocks:          # address order: a block only ever moves towards lower addresses
+            if block.start != cursor:
+                src = self.buffer.narrow(0, block.start, block.size)
+                dst = self.buffer.narrow(0, cursor, block.size)
+                overlap = cursor + block.size > block.start
+                dst.copy_(src.clone() if overlap else src)
+                block.start = cursor
+                block.view.data = dst.data
+                for p in block.params:
+                    p.data = dst.narrow(0, 0, p.numel()).view(p.data.shape).data
+            cursor += block.size
