@@ -281,19 +281,22 @@ ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __
     }
 }
 
-// Fold the per-CTA partial rows: CTA = 32 columns x 8 row slices, one output column per lane, smem cross-slice sum.
+// Fold the per-CTA partial rows: CTA = 32 columns x 32 row slices (1024 threads), one output column per lane, shared
+// memory cross-slice sum. (With 8 slices every thread walked 37 rows back to back and the kernel took 10.5 us, a third
+// of the backward itself: profiles/ncu_ops_table.txt.)
+constexpr int FIN_SLICES = 32;
 template <typename T>
-__global__ void __launch_bounds__(256) ln_bwd_finalize(const float* __restrict__ part_g,
-                                                       const float* __restrict__ part_b, int nparts, int hidden,
-                                                       T* __restrict__ dgamma, T* __restrict__ dbeta,
-                                                       int accumulate) {
-    __shared__ float sg[8][33], sb[8][33];
+__global__ void __launch_bounds__(32 * FIN_SLICES) ln_bwd_finalize(const float* __restrict__ part_g,
+                                                                   const float* __restrict__ part_b, int nparts,
+                                                                   int hidden, T* __restrict__ dgamma,
+                                                                   T* __restrict__ dbeta, int accumulate) {
+    __shared__ float sg[FIN_SLICES][33], sb[FIN_SLICES][33];
     const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + lane;
     float g = 0.f, b = 0.f;
     if (c < hidden) {
 #pragma unroll 4
-        for (int r = slice; r < nparts; r += 8) {
+        for (int r = slice; r < nparts; r += FIN_SLICES) {
             g += part_g[(long)r * hidden + c];
             b += part_b[(long)r * hidden + c];
         }
@@ -303,7 +306,7 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize(const float* __restrict__
     __syncthreads();
     if (slice == 0 && c < hidden) {
 #pragma unroll
-        for (int s = 1; s < 8; ++s) { g += sg[s][lane]; b += sb[s][lane]; }
+        for (int s = 1; s < FIN_SLICES; ++s) { g += sg[s][lane]; b += sb[s][lane]; }
         if (accumulate) {   // add into the parameters' existing gradient (views of the flat gradient arena)
             g += Cvt<T>::to_f(dgamma[c]);
             b += Cvt<T>::to_f(dbeta[c]);
@@ -358,7 +361,7 @@ extern "C" int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float*
     float* pb = pg + (long)LN_BWD_BLOCKS * hidden;
 #define LNB(T, I, RR) ln_bwd_kernel<T, I, RR><<<grid, LN_THREADS, 0, s>>>((const T*)dy, (const T*)x, mean, rstd, (const T*)gamma, (const T*)dres, (T*)dx, pg, pb, rows, hidden)
 #define LNB_D(T) do { if (iters <= 1) LNB(T, 1, 2); else if (iters <= 2) LNB(T, 2, 1); else LNB(T, 4, 1); \
-        ln_bwd_finalize<T><<<(hidden + 31) / 32, 256, 0, s>>>(pg, pb, grid, hidden, (T*)dgamma, (T*)dbeta, accumulate); } while (0)
+        ln_bwd_finalize<T><<<(hidden + 31) / 32, 32 * FIN_SLICES, 0, s>>>(pg, pb, grid, hidden, (T*)dgamma, (T*)dbeta, accumulate); } while (0)
     if (dtype == DSB_DTYPE_F16) LNB_D(__half);
     else if (dtype == DSB_DTYPE_BF16) LNB_D(__nv_bfloat16);
     else return DSB_ERR_DTYPE;

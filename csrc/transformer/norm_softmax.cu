@@ -218,7 +218,8 @@ static int softmax_fwd_launch(const void* x, const void* mask, void* y, long row
     const T* mp = reinterpret_cast<const T*>(mask);
     T* yp = reinterpret_cast<T*>(y);
     const int nvec = k_len >> 3;
-    if (nvec <= 256) {   // k_len <= 2048: row per lane group
+    if (nvec <= 64) {   // k_len <= 512: row per lane group (longer rows keep too many values per lane: 145 registers,
+                        // 11 % occupancy at k_len 2048, profiles/ncu_ops_table.txt) -> one CTA per row above that
 #define SMG(I, GG) softmax_fwd_group_kernel<T, I, GG><<<(unsigned)((rows + SM_THREADS / GG - 1) / (SM_THREADS / GG)), SM_THREADS, 0, s>>>(xp, mp, yp, rows, heads, q_len, k_len, scale, causal)
         if (nvec <= 8) SMG(1, 8); else if (nvec <= 16) SMG(1, 16); else if (nvec <= 32) SMG(1, 32);
         else if (nvec <= 64) SMG(2, 32); else if (nvec <= 128) SMG(4, 32); else SMG(8, 32);
@@ -240,7 +241,7 @@ static int softmax_bwd_launch(const void* dy, const void* y, void* dx, long rows
     const T* yp = reinterpret_cast<const T*>(y);
     T* dp = reinterpret_cast<T*>(dx);
     const int nvec = k_len >> 3;
-    if (nvec <= 256) {
+    if (nvec <= 64) {
 #define SBG(I, GG) softmax_bwd_group_kernel<T, I, GG><<<(unsigned)((rows + SM_THREADS / GG - 1) / (SM_THREADS / GG)), SM_THREADS, 0, s>>>(gp, yp, dp, rows, k_len, scale)
         if (nvec <= 8) SBG(1, 8); else if (nvec <= 16) SBG(1, 16); else if (nvec <= 32) SBG(1, 32);
         else if (nvec <= 64) SBG(2, 32); else if (nvec <= 128) SBG(4, 32); else SBG(8, 32);

@@ -115,6 +115,15 @@ def main():
     # ---- fused add
     report("fused_add(3)", timeit([lambda i=i: K.fused_add(xs[i], rs[i], ys[i], out=ss[i]) for i in range(NBUF)]), 4 * act)
 
+    # ---- attention softmax fwd / bwd: BERT (64 x 16 heads, 128 x 128) and long rows (4 x 16 heads, 2048 x 2048)
+    for shape, tag in (((64, 16, 128, 128), "seq128"), ((4, 16, 2048, 2048), "seq2048")):
+        sx = [torch.randn(*shape, device=dev, dtype=dt) for _ in range(2)]
+        sy = [K.softmax_fwd(t, scale=0.125) for t in sx]
+        nb = sx[0].numel() * 2
+        report(f"softmax_fwd({tag})", timeit([lambda i=i: K.softmax_fwd(sx[i], scale=0.125, out=sy[i]) for i in range(2)]), 2 * nb)
+        report(f"softmax_bwd({tag})", timeit([lambda i=i: K.softmax_bwd(sx[i], sy[i], scale=0.125) for i in range(2)]), 3 * nb)
+        del sx, sy
+
     # ---- Adam on a 256M-element shard: fp32 p/m/v rw + fp16 grad read + fp16 param write
     n = 256 * 1024 * 1024
     p = torch.randn(n, device=dev)
