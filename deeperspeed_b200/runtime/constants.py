@@ -119,6 +119,9 @@ ZERO_DEFAULTS = {
     "stage3_gather_fp16_weights_on_model_save": False,
     # B200-native extension: fuse reduce-scatter + cast + Adam + all-gather over NVSwitch peer memory
     "fused_nvlink": "auto",
+    # B200-native extension (stage 3): Linear forwards run the weight all-gather inside the GEMM kernel; shards of
+    # eligible weights live on a peer-mapped heap (zero/partition_parameters.py, parallel/ag_gemm.py)
+    "stage3_fused_allgather_gemm": False,
 }
 OFFLOAD_PARAM = "offload_param"
 OFFLOAD_OPTIMIZER = "offload_optimizer"

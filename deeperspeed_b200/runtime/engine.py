@@ -663,7 +663,8 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
                 mpu=self.mpu, postscale_gradients=self.postscale_gradients(),
                 gradient_predivide_factor=self.gradient_predivide_factor(),
                 gradient_accumulation_steps=self.gradient_accumulation_steps(), aio_config=self.aio_config(),
-                precision=self.precision())
+                precision=self.precision(),
+                fused_allgather_gemm=bool(self._config.zero_config.stage3_fused_allgather_gemm) or None)
         else:
             raise NotImplementedError("ZeRO stage {} not implemented".format(zero_stage))
         return optimizer

@@ -169,7 +169,8 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                  param_persistence_threshold=100000, dp_process_group=None, reduce_scatter=True, overlap_comm=False,
                  offload_optimizer_config=None, offload_param_config=None, sub_group_size=1000000000000, mpu=None,
                  clip_grad=0.0, allreduce_always_fp32=False, postscale_gradients=True, gradient_predivide_factor=1.0,
-                 gradient_accumulation_steps=1, elastic_checkpoint=False, aio_config=None, precision=torch.float16):
+                 gradient_accumulation_steps=1, elastic_checkpoint=False, aio_config=None, precision=torch.float16,
+                 fused_allgather_gemm=None):
         self.module = module
         self.optimizer = init_optimizer
         self.timers = timers
@@ -208,6 +209,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         if any(not is_zero_param(p) for p in module.parameters()):
             remote = offload_param_config["device"] if self.offload_param else None
             Init(module=module, data_parallel_group=dp_process_group, mem_efficient_linear=False,
+                 fused_allgather_gemm=fused_allgather_gemm,
                  remote_device=remote, pin_memory=bool(offload_param_config.get("pin_memory", False)) if self.offload_param else False)
         self.device = next((p.ds_tensor.device for p in module.parameters() if torch.cuda.is_available() is False), None)
         self.device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
