@@ -269,7 +269,11 @@ class PipelineModule(nn.Module):
                 funcs = self.forward_funcs[start_idx:end_idx]
                 if not isinstance(x, tuple):
                     x = (x,)
-                if self._is_checkpointable(funcs):
+                # a chunk fed only by tensors that carry no gradient (token ids into an embedding) cannot be
+                # re-entered by autograd through a checkpoint: its parameters would silently get no gradient (the
+                # reference raises in backward here), so it runs un-checkpointed
+                differentiable_input = any(torch.is_tensor(t) and t.requires_grad for t in x)
+                if self._is_checkpointable(funcs) and differentiable_input:
                     x = self.activation_checkpoint_func(exec_range_func(start_idx, end_idx), *x)
                 else:
                     x = exec_range_func(start_idx, end_idx)(*x)

@@ -546,3 +546,58 @@ def test_deprecated_zero_flag_and_untested_optimizer(tmp_path):
         for x, y in random_dataloader(engine, 4, HID, engine.device, dtype=torch.bfloat16):
             loss = engine(x, y); engine.backward(loss); engine.step()
     run()
+
+
+# ------------------------------------------------------------------------------------------------- tied layers in a pipeline
+def test_pipeline_tied_embedding_matches_single_process(tmp_path):
+    """TiedLayerSpec: the embedding of stage 0 is reused as the output projection on the last stage; the tied
+    gradient all-reduce must make a 2-stage run (with activation checkpointing) equal the 1-stage run."""
+    from deeperspeed_b200.pipe import PipelineModule, LayerSpec, TiedLayerSpec
+    from deeperspeed_b200.runtime.pipe.topology import PipeDataParallelTopology
+    VOCAB, DIM = 32, 16
+
+    def out_proj(embedding, x):
+        return torch.nn.functional.linear(x, embedding.weight)
+
+    def build(num_pp, ckpt_interval):
+        torch.manual_seed(77)
+        specs = [TiedLayerSpec("embed", torch.nn.Embedding, VOCAB, DIM),
+                 LayerSpec(torch.nn.Linear, DIM, DIM), torch.nn.Tanh(),
+                 LayerSpec(torch.nn.Linear, DIM, DIM), torch.nn.Tanh(),
+                 LayerSpec(torch.nn.Linear, DIM, DIM),
+                 TiedLayerSpec("embed", torch.nn.Embedding, VOCAB, DIM, forward_fn=out_proj)]
+        return PipelineModule(layers=specs, topology=PipeDataParallelTopology(num_pp=num_pp, num_dp=1),
+                              loss_fn=lambda out, y: torch.nn.functional.cross_entropy(out.float().view(-1, VOCAB), y.view(-1)),
+                              partition_method="uniform", activation_checkpoint_interval=ckpt_interval, seed_layers=True)
+
+    cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 1, "steps_per_print": 100,
+           "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}}
+    g = torch.Generator().manual_seed(3)
+    data = [(torch.randint(0, VOCAB, (1, 6), generator=g), torch.randint(0, VOCAB, (1, 6), generator=g)) for _ in range(8)]
+
+    def train(engine):
+        it = iter(deepspeed.utils.RepeatingLoader(data))
+        return [float(engine.train_batch(it)) for _ in range(3)]
+
+    @distributed_test(world_size=1)
+    def single():
+        model = build(1, 0)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=[p for p in model.parameters()])
+        losses = train(engine)
+        emb = model.tied_modules["embed"].weight.detach().clone()
+        torch.save({"losses": losses, "emb": emb}, os.path.join(str(tmp_path), "single.pt"))
+    single()
+
+    @distributed_test(world_size=2)
+    def piped():
+        model = build(2, 1)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=[p for p in model.parameters()])
+        losses = train(engine)
+        ref = torch.load(os.path.join(str(tmp_path), "single.pt"), weights_only=False)
+        assert losses == pytest.approx(ref["losses"], rel=1e-4, abs=1e-5)
+        # both stages hold the same (trained) tied weight, equal to the single-process result
+        emb = model.tied_modules["embed"].weight.detach()
+        assert torch.allclose(emb, ref["emb"], atol=1e-5)
+    piped()
