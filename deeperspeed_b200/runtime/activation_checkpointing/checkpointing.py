@@ -454,7 +454,8 @@ def reset():
     if CONTIGUOUS_CHECKPOINTING:
         for buffers in (contiguous_data_buffers, contiguous_size_buffers):
             for i in range(len(buffers)):
-                buffers[i] = torch.tensor(())
+                buffers[i] = None       # re-allocated by the next forward (the reference stores an empty tensor here,
+                                        # which its own forward then fails to narrow)
         data_offsets[:] = [0] * len(data_offsets)
         size_offsets[:] = [0] * len(size_offsets)
 

@@ -601,3 +601,69 @@ def test_pipeline_tied_embedding_matches_single_process(tmp_path):
         emb = model.tied_modules["embed"].weight.detach()
         assert torch.allclose(emb, ref["emb"], atol=1e-5)
     piped()
+
+
+# ------------------------------------------------------------------------------------------------- partitioned activations
+class _FakeMPU:
+    """Model-parallel group = the whole (2-rank) world, data-parallel size 1."""
+
+    def get_model_parallel_rank(self):
+        return dist.get_rank()
+
+    def get_model_parallel_world_size(self):
+        return dist.get_world_size()
+
+    def get_model_parallel_group(self):
+        return dist.group.WORLD
+
+    def get_data_parallel_rank(self):
+        return 0
+
+    def get_data_parallel_world_size(self):
+        return 1
+
+    def get_data_parallel_group(self):
+        return None
+
+
+@pytest.mark.parametrize("cpu_ckpt,contiguous", [(False, False), (True, False), (False, True), (True, True)])
+def test_partitioned_activation_checkpointing(cpu_ckpt, contiguous):
+    """Activation checkpointing with partition_activations over a 2-rank model-parallel group (+ CPU offload of the
+    partitions, + contiguous buffers): the saved input is split across the ranks and all-gathered for the recompute;
+    outputs and gradients equal the plain run (reference checkpointing.py:256-291,340-420)."""
+    @distributed_test(world_size=2)
+    def run():
+        ckpt = deepspeed.checkpointing
+        ckpt.reset() if hasattr(ckpt, "reset") else None
+        ckpt.configure(_FakeMPU(), partition_activations=True, checkpoint_in_cpu=cpu_ckpt,
+                       contiguous_checkpointing=contiguous, num_checkpoints=2, synchronize=False, profile=False)
+        torch.manual_seed(0)            # identical parameters and inputs on both model-parallel ranks
+        l1, l2 = torch.nn.Linear(16, 16), torch.nn.Linear(16, 16)
+        x = torch.randn(4, 6, 16, requires_grad=True)
+
+        def block1(a):
+            return torch.tanh(l1(a))
+
+        def block2(a):
+            return torch.tanh(l2(a))
+
+        ref = block2(block1(x))
+        ref.sum().backward()
+        gx = x.grad.clone()
+        gw = [p.grad.clone() for p in list(l1.parameters()) + list(l2.parameters())]
+        x.grad = None
+        for p in list(l1.parameters()) + list(l2.parameters()):
+            p.grad = None
+        for _ in range(2):              # second pass reuses the contiguous buffers
+            x.grad = None
+            for p in list(l1.parameters()) + list(l2.parameters()):
+                p.grad = None
+            out = ckpt.checkpoint(block2, ckpt.checkpoint(block1, x))
+            assert torch.allclose(out, ref, atol=1e-6)
+            out.sum().backward()
+            assert torch.allclose(x.grad, gx, atol=1e-6)
+            for p, g in zip(list(l1.parameters()) + list(l2.parameters()), gw):
+                assert torch.allclose(p.grad, g, atol=1e-6)
+            ckpt.reset()
+        ckpt.configure(None, partition_activations=False, checkpoint_in_cpu=False, contiguous_checkpointing=False)
+    run()
