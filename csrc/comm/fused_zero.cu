@@ -172,6 +172,192 @@ __global__ void __launch_bounds__(512) fused_adam_ag_kernel(const float* __restr
     if (blockIdx.x == 0) xgpu_barrier(flags, R, me, 1, epoch);
 }
 
+// ---- LAMB variant ------------------------------------------------------------------------------------------------
+// One launch per parameter group covers every bucket slice this rank owns (local index l -> bucket l / sub, arena
+// offset (bucket * R + me) * sub + l % sub). LAMB's trust ratio is per TENSOR while a tensor may be spread over
+// several ranks' slices, so the kernel has three phases separated by cross-GPU barriers:
+//   1. moments + update u (kept in place of the reduced gradient) + per-tensor partial sums of w^2 and u^2, folded
+//      per CTA in shared-memory bins and added to this rank's norm table in the symmetric heap;
+//   2. after a cross-GPU barrier every CTA reads the R norm tables over NVLink for the tensors it touches and
+//      forms coeff = clamp(|w| / |u|, min, max);
+//   3. p -= step_size * coeff * u on the fp32 master, cast, and push into every peer's parameter arena.
+// Replaces reference csrc/lamb/fused_lamb_cuda_kernel.cu:186-310 + the stage-1 all_gather (zero/stage1.py:763-773);
+// the reference itself applies LAMB per flat sub-partition under ZeRO, i.e. with a per-partition ratio.
+struct LambH {
+    float beta1, beta2, eps, wd, max_coeff, min_coeff, step_size;
+    int eps_inside;
+};
+
+DSB_DEVICE int find_seg(const long* __restrict__ seg_start, int nseg, long e) {
+    int lo = 0, hi = nseg - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (seg_start[mid] <= e) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+constexpr int LAMB_BINS = 256;
+
+template <typename T>
+__global__ void __launch_bounds__(512) fused_lamb_ag_kernel(float* __restrict__ u32, float* __restrict__ p32,
+                                                            float* __restrict__ m, float* __restrict__ v,
+                                                            PeerPtrs params, PeerPtrs norms, FlagPtrs flags, int R,
+                                                            int me, long sub, long n,
+                                                            const long* __restrict__ seg_start,
+                                                            const int* __restrict__ seg_tid, int nseg, int ntensors,
+                                                            LambH h, const float* __restrict__ inv_scale_dev,
+                                                            const int* __restrict__ skip_dev,
+                                                            float* __restrict__ coeff_out, uint32_t epoch) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ float bin_w[LAMB_BINS], bin_u[LAMB_BINS], bin_c[LAMB_BINS];
+    const bool skip = skip_dev != nullptr && *skip_dev != 0;
+    const float inv = inv_scale_dev != nullptr ? *inv_scale_dev : 1.f;
+    float* my_norms = reinterpret_cast<float*>(norms.p[me]);
+    // the previous launch's closing barrier guarantees that no peer still reads this table
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * ntensors; i += gridDim.x * blockDim.x) my_norms[i] = 0.f;
+    for (int i = threadIdx.x; i < LAMB_BINS; i += blockDim.x) {
+        bin_w[i] = 0.f;
+        bin_u[i] = 0.f;
+        bin_c[i] = 1.f;
+    }
+    grid.sync();
+
+    // contiguous range of 8-element vectors per CTA, so a CTA crosses few tensor boundaries
+    const long nvec = n >> 3;
+    const long per_block = (nvec + gridDim.x - 1) / gridDim.x;
+    const long v0 = (long)blockIdx.x * per_block;
+    const long v1 = v0 + per_block < nvec ? v0 + per_block : nvec;
+    const bool have = v0 < v1;
+    const int seg0 = have ? find_seg(seg_start, nseg, v0 * 8) : 0;
+    const int seg1 = have ? find_seg(seg_start, nseg, (v1 - 1) * 8) : -1;
+
+    if (!skip && have) {
+        int cur = -1;
+        long next_start = 0;
+        float w2 = 0.f, u2 = 0.f;
+        for (long i = v0 + threadIdx.x; i < v1; i += blockDim.x) {
+            const long e = i * 8;
+            if (cur < 0 || e >= next_start) {
+                if (cur >= 0) {
+                    const int rel = cur - seg0;
+                    if (rel < LAMB_BINS) {
+                        atomicAdd(&bin_w[rel], w2);
+                        atomicAdd(&bin_u[rel], u2);
+                    } else {
+                        atomicAdd(&my_norms[2 * seg_tid[cur]], w2);
+                        atomicAdd(&my_norms[2 * seg_tid[cur] + 1], u2);
+                    }
+                    w2 = u2 = 0.f;
+                }
+                cur = find_seg(seg_start, nseg, e);
+                next_start = seg_start[cur + 1];
+            }
+            float g[8], p[8], mm[8], vv[8];
+            *reinterpret_cast<float4*>(g) = *reinterpret_cast<const float4*>(u32 + e);
+            *reinterpret_cast<float4*>(g + 4) = *reinterpret_cast<const float4*>(u32 + e + 4);
+            *reinterpret_cast<float4*>(p) = *reinterpret_cast<const float4*>(p32 + e);
+            *reinterpret_cast<float4*>(p + 4) = *reinterpret_cast<const float4*>(p32 + e + 4);
+            *reinterpret_cast<float4*>(mm) = *reinterpret_cast<const float4*>(m + e);
+            *reinterpret_cast<float4*>(mm + 4) = *reinterpret_cast<const float4*>(m + e + 4);
+            *reinterpret_cast<float4*>(vv) = *reinterpret_cast<const float4*>(v + e);
+            *reinterpret_cast<float4*>(vv + 4) = *reinterpret_cast<const float4*>(v + e + 4);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float gr = g[k] * inv;
+                mm[k] = h.beta1 * mm[k] + (1.f - h.beta1) * gr;
+                vv[k] = h.beta2 * vv[k] + (1.f - h.beta2) * gr * gr;
+                const float denom = h.eps_inside ? sqrtf(vv[k] + h.eps) : sqrtf(vv[k]) + h.eps;
+                g[k] = mm[k] / denom + h.wd * p[k];
+                w2 += p[k] * p[k];
+                u2 += g[k] * g[k];
+            }
+            *reinterpret_cast<float4*>(u32 + e) = *reinterpret_cast<float4*>(g);
+            *reinterpret_cast<float4*>(u32 + e + 4) = *reinterpret_cast<float4*>(g + 4);
+            *reinterpret_cast<float4*>(m + e) = *reinterpret_cast<float4*>(mm);
+            *reinterpret_cast<float4*>(m + e + 4) = *reinterpret_cast<float4*>(mm + 4);
+            *reinterpret_cast<float4*>(v + e) = *reinterpret_cast<float4*>(vv);
+            *reinterpret_cast<float4*>(v + e + 4) = *reinterpret_cast<float4*>(vv + 4);
+        }
+        if (cur >= 0) {
+            const int rel = cur - seg0;
+            if (rel < LAMB_BINS) {
+                atomicAdd(&bin_w[rel], w2);
+                atomicAdd(&bin_u[rel], u2);
+            } else {
+                atomicAdd(&my_norms[2 * seg_tid[cur]], w2);
+                atomicAdd(&my_norms[2 * seg_tid[cur] + 1], u2);
+            }
+        }
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < LAMB_BINS && seg0 + b <= seg1; b += blockDim.x) {
+        if (bin_w[b] != 0.f || bin_u[b] != 0.f) {
+            atomicAdd(&my_norms[2 * seg_tid[seg0 + b]], bin_w[b]);
+            atomicAdd(&my_norms[2 * seg_tid[seg0 + b] + 1], bin_u[b]);
+        }
+    }
+    __threadfence_system();
+    grid.sync();
+    // every rank's norm table is complete and visible before anybody reads it
+    if (blockIdx.x == 0) xgpu_barrier(flags, R, me, 2, epoch);
+    grid.sync();
+
+    auto coeff_for = [&](int tid) -> float {
+        float w = 0.f, u = 0.f;
+        for (int r = 0; r < R; ++r) {
+            const uint32_t* t = reinterpret_cast<const uint32_t*>(norms.p[r]) + 2 * tid;
+            w += __uint_as_float(ld_relaxed_sys(t));
+            u += __uint_as_float(ld_relaxed_sys(t + 1));
+        }
+        float c = 1.f;
+        if (w > 0.f && u > 0.f) c = fminf(fmaxf(sqrtf(w) / sqrtf(u), h.min_coeff), h.max_coeff);
+        return c;
+    };
+    for (int b = threadIdx.x; b < LAMB_BINS && seg0 + b <= seg1; b += blockDim.x) {
+        const int tid = seg_tid[seg0 + b];
+        const float c = coeff_for(tid);
+        bin_c[b] = c;
+        if (coeff_out != nullptr && !skip) coeff_out[tid] = c;
+    }
+    __syncthreads();
+
+    if (!skip && have) {
+        int cur = -1;
+        long next_start = 0;
+        float c = 1.f;
+        for (long i = v0 + threadIdx.x; i < v1; i += blockDim.x) {
+            const long e = i * 8;
+            if (cur < 0 || e >= next_start) {
+                cur = find_seg(seg_start, nseg, e);
+                next_start = seg_start[cur + 1];
+                c = (cur - seg0 < LAMB_BINS) ? bin_c[cur - seg0] : coeff_for(seg_tid[cur]);
+            }
+            float u[8], p[8];
+            *reinterpret_cast<float4*>(u) = *reinterpret_cast<const float4*>(u32 + e);
+            *reinterpret_cast<float4*>(u + 4) = *reinterpret_cast<const float4*>(u32 + e + 4);
+            *reinterpret_cast<float4*>(p) = *reinterpret_cast<const float4*>(p32 + e);
+            *reinterpret_cast<float4*>(p + 4) = *reinterpret_cast<const float4*>(p32 + e + 4);
+            const float s = h.step_size * c;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) p[k] -= s * u[k];
+            *reinterpret_cast<float4*>(p32 + e) = *reinterpret_cast<float4*>(p);
+            *reinterpret_cast<float4*>(p32 + e + 4) = *reinterpret_cast<float4*>(p + 4);
+            const uint4 lp = pack8<T>(p);
+            const long arena_off = ((e / sub) * R + me) * sub + e % sub;
+#pragma unroll 4
+            for (int j = 0; j < R; ++j) {
+                const int r = (me + j) % R;
+                st_na_v4(reinterpret_cast<T*>(params.p[r]) + arena_off, lp);
+            }
+        }
+    }
+    __threadfence_system();
+    grid.sync();
+    // nobody leaves before every peer's stores into my arena are visible and every peer is done with my norm table
+    if (blockIdx.x == 0) xgpu_barrier(flags, R, me, 1, epoch);
+}
+
 static int coop_grid(const void* kern, int threads) {
     int dev = 0, sms = 0, per_sm = 0;
     cudaGetDevice(&dev);
@@ -234,7 +420,38 @@ extern "C" int dsb_fused_adam_ag(const float* red32, float* p32, float* m, float
     return e == cudaSuccess ? 0 : -(int)e;
 }
 
-// ---- symmetric heap plumbing (CUDA IPC) ------------------------------------------------------------------------
+extern "C" int dsb_fused_lamb_ag(float* upd32, float* p32, float* m, float* v, void* const* param_ptrs,
+                                 void* const* norm_ptrs, void* const* flag_ptrs, int R, int me, long sub, long n,
+                                 const long* seg_start, const int* seg_tid, int nseg, int ntensors, int dtype, float lr,
+                                 float beta1, float beta2, float eps, float weight_decay, float max_coeff,
+                                 float min_coeff, int eps_inside_sqrt, int bias_correction, int step,
+                                 const float* inv_scale_dev, const int* skip_dev, float* coeff_out,
+                                 unsigned int epoch, void* stream) {
+    if (R < 1 || R > MAX_RANKS || sub <= 0 || (sub % 8) || (n % sub) || nseg < 1 || ntensors < 1 || !seg_start ||
+        !seg_tid)
+        return DSB_ERR_ARG;
+    if (dtype != DSB_DTYPE_BF16 && dtype != DSB_DTYPE_F16) return DSB_ERR_DTYPE;
+    PeerPtrs pp, nn;
+    FlagPtrs f;
+    for (int i = 0; i < R; ++i) {
+        pp.p[i] = param_ptrs[i];
+        nn.p[i] = norm_ptrs[i];
+        f.p[i] = reinterpret_cast<uint32_t*>(flag_ptrs[i]);
+    }
+    LambH h;
+    h.beta1 = beta1; h.beta2 = beta2; h.eps = eps; h.wd = weight_decay;
+    h.max_coeff = max_coeff; h.min_coeff = min_coeff; h.eps_inside = eps_inside_sqrt;
+    h.step_size = bias_correction ? lr * sqrtf(1.f - powf(beta2, (float)step)) / (1.f - powf(beta1, (float)step)) : lr;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    void* args[] = {&upd32, &p32, &m, &v, &pp, &nn, &f, &R, &me, &sub, &n, &seg_start, &seg_tid, &nseg, &ntensors,
+                    &h, &inv_scale_dev, &skip_dev, &coeff_out, &epoch};
+    const void* kern = dtype == DSB_DTYPE_BF16 ? (const void*)fused_lamb_ag_kernel<__nv_bfloat16>
+                                               : (const void*)fused_lamb_ag_kernel<__half>;
+    cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(coop_grid(kern, 512)), dim3(512), args, 0, s);
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+// ---- symmetric heap plumbing (CUDA IPC)------------------------------------------------------------------------
 extern "C" int dsb_symm_alloc(long bytes, void** out) {
     cudaError_t e = cudaMalloc(out, bytes);
     if (e != cudaSuccess) return -(int)e;

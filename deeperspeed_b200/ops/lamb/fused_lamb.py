@@ -7,6 +7,10 @@ from .. import native as N
 
 
 class FusedLamb(torch.optim.Optimizer):
+    # under ZeRO-1/2 on one NVLink domain the sharded step runs as the fused reduce-scatter + LAMB + all-gather
+    # kernels of parallel/fused_zero.py (per-tensor trust ratio summed over the shards)
+    supports_fused_zero_lamb = True
+
     def __init__(self, params, lr=1e-3, bias_correction=True, betas=(0.9, 0.999), eps=1e-8, eps_inside_sqrt=False,
                  weight_decay=0.0, max_grad_norm=0.0, max_coeff=10.0, min_coeff=0.01, amsgrad=False):
         if amsgrad:
@@ -106,4 +110,4 @@ class FusedLamb(torch.optim.Optimizer):
         return torch.tensor([coeff])
 
     def get_lamb_coeffs(self):
-        return [float(c) for c in self.lamb_coeffs]
+        return [float(x) for c in self.lamb_coeffs for x in torch.as_tensor(c).reshape(-1).tolist()]

@@ -16,6 +16,10 @@ N.register_sigs({
     "dsb_fused_rs_norm": [_p, _p, _i, _i, _l, _l, _i, _f, _p, _p, _p, _p, _u, _p],
     "dsb_fused_adam_ag": [_p, _p, _p, _p, _p, _p, _i, _i, _l, _l, _i, _f, _f, _f, _f, _f, _i, _i, _i, _p, _p, _u, _p],
 })
+N.register_sigs({
+    "dsb_fused_lamb_ag": [_p, _p, _p, _p, _p, _p, _p, _i, _i, _l, _l, _p, _p, _i, _i, _i, _f, _f, _f, _f, _f, _f, _f,
+                          _i, _i, _i, _p, _p, _p, _u, _p],
+})
 N.register_sigs({"dsb_fused_zero_scratch_bytes": []}, restype=_l)
 
 
@@ -35,6 +39,7 @@ class FusedZeroStep:
             n = sum((p.numel() + 7) // 8 * 8 for p in g["params"])
             n = (n + dp * 8 - 1) // (dp * 8) * (dp * 8) + 4096
             total += 2 * n * 2 + 1024
+            total += 8 * (len(g["params"]) + 1) + 512   # per-tensor norm table of the LAMB kernel
         return total
 
     @staticmethod
@@ -75,8 +80,84 @@ class FusedZeroStep:
         for a in opt.arenas:
             self.grad_ptrs.append(_ptr_array(heap.peer_ptrs(heap.offsets[a.grad.data_ptr()])))
             self.param_ptrs.append(_ptr_array(heap.peer_ptrs(heap.offsets[a.data.data_ptr()])))
+        self.is_lamb = bool(getattr(opt.optimizer, "supports_fused_zero_lamb", False))
+        if self.is_lamb:
+            self._init_lamb()
         logger.info(f"[fused-zero] rank {opt.dp_rank}/{opt.dp_world}: NVLink peer-memory ZeRO step enabled "
-                    f"({sum(a.numel for a in opt.arenas)} elements)")
+                    f"({sum(a.numel for a in opt.arenas)} elements, {'LAMB' if self.is_lamb else 'Adam'})")
+
+    # ---- LAMB: per-tensor segment tables of the owned slices + norm tables in the symmetric heap
+    @staticmethod
+    def owned_segments(arena, sub, count, R, me):
+        """Segments of this rank's owned range in LOCAL order (bucket-major): returns (starts, tids) with
+        starts[i] .. starts[i+1] belonging to tensor tids[i]; id len(arena.segments) stands for arena padding."""
+        pad_tid = len(arena.segments)
+        starts, tids = [], []
+        for k in range(count):
+            lo = (k * R + me) * sub
+            hi = lo + sub
+            pos = lo
+            for ti, sg in enumerate(arena.segments):
+                # a tensor owns its alignment padding up to the next tensor's start
+                nxt = arena.segments[ti + 1].offset if ti + 1 < len(arena.segments) else arena.numel_used
+                a, b = max(lo, sg.offset), min(hi, nxt)
+                if a < b:
+                    if a > pos:
+                        starts.append(pos - lo + k * sub)
+                        tids.append(pad_tid)
+                    starts.append(a - lo + k * sub)
+                    tids.append(ti)
+                    pos = b
+            if pos < hi:
+                starts.append(pos - lo + k * sub)
+                tids.append(pad_tid)
+        starts.append(count * sub)
+        return starts, tids
+
+    def _init_lamb(self):
+        o = self.opt
+        self.lamb_red, self.lamb_seg, self.lamb_norm_ptrs, self.lamb_coeff = [], [], [], []
+        for gi, arena in enumerate(o.arenas):
+            sub, count = o.sub_size[gi], o.num_buckets[gi]
+            starts, tids = self.owned_segments(arena, sub, count, o.dp_world, o.dp_rank)
+            assert all(s % 8 == 0 for s in starts)
+            nt = len(arena.segments) + 1
+            _, off = self.heap.alloc(2 * nt, torch.float32)
+            self.lamb_norm_ptrs.append(_ptr_array(self.heap.peer_ptrs(off)))
+            self.lamb_seg.append((torch.tensor(starts, dtype=torch.int64, device=o._dev),
+                                  torch.tensor(tids, dtype=torch.int32, device=o._dev), len(tids), nt))
+            self.lamb_red.append(torch.empty(count * sub, dtype=torch.float32, device=o._dev))
+            self.lamb_coeff.append(torch.ones(nt, dtype=torch.float32, device=o._dev))
+            st = o.optimizer.state[o.fp32_masters[gi]]
+            if "exp_avg" not in st:
+                st["step"] = 0
+                st["exp_avg"] = torch.zeros_like(o.fp32_masters[gi].data)
+                st["exp_avg_sq"] = torch.zeros_like(o.fp32_masters[gi].data)
+        dist.barrier(group=self.heap.group)
+
+    def _lamb_update(self, s):
+        o = self.opt
+        R, me = o.dp_world, o.dp_rank
+        inner = o.optimizer
+        del inner.lamb_coeffs[:]
+        for gi, arena in enumerate(o.arenas):
+            group = inner.param_groups[gi]
+            master = o.fp32_masters[gi]
+            st = inner.state[master]
+            st["step"] = st.get("step", 0) + 1
+            beta1, beta2 = group["betas"]
+            starts, tids, nseg, nt = self.lamb_seg[gi]
+            sub = o.sub_size[gi]
+            N.check(self.lib.dsb_fused_lamb_ag(
+                N.ptr(self.lamb_red[gi]), N.ptr(master.data), N.ptr(st["exp_avg"]), N.ptr(st["exp_avg_sq"]),
+                self.param_ptrs[gi], self.lamb_norm_ptrs[gi], self.flag_ptrs, R, me, sub, sub * o.num_buckets[gi],
+                N.ptr(starts), N.ptr(tids), nseg, nt, N.dtype_code(arena.dtype), float(group["lr"]), float(beta1),
+                float(beta2), float(group["eps"]), float(group["weight_decay"]), float(group["max_coeff"]),
+                float(group["min_coeff"]), int(inner.eps_mode == 0), int(bool(group["bias_correction"])),
+                int(st["step"]), N.ptr(o._inv_scale), N.ptr(o._skip), N.ptr(self.lamb_coeff[gi]),
+                self.heap.next_epoch(), s), "dsb_fused_lamb_ag")
+            K._count()
+            inner.lamb_coeffs.append(self.lamb_coeff[gi][:nt - 1])
 
     def step(self):
         o = self.opt
@@ -92,7 +173,10 @@ class FusedZeroStep:
         for gi, arena in enumerate(o.arenas):
             sub = o.sub_size[gi]
             for k in range(o.num_buckets[gi]):
-                red = self.red32[gi] if k == 0 else torch.empty(sub, dtype=torch.float32, device=o._dev)
+                if self.is_lamb:
+                    red = self.lamb_red[gi].narrow(0, k * sub, sub)
+                else:
+                    red = self.red32[gi] if k == 0 else torch.empty(sub, dtype=torch.float32, device=o._dev)
                 reds[(gi, k)] = red
                 off = (k * o.partition_count + me) * sub
                 N.check(self.lib.dsb_fused_rs_norm(self.grad_ptrs[gi], self.flag_ptrs, R, me, off, sub,
@@ -103,7 +187,9 @@ class FusedZeroStep:
         o._sumsq[1] = o._flag[0].float()
         o._mp_owned_correction()
         norm, bad = o._global_scalars()
-        for gi, arena in enumerate(o.arenas):
+        if self.is_lamb:
+            self._lamb_update(s)
+        for gi, arena in enumerate(() if self.is_lamb else o.arenas):
             group = o.optimizer.param_groups[gi]
             master = o.fp32_masters[gi]
             st = o.optimizer.state[master]
@@ -126,9 +212,14 @@ class FusedZeroStep:
         o._global_grad_norm = -1 if overflow else host[0] / float(o._loss_scale())
         prev = o._loss_scale()
         o._on_step_result(overflow)
-        if overflow:
-            for group in o.optimizer.param_groups:
-                group["step"] = max(group.get("step", 1) - 1, 0)
+        if overflow:   # the kernels were no-ops: undo the step count
+            if self.is_lamb:
+                for master in o.fp32_masters:
+                    st = o.optimizer.state[master]
+                    st["step"] = max(st.get("step", 1) - 1, 0)
+            else:
+                for group in o.optimizer.param_groups:
+                    group["step"] = max(group.get("step", 1) - 1, 0)
             logger.info("[deepspeed] OVERFLOW! Rank {} Skipping step. Attempted loss scale: {}, reducing to {}".format(
                 dist.get_rank(), prev, o._loss_scale()))
         o.zero_grad()

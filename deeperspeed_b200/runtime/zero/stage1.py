@@ -46,7 +46,8 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
         self.precision = precision
         self.all_gather_partitions = all_gather_partitions
         self._symm_heap = None
-        if fused_nvlink and allocator is None and getattr(init_optimizer, "supports_flat_fused", False):
+        if fused_nvlink and allocator is None and (getattr(init_optimizer, "supports_flat_fused", False)
+                                                   or getattr(init_optimizer, "supports_fused_zero_lamb", False)):
             # arenas go into a symmetric (peer-mapped) heap so the fused NVLink kernels can address every rank
             from ...parallel.fused_zero import FusedZeroStep
             try:
@@ -92,7 +93,8 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
         self.loss_scaler.update_scale(overflow)
 
     def _use_fused(self):
-        return getattr(self, "fused", None) is not None and self.fused_inner
+        fused = getattr(self, "fused", None)
+        return fused is not None and (self.fused_inner or fused.is_lamb)
 
     def reduce_gradients(self):
         if self._use_fused():

@@ -209,6 +209,19 @@ int dsb_fused_adam_ag(const float* red32, float* p32, float* m, float* v, void* 
                       void* const* flag_ptrs, int R, int me, long slice_off, long n, int dtype, float lr, float beta1,
                       float beta2, float eps, float weight_decay, int adamw_mode, int bias_correction, int step,
                       const float* inv_scale_dev, const int* skip_dev, unsigned int epoch, void* stream);
+/* LAMB counterpart of dsb_fused_adam_ag, one launch per parameter group over all `n / sub` bucket slices this rank
+ * owns. `upd32` holds the reduced fp32 gradients on entry (it is overwritten with the update). The owned range is
+ * described by `nseg` segments: seg_start[i] .. seg_start[i+1] (local element offsets, multiples of 8,
+ * seg_start[nseg] == n) belongs to tensor seg_tid[i] < ntensors. `norm_ptrs[r]` is rank r's table of 2 * ntensors
+ * floats in the symmetric heap; per-tensor |w|^2, |u|^2 are summed over the ranks through it, so the trust ratio is
+ * per tensor even when a tensor is spread over several ranks. `coeff_out` (ntensors floats, may be NULL) receives
+ * the ratios of the tensors this rank touches. Reference math: csrc/lamb/fused_lamb_cuda_kernel.cu:186-310. */
+int dsb_fused_lamb_ag(float* upd32, float* p32, float* m, float* v, void* const* param_ptrs, void* const* norm_ptrs,
+                      void* const* flag_ptrs, int R, int me, long sub, long n, const long* seg_start,
+                      const int* seg_tid, int nseg, int ntensors, int dtype, float lr, float beta1, float beta2,
+                      float eps, float weight_decay, float max_coeff, float min_coeff, int eps_inside_sqrt,
+                      int bias_correction, int step, const float* inv_scale_dev, const int* skip_dev, float* coeff_out,
+                      unsigned int epoch, void* stream);
 /* 1-bit (sign + scale, error feedback) allreduce as ONE cooperative kernel: compress, exchange packed signs through
  * the peers' heaps, server-side average + recompress, gather. Reference: runtime/comm/nccl.py:47-186. */
 long dsb_onebit_heap_bytes(long n, int W);

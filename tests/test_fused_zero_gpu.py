@@ -77,6 +77,76 @@ def test_fused_matches_nccl_path():
     run_distributed(_fused_vs_nccl_worker, world_size=2, use_cuda=True)
 
 
+def _lamb_reference(w, g, lr, betas, eps, wd, max_coeff, min_coeff, step, m, v):
+    """Plain fp32 LAMB on one whole tensor (reference csrc/lamb/fused_lamb_cuda_kernel.cu:186-310 math)."""
+    b1, b2 = betas
+    m.mul_(b1).add_(g, alpha=1 - b1)
+    v.mul_(b2).addcmul_(g, g, value=1 - b2)
+    u = m / (v.sqrt() + eps) + wd * w
+    wn, un = w.norm(), u.norm()
+    coeff = 1.0
+    if wn > 0 and un > 0:
+        coeff = float(min(max(wn / un, min_coeff), max_coeff))
+    step_size = lr * (1 - b2 ** step) ** 0.5 / (1 - b1 ** step)
+    return w - step_size * coeff * u, coeff
+
+
+def _fused_lamb_worker():
+    torch.manual_seed(5)
+    model = Net()
+    hp = {"lr": 2e-3, "weight_decay": 0.01, "max_coeff": 10.0, "min_coeff": 0.01}
+    cfg = {"train_batch_size": 8, "train_micro_batch_size_per_gpu": 4, "steps_per_print": 100,
+           "optimizer": {"type": "Lamb", "params": dict(hp)},
+           "fp16": {"enabled": True, "initial_scale_power": 6}, "zero_allow_untested_optimizer": True,
+           # small buckets: several comm intervals, so tensors straddle both ranks AND bucket boundaries
+           "zero_optimization": {"stage": 1, "fused_nvlink": True, "reduce_bucket_size": 100000}}
+    engine, opt, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+    assert opt.fused is not None and opt.fused.is_lamb
+    arena = opt.arenas[0]
+    assert opt.num_buckets[0] > 1
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ws = [s.param.detach().float().clone() for s in arena.segments]
+    ms = [torch.zeros_like(w) for w in ws]
+    vs = [torch.zeros_like(w) for w in ws]
+    for step in (1, 2):
+        gens = [torch.Generator(device="cuda").manual_seed(1000 * step + r) for r in range(world)]
+        per_rank = [(torch.randn(arena.numel, device="cuda", generator=gens[r]) * 0.05 * (1 + r)).half()
+                    for r in range(world)]
+        opt.zero_grad()
+        scale = float(opt.loss_scale)
+        for s in arena.segments:   # write through the parameter views so arena padding stays zero
+            s.param.grad.copy_(per_rank[rank].narrow(0, s.offset, s.numel).view(s.shape))
+        opt.step()
+        torch.cuda.synchronize()
+        assert not opt.overflow
+        coeffs = opt.optimizer.get_lamb_coeffs()
+        for ti, s in enumerate(arena.segments):
+            g = sum(pr.narrow(0, s.offset, s.numel).float() for pr in per_rank).view(s.shape) / world / scale
+            ws[ti], c = _lamb_reference(ws[ti], g, hp["lr"], (0.9, 0.999), 1e-8, hp["weight_decay"], hp["max_coeff"],
+                                        hp["min_coeff"], step, ms[ti], vs[ti])
+            got = s.param.detach().float()
+            assert (got - ws[ti]).abs().max().item() < 2e-3 * max(1.0, ws[ti].abs().max().item()), (ti, step)
+            # the ratio is per whole tensor although every tensor here is split over ranks and buckets
+            _, mine = opt.fused.owned_segments(arena, opt.sub_size[0], opt.num_buckets[0], world, rank)
+            if ti in mine:
+                assert abs(coeffs[ti] - c) < 1e-3 * max(1.0, c), (ti, coeffs[ti], c)
+    flat = arena.data.clone()
+    other = flat.clone()
+    dist.broadcast(other, src=0)
+    assert torch.equal(flat, other)
+    # overflow: skipped on every rank, moments and step count untouched
+    before = opt.fp32_masters[0].detach().clone()
+    opt.arenas[0].grad[3] = float("inf")
+    opt.step()
+    assert opt.overflow
+    assert torch.equal(before, opt.fp32_masters[0].detach())
+    assert opt.optimizer.state[opt.fp32_masters[0]]["step"] == 2
+
+
+def test_fused_lamb_per_tensor_trust_ratio_2gpu():
+    run_distributed(_fused_lamb_worker, world_size=2, use_cuda=True)
+
+
 def _ag_gemm_worker():
     from deeperspeed_b200.parallel.ag_gemm import ShardedWeight, ag_linear
     torch.manual_seed(3)   # same full weight on every rank; each keeps only its rows

@@ -186,3 +186,28 @@ def test_config_batch_triple_and_duplicates(tmp_path):
     c = DeepSpeedConfig(None, param_dict={"train_batch_size": 2, "fp16": {"enabled": True, "hysteresis": 4},
                                           "sparse_attention": {"mode": "bigbird", "block": 32}})
     assert c.dynamic_loss_scale_args["delayed_shift"] == 4 and c.sparse_attention["num_random_blocks"] == 1
+
+
+def test_fused_zero_lamb_owned_segments_cover_the_owned_range():
+    """Segment tables handed to the fused ZeRO LAMB kernel: every rank's owned range is tiled exactly, 8-aligned,
+    and the union over ranks gives every tensor its full (padded) extent once."""
+    import torch
+    from deeperspeed_b200.parallel.fused_zero import FusedZeroStep
+    from deeperspeed_b200.runtime.flat import FlatArena
+    R, count = 3, 2
+    params = [torch.nn.Parameter(torch.zeros(n)) for n in (5, 64, 1001, 8, 333)]
+    arena = FlatArena(params, shard_count=R * count, shard_align=8)
+    sub = arena.numel // (R * count)
+    seen = {}
+    for me in range(R):
+        starts, tids = FusedZeroStep.owned_segments(arena, sub, count, R, me)
+        assert starts[0] == 0 and starts[-1] == count * sub and len(starts) == len(tids) + 1
+        assert all(s % 8 == 0 for s in starts) and all(a < b for a, b in zip(starts, starts[1:]))
+        for (a, b), t in zip(zip(starts, starts[1:]), tids):
+            assert a // sub == (b - 1) // sub, "a segment never crosses a bucket boundary"
+            seen[t] = seen.get(t, 0) + (b - a)
+    pad_tid = len(params)
+    for ti, sg in enumerate(arena.segments):
+        nxt = arena.segments[ti + 1].offset if ti + 1 < len(arena.segments) else arena.numel_used
+        assert seen[ti] == nxt - sg.offset
+    assert seen.get(pad_tid, 0) == arena.numel - arena.numel_used
