@@ -48,9 +48,15 @@ if rank == 0:
     # (LAMB: update written and re-read, master re-read in the apply phase)
     hbm_bytes = N / world * (2 * world + 4 + 4 + 12 + 12 + 2 * world + (12 if LAMB else 0))
     roof_ms = max(nvlink_bytes / 770e9, hbm_bytes / 6545e9) * 1e3
+    # the global gradient norm (clipping, overflow skip) must be known before any element is updated, so the pull
+    # phase cannot overlap the update phase: a dependency-aware bound is pull over NVLink + max(update HBM, push)
+    pull_ms = (world - 1) / world * 2 * N / 770e9 * 1e3
+    upd_ms = max(N / world * (hbm_bytes / (N / world) - 2 * world - 4) / 6545e9, (world - 1) / world * 2 * N / 770e9) * 1e3
     out = {"world": world, "numel": N, "optimizer": "lamb" if LAMB else "adam", "nccl_ms": res["nccl"], "fused_ms": res["fused"],
            "speedup": round(res["nccl"] / res["fused"], 2), "roofline_ms": round(roof_ms, 3),
-           "fused_fraction_of_roofline": round(roof_ms / res["fused"], 3)}
+           "fused_fraction_of_roofline": round(roof_ms / res["fused"], 3),
+           "two_phase_bound_ms": round(pull_ms + upd_ms, 3),
+           "fused_fraction_of_two_phase_bound": round((pull_ms + upd_ms) / res["fused"], 3)}
     print(json.dumps(out))
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(out, open(f"gpurun_out/fused_zero{'_lamb' if LAMB else ''}_bench_w{world}.json", "w"))

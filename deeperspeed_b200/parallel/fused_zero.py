@@ -72,6 +72,7 @@ class FusedZeroStep:
         self.opt = opt
         self.heap = heap
         self.lib = N.cuda_lib()
+        self._prof = [] if os.environ.get("DSB_FUSED_ZERO_PROFILE") == "1" else None
         self.scratch = torch.zeros(self.lib.dsb_fused_zero_scratch_bytes(), dtype=torch.uint8, device=opt._dev)
         self.red32 = [torch.empty(opt.sub_size[gi], dtype=torch.float32, device=opt._dev)
                       for gi in range(len(opt.arenas))]
@@ -159,8 +160,25 @@ class FusedZeroStep:
             K._count()
             inner.lamb_coeffs.append(self.lamb_coeff[gi][:nt - 1])
 
+    def _mark(self, name):
+        """DSB_FUSED_ZERO_PROFILE=1: CUDA-event timestamps between the phases of the step (printed by rank 0)."""
+        if self._prof is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self._prof.append((name, ev))
+
+    def _report(self):
+        if self._prof is None or len(self._prof) < 2:
+            return
+        torch.cuda.synchronize()
+        parts = [f"{b[0]}={a[1].elapsed_time(b[1]):.3f}ms" for a, b in zip(self._prof, self._prof[1:])]
+        if self.opt.dp_rank == 0:
+            logger.info("[fused-zero] " + " ".join(parts))
+        self._prof = []
+
     def step(self):
         o = self.opt
+        self._mark("start")
         for a in o.arenas:
             a.absorb_stray_grads()
         R, me = o.dp_world, o.dp_rank
@@ -184,9 +202,11 @@ class FusedZeroStep:
                                                    N.ptr(o._flag), N.ptr(self.scratch), self.heap.next_epoch(), s),
                         "dsb_fused_rs_norm")
                 K._count()
+        self._mark("rs_norm")
         o._sumsq[1] = o._flag[0].float()
         o._mp_owned_correction()
         norm, bad = o._global_scalars()
+        self._mark("scalars")
         if self.is_lamb:
             self._lamb_update(s)
         for gi, arena in enumerate(() if self.is_lamb else o.arenas):
@@ -206,7 +226,9 @@ class FusedZeroStep:
                     int(o.optimizer.adam_w_mode), int(group["bias_correction"]), int(group["step"]),
                     N.ptr(o._inv_scale), N.ptr(o._skip), self.heap.next_epoch(), s), "dsb_fused_adam_ag")
                 K._count()
+        self._mark("update_ag")
         host = torch.stack([norm, bad.float()]).tolist()
+        self._report()
         overflow = bool(host[1])
         o.overflow = overflow
         o._global_grad_norm = -1 if overflow else host[0] / float(o._loss_scale())
