@@ -46,6 +46,17 @@ struct GemmParams {
     const void* peer_shards[8];
     void* gathered;
     int* panel_ready;
+    // GEMM -> reduce-scatter variant (rs_mode != 0, wgrad of a ZeRO-3 linear): rows of D are owned by ranks
+    // (rows_per_rank each). Every output tile is TMA-stored into slot `me` of the OWNER's staging buffer
+    // ([nranks, rows_per_rank, N], peer-mapped; tmBs.m[owner] for remote owners, tmD for the own one), remote owners
+    // first so that the transfers run under the remaining tiles. After a grid + cross-GPU barrier (flag blocks at
+    // peer_shards[r], slot 3) all CTAs sum the nranks slots of the local staging into rs_out, scaled by rs_scale.
+    int rs_mode;
+    unsigned int rs_epoch;
+    float rs_scale;
+    void* rs_out;       // [rows_per_rank, N]
+    const void* rs_stage;   // local staging base
+    int* rs_sync;       // [2] zeroed by the host: arrive counter, go flag
 };
 
 template <int BN> struct GemmCfg {
@@ -123,6 +134,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 nb = (seq + p.me * (p.rows_per_rank / BN)) % n_blocks;
                 return;
             }
+            if (p.rs_mode) {
+                // owner-major order: (me + 1) % R first, own rows last
+                b = 0;
+                const int mbpr = p.rows_per_rank / BM;
+                const int per_owner = mbpr * n_blocks;
+                const int seq = tile / per_owner;
+                const int r = tile - seq * per_owner;
+                const int owner = (p.me + 1 + seq) % p.nranks;
+                mb = owner * mbpr + r % mbpr;
+                nb = r / mbpr;
+                return;
+            }
         }
         b = tile / tiles_per_batch;
         int t = tile - b * tiles_per_batch;
@@ -160,9 +183,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         for (int j = 0; j < BM / 64; ++j)
                             tma_load_3d(sa + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * BK, b);
                     }
+                    const int bslot = (NMAPS > 1 && p.rs_mode) ? p.me : 0;   // rs mode: B is local, its map sits in slot me
                     if (!p.b_mn) {
                         if (NMAPS == 1) {
                             tma_load_3d(sb, &tmBs.m[0], &full_bar[stage], kb * BK, n0, b);
+                        } else if (p.rs_mode) {
+                            tma_load_3d(sb, &tmBs.m[bslot], &full_bar[stage], kb * BK, n0, b);
                         } else if (!p.ag_overlap) {
                             const int owner = n0 / p.rows_per_rank;
                             tma_load_3d(sb, &tmBs.m[owner], &full_bar[stage], kb * BK, n0 - owner * p.rows_per_rank, b);
@@ -181,7 +207,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
-                            tma_load_3d(sb + j * (BK * 128), &tmBs.m[0], &full_bar[stage], n0 + j * 64, kb * BK, b);
+                            tma_load_3d(sb + j * (BK * 128), &tmBs.m[bslot], &full_bar[stage], n0 + j * 64, kb * BK, b);
                     }
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -335,13 +361,31 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 fence_proxy_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    tma_store_3d(&tmD, sbuf, col0, m0 + q * 32, b);
+                    if constexpr (NMAPS > 1) {
+                        if (p.rs_mode) {
+                            const int owner = m0 / p.rows_per_rank;
+                            const int srow = p.me * p.rows_per_rank + (m0 - owner * p.rows_per_rank) + q * 32;
+                            tma_store_3d(owner == p.me ? &tmD : &tmBs.m[owner], sbuf, col0, srow, 0);
+                        } else {
+                            tma_store_3d(&tmD, sbuf, col0, m0 + q * 32, b);
+                        }
+                    } else {
+                        tma_store_3d(&tmD, sbuf, col0, m0 + q * 32, b);
+                    }
                     tma_store_commit();
                 }
                 buf ^= 1;
             }
         }
-        if (lane == 0) tma_store_wait<0>();
+        if (lane == 0) {
+            tma_store_wait<0>();
+            if constexpr (NMAPS > 1) {
+                if (p.rs_mode) {   // the tile stores (async proxy, possibly into a peer) precede the barrier below
+                    fence_proxy_async_all();
+                    __threadfence_system();
+                }
+            }
+        }
     } else {
         // ------------------------------------------------------------------ warps 2-3: all-gather copier (overlap mode)
         if constexpr (NMAPS > 1) {
@@ -396,6 +440,48 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     __syncthreads();
     tc_fence_after();
     if (warp == 2) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
+
+    if constexpr (NMAPS > 1) {
+        if (p.rs_mode) {
+            // every CTA of every rank has delivered its tiles -> reduce the slots that landed here
+            if (threadIdx.x == 0) {
+                __threadfence_system();
+                red_release_gpu_add_s32(p.rs_sync, 1);
+            }
+            if (blockIdx.x == 0) {
+                if (threadIdx.x == 0)
+                    while (ld_acquire_gpu_s32(p.rs_sync) < (int)gridDim.x) {}
+                __syncthreads();
+                if ((int)threadIdx.x < p.nranks) {
+                    __threadfence_system();
+                    uint32_t* theirs = reinterpret_cast<uint32_t*>(const_cast<void*>(p.peer_shards[threadIdx.x]));
+                    st_release_sys(theirs + 3 * 16 + p.me, p.rs_epoch);
+                    const uint32_t* mine = reinterpret_cast<const uint32_t*>(p.peer_shards[p.me]) + 3 * 16 + threadIdx.x;
+                    while ((int32_t)(ld_acquire_sys(mine) - p.rs_epoch) < 0) {}
+                }
+                __syncthreads();
+                if (threadIdx.x == 0) red_release_gpu_add_s32(p.rs_sync + 1, 1);
+            }
+            if (threadIdx.x == 0)
+                while (ld_acquire_gpu_s32(p.rs_sync + 1) < 1) {}
+            __syncthreads();
+            const long nvec = (long)p.rows_per_rank * p.N / 8;
+            const uint4* st = reinterpret_cast<const uint4*>(p.rs_stage);
+            uint4* out = reinterpret_cast<uint4*>(p.rs_out);
+            for (long i = (long)blockIdx.x * NUM_THREADS + threadIdx.x; i < nvec; i += (long)gridDim.x * NUM_THREADS) {
+                float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+                for (int r = 0; r < p.nranks; ++r) {
+                    float f[8];
+                    unpack8<T>(ld_na_v4(st + (long)r * nvec + i), f);
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[k] += f[k];
+                }
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] *= p.rs_scale;
+                out[i] = pack8<T>(acc);
+            }
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------- host side
@@ -544,6 +630,7 @@ extern "C" int dsb_gemm_gather_b(const void* A, void* const* shard_ptrs, int nra
     p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
     p.rows_per_rank = rows;
     p.ag_overlap = 0; p.me = 0; p.nranks = nranks; p.gathered = nullptr; p.panel_ready = nullptr;
+    p.rs_mode = 0;
     for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = nullptr;
     if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);
     return launch<__half, 256, MAXR>(ta, tbs, td, p, sms, stream);
@@ -597,7 +684,78 @@ extern "C" int dsb_gemm_ag_overlap(const void* A, void* const* shard_ptrs, int n
     p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
     p.rows_per_rank = rows;
     p.ag_overlap = 1; p.me = me; p.nranks = nranks; p.gathered = gathered; p.panel_ready = panel_flags;
+    p.rs_mode = 0;
     for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = shard_ptrs[r < nranks ? r : 0];
     if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);
     return launch<__half, 256, MAXR>(ta, tbs, td, p, sms, stream);
+}
+
+// GEMM + reduce-scatter in ONE kernel (ZeRO-3 weight gradient): D = alpha * op(A) op(B)^T with D [M, N] row-owned by
+// `nranks` ranks (M / nranks rows each, a multiple of 128). Every rank computes its full local product; each output
+// tile is TMA-stored straight into the owner's staging buffer over NVLink while later tiles are still in the tensor
+// pipe (remote owners first); after a cross-GPU barrier every rank sums the nranks slots that landed in ITS staging
+// into `out` ([M / nranks, N]) times `scale`. `stage_ptrs[r]`: rank r's staging buffer ([nranks, M / nranks, N] of
+// the GEMM dtype, peer-mapped; callers alternate between two such buffers from call to call so a rank may still be
+// reducing the previous call's slots). `flag_bases[r]`: rank r's symmetric-heap flag block. `sync2`: two ints of
+// local scratch. Launched cooperatively: CTAs wait for each other.
+extern "C" int dsb_gemm_reduce_scatter(const void* A, const void* B, void* out, void* const* stage_ptrs,
+                                       void* const* flag_bases, int nranks, int me, int* sync2, int M, int N, int K,
+                                       long lda, long ldb, int a_mn_major, int b_mn_major, int dtype, float alpha,
+                                       float scale, unsigned int epoch, void* stream_) {
+    using namespace dsb;
+    ensure_context_on_this_thread();
+    constexpr int MAXR = 8;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (M <= 0 || N <= 0 || K <= 0) return 0;
+    if (nranks < 1 || nranks > MAXR || me < 0 || me >= nranks || (M % nranks) || !sync2 || !out) return DSB_ERR_ARG;
+    const int rows = M / nranks;
+    if ((rows % BM) || (lda % 8) || (ldb % 8) || (N % 8)) return DSB_ERR_SIZE;
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int bf = dtype == DSB_DTYPE_BF16;
+    CUtensorMap ta, td;
+    BMapSet<MAXR> tbs;
+    int rc;
+    if (!a_mn_major) rc = make_map(&ta, bf, A, K, M, 1, lda, (long)M * lda, BK, BM);
+    else rc = make_map(&ta, bf, A, M, K, 1, lda, (long)K * lda, 64, BK);
+    if (rc) return rc;
+    for (int r = 0; r < MAXR; ++r) {
+        if (r == me || r >= nranks) {
+            if (!b_mn_major) rc = make_map(&tbs.m[r], bf, B, K, N, 1, ldb, (long)N * ldb, BK, 256);
+            else rc = make_map(&tbs.m[r], bf, B, N, K, 1, ldb, (long)K * ldb, 64, BK);
+        } else {
+            rc = make_map(&tbs.m[r], bf, stage_ptrs[r], N, (uint64_t)nranks * rows, 1, N, (long)nranks * rows * N,
+                          EPI_COLS, 32);
+        }
+        if (rc) return rc;
+    }
+    rc = make_map(&td, bf, stage_ptrs[me], N, (uint64_t)nranks * rows, 1, N, (long)nranks * rows * N, EPI_COLS, 32);
+    if (rc) return rc;
+    cudaError_t e = cudaMemsetAsync(sync2, 0, 2 * sizeof(int), stream);
+    if (e != cudaSuccess) return -(int)e;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.batch = 1;
+    p.a_mn = a_mn_major; p.b_mn = b_mn_major;
+    p.epilogue = DSB_EPI_NONE; p.alpha = alpha;
+    p.bias = nullptr; p.aux = nullptr; p.ldaux = 0; p.stride_aux = 0;
+    p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
+    p.rows_per_rank = rows;
+    p.ag_overlap = 0; p.me = me; p.nranks = nranks; p.gathered = nullptr; p.panel_ready = nullptr;
+    for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = flag_bases[r < nranks ? r : 0];
+    p.rs_mode = 1; p.rs_epoch = epoch; p.rs_scale = scale; p.rs_out = out; p.rs_stage = stage_ptrs[me];
+    p.rs_sync = sync2;
+    using Cfg = GemmCfg<256>;
+    const void* kern = bf ? (const void*)gemm_tcgen05_kernel<__nv_bfloat16, 256, MAXR>
+                          : (const void*)gemm_tcgen05_kernel<__half, 256, MAXR>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    if (e != cudaSuccess) return -(int)e;
+    const long tiles = (long)(M / BM) * ((N + 255) / 256);
+    const int grid = (int)(tiles < sms ? tiles : sms);
+    void* args[] = {&ta, &tbs, &td, &p};
+    e = cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(NUM_THREADS), args, Cfg::SMEM_BYTES, stream);
+    return e == cudaSuccess ? 0 : -(int)e;
 }

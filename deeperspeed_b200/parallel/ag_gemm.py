@@ -16,6 +16,7 @@ _p, _i, _l, _f = C.c_void_p, C.c_int, C.c_long, C.c_float
 N.register_sigs({
     "dsb_gemm_gather_b": [_p, _p, _i, _p, _i, _i, _i, _l, _l, _l, _i, _i, _f, _p, _p, _l, _p],
     "dsb_gemm_ag_overlap": [_p, _p, _i, _i, _p, _p, _p, _i, _i, _i, _l, _l, _i, _i, _f, _p, _p, _l, _p],
+    "dsb_gemm_reduce_scatter": [_p, _p, _p, _p, _p, _i, _i, _p, _i, _i, _i, _l, _l, _i, _i, _i, _f, _f, C.c_uint, _p],
 })
 
 
@@ -75,3 +76,58 @@ def ag_linear(x, sw, bias=None, direct=False):
     N.check(rc, "dsb_gemm_gather_b")
     K._count()
     return out.view(*x.shape[:-1], sw.N)
+
+
+class GemmReduceScatter:
+    """GEMM followed by a reduce-scatter of its result, in ONE kernel (csrc/gemm/gemm_tcgen05.cu:
+    dsb_gemm_reduce_scatter): every rank computes its local product D [M, N]; each output tile is TMA-stored into
+    the row owner's staging buffer over NVLink while the tensor pipe works on the next tiles, then every rank sums
+    the slots that arrived in its own staging. Used for the weight gradient of ZeRO-3 linears (reference:
+    `_reduce_scatter_gradient`, deepspeed/runtime/zero/partition_parameters.py:888-926, after the wgrad GEMM).
+
+    Two staging buffers of `max_elems` elements alternate from call to call, so a peer that is still summing the
+    previous call's slots is never overwritten."""
+
+    def __init__(self, max_elems, dtype=torch.float16, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group=group)
+        self.rank = dist.get_rank(group=group)
+        self.max_elems = int(max_elems)
+        self.dtype = dtype
+        self.heap = SymmetricHeap(2 * (self.max_elems * 2 + 512) + 4096, group=group)
+        self.stage_ptrs = []
+        for _ in range(2):
+            _, off = self.heap.alloc(self.max_elems, dtype)
+            self.stage_ptrs.append((C.c_void_p * self.world)(*self.heap.peer_ptrs(off)))
+        self.flag_ptrs = (C.c_void_p * self.world)(*self.heap.flag_ptrs())
+        self.sync = torch.zeros(2, dtype=torch.int32, device="cuda")
+        self.calls = 0
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+
+    def supported(self, M, Nn, K):
+        return (M % self.world == 0 and (M // self.world) % 128 == 0 and Nn % 8 == 0 and M * Nn <= self.max_elems
+                and self.world <= 8)
+
+    def __call__(self, a, b, trans_a=False, trans_b=True, average=True, out=None):
+        """out [M / world, N] = (sum over ranks of op(a) @ op(b)) rows owned by this rank (/ world if average).
+        Layouts as ops.kernels.gemm: trans_a=True: a is [K, M]; trans_b=False: b is [K, N]."""
+        if trans_a:
+            Kk, M = a.shape
+        else:
+            M, Kk = a.shape
+        Nn = b.shape[0] if trans_b else b.shape[1]
+        assert self.supported(M, Nn, Kk), (M, Nn, Kk, self.max_elems)
+        assert a.stride(-1) == 1 and b.stride(-1) == 1 and a.dtype == self.dtype and b.dtype == self.dtype
+        rows = M // self.world
+        if out is None:
+            out = torch.empty(rows, Nn, dtype=a.dtype, device=a.device)
+        stage = self.stage_ptrs[self.calls & 1]
+        self.calls += 1
+        rc = N.cuda_lib().dsb_gemm_reduce_scatter(
+            N.ptr(a), N.ptr(b), N.ptr(out), stage, self.flag_ptrs, self.world, self.rank, N.ptr(self.sync), M, Nn, Kk,
+            a.stride(0), b.stride(0), int(trans_a), int(not trans_b), N.dtype_code(a.dtype), 1.0,
+            1.0 / self.world if average else 1.0, self.heap.next_epoch(), N.stream_ptr())
+        N.check(rc, "dsb_gemm_reduce_scatter")
+        K._count()
+        return out

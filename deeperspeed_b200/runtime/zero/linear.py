@@ -96,7 +96,15 @@ class FusedAGLinearFunction(torch.autograd.Function):
         if bias is not None and ctx.needs_input_grad[1]:
             grad_bias = go2.float().sum(0).to(go2.dtype)
         if w.requires_grad:
-            gw = K.gemm(go2, x2.contiguous(), trans_a=True, trans_b=False) if fast else go2.t().matmul(x2)
+            rs = getattr(w, "ds_gemm_rs", None)
+            x2c = x2.contiguous()
+            if (rs is not None and fast and w.grad is None and go2.dtype == rs.dtype
+                    and rs.supported(go2.shape[1], x2c.shape[1], go2.shape[0])):
+                # weight-gradient GEMM with the reduce-scatter inside the kernel: only this rank's averaged rows
+                # come back, straight into the gradient partition
+                w.ds_reduced_grad_hook(rs(go2, x2c, trans_a=True, trans_b=False, average=True))
+                return grad_input, grad_bias, None, None
+            gw = K.gemm(go2, x2c, trans_a=True, trans_b=False) if fast else go2.t().matmul(x2)
             w.grad = gw if w.grad is None else w.grad + gw
             hook = getattr(w, "ds_grad_hook", None)
             if hook is not None:

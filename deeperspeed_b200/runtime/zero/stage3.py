@@ -368,6 +368,39 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 hook = self._make_grad_hook(p)
                 p.ds_grad_hook = hook   # also called directly by FusedAGLinearFunction.backward
                 p.register_post_accumulate_grad_hook(hook)
+        self._setup_fused_wgrad_reduce_scatter()
+
+    def _setup_fused_wgrad_reduce_scatter(self):
+        """Weights on the fused all-gather + GEMM path also get their gradient reduce-scattered INSIDE the wgrad GEMM
+        (parallel/ag_gemm.py:GemmReduceScatter): the kernel hands back this rank's averaged shard, which is added
+        to the gradient partition without any NCCL call. DSB_ZERO3_FUSED_RS=0 keeps the NCCL reduce-scatter."""
+        import os
+        self._gemm_rs = None
+        fused = [p for params in self.sub_groups for p in params if getattr(p, "ds_fused_ag", False)]
+        if not fused or self.partition_count < 2 or os.environ.get("DSB_ZERO3_FUSED_RS", "1") != "1":
+            return
+        from ...parallel.ag_gemm import GemmReduceScatter
+        try:
+            self._gemm_rs = GemmReduceScatter(max(p.ds_numel for p in fused), dtype=fused[0].dtype,
+                                              group=self.dp_process_group)
+        except Exception as e:   # no peer mapping: stay on NCCL, loudly
+            logger.warning(f"[zero3] fused wgrad reduce-scatter unavailable ({e!r}); using NCCL reduce_scatter")
+            return
+        for p in fused:
+            if p.dtype != fused[0].dtype:
+                continue
+            p.ds_gemm_rs = self._gemm_rs
+            p.ds_reduced_grad_hook = self._make_reduced_grad_hook(p)
+
+    def _make_reduced_grad_hook(self, param):
+        def hook(shard):
+            """`shard`: this rank's rows of the weight gradient, already summed over the ranks and averaged."""
+            idx, off = self._param_slot[param]
+            dst = self.grad_partitions_flat[idx].narrow(0, off, shard.numel())
+            dst.add_(shard.view(-1).to(dst.dtype))     # accumulates over micro-batches
+            param.grad = None
+            self.param_coordinator.release_and_reset_parameter(param)
+        return hook
 
     def _make_grad_hook(self, param):
         init = Init.__new__(Init)   # size helpers only

@@ -197,6 +197,15 @@ int dsb_symm_free(void* p);
 int dsb_ipc_get_handle(void* devptr, void* handle64);
 int dsb_ipc_open(const void* handle64, void** out);
 int dsb_ipc_close(void* p);
+/* GEMM + reduce-scatter in one cooperative kernel (ZeRO-3 weight gradient): every rank computes
+ * D = alpha * op(A) op(B)^T ([M, N], rows owned by nranks ranks, M / nranks a multiple of 128); tiles are TMA-stored
+ * into slot `me` of the owner's staging buffer (stage_ptrs[r]: [nranks, M / nranks, N], peer-mapped) as they are
+ * produced, and after a cross-GPU barrier (flag blocks at flag_bases[r]) each rank sums its nranks slots into
+ * out [M / nranks, N] times `scale`. `sync2`: two ints of local scratch. Callers alternate two staging buffers.
+ * Replaces the wgrad GEMM + dist.reduce_scatter of reference zero/partition_parameters.py:888-926. */
+int dsb_gemm_reduce_scatter(const void* A, const void* B, void* out, void* const* stage_ptrs, void* const* flag_bases,
+                            int nranks, int me, int* sync2, int M, int N, int K, long lda, long ldb, int a_mn_major,
+                            int b_mn_major, int dtype, float alpha, float scale, unsigned int epoch, void* stream);
 /* ZeRO-1/2 step as two cooperative kernels. rs_norm: every rank pulls its slice of all peers' gradient arenas,
  * reduces in fp32, unscales, accumulates sum-of-squares + non-finite flag. adam_ag: Adam on the owned slice and
  * stores the new low-precision parameters into every peer's parameter arena. Replaces reduce_scatter + cast +

@@ -147,6 +147,37 @@ def test_fused_lamb_per_tensor_trust_ratio_2gpu():
     run_distributed(_fused_lamb_worker, world_size=2, use_cuda=True)
 
 
+def _gemm_rs_worker():
+    from deeperspeed_b200.parallel.ag_gemm import GemmReduceScatter
+    rank, world = dist.get_rank(), dist.get_world_size()
+    torch.cuda.set_device(rank)
+    rs = GemmReduceScatter(1024 * 2048, dtype=torch.float16)
+    for it, (tokens, out_f, in_f) in enumerate([(2048, 1024, 2048), (2048, 1024, 2048), (1024, 512, 520), (4096, 256, 1024)]):
+        g = torch.Generator(device="cuda").manual_seed(10 * it + rank)
+        go = (torch.randn(tokens, out_f, device="cuda", generator=g) * 0.1).half()
+        x = (torch.randn(tokens, in_f, device="cuda", generator=g) * 0.1).half()
+        got = rs(go, x, trans_a=True, trans_b=False)          # weight gradient rows owned by this rank, averaged
+        ref = go.float().t() @ x.float()
+        dist.all_reduce(ref)
+        ref = ref[rank * (out_f // world):(rank + 1) * (out_f // world)] / world
+        torch.cuda.synchronize()
+        assert got.shape == ref.shape
+        err = (got.float() - ref).abs().max().item()
+        assert err < 2e-2 * max(1.0, ref.abs().max().item()), (it, err)
+    # forward-layout operands (NT) as well
+    a = (torch.randn(512, 256, device="cuda") * 0.1).half()
+    b = (torch.randn(384, 256, device="cuda") * 0.1).half()
+    got = rs(a, b, average=False)
+    ref = a.float() @ b.float().t()
+    dist.all_reduce(ref)
+    ref = ref[rank * (512 // world):(rank + 1) * (512 // world)]
+    assert (got.float() - ref).abs().max().item() < 2e-2 * max(1.0, ref.abs().max().item())
+
+
+def test_fused_gemm_reduce_scatter_2gpu():
+    run_distributed(_gemm_rs_worker, world_size=2, use_cuda=True)
+
+
 def _ag_gemm_worker():
     from deeperspeed_b200.parallel.ag_gemm import ShardedWeight, ag_linear
     torch.manual_seed(3)   # same full weight on every rank; each keeps only its rows
