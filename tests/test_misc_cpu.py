@@ -213,3 +213,27 @@ def test_engine_lr_scheduler_and_tag_validation(tmp_path):
             assert open(os.path.join(str(tmp_path), "latest")).read() == "same"
         assert engine.load_checkpoint(str(tmp_path / "missing")) == (None, None)
     run()
+
+
+def test_timer_chrome_trace_export(tmp_path):
+    """Timer intervals can be dumped as a Chrome / Perfetto trace (device timestamps on CUDA, host time here)."""
+    import json
+    import time
+    from deeperspeed_b200.utils.timer import SynchronizedWallClockTimer
+    timers = SynchronizedWallClockTimer()
+    timers.enable_trace()
+    for _ in range(3):
+        timers("forward").start()
+        time.sleep(0.002)
+        timers("forward").stop()
+        timers("step").start()
+        timers("step").stop()
+    assert timers("forward").elapsed(reset=True) >= 0.006
+    path = tmp_path / "trace.json"
+    n = timers.export_chrome_trace(str(path), rank=1)
+    ev = json.load(open(path))["traceEvents"]
+    spans = [e for e in ev if e["ph"] == "X"]
+    assert n == len(ev) and len(spans) == 6
+    assert {e["name"] for e in spans} == {"forward", "step"} and all(e["pid"] == 1 for e in spans)
+    fw = sorted(e["ts"] for e in spans if e["name"] == "forward")
+    assert fw[0] < fw[1] < fw[2] and all(e["dur"] >= 0 for e in spans)
