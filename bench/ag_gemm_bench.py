@@ -13,7 +13,7 @@ import torch.distributed as dist
 
 import deeperspeed_b200 as deepspeed
 from deeperspeed_b200.ops import kernels as K
-from deeperspeed_b200.parallel.ag_gemm import ShardedWeight, ag_linear
+from deeperspeed_b200.parallel.ag_gemm import ShardedWeight, ag_linear, ag_linear_dgrad
 
 deepspeed.init_distributed(verbose=False)
 rank, world = dist.get_rank(), dist.get_world_size()
@@ -70,12 +70,27 @@ for (Nn, Kk, tag) in [(8192, 2048, "ff1"), (6144, 2048, "qkv"), (2048, 8192, "ff
     t_d = timed(lambda: ag_linear(x, sw, direct=True), iters=8, warm=2)
     t_u = timed(unfused)
     t_local = timed(lambda: K.gemm(x, full))
+    # input gradient of the same layer: the shards split the reduction dimension (dsb_gemm_ag_overlap_k)
+    go = torch.randn(tokens, Nn, device="cuda", dtype=dt) * 0.1
+
+    def unfused_dgrad():
+        dist.all_gather_into_tensor(gathered, sw.shard)
+        return K.gemm(go, gathered, trans_b=False)
+
+    gd_f, gd_u = ag_linear_dgrad(go, sw), unfused_dgrad()
+    err_d = ((gd_f.float() - gd_u.float()).abs().max() / gd_u.float().abs().max()).item()
+    t_df = timed(lambda: ag_linear_dgrad(go, sw))
+    t_du = timed(unfused_dgrad)
     fl = 2.0 * tokens * Nn * Kk
     res["shapes"].append({"tag": tag, "N": Nn, "K": Kk, "fused_ms": round(t_f, 4), "nccl_ag_plus_gemm_ms": round(t_u, 4),
                           "direct_remote_tma_ms": round(t_d, 4),
                           "local_gemm_ms": round(t_local, 4), "speedup": round(t_u / t_f, 2),
                           "fused_tflops": round(fl / t_f / 1e9, 1),
-                          "fused_fraction_of_roofline": round(fl / t_f / 1e9 / peak, 3), "rel_err_vs_unfused": err})
+                          "fused_fraction_of_roofline": round(fl / t_f / 1e9 / peak, 3), "rel_err_vs_unfused": err,
+                          "dgrad_fused_ms": round(t_df, 4), "dgrad_nccl_ag_plus_gemm_ms": round(t_du, 4),
+                          "dgrad_speedup": round(t_du / t_df, 2),
+                          "dgrad_fraction_of_roofline": round(fl / t_df / 1e9 / peak, 3),
+                          "dgrad_rel_err_vs_unfused": err_d})
 if rank == 0:
     print(json.dumps(res))
     os.makedirs("gpurun_out", exist_ok=True)

@@ -42,6 +42,9 @@ struct GemmParams {
     // overlapped all-gather variant (ag_overlap != 0): warps 2-3 of every CTA copy the remote shards panel by panel
     // (one panel = the BN rows of B one n-block needs) into `gathered`, the producer loads a remote panel from there
     // once panel_ready[nb] shows that every CTA has delivered its share; own panels come straight from the own shard.
+    // ag_overlap == 2: B is MN-major ([K, N], the dgrad of a row-sharded weight) and the shards split K. A panel is
+    // 256 rows of B = a K range; every tile needs all panels, so the k loop starts at the own shard's range and
+    // walks the remote ranges in the order the copiers deliver them.
     int ag_overlap, me, nranks;
     const void* peer_shards[8];
     void* gathered;
@@ -100,6 +103,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int tiles_per_batch = m_blocks * n_blocks;
     const int num_tiles = tiles_per_batch * p.batch;
     const int k_blocks = (p.K + BK - 1) / BK;
+    // K-sharded gather (ag_overlap == 2): two passes over the tile list, each tile on the same CTA both times. Pass 0
+    // multiplies the own shard's K range (nothing to wait for), pass 1 the remote ranges and adds the pass-0 result
+    // in its epilogue, so the remote panels are first needed half-way through the kernel.
+    const bool ksplit = NMAPS > 1 && p.ag_overlap == 2;
+    const int n_pass = (ksplit && p.nranks > 1) ? 2 : 1;
+    const int kb_own = ksplit ? p.rows_per_rank / BK : 0;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -126,7 +135,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // tile -> (batch, m_blk, n_blk) with groups of 8 M-blocks sweeping N (keeps a B panel hot in L2)
     auto decode = [&](int tile, int& b, int& mb, int& nb) {
         if constexpr (NMAPS > 1) {
-            if (p.ag_overlap) {
+            if (p.ag_overlap == 1) {
                 // panel-major order starting at the own shard: remote panels are needed as late as possible
                 b = 0;
                 const int seq = tile / m_blocks;
@@ -167,11 +176,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
+            for (int pass = 0; pass < n_pass; ++pass) {
+            const int kbi0 = (n_pass == 2 && pass == 1) ? kb_own : 0;
+            const int kbi1 = (n_pass == 2 && pass == 0) ? kb_own : k_blocks;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 int b, mb, nb;
                 decode(tile, b, mb, nb);
                 const int m0 = mb * BM, n0 = nb * BN;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                const int kb_rot = ksplit ? p.me * kb_own : 0;
+                for (int kbi = kbi0; kbi < kbi1; ++kbi) {
+                    // K-sharded gather: own K range first, then the remote ranges in copier order
+                    const int kb = ksplit ? (kbi + kb_rot) % k_blocks : kbi;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
                     uint8_t* sb = sa + Cfg::A_BYTES;
@@ -204,6 +219,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                 tma_load_3d(sb, &tmBs.m[0], &full_bar[stage], kb * BK, n0, b);
                             }
                         }
+                    } else if (ksplit) {
+                        const int krow = kb * BK;
+                        const int owner = krow / p.rows_per_rank;
+                        if (owner == p.me) {
+#pragma unroll
+                            for (int j = 0; j < BN / 64; ++j)
+                                tma_load_3d(sb + j * (BK * 128), &tmBs.m[1], &full_bar[stage], n0 + j * 64,
+                                            krow - owner * p.rows_per_rank, 0);
+                        } else {
+                            if ((krow & 255) == 0 || kbi == kbi0) {   // first k-block of a 256-row panel
+                                while (ld_acquire_gpu_s32(p.panel_ready + (krow >> 8)) < (int)gridDim.x) {}
+                                fence_proxy_async_all();
+                            }
+#pragma unroll
+                            for (int j = 0; j < BN / 64; ++j)
+                                tma_load_3d(sb + j * (BK * 128), &tmBs.m[0], &full_bar[stage], n0 + j * 64, krow, 0);
+                        }
                     } else {
 #pragma unroll
                         for (int j = 0; j < BN / 64; ++j)
@@ -211,6 +243,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                     if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
                 }
+            }
             }
         }
     } else if (warp == 1) {
@@ -230,13 +263,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
+            for (int pass = 0; pass < n_pass; ++pass) {
+            const int kcount = n_pass == 2 ? (pass == 0 ? kb_own : k_blocks - kb_own) : k_blocks;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 mbar_wait(&tempty_bar[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * BN;
-                for (int kb = 0; kb < k_blocks; ++kb) {
+                for (int kb = 0; kb < kcount; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
                     const uint32_t a_lo = a_lo0 + stage * (Cfg::STAGE_BYTES >> 4);
@@ -249,6 +284,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
                 umma_commit(&tfull_bar[as]);
             }
+            }
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------------ epilogue (4 warps, 32 rows each)
@@ -256,6 +292,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         uint8_t* my_epi = smem_epi + q * (2 * 32 * 128);
         int it = 0;
         int buf = 0;
+        for (int pass = 0; pass < n_pass; ++pass) {
+        if (pass == 1) {   // pass 1 reads (generic proxy) what this warp's pass-0 TMA stores wrote
+            if (lane == 0) {
+                tma_store_wait<0>();
+                fence_proxy_async_all();
+            }
+            __syncwarp();
+        }
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             int b, mb, nb;
             decode(tile, b, mb, nb);
@@ -288,7 +332,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     v[i] = __uint_as_float(r0[i]) * p.alpha;
                     v[32 + i] = __uint_as_float(r1[i]) * p.alpha;
                 }
-                const int epi = p.epilogue;
+                const int epi = pass == 1 ? DSB_EPI_BIAS_RESIDUAL : p.epilogue;   // pass 1: aux = D of pass 0
                 if (p.bias != nullptr && epi != DSB_EPI_DGELU) {
                     const T* bp = reinterpret_cast<const T*>(p.bias) + col0;
 #pragma unroll
@@ -377,6 +421,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 buf ^= 1;
             }
         }
+        }
         if (lane == 0) {
             tma_store_wait<0>();
             if constexpr (NMAPS > 1) {
@@ -391,8 +436,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if constexpr (NMAPS > 1) {
             if (p.ag_overlap && p.nranks > 1) {
                 const int t = threadIdx.x - 64;                       // 0..63
-                const int ppr = p.rows_per_rank / BN;                 // panels per rank
-                const long panel_vecs = (long)BN * p.K / 8;           // 16-byte vectors per panel (shards are dense)
+                // a panel = 256 rows of the sharded operand; its rows are K long (mode 1) or N long (mode 2)
+                const int ppr = p.rows_per_rank / 256;                // panels per rank
+                const long panel_vecs = 256L * (p.ag_overlap == 2 ? p.N : p.K) / 8;   // shards are dense
+                const int n_panels = ppr * p.nranks;
                 const long cta_stride = (long)gridDim.x * 64;
                 uint4* gath = reinterpret_cast<uint4*>(p.gathered);
                 // remote panels in the order the tiles will need them, two panels per round so that every thread keeps
@@ -402,8 +449,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int pv = (int)panel_vecs;
                 const int cstride = (int)cta_stride;
                 (void)gath;
-                for (int seq0 = ppr; seq0 < n_blocks; seq0 += PG) {
-                    const int np = min(PG, n_blocks - seq0);
+                for (int seq0 = ppr; seq0 < n_panels; seq0 += PG) {
+                    const int np = min(PG, n_panels - seq0);
                     const int total = np * pv;
                     for (int i0 = blockIdx.x * 64 + t; i0 < total; i0 += UNR * cstride) {
                         uint4 v[UNR];
@@ -412,7 +459,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             const int i = i0 + u * cstride;
                             if (i < total) {
                                 const int pi = i / pv, off = i - pi * pv;
-                                const int nb = (seq0 + pi + p.me * ppr) % n_blocks;
+                                const int nb = (seq0 + pi + p.me * ppr) % n_panels;
                                 const int owner = nb / ppr;
                                 v[u] = ld_na_v4(reinterpret_cast<const uint4*>(p.peer_shards[owner]) +
                                                 (long)(nb - owner * ppr) * panel_vecs + off);
@@ -423,14 +470,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             const int i = i0 + u * cstride;
                             if (i < total) {
                                 const int pi = i / pv, off = i - pi * pv;
-                                const int nb = (seq0 + pi + p.me * ppr) % n_blocks;
+                                const int nb = (seq0 + pi + p.me * ppr) % n_panels;
                                 reinterpret_cast<uint4*>(p.gathered)[(long)nb * panel_vecs + off] = v[u];
                             }
                         }
                     }
                     __threadfence();
                     named_bar_sync(1, 64);
-                    if (t < np) red_release_gpu_add_s32(p.panel_ready + (seq0 + t + p.me * ppr) % n_blocks, 1);
+                    if (t < np) red_release_gpu_add_s32(p.panel_ready + (seq0 + t + p.me * ppr) % n_panels, 1);
                 }
             }
         }
@@ -684,6 +731,58 @@ extern "C" int dsb_gemm_ag_overlap(const void* A, void* const* shard_ptrs, int n
     p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
     p.rows_per_rank = rows;
     p.ag_overlap = 1; p.me = me; p.nranks = nranks; p.gathered = gathered; p.panel_ready = panel_flags;
+    p.rs_mode = 0;
+    for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = shard_ptrs[r < nranks ? r : 0];
+    if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);
+    return launch<__half, 256, MAXR>(ta, tbs, td, p, sms, stream);
+}
+
+// Overlapped all-gather + GEMM for the DGRAD of a row-sharded weight: D [M, N] = alpha * A [M, K] * W where
+// W [K, N] (nn.Linear weight: K = out features, N = in features) is row-sharded over `nranks` peers (dense shards,
+// K / nranks rows each, a multiple of 256). The shards split the REDUCTION dimension, so every output tile needs all of
+// them: the k loop of every tile starts with the own shard's K range and then walks the remote ranges in the order
+// in which two copier warps per CTA stream them (256-row panels) into `gathered` ([K, N], local scratch);
+// `panel_flags`: K / 256 ints, zeroed here. Each weight byte crosses NVLink once.
+extern "C" int dsb_gemm_ag_overlap_k(const void* A, void* const* shard_ptrs, int nranks, int me, void* gathered,
+                                     int* panel_flags, void* D, int M, int N, int K, long lda, long ldd, int dtype,
+                                     float alpha, void* stream_) {
+    using namespace dsb;
+    ensure_context_on_this_thread();
+    constexpr int MAXR = 8;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (M <= 0 || N <= 0 || K <= 0) return 0;
+    if (nranks < 1 || nranks > MAXR || me < 0 || me >= nranks || (K % nranks) || !gathered || !panel_flags)
+        return DSB_ERR_ARG;
+    const int rows = K / nranks;
+    if ((rows % 256) || (lda % 8) || (N % 8) || (ldd % 8)) return DSB_ERR_SIZE;
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    const int bf = dtype == DSB_DTYPE_BF16;
+    CUtensorMap ta, td;
+    BMapSet<MAXR> tbs;
+    int rc = make_map(&ta, bf, A, K, M, 1, lda, (long)M * lda, BK, BM);
+    if (rc) return rc;
+    rc = make_map(&tbs.m[0], bf, gathered, N, K, 1, N, (long)K * N, 64, BK);
+    if (rc) return rc;
+    rc = make_map(&tbs.m[1], bf, shard_ptrs[me], N, rows, 1, N, (long)rows * N, 64, BK);
+    if (rc) return rc;
+    for (int r = 2; r < MAXR; ++r) tbs.m[r] = tbs.m[0];
+    rc = make_map(&td, bf, D, N, M, 1, ldd, (long)M * ldd, EPI_COLS, 32);
+    if (rc) return rc;
+    cudaError_t e = cudaMemsetAsync(panel_flags, 0, sizeof(int) * (K / 256), stream);
+    if (e != cudaSuccess) return -(int)e;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K; p.batch = 1;
+    p.a_mn = 0; p.b_mn = 1;
+    p.epilogue = DSB_EPI_NONE; p.alpha = alpha;
+    p.bias = nullptr; p.aux = D; p.ldaux = ldd; p.stride_aux = 0;   // pass 1 accumulates onto pass 0's D
+    p.aux_out = nullptr; p.ldaux_out = 0; p.stride_aux_out = 0;
+    p.rows_per_rank = rows;
+    p.ag_overlap = 2; p.me = me; p.nranks = nranks; p.gathered = gathered; p.panel_ready = panel_flags;
     p.rs_mode = 0;
     for (int r = 0; r < MAXR; ++r) p.peer_shards[r] = shard_ptrs[r < nranks ? r : 0];
     if (bf) return launch<__nv_bfloat16, 256, MAXR>(ta, tbs, td, p, sms, stream);

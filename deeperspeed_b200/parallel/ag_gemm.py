@@ -16,6 +16,7 @@ _p, _i, _l, _f = C.c_void_p, C.c_int, C.c_long, C.c_float
 N.register_sigs({
     "dsb_gemm_gather_b": [_p, _p, _i, _p, _i, _i, _i, _l, _l, _l, _i, _i, _f, _p, _p, _l, _p],
     "dsb_gemm_ag_overlap": [_p, _p, _i, _i, _p, _p, _p, _i, _i, _i, _l, _l, _i, _i, _f, _p, _p, _l, _p],
+    "dsb_gemm_ag_overlap_k": [_p, _p, _i, _i, _p, _p, _p, _i, _i, _i, _l, _l, _i, _f, _p],
     "dsb_gemm_reduce_scatter": [_p, _p, _p, _p, _p, _i, _i, _p, _i, _i, _i, _l, _l, _i, _i, _i, _f, _f, C.c_uint, _p],
 })
 
@@ -76,6 +77,26 @@ def ag_linear(x, sw, bias=None, direct=False):
     N.check(rc, "dsb_gemm_gather_b")
     K._count()
     return out.view(*x.shape[:-1], sw.N)
+
+
+def ag_linear_dgrad(grad_out, sw):
+    """grad_out [.., N_out] @ gather(sw) -> [.., K_in]: the input gradient of a linear whose weight [N_out, K_in] is
+    row-sharded, with the all-gather inside the GEMM kernel (`dsb_gemm_ag_overlap_k`: the shards split the reduction
+    dimension, every tile starts on the own shard's range while copier warps bring in the others)."""
+    g2 = grad_out.reshape(-1, grad_out.shape[-1])
+    if not g2.is_contiguous():
+        g2 = g2.contiguous()
+    M = g2.shape[0]
+    out = torch.empty(M, sw.K, dtype=g2.dtype, device=g2.device)
+    ptrs = (C.c_void_p * sw.world)(*sw.peer_ptrs)
+    gathered = N.scratch(sw.N * sw.K * 2, g2.device, "ag_gather")
+    flags = N.scratch(4 * (sw.N // 256), g2.device, "ag_flags")
+    rc = N.cuda_lib().dsb_gemm_ag_overlap_k(N.ptr(g2), ptrs, sw.world, sw.rank, N.ptr(gathered), N.ptr(flags),
+                                            N.ptr(out), M, sw.K, sw.N, g2.stride(0), out.stride(0),
+                                            N.dtype_code(g2.dtype), 1.0, N.stream_ptr())
+    N.check(rc, "dsb_gemm_ag_overlap_k")
+    K._count()
+    return out.view(*grad_out.shape[:-1], sw.K)
 
 
 class GemmReduceScatter:

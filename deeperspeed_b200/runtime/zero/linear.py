@@ -68,9 +68,11 @@ class WeightHolder:
 
 class FusedAGLinearFunction(torch.autograd.Function):
     """ZeRO-3 linear whose forward gathers the weight INSIDE the GEMM kernel from the peers' shards
-    (parallel/ag_gemm.py). The weight is not an autograd input: backward computes its gradient from the copy the
-    ZeRO-3 pre-backward hook has gathered, stores it in `.grad` and runs the parameter's ZeRO gradient hook
-    (reduce-scatter + release) itself."""
+    (parallel/ag_gemm.py). The weight is not an autograd input and stays partitioned in backward too: the input
+    gradient comes from the K-sharded all-gather + GEMM kernel (`ag_linear_dgrad`), the weight gradient from the
+    GEMM + reduce-scatter kernel (`GemmReduceScatter`), whose result goes straight into the gradient partition.
+    Where a fused kernel does not apply (shape, or the weight happens to be gathered) the plain GEMMs and the
+    parameter's ZeRO gradient hook (NCCL reduce-scatter + release) are used."""
 
     @staticmethod
     def forward(ctx, input, bias, dummy, holder):
@@ -83,7 +85,7 @@ class FusedAGLinearFunction(torch.autograd.Function):
     def backward(ctx, grad_output):
         input, bias = ctx.saved_tensors
         w = ctx.holder.param
-        assert w.numel() == w.ds_numel, "ZeRO-3 pre-backward hook did not gather the weight"
+        gathered = w.numel() == w.ds_numel
         go2 = grad_output.reshape(-1, grad_output.shape[-1])
         if not go2.is_contiguous():
             go2 = go2.contiguous()
@@ -91,7 +93,11 @@ class FusedAGLinearFunction(torch.autograd.Function):
         fast = go2.shape[0] % 64 == 0 and go2.shape[1] % 8 == 0 and x2.shape[1] % 8 == 0
         grad_input = grad_bias = None
         if ctx.needs_input_grad[0]:
-            gi = K.gemm(go2, w.data, trans_b=False) if fast else go2.matmul(w.data)
+            if not gathered:
+                from ...parallel.ag_gemm import ag_linear_dgrad
+                gi = ag_linear_dgrad(go2, w.ds_sharded)
+            else:
+                gi = K.gemm(go2, w.data, trans_b=False) if fast else go2.matmul(w.data)
             grad_input = gi.view(input.shape)
         if bias is not None and ctx.needs_input_grad[1]:
             grad_bias = go2.float().sum(0).to(go2.dtype)

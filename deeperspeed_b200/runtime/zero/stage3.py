@@ -351,7 +351,9 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         self.param_coordinator.release_sub_module(module)
 
     def _pre_backward(self, module, grad_output):
-        self.param_coordinator.fetch_sub_module(module)
+        # weights on the fused path stay partitioned in backward as well (K-sharded all-gather + GEMM for the input
+        # gradient, GEMM + reduce-scatter for the weight gradient); DSB_ZERO3_FUSED_DGRAD=0 gathers them with NCCL
+        self.param_coordinator.fetch_sub_module(module, forward=self._fused_dgrad)
 
     def _post_backward(self, module, grad_input, grad_output):
         # parameters are released from their own post-accumulate-grad hook: AccumulateGrad may run after this hook
@@ -370,11 +372,14 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 p.register_post_accumulate_grad_hook(hook)
         self._setup_fused_wgrad_reduce_scatter()
 
+    @property
+    def _fused_dgrad(self):
+        return os.environ.get("DSB_ZERO3_FUSED_DGRAD", "1") == "1"
+
     def _setup_fused_wgrad_reduce_scatter(self):
         """Weights on the fused all-gather + GEMM path also get their gradient reduce-scattered INSIDE the wgrad GEMM
         (parallel/ag_gemm.py:GemmReduceScatter): the kernel hands back this rank's averaged shard, which is added
         to the gradient partition without any NCCL call. DSB_ZERO3_FUSED_RS=0 keeps the NCCL reduce-scatter."""
-        import os
         self._gemm_rs = None
         fused = [p for params in self.sub_groups for p in params if getattr(p, "ds_fused_ag", False)]
         if not fused or self.partition_count < 2 or os.environ.get("DSB_ZERO3_FUSED_RS", "1") != "1":

@@ -197,6 +197,12 @@ int dsb_symm_free(void* p);
 int dsb_ipc_get_handle(void* devptr, void* handle64);
 int dsb_ipc_open(const void* handle64, void** out);
 int dsb_ipc_close(void* p);
+/* Same overlap for the dgrad of a row-sharded weight W [K, N]: D [M, N] = alpha * A [M, K] * gather(W). The shards
+ * split the reduction dimension; every tile's k loop starts at the own shard's range and follows the copiers' panel
+ * order over the remote ranges. rows per shard a multiple of 256; `panel_flags`: K / 256 ints.
+ * Replaces `_allgather_param` before the backward of a linear (reference zero/stage3.py:1471-1559). */
+int dsb_gemm_ag_overlap_k(const void* A, void* const* shard_ptrs, int nranks, int me, void* gathered, int* panel_flags,
+                          void* D, int M, int N, int K, long lda, long ldd, int dtype, float alpha, void* stream);
 /* GEMM + reduce-scatter in one cooperative kernel (ZeRO-3 weight gradient): every rank computes
  * D = alpha * op(A) op(B)^T ([M, N], rows owned by nranks ranks, M / nranks a multiple of 128); tiles are TMA-stored
  * into slot `me` of the owner's staging buffer (stage_ptrs[r]: [nranks, M / nranks, N], peer-mapped) as they are

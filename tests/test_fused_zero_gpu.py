@@ -197,6 +197,16 @@ def _ag_gemm_worker():
         rel = ((y.float() - ref).abs().max() / ref.abs().max()).item()
         assert rel < 3e-3, (kwargs, rel)
         dist.barrier()
+    # input gradient of the same sharded weight: the shards split the reduction dimension
+    from deeperspeed_b200.parallel.ag_gemm import ag_linear_dgrad
+    go = (torch.randn(384, Nn, device="cuda") * 0.1).half()
+    ref_gi = go.float() @ w.float()
+    for _ in range(2):
+        gi = ag_linear_dgrad(go, sw)
+        torch.cuda.synchronize()
+        rel = ((gi.float() - ref_gi).abs().max() / ref_gi.abs().max()).item()
+        assert gi.shape == (384, Kk) and rel < 3e-3, rel
+        dist.barrier()
     # a taller problem so that several waves of tiles wait on remote panels
     x2 = torch.randn(4096, Kk, device="cuda").half()
     y2 = ag_linear(x2, sw, None)
@@ -214,12 +224,26 @@ def _zero3_fused_ag_worker(tmp):
     import deeperspeed_b200 as deepspeed
     from deeperspeed_b200.parallel import ag_gemm
     calls = [0]
+    dgrad_calls = [0]
+    rs_calls = [0]
     orig = ag_gemm.ag_linear
+    orig_dgrad = ag_gemm.ag_linear_dgrad
+    orig_rs = ag_gemm.GemmReduceScatter.__call__
 
     def counting(*a, **k):
         calls[0] += 1
         return orig(*a, **k)
+
+    def counting_dgrad(*a, **k):
+        dgrad_calls[0] += 1
+        return orig_dgrad(*a, **k)
+
+    def counting_rs(self, *a, **k):
+        rs_calls[0] += 1
+        return orig_rs(self, *a, **k)
     ag_gemm.ag_linear = counting
+    ag_gemm.ag_linear_dgrad = counting_dgrad
+    ag_gemm.GemmReduceScatter.__call__ = counting_rs
 
     class MLP(torch.nn.Module):
         def __init__(self):
@@ -232,7 +256,8 @@ def _zero3_fused_ag_worker(tmp):
             h = torch.nn.functional.gelu(self.l1(x))
             return torch.nn.functional.cross_entropy(self.head(self.l2(h)).float(), y)
 
-    cfg = {"train_batch_size": 16, "train_micro_batch_size_per_gpu": 8, "steps_per_print": 100,
+    # 64 rows per rank: the weight-gradient GEMM + reduce-scatter kernel applies as well
+    cfg = {"train_batch_size": 128, "train_micro_batch_size_per_gpu": 64, "steps_per_print": 100,
            "optimizer": {"type": "Adam", "params": {"lr": 1e-3}},
            "fp16": {"enabled": True, "loss_scale": 128},
            "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 10}}
@@ -246,8 +271,8 @@ def _zero3_fused_ag_worker(tmp):
         g = torch.Generator().manual_seed(100 + dist.get_rank())
         losses = []
         for _ in range(4):
-            x = torch.randn(8, 256, generator=g).cuda().half()
-            y = torch.randint(0, 16, (8,), generator=g).cuda()
+            x = torch.randn(64, 256, generator=g).cuda().half()
+            y = torch.randint(0, 16, (64,), generator=g).cuda()
             loss = engine(x, y)
             engine.backward(loss)
             engine.step()
@@ -256,6 +281,10 @@ def _zero3_fused_ag_worker(tmp):
             results.append((losses, [p.detach().float().clone() for p in model.parameters()]))
     (l0, p0), (l1, p1) = results
     assert calls[0] == 2 * 4, calls   # l1 and l2 forwards of the fused run, nothing else
+    # backward of the fused run: l2's input gradient through the K-sharded all-gather + GEMM (l1's input needs no
+    # gradient), both weight gradients through GEMM + reduce-scatter; no NCCL gather / reduce-scatter for them
+    assert dgrad_calls[0] == 1 * 4, dgrad_calls
+    assert rs_calls[0] == 2 * 4, rs_calls
     assert all(abs(a - b) < 2e-2 for a, b in zip(l0, l1)), (l0, l1)
     for a, b in zip(p0, p1):
         assert (a - b).abs().max().item() < 5e-3

@@ -417,3 +417,101 @@ def test_causal_self_attention_op():
     ref.backward(g.float().cpu())
     assert _rel(out.cpu(), ref) < 5e-3
     assert _rel(qkv.grad.cpu(), ref_in.grad) < 1e-2
+
+
+def test_fused_zero_kernels_single_rank():
+    """The fused ZeRO step kernels with R = 1 (this GPU is its own peer): reduce + norm, Adam + push, and the LAMB
+    variant's per-tensor trust ratios, against plain fp32 PyTorch. (The multi-GPU behaviour is in
+    tests/test_fused_zero_gpu.py; this one also runs where only one GPU is visible.)"""
+    from deeperspeed_b200.parallel.fused_zero_single import SingleRankFusedZero
+    torch.manual_seed(0)
+    sizes = [4096, 8, 100000, 2048 * 64, 40]
+    n = (sum(sizes) + 1024 + 7) // 8 * 8
+    lr, betas, eps, wd = 1e-2, (0.9, 0.999), 1e-8, 0.01
+    for mode in ("adam", "lamb"):
+        z = SingleRankFusedZero(n, tensor_sizes=sizes)
+        used = sum(sizes)
+        w0 = torch.zeros(n, device="cuda")
+        w0[:used] = torch.randn(used, device="cuda") * 0.5
+        z.master.copy_(w0)
+        w, m, v = w0.clone(), torch.zeros_like(w0), torch.zeros_like(w0)
+        for step in (1, 2, 3):
+            g16 = torch.zeros(n, device="cuda", dtype=torch.float16)
+            g16[:used] = (torch.randn(used, device="cuda") * 0.1).half()
+            z.grad.copy_(g16)
+            z.rs_norm(scale=0.5)
+            g = g16.float() * 0.5
+            torch.testing.assert_close(z.red, g, rtol=0, atol=0)
+            torch.testing.assert_close(z.sumsq[0], (g * g).sum(), rtol=1e-4, atol=0)
+            assert z.flag.item() == 0
+            m = betas[0] * m + (1 - betas[0]) * g
+            v = betas[1] * v + (1 - betas[1]) * g * g
+            if mode == "adam":
+                z.adam_ag(lr, betas, eps, wd, True, step)
+                upd = (m / (1 - betas[0] ** step)) / ((v / (1 - betas[1] ** step)).sqrt() + eps) + wd * w
+                w = w - lr * upd
+            else:
+                z.lamb_ag(lr, betas, eps, wd, 10.0, 0.01, step)
+                u = m / (v.sqrt() + eps) + wd * w
+                step_size = lr * (1 - betas[1] ** step) ** 0.5 / (1 - betas[0] ** step)
+                pos = 0
+                for ti, s in enumerate(sizes):
+                    wn, un = w[pos:pos + s].norm(), u[pos:pos + s].norm()
+                    c = float(min(max(wn / un, 0.01), 10.0)) if wn > 0 and un > 0 else 1.0
+                    assert abs(z.coeff[ti].item() - c) < 1e-4 * max(1.0, c), (ti, z.coeff[ti].item(), c)
+                    w[pos:pos + s] -= step_size * c * u[pos:pos + s]
+                    pos += s
+            torch.cuda.synchronize()
+            torch.testing.assert_close(z.master, w, rtol=1e-5, atol=1e-6)
+            torch.testing.assert_close(z.param.float(), w.half().float(), rtol=0, atol=4e-3)
+        # non-finite gradients raise the flag; a set skip flag leaves everything untouched
+        z.grad[5] = float("inf")
+        z.rs_norm()
+        assert z.flag.item() == 1
+        z.skip.fill_(1)
+        before = z.master.clone()
+        (z.adam_ag(lr, betas, eps, wd, True, 4) if mode == "adam" else z.lamb_ag(lr, betas, eps, wd, 10.0, 0.01, 4))
+        torch.cuda.synchronize()
+        assert torch.equal(before, z.master)
+
+
+def test_collective_gemm_variants_single_rank():
+    """The GEMM kernels that carry a collective (all-gather of a row-sharded weight in forward and dgrad layout,
+    reduce-scatter of the result) with ONE rank: the GPU is its own peer, so tile order, panel flags, the k-loop
+    rotation, the staging stores, the barriers and the slot sum all run; results against fp32 matmul."""
+    import ctypes as C
+    from deeperspeed_b200.parallel import ag_gemm  # noqa: F401  (ctypes signatures)
+    lib = N.cuda_lib()
+    torch.manual_seed(1)
+    tokens, out_f, in_f = 384, 512, 264
+    w = (torch.randn(out_f, in_f, device="cuda") * 0.1).half()
+    x = (torch.randn(tokens, in_f, device="cuda") * 0.1).half()
+    go = (torch.randn(tokens, out_f, device="cuda") * 0.1).half()
+    flags = torch.zeros(1024, dtype=torch.int32, device="cuda")
+    one = lambda t: (C.c_void_p * 1)(t.data_ptr())
+    dc, st = N.dtype_code(torch.float16), N.stream_ptr()
+    gathered = torch.empty_like(w)
+    pflags = torch.zeros(64, dtype=torch.int32, device="cuda")
+    # forward: y = x @ gather(w)^T
+    y = torch.empty(tokens, out_f, device="cuda", dtype=torch.float16)
+    N.check(lib.dsb_gemm_ag_overlap(N.ptr(x), one(w), 1, 0, N.ptr(gathered), N.ptr(pflags), N.ptr(y), tokens, out_f,
+                                    in_f, x.stride(0), y.stride(0), dc, 0, 1.0, None, None, 0, st), "ag_overlap")
+    ref = x.float() @ w.float().t()
+    assert ((y.float() - ref).abs().max() / ref.abs().max()).item() < 3e-3
+    # dgrad: gi = go @ gather(w), shards split the reduction dimension
+    gi = torch.empty(tokens, in_f, device="cuda", dtype=torch.float16)
+    N.check(lib.dsb_gemm_ag_overlap_k(N.ptr(go), one(w), 1, 0, N.ptr(gathered), N.ptr(pflags), N.ptr(gi), tokens, in_f,
+                                      out_f, go.stride(0), gi.stride(0), dc, 1.0, st), "ag_overlap_k")
+    ref = go.float() @ w.float()
+    assert ((gi.float() - ref).abs().max() / ref.abs().max()).item() < 3e-3
+    # wgrad + reduce-scatter: dW = go^T @ x, all rows owned by this rank
+    stage = torch.zeros(out_f * in_f, device="cuda", dtype=torch.float16)
+    sync = torch.zeros(2, dtype=torch.int32, device="cuda")
+    dw = torch.empty(out_f, in_f, device="cuda", dtype=torch.float16)
+    for epoch in (1, 2):
+        N.check(lib.dsb_gemm_reduce_scatter(N.ptr(go), N.ptr(x), N.ptr(dw), one(stage), one(flags), 1, 0, N.ptr(sync),
+                                            out_f, in_f, tokens, go.stride(0), x.stride(0), 1, 1, dc, 1.0, 0.5, epoch,
+                                            st), "gemm_reduce_scatter")
+        ref = 0.5 * (go.float().t() @ x.float())
+        torch.cuda.synchronize()
+        assert ((dw.float() - ref).abs().max() / ref.abs().max()).item() < 3e-3
