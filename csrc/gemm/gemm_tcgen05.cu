@@ -106,9 +106,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // K-sharded gather (ag_overlap == 2): two passes over the tile list, each tile on the same CTA both times. Pass 0
     // multiplies the own shard's K range (nothing to wait for), pass 1 the remote ranges and adds the pass-0 result
     // in its epilogue, so the remote panels are first needed half-way through the kernel.
+    // With a short own range (< 32 k-blocks) a pass's mainloop no longer covers the epilogue and the second trip
+    // through D costs more than the first wave's wait for the first panels, so such shapes run in one pass.
     const bool ksplit = NMAPS > 1 && p.ag_overlap == 2;
-    const int n_pass = (ksplit && p.nranks > 1) ? 2 : 1;
     const int kb_own = ksplit ? p.rows_per_rank / BK : 0;
+    const int n_pass = (ksplit && p.nranks > 1 && kb_own >= 32) ? 2 : 1;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -176,6 +178,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (elect_one()) {
             int stage = 0;
             uint32_t phase = 0;
+            int ready_seq = -1;   // K-sharded gather: last remote panel (copier order) this CTA has seen complete
+            const int last_panel = ksplit ? ((p.me * kb_own + k_blocks - 1) % k_blocks) >> 2 : 0;
             for (int pass = 0; pass < n_pass; ++pass) {
             const int kbi0 = (n_pass == 2 && pass == 1) ? kb_own : 0;
             const int kbi1 = (n_pass == 2 && pass == 0) ? kb_own : k_blocks;
@@ -186,7 +190,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int kb_rot = ksplit ? p.me * kb_own : 0;
                 for (int kbi = kbi0; kbi < kbi1; ++kbi) {
                     // K-sharded gather: own K range first, then the remote ranges in copier order
-                    const int kb = ksplit ? (kbi + kb_rot) % k_blocks : kbi;
+                    int kb = kbi + kb_rot;
+                    if (kb >= k_blocks) kb -= k_blocks;
                     mbar_wait(&empty_bar[stage], phase ^ 1);
                     uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
                     uint8_t* sb = sa + Cfg::A_BYTES;
@@ -221,15 +226,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         }
                     } else if (ksplit) {
                         const int krow = kb * BK;
-                        const int owner = krow / p.rows_per_rank;
-                        if (owner == p.me) {
+                        if (kbi < kb_own) {   // the rotation puts the own shard's range first
 #pragma unroll
                             for (int j = 0; j < BN / 64; ++j)
                                 tma_load_3d(sb + j * (BK * 128), &tmBs.m[1], &full_bar[stage], n0 + j * 64,
-                                            krow - owner * p.rows_per_rank, 0);
+                                            krow - p.me * p.rows_per_rank, 0);
                         } else {
-                            if ((krow & 255) == 0 || kbi == kbi0) {   // first k-block of a 256-row panel
+                            // Panels become ready in copier order and stay ready, so a panel is polled (an L2 round
+                            // trip plus a proxy fence on the producer's critical path) only the first time this CTA
+                            // gets that far; with a poll at every panel start of every tile the producer could not
+                            // keep the ring full (dgrad ran at 0.31 ms instead of 0.20 ms).
+                            const int seq = (kbi - kb_own) >> 2;   // remote panel index in copier order (4 k-blocks each)
+                            if (seq > ready_seq) {
                                 while (ld_acquire_gpu_s32(p.panel_ready + (krow >> 8)) < (int)gridDim.x) {}
+                                ready_seq = seq;
+                                if (ld_acquire_gpu_s32(p.panel_ready + last_panel) >= (int)gridDim.x) ready_seq = 1 << 30;
                                 fence_proxy_async_all();
                             }
 #pragma unroll
@@ -515,17 +526,46 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const long nvec = (long)p.rows_per_rank * p.N / 8;
             const uint4* st = reinterpret_cast<const uint4*>(p.rs_stage);
             uint4* out = reinterpret_cast<uint4*>(p.rs_out);
-            for (long i = (long)blockIdx.x * NUM_THREADS + threadIdx.x; i < nvec; i += (long)gridDim.x * NUM_THREADS) {
-                float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-                for (int r = 0; r < p.nranks; ++r) {
-                    float f[8];
-                    unpack8<T>(ld_na_v4(st + (long)r * nvec + i), f);
+            // one CTA per SM and 256 threads: keep UN x nranks 16-byte loads in flight per thread, otherwise the slot
+            // sum runs at a fraction of the HBM bandwidth (it was ~40 us of the 75 us this kernel spent beyond its GEMM)
+            constexpr int UN = 4;
+            const long gstride = (long)gridDim.x * NUM_THREADS;
+            for (long i0 = (long)blockIdx.x * NUM_THREADS + threadIdx.x; i0 < nvec; i0 += UN * gstride) {
+                float acc[UN][8];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) acc[k] += f[k];
+                for (int u = 0; u < UN; ++u)
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc[u][k] = 0.f;
+                for (int r0 = 0; r0 < p.nranks; r0 += 2) {
+                    uint4 raw[UN][2];
+#pragma unroll
+                    for (int u = 0; u < UN; ++u)
+#pragma unroll
+                        for (int rr = 0; rr < 2; ++rr) {
+                            const long i = i0 + u * gstride;
+                            if (i < nvec && r0 + rr < p.nranks) raw[u][rr] = ld_na_v4(st + (long)(r0 + rr) * nvec + i);
+                        }
+#pragma unroll
+                    for (int u = 0; u < UN; ++u)
+#pragma unroll
+                        for (int rr = 0; rr < 2; ++rr) {
+                            if (i0 + u * gstride < nvec && r0 + rr < p.nranks) {
+                                float f[8];
+                                unpack8<T>(raw[u][rr], f);
+#pragma unroll
+                                for (int k = 0; k < 8; ++k) acc[u][k] += f[k];
+                            }
+                        }
                 }
 #pragma unroll
-                for (int k = 0; k < 8; ++k) acc[k] *= p.rs_scale;
-                out[i] = pack8<T>(acc);
+                for (int u = 0; u < UN; ++u) {
+                    const long i = i0 + u * gstride;
+                    if (i < nvec) {
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) acc[u][k] *= p.rs_scale;
+                        out[i] = pack8<T>(acc[u]);
+                    }
+                }
             }
         }
     }

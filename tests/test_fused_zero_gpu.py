@@ -207,6 +207,17 @@ def _ag_gemm_worker():
         rel = ((gi.float() - ref_gi).abs().max() / ref_gi.abs().max()).item()
         assert gi.shape == (384, Kk) and rel < 3e-3, rel
         dist.barrier()
+    # long reduction (2048 rows per shard): the two-pass form (own range, then remote ranges accumulated on top)
+    torch.manual_seed(4)
+    w_long = (torch.randn(4096, 512, device="cuda") * 0.05).half()
+    sw_long = ShardedWeight(w_long, group=None)
+    torch.manual_seed(20 + dist.get_rank())
+    go = (torch.randn(640, 4096, device="cuda") * 0.1).half()
+    ref_gi = go.float() @ w_long.float()
+    gi = ag_linear_dgrad(go, sw_long)
+    torch.cuda.synchronize()
+    assert ((gi.float() - ref_gi).abs().max() / ref_gi.abs().max()).item() < 3e-3
+    dist.barrier()
     # a taller problem so that several waves of tiles wait on remote panels
     x2 = torch.randn(4096, Kk, device="cuda").half()
     y2 = ag_linear(x2, sw, None)

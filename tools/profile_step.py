@@ -21,10 +21,16 @@ for _ in range(2):
     engine.train_batch(it)
 torch.cuda.synchronize()
 from torch.profiler import profile, ProfilerActivity
-with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU], record_shapes=True) as prof:
     engine.train_batch(it)
     torch.cuda.synchronize()
 tab = prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70)
 os.makedirs("gpurun_out", exist_ok=True)
 open("gpurun_out/profile_step.txt", "w").write(tab)
 print(tab[-9000:])
+# which framework (aten) ops still launch kernels, by input shape: candidates for fusion into our own kernels
+ops = [e for e in prof.key_averages(group_by_input_shape=True) if e.key.startswith("aten::") and e.self_device_time_total > 0]
+ops.sort(key=lambda e: -e.self_device_time_total)
+lines = ["%-40s %10.1f us  x%-4d %s" % (e.key, e.self_device_time_total, e.count, str(e.input_shapes)[:110]) for e in ops[:30]]
+open("gpurun_out/profile_step_aten_ops.txt", "w").write("\n".join(lines))
+print("\n".join(lines))
