@@ -152,6 +152,19 @@ def main():
         loss.backward()
     report("cross_entropy fwd+bwd", timeit([ce], iters=6, warm=2, graph=False), ROWS * V * 2 * 3)
 
+    # ---- rotary: forward (q, k out of the fused QKV activation) and backward (+ dV copy into the dQKV buffer)
+    from deeperspeed_b200.ops.attention import rotary_oop
+    Bq, Sq, Hq, Dq = 4, 2048, 16, 128
+    qkv = torch.randn(Bq, Sq, 3, Hq, Dq, device=dev, dtype=dt)
+    q = torch.empty(Bq, Sq, Hq, Dq, device=dev, dtype=dt)
+    k = torch.empty_like(q)
+    dq, dk, dv = torch.randn_like(q), torch.randn_like(q), torch.randn_like(q)
+    dqkv = torch.empty_like(qkv)
+    one = Bq * Sq * Hq * Dq * 2
+    report("rotary fwd (q,k)", timeit([lambda: rotary_oop(qkv[:, :, 0], qkv[:, :, 1], q, k, Dq, 10000.0)]), 4 * one)
+    report("rotary bwd (dq,dk,+dv)", timeit([lambda: rotary_oop(dq, dk, dqkv[:, :, 0], dqkv[:, :, 1], Dq, 10000.0,
+                                                               inverse=True, v_in=dv, v_out=dqkv[:, :, 2])]), 6 * one)
+
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(dict(copy_peak_GBps=peak, ops=res), open("gpurun_out/bench_ops.json", "w"), indent=1)
 
