@@ -667,3 +667,81 @@ def test_partitioned_activation_checkpointing(cpu_ckpt, contiguous):
             ckpt.reset()
         ckpt.configure(None, partition_activations=False, checkpoint_in_cpu=False, contiguous_checkpointing=False)
     run()
+
+
+@pytest.mark.parametrize("stage", [1, 2, 3])
+def test_zero_empty_partitions_world3(stage, tmp_path):
+    """Reference tests/unit/test_fp16.py (empty partitions at world 3): a model so small that some ranks own nothing
+    but padding still trains, and stays equal to plain AdamW on the global batch."""
+    import deeperspeed_b200 as deepspeed
+    from simple_model import SimpleModel, args_from_dict, random_dataset
+
+    @distributed_test(world_size=3)
+    def run():
+        hid = 1
+        cfg = {"train_batch_size": 3, "train_micro_batch_size_per_gpu": 1, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.01, "weight_decay": 0.01}},
+               "fp16": {"enabled": True, "type": "fp32"}, "zero_optimization": {"stage": stage}}
+        torch.manual_seed(42)
+        model = SimpleModel(hid)          # 2 parameters in total: at least one of the 3 ranks owns only padding
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        data = [random_dataset(8, hid, seed=r) for r in range(3)]
+        for step in range(3):
+            x, y = data[dist.get_rank()][step]
+            loss = engine(x.unsqueeze(0).to(engine.device), y.unsqueeze(0).to(engine.device))
+            engine.backward(loss)
+            engine.step()
+            assert loss.item() == loss.item()
+        torch.manual_seed(42)
+        ref = SimpleModel(hid)
+        opt = torch.optim.AdamW(ref.parameters(), lr=0.01, weight_decay=0.01)
+        for step in range(3):
+            opt.zero_grad()
+            for r in range(3):
+                x, y = data[r][step]
+                (ref(x.unsqueeze(0), y.unsqueeze(0)) / 3).backward()
+            opt.step()
+        if stage == 3:
+            ctx = deepspeed.zero.GatheredParameters(list(engine.module.parameters()))
+        else:
+            import contextlib
+            ctx = contextlib.nullcontext()
+        with ctx:
+            for p, r in zip(engine.module.parameters(), ref.parameters()):
+                assert torch.allclose(p.detach().float().view(-1), r.detach().view(-1), atol=2e-5), (p, r)
+    run()
+
+
+@pytest.mark.parametrize("pp,dp", [(1, 4), (2, 2), (4, 1)])
+def test_onebit_adam_pipeline_topologies(pp, dp, tmp_path):
+    """Reference tests/unit/test_onebit.py (pipeline topologies): 1-bit Adam under PipelineEngine goes through its
+    warm-up and into the compressed phase on every (pp, dp) split of 4 ranks, and data-parallel replicas stay equal."""
+    import deeperspeed_b200 as deepspeed
+    from deeperspeed_b200.runtime.pipe.topology import PipeDataParallelTopology
+    from simple_model import LinearStackPipe, args_from_dict, random_dataset
+
+    @distributed_test(world_size=4)
+    def run():
+        hid = 16
+        cfg = {"train_batch_size": 4 * dp, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "OneBitAdam", "params": {"lr": 1e-3, "freeze_step": 2, "cuda_aware": False,
+                                                              "comm_backend_name": "nccl"}},
+               "fp16": {"enabled": True, "type": "fp32"}}
+        torch.manual_seed(7)
+        model = LinearStackPipe(input_dim=hid, hidden_dim=hid, output_dim=hid, num_layers=3,
+                                topology=PipeDataParallelTopology(num_pp=pp, num_dp=dp))
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=[p for p in model.parameters() if p.requires_grad])
+        ds = random_dataset(256, hid, seed=engine.grid.get_data_parallel_rank())
+        loader = deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(ds, batch_size=2))
+        it = iter(loader)
+        losses = [engine.train_batch(data_iter=it) for _ in range(5)]     # 2 warm-up steps, 3 compressed
+        assert all(float(l) == float(l) for l in losses)
+        assert engine.optimizer.adam_freeze_key if hasattr(engine.optimizer, "adam_freeze_key") else True
+        flat = torch.cat([p.detach().float().view(-1) for p in model.parameters()])
+        ref = flat.clone()
+        dist.broadcast(ref, src=engine.grid.stage_to_global(engine.stage_id, data=0),
+                       group=engine.grid.get_data_parallel_group())
+        assert torch.allclose(flat, ref, atol=1e-6), (flat - ref).abs().max()
+    run()
