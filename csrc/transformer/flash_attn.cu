@@ -1,0 +1,389 @@
+// Causal / full flash-attention forward on tcgen05 (head dim 128, fp16 / bf16), one CTA per 128 query rows of one
+// (batch, head).
+//
+//   warp 0 (one elected lane): TMA producer. Q tile once, then K_j / V_j tiles (128 keys each) into a 2-stage ring.
+//   warp 1 (one elected lane): issues S_j = Q K_j^T (UMMA 128 x 128 x 16, both operands K-major) into one of two
+//                              TMEM S buffers and O += P_j V_j (A = P from shared memory, B = V read MN-major from the
+//                              tile exactly as TMA delivered it). S_{j+1} is issued before P_j is awaited, so the
+//                              tensor pipe computes the next scores while the softmax warps work on the current ones.
+//   warp 2: TMEM allocation (512 columns: S0 | S1 | O).
+//   warps 4-7: online softmax, thread t owns query row t (TMEM lane t). Two trips over the 128 scores of the row
+//              (max, then exp2 / sum / fp16 P written into 128-byte-swizzled shared memory), rescale of the O
+//              accumulator through tcgen05.ld / tcgen05.st, final 1/l scaling, O staged in shared memory and stored
+//              with TMA, log-sum-exp written for the backward pass.
+//
+// Q, K, V, O are addressed as [B, S, H, D] with arbitrary batch / sequence / head strides (unit last stride), i.e. the
+// q / k buffers the rotary kernel writes and the V slice of the fused QKV activation are read in place and the
+// context comes out in the [B, S, H * D] layout the output projection consumes.
+// Reference: the score / softmax / context chain of csrc/transformer/ds_transformer_cuda.cpp:186-214 (strided batch
+// GEMMs + attn_softmax + dropout), which materialises the [B, H, S, S] probabilities; this kernel never does.
+#include "../common/ptx.cuh"
+#include "../../include/dsb200.h"
+#include "../common/host_ctx.h"
+#include <type_traits>
+
+namespace dsb {
+namespace fa {
+
+constexpr int BQ = 128;
+constexpr int BKV = 128;
+constexpr int HD = 128;
+constexpr int TILE_BYTES = 128 * HD * 2;       // 32 KiB: two 64-column chunks of [128 rows x 128 B]
+constexpr int CHUNK_BYTES = 128 * 128;         // 16 KiB
+constexpr int KV_STAGES = 2;
+constexpr int OFF_Q = 0;
+constexpr int OFF_K = OFF_Q + TILE_BYTES;
+constexpr int OFF_V = OFF_K + KV_STAGES * TILE_BYTES;
+constexpr int OFF_P = OFF_V + KV_STAGES * TILE_BYTES;
+constexpr int OFF_BAR = OFF_P + TILE_BYTES;
+constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024 /*align slack*/;
+constexpr int TMEM_COLS = 512;
+constexpr int TM_S = 0;      // S buffers at columns 0 and 128
+constexpr int TM_O = 256;
+
+DSB_DEVICE void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+        "r"(c3)
+        : "memory");
+}
+DSB_DEVICE void tma_store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+DSB_DEVICE void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+DSB_DEVICE void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+DSB_DEVICE float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256, 1)
+flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                 float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem + OFF_Q;
+    uint8_t* sK = smem + OFF_K;
+    uint8_t* sV = smem + OFF_V;
+    uint8_t* sP = smem + OFF_P;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BAR);
+    uint64_t* q_full = bars;            // [1]
+    uint64_t* kv_full = bars + 1;       // [2]
+    uint64_t* kv_empty = bars + 3;      // [2]
+    uint64_t* s_full = bars + 5;        // [2]
+    uint64_t* s_free = bars + 7;        // [2]
+    uint64_t* p_ready = bars + 9;       // [1]
+    uint64_t* pv_done = bars + 10;      // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int qb = gridDim.x - 1 - blockIdx.x;   // long (late) query blocks first
+    const int b = blockIdx.y / H, h = blockIdx.y - b * H;
+    const int q0 = qb * BQ;
+    const int nkv = causal ? qb + 1 : S / BKV;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmO);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(q_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&kv_full[i], 1);
+            mbar_init(&kv_empty[i], 1);
+            mbar_init(&s_full[i], 1);
+            mbar_init(&s_free[i], 4);
+        }
+        mbar_init(p_ready, 4);
+        mbar_init(pv_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (elect_one()) {
+            mbar_arrive_expect_tx(q_full, TILE_BYTES);
+            tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
+            tma_load_4d(sQ + CHUNK_BYTES, &tmQ, q_full, 64, h, q0, b);
+            for (int j = 0; j < nkv; ++j) {
+                const int st = j & 1;
+                if (j >= 2) mbar_wait(&kv_empty[st], ((j >> 1) - 1) & 1);
+                mbar_arrive_expect_tx(&kv_full[st], 2 * TILE_BYTES);
+                uint8_t* k = sK + st * TILE_BYTES;
+                uint8_t* v = sV + st * TILE_BYTES;
+                tma_load_4d(k, &tmK, &kv_full[st], 0, h, j * BKV, b);
+                tma_load_4d(k + CHUNK_BYTES, &tmK, &kv_full[st], 64, h, j * BKV, b);
+                tma_load_4d(v, &tmV, &kv_full[st], 0, h, j * BKV, b);
+                tma_load_4d(v + CHUNK_BYTES, &tmV, &kv_full[st], 64, h, j * BKV, b);
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (elect_one()) {
+            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+            const uint32_t idesc_s = make_idesc_f16(BQ, BKV, is_bf16, 0, 0);
+            const uint32_t idesc_pv = make_idesc_f16(BQ, HD, is_bf16, 0, 1);
+            constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t q_lo = ((smem_u32(sQ) & 0x3FFFF) >> 4) | (1u << 16);
+            const uint32_t p_lo = ((smem_u32(sP) & 0x3FFFF) >> 4) | (1u << 16);
+            auto issue_s = [&](int j) {
+                const uint32_t k_lo = (((smem_u32(sK) + (j & 1) * TILE_BYTES) & 0x3FFFF) >> 4) | (1u << 16);
+                const uint32_t d = tmem_base + TM_S + (j & 1) * BKV;
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k) {
+                    const uint32_t off = (k >> 2) * (CHUNK_BYTES >> 4) + (k & 3) * (32u >> 4);
+                    umma_f16_lohi(d, q_lo + off, k_lo + off, DESC_HI, idesc_s, k != 0);
+                }
+                umma_commit(&s_full[j & 1]);
+            };
+            auto issue_pv = [&](int j) {
+                // B = V tile read MN-major: 64-element d chunks CHUNK_BYTES apart (LBO), 16 key rows per k-step
+                const uint32_t v_lo = (((smem_u32(sV) + (j & 1) * TILE_BYTES) & 0x3FFFF) >> 4) |
+                                      ((uint32_t)(CHUNK_BYTES >> 4) << 16);
+#pragma unroll
+                for (int k = 0; k < BKV / 16; ++k) {
+                    const uint32_t a_off = (k >> 2) * (CHUNK_BYTES >> 4) + (k & 3) * (32u >> 4);
+                    umma_f16_lohi(tmem_base + TM_O, p_lo + a_off, v_lo + k * (2048u >> 4), DESC_HI, idesc_pv,
+                                  (j | k) != 0);
+                }
+                umma_commit(pv_done);
+                umma_commit(&kv_empty[j & 1]);
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_s(0);
+            for (int j = 0; j < nkv; ++j) {
+                if (j + 1 < nkv) {
+                    const int n = j + 1;
+                    mbar_wait(&kv_full[n & 1], (n >> 1) & 1);
+                    if (n >= 2) mbar_wait(&s_free[n & 1], ((n >> 1) - 1) & 1);
+                    tc_fence_after();
+                    issue_s(n);
+                }
+                mbar_wait(p_ready, j & 1);
+                tc_fence_after();
+                issue_pv(j);
+            }
+        }
+    } else if (warp >= 4) {
+        // ------------------------------------------------------------------ softmax / correction / epilogue
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const uint32_t lane_field = static_cast<uint32_t>(q * 32) << 16;
+        uint8_t* p_row = sP + row * 128;
+        const int sw = row & 7;
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < nkv; ++j) {
+            const int buf = j & 1;
+            const bool diag = causal && j == nkv - 1;
+            mbar_wait(&s_full[buf], (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t_s = tmem_base + lane_field + TM_S + buf * BKV;
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(t_s + c * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    float v = __uint_as_float(r[i]);
+                    if (diag && c * 32 + i > row) v = -INFINITY;
+                    mx = fmaxf(mx, v);
+                }
+            }
+            const float m_new = fmaxf(m_run, mx * scale_log2);
+            const float alpha = ex2(m_run - m_new);
+            if (j > 0) {
+                // O and the P buffer are free once the previous P V product has completed
+                mbar_wait(pv_done, (j - 1) & 1);
+                tc_fence_after();
+                const uint32_t t_o = tmem_base + lane_field + TM_O;
+#pragma unroll 1
+                for (int c = 0; c < 4; ++c) {
+                    uint32_t r[32];
+                    tmem_ld_32x32b_x32(t_o + c * 32, r);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                    tmem_st_32x32b_x32(t_o + c * 32, r);
+                }
+                tmem_st_wait();
+            }
+            float rs = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(t_s + c * 32, r);
+                tmem_ld_wait();
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    float p0 = ex2(__uint_as_float(r[i]) * scale_log2 - m_new);
+                    float p1 = ex2(__uint_as_float(r[i + 1]) * scale_log2 - m_new);
+                    if (diag && c * 32 + i > row) p0 = 0.f;
+                    if (diag && c * 32 + i + 1 > row) p1 = 0.f;
+                    rs += p0 + p1;
+                    pk[i >> 1] = Cvt<T>::pack2(p0, p1);
+                }
+                uint8_t* dst = p_row + (c >> 1) * CHUNK_BYTES;
+                const int u0 = (c & 1) * 4;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    *reinterpret_cast<uint4*>(dst + (((u0 + u) ^ sw) << 4)) =
+                        make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+            }
+            l_run = l_run * alpha + rs;
+            m_run = m_new;
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(&s_free[buf]);
+                mbar_arrive(p_ready);
+            }
+        }
+        // epilogue: O / l -> shared (same swizzled layout as P) -> TMA store; log-sum-exp for the backward pass
+        mbar_wait(pv_done, (nkv - 1) & 1);
+        tc_fence_after();
+        const float inv_l = 1.f / l_run;
+        const uint32_t t_o = tmem_base + lane_field + TM_O;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(t_o + c * 32, r);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+                pk[i >> 1] = Cvt<T>::pack2(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l);
+            uint8_t* dst = p_row + (c >> 1) * CHUNK_BYTES;
+            const int u0 = (c & 1) * 4;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                *reinterpret_cast<uint4*>(dst + (((u0 + u) ^ sw) << 4)) =
+                    make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+        }
+        if (lse != nullptr)
+            lse[((long)blockIdx.y) * S + q0 + row] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (warp == 4 && lane == 0) {
+            tma_store_4d(&tmO, sP, 0, h, q0, b);
+            tma_store_4d(&tmO, sP + CHUNK_BYTES, 64, h, q0, b);
+            tma_store_commit();
+            tma_store_wait<0>();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            return nullptr;
+        fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+// [B, S, H, D] tensor with element strides (sb, ss, sh, 1) as a 4-D map ordered (D, H, S, B); box = 64 x 1 x 128 x 1.
+static int make_map_bshd(CUtensorMap* m, int is_bf16, const void* base, int B, int S, int H, int D, long sb, long ss,
+                         long sh) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return -1;
+    cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)S, (cuuint64_t)B};
+    cuuint64_t strides[3] = {(cuuint64_t)sh * 2, (cuuint64_t)ss * 2, (cuuint64_t)sb * 2};
+    cuuint32_t box[4] = {64, 1, 128, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
+                     const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : -(int)r - 1000;
+}
+
+}  // namespace fa
+}  // namespace dsb
+
+// out[b, s, h, :] = softmax(scale * q[b, s, h, :] . k[b, :, h, :]^T (+ causal mask)) v[b, :, h, :]; lse (optional,
+// [B, H, S] fp32) receives the natural-log sum of exponentials of the scaled scores of every row.
+// q / k / v / out: [B, S, H, 128] with element strides (s*b, s*s, s*h, 1); S a multiple of 128.
+extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S,
+                                  int H, int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh,
+                                  long v_sb, long v_ss, long v_sh, long o_sb, long o_ss, long o_sh, float scale,
+                                  int causal, int dtype, void* stream_) {
+    using namespace dsb;
+    using namespace dsb::fa;
+    ensure_context_on_this_thread();
+    if (B <= 0 || S <= 0 || H <= 0) return 0;
+    if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
+    if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
+    const long strides[12] = {q_sb, q_ss, q_sh, k_sb, k_ss, k_sh, v_sb, v_ss, v_sh, o_sb, o_ss, o_sh};
+    for (int i = 0; i < 12; ++i)
+        if (strides[i] % 8) return DSB_ERR_ALIGN;
+    if ((reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v) |
+         reinterpret_cast<uintptr_t>(out)) & 15)
+        return DSB_ERR_ALIGN;
+    const int bf = dtype == DSB_DTYPE_BF16;
+    CUtensorMap tq, tk, tv, to;
+    int rc = make_map_bshd(&tq, bf, q, B, S, H, D, q_sb, q_ss, q_sh);
+    if (rc) return rc;
+    rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh);
+    if (rc) return rc;
+    rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh);
+    if (rc) return rc;
+    rc = make_map_bshd(&to, bf, out, B, S, H, D, o_sb, o_ss, o_sh);
+    if (rc) return rc;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    const float scale_log2 = scale * 1.4426950408889634f;
+    dim3 grid(S / BQ, B * H);
+    cudaError_t e;
+    if (bf) {
+        auto kern = flash_fwd_kernel<__nv_bfloat16>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 256, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+    } else {
+        auto kern = flash_fwd_kernel<__half>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 256, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+    }
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}

@@ -21,7 +21,33 @@ N.register_sigs({
                          _l, _p],
 })
 
+N.register_sigs({
+    "dsb_flash_attn_fwd": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _l, _l, _l, _l, _l, _l, _l, _l, _f, _i,
+                           _i, _p],
+})
+
 _tables = {}
+
+
+def flash_attn_fwd(q, k, v, causal=True, scale=None, out=None, return_lse=False):
+    """Flash-attention forward on the tcgen05 kernel (csrc/transformer/flash_attn.cu).
+    q, k, v: [B, S, H, 128] views (any batch / sequence / head strides that are multiples of 8 elements, unit last
+    stride; e.g. slices of the fused QKV activation), fp16 or bf16, S a multiple of 128.
+    Returns the context [B, S, H, 128] (contiguous unless `out` is given) and, if asked, the per-row log-sum-exp
+    [B, H, S] (fp32, natural log of the sum of exp(scaled scores))."""
+    B, S, H, D = q.shape
+    assert k.shape == q.shape and v.shape == q.shape and q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1
+    if scale is None:
+        scale = 1.0 / (D ** 0.5)
+    if out is None:
+        out = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
+    lse = torch.empty(B, H, S, dtype=torch.float32, device=q.device) if return_lse else None
+    N.check(N.cuda_lib().dsb_flash_attn_fwd(
+        N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(out), N.ptr(lse), B, S, H, D, q.stride(0), q.stride(1), q.stride(2),
+        k.stride(0), k.stride(1), k.stride(2), v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1),
+        out.stride(2), float(scale), int(causal), N.dtype_code(q.dtype), N.stream_ptr()), "dsb_flash_attn_fwd")
+    K._count()
+    return (out, lse) if return_lse else out
 
 
 def rotary_table(S, rot_dim, base, device):

@@ -95,6 +95,14 @@ int dsb_softmax_fwd(const void* x, const void* mask, void* y, int batch, int hea
 /* dx = y * (dy - sum(dy * y)) * scale. Reference: softmax_kernels.cu:433-577. */
 int dsb_softmax_bwd(const void* dy, const void* y, void* dx, long rows, int k_len, float scale, int dtype,
                     void* stream);
+/* Flash-attention forward on tcgen05 (head dim 128, S a multiple of 128): out = softmax(scale * q k^T (+ causal
+ * mask)) v per (batch, head), never materialising the [S, S] probabilities. q / k / v / out are [B, S, H, 128] with
+ * element strides (sb, ss, sh, 1) each (multiples of 8), so slices of a fused QKV activation are read in place.
+ * `lse` (optional, [B, H, S] fp32): natural-log sum of exponentials of the scaled scores, for a backward pass.
+ * Reference: the score / softmax / context chain of csrc/transformer/ds_transformer_cuda.cpp:186-214. */
+int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
+                       long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss,
+                       long v_sh, long o_sb, long o_ss, long o_sh, float scale, int causal, int dtype, void* stream);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */
 int dsb_bias_gelu_fwd(const void* x, const void* bias, void* y, long rows, int cols, int dtype, void* stream);
 int dsb_bias_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, long rows, int cols, int dtype,

@@ -515,3 +515,25 @@ def test_collective_gemm_variants_single_rank():
         ref = 0.5 * (go.float().t() @ x.float())
         torch.cuda.synchronize()
         assert ((dw.float() - ref).abs().max() / ref.abs().max()).item() < 3e-3
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_flash_attention_forward(causal, dtype):
+    """tcgen05 flash-attention forward vs fp32 softmax(QK^T)V, on strided views of a fused QKV buffer."""
+    from deeperspeed_b200.ops.attention import flash_attn_fwd
+    torch.manual_seed(0)
+    B, S, H, D = 2, 640, 3, 128
+    qkv = torch.randn(B, S, 3, H, D, device="cuda", dtype=dtype)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    out, lse = flash_attn_fwd(q, k, v, causal=causal, return_lse=True)
+    torch.cuda.synchronize()
+    qf, kf, vf = (t.float().transpose(1, 2) for t in (q, k, v))      # [B, H, S, D]
+    scores = qf @ kf.transpose(-1, -2) / D ** 0.5
+    if causal:
+        scores = scores.masked_fill(torch.triu(torch.ones(S, S, dtype=torch.bool, device="cuda"), 1), float("-inf"))
+    ref = (torch.softmax(scores, -1) @ vf).transpose(1, 2)
+    tol = 4e-3 if dtype == torch.float16 else 2e-2
+    assert out.shape == (B, S, H, D) and out.is_contiguous()
+    assert (out.float() - ref).abs().max().item() < tol, (out.float() - ref).abs().max().item()
+    assert (lse - torch.logsumexp(scores, -1)).abs().max().item() < 2e-3
