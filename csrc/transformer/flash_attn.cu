@@ -307,6 +307,258 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------ backward
+// delta[b, h, s] = sum_d dO[b, s, h, d] * O[b, s, h, d] (fp32); one warp per row of 128 elements.
+template <typename T>
+__global__ void __launch_bounds__(256) flash_delta_kernel(const T* __restrict__ dO, const T* __restrict__ O,
+                                                          float* __restrict__ delta, int B, int S, int H, long do_sb,
+                                                          long do_ss, long do_sh, long o_sb, long o_ss, long o_sh) {
+    const long rows = (long)B * S * H;
+    const int lane = threadIdx.x & 31;
+    for (long r = (long)blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += (long)gridDim.x * 8) {
+        const int h = (int)(r % H);
+        const long t = r / H;
+        const int s = (int)(t % S);
+        const int b = (int)(t / S);
+        const uint2 a = *reinterpret_cast<const uint2*>(dO + b * do_sb + s * do_ss + h * do_sh + lane * 4);
+        const uint2 c = *reinterpret_cast<const uint2*>(O + b * o_sb + s * o_ss + h * o_sh + lane * 4);
+        const float2 a0 = Cvt<T>::unpack2(a.x), a1 = Cvt<T>::unpack2(a.y);
+        const float2 c0 = Cvt<T>::unpack2(c.x), c1 = Cvt<T>::unpack2(c.y);
+        float v = a0.x * c0.x + a0.y * c0.y + a1.x * c1.x + a1.y * c1.y;
+        v = warp_sum(v);
+        if (lane == 0) delta[((long)b * H + h) * S + s] = v;
+    }
+}
+
+constexpr int B_OFF_K = 0;
+constexpr int B_OFF_V = B_OFF_K + TILE_BYTES;
+constexpr int B_OFF_Q = B_OFF_V + TILE_BYTES;
+constexpr int B_OFF_DO = B_OFF_Q + TILE_BYTES;
+constexpr int B_OFF_P = B_OFF_DO + TILE_BYTES;
+constexpr int B_OFF_DS = B_OFF_P + TILE_BYTES;
+constexpr int B_OFF_BAR = B_OFF_DS + TILE_BYTES;
+constexpr int B_SMEM_BYTES = B_OFF_BAR + 256 + 1024;
+constexpr int TM_DP = 128, TM_DV = 256, TM_DK = 384;
+
+DSB_DEVICE void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// One CTA per (key block j, batch, head): K_j / V_j stay in shared memory, the CTA walks the query blocks i >= j
+// (causal) and per block issues five UMMAs: S = Q K^T and dP = dO V^T (TMEM), then - once the softmax warps have
+// turned them into P and dS in shared memory - dV += P^T dO, dK += dS^T Q (accumulated in TMEM over the whole walk;
+// P and dS are read MN-major, i.e. transposed for free) and dQ_i = dS K into the TMEM columns S has vacated. dQ_i is
+// added to an fp32 accumulator in global memory with vector reductions (other key blocks add to the same rows).
+template <typename T>
+__global__ void __launch_bounds__(256, 1)
+flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                 const __grid_constant__ CUtensorMap tmdK, const __grid_constant__ CUtensorMap tmdV,
+                 const float* __restrict__ lse, const float* __restrict__ delta, float* __restrict__ dq_acc, int S,
+                 int H, float scale, float scale_log2, int causal) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sK = smem + B_OFF_K;
+    uint8_t* sV = smem + B_OFF_V;
+    uint8_t* sQ = smem + B_OFF_Q;
+    uint8_t* sdO = smem + B_OFF_DO;
+    uint8_t* sP = smem + B_OFF_P;
+    uint8_t* sdS = smem + B_OFF_DS;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + B_OFF_BAR);
+    uint64_t* kv_full = bars;          // K_j, V_j landed
+    uint64_t* qdo_full = bars + 1;     // Q_i, dO_i landed
+    uint64_t* sdp_full = bars + 2;     // S and dP are in TMEM
+    uint64_t* pds_ready = bars + 3;    // P and dS are in shared memory (4 warps)
+    uint64_t* mma2_done = bars + 4;    // dV, dK, dQ UMMAs of this query block completed
+    uint64_t* s_free = bars + 5;       // dQ drained from TMEM (4 warps)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int jb = blockIdx.x;
+    const int b = blockIdx.y / H, h = blockIdx.y - b * H;
+    const int nq = S / BQ;
+    const int i0 = causal ? jb : 0;
+    const int nit = nq - i0;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmdO);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(kv_full, 1);
+        mbar_init(qdo_full, 1);
+        mbar_init(sdp_full, 1);
+        mbar_init(pds_ready, 4);
+        mbar_init(mma2_done, 1);
+        mbar_init(s_free, 4);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            mbar_arrive_expect_tx(kv_full, 2 * TILE_BYTES);
+            tma_load_4d(sK, &tmK, kv_full, 0, h, jb * BKV, b);
+            tma_load_4d(sK + CHUNK_BYTES, &tmK, kv_full, 64, h, jb * BKV, b);
+            tma_load_4d(sV, &tmV, kv_full, 0, h, jb * BKV, b);
+            tma_load_4d(sV + CHUNK_BYTES, &tmV, kv_full, 64, h, jb * BKV, b);
+            for (int it = 0; it < nit; ++it) {
+                if (it > 0) mbar_wait(mma2_done, (it - 1) & 1);   // every reader of Q_i / dO_i is done
+                const int q0 = (i0 + it) * BQ;
+                mbar_arrive_expect_tx(qdo_full, 2 * TILE_BYTES);
+                tma_load_4d(sQ, &tmQ, qdo_full, 0, h, q0, b);
+                tma_load_4d(sQ + CHUNK_BYTES, &tmQ, qdo_full, 64, h, q0, b);
+                tma_load_4d(sdO, &tmdO, qdo_full, 0, h, q0, b);
+                tma_load_4d(sdO + CHUNK_BYTES, &tmdO, qdo_full, 64, h, q0, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+            const uint32_t id_kk = make_idesc_f16(128, 128, is_bf16, 0, 0);   // both operands K-major
+            const uint32_t id_mm = make_idesc_f16(128, 128, is_bf16, 1, 1);   // both MN-major (transposed reads)
+            const uint32_t id_km = make_idesc_f16(128, 128, is_bf16, 0, 1);
+            constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+            constexpr uint32_t LBO_MN = (uint32_t)(CHUNK_BYTES >> 4) << 16;
+            auto kmaj = [](const uint8_t* p) { return ((smem_u32(p) & 0x3FFFF) >> 4) | (1u << 16); };
+            auto mnmaj = [](const uint8_t* p) { return ((smem_u32(p) & 0x3FFFF) >> 4) | LBO_MN; };
+            auto koff = [](int k) { return (uint32_t)((k >> 2) * (CHUNK_BYTES >> 4) + (k & 3) * 2); };
+            mbar_wait(kv_full, 0);
+            for (int it = 0; it < nit; ++it) {
+                mbar_wait(qdo_full, it & 1);
+                if (it > 0) mbar_wait(s_free, (it - 1) & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_f16_lohi(tmem_base + TM_S, kmaj(sQ) + koff(k), kmaj(sK) + koff(k), DESC_HI, id_kk, k != 0);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_f16_lohi(tmem_base + TM_DP, kmaj(sdO) + koff(k), kmaj(sV) + koff(k), DESC_HI, id_kk, k != 0);
+                umma_commit(sdp_full);
+                mbar_wait(pds_ready, it & 1);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < 8; ++k)   // dV[kv, d] += sum_q P[q, kv] dO[q, d]
+                    umma_f16_lohi(tmem_base + TM_DV, mnmaj(sP) + k * (2048u >> 4), mnmaj(sdO) + k * (2048u >> 4),
+                                  DESC_HI, id_mm, (it | k) != 0);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)   // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
+                    umma_f16_lohi(tmem_base + TM_DK, mnmaj(sdS) + k * (2048u >> 4), mnmaj(sQ) + k * (2048u >> 4),
+                                  DESC_HI, id_mm, (it | k) != 0);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)   // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
+                    umma_f16_lohi(tmem_base + TM_S, kmaj(sdS) + koff(k), mnmaj(sK) + k * (2048u >> 4), DESC_HI, id_km,
+                                  k != 0);
+                umma_commit(mma2_done);
+            }
+        }
+    } else if (warp >= 4) {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const uint32_t lane_field = static_cast<uint32_t>(q * 32) << 16;
+        const int sw = row & 7;
+        const long bh = blockIdx.y;
+        for (int it = 0; it < nit; ++it) {
+            const int q0 = (i0 + it) * BQ;
+            const bool diag = causal && it == 0;
+            const float lse2 = lse[bh * S + q0 + row] * 1.4426950408889634f;
+            const float dl = delta[bh * S + q0 + row];
+            mbar_wait(sdp_full, it & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t rs[32], rp[32];
+                tmem_ld_32x32b_x32(tmem_base + lane_field + TM_S + c * 32, rs);
+                tmem_ld_32x32b_x32(tmem_base + lane_field + TM_DP + c * 32, rp);
+                tmem_ld_wait();
+                uint32_t pk[16], dk[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) {
+                    float p0 = ex2(__uint_as_float(rs[i]) * scale_log2 - lse2);
+                    float p1 = ex2(__uint_as_float(rs[i + 1]) * scale_log2 - lse2);
+                    if (diag && c * 32 + i > row) p0 = 0.f;
+                    if (diag && c * 32 + i + 1 > row) p1 = 0.f;
+                    const float d0 = p0 * (__uint_as_float(rp[i]) - dl) * scale;
+                    const float d1 = p1 * (__uint_as_float(rp[i + 1]) - dl) * scale;
+                    pk[i >> 1] = Cvt<T>::pack2(p0, p1);
+                    dk[i >> 1] = Cvt<T>::pack2(d0, d1);
+                }
+                const int off = (c >> 1) * CHUNK_BYTES + row * 128;
+                const int u0 = (c & 1) * 4;
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int o = off + (((u0 + u) ^ sw) << 4);
+                    *reinterpret_cast<uint4*>(sP + o) = make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+                    *reinterpret_cast<uint4*>(sdS + o) = make_uint4(dk[u * 4], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]);
+                }
+            }
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(pds_ready);
+            // dQ_i of this key block -> fp32 accumulator
+            mbar_wait(mma2_done, it & 1);
+            tc_fence_after();
+            float* dq_row = dq_acc + (((long)b * S + q0 + row) * H + h) * HD;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(tmem_base + lane_field + TM_S + c * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; i += 4)
+                    red_add_v4(dq_row + c * 32 + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]),
+                               __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_free);
+        }
+        // dV, dK (TMEM lane = key row) -> shared (P / dS buffers are free) -> TMA store
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {
+            uint8_t* stage = which == 0 ? sP : sdS;
+            const uint32_t t_acc = tmem_base + lane_field + (which == 0 ? TM_DV : TM_DK);
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(t_acc + c * 32, r);
+                tmem_ld_wait();
+                uint32_t pk[16];
+#pragma unroll
+                for (int i = 0; i < 32; i += 2) pk[i >> 1] = Cvt<T>::pack2(__uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+                uint8_t* dst = stage + (c >> 1) * CHUNK_BYTES + row * 128;
+                const int u0 = (c & 1) * 4;
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    *reinterpret_cast<uint4*>(dst + (((u0 + u) ^ sw) << 4)) =
+                        make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+            }
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (warp == 4 && lane == 0) {
+            tma_store_4d(&tmdV, sP, 0, h, jb * BKV, b);
+            tma_store_4d(&tmdV, sP + CHUNK_BYTES, 64, h, jb * BKV, b);
+            tma_store_4d(&tmdK, sdS, 0, h, jb * BKV, b);
+            tma_store_4d(&tmdK, sdS + CHUNK_BYTES, 64, h, jb * BKV, b);
+            tma_store_commit();
+            tma_store_wait<0>();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -383,6 +635,62 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 256, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+    }
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+// Backward of dsb_flash_attn_fwd. dO / q / k / v / out / dk / dv: [B, S, H, 128] with their own element strides (unit
+// last stride, multiples of 8). lse: [B, H, S] from the forward. delta: [B, H, S] fp32 scratch. dq_acc: [B, S, H, 128]
+// fp32, contiguous, ZEROED by the caller; it receives dQ (key blocks add their contributions with reductions).
+extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                                  const float* lse, float* delta, float* dq_acc, void* dk, void* dv, int B, int S,
+                                  int H, int D, const long* strides /* 7 x (sb, ss, sh): dO q k v out dk dv */,
+                                  float scale, int causal, int dtype, void* stream_) {
+    using namespace dsb;
+    using namespace dsb::fa;
+    ensure_context_on_this_thread();
+    if (B <= 0 || S <= 0 || H <= 0) return 0;
+    if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
+    if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
+    for (int i = 0; i < 21; ++i)
+        if (strides[i] % 8) return DSB_ERR_ALIGN;
+    const int bf = dtype == DSB_DTYPE_BF16;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    const long* s_do = strides, *s_q = strides + 3, *s_k = strides + 6, *s_v = strides + 9, *s_o = strides + 12,
+               *s_dk = strides + 15, *s_dv = strides + 18;
+    const long rows = (long)B * S * H;
+    int grid_d = (int)((rows + 7) / 8 < 148L * 16 ? (rows + 7) / 8 : 148L * 16);
+    if (bf)
+        flash_delta_kernel<__nv_bfloat16><<<grid_d, 256, 0, stream>>>((const __nv_bfloat16*)dO, (const __nv_bfloat16*)out, delta, B, S, H, s_do[0], s_do[1], s_do[2], s_o[0], s_o[1], s_o[2]);
+    else
+        flash_delta_kernel<__half><<<grid_d, 256, 0, stream>>>((const __half*)dO, (const __half*)out, delta, B, S, H, s_do[0], s_do[1], s_do[2], s_o[0], s_o[1], s_o[2]);
+    CUtensorMap tq, tk, tv, tdo, tdk, tdv;
+    int rc = make_map_bshd(&tq, bf, q, B, S, H, D, s_q[0], s_q[1], s_q[2]);
+    if (rc) return rc;
+    rc = make_map_bshd(&tk, bf, k, B, S, H, D, s_k[0], s_k[1], s_k[2]);
+    if (rc) return rc;
+    rc = make_map_bshd(&tv, bf, v, B, S, H, D, s_v[0], s_v[1], s_v[2]);
+    if (rc) return rc;
+    rc = make_map_bshd(&tdo, bf, dO, B, S, H, D, s_do[0], s_do[1], s_do[2]);
+    if (rc) return rc;
+    rc = make_map_bshd(&tdk, bf, dk, B, S, H, D, s_dk[0], s_dk[1], s_dk[2]);
+    if (rc) return rc;
+    rc = make_map_bshd(&tdv, bf, dv, B, S, H, D, s_dv[0], s_dv[1], s_dv[2]);
+    if (rc) return rc;
+    const float scale_log2 = scale * 1.4426950408889634f;
+    dim3 grid(S / BKV, B * H);
+    cudaError_t e;
+    if (bf) {
+        auto kern = flash_bwd_kernel<__nv_bfloat16>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM_BYTES);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 256, B_SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdk, tdv, lse, delta, dq_acc, S, H, scale, scale_log2, causal);
+    } else {
+        auto kern = flash_bwd_kernel<__half>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM_BYTES);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 256, B_SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdk, tdv, lse, delta, dq_acc, S, H, scale, scale_log2, causal);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

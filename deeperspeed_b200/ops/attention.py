@@ -26,7 +26,35 @@ N.register_sigs({
                            _i, _p],
 })
 
+N.register_sigs({
+    "dsb_flash_attn_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p],
+})
+
 _tables = {}
+
+
+def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv=None):
+    """Backward of `flash_attn_fwd` on the tcgen05 kernel. All tensors [B, S, H, 128] views with unit last stride
+    (dk / dv may be slices of a fused dQKV buffer). Returns (dq fp32 [B, S, H, 128] contiguous, dk, dv): dq is
+    accumulated in fp32 across key blocks and left to the caller to cast (the inverse rotary / cast that follows)."""
+    B, S, H, D = q.shape
+    if scale is None:
+        scale = 1.0 / (D ** 0.5)
+    if dk is None:
+        dk = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
+    if dv is None:
+        dv = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
+    dq_acc = torch.zeros(B, S, H, D, dtype=torch.float32, device=q.device)
+    delta = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
+    ts = (dout, q, k, v, out, dk, dv)
+    assert all(t.stride(-1) == 1 and t.shape == q.shape for t in ts)
+    strides = (C.c_long * 21)(*[t.stride(i) for t in ts for i in range(3)])
+    N.check(N.cuda_lib().dsb_flash_attn_bwd(N.ptr(dout), N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(out), N.ptr(lse),
+                                            N.ptr(delta), N.ptr(dq_acc), N.ptr(dk), N.ptr(dv), B, S, H, D, strides,
+                                            float(scale), int(causal), N.dtype_code(q.dtype), N.stream_ptr()),
+            "dsb_flash_attn_bwd")
+    K._count(2)
+    return dq_acc, dk, dv
 
 
 def flash_attn_fwd(q, k, v, causal=True, scale=None, out=None, return_lse=False):

@@ -103,6 +103,13 @@ int dsb_softmax_bwd(const void* dy, const void* y, void* dx, long rows, int k_le
 int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
                        long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss,
                        long v_sh, long o_sb, long o_ss, long o_sh, float scale, int causal, int dtype, void* stream);
+/* Backward of dsb_flash_attn_fwd: one CTA per (key block, batch, head) keeps K / V resident, walks the query blocks
+ * and accumulates dV, dK in TMEM; dQ contributions are added to `dq_acc` ([B, S, H, 128] fp32, contiguous, zeroed by
+ * the caller) with vector reductions. `strides`: 7 x (sb, ss, sh) for dO, q, k, v, out, dk, dv. `delta`: [B, H, S]
+ * fp32 scratch (rowsum(dO * O), computed here). */
+int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, const void* v, const void* out, const float* lse,
+                       float* delta, float* dq_acc, void* dk, void* dv, int B, int S, int H, int D,
+                       const long* strides, float scale, int causal, int dtype, void* stream);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */
 int dsb_bias_gelu_fwd(const void* x, const void* bias, void* y, long rows, int cols, int dtype, void* stream);
 int dsb_bias_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, long rows, int cols, int dtype,

@@ -537,3 +537,29 @@ def test_flash_attention_forward(causal, dtype):
     assert out.shape == (B, S, H, D) and out.is_contiguous()
     assert (out.float() - ref).abs().max().item() < tol, (out.float() - ref).abs().max().item()
     assert (lse - torch.logsumexp(scores, -1)).abs().max().item() < 2e-3
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_flash_attention_backward(causal, dtype):
+    """tcgen05 flash-attention backward vs autograd through fp32 softmax(QK^T)V."""
+    from deeperspeed_b200.ops.attention import flash_attn_fwd, flash_attn_bwd
+    torch.manual_seed(1)
+    B, S, H, D = 2, 512, 3, 128
+    qkv = torch.randn(B, S, 3, H, D, device="cuda", dtype=dtype)
+    q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
+    out, lse = flash_attn_fwd(q, k, v, causal=causal, return_lse=True)
+    dout = torch.randn(B, S, H, D, device="cuda", dtype=dtype)
+    dqkv = torch.empty_like(qkv)
+    dq, dk, dv = flash_attn_bwd(dout, q, k, v, out, lse, causal=causal, dk=dqkv[:, :, 1], dv=dqkv[:, :, 2])
+    torch.cuda.synchronize()
+    qf, kf, vf = (t.float().detach().requires_grad_() for t in (q, k, v))
+    scores = qf.transpose(1, 2) @ kf.transpose(1, 2).transpose(-1, -2) / D ** 0.5
+    if causal:
+        scores = scores.masked_fill(torch.triu(torch.ones(S, S, dtype=torch.bool, device="cuda"), 1), float("-inf"))
+    ref = (torch.softmax(scores, -1) @ vf.transpose(1, 2)).transpose(1, 2)
+    rq, rk, rv = torch.autograd.grad(ref, (qf, kf, vf), dout.float())
+    tol = 2e-2 if dtype == torch.float16 else 8e-2
+    for name, got, want in (("dq", dq, rq), ("dk", dk.float(), rk), ("dv", dv.float(), rv)):
+        err = (got - want).abs().max().item()
+        assert err < tol * max(1.0, want.abs().max().item()), (name, err, want.abs().max().item())
