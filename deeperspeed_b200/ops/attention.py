@@ -1,11 +1,19 @@
 """Causal self-attention block op for decoder models: fused-QKV in, context out.
 
 forward : rotary (our vectorised out-of-place kernel, reads q/k straight from the fused QKV activation) -> causal
-          flash attention (library SDPA) -> context [B, S, h]
+          flash attention -> context [B, S, h]
 backward: attention backward -> inverse rotary written DIRECTLY into the dQKV buffer (no slice-backward zero fills,
           no gradient-accumulation adds, no clones).
+
+Two attention back ends, selected with DSB_ATTN (or `set_attention_backend`):
+  "native": the tcgen05 flash-attention kernels of csrc/transformer/flash_attn.cu (forward + backward, V read in place
+            from the fused activation, dV written in place into the dQKV buffer);
+  "sdpa"  : the library flash kernel behind torch SDPA. Default, because it is the faster one today
+            (bench/flash_attn_bench.py: 0.072 / 0.237 ms vs 0.156 / 0.448 ms forward / backward at batch 4 x 16 heads x
+            seq 2048); the native path needs head dim 128 and seq % 128 == 0 and falls back to "sdpa" otherwise.
 """
 import ctypes as C
+import os
 
 import torch
 import torch.nn.functional as F
@@ -112,6 +120,64 @@ def rotary_oop(q_in, k_in, q_out, k_out, rot_dim, base, inverse=False, v_in=None
     K._count()
 
 
+_BACKEND = os.environ.get("DSB_ATTN", "sdpa").lower()
+
+
+def set_attention_backend(name):
+    """"native" (tcgen05 flash-attention kernels) or "sdpa" (library kernel). Returns the previous setting."""
+    global _BACKEND
+    assert name in ("native", "sdpa")
+    prev, _BACKEND = _BACKEND, name
+    return prev
+
+
+def attention_backend():
+    return _BACKEND
+
+
+class NativeCausalSelfAttentionFn(torch.autograd.Function):
+    """Same contract as CausalSelfAttentionFn with the attention itself on our tcgen05 kernels."""
+
+    @staticmethod
+    def forward(ctx, qkv, H, D, rot_dim, base):
+        B, S = qkv.shape[0], qkv.shape[1]
+        qkv5 = qkv.view(B, S, 3, H, D)
+        if rot_dim > 0:
+            q = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
+            k = torch.empty_like(q)
+            rotary_oop(qkv5[:, :, 0], qkv5[:, :, 1], q, k, rot_dim, base)
+        else:
+            q, k = qkv5[:, :, 0], qkv5[:, :, 1]
+        out, lse = flash_attn_fwd(q, k, qkv5[:, :, 2], causal=True, return_lse=True)
+        ctx.save_for_backward(qkv, q if rot_dim > 0 else None, k if rot_dim > 0 else None, out, lse)
+        ctx.meta = (B, S, H, D, rot_dim, base)
+        return out.view(B, S, H * D)
+
+    @staticmethod
+    def backward(ctx, dctx):
+        qkv, q, k, out, lse = ctx.saved_tensors
+        B, S, H, D, rot_dim, base = ctx.meta
+        qkv5 = qkv.view(B, S, 3, H, D)
+        if q is None:
+            q, k = qkv5[:, :, 0], qkv5[:, :, 1]
+        dout = dctx.reshape(B, S, H, D)
+        if dout.stride(-1) != 1 or any(st % 8 for st in dout.stride()[:3]):
+            dout = dout.contiguous()
+        dqkv = torch.empty(B, S, 3, H, D, dtype=qkv.dtype, device=qkv.device)
+        if rot_dim > 0:
+            dk_tmp = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
+            dq32, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dk_tmp,
+                                        dv=dqkv[:, :, 2])
+            dq = torch.empty_like(dk_tmp)
+            K.cast(dq32, dq)
+            rotary_oop(dq, dk_tmp, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
+        else:
+            dq32, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dqkv[:, :, 1],
+                                        dv=dqkv[:, :, 2])
+            dqkv[:, :, 0].copy_(dq32)
+        return dqkv.view(B, S, 3 * H * D), None, None, None, None
+
+
 class CausalSelfAttentionFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv, H, D, rot_dim, base):
@@ -162,6 +228,8 @@ def causal_self_attention(qkv, H, D, rot_dim, base=10000.0):
     """qkv: [B, S, 3*H*D] laid out (3, H, D). Returns the attention context [B, S, H*D]."""
     if qkv.is_cuda and qkv.dtype in (torch.float16, torch.bfloat16) and D % 8 == 0 and (rot_dim % 16 == 0):
         N.cuda_lib()
+        if _BACKEND == "native" and D == 128 and qkv.shape[1] % 128 == 0:
+            return NativeCausalSelfAttentionFn.apply(qkv.contiguous(), H, D, rot_dim, base)
         return CausalSelfAttentionFn.apply(qkv.contiguous(), H, D, rot_dim, base)
     B, S = qkv.shape[0], qkv.shape[1]
     t = qkv.view(B, S, 3, H, D)

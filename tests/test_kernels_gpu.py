@@ -563,3 +563,32 @@ def test_flash_attention_backward(causal, dtype):
     for name, got, want in (("dq", dq, rq), ("dk", dk.float(), rk), ("dv", dv.float(), rv)):
         err = (got - want).abs().max().item()
         assert err < tol * max(1.0, want.abs().max().item()), (name, err, want.abs().max().item())
+
+
+@pytest.mark.parametrize("rot", [128, 32, 0])
+def test_causal_self_attention_op_native_backend(rot):
+    """The attention block op on the tcgen05 flash-attention kernels (rotary in, inverse rotary out, dV written
+    straight into the dQKV buffer) against the fp32 reference of the same block."""
+    from deeperspeed_b200.ops import attention as A
+    prev = A.set_attention_backend("native")
+    try:
+        torch.manual_seed(13)
+        B, S, H, D = 2, 384, 3, 128
+        qkv = (torch.randn(B, S, 3 * H * D, device=DEV, dtype=torch.float16) * 0.5).requires_grad_()
+        out = A.causal_self_attention(qkv, H, D, rot_dim=rot)
+        assert out.grad_fn is not None and "Native" in type(out.grad_fn).__name__
+        g = torch.randn_like(out)
+        out.backward(g)
+    finally:
+        A.set_attention_backend(prev)
+    ref_in = qkv.detach().float().cpu().requires_grad_()
+    t = ref_in.view(B, S, 3, H, D)
+    q, k = t[:, :, 0], t[:, :, 1]
+    if rot > 0:
+        q, k = K._rotary_ref(q, k, rot, 10000.0, False)
+    ctx = torch.nn.functional.scaled_dot_product_attention(q.transpose(1, 2), k.transpose(1, 2), t[:, :, 2].transpose(1, 2),
+                                                           is_causal=True)
+    ref = ctx.transpose(1, 2).reshape(B, S, H * D)
+    ref.backward(g.float().cpu())
+    assert _rel(out.cpu(), ref) < 5e-3
+    assert _rel(qkv.grad.cpu(), ref_in.grad) < 1e-2
