@@ -36,7 +36,8 @@ constexpr int OFF_K = OFF_Q + TILE_BYTES;
 constexpr int OFF_V = OFF_K + KV_STAGES * TILE_BYTES;
 constexpr int OFF_P = OFF_V + KV_STAGES * TILE_BYTES;
 constexpr int OFF_BAR = OFF_P + TILE_BYTES;
-constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024 /*align slack*/;
+constexpr int OFF_XCH = OFF_BAR + 256;
+constexpr int SMEM_BYTES = OFF_XCH + 2048 + 1024 /*align slack*/;
 constexpr int TMEM_COLS = 512;
 constexpr int TM_S = 0;      // S buffers at columns 0 and 128
 constexpr int TM_O = 256;
@@ -73,7 +74,7 @@ DSB_DEVICE float ex2(float x) {
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(384, 1)
 flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                  float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
@@ -92,6 +93,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     uint64_t* p_ready = bars + 9;       // [1]
     uint64_t* pv_done = bars + 10;      // [1]
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    float* xch = reinterpret_cast<float*>(smem + OFF_XCH);   // [2 parities][2 halves][128 rows] partial row maxima / sums
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
@@ -112,9 +114,9 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             mbar_init(&kv_full[i], 1);
             mbar_init(&kv_empty[i], 1);
             mbar_init(&s_full[i], 1);
-            mbar_init(&s_free[i], 4);
+            mbar_init(&s_free[i], 8);
         }
-        mbar_init(p_ready, 4);
+        mbar_init(p_ready, 8);
         mbar_init(pv_done, 1);
         fence_barrier_init();
     }
@@ -193,7 +195,12 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         }
     } else if (warp >= 4) {
         // ------------------------------------------------------------------ softmax / correction / epilogue
+        // Eight warps: warp w owns TMEM lane quarter w % 4 (32 query rows) and one half of the 128 columns, so a row
+        // is shared by two threads; they exchange their partial row maximum through shared memory once per key block
+        // and their partial row sums once at the end (both use the same running maximum).
         const int q = warp & 3;
+        const int half = (warp - 4) >> 2;
+        const int c_lo = half * 2;
         const int row = q * 32 + lane;
         const uint32_t lane_field = static_cast<uint32_t>(q * 32) << 16;
         uint8_t* p_row = sP + row * 128;
@@ -207,7 +214,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             const uint32_t t_s = tmem_base + lane_field + TM_S + buf * BKV;
             float mx = -INFINITY;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = c_lo; c < c_lo + 2; ++c) {
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(t_s + c * 32, r);
                 tmem_ld_wait();
@@ -218,6 +225,10 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                     mx = fmaxf(mx, v);
                 }
             }
+            float* xm = xch + (j & 1) * 256;
+            xm[half * 128 + row] = mx;
+            named_bar_sync(2, 256);
+            mx = fmaxf(mx, xm[(half ^ 1) * 128 + row]);
             const float m_new = fmaxf(m_run, mx * scale_log2);
             const float alpha = ex2(m_run - m_new);
             if (j > 0) {
@@ -225,20 +236,22 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                 mbar_wait(pv_done, (j - 1) & 1);
                 tc_fence_after();
                 const uint32_t t_o = tmem_base + lane_field + TM_O;
+                if (!__all_sync(0xffffffffu, alpha == 1.f)) {   // the running maxima of these 32 rows moved
 #pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    uint32_t r[32];
-                    tmem_ld_32x32b_x32(t_o + c * 32, r);
-                    tmem_ld_wait();
+                    for (int c = c_lo; c < c_lo + 2; ++c) {
+                        uint32_t r[32];
+                        tmem_ld_32x32b_x32(t_o + c * 32, r);
+                        tmem_ld_wait();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-                    tmem_st_32x32b_x32(t_o + c * 32, r);
+                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                        tmem_st_32x32b_x32(t_o + c * 32, r);
+                    }
+                    tmem_st_wait();
                 }
-                tmem_st_wait();
             }
             float rs = 0.f;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = c_lo; c < c_lo + 2; ++c) {
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(t_s + c * 32, r);
                 tmem_ld_wait();
@@ -272,10 +285,14 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         // epilogue: O / l -> shared (same swizzled layout as P) -> TMA store; log-sum-exp for the backward pass
         mbar_wait(pv_done, (nkv - 1) & 1);
         tc_fence_after();
+        float* xl = xch + (nkv & 1) * 256;
+        xl[half * 128 + row] = l_run;
+        named_bar_sync(2, 256);
+        l_run += xl[(half ^ 1) * 128 + row];
         const float inv_l = 1.f / l_run;
         const uint32_t t_o = tmem_base + lane_field + TM_O;
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = c_lo; c < c_lo + 2; ++c) {
             uint32_t r[32];
             tmem_ld_32x32b_x32(t_o + c * 32, r);
             tmem_ld_wait();
@@ -290,10 +307,10 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                 *reinterpret_cast<uint4*>(dst + (((u0 + u) ^ sw) << 4)) =
                     make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
         }
-        if (lse != nullptr)
+        if (lse != nullptr && half == 0)
             lse[((long)blockIdx.y) * S + q0 + row] = (m_run + log2f(l_run)) * 0.6931471805599453f;
         fence_proxy_async_smem();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 256);
         if (warp == 4 && lane == 0) {
             tma_store_4d(&tmO, sP, 0, h, q0, b);
             tma_store_4d(&tmO, sP + CHUNK_BYTES, 64, h, q0, b);
@@ -350,7 +367,7 @@ DSB_DEVICE void red_add_v4(float* p, float a, float b, float c, float d) {
 // P and dS are read MN-major, i.e. transposed for free) and dQ_i = dS K into the TMEM columns S has vacated. dQ_i is
 // added to an fp32 accumulator in global memory with vector reductions (other key blocks add to the same rows).
 template <typename T>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(384, 1)
 flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
                  const __grid_constant__ CUtensorMap tmdK, const __grid_constant__ CUtensorMap tmdV,
@@ -368,9 +385,9 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     uint64_t* kv_full = bars;          // K_j, V_j landed
     uint64_t* qdo_full = bars + 1;     // Q_i, dO_i landed
     uint64_t* sdp_full = bars + 2;     // S and dP are in TMEM
-    uint64_t* pds_ready = bars + 3;    // P and dS are in shared memory (4 warps)
+    uint64_t* pds_ready = bars + 3;    // P and dS are in shared memory (8 warps)
     uint64_t* mma2_done = bars + 4;    // dV, dK, dQ UMMAs of this query block completed
-    uint64_t* s_free = bars + 5;       // dQ drained from TMEM (4 warps)
+    uint64_t* s_free = bars + 5;       // dQ drained from TMEM (8 warps)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
@@ -391,9 +408,9 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         mbar_init(kv_full, 1);
         mbar_init(qdo_full, 1);
         mbar_init(sdp_full, 1);
-        mbar_init(pds_ready, 4);
+        mbar_init(pds_ready, 8);
         mbar_init(mma2_done, 1);
-        mbar_init(s_free, 4);
+        mbar_init(s_free, 8);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -460,7 +477,10 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             }
         }
     } else if (warp >= 4) {
+        // eight warps: warp w works on TMEM lane quarter w % 4 (= 32 query rows) and on one half of the 128 columns,
+        // so every row of S / dP / dQ / dV / dK is split between two threads
         const int q = warp & 3;
+        const int c_lo = ((warp - 4) >> 2) * 2;
         const int row = q * 32 + lane;
         const uint32_t lane_field = static_cast<uint32_t>(q * 32) << 16;
         const int sw = row & 7;
@@ -473,7 +493,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             mbar_wait(sdp_full, it & 1);
             tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = c_lo; c < c_lo + 2; ++c) {
                 uint32_t rs[32], rp[32];
                 tmem_ld_32x32b_x32(tmem_base + lane_field + TM_S + c * 32, rs);
                 tmem_ld_32x32b_x32(tmem_base + lane_field + TM_DP + c * 32, rp);
@@ -508,7 +528,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             tc_fence_after();
             float* dq_row = dq_acc + (((long)b * S + q0 + row) * H + h) * HD;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = c_lo; c < c_lo + 2; ++c) {
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(tmem_base + lane_field + TM_S + c * 32, r);
                 tmem_ld_wait();
@@ -527,7 +547,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             uint8_t* stage = which == 0 ? sP : sdS;
             const uint32_t t_acc = tmem_base + lane_field + (which == 0 ? TM_DV : TM_DK);
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = c_lo; c < c_lo + 2; ++c) {
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(t_acc + c * 32, r);
                 tmem_ld_wait();
@@ -543,7 +563,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             }
         }
         fence_proxy_async_smem();
-        named_bar_sync(1, 128);
+        named_bar_sync(1, 256);
         if (warp == 4 && lane == 0) {
             tma_store_4d(&tmdV, sP, 0, h, jb * BKV, b);
             tma_store_4d(&tmdV, sP + CHUNK_BYTES, 64, h, jb * BKV, b);
@@ -629,12 +649,12 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
         auto kern = flash_fwd_kernel<__nv_bfloat16>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 256, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+        kern<<<grid, 384, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
     } else {
         auto kern = flash_fwd_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 256, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+        kern<<<grid, 384, SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
@@ -685,12 +705,12 @@ extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, 
         auto kern = flash_bwd_kernel<__nv_bfloat16>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 256, B_SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdk, tdv, lse, delta, dq_acc, S, H, scale, scale_log2, causal);
+        kern<<<grid, 384, B_SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdk, tdv, lse, delta, dq_acc, S, H, scale, scale_log2, causal);
     } else {
         auto kern = flash_bwd_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 256, B_SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdk, tdv, lse, delta, dq_acc, S, H, scale, scale_log2, causal);
+        kern<<<grid, 384, B_SMEM_BYTES, stream>>>(tq, tk, tv, tdo, tdk, tdv, lse, delta, dq_acc, S, H, scale, scale_log2, causal);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
