@@ -388,6 +388,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     uint64_t* pds_ready = bars + 3;    // P and dS are in shared memory (8 warps)
     uint64_t* mma2_done = bars + 4;    // dV, dK, dQ UMMAs of this query block completed
     uint64_t* s_free = bars + 5;       // dQ drained from TMEM (8 warps)
+    uint64_t* qdo_free = bars + 6;     // dV and dK UMMAs (the last readers of Q_i / dO_i) completed
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
@@ -411,6 +412,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
         mbar_init(pds_ready, 8);
         mbar_init(mma2_done, 1);
         mbar_init(s_free, 8);
+        mbar_init(qdo_free, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -427,7 +429,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             tma_load_4d(sV, &tmV, kv_full, 0, h, jb * BKV, b);
             tma_load_4d(sV + CHUNK_BYTES, &tmV, kv_full, 64, h, jb * BKV, b);
             for (int it = 0; it < nit; ++it) {
-                if (it > 0) mbar_wait(mma2_done, (it - 1) & 1);   // every reader of Q_i / dO_i is done
+                // the next Q / dO tiles travel while the dQ product and its drain are still running
+                if (it > 0) mbar_wait(qdo_free, (it - 1) & 1);
                 const int q0 = (i0 + it) * BQ;
                 mbar_arrive_expect_tx(qdo_full, 2 * TILE_BYTES);
                 tma_load_4d(sQ, &tmQ, qdo_full, 0, h, q0, b);
@@ -469,6 +472,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                 for (int k = 0; k < 8; ++k)   // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
                     umma_f16_lohi(tmem_base + TM_DK, mnmaj(sdS) + k * (2048u >> 4), mnmaj(sQ) + k * (2048u >> 4),
                                   DESC_HI, id_mm, (it | k) != 0);
+                umma_commit(qdo_free);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)   // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
                     umma_f16_lohi(tmem_base + TM_S, kmaj(sdS) + koff(k), mnmaj(sK) + k * (2048u >> 4), DESC_HI, id_km,
