@@ -26,10 +26,13 @@ for (B, S, H, D) in ((4, 2048, 16, 128), (1, 8192, 16, 128)):
     qkv = torch.randn(B, S, 3, H, D, device="cuda", dtype=torch.float16)
     q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
     fl = 4.0 * B * H * S * S * D / 2
+    A.set_flash_fwd_variant(128)
+    t_128 = timed(lambda: A.flash_attn_fwd(q, k, v, causal=True, return_lse=True))
+    A.set_flash_fwd_variant(64)
     t_ours = timed(lambda: A.flash_attn_fwd(q, k, v, causal=True, return_lse=True))
     qt, kt, vt = (t.transpose(1, 2) for t in (q, k, v))
     t_lib = timed(lambda: F.scaled_dot_product_attention(qt, kt, vt, is_causal=True))
-    row = {"B": B, "S": S, "H": H, "D": D, "fwd_ours_ms": round(t_ours, 4), "fwd_sdpa_ms": round(t_lib, 4),
+    row = {"B": B, "S": S, "H": H, "D": D, "fwd_ours_ms": round(t_ours, 4), "fwd_ours_128key_1cta_ms": round(t_128, 4), "fwd_sdpa_ms": round(t_lib, 4),
            "fwd_ours_tflops": round(fl / t_ours / 1e9, 1), "fwd_sdpa_tflops": round(fl / t_lib / 1e9, 1)}
     if hasattr(A, "flash_attn_bwd"):
         out, lse = A.flash_attn_fwd(q, k, v, causal=True, return_lse=True)

@@ -324,6 +324,265 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
+// ------------------------------------------------------------------------------------------------ forward, 64-key blocks
+// Same algorithm with 64 keys per step: 112 KiB of shared memory and 256 TMEM columns per CTA, so TWO CTAs share an SM
+// and one CTA's S -> softmax -> P -> PV chain runs in the shadow of the other's (with one CTA per SM that chain is
+// latency-bound: about 2 us per 128-key block against 0.55 us of tensor time).
+constexpr int K64 = 64;
+constexpr int KV64_TILE = K64 * HD * 2;          // 16 KiB: two 64-column chunks of [64 rows x 128 B]
+constexpr int KV64_CHUNK = K64 * 128;            // 8 KiB
+constexpr int P64_BYTES = BQ * K64 * 2;          // 16 KiB: one chunk of [128 rows x 128 B]
+constexpr int F_OFF_Q = 0;
+constexpr int F_OFF_K = F_OFF_Q + TILE_BYTES;
+constexpr int F_OFF_V = F_OFF_K + 2 * KV64_TILE;
+constexpr int F_OFF_P = F_OFF_V + 2 * KV64_TILE;
+constexpr int F_OFF_BAR = F_OFF_P + P64_BYTES;
+constexpr int F_SMEM_BYTES = F_OFF_BAR + 256 + 512;   // 115456 B: two CTAs fit in the 228 KiB of an SM
+constexpr int F_TMEM_COLS = 256;
+constexpr int F_TM_O = 128;                      // S buffers at columns 0 and 64
+
+// One 64-key block of the online softmax for one row: maximum, rescale factor, probabilities packed to 16 bit and
+// their sum. MASK = false is the code for blocks no row of the warp has to mask (all but the last two of a causal
+// row block): without the per-score compares it is about half the instructions.
+template <typename T, bool MASK>
+DSB_DEVICE void softmax_block64(const uint32_t (&r0)[32], const uint32_t (&r1)[32], int lim, float scale_log2,
+                                float m_run, float& m_new, float& alpha, float& rs, uint32_t (&pk)[32]) {
+    float mx = -INFINITY;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        if (!MASK || i <= lim) mx = fmaxf(mx, __uint_as_float(r0[i]));
+        if (!MASK || 32 + i <= lim) mx = fmaxf(mx, __uint_as_float(r1[i]));
+    }
+    m_new = fmaxf(m_run, mx * scale_log2);
+    alpha = ex2(m_run - m_new);
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+        float a0 = ex2(__uint_as_float(r0[i]) * scale_log2 - m_new);
+        float a1 = ex2(__uint_as_float(r0[i + 1]) * scale_log2 - m_new);
+        float b0 = ex2(__uint_as_float(r1[i]) * scale_log2 - m_new);
+        float b1 = ex2(__uint_as_float(r1[i + 1]) * scale_log2 - m_new);
+        if (MASK) {
+            if (i > lim) a0 = 0.f;
+            if (i + 1 > lim) a1 = 0.f;
+            if (32 + i > lim) b0 = 0.f;
+            if (33 + i > lim) b1 = 0.f;
+        }
+        s0 += a0 + a1;
+        s1 += b0 + b1;
+        pk[i >> 1] = Cvt<T>::pack2(a0, a1);
+        pk[16 + (i >> 1)] = Cvt<T>::pack2(b0, b1);
+    }
+    rs = s0 + s1;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256, 2)
+flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                   float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    if (smem - smem_raw > 512) __trap();   // the launch reserves only 512 bytes of alignment slack
+    uint8_t* sQ = smem + F_OFF_Q;
+    uint8_t* sK = smem + F_OFF_K;
+    uint8_t* sV = smem + F_OFF_V;
+    uint8_t* sP = smem + F_OFF_P;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + F_OFF_BAR);
+    uint64_t* q_full = bars;
+    uint64_t* kv_full = bars + 1;
+    uint64_t* kv_empty = bars + 3;
+    uint64_t* s_full = bars + 5;
+    uint64_t* s_free = bars + 7;
+    uint64_t* p_ready = bars + 9;
+    uint64_t* pv_done = bars + 10;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int qb = gridDim.x - 1 - blockIdx.x;
+    const int b = blockIdx.y / H, h = blockIdx.y - b * H;
+    const int q0 = qb * BQ;
+    const int nkv = causal ? (q0 + BQ) / K64 : S / K64;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmO);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(q_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&kv_full[i], 1);
+            mbar_init(&kv_empty[i], 1);
+            mbar_init(&s_full[i], 1);
+            mbar_init(&s_free[i], 4);
+        }
+        mbar_init(p_ready, 4);
+        mbar_init(pv_done, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<F_TMEM_COLS>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            mbar_arrive_expect_tx(q_full, TILE_BYTES);
+            tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
+            tma_load_4d(sQ + CHUNK_BYTES, &tmQ, q_full, 64, h, q0, b);
+            for (int j = 0; j < nkv; ++j) {
+                const int st = j & 1;
+                if (j >= 2) mbar_wait(&kv_empty[st], ((j >> 1) - 1) & 1);
+                mbar_arrive_expect_tx(&kv_full[st], 2 * KV64_TILE);
+                uint8_t* k = sK + st * KV64_TILE;
+                uint8_t* v = sV + st * KV64_TILE;
+                tma_load_4d(k, &tmK, &kv_full[st], 0, h, j * K64, b);
+                tma_load_4d(k + KV64_CHUNK, &tmK, &kv_full[st], 64, h, j * K64, b);
+                tma_load_4d(v, &tmV, &kv_full[st], 0, h, j * K64, b);
+                tma_load_4d(v + KV64_CHUNK, &tmV, &kv_full[st], 64, h, j * K64, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+            const uint32_t idesc_s = make_idesc_f16(BQ, K64, is_bf16, 0, 0);
+            const uint32_t idesc_pv = make_idesc_f16(BQ, HD, is_bf16, 0, 1);
+            constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t q_lo = ((smem_u32(sQ) & 0x3FFFF) >> 4) | (1u << 16);
+            const uint32_t p_lo = ((smem_u32(sP) & 0x3FFFF) >> 4) | (1u << 16);
+            auto issue_s = [&](int j) {
+                const uint32_t k_lo = (((smem_u32(sK) + (j & 1) * KV64_TILE) & 0x3FFFF) >> 4) | (1u << 16);
+                const uint32_t d = tmem_base + (j & 1) * K64;
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    umma_f16_lohi(d, q_lo + (k >> 2) * (CHUNK_BYTES >> 4) + (k & 3) * 2,
+                                  k_lo + (k >> 2) * (KV64_CHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
+                umma_commit(&s_full[j & 1]);
+            };
+            auto issue_pv = [&](int j) {
+                const uint32_t v_lo = (((smem_u32(sV) + (j & 1) * KV64_TILE) & 0x3FFFF) >> 4) |
+                                      ((uint32_t)(KV64_CHUNK >> 4) << 16);
+#pragma unroll
+                for (int k = 0; k < K64 / 16; ++k)
+                    umma_f16_lohi(tmem_base + F_TM_O, p_lo + k * 2, v_lo + k * (2048u >> 4), DESC_HI, idesc_pv,
+                                  (j | k) != 0);
+                umma_commit(pv_done);
+                umma_commit(&kv_empty[j & 1]);
+            };
+            mbar_wait(q_full, 0);
+            mbar_wait(&kv_full[0], 0);
+            tc_fence_after();
+            issue_s(0);
+            for (int j = 0; j < nkv; ++j) {
+                if (j + 1 < nkv) {
+                    const int n = j + 1;
+                    mbar_wait(&kv_full[n & 1], (n >> 1) & 1);
+                    if (n >= 2) mbar_wait(&s_free[n & 1], ((n >> 1) - 1) & 1);
+                    tc_fence_after();
+                    issue_s(n);
+                }
+                mbar_wait(p_ready, j & 1);
+                tc_fence_after();
+                issue_pv(j);
+            }
+        }
+    } else if (warp >= 4) {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const uint32_t lane_field = static_cast<uint32_t>(q * 32) << 16;
+        const int sw = row & 7;
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < nkv; ++j) {
+            const int buf = j & 1;
+            const int lim = causal ? q0 + row - j * K64 : K64;   // columns <= lim of this block are visible
+            const bool edge = lim < K64 - 1;
+            mbar_wait(&s_full[buf], (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t_s = tmem_base + lane_field + buf * K64;
+            uint32_t r0[32], r1[32];
+            tmem_ld_32x32b_x32(t_s, r0);
+            tmem_ld_32x32b_x32(t_s + 32, r1);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&s_free[buf]);   // the scores are in registers: the buffer can be refilled
+            float m_new, alpha, rs;
+            uint32_t pk[32];
+            if (__any_sync(0xffffffffu, edge))
+                softmax_block64<T, true>(r0, r1, lim, scale_log2, m_run, m_new, alpha, rs, pk);
+            else
+                softmax_block64<T, false>(r0, r1, lim, scale_log2, m_run, m_new, alpha, rs, pk);
+            if (j > 0) {
+                mbar_wait(pv_done, (j - 1) & 1);   // O and the P buffer are free
+                tc_fence_after();
+                if (!__all_sync(0xffffffffu, alpha == 1.f)) {
+                    const uint32_t t_o = tmem_base + lane_field + F_TM_O;
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t r[32];
+                        tmem_ld_32x32b_x32(t_o + c * 32, r);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                        tmem_st_32x32b_x32(t_o + c * 32, r);
+                    }
+                    tmem_st_wait();
+                }
+            }
+            uint8_t* dst = sP + row * 128;
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                *reinterpret_cast<uint4*>(dst + ((u ^ sw) << 4)) =
+                    make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+            l_run = l_run * alpha + rs;
+            m_run = m_new;
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_ready);
+        }
+        mbar_wait(pv_done, (nkv - 1) & 1);
+        tc_fence_after();
+        const float inv_l = 1.f / l_run;
+        const uint32_t t_o = tmem_base + lane_field + F_TM_O;
+        uint8_t* o_row = sQ + row * 128;   // the Q tile is no longer needed: stage O there
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(t_o + c * 32, r);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+                pk[i >> 1] = Cvt<T>::pack2(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l);
+            uint8_t* dst = o_row + (c >> 1) * CHUNK_BYTES;
+            const int u0 = (c & 1) * 4;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                *reinterpret_cast<uint4*>(dst + (((u0 + u) ^ sw) << 4)) =
+                    make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+        }
+        if (lse != nullptr)
+            lse[((long)blockIdx.y) * S + q0 + row] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+        fence_proxy_async_smem();
+        named_bar_sync(1, 128);
+        if (warp == 4 && lane == 0) {
+            tma_store_4d(&tmO, sQ, 0, h, q0, b);
+            tma_store_4d(&tmO, sQ + CHUNK_BYTES, 64, h, q0, b);
+            tma_store_commit();
+            tma_store_wait<0>();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 2) tmem_dealloc<F_TMEM_COLS>(tmem_base);
+}
+
 // ------------------------------------------------------------------------------------------------ backward
 // delta[b, h, s] = sum_d dO[b, s, h, d] * O[b, s, h, d] (fp32); one warp per row of 128 elements.
 template <typename T>
@@ -600,12 +859,12 @@ static EncodeTiledFn get_encode() {
 }
 // [B, S, H, D] tensor with element strides (sb, ss, sh, 1) as a 4-D map ordered (D, H, S, B); box = 64 x 1 x 128 x 1.
 static int make_map_bshd(CUtensorMap* m, int is_bf16, const void* base, int B, int S, int H, int D, long sb, long ss,
-                         long sh) {
+                         long sh, int box_rows = 128) {
     EncodeTiledFn enc = get_encode();
     if (!enc) return -1;
     cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)S, (cuuint64_t)B};
     cuuint64_t strides[3] = {(cuuint64_t)sh * 2, (cuuint64_t)ss * 2, (cuuint64_t)sb * 2};
-    cuuint32_t box[4] = {64, 1, 128, 1};
+    cuuint32_t box[4] = {64, 1, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(m, is_bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4,
                      const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -615,6 +874,14 @@ static int make_map_bshd(CUtensorMap* m, int is_bf16, const void* base, int B, i
 
 }  // namespace fa
 }  // namespace dsb
+
+// Forward variant: 64 = 64-key blocks, two CTAs per SM (default); 128 = 128-key blocks, one CTA per SM.
+static int g_fa_fwd_variant = 64;
+extern "C" int dsb_flash_attn_fwd_variant(int v) {
+    const int prev = g_fa_fwd_variant;
+    if (v == 64 || v == 128) g_fa_fwd_variant = v;
+    return prev;
+}
 
 // out[b, s, h, :] = softmax(scale * q[b, s, h, :] . k[b, :, h, :]^T (+ causal mask)) v[b, :, h, :]; lse (optional,
 // [B, H, S] fp32) receives the natural-log sum of exponentials of the scaled scores of every row.
@@ -649,7 +916,23 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
     const float scale_log2 = scale * 1.4426950408889634f;
     dim3 grid(S / BQ, B * H);
     cudaError_t e;
-    if (bf) {
+    if (g_fa_fwd_variant == 64) {
+        rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
+        if (rc) return rc;
+        rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);
+        if (rc) return rc;
+        if (bf) {
+            auto kern = flash_fwd64_kernel<__nv_bfloat16>;
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES);
+            if (e != cudaSuccess) return -(int)e;
+            kern<<<grid, 256, F_SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+        } else {
+            auto kern = flash_fwd64_kernel<__half>;
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES);
+            if (e != cudaSuccess) return -(int)e;
+            kern<<<grid, 256, F_SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+        }
+    } else if (bf) {
         auto kern = flash_fwd_kernel<__nv_bfloat16>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
         if (e != cudaSuccess) return -(int)e;

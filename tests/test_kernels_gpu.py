@@ -517,11 +517,21 @@ def test_collective_gemm_variants_single_rank():
         assert ((dw.float() - ref).abs().max() / ref.abs().max()).item() < 3e-3
 
 
+@pytest.mark.parametrize("variant", [64, 128])
 @pytest.mark.parametrize("causal", [True, False])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-def test_flash_attention_forward(causal, dtype):
-    """tcgen05 flash-attention forward vs fp32 softmax(QK^T)V, on strided views of a fused QKV buffer."""
-    from deeperspeed_b200.ops.attention import flash_attn_fwd
+def test_flash_attention_forward(causal, dtype, variant):
+    """tcgen05 flash-attention forward (both block shapes) vs fp32 softmax(QK^T)V, on strided views of a fused QKV
+    buffer."""
+    from deeperspeed_b200.ops.attention import flash_attn_fwd, set_flash_fwd_variant
+    prev = set_flash_fwd_variant(variant)
+    try:
+        _check_flash_forward(causal, dtype, flash_attn_fwd)
+    finally:
+        set_flash_fwd_variant(prev)
+
+
+def _check_flash_forward(causal, dtype, flash_attn_fwd):
     torch.manual_seed(0)
     B, S, H, D = 2, 640, 3, 128
     qkv = torch.randn(B, S, 3, H, D, device="cuda", dtype=dtype)
