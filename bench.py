@@ -79,6 +79,14 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def _attention_backend():
+    try:
+        from deeperspeed_b200.ops.attention import attention_backend
+        return {"native": "tcgen05 flash attention (ours)", "sdpa": "library SDPA"}[attention_backend()]
+    except Exception:
+        return "unknown"
+
+
 def ds_config(n_gpus, pp, dp):
     gas = MICRO_BATCHES_PER_STAGE * pp
     return {
@@ -255,7 +263,7 @@ def run_ours(args):
                        "layers": cfg.num_layers, "global_batch": conf["train_batch_size"], "seq_len": SEQ,
                        "micro_batch": MICRO_BATCH, "grad_accum": conf["gradient_accumulation_steps"],
                        "parallelism": f"pp{pp}xdp{dp} zero1", "l2": "working set per step >> 126 MB L2 (no flush needed)",
-                       "params": cfg.num_params()},
+                       "params": cfg.num_params(), "attention_backend": _attention_backend()},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": float(h2d.item()) / args.steps,
                     "d2h_bytes_per_step": loss_bytes / args.steps, "ms_per_step": ms_e2e / args.steps,
