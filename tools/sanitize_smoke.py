@@ -5,7 +5,7 @@
     compute-sanitizer --tool synccheck  python tools/sanitize_smoke.py
 
 (the reference has no sanitizer coverage at all). Also checks the results, so a plain run is a quick
-numerics smoke test. On the development GPU pool of this repository compute-sanitizer is administratively closed, so
+numerics smoke test (GEMMs, transformer kernels, flash attention, fused ZeRO kernels). On the development GPU pool of this repository compute-sanitizer is administratively closed, so
 only the plain run has been exercised there (profiles/README.md)."""
 import os
 import sys
@@ -97,5 +97,38 @@ pr = p.clone()
 K.adam_flat(p, m, v, gr, lp=lp, lr=1e-2, beta1=0.9, beta2=0.99, eps=1e-8, weight_decay=0.0, step=1)
 check("adam flat (first step = lr*sign)", p, pr - 1e-2 * torch.sign(gr.float()), 1e-3)
 check("sumsq", K.sumsq(gr), gr.float().square().sum(), 1e-3)
+
+# ---- flash attention (tcgen05), both forward block shapes + backward, against fp32 attention
+from deeperspeed_b200.ops import attention as A
+Bq, Sq, Hq, Dq = 1, 256, 2, 128
+qkv5 = torch.randn(Bq, Sq, 3, Hq, Dq, device=dev, dtype=dt)
+q_, k_, v_ = qkv5[:, :, 0], qkv5[:, :, 1], qkv5[:, :, 2]
+qf, kf, vf = (t.float().transpose(1, 2).detach().requires_grad_() for t in (q_, k_, v_))
+sc = (qf @ kf.transpose(-1, -2) / Dq ** 0.5).masked_fill(torch.triu(torch.ones(Sq, Sq, dtype=torch.bool, device=dev), 1), float("-inf"))
+ref_o = (torch.softmax(sc, -1) @ vf).transpose(1, 2)
+for variant in (128, 64):
+    A.set_flash_fwd_variant(variant)
+    o_, lse_ = A.flash_attn_fwd(q_, k_, v_, causal=True, return_lse=True)
+    check(f"flash attention fwd ({variant}-key blocks)", o_, ref_o, 5e-3)
+do_ = torch.randn_like(o_)
+dq_, dk_, dv_ = A.flash_attn_bwd(do_, q_, k_, v_, o_, lse_, causal=True)
+rq, rk, rv = torch.autograd.grad(ref_o, (qf, kf, vf), do_.float())
+check("flash attention bwd dq", dq_, rq.transpose(1, 2), 2e-2)
+check("flash attention bwd dk", dk_, rk.transpose(1, 2), 2e-2)
+check("flash attention bwd dv", dv_, rv.transpose(1, 2), 2e-2)
+
+# ---- kernels that carry a collective, with this GPU as its own peer (barriers, flags, staging all exercised)
+from deeperspeed_b200.parallel.fused_zero_single import SingleRankFusedZero
+z = SingleRankFusedZero(1 << 16, tensor_sizes=[4096, 8192, 1 << 15])
+z.master.normal_(0, 0.1)
+z.grad.normal_(0, 0.01)
+z.rs_norm()
+check("fused zero: reduce + norm", z.sumsq[0], z.grad.float().square().sum(), 1e-3)
+w_before = z.master.clone()
+z.adam_ag(1e-2, (0.9, 0.99), 1e-8, 0.0, True, 1)
+check("fused zero: adam + push", z.param, w_before - 1e-2 * torch.sign(z.grad.float()), 2e-3)
+z.rs_norm()
+z.lamb_ag(1e-2, (0.9, 0.99), 1e-8, 0.0, 10.0, 0.01, 2)
+assert torch.isfinite(z.master).all() and (z.coeff[:3] > 0).all()
 torch.cuda.synchronize()
 print("sanitize_smoke: ok")
