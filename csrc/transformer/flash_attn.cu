@@ -380,7 +380,7 @@ template <typename T>
 __global__ void __launch_bounds__(256, 2)
 flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                    const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                   float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
+                   float* __restrict__ lse, int S, int H, float scale_log2, int causal, long long* dbg) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     if (smem - smem_raw > 512) __trap();   // the launch reserves only 512 bytes of alignment slack
@@ -390,13 +390,15 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     uint8_t* sP = smem + F_OFF_P;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + F_OFF_BAR);
     uint64_t* q_full = bars;
-    uint64_t* kv_full = bars + 1;
-    uint64_t* kv_empty = bars + 3;
+    uint64_t* k_full = bars + 1;        // K and V have their own rings: a K tile is free as soon as its S product
+    uint64_t* k_empty = bars + 3;       // has completed, one block before the matching V tile
+    uint64_t* v_full = bars + 11;
+    uint64_t* v_empty = bars + 13;
     uint64_t* s_full = bars + 5;
     uint64_t* s_free = bars + 7;
     uint64_t* p_ready = bars + 9;
     uint64_t* pv_done = bars + 10;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
@@ -404,6 +406,9 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const int b = blockIdx.y / H, h = blockIdx.y - b * H;
     const int q0 = qb * BQ;
     const int nkv = causal ? (q0 + BQ) / K64 : S / K64;
+    const bool tm = dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
+    long long t0 = 0, acc[6] = {0, 0, 0, 0, 0, 0};
+#define TICK(n) if (tm) { long long t1 = clock64(); acc[n] += t1 - t0; t0 = t1; }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
@@ -414,8 +419,10 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (warp == 1 && lane == 0) {
         mbar_init(q_full, 1);
         for (int i = 0; i < 2; ++i) {
-            mbar_init(&kv_full[i], 1);
-            mbar_init(&kv_empty[i], 1);
+            mbar_init(&k_full[i], 1);
+            mbar_init(&k_empty[i], 1);
+            mbar_init(&v_full[i], 1);
+            mbar_init(&v_empty[i], 1);
             mbar_init(&s_full[i], 1);
             mbar_init(&s_free[i], 4);
         }
@@ -434,16 +441,27 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             mbar_arrive_expect_tx(q_full, TILE_BYTES);
             tma_load_4d(sQ, &tmQ, q_full, 0, h, q0, b);
             tma_load_4d(sQ + CHUNK_BYTES, &tmQ, q_full, 64, h, q0, b);
+            // With one ring for both, tile j + 2 could only be requested after P V of block j and the ~1800-cycle TMA
+            // round trip sat on the critical path of every other block (measured with the clock64 timers below: the
+            // MMA thread waited 1790 cycles per block for its operands).
             for (int j = 0; j < nkv; ++j) {
                 const int st = j & 1;
-                if (j >= 2) mbar_wait(&kv_empty[st], ((j >> 1) - 1) & 1);
-                mbar_arrive_expect_tx(&kv_full[st], 2 * KV64_TILE);
-                uint8_t* k = sK + st * KV64_TILE;
+                if (j >= 2) mbar_wait(&k_empty[st], ((j >> 1) - 1) & 1);
+                mbar_arrive_expect_tx(&k_full[st], KV64_TILE);
+                uint8_t* kk = sK + st * KV64_TILE;
+                tma_load_4d(kk, &tmK, &k_full[st], 0, h, j * K64, b);
+                tma_load_4d(kk + KV64_CHUNK, &tmK, &k_full[st], 64, h, j * K64, b);
+            }
+        }
+    } else if (warp == 3) {
+        if (elect_one()) {
+            for (int j = 0; j < nkv; ++j) {
+                const int st = j & 1;
+                if (j >= 2) mbar_wait(&v_empty[st], ((j >> 1) - 1) & 1);
+                mbar_arrive_expect_tx(&v_full[st], KV64_TILE);
                 uint8_t* v = sV + st * KV64_TILE;
-                tma_load_4d(k, &tmK, &kv_full[st], 0, h, j * K64, b);
-                tma_load_4d(k + KV64_CHUNK, &tmK, &kv_full[st], 64, h, j * K64, b);
-                tma_load_4d(v, &tmV, &kv_full[st], 0, h, j * K64, b);
-                tma_load_4d(v + KV64_CHUNK, &tmV, &kv_full[st], 64, h, j * K64, b);
+                tma_load_4d(v, &tmV, &v_full[st], 0, h, j * K64, b);
+                tma_load_4d(v + KV64_CHUNK, &tmV, &v_full[st], 64, h, j * K64, b);
             }
         }
     } else if (warp == 1) {
@@ -462,6 +480,7 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     umma_f16_lohi(d, q_lo + (k >> 2) * (CHUNK_BYTES >> 4) + (k & 3) * 2,
                                   k_lo + (k >> 2) * (KV64_CHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
                 umma_commit(&s_full[j & 1]);
+                umma_commit(&k_empty[j & 1]);
             };
             auto issue_pv = [&](int j) {
                 const uint32_t v_lo = (((smem_u32(sV) + (j & 1) * KV64_TILE) & 0x3FFFF) >> 4) |
@@ -471,24 +490,31 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     umma_f16_lohi(tmem_base + F_TM_O, p_lo + k * 2, v_lo + k * (2048u >> 4), DESC_HI, idesc_pv,
                                   (j | k) != 0);
                 umma_commit(pv_done);
-                umma_commit(&kv_empty[j & 1]);
+                umma_commit(&v_empty[j & 1]);
             };
             mbar_wait(q_full, 0);
-            mbar_wait(&kv_full[0], 0);
+            mbar_wait(&k_full[0], 0);
             tc_fence_after();
             issue_s(0);
+            t0 = clock64();
             for (int j = 0; j < nkv; ++j) {
                 if (j + 1 < nkv) {
                     const int n = j + 1;
-                    mbar_wait(&kv_full[n & 1], (n >> 1) & 1);
+                    mbar_wait(&k_full[n & 1], (n >> 1) & 1);
                     if (n >= 2) mbar_wait(&s_free[n & 1], ((n >> 1) - 1) & 1);
                     tc_fence_after();
+                    TICK(0)
                     issue_s(n);
+                    TICK(1)
                 }
                 mbar_wait(p_ready, j & 1);
+                mbar_wait(&v_full[j & 1], (j >> 1) & 1);
                 tc_fence_after();
+                TICK(2)
                 issue_pv(j);
+                TICK(3)
             }
+            if (tm) { for (int i = 0; i < 4; ++i) dbg[8 + i] = acc[i]; dbg[15] = nkv; }
         }
     } else if (warp >= 4) {
         const int q = warp & 3;
@@ -496,12 +522,14 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const uint32_t lane_field = static_cast<uint32_t>(q * 32) << 16;
         const int sw = row & 7;
         float m_run = -INFINITY, l_run = 0.f;
+        t0 = clock64();
         for (int j = 0; j < nkv; ++j) {
             const int buf = j & 1;
             const int lim = causal ? q0 + row - j * K64 : K64;   // columns <= lim of this block are visible
             const bool edge = lim < K64 - 1;
             mbar_wait(&s_full[buf], (j >> 1) & 1);
             tc_fence_after();
+            TICK(0)
             const uint32_t t_s = tmem_base + lane_field + buf * K64;
             uint32_t r0[32], r1[32];
             tmem_ld_32x32b_x32(t_s, r0);
@@ -510,12 +538,14 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&s_free[buf]);   // the scores are in registers: the buffer can be refilled
+            TICK(1)
             float m_new, alpha, rs;
             uint32_t pk[32];
             if (__any_sync(0xffffffffu, edge))
                 softmax_block64<T, true>(r0, r1, lim, scale_log2, m_run, m_new, alpha, rs, pk);
             else
                 softmax_block64<T, false>(r0, r1, lim, scale_log2, m_run, m_new, alpha, rs, pk);
+            TICK(2)
             if (j > 0) {
                 mbar_wait(pv_done, (j - 1) & 1);   // O and the P buffer are free
                 tc_fence_after();
@@ -533,6 +563,7 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
                     tmem_st_wait();
                 }
             }
+            TICK(3)
             uint8_t* dst = sP + row * 128;
 #pragma unroll
             for (int u = 0; u < 8; ++u)
@@ -544,7 +575,9 @@ flash_fwd64_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(p_ready);
+            TICK(4)
         }
+        if (tm && warp == 4 && lane == 0) for (int i = 0; i < 5; ++i) dbg[i] = acc[i];
         mbar_wait(pv_done, (nkv - 1) & 1);
         tc_fence_after();
         const float inv_l = 1.f / l_run;
@@ -877,6 +910,8 @@ static int make_map_bshd(CUtensorMap* m, int is_bf16, const void* base, int B, i
 
 // Forward variant: 64 = 64-key blocks, two CTAs per SM (default); 128 = 128-key blocks, one CTA per SM.
 static int g_fa_fwd_variant = 64;
+static long long* g_fa_dbg = nullptr;
+extern "C" void dsb_flash_attn_debug_timers(long long* p) { g_fa_dbg = p; }
 extern "C" int dsb_flash_attn_fwd_variant(int v) {
     const int prev = g_fa_fwd_variant;
     if (v == 64 || v == 128) g_fa_fwd_variant = v;
@@ -925,12 +960,12 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
             auto kern = flash_fwd64_kernel<__nv_bfloat16>;
             e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES);
             if (e != cudaSuccess) return -(int)e;
-            kern<<<grid, 256, F_SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+            kern<<<grid, 256, F_SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_fa_dbg);
         } else {
             auto kern = flash_fwd64_kernel<__half>;
             e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM_BYTES);
             if (e != cudaSuccess) return -(int)e;
-            kern<<<grid, 256, F_SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+            kern<<<grid, 256, F_SMEM_BYTES, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_fa_dbg);
         }
     } else if (bf) {
         auto kern = flash_fwd_kernel<__nv_bfloat16>;
