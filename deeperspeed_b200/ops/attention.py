@@ -9,7 +9,7 @@ Two attention back ends, selected with DSB_ATTN (or `set_attention_backend`):
   "native": the tcgen05 flash-attention kernels of csrc/transformer/flash_attn.cu (forward + backward, V read in place
             from the fused activation, dV written in place into the dQKV buffer);
   "sdpa"  : the library flash kernel behind torch SDPA. Default, because it is the faster one today
-            (bench/flash_attn_bench.py: 0.072 / 0.235 ms vs 0.132 / 0.421 ms forward / backward at batch 4 x 16 heads x
+            (bench/flash_attn_bench.py: 0.073 / 0.235 ms vs 0.119 / 0.378 ms forward / backward at batch 4 x 16 heads x
             seq 2048); the native path needs head dim 128 and seq % 128 == 0 and falls back to "sdpa" otherwise.
 """
 import ctypes as C
