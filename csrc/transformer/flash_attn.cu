@@ -645,7 +645,8 @@ constexpr int B_OFF_Q = B_OFF_V + TILE_BYTES;
 constexpr int B_OFF_DO = B_OFF_Q + TILE_BYTES;
 constexpr int B_OFF_P = B_OFF_DO + TILE_BYTES;
 constexpr int B_OFF_DS = B_OFF_P + TILE_BYTES;
-constexpr int B_OFF_BAR = B_OFF_DS + TILE_BYTES;
+constexpr int B_OFF_Q1 = B_OFF_DS + TILE_BYTES;   // second Q stage (the next query block is prefetched)
+constexpr int B_OFF_BAR = B_OFF_Q1 + TILE_BYTES;
 constexpr int B_SMEM_BYTES = B_OFF_BAR + 256 + 1024;
 constexpr int TM_DP = 128, TM_DV = 256, TM_DK = 384;
 
@@ -678,19 +679,22 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + B_OFF_K;
     uint8_t* sV = smem + B_OFF_V;
-    uint8_t* sQ = smem + B_OFF_Q;
+    uint8_t* sQ0 = smem + B_OFF_Q;
+    uint8_t* sQ1 = smem + B_OFF_Q1;
     uint8_t* sdO = smem + B_OFF_DO;
     uint8_t* sP = smem + B_OFF_P;
     uint8_t* sdS = smem + B_OFF_DS;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + B_OFF_BAR);
     uint64_t* kv_full = bars;          // K_j, V_j landed
-    uint64_t* qdo_full = bars + 1;     // Q_i, dO_i landed
+    uint64_t* do_full = bars + 1;      // dO_i landed
     uint64_t* sdp_full = bars + 2;     // S and dP are in TMEM
     uint64_t* pds_ready = bars + 3;    // P and dS are in shared memory (8 warps)
     uint64_t* mma2_done = bars + 4;    // dV, dK, dQ UMMAs of this query block completed
     uint64_t* s_free = bars + 5;       // dQ drained from TMEM (8 warps)
-    uint64_t* qdo_free = bars + 6;     // dV and dK UMMAs (the last readers of Q_i / dO_i) completed
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+    uint64_t* do_free = bars + 6;      // dV UMMAs (the last readers of dO_i) completed
+    uint64_t* q_full = bars + 9;       // [2] Q ring: Q_{i+1} travels while block i is being worked on
+    uint64_t* q_free = bars + 11;      // [2] dK UMMAs (the last readers of that Q stage) completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
@@ -710,12 +714,16 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
     }
     if (warp == 1 && lane == 0) {
         mbar_init(kv_full, 1);
-        mbar_init(qdo_full, 1);
+        mbar_init(do_full, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&q_full[i], 1);
+            mbar_init(&q_free[i], 1);
+        }
         mbar_init(sdp_full, 1);
         mbar_init(pds_ready, 8);
         mbar_init(mma2_done, 1);
         mbar_init(s_free, 8);
-        mbar_init(qdo_free, 1);
+        mbar_init(do_free, 1);
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -731,15 +739,24 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             tma_load_4d(sK + CHUNK_BYTES, &tmK, kv_full, 64, h, jb * BKV, b);
             tma_load_4d(sV, &tmV, kv_full, 0, h, jb * BKV, b);
             tma_load_4d(sV + CHUNK_BYTES, &tmV, kv_full, 64, h, jb * BKV, b);
-            for (int it = 0; it < nit; ++it) {
-                // the next Q / dO tiles travel while the dQ product and its drain are still running
-                if (it > 0) mbar_wait(qdo_free, (it - 1) & 1);
+            for (int it = 0; it < nit; ++it) {   // Q ring, two stages
+                const int st = it & 1;
+                if (it >= 2) mbar_wait(&q_free[st], ((it >> 1) - 1) & 1);
                 const int q0 = (i0 + it) * BQ;
-                mbar_arrive_expect_tx(qdo_full, 2 * TILE_BYTES);
-                tma_load_4d(sQ, &tmQ, qdo_full, 0, h, q0, b);
-                tma_load_4d(sQ + CHUNK_BYTES, &tmQ, qdo_full, 64, h, q0, b);
-                tma_load_4d(sdO, &tmdO, qdo_full, 0, h, q0, b);
-                tma_load_4d(sdO + CHUNK_BYTES, &tmdO, qdo_full, 64, h, q0, b);
+                uint8_t* dst = st ? sQ1 : sQ0;
+                mbar_arrive_expect_tx(&q_full[st], TILE_BYTES);
+                tma_load_4d(dst, &tmQ, &q_full[st], 0, h, q0, b);
+                tma_load_4d(dst + CHUNK_BYTES, &tmQ, &q_full[st], 64, h, q0, b);
+            }
+        }
+    } else if (warp == 3) {
+        if (elect_one()) {
+            for (int it = 0; it < nit; ++it) {   // dO: one stage, re-requested as soon as dV of the block has completed
+                if (it > 0) mbar_wait(do_free, (it - 1) & 1);
+                const int q0 = (i0 + it) * BQ;
+                mbar_arrive_expect_tx(do_full, TILE_BYTES);
+                tma_load_4d(sdO, &tmdO, do_full, 0, h, q0, b);
+                tma_load_4d(sdO + CHUNK_BYTES, &tmdO, do_full, 64, h, q0, b);
             }
         }
     } else if (warp == 1) {
@@ -756,7 +773,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
             mbar_wait(kv_full, 0);
             t0 = clock64();
             for (int it = 0; it < nit; ++it) {
-                mbar_wait(qdo_full, it & 1);
+                const uint8_t* sQ = (it & 1) ? sQ1 : sQ0;
+                mbar_wait(&q_full[it & 1], (it >> 1) & 1);
                 TICK(0)
                 if (it > 0) mbar_wait(s_free, (it - 1) & 1);
                 tc_fence_after();
@@ -764,6 +782,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
                     umma_f16_lohi(tmem_base + TM_S, kmaj(sQ) + koff(k), kmaj(sK) + koff(k), DESC_HI, id_kk, k != 0);
+                mbar_wait(do_full, it & 1);
+                tc_fence_after();
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
                     umma_f16_lohi(tmem_base + TM_DP, kmaj(sdO) + koff(k), kmaj(sV) + koff(k), DESC_HI, id_kk, k != 0);
@@ -776,11 +796,12 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant_
                 for (int k = 0; k < 8; ++k)   // dV[kv, d] += sum_q P[q, kv] dO[q, d]
                     umma_f16_lohi(tmem_base + TM_DV, mnmaj(sP) + k * (2048u >> 4), mnmaj(sdO) + k * (2048u >> 4),
                                   DESC_HI, id_mm, (it | k) != 0);
+                umma_commit(do_free);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)   // dK[kv, d] += sum_q dS[q, kv] Q[q, d]
                     umma_f16_lohi(tmem_base + TM_DK, mnmaj(sdS) + k * (2048u >> 4), mnmaj(sQ) + k * (2048u >> 4),
                                   DESC_HI, id_mm, (it | k) != 0);
-                umma_commit(qdo_free);
+                umma_commit(&q_free[it & 1]);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)   // dQ[q, d] = sum_kv dS[q, kv] K[kv, d]
                     umma_f16_lohi(tmem_base + TM_S, kmaj(sdS) + koff(k), mnmaj(sK) + k * (2048u >> 4), DESC_HI, id_km,
