@@ -9,7 +9,15 @@ class CSRTensor:
     def __init__(self, dense_tensor=None):
         self.orig_dense_tensor = dense_tensor
         self.indices = self.values = self.dense_size = None
-        if dense_tensor is not None:
+        self.orig_param = None     # set by the engine when the gradient arrived as a torch sparse tensor
+        if dense_tensor is not None and dense_tensor.is_sparse:
+            # nn.Embedding(sparse=True) hands over a COO gradient whose first index dimension is the row
+            coo = dense_tensor.coalesce()
+            self.indices = coo.indices()[0].clone()
+            self.values = coo.values().clone()
+            self.dense_size = list(dense_tensor.shape)
+            self.orig_dense_tensor = None
+        elif dense_tensor is not None:
             touched = dense_tensor.ne(0).any(dim=1)          # rows with at least one non-zero entry
             self.indices = touched.nonzero(as_tuple=False).reshape(-1)
             self.values = dense_tensor.index_select(0, self.indices)

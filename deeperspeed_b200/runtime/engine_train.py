@@ -302,7 +302,13 @@ class TrainStepMixin:
             else:
                 grad_data = param.grad.data
                 if self.sparse_gradients_enabled() and param_name in self.csr_tensor_module_names:
-                    grads.append(CSRTensor(grad_data))
+                    csr = CSRTensor(grad_data)
+                    if grad_data.is_sparse:   # the reduced gradient replaces the sparse one as a dense tensor
+                        csr.orig_param = param
+                    grads.append(csr)
+                elif grad_data.is_sparse:
+                    param.grad = grad_data.to_dense()
+                    grads.append(param.grad.data)
                 else:
                     grads.append(grad_data)
         split_buckets = split_half_float_double_csr(grads)
@@ -317,7 +323,10 @@ class TrainStepMixin:
         allreduced_csrs = self.csr_allreduce_bucket(bucket)
         for csr in allreduced_csrs:
             dense_tensor = csr.to_dense()
-            csr.orig_dense_tensor.copy_(dense_tensor)
+            if csr.orig_param is not None:
+                csr.orig_param.grad = dense_tensor
+            else:
+                csr.orig_dense_tensor.copy_(dense_tensor)
 
     def csr_allreduce_bucket(self, bucket):
         return [self.csr_allreduce(csr) for csr in bucket]

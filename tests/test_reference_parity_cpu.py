@@ -745,3 +745,109 @@ def test_onebit_adam_pipeline_topologies(pp, dp, tmp_path):
                        group=engine.grid.get_data_parallel_group())
         assert torch.allclose(flat, ref, atol=1e-6), (flat - ref).abs().max()
     run()
+
+
+def test_sparse_gradients_csr_allreduce_world2(tmp_path):
+    """`sparse_gradients: true`: an nn.Embedding(sparse=True) gradient travels as a CSR tensor (padded all_gather of
+    indices and values, reference engine.py:1397-1453) and the result equals the dense data-parallel run."""
+    import deeperspeed_b200 as deepspeed
+    from simple_model import args_from_dict
+
+    class EmbModel(torch.nn.Module):
+        def __init__(self, sparse):
+            super().__init__()
+            self.emb = torch.nn.Embedding(50, 8, sparse=sparse)
+            self.lin = torch.nn.Linear(8, 4)
+
+        def forward(self, idx, y):
+            return torch.nn.functional.cross_entropy(self.lin(self.emb(idx).mean(1)), y)
+
+    @distributed_test(world_size=2)
+    def run():
+        results = []
+        for sparse in (False, True):
+            torch.manual_seed(3)
+            model = EmbModel(sparse)
+            cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+                   "sparse_gradients": sparse, "optimizer": {"type": "SGD", "params": {"lr": 0.1}}}
+            opt = torch.optim.SGD(model.parameters(), lr=0.1)
+            engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model, optimizer=opt,
+                                                   model_parameters=model.parameters())
+            if sparse:
+                assert engine.sparse_gradients_enabled() and len(engine.csr_tensor_module_names) == 1
+            g = torch.Generator().manual_seed(10 + dist.get_rank())
+            for _ in range(3):
+                idx = torch.randint(0, 50, (2, 5), generator=g)
+                y = torch.randint(0, 4, (2,), generator=g)
+                loss = engine(idx, y)
+                engine.backward(loss)
+                engine.step()
+            results.append([p.detach().clone() for p in model.parameters()])
+        for a, b in zip(*results):
+            assert torch.allclose(a, b, atol=1e-6), (a - b).abs().max()
+        # replicas agree
+        flat = torch.cat([p.view(-1) for p in results[1]])
+        other = flat.clone()
+        dist.broadcast(other, src=0)
+        assert torch.equal(flat, other)
+    run()
+
+
+def test_save_fp16_model_zero3_consolidates_on_rank0(tmp_path):
+    """`save_fp16_model` under ZeRO-3 gathers the partitioned weights layer by layer on rank 0 into a plain state_dict
+    (reference engine.py:1820-1915); with the gather switch off nothing is written."""
+    import deeperspeed_b200 as deepspeed
+    from simple_model import LinearStack, args_from_dict
+
+    @distributed_test(world_size=2)
+    def run():
+        for gather in (True, False):
+            torch.manual_seed(11)
+            cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+                   "optimizer": {"type": "Adam", "params": {"lr": 1e-3}}, "fp16": {"enabled": True, "type": "fp32"},
+                   "zero_optimization": {"stage": 3, "stage3_gather_fp16_weights_on_model_save": gather}}
+            ref = LinearStack(16, 16, 16, 2)
+            ref_sd = {k: v.detach().clone() for k, v in ref.state_dict().items()}
+            with deepspeed.zero.Init():
+                model = LinearStack(16, 16, 16, 2)
+            with deepspeed.zero.GatheredParameters(list(model.parameters()), modifier_rank=0):
+                if dist.get_rank() == 0:
+                    model.load_state_dict(ref_sd)
+            engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=model.parameters())
+            out_dir = os.path.join(str(tmp_path), f"export_{gather}")
+            engine.save_fp16_model(out_dir, "weights.bin")
+            dist.barrier()
+            path = os.path.join(out_dir, "weights.bin")
+            if not gather:
+                assert not os.path.exists(path)
+                continue
+            if dist.get_rank() == 0:
+                sd = torch.load(path, weights_only=False)
+                assert set(sd.keys()) == set(ref_sd.keys())
+                for k in ref_sd:
+                    assert sd[k].shape == ref_sd[k].shape and torch.allclose(sd[k].float(), ref_sd[k], atol=1e-6), k
+            dist.barrier()
+    run()
+
+
+def test_memory_efficient_linear_matches_f_linear():
+    """zero.Init(mem_efficient_linear=True) routes F.linear through LinearFunctionForZeroStage3 (saves parameter ids,
+    not tensors, reference zero/linear.py:29-99): same forward and gradients as torch's own linear."""
+    from deeperspeed_b200.runtime.zero.linear import LinearFunctionForZeroStage3, LinearModuleForZeroStage3
+    torch.manual_seed(0)
+    x = torch.randn(3, 5, 8, requires_grad=True)
+    w = torch.randn(6, 8, requires_grad=True)
+    b = torch.randn(6, requires_grad=True)
+    out = LinearFunctionForZeroStage3.apply(x, w, b)
+    g = torch.randn_like(out)
+    out.backward(g)
+    x2, w2, b2 = (t.detach().clone().requires_grad_() for t in (x, w, b))
+    ref = torch.nn.functional.linear(x2, w2, b2)
+    ref.backward(g)
+    assert torch.allclose(out, ref, atol=1e-6)
+    for a, r in ((x, x2), (w, w2), (b, b2)):
+        assert torch.allclose(a.grad, r.grad, atol=1e-5)
+    mod = LinearModuleForZeroStage3(8, 6)
+    y = mod(x.detach())
+    assert y.shape == (3, 5, 6) and torch.allclose(y, torch.nn.functional.linear(x.detach(), mod.weight, mod.bias), atol=1e-6)
