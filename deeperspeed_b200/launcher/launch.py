@@ -96,7 +96,10 @@ def main(args=None):
             except Exception:
                 pass
         if last_return_code is not None:
-            raise subprocess.CalledProcessError(returncode=last_return_code, cmd=cmd)
+            # the reference raises CalledProcessError here, which makes the launcher itself exit with 1; handing the
+            # failed rank's own code to the caller (runner / scheduler) is more useful
+            logger.error(f"{cmd} exited with code {last_return_code}; siblings killed")
+            sys.exit(last_return_code if 0 < last_return_code < 256 else 1)
         if signum in sig_names:
             logger.info(f"Main process received {sig_names[signum]}, exiting")
         sys.exit(1)

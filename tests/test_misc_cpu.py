@@ -237,3 +237,40 @@ def test_timer_chrome_trace_export(tmp_path):
     assert {e["name"] for e in spans} == {"forward", "step"} and all(e["pid"] == 1 for e in spans)
     fw = sorted(e["ts"] for e in spans if e["name"] == "forward")
     assert fw[0] < fw[1] < fw[2] and all(e["dur"] >= 0 for e in spans)
+
+
+def test_launch_spawns_ranks_and_propagates_failure(tmp_path):
+    """launcher/launch.py end to end on this host: two local ranks rendezvous over gloo with the environment the
+    launcher sets; when one rank fails, its sibling is killed and the exit code is propagated
+    (reference launcher/launch.py:139-175)."""
+    import base64
+    import json
+    import subprocess
+    import sys
+    import time
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ok_script = tmp_path / "ok.py"
+    ok_script.write_text(
+        "import os, torch, torch.distributed as dist\n"
+        "dist.init_process_group('gloo')\n"
+        "t = torch.tensor([float(os.environ['RANK']) + 1.0])\n"
+        "dist.all_reduce(t)\n"
+        "assert int(os.environ['WORLD_SIZE']) == 2 and os.environ['LOCAL_RANK'] == os.environ['RANK']\n"
+        "open(os.path.join(os.path.dirname(__file__), 'out%s.txt' % os.environ['RANK']), 'w').write(str(t.item()))\n")
+    bad_script = tmp_path / "bad.py"
+    bad_script.write_text(
+        "import os, sys, time\n"
+        "if os.environ['RANK'] == '1':\n"
+        "    sys.exit(7)\n"
+        "time.sleep(120)\n")
+    world = base64.urlsafe_b64encode(json.dumps({"localhost": [0, 1]}).encode()).decode()
+    env = dict(os.environ, PYTHONPATH=repo + os.pathsep + os.environ.get("PYTHONPATH", ""))
+    base = [sys.executable, "-u", "-m", "deeperspeed_b200.launcher.launch", f"--world_info={world}",
+            "--master_addr=127.0.0.1"]
+    r = subprocess.run(base + ["--master_port=29677", str(ok_script)], env=env, cwd=repo, capture_output=True, timeout=120)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    assert (tmp_path / "out0.txt").read_text() == "3.0" and (tmp_path / "out1.txt").read_text() == "3.0"
+    t0 = time.time()
+    r = subprocess.run(base + ["--master_port=29678", str(bad_script)], env=env, cwd=repo, capture_output=True, timeout=100)
+    assert r.returncode == 7, (r.returncode, r.stderr.decode()[-2000:])
+    assert time.time() - t0 < 60, "the surviving rank was not killed"
