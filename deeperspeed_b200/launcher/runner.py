@@ -144,6 +144,9 @@ def main(args=None):
     if not resource_pool:
         resource_pool = {}
         device_count = torch.cuda.device_count()
+        if device_count == 0 and args.num_gpus > 0:
+            # CPU-only host (gloo back end): --num_gpus then simply says how many local processes to start
+            device_count = args.num_gpus
         if device_count == 0:
             raise RuntimeError("Unable to proceed, no GPU resources available")
         resource_pool["localhost"] = device_count
