@@ -10,10 +10,35 @@ on purpose: it is copied into every checkpoint directory."""
 import argparse
 import glob
 import os
+import pickle
 import re
+import types
 from collections import OrderedDict
 
 import torch
+
+
+class _TolerantUnpickler(pickle.Unpickler):
+    """The optimizer files pickle a few framework objects (loss scalers). This script only needs the tensors, so a
+    class that cannot be imported (the framework is not installed where the checkpoint was moved to) becomes an empty
+    stand-in instead of an ImportError."""
+
+    def find_class(self, mod_name, name):
+        try:
+            return super().find_class(mod_name, name)
+        except (ImportError, AttributeError):
+            def _setstate(self, state):
+                if isinstance(state, dict):
+                    self.__dict__.update(state)
+            return type(name, (), {"__module__": mod_name, "__setstate__": _setstate})
+
+
+_tolerant_pickle = types.SimpleNamespace(Unpickler=_TolerantUnpickler, load=pickle.load, loads=pickle.loads,
+                                         __name__="pickle")
+
+
+def _load(path):
+    return torch.load(path, map_location="cpu", weights_only=False, pickle_module=_tolerant_pickle)
 
 
 def _rank_key(path):
@@ -48,7 +73,7 @@ def _take_params(flat, param_shapes, state_dict, aligned):
 
 def convert_zero_chkpt_to_fp32_consolid_state_dict(checkpoint_dir, output_file=None):
     files = get_optim_files(checkpoint_dir)
-    sds = [torch.load(f, map_location="cpu", weights_only=False) for f in files]
+    sds = [_load(f) for f in files]
     osd = [sd["optimizer_state_dict"] for sd in sds]
     stage = osd[0]["zero_stage"]
     world = osd[0]["partition_count"]

@@ -258,3 +258,34 @@ def test_dynamic_loss_scale_overflow_skips(tmp_path):
             loss = engine(x, y); engine.backward(loss); engine.step()
         assert not opt.overflow and opt.cur_scale == 2.0 ** 8
     run()
+
+
+def test_zero_to_fp32_script_runs_standalone_from_checkpoint_dir(tmp_path):
+    """The recovery script copied next to every ZeRO checkpoint works as a plain command, also where this package is
+    not importable (the pickled loss-scaler objects are stubbed): `python zero_to_fp32.py . out.bin`."""
+    import subprocess
+    import sys
+
+    @distributed_test(world_size=2)
+    def save():
+        torch.manual_seed(42)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(2)), model=model,
+                                               model_parameters=model.parameters())
+        _train(engine, 2)
+        engine.save_checkpoint(str(tmp_path), tag="final")
+        if dist.get_rank() == 0:
+            torch.save({k: v.detach().float().clone() for k, v in model.state_dict().items()},
+                       os.path.join(str(tmp_path), "expected.pt"))
+    save()
+    tag_dir = os.path.join(str(tmp_path), "final")
+    assert os.path.isfile(os.path.join(tag_dir, "zero_to_fp32.py"))
+    env = {k: v for k, v in os.environ.items() if k != "PYTHONPATH"}
+    out = os.path.join(str(tmp_path), "consolidated.bin")
+    r = subprocess.run([sys.executable, "zero_to_fp32.py", ".", out], cwd=tag_dir, env=env, capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    got = torch.load(out, weights_only=False)
+    want = torch.load(os.path.join(str(tmp_path), "expected.pt"))
+    assert set(got.keys()) == set(want.keys())
+    for k in want:
+        assert torch.allclose(got[k].float(), want[k], atol=1e-6), k
