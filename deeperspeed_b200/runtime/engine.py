@@ -150,19 +150,33 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
 
     # ------------------------------------------------------------------ DeeperSpeed extras
     def register_forward_hook(self, layers_to_hook, layer_name_pattern="transformerlayer"):
-        """Capture the outputs of the selected transformer layers into `self.layer_outputs[idx]`."""
+        """DeeperSpeed extra (reference runtime/engine.py:226-254): forward hooks on every module whose class name
+        matches `layer_name_pattern`; after a forward, `self.layer_outputs[key]` holds the (CPU) outputs of the layers
+        selected by `layers_to_hook` (a list of `layer_number`s, or "all"). key = module.layer_number when the
+        module has one, else its position among the matching modules. `self.layers_to_hook` can be changed between
+        calls without re-registering (PipelineEngine.train_batch / eval_batch / inference_batch do that)."""
+        import re
         for h in self._hook_handles:
             h.remove()
         self._hook_handles = []
         self.layer_outputs = {}
+        self.layers_to_hook = layers_to_hook
+        pattern = re.compile(layer_name_pattern, re.IGNORECASE)
         idx = 0
         for name, module in self.module.named_modules():
-            if layer_name_pattern.lower() in module.__class__.__name__.lower():
-                if layers_to_hook == "all" or idx in layers_to_hook:
-                    def _hook(mod, inp, out, _idx=idx):
-                        self.layer_outputs[_idx] = out[0] if isinstance(out, (tuple, list)) else out
-                    self._hook_handles.append(module.register_forward_hook(_hook))
+            if pattern.search(module.__class__.__name__):
+                def _hook(mod, inp, out, _idx=idx):
+                    key = getattr(mod, "layer_number", _idx)
+                    want = self.layers_to_hook
+                    if not (want == "all" or (want and int(key) in want)):
+                        return
+                    outs = out if isinstance(out, (tuple, list)) else (out,)
+                    self.layer_outputs[key] = [o.detach().cpu() if torch.is_tensor(o) else o for o in outs]
+                self._hook_handles.append(module.register_forward_hook(_hook))
                 idx += 1
+
+    def swap_tensor_config(self):
+        return getattr(self._config, "swap_tensor_config", None)
 
     def autotune_gemms(self, tokens_per_micro_batch, iters=7, verbose=False):
         """Time every GEMM kernel variant (single-CTA / CTA-pair / tail-wave K split) for the linear layers of this

@@ -182,9 +182,32 @@ class PipelineEngine(PipeExecMixin, DeepSpeedEngine):
         self.num_pipe_buffers = num_buffers
 
     # ------------------------------------------------------------------ public batch APIs
-    def train_batch(self, data_iter=None):
+    def _hooked(self, layers_to_hook):
+        """Context for the `layers_to_hook` argument of the batch APIs (reference pipe/engine.py:292-293,346-347)."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def ctx():
+            if layers_to_hook is None:
+                yield
+                return
+            if not self._hook_handles:
+                self.register_forward_hook(layers_to_hook)
+            self.layers_to_hook = layers_to_hook
+            self.layer_outputs = {}
+            try:
+                yield
+            finally:
+                self.layers_to_hook = []
+        return ctx()
+
+    def train_batch(self, data_iter=None, layers_to_hook=None):
         """Progress the pipeline to train the next batch of data (gradient_accumulation_steps micro-batches).
         Returns the loss averaged over micro-batches and data-parallel replicas."""
+        with self._hooked(layers_to_hook):
+            return self._train_batch(data_iter)
+
+    def _train_batch(self, data_iter=None):
         if not torch._C.is_grad_enabled():
             raise RuntimeError("train_batch() requires gradients enabled. Use eval_batch() instead.")
         if data_iter is not None:
@@ -226,8 +249,12 @@ class PipelineEngine(PipeExecMixin, DeepSpeedEngine):
                 logger.info(" | ".join(f"{k}: {v:.2f}" for k, v in self.timer_values.items()))
         return self.agg_train_loss
 
-    def eval_batch(self, data_iter, return_logits=False):
+    def eval_batch(self, data_iter, return_logits=False, layers_to_hook=None):
         """Evaluate the pipeline on a batch of data (no gradients, no optimizer step)."""
+        with self._hooked(layers_to_hook):
+            return self._eval_batch(data_iter, return_logits)
+
+    def _eval_batch(self, data_iter, return_logits=False):
         self.eval_return_logits = return_logits
         self.module.eval()
         self.total_loss = None
@@ -248,7 +275,11 @@ class PipelineEngine(PipeExecMixin, DeepSpeedEngine):
             return self.agg_eval_loss, outputs
         return self.agg_eval_loss
 
-    def inference_batch(self, data_iter):
+    def inference_batch(self, data_iter, layers_to_hook=None):
+        with self._hooked(layers_to_hook):
+            return self._inference_batch(data_iter)
+
+    def _inference_batch(self, data_iter):
         """Run one forward-only micro-batch through the pipeline and return (logits, presents) on every rank of the
         pipe group (broadcast from the last stage). Shapes may vary call to call, so the meta handshake is redone."""
         self.module.eval()

@@ -851,3 +851,38 @@ def test_memory_efficient_linear_matches_f_linear():
     mod = LinearModuleForZeroStage3(8, 6)
     y = mod(x.detach())
     assert y.shape == (3, 5, 6) and torch.allclose(y, torch.nn.functional.linear(x.detach(), mod.weight, mod.bias), atol=1e-6)
+
+
+def test_pipeline_batch_apis_capture_layer_outputs(tmp_path):
+    """DeeperSpeed extra: train_batch / eval_batch(layers_to_hook=...) leave the selected layers' outputs in
+    engine.layer_outputs (reference pipe/engine.py:264-411, runtime/engine.py:226-254)."""
+    import deeperspeed_b200 as deepspeed
+    from deeperspeed_b200.pipe import PipelineModule, LayerSpec
+    from simple_model import args_from_dict, random_dataset
+
+    class TransformerLayerStandIn(torch.nn.Linear):     # class name matches the default "transformerlayer" pattern
+        pass
+
+    @distributed_test(world_size=2)
+    def run():
+        hid = 8
+        torch.manual_seed(0)
+        layers = [LayerSpec(TransformerLayerStandIn, hid, hid) for _ in range(4)]
+        model = PipelineModule(layers=layers, num_stages=2, loss_fn=lambda o, y: torch.nn.functional.cross_entropy(o.float(), y))
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-3}}}
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=[p for p in model.parameters() if p.requires_grad])
+        loader = deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(random_dataset(64, hid), batch_size=2))
+        it = iter(loader)
+        engine.train_batch(data_iter=it)
+        assert engine.layer_outputs == {}                      # nothing asked for, nothing kept
+        engine.train_batch(data_iter=it, layers_to_hook="all")
+        assert sorted(engine.layer_outputs.keys()) == [0, 1]   # this stage owns two of the four layers
+        out0 = engine.layer_outputs[0]
+        assert isinstance(out0, list) and out0[0].shape == (2, hid) and out0[0].device.type == "cpu"
+        engine.eval_batch(it, layers_to_hook=[1])
+        assert list(engine.layer_outputs.keys()) == [1]
+        assert engine.layers_to_hook == []
+        assert engine.swap_tensor_config() is None or engine.swap_tensor_config() is not False
+    run()
