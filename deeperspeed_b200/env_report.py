@@ -75,3 +75,11 @@ def main():
 
 if __name__ == "__main__":
     main()
+
+
+def ninja_installed():
+    try:
+        import ninja  # noqa: F401
+    except ImportError:
+        return False
+    return True

@@ -114,6 +114,24 @@ class DeepSpeedFlopsProfilerConfig(DeepSpeedConfigObject):
             setattr(self, k, a.get(k, v))
 
 
+class DeepSpeedConfigWriter:
+    """Build / load / write a config JSON programmatically (reference runtime/config.py:519-533)."""
+
+    def __init__(self, data=None):
+        self.data = data if data is not None else {}
+
+    def add_config(self, key, value):
+        self.data[key] = value
+
+    def load_config(self, filename):
+        with open(filename, "r") as f:
+            self.data = json.load(f, object_pairs_hook=dict_raise_error_on_duplicate_keys)
+
+    def write_config(self, filename):
+        with open(filename, "w") as outfile:
+            json.dump(self.data, outfile)
+
+
 def get_aio_config(param_dict):
     a = param_dict.get(C.AIO, {}) or {}
     return {k: a.get(k, v) for k, v in C.AIO_DEFAULTS.items()}

@@ -156,3 +156,10 @@ ROUTE_ENCODE = "encode"
 
 TORCH_DISTRIBUTED_DEFAULT_PORT = 29500
 DEFAULT_PROCESS_GROUP_TIMEOUT_MINUTES = 30
+
+
+class ValidationMode:
+    """Checkpoint tag validation modes (reference runtime/constants.py:323-326)."""
+    WARN = "WARN"
+    IGNORE = "IGNORE"
+    FAIL = "FAIL"

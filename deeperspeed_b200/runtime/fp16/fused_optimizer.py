@@ -138,3 +138,11 @@ class FP16_Optimizer(FlatMixedPrecisionOptimizer):
 
     def __repr__(self):
         return repr(self.optimizer)
+
+
+def is_fp16_fused_supported_optimizer(optimizer):
+    """Is `optimizer` one FP16_Optimizer drives through its fused path (reference fp16/fused_optimizer.py:35-51)?"""
+    from ...ops.adam import FusedAdam
+    if isinstance(optimizer, (FusedAdam, torch.optim.Adam, torch.optim.AdamW)):
+        return True
+    return optimizer.__class__.__name__.lower() == "onebitadam"

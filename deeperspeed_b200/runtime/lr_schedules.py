@@ -75,6 +75,21 @@ def override_params(args, params, keys):
             params[k] = getattr(args, k)
 
 
+def override_lr_range_test_params(args, params):
+    override_params(args, params, [LR_RANGE_TEST_MIN_LR, LR_RANGE_TEST_STEP_RATE, LR_RANGE_TEST_STEP_SIZE,
+                                   LR_RANGE_TEST_STAIRCASE])
+
+
+def override_1cycle_params(args, params):
+    override_params(args, params, [CYCLE_FIRST_STEP_SIZE, CYCLE_FIRST_STAIR_COUNT, CYCLE_SECOND_STEP_SIZE,
+                                   CYCLE_SECOND_STAIR_COUNT, DECAY_STEP_SIZE, CYCLE_MIN_LR, CYCLE_MAX_LR, DECAY_LR_RATE,
+                                   CYCLE_MIN_MOM, CYCLE_MAX_MOM, DECAY_MOM_RATE])
+
+
+def override_warmupLR_params(args, params):
+    override_params(args, params, [WARMUP_MIN_LR, WARMUP_MAX_LR, WARMUP_NUM_STEPS])
+
+
 def get_config_from_args(args):
     if not hasattr(args, LR_SCHEDULE) or args.lr_schedule is None:
         return None, "--{} not specified on command line".format(LR_SCHEDULE)

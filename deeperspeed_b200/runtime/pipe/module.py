@@ -235,6 +235,10 @@ class PipelineModule(nn.Module):
         self._local_stop = stop
 
     # ------------------------------------------------------------------ forward
+    def set_checkpoint_interval(self, interval):
+        assert interval >= 0
+        self.activation_checkpoint_interval = interval
+
     def forward(self, forward_input):
         # micro_offset keeps layer seeds distinct across micro-batches (dropout) when seed_layers is on
         self.micro_offset += 1

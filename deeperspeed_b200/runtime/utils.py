@@ -433,6 +433,13 @@ class GradientNoiseScale:
         self.model_parallel = mpu is not None
         self.mpu = mpu
 
+    def ema(self, avg, yi, i):
+        """Exponential moving average with bias correction: returns (new raw average, corrected value)."""
+        if avg is None:
+            avg = 0
+        avg = self.beta * avg + (1 - self.beta) * yi
+        return avg, avg / (1 - self.beta ** (i + 1))
+
     def flatten_grads(self):
         grads = []
         module = getattr(self.model, "module", self.model)

@@ -93,3 +93,55 @@ def test_cli_entry_points_exist():
     for exe in ("deepspeed", "ds", "ds_report", "ds_elastic", "ds_ssh"):
         path = os.path.join(root, "bin", exe)
         assert os.path.isfile(path) and os.access(path, os.X_OK), path
+
+
+def test_reference_module_paths_and_helper_names(tmp_path):
+    """Import paths and helper names that code written against the reference may touch (found by diffing the public
+    names of every reference module against this package)."""
+    import importlib
+    import torch
+    for mod in ("constants", "runtime.config_utils", "runtime.zero.constants", "runtime.zero.offload_constants",
+                "runtime.zero.offload_config", "runtime.zero.utils", "runtime.activation_checkpointing.config",
+                "profiling.constants", "profiling.config", "ops.adam.multi_tensor_apply"):
+        importlib.import_module("deeperspeed_b200." + mod)
+    from deeperspeed_b200.constants import default_pg_timeout
+    assert default_pg_timeout.total_seconds() == 30 * 60
+    from deeperspeed_b200.runtime.zero.constants import ZERO_OPTIMIZATION_REDUCE_BUCKET_SIZE_DEFAULT, ZERO_OPTIMIZATION_STAGE
+    assert ZERO_OPTIMIZATION_REDUCE_BUCKET_SIZE_DEFAULT == int(5e8) and ZERO_OPTIMIZATION_STAGE == "stage"
+    from deeperspeed_b200.runtime.zero.offload_config import get_offload_optimizer_config, get_offload_param_config
+    cfg = get_offload_optimizer_config({"offload_optimizer": {"device": "nvme", "pipeline_read": True}})
+    assert cfg["device"] == "nvme" and cfg["pipeline"] is True and cfg["buffer_count"] == 4
+    assert get_offload_param_config({}) is None
+    from deeperspeed_b200.runtime.zero.utils import is_zero_supported_optimizer
+    p = torch.nn.Parameter(torch.zeros(2))
+    assert is_zero_supported_optimizer(torch.optim.Adam([p])) and not is_zero_supported_optimizer(torch.optim.SGD([p], lr=0.1))
+    from deeperspeed_b200.runtime.config import DeepSpeedConfigWriter
+    w = DeepSpeedConfigWriter()
+    w.add_config("train_batch_size", 8)
+    w.write_config(str(tmp_path / "c.json"))
+    w2 = DeepSpeedConfigWriter()
+    w2.load_config(str(tmp_path / "c.json"))
+    assert w2.data == {"train_batch_size": 8}
+    from deeperspeed_b200.runtime.constants import ValidationMode
+    assert (ValidationMode.WARN, ValidationMode.IGNORE, ValidationMode.FAIL) == ("WARN", "IGNORE", "FAIL")
+    from deeperspeed_b200.runtime.fp16.fused_optimizer import is_fp16_fused_supported_optimizer
+    assert is_fp16_fused_supported_optimizer(torch.optim.Adam([p]))
+    from deeperspeed_b200.runtime.lr_schedules import override_1cycle_params, override_warmupLR_params
+    import argparse
+    params = {}
+    override_1cycle_params(argparse.Namespace(cycle_min_lr=0.01, cycle_max_lr=None), params)
+    assert params == {"cycle_min_lr": 0.01}
+    override_warmupLR_params(argparse.Namespace(warmup_num_steps=7), params)
+    assert params["warmup_num_steps"] == 7
+    from deeperspeed_b200.runtime.utils import GradientNoiseScale
+    gns = GradientNoiseScale.__new__(GradientNoiseScale)
+    gns.beta = 0.9
+    raw, corrected = gns.ema(None, 2.0, 0)
+    assert abs(raw - 0.2) < 1e-9 and abs(corrected - 2.0) < 1e-9
+    from deeperspeed_b200.ops.adam.multi_tensor_apply import MultiTensorApply
+    assert MultiTensorApply(64)(lambda chunk, flag, lists, x: (chunk, x), None, [[]], 5) == (64, 5)
+    from deeperspeed_b200.ops.module_inject import revert_module, replace_module  # noqa: F401
+    from deeperspeed_b200.env_report import ninja_installed
+    assert isinstance(ninja_installed(), bool)
+    from deeperspeed_b200.pipe import PipelineModule, LayerSpec
+    assert hasattr(PipelineModule, "set_checkpoint_interval")
