@@ -371,3 +371,99 @@ class DeepSpeedConfig:
                 logger.info("  {} {} {}".format(arg, "." * (29 - len(arg)), getattr(self, arg)))
         logger.info("  json = {}".format(json.dumps(self._param_dict, sort_keys=True, indent=4,
                                                     cls=ScientificNotationEncoder, separators=(",", ":"))))
+
+
+# ---- module-level getters of the reference (runtime/config.py:45-516) ------------------------------------------------
+# The reference parses every key with a free function `get_<name>(param_dict)`; here one parser fills DeepSpeedConfig
+# and the free functions read the attribute it produced, so both spellings always agree.
+def _parsed(param_dict):
+    cfg = DeepSpeedConfig.__new__(DeepSpeedConfig)
+    cfg._param_dict = param_dict
+    cfg._initialize_params(param_dict)
+    return cfg
+
+
+def _getter(attr, post=None):
+    def get(param_dict):
+        v = getattr(_parsed(param_dict), attr)
+        return post(v) if post else v
+    get.__name__ = "get_" + attr
+    return get
+
+
+get_pld_enabled = _getter("pld_enabled")
+get_pld_params = _getter("pld_params")
+get_amp_enabled = _getter("amp_enabled")
+get_amp_params = _getter("amp_params")
+get_fp16_enabled = _getter("fp16_enabled")
+get_fp16_type = _getter("precision", lambda p: {torch.float16: "fp16", torch.bfloat16: "bfloat16"}.get(p, "fp32"))
+get_loss_scale = _getter("loss_scale")
+get_initial_dynamic_scale = _getter("initial_dynamic_scale")
+get_dynamic_loss_scale_args = _getter("dynamic_loss_scale_args")
+get_gradient_accumulation_steps = _getter("gradient_accumulation_steps")
+get_sparse_gradients_enabled = _getter("sparse_gradients_enabled")
+get_zero_optimization = _getter("zero_enabled")
+get_zero_reduce_scatter = _getter("zero_config", lambda z: z.reduce_scatter)
+get_allreduce_always_fp32 = _getter("fp32_allreduce")
+get_prescale_gradients = _getter("prescale_gradients")
+get_gradient_predivide_factor = _getter("gradient_predivide_factor")
+get_steps_per_print = _getter("steps_per_print")
+get_disable_allgather = _getter("disable_allgather")
+get_dump_state = _getter("dump_state")
+get_gradient_clipping = _getter("gradient_clipping")
+get_optimizer_name = _getter("optimizer_name")
+get_optimizer_params = _getter("optimizer_params")
+get_optimizer_legacy_fusion = _getter("optimizer_legacy_fusion")
+get_zero_allow_untested_optimizer = _getter("zero_allow_untested_optimizer")
+get_scheduler_name = _getter("scheduler_name")
+get_scheduler_params = _getter("scheduler_params")
+get_train_batch_size = _getter("train_batch_size")
+get_train_micro_batch_size_per_gpu = _getter("train_micro_batch_size_per_gpu")
+get_wall_clock_breakdown = _getter("wall_clock_breakdown")
+get_memory_breakdown = _getter("memory_breakdown")
+get_tensorboard_enabled = _getter("tensorboard_enabled")
+get_tensorboard_output_path = _getter("tensorboard_output_path")
+get_tensorboard_job_name = _getter("tensorboard_job_name")
+
+
+def get_optimizer_gradient_clipping(param_dict):
+    params = get_optimizer_params(param_dict)
+    return params.get("max_grad_norm", None) if params else None
+
+
+def get_checkpoint_params(param_dict):
+    return param_dict.get(C.CHECKPOINT, {})
+
+
+def get_checkpoint_tag_validation_mode(checkpoint_params):
+    mode = str(checkpoint_params.get(C.CHECKPOINT_TAG_VALIDATION, C.CHECKPOINT_TAG_VALIDATION_DEFAULT)).upper()
+    if mode not in C.CHECKPOINT_TAG_VALIDATION_MODES:
+        raise DeepSpeedConfigError(f"Checkpoint config contains invalid tag_validation value of {mode}, "
+                                   f"expecting one of {C.CHECKPOINT_TAG_VALIDATION_MODES}")
+    return mode
+
+
+def get_sparse_attention_mode(param_dict):
+    return param_dict.get(C.SPARSE_MODE, C.SPARSE_MODE_DEFAULT)
+
+
+def get_sparse_attention_type(param_dict):
+    return param_dict.get("attention", "bidirectional")
+
+
+def _sparse_mode_config(mode):
+    def get(sparsity):
+        out = {C.SPARSE_MODE: mode, C.SPARSE_BLOCK: sparsity.get(C.SPARSE_BLOCK, C.SPARSE_BLOCK_DEFAULT)}
+        if mode != C.SPARSE_DENSE_MODE:
+            out["different_layout_per_head"] = sparsity.get("different_layout_per_head", False)
+        for k, v in _SPARSE_KEYS[mode].items():
+            out[k] = sparsity.get(k, v)
+        return out
+    return get
+
+
+get_sparse_dense_config = _sparse_mode_config(C.SPARSE_DENSE_MODE)
+get_sparse_fixed_config = _sparse_mode_config(C.SPARSE_FIXED_MODE)
+get_sparse_variable_config = _sparse_mode_config(C.SPARSE_VARIABLE_MODE)
+get_sparse_bigbird_config = _sparse_mode_config(C.SPARSE_BIGBIRD_MODE)
+get_sparse_bslongformer_config = _sparse_mode_config(C.SPARSE_BSLONGFORMER_MODE)

@@ -145,3 +145,28 @@ def test_reference_module_paths_and_helper_names(tmp_path):
     assert isinstance(ninja_installed(), bool)
     from deeperspeed_b200.pipe import PipelineModule, LayerSpec
     assert hasattr(PipelineModule, "set_checkpoint_interval")
+
+
+def test_config_free_getters_agree_with_the_config_object():
+    """The reference's `get_<key>(param_dict)` free functions (runtime/config.py:45-516) exist and return what
+    DeepSpeedConfig parses."""
+    from deeperspeed_b200.runtime import config as c
+    d = {"train_batch_size": 8, "fp16": {"enabled": True, "loss_scale": 0, "initial_scale_power": 10},
+         "optimizer": {"type": "Adam", "params": {"lr": 1e-3, "max_grad_norm": 1.0}},
+         "scheduler": {"type": "WarmupLR", "params": {"warmup_num_steps": 5}},
+         "zero_optimization": {"stage": 2}, "gradient_clipping": 0.5, "checkpoint": {"tag_validation": "fail"},
+         "tensorboard": {"enabled": True, "output_path": "/tmp/tb"}, "steps_per_print": 7}
+    cfg = c.DeepSpeedConfig(None, param_dict=dict(d))
+    assert c.get_fp16_enabled(d) is True and c.get_fp16_type(d) == "fp16"
+    assert c.get_initial_dynamic_scale(d) == 1024 == cfg.initial_dynamic_scale
+    assert c.get_dynamic_loss_scale_args(d) == cfg.dynamic_loss_scale_args
+    assert c.get_optimizer_name(d) == "adam" and c.get_optimizer_params(d)["lr"] == 1e-3
+    assert c.get_optimizer_gradient_clipping(d) == 1.0 and c.get_gradient_clipping(d) == 0.5
+    assert c.get_scheduler_name(d) == "WarmupLR" and c.get_scheduler_params(d) == {"warmup_num_steps": 5}
+    assert c.get_zero_optimization(d) is True and c.get_zero_reduce_scatter(d) is True
+    assert c.get_checkpoint_tag_validation_mode(c.get_checkpoint_params(d)) == "FAIL"
+    assert c.get_tensorboard_enabled(d) and c.get_tensorboard_output_path(d) == "/tmp/tb"
+    assert c.get_steps_per_print(d) == 7 and c.get_train_batch_size(d) == 8
+    assert c.get_pld_enabled(d) is False and c.get_amp_enabled(d) is False and c.get_sparse_gradients_enabled(d) is False
+    assert c.get_sparse_fixed_config({"block": 32})["block"] == 32
+    assert c.get_sparse_bigbird_config({})["num_sliding_window_blocks"] == 3
