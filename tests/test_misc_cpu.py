@@ -56,6 +56,23 @@ def test_gpu_topology_parse():
     assert detect_nvlink_pairs(text) == [0, 2, 1, 3]
 
 
+def test_gpu_topology_reference_names():
+    """The reference's launcher/gpu_topology.py function names on top of the same parser."""
+    from deeperspeed_b200.launcher import gpu_topology as g
+    txt = ("        GPU0    GPU1    GPU2    GPU3    CPU Affinity\n"
+           "GPU0     X      SYS     NV2     SYS     0-15\n"
+           "GPU1    SYS      X      SYS     NV1     0-15\n"
+           "GPU2    NV2     SYS      X      SYS     16-31\n"
+           "GPU3    SYS     NV1     SYS      X      16-31\n\nLegend:\n  X = Self\n")
+    topo = g.topology_from_string(txt)
+    assert topo[0] == ["X", "SYS", "NV2", "SYS"] and len(topo) == 4
+    assert g.contains_nvlinks(topo) and g.is_nvlink("NV18") and not g.is_nvlink("SYS")
+    assert sorted(g.get_nvlink_pairs(topo)) == [(0, 2), (1, 3)]
+    assert g.get_cuda_visible_device_mapping(g.get_nvlink_pairs(topo)) == "0,2,1,3"
+    assert g.get_cuda_visible_device_mapping(g.get_nvlink_pairs(topo), local_gpu_ids=[1, 3]) == "1,3"
+    assert not g.contains_nvlinks([["X", "SYS"], ["SYS", "X"]])
+
+
 def test_csr_and_repeating_loader_and_pld():
     from deeperspeed_b200.runtime.csr_tensor import CSRTensor
     from deeperspeed_b200.runtime.progressive_layer_drop import ProgressiveLayerDrop
