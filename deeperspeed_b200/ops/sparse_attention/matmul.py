@@ -218,6 +218,11 @@ class MatMul:
         self.bench = bench
         self.lut = get_lut(layout, block)
 
+    def make_lut(self, dtype=None, device=None):
+        """The look-up tables of this layout (reference matmul.py:623-660 builds Triton-specific tables per dtype and
+        device; ours are built once, natively, and are dtype-independent). Returns the cached BlockSparseLUT."""
+        return self.lut
+
     def __call__(self, a, b):
         a, b = self._pad(a), self._pad(b)
         return _SparseMatMul.apply(a, b, self.mode, self.trans_a, self.trans_b, self.layout, self.block, self.lut)

@@ -75,6 +75,10 @@ class Softmax:
         self.bench = bench
         self.lut = get_lut(layout, block)
 
+    def make_lut(self, device=None):
+        """The look-up table of this layout (reference softmax.py:241-249); the same native table as MatMul's."""
+        return self.lut
+
     def __call__(self, x, scale=1., rpe=None, key_padding_mask=None, attn_mask=None, key_padding_mask_mode="add",
                  attn_mask_mode="add"):
         if rpe is not None and rpe.dtype != x.dtype:
