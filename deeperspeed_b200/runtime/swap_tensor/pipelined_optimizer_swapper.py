@@ -26,6 +26,10 @@ class PipelinedOptimizerSwapper(OptimizerSwapper):
 
     def _issue_read(self, parameter):
         info = self._get_param_swap_info(parameter)
+        if self._pending_write is not None and self._pending_write[0] is info:
+            # this very state is still on its way to the file (asynchronous swap-out of the previous step; with a
+            # single sub-group nothing else flushes it in between): reading now would return the old contents
+            self._flush_write()
         n = info.numel()
         bufs = []
         for path in info.swap_paths:

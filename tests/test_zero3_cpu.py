@@ -81,10 +81,12 @@ def test_stage3_matches_adamw(offload, tmp_path):
     run()
 
 
+@pytest.mark.parametrize("sub_group", [150, 40])      # one sub-group per rank / several
 @pytest.mark.parametrize("pipeline", [False, True])
-def test_stage3_nvme_offload_matches_adamw(pipeline, tmp_path):
+def test_stage3_nvme_offload_matches_adamw(pipeline, sub_group, tmp_path):
     """ZeRO-Infinity on files: optimizer state (and fp16 parameter shards) live under nvme_path and stream through the
-    async I/O engine sub-group by sub-group (reference swap_tensor/*, stage3.py:1569-1700); result equals AdamW."""
+    async I/O engine sub-group by sub-group (reference swap_tensor/*, stage3.py:1569-1700); result equals AdamW.
+    (The single-sub-group pipelined case once read a state file whose asynchronous write was still in flight.)"""
     @distributed_test(world_size=2)
     def run():
         nvme = os.path.join(str(tmp_path), "nvme")
@@ -94,7 +96,7 @@ def test_stage3_nvme_offload_matches_adamw(pipeline, tmp_path):
                "fp16": {"enabled": True, "type": "fp32"},
                "aio": {"block_size": 65536, "queue_depth": 4, "thread_count": 1, "single_submit": False,
                        "overlap_events": True},
-               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 20, "sub_group_size": 150,
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 20, "sub_group_size": sub_group,
                                      "offload_optimizer": {"device": "nvme", "nvme_path": nvme, "buffer_count": 4,
                                                            "pipeline_read": pipeline, "pipeline_write": pipeline},
                                      "offload_param": {"device": "nvme", "nvme_path": nvme, "buffer_count": 5,
