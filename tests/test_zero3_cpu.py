@@ -43,7 +43,7 @@ def test_tiled_linear_matches_linear():
         deepspeed.zero.TiledLinear(8, 8, in_splits=9)
 
 
-@pytest.mark.parametrize("offload", [False, True])
+@pytest.mark.parametrize("offload", [False, True, "params"])
 def test_stage3_matches_adamw(offload, tmp_path):
     @distributed_test(world_size=2)
     def run():
@@ -53,6 +53,8 @@ def test_stage3_matches_adamw(offload, tmp_path):
                "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 20}}
         if offload:
             cfg["zero_optimization"]["offload_optimizer"] = {"device": "cpu"}
+        if offload == "params":   # parameter shards on the host as well (ZeRO-3 Offload)
+            cfg["zero_optimization"]["offload_param"] = {"device": "cpu", "pin_memory": False}
         torch.manual_seed(42)
         model = SimpleModel(HID)
         ref = SimpleModel(HID)
