@@ -886,3 +886,51 @@ def test_pipeline_batch_apis_capture_layer_outputs(tmp_path):
         assert engine.layers_to_hook == []
         assert engine.swap_tensor_config() is None or engine.swap_tensor_config() is not False
     run()
+
+
+@pytest.mark.parametrize("zero_stage", [0, 1])
+def test_pipeline_overflow_on_one_stage_skips_every_stage(zero_stage, tmp_path):
+    """A non-finite gradient on ONE pipeline stage must make every stage skip the step and lower the loss scale
+    together (overflow flag reduced over the pipe group, reference runtime/utils.py:65-175 via the mpu interface)."""
+    import deeperspeed_b200 as deepspeed
+    from simple_model import LinearStackPipe, args_from_dict, random_dataset
+
+    @distributed_test(world_size=2)
+    def run():
+        hid = 16
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-2}},
+               # real half precision; hysteresis 1 so that ZeRO's DynamicLossScaler lowers the scale on the first
+               # overflow like FP16_Optimizer's inline scaler does (SURVEY C.1: the two differ by default)
+               "fp16": {"enabled": True, "loss_scale": 0, "initial_scale_power": 8, "hysteresis": 1}}
+        if zero_stage:
+            cfg["zero_optimization"] = {"stage": zero_stage}
+        torch.manual_seed(3)
+        model = LinearStackPipe(input_dim=hid, hidden_dim=hid, output_dim=hid, num_layers=2, num_stages=2)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=[p for p in model.parameters() if p.requires_grad])
+        loader = deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(random_dataset(64, hid, dtype=torch.float16), batch_size=2))
+        it = iter(loader)
+        engine.train_batch(data_iter=it)
+        scale0 = engine.optimizer.cur_scale if hasattr(engine.optimizer, "cur_scale") else engine.optimizer.loss_scale
+        before = [p.detach().clone() for p in model.parameters()]
+        poison = {"on": engine.stage_id == 1}      # only the last stage produces a bad gradient
+
+        def bad(grad):
+            if poison["on"]:
+                g = grad.clone()
+                g.view(-1)[0] = float("inf")
+                return g
+            return grad
+        handle = next(p for p in model.parameters() if p.requires_grad).register_hook(bad)
+        engine.train_batch(data_iter=it)
+        handle.remove()
+        poison["on"] = False
+        assert engine.skipped_steps == 1, (engine.stage_id, engine.skipped_steps)
+        for p, b in zip(model.parameters(), before):
+            assert torch.equal(p.detach(), b), "a skipped step must not touch the parameters of any stage"
+        scale1 = engine.optimizer.cur_scale if hasattr(engine.optimizer, "cur_scale") else engine.optimizer.loss_scale
+        assert scale1 < scale0
+        engine.train_batch(data_iter=it)
+        assert engine.skipped_steps == 1 and any(not torch.equal(p.detach(), b) for p, b in zip(model.parameters(), before))
+    run()
