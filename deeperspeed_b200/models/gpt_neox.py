@@ -3,7 +3,8 @@ reference deepspeed/runtime/pipe/engine.py:185, pipe/module.py:585-587 — so th
 
 Layer math on the sm_100a kernel stack: fused LayerNorm(+residual) kernels, tcgen05 GEMMs with bias / bias+GeLU /
 bias+residual epilogues, in-place rotary kernel, fused cross-entropy (in-place gradient). Causal attention uses
-torch SDPA (library flash kernel). 1.3B preset: 24 layers, d_model 2048, 16 heads, seq 2048, vocab 50432."""
+the attention block op of ops/attention.py (library flash kernel by default, our tcgen05 flash-attention kernels with
+DSB_ATTN=native). 1.3B preset: 24 layers, d_model 2048, 16 heads, seq 2048, vocab 50432."""
 import math
 
 import torch
