@@ -289,3 +289,58 @@ def test_zero_to_fp32_script_runs_standalone_from_checkpoint_dir(tmp_path):
     assert set(got.keys()) == set(want.keys())
     for k in want:
         assert torch.allclose(got[k].float(), want[k], atol=1e-6), k
+
+
+@pytest.mark.parametrize("stage", [1, 2])
+def test_elastic_reload_world3_to_world2_continues_identically(stage, tmp_path):
+    """Elastic ZeRO checkpoints (padding-free shards, reference stage1.py:924-1098 / stage2.py:1685-1823): a run saved
+    on 3 ranks and resumed on 2 has the same master weights and Adam moments, i.e. the same next update as the run
+    that was never interrupted (same global batch, same data)."""
+    def cfg_for(world):
+        c = _cfg(stage)
+        c["train_batch_size"] = 12
+        c["train_micro_batch_size_per_gpu"] = 2
+        return c          # gas = 2 on 3 ranks, 3 on 2 ranks
+
+    data = torch.utils.data.TensorDataset(*random_dataset(48, HID, seed=99).tensors)
+
+    def batches(world, rank, gas, step):
+        """Micro-batches of global step `step` for this rank: the 12 samples of the step split rank-major."""
+        xs, ys = data.tensors
+        lo = step * 12
+        per_rank = 12 // world
+        sl = slice(lo + rank * per_rank, lo + (rank + 1) * per_rank)
+        return [(xs[sl][i * 2:(i + 1) * 2], ys[sl][i * 2:(i + 1) * 2]) for i in range(gas)]
+
+    def run_steps(engine, world, steps, first_step):
+        for s in range(first_step, first_step + steps):
+            for x, y in batches(world, dist.get_rank(), engine.gradient_accumulation_steps(), s):
+                loss = engine(x, y)
+                engine.backward(loss)
+                engine.step()
+
+    @distributed_test(world_size=3)
+    def save():
+        torch.manual_seed(7)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg_for(3)), model=model,
+                                               model_parameters=model.parameters())
+        run_steps(engine, 3, 2, 0)
+        engine.save_checkpoint(str(tmp_path), tag="w3")
+        run_steps(engine, 3, 1, 2)            # the uninterrupted run goes one step further
+        if dist.get_rank() == 0:
+            torch.save([p.detach().clone() for p in engine.module.parameters()], os.path.join(str(tmp_path), "w3_step3.pt"))
+    save()
+
+    @distributed_test(world_size=2)
+    def resume():
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg_for(2)), model=model,
+                                               model_parameters=model.parameters())
+        path, _ = engine.load_checkpoint(str(tmp_path), tag="w3")
+        assert path is not None and engine.global_steps == 2
+        run_steps(engine, 2, 1, 2)
+        want = torch.load(os.path.join(str(tmp_path), "w3_step3.pt"))
+        for p, w in zip(engine.module.parameters(), want):
+            assert torch.allclose(p.detach(), w, atol=2e-6), (p.detach() - w).abs().max()
+    resume()
