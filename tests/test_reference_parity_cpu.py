@@ -934,3 +934,34 @@ def test_pipeline_overflow_on_one_stage_skips_every_stage(zero_stage, tmp_path):
         engine.train_batch(data_iter=it)
         assert engine.skipped_steps == 1 and any(not torch.equal(p.detach(), b) for p, b in zip(model.parameters(), before))
     run()
+
+
+def test_pipeline_activation_checkpointing_config_block_matches_plain(tmp_path):
+    """The `activation_checkpointing` config block (CPU checkpointing on) with activation_checkpoint_interval=1 in a
+    2-stage pipeline gives the same parameters as the un-checkpointed run."""
+    import deeperspeed_b200 as deepspeed
+    from simple_model import LinearStackPipe, args_from_dict, random_dataset
+
+    @distributed_test(world_size=2)
+    def run():
+        hid = 16
+        finals = []
+        for interval, block in ((0, None), (1, {"partition_activations": False, "cpu_checkpointing": True,
+                                              "contiguous_memory_optimization": False, "profile": True})):
+            cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+                   "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}}
+            if block is not None:
+                cfg["activation_checkpointing"] = block
+            torch.manual_seed(5)
+            model = LinearStackPipe(input_dim=hid, hidden_dim=hid, output_dim=hid, num_layers=3, num_stages=2,
+                                    activation_checkpoint_interval=interval)
+            engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=[p for p in model.parameters() if p.requires_grad])
+            loader = deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(random_dataset(64, hid), batch_size=2))
+            it = iter(loader)
+            for _ in range(3):
+                engine.train_batch(data_iter=it)
+            finals.append([p.detach().clone() for p in model.parameters()])
+        for a, b in zip(*finals):
+            assert torch.allclose(a, b, atol=1e-6), (a - b).abs().max()
+    run()
