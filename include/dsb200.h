@@ -103,6 +103,12 @@ int dsb_softmax_bwd(const void* dy, const void* y, void* dx, long rows, int k_le
 int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
                        long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss,
                        long v_sh, long o_sb, long o_ss, long o_sh, float scale, int causal, int dtype, void* stream);
+/* Forward block shape: 64 = 64-key blocks, two CTAs per SM (default); 128 = 128-key blocks, one CTA per SM. Returns
+ * the previous setting; other values only query. */
+int dsb_flash_attn_fwd_variant(int keys_per_step);
+/* Debug aid: when `p` is not NULL, CTA (0, 0) of the following attention launches adds its clock64 phase totals to
+ * the 16 int64 at `p` ([0..4] softmax warp, [8..12] MMA thread, [15] blocks walked); NULL switches it off. */
+void dsb_flash_attn_debug_timers(long long* p);
 /* Backward of dsb_flash_attn_fwd: one CTA per (key block, batch, head) keeps K / V resident, walks the query blocks
  * and accumulates dV, dK in TMEM; dQ contributions are added to `dq_acc` ([B, S, H, 128] fp32, contiguous, zeroed by
  * the caller) with vector reductions. `strides`: 7 x (sb, ss, sh) for dO, q, k, v, out, dk, dv. `delta`: [B, H, S]
