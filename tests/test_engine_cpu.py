@@ -344,3 +344,33 @@ def test_elastic_reload_world3_to_world2_continues_identically(stage, tmp_path):
         for p, w in zip(engine.module.parameters(), want):
             assert torch.allclose(p.detach(), w, atol=2e-6), (p.detach() - w).abs().max()
     resume()
+
+
+@pytest.mark.parametrize("stage", [1, 2])
+def test_zero_bf16_world2_tracks_fp32(stage, tmp_path):
+    """fp16.type = bfloat16 (DeeperSpeed's bf16 mode, reference runtime/config.py:104-113: loss scale pinned to 1,
+    fp32 all-reduce) under ZeRO-1/2 at world 2: fp32 masters follow the fp32 run closely, replicas stay identical."""
+    @distributed_test(world_size=2)
+    def run():
+        cfg = _cfg(stage)
+        cfg["fp16"] = {"enabled": True, "type": "bfloat16"}
+        torch.manual_seed(42)
+        model = SimpleModel(HID)
+        engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                 model_parameters=model.parameters())
+        assert next(engine.module.parameters()).dtype == torch.bfloat16 and float(opt.loss_scale) == 1.0
+        dl = random_dataloader(engine, 64, HID, engine.device, dtype=torch.bfloat16, seed=dist.get_rank())
+        it = iter(dl)
+        for _ in range(3 * engine.gradient_accumulation_steps()):
+            x, y = next(it)
+            loss = engine(x, y)
+            engine.backward(loss)
+            engine.step()
+        ref = _reference_run(3, 2, 2)
+        flat = torch.cat([p.detach().float().view(-1) for p in engine.module.parameters()])
+        want = torch.cat([r.view(-1) for r in ref])
+        assert (flat - want).abs().max().item() < 0.05 and (flat - want).abs().mean().item() < 0.01
+        other = flat.clone()
+        dist.broadcast(other, src=0)
+        assert torch.equal(flat, other)
+    run()
