@@ -92,3 +92,44 @@ def test_cuda_graph_capture_of_neox_layer():
         assert torch.allclose(xg.grad.float(), xe.grad.float(), atol=2e-3, rtol=2e-3)
         for (n, a), b in zip(layer.named_parameters(), eager.parameters()):
             assert a.grad is not None and torch.allclose(a.grad.float(), b.grad.float(), atol=5e-3, rtol=5e-3), n
+
+
+@pytest.mark.parametrize("preln", [False, True])
+def test_module_injection_replace_and_revert_cpu(preln):
+    """module_inject: every BERT layer of a model is swapped for a DeepSpeedTransformerLayer carrying the same weights
+    (same outputs), and reverted to layers with the original weights (reference module_inject/replace_module.py,
+    ops/module_inject.py:8-216)."""
+    from deeperspeed_b200.models.bert import BertConfig, BertLayer, BertLayerPreLN
+    from deeperspeed_b200.module_inject import replace_transformer_layer, revert_transformer_layer
+    from deeperspeed_b200.ops.transformer import DeepSpeedTransformerLayer
+    torch.manual_seed(0)
+    bc = BertConfig(hidden_size=32, num_hidden_layers=2, num_attention_heads=4, hidden_dropout_prob=0.0,
+                    attention_probs_dropout_prob=0.0, layer_norm_eps=1e-5)
+    layer_cls = BertLayerPreLN if preln else BertLayer
+
+    class Encoder(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.layers = torch.nn.ModuleList([layer_cls(bc) for _ in range(2)])
+
+        def forward(self, x, mask):
+            for l in self.layers:
+                x = l(x, mask)
+                x = x[0] if isinstance(x, tuple) else x
+            return x
+
+    model = Encoder().eval()
+    original = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    x = torch.randn(2, 16, 32)
+    mask = torch.zeros(2, 1, 1, 16)
+    want = model(x, mask)
+    replace_transformer_layer(layer_cls, model, micro_batch_size=2, bert_config=bc, seed=1, max_seq_length=16,
+                              preln=preln, fp16=False)
+    assert all(isinstance(l, DeepSpeedTransformerLayer) for l in model.layers)
+    got = model.eval()(x, mask)
+    assert (got - want).abs().max().item() < 2e-4, (got - want).abs().max().item()
+    revert_transformer_layer(layer_cls, model, bc, preln=preln)
+    assert all(isinstance(l, layer_cls) for l in model.layers)
+    for k, v in model.state_dict().items():
+        assert torch.equal(v, original[k]), k
+    assert (model.eval()(x, mask) - want).abs().max().item() < 1e-6
