@@ -1,4 +1,5 @@
-"""BertSparseSelfAttention: q/k/v projections + SparseSelfAttention
+"""BertSparseSelfAttention: drop-in for the self-attention block of a BERT layer with block-sparse attention inside.
+Keeps the attribute names (`query`, `key`, `value`) that SparseAttentionUtils re-points at the original projections
 (reference deepspeed/ops/sparse_attention/bert_sparse_self_attention.py:16-78)."""
 from torch import nn
 
@@ -9,26 +10,26 @@ from .sparsity_config import FixedSparsityConfig
 class BertSparseSelfAttention(nn.Module):
     def __init__(self, config, sparsity_config=FixedSparsityConfig(num_heads=4)):
         super().__init__()
-        if config.hidden_size % config.num_attention_heads != 0:
-            raise ValueError("The hidden size (%d) is not a multiple of the number of attention heads (%d)" %
-                             (config.hidden_size, config.num_attention_heads))
-        self.num_attention_heads = config.num_attention_heads
-        self.attention_head_size = int(config.hidden_size / config.num_attention_heads)
-        self.all_head_size = self.num_attention_heads * self.attention_head_size
-        self.query = nn.Linear(config.hidden_size, self.all_head_size)
-        self.key = nn.Linear(config.hidden_size, self.all_head_size)
-        self.value = nn.Linear(config.hidden_size, self.all_head_size)
+        hidden, heads = config.hidden_size, config.num_attention_heads
+        if hidden % heads:
+            raise ValueError("The hidden size (%d) is not a multiple of the number of attention heads (%d)" % (hidden, heads))
+        self.num_attention_heads = heads
+        self.attention_head_size = hidden // heads
+        self.all_head_size = hidden
+        for name in ("query", "key", "value"):
+            setattr(self, name, nn.Linear(hidden, hidden))
         self.sparse_self_attention = SparseSelfAttention(sparsity_config)
 
     def transpose_for_scores(self, x):
-        new_x_shape = x.size()[:-1] + (self.num_attention_heads, self.attention_head_size)
-        return x.view(*new_x_shape).permute(0, 2, 1, 3)
+        """[batch, seq, hidden] -> [batch, heads, seq, head_size]"""
+        b, s, _ = x.shape
+        return x.view(b, s, self.num_attention_heads, self.attention_head_size).transpose(1, 2)
 
     def forward(self, hidden_states, attention_mask):
-        query_layer = self.transpose_for_scores(self.query(hidden_states)).contiguous()
-        key_layer = self.transpose_for_scores(self.key(hidden_states)).contiguous()
-        value_layer = self.transpose_for_scores(self.value(hidden_states)).contiguous()
-        context_layer = self.sparse_self_attention(query_layer, key_layer, value_layer, key_padding_mask=attention_mask)
-        context_layer = context_layer.permute(0, 2, 1, 3).contiguous()
-        new_context_layer_shape = context_layer.size()[:-2] + (self.all_head_size,)
-        return context_layer.view(*new_context_layer_shape)
+        """hidden_states [batch, seq, hidden]; attention_mask is used as the key padding mask. Returns the context in
+        the same [batch, seq, hidden] layout."""
+        q, k, v = (self.transpose_for_scores(proj(hidden_states)).contiguous()
+                   for proj in (self.query, self.key, self.value))
+        ctx = self.sparse_self_attention(q, k, v, key_padding_mask=attention_mask)     # [batch, heads, seq, head_size]
+        b, _, s, _ = ctx.shape
+        return ctx.transpose(1, 2).reshape(b, s, self.all_head_size)
