@@ -1,8 +1,11 @@
-"""SparseSelfAttention: SDD(QK^T) -> block-sparse softmax(scale, rpe, masks) -> DSD(P V).
-API per reference deepspeed/ops/sparse_attention/sparse_self_attention.py:14-174."""
+"""SparseSelfAttention: scores = SDD(Q K^T) on the layout's blocks, block-sparse softmax (scale, relative position
+embedding, key-padding and attention masks), context = DSD(P V).
+API per reference deepspeed/ops/sparse_attention/sparse_self_attention.py:14-174 (constructor arguments, `get_layout`,
+`get_ops`, mask handling, [batch, heads, seq, head_dim] operands). Unlike the reference, the per-length operator cache
+is keyed by the layout as well, so modules with different sparsity configs never pick up each other's operators."""
 import torch
-import torch.nn as nn
 import torch.distributed as dist
+import torch.nn as nn
 
 from .matmul import MatMul
 from .softmax import Softmax
@@ -10,72 +13,78 @@ from .sparsity_config import SparsityConfig
 
 
 class SparseSelfAttention(nn.Module):
-    ops = dict()
+    ops = dict()      # (seq_len, block, layout fingerprint) -> (sdd, dsd, softmax)
 
     def __init__(self, sparsity_config=SparsityConfig(num_heads=4), key_padding_mask_mode="add", attn_mask_mode="mul",
                  max_seq_length=2048):
         super().__init__()
         self.sparsity_config = sparsity_config
         self.max_seq_length = max_seq_length
-        master_layout = self.sparsity_config.make_layout(max_seq_length)
-        self.register_buffer("master_layout", master_layout)
-        self._need_layout_synchronization = True
         self.key_padding_mask_mode = key_padding_mask_mode
         self.attn_mask_mode = attn_mask_mode
+        # the layout for the longest sequence; shorter sequences use its top-left corner
+        self.register_buffer("master_layout", sparsity_config.make_layout(max_seq_length))
+        self._need_layout_synchronization = True
+
+    # ---- layout / operators
+    def _sync_layout_once(self):
+        """Layouts with random blocks (Variable, BigBird) must be identical on every rank: take rank 0's."""
+        if not self._need_layout_synchronization or not dist.is_initialized():
+            return
+        on_gpu = torch.cuda.is_available() and dist.get_backend() == "nccl"
+        buf = self.master_layout.to(torch.device("cuda", torch.cuda.current_device()) if on_gpu else "cpu")
+        dist.broadcast(buf, src=0)
+        self.master_layout.copy_(buf.to(self.master_layout.device))
+        self._need_layout_synchronization = False
 
     def get_layout(self, L):
-        # random layouts (Variable / BigBird) must agree across ranks: rank 0's layout is broadcast once
-        if self._need_layout_synchronization and dist.is_initialized():
-            dev = torch.device("cuda", torch.cuda.current_device()) if (torch.cuda.is_available() and dist.get_backend() == "nccl") else torch.device("cpu")
-            t = self.master_layout.to(dev)
-            dist.broadcast(t, src=0)
-            self.master_layout.copy_(t.to(self.master_layout.device))
-            self._need_layout_synchronization = False
-        if (L % self.sparsity_config.block != 0):
-            raise ValueError(f"Sequence Length, {L}, needs to be dividable by Block size {self.sparsity_config.block}!")
-        num_blocks = L // self.sparsity_config.block
-        return self.master_layout[..., :num_blocks, :num_blocks].cpu()
+        self._sync_layout_once()
+        block = self.sparsity_config.block
+        if L % block:
+            raise ValueError(f"Sequence Length, {L}, needs to be dividable by Block size {block}!")
+        n = L // block
+        return self.master_layout[..., :n, :n].cpu()
 
     def get_ops(self, H, L):
-        if L not in SparseSelfAttention.ops:
-            sparsity_layout = self.get_layout(L)
-            sparse_dot_sdd_nt = MatMul(sparsity_layout, self.sparsity_config.block, "sdd", trans_a=False, trans_b=True)
-            sparse_dot_dsd_nn = MatMul(sparsity_layout, self.sparsity_config.block, "dsd", trans_a=False, trans_b=False)
-            sparse_softmax = Softmax(sparsity_layout, self.sparsity_config.block)
-            SparseSelfAttention.ops[L] = (sparse_dot_sdd_nt, sparse_dot_dsd_nn, sparse_softmax)
-        return SparseSelfAttention.ops[L]
+        layout = self.get_layout(L)
+        block = self.sparsity_config.block
+        key = (L, block, hash(layout.numpy().tobytes()))
+        cached = SparseSelfAttention.ops.get(key)
+        if cached is None:
+            cached = (MatMul(layout, block, "sdd", trans_a=False, trans_b=True),      # Q K^T -> sparse scores
+                      MatMul(layout, block, "dsd", trans_a=False, trans_b=False),     # sparse P, dense V -> context
+                      Softmax(layout, block))
+            SparseSelfAttention.ops[key] = cached
+        return cached
 
+    # ---- operand helpers
     def transpose_key_for_scores(self, x, L):
-        bsz, num_heads, seq_len, head_dim = x.size()
-        if seq_len != L:
-            return x.permute(0, 1, 3, 2)
-        return x
+        """Keys may arrive already transposed ([batch, heads, head_dim, seq]); bring them to [.., seq, head_dim]."""
+        return x if x.size(2) == L else x.transpose(2, 3)
 
     def transpose_mask_for_sparse(self, qtype, x, is_key_padding_mask=False):
+        """Masks in the operand dtype with their singleton dimensions removed (key padding mask -> [batch, seq])."""
         x = x.type(qtype)
-        if is_key_padding_mask:
-            xdim = x.dim()
-            for d in range(xdim - 1, 0, -1):
-                x = x.squeeze(dim=d)
-            return x
-        return x.squeeze()
+        if not is_key_padding_mask:
+            return x.squeeze()
+        for d in range(x.dim() - 1, 0, -1):
+            x = x.squeeze(dim=d)
+        return x
 
     def forward(self, query, key, value, rpe=None, key_padding_mask=None, attn_mask=None):
-        """query/key/value: [batch, heads, seq, head_dim]; returns the attention context of the same shape."""
-        assert query.dtype in (torch.half, torch.bfloat16) or not query.is_cuda, "sparse attention only supports training in fp16/bf16 on GPU"
-        bsz, num_heads, tgt_len, head_dim = query.size()
-        key = self.transpose_key_for_scores(key, tgt_len)
-        if query.shape != key.shape or key.shape != value.shape:
+        """query / key / value: [batch, heads, seq, head_dim]; returns the attention context of the same shape."""
+        if query.is_cuda and query.dtype not in (torch.half, torch.bfloat16):
+            raise AssertionError("sparse attention only supports training in fp16/bf16 on GPU")
+        _, heads, seq, head_dim = query.shape
+        key = self.transpose_key_for_scores(key, seq)
+        if not (query.shape == key.shape == value.shape):
             raise NotImplementedError("only self-attention is supported for now")
         if key_padding_mask is not None:
             key_padding_mask = self.transpose_mask_for_sparse(query.dtype, key_padding_mask, is_key_padding_mask=True)
         if attn_mask is not None:
             attn_mask = self.transpose_mask_for_sparse(query.dtype, attn_mask)
-        sparse_dot_sdd_nt, sparse_dot_dsd_nn, sparse_softmax = self.get_ops(num_heads, tgt_len)
-        scaling = float(head_dim) ** -0.5
-        attn_output_weights = sparse_dot_sdd_nt(query, key)
-        attn_output_weights = sparse_softmax(attn_output_weights, scale=scaling, rpe=rpe,
-                                             key_padding_mask=key_padding_mask, attn_mask=attn_mask,
-                                             key_padding_mask_mode=self.key_padding_mask_mode,
-                                             attn_mask_mode=self.attn_mask_mode)
-        return sparse_dot_dsd_nn(attn_output_weights, value)
+        scores_op, context_op, softmax_op = self.get_ops(heads, seq)
+        probs = softmax_op(scores_op(query, key), scale=float(head_dim) ** -0.5, rpe=rpe,
+                           key_padding_mask=key_padding_mask, attn_mask=attn_mask,
+                           key_padding_mask_mode=self.key_padding_mask_mode, attn_mask_mode=self.attn_mask_mode)
+        return context_op(probs, value)
