@@ -20,9 +20,9 @@ def init_process_groups(grid):
 
 
 def _is_valid_send_recv(src_stage, dest_stage):
-    first_stage, last_stage = 0, _grid.pipe_parallel_size - 1
-    assert abs(src_stage - dest_stage) == 1 or (src_stage == first_stage and dest_stage == last_stage) or \
-        (src_stage == last_stage and dest_stage == first_stage), \
+    """Only ring neighbours talk to each other (the last stage wraps around to the first)."""
+    n = _grid.pipe_parallel_size
+    assert (src_stage - dest_stage) % n in (1, n - 1), \
         "Functionality currently limited to send and receive between adjacent ranks only"
 
 
@@ -63,13 +63,9 @@ def barrier(stage_id):
 
 
 def _get_send_recv_group(src_stage, dest_stage):
-    """Pair group keyed by the lower stage's rank, except the wrap-around pair keyed by the last stage."""
-    first_stage, last_stage = 0, _grid.pipe_parallel_size - 1
-    if (src_stage == first_stage and dest_stage == last_stage) or (dest_stage == first_stage and src_stage == last_stage):
-        stage_id = last_stage
-    elif src_stage > dest_stage:
-        stage_id = dest_stage
-    else:
-        stage_id = src_stage
-    group_id = _grid.stage_to_global(stage_id=stage_id)
-    return _groups[group_id]
+    """The 2-rank group of a neighbour pair: groups are listed by the pair's lower stage, the wrap-around pair
+    (last, first) by the last stage."""
+    lo, hi = sorted((src_stage, dest_stage))
+    wraps = lo == 0 and hi == _grid.pipe_parallel_size - 1
+    owner = hi if wraps else lo
+    return _groups[_grid.stage_to_global(stage_id=owner)]
