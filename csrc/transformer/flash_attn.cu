@@ -20,6 +20,7 @@
 #include "../common/ptx.cuh"
 #include "../../include/dsb200.h"
 #include "../common/host_ctx.h"
+#include "flash_v2.cuh"
 #include <type_traits>
 
 namespace dsb {
@@ -968,13 +969,21 @@ static int make_map_bshd(CUtensorMap* m, int is_bf16, const void* base, int B, i
 }  // namespace fa
 }  // namespace dsb
 
-// Forward variant: 64 = 64-key blocks, two CTAs per SM (default); 128 = 128-key blocks, one CTA per SM.
-static int g_fa_fwd_variant = 64;
+// Forward variant: 2 = two query tiles per CTA with P kept in tensor memory (flash_attn_v2.cu, default);
+// 64 = 64-key blocks, two CTAs per SM; 128 = 128-key blocks, one CTA per SM (first generation, kept for comparison).
+static int g_fa_fwd_variant = 2;
+// Backward variant: 2 = transposed formulation with P^T / dS^T in tensor memory (default); 1 = first generation.
+static int g_fa_bwd_variant = 2;
+extern "C" int dsb_flash_attn_bwd_variant(int v) {
+    const int prev = g_fa_bwd_variant;
+    if (v == 1 || v == 2) g_fa_bwd_variant = v;
+    return prev;
+}
 static long long* g_fa_dbg = nullptr;
 extern "C" void dsb_flash_attn_debug_timers(long long* p) { g_fa_dbg = p; }
 extern "C" int dsb_flash_attn_fwd_variant(int v) {
     const int prev = g_fa_fwd_variant;
-    if (v == 64 || v == 128) g_fa_fwd_variant = v;
+    if (v == 2 || v == 64 || v == 128) g_fa_fwd_variant = v;
     return prev;
 }
 
@@ -1011,7 +1020,14 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
     const float scale_log2 = scale * 1.4426950408889634f;
     dim3 grid(S / BQ, B * H);
     cudaError_t e;
-    if (g_fa_fwd_variant == 64) {
+    if (g_fa_fwd_variant == 2 && S % 256 == 0) {
+        rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
+        if (rc) return rc;
+        rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);
+        if (rc) return rc;
+        return dsb::fa2::launch_fwd(tq, tk, tv, to, lse, B, S, H, scale_log2, causal, bf, stream);
+    }
+    if (g_fa_fwd_variant != 128) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
         if (rc) return rc;
         rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);
@@ -1045,6 +1061,7 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
 // Backward of dsb_flash_attn_fwd. dO / q / k / v / out / dk / dv: [B, S, H, 128] with their own element strides (unit
 // last stride, multiples of 8). lse: [B, H, S] from the forward. delta: [B, H, S] fp32 scratch. dq_acc: [B, S, H, 128]
 // fp32, contiguous, ZEROED by the caller; it receives dQ (key blocks add their contributions with reductions).
+// delta must hold 2 * B * H * S floats (the default backward keeps -lse * log2 e and -scale * delta there).
 extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, const void* v, const void* out,
                                   const float* lse, float* delta, float* dq_acc, void* dk, void* dv, int B, int S,
                                   int H, int D, const long* strides /* 7 x (sb, ss, sh): dO q k v out dk dv */,
@@ -1061,6 +1078,31 @@ extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, 
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     const long* s_do = strides, *s_q = strides + 3, *s_k = strides + 6, *s_v = strides + 9, *s_o = strides + 12,
                *s_dk = strides + 15, *s_dv = strides + 18;
+    if (g_fa_bwd_variant == 2) {
+        float* nlse2 = delta;
+        float* ndelta = delta + (long)B * H * S;
+        int rc2 = dsb::fa2::launch_prep(dO, out, lse, nlse2, ndelta, B, S, H, s_do, s_o, scale, bf, stream);
+        if (rc2) return rc2;
+        CUtensorMap tq, tk, tv, tdo, tdk, tdv, tdq;
+        if ((rc2 = make_map_bshd(&tq, bf, q, B, S, H, D, s_q[0], s_q[1], s_q[2], 64))) return rc2;
+        if ((rc2 = make_map_bshd(&tdo, bf, dO, B, S, H, D, s_do[0], s_do[1], s_do[2], 64))) return rc2;
+        if ((rc2 = make_map_bshd(&tk, bf, k, B, S, H, D, s_k[0], s_k[1], s_k[2]))) return rc2;
+        if ((rc2 = make_map_bshd(&tv, bf, v, B, S, H, D, s_v[0], s_v[1], s_v[2]))) return rc2;
+        if ((rc2 = make_map_bshd(&tdk, bf, dk, B, S, H, D, s_dk[0], s_dk[1], s_dk[2]))) return rc2;
+        if ((rc2 = make_map_bshd(&tdv, bf, dv, B, S, H, D, s_dv[0], s_dv[1], s_dv[2]))) return rc2;
+        EncodeTiledFn enc = get_encode();
+        if (!enc) return -1;
+        cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)S, (cuuint64_t)B};
+        cuuint64_t st[3] = {(cuuint64_t)D * 4, (cuuint64_t)H * D * 4, (cuuint64_t)S * H * D * 4};
+        cuuint32_t box[4] = {128, 1, 64, 1};
+        cuuint32_t estr[4] = {1, 1, 1, 1};
+        CUresult r = enc(&tdq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dq_acc, dims, st, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return -(int)r - 1000;
+        return dsb::fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale,
+                                    scale * 1.4426950408889634f, causal, bf, stream);
+    }
     const long rows = (long)B * S * H;
     int grid_d = (int)((rows + 7) / 8 < 148L * 16 ? (rows + 7) / 8 : 148L * 16);
     if (bf)

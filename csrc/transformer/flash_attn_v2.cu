@@ -1,0 +1,860 @@
+// Second-generation flash attention for sm_100a (head dim 128, fp16 / bf16): the probabilities never leave the tensor
+// core's own memory.
+//
+// Forward (flash_fwd2_kernel): one CTA per 256 query rows of one (batch, head) = two 128-row tiles that share every
+//   K / V tile (one TMA load feeds both), 64 keys per step.
+//     warp 0 / warp 3 : TMA producers (Q tiles + K ring / V ring, 4 stages each)
+//     warp 1          : issues all UMMAs. S_t(j) = Q_t K_j^T goes to one of two TMEM score buffers per tile;
+//                       O_t += P_t(j) V_j takes its A operand (P, 16 bit) straight from TENSOR MEMORY - the softmax
+//                       warps overwrite the scores they have just read with the packed probabilities, so there is no
+//                       shared-memory round trip, no proxy fence and no bank conflict on that path.
+//     warps 4-7 / 8-11: online softmax of tile 0 / tile 1, one query row per thread (TMEM lane). The running maximum
+//                       is only raised when it grows by more than 2^8 (the O accumulator is then rescaled by the same
+//                       warps); otherwise a block costs one TMEM load, 32 three-input maxima, 32 packed FFMA2, 64
+//                       exponentials, 32 packed adds, 32 converts and one TMEM store, and never waits for the P V
+//                       product of the previous block.
+//   Buffer reuse needs no barrier: the tensor pipe executes the UMMAs of the issuing thread in order, so S_t(j+2) may
+//   overwrite the columns P_t(j) was read from as soon as it has been issued after O_t += P_t(j) V_j.
+//
+// Backward (flash_bwd2_kernel): one CTA per (128-key block, batch, head), K / V resident, walks 64-row query blocks.
+//   Everything is computed TRANSPOSED (lane = key row): S^T = K Q^T and dP^T = V dO^T land in TMEM, the softmax warps
+//   write P^T and dS^T (16 bit) back over the scores, and dV += P^T dO, dK += dS^T Q read that A operand from TMEM.
+//   dQ^T = K^T dS^T needs dS^T as the B operand, so it is also staged in shared memory (one 128-byte row per thread,
+//   conflict-free). TMEM: 2 x S^T (64) + dP^T (64) + dQ^T (64) + dV (128) + dK (128) = 512 columns, i.e. dQ has its own
+//   region and S^T is double-buffered, which removes the serial chain of the first-generation kernel.
+//     warp 0: TMA producer (K, V once; Q ring of 3, dO ring of 2, -lse*log2e / -scale*delta rows with the Q tile)
+//     warp 1: UMMA issuer          warp 2: TMEM allocation
+//     warps 4-11 : P^T / dS^T (lane = key row, each warp half of the 64 query columns)
+//     warps 12-15: dQ^T drain: TMEM -> transposed fp32 tile in shared memory -> one TMA reduce-add per block
+// Reference for the math: csrc/transformer/ds_transformer_cuda.cpp:186-214 and :340-420 (score, softmax, context and
+// their gradients as separate strided-batch GEMMs and softmax kernels).
+#include "../common/ptx.cuh"
+#include "../../include/dsb200.h"
+#include "flash_v2.cuh"
+#include <type_traits>
+
+namespace dsb {
+namespace fa2 {
+
+// ------------------------------------------------------------------------------------------------ device helpers
+DSB_DEVICE void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2),
+        "r"(c3)
+        : "memory");
+}
+DSB_DEVICE void tma_store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+DSB_DEVICE void tma_reduce_add_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.reduce.async.bulk.tensor.4d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(smem_u32(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+// plain (non-tensor) bulk copy global -> shared, completion on an mbarrier; 16-byte aligned, size % 16 == 0
+DSB_DEVICE void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc]
+DSB_DEVICE void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc)
+        : "memory");
+}
+DSB_DEVICE void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+DSB_DEVICE void tmem_st_x32(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+DSB_DEVICE void tmem_st_x16(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+        : "memory");
+}
+DSB_DEVICE void tmem_ld_x32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+DSB_DEVICE float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+DSB_DEVICE float max3(float a, float b, float c) {
+    float y;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(y) : "f"(a), "f"(b), "f"(c));
+    return y;
+}
+// packed fp32 pairs (one 64-bit register): FFMA2 / FADD2 / FMUL2 halve the issue slots of the softmax arithmetic
+DSB_DEVICE uint64_t pk2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+DSB_DEVICE uint64_t pk2u(uint32_t lo, uint32_t hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+    return r;
+}
+DSB_DEVICE void upk2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+DSB_DEVICE uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+DSB_DEVICE uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+DSB_DEVICE uint64_t mul2(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version, 128 B swizzle
+DSB_DEVICE uint32_t desc_lo(const void* p, uint32_t lbo_bytes) {
+    return ((smem_u32(p) & 0x3FFFF) >> 4) | ((lbo_bytes >> 4) << 16);
+}
+constexpr uint32_t NEG_INF_BITS = 0xff800000u;
+
+// ================================================================================================ forward
+constexpr int F_BQ = 128;                  // rows per query tile
+constexpr int F_BK = 64;                   // keys per step
+constexpr int F_NS = 4;                    // K / V ring stages
+constexpr int F_QTILE = 128 * 128 * 2;     // 32 KiB = two chunks of [128 rows x 128 B]
+constexpr int F_QCHUNK = 128 * 128;        // 16 KiB
+constexpr int F_KVTILE = 64 * 128 * 2;     // 16 KiB = two chunks of [64 rows x 128 B]
+constexpr int F_KVCHUNK = 64 * 128;        // 8 KiB
+constexpr int F_OFF_Q = 0;
+constexpr int F_OFF_K = F_OFF_Q + 2 * F_QTILE;
+constexpr int F_OFF_V = F_OFF_K + F_NS * F_KVTILE;
+constexpr int F_OFF_BAR = F_OFF_V + F_NS * F_KVTILE;
+constexpr int F_SMEM = F_OFF_BAR + 512 + 1024;
+constexpr float F_TAU = 8.f;               // the running maximum may lag the true one by 2^8
+
+template <typename T>
+__global__ void __launch_bounds__(384, 1)
+flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                  float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sQ = smem + F_OFF_Q;
+    uint8_t* sK = smem + F_OFF_K;
+    uint8_t* sV = smem + F_OFF_V;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + F_OFF_BAR);
+    uint64_t* q_full = bars;                    // [2]
+    uint64_t* k_full = bars + 2;                // [NS]
+    uint64_t* k_empty = k_full + F_NS;          // [NS]
+    uint64_t* v_full = k_empty + F_NS;          // [NS]
+    uint64_t* v_empty = v_full + F_NS;          // [NS]
+    uint64_t* s_full = v_empty + F_NS;          // [tile][buf]
+    uint64_t* p_ready = s_full + 4;             // [tile][buf]
+    uint64_t* pv_done = p_ready + 4;            // [tile] every P V product (parity = block index; rescale path only)
+    uint64_t* o_final = pv_done + 2;            // [tile] the LAST P V product of the tile (single use)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_final + 2);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x / H, h = blockIdx.x - b * H;
+    const int pr = gridDim.y - 1 - blockIdx.y;   // the long (late) row blocks are dispatched first
+    const int q0 = pr * 2 * F_BQ;
+    const int nA = causal ? (q0 + F_BQ) / F_BK : S / F_BK;
+    const int nB = causal ? (q0 + 2 * F_BQ) / F_BK : S / F_BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmO);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(&q_full[0], 1);
+        mbar_init(&q_full[1], 1);
+        for (int i = 0; i < F_NS; ++i) {
+            mbar_init(&k_full[i], 1);
+            mbar_init(&k_empty[i], 1);
+            mbar_init(&v_full[i], 1);
+            mbar_init(&v_empty[i], 1);
+        }
+        for (int i = 0; i < 4; ++i) {
+            mbar_init(&s_full[i], 1);
+            mbar_init(&p_ready[i], 4);
+        }
+        mbar_init(&pv_done[0], 1);
+        mbar_init(&pv_done[1], 1);
+        mbar_init(&o_final[0], 1);
+        mbar_init(&o_final[1], 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    // TMEM columns: scores of tile t, buffer u at t * 128 + u * 64 (P overwrites the first 32 of them); O_t at 256 + t * 128
+
+    if (warp == 0) {
+        if (elect_one()) {
+            for (int t = 0; t < 2; ++t) {
+                mbar_arrive_expect_tx(&q_full[t], F_QTILE);
+                tma_load_4d(sQ + t * F_QTILE, &tmQ, &q_full[t], 0, h, q0 + t * F_BQ, b);
+                tma_load_4d(sQ + t * F_QTILE + F_QCHUNK, &tmQ, &q_full[t], 64, h, q0 + t * F_BQ, b);
+            }
+            for (int j = 0; j < nB; ++j) {
+                const int st = j % F_NS;
+                if (j >= F_NS) mbar_wait(&k_empty[st], ((j / F_NS) - 1) & 1);
+                mbar_arrive_expect_tx(&k_full[st], F_KVTILE);
+                uint8_t* dst = sK + st * F_KVTILE;
+                tma_load_4d(dst, &tmK, &k_full[st], 0, h, j * F_BK, b);
+                tma_load_4d(dst + F_KVCHUNK, &tmK, &k_full[st], 64, h, j * F_BK, b);
+            }
+        }
+    } else if (warp == 3) {
+        if (elect_one()) {
+            for (int j = 0; j < nB; ++j) {
+                const int st = j % F_NS;
+                if (j >= F_NS) mbar_wait(&v_empty[st], ((j / F_NS) - 1) & 1);
+                mbar_arrive_expect_tx(&v_full[st], F_KVTILE);
+                uint8_t* dst = sV + st * F_KVTILE;
+                tma_load_4d(dst, &tmV, &v_full[st], 0, h, j * F_BK, b);
+                tma_load_4d(dst + F_KVCHUNK, &tmV, &v_full[st], 64, h, j * F_BK, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+            const uint32_t idesc_s = make_idesc_f16(F_BQ, F_BK, is_bf16, 0, 0);
+            const uint32_t idesc_pv = make_idesc_f16(F_BQ, 128, is_bf16, 0, 1);
+            auto issue_s = [&](int t, int j) {
+                const uint32_t q_lo = desc_lo(sQ + t * F_QTILE, 16);
+                const uint32_t k_lo = desc_lo(sK + (j % F_NS) * F_KVTILE, 16);
+                const uint32_t d = tmem_base + t * 128 + (j & 1) * 64;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_f16_lohi(d, q_lo + (k >> 2) * (F_QCHUNK >> 4) + (k & 3) * 2,
+                                  k_lo + (k >> 2) * (F_KVCHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
+                umma_commit(&s_full[t * 2 + (j & 1)]);
+            };
+            auto issue_pv = [&](int t, int j) {
+                // A = P_t(j) in TMEM (16 keys = 8 columns per k-step); B = V_j read MN-major exactly as TMA delivered it
+                const uint32_t v_lo = desc_lo(sV + (j % F_NS) * F_KVTILE, F_KVCHUNK);
+                const uint32_t a = tmem_base + t * 128 + (j & 1) * 64;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_ts(tmem_base + 256 + t * 128, a + k * 8, v_lo + k * (2048u >> 4), DESC_HI, idesc_pv,
+                            (j | k) != 0);
+                umma_commit(&pv_done[t]);
+                if (j == (t ? nB : nA) - 1) umma_commit(&o_final[t]);
+            };
+            mbar_wait(&q_full[0], 0);
+            mbar_wait(&k_full[0], 0);
+            tc_fence_after();
+            if (nA > 0) issue_s(0, 0);
+            mbar_wait(&q_full[1], 0);
+            tc_fence_after();
+            issue_s(1, 0);
+            umma_commit(&k_empty[0]);
+            for (int j = 0; j < nB; ++j) {
+                if (j + 1 < nB) {
+                    const int n = j + 1, st = n % F_NS;
+                    mbar_wait(&k_full[st], (n / F_NS) & 1);
+                    tc_fence_after();
+                    if (n < nA) issue_s(0, n);
+                    issue_s(1, n);
+                    umma_commit(&k_empty[st]);
+                }
+                mbar_wait(&v_full[j % F_NS], (j / F_NS) & 1);
+                if (j < nA) {
+                    mbar_wait(&p_ready[(j & 1)], (j >> 1) & 1);
+                    tc_fence_after();
+                    issue_pv(0, j);
+                }
+                mbar_wait(&p_ready[2 + (j & 1)], (j >> 1) & 1);
+                tc_fence_after();
+                issue_pv(1, j);
+                umma_commit(&v_empty[j % F_NS]);
+            }
+        }
+    } else if (warp >= 4) {
+        const int t = (warp - 4) >> 2;
+        const int qd = warp & 3;
+        const int row = qd * 32 + lane;
+        const uint32_t lane_field = static_cast<uint32_t>(qd * 32) << 16;
+        const int n = t ? nB : nA;
+        const int qrow = q0 + t * F_BQ + row;
+        const uint32_t t_o = tmem_base + lane_field + 256 + t * 128;
+        const uint64_t sc2 = pk2(scale_log2, scale_log2);
+        float m_run = -INFINITY, l_run = 0.f;
+        for (int j = 0; j < n; ++j) {
+            const int buf = j & 1;
+            mbar_wait(&s_full[t * 2 + buf], (j >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t_s = tmem_base + lane_field + t * 128 + buf * 64;
+            uint32_t r[64];
+            tmem_ld_x32(t_s, r);
+            tmem_ld_x32(t_s + 32, r + 32);
+            tmem_ld_wait();
+            if (causal) {
+                const int lim = qrow - j * F_BK;   // columns <= lim of this block are visible to this row
+                if (__any_sync(0xffffffffu, lim < F_BK - 1)) {
+#pragma unroll
+                    for (int i = 0; i < 64; ++i)
+                        if (i > lim) r[i] = NEG_INF_BITS;
+                }
+            }
+            float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < 64; i += 8) {
+                m0 = max3(m0, __uint_as_float(r[i]), __uint_as_float(r[i + 1]));
+                m1 = max3(m1, __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+                m2 = max3(m2, __uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
+                m3 = max3(m3, __uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
+            }
+            const float m_cand = max3(m0, m1, fmaxf(m2, m3)) * scale_log2;
+            const bool grow = m_cand > m_run + F_TAU;   // always true for the first block (m_run = -inf)
+            if (__any_sync(0xffffffffu, grow)) {
+                const float m_new = grow ? m_cand : m_run;
+                const float alpha = ex2(m_run - m_new);
+                if (j > 0) {
+                    mbar_wait(&pv_done[t], (j - 1) & 1);   // O_t is quiescent: P V of the previous block has completed
+                    tc_fence_after();
+#pragma unroll 1
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t o[32];
+                        tmem_ld_x32(t_o + c * 32, o);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                        tmem_st_x32(t_o + c * 32, o);
+                    }
+                }
+                l_run *= alpha;
+                m_run = m_new;
+            }
+            const uint64_t nm2 = pk2(-m_run, -m_run);
+            uint64_t sa = 0ull, sb = 0ull;
+            uint32_t pk[32];
+#pragma unroll
+            for (int i = 0; i < 64; i += 4) {
+                float a0, a1, b0, b1;
+                upk2(fma2(pk2u(r[i], r[i + 1]), sc2, nm2), a0, a1);
+                upk2(fma2(pk2u(r[i + 2], r[i + 3]), sc2, nm2), b0, b1);
+                a0 = ex2(a0);
+                a1 = ex2(a1);
+                b0 = ex2(b0);
+                b1 = ex2(b1);
+                pk[i >> 1] = Cvt<T>::pack2(a0, a1);
+                pk[(i >> 1) + 1] = Cvt<T>::pack2(b0, b1);
+                sa = add2(sa, pk2(a0, a1));
+                sb = add2(sb, pk2(b0, b1));
+            }
+            tmem_st_x32(t_s, pk);
+            float s0, s1;
+            upk2(add2(sa, sb), s0, s1);
+            l_run += s0 + s1;
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_ready[t * 2 + buf]);
+        }
+        // epilogue: O / l -> shared (the tile's Q buffer, same swizzled layout) -> TMA store; log-sum-exp for backward
+        // (a parity wait on pv_done would be ambiguous here: this thread may be two products behind)
+        mbar_wait(&o_final[t], 0);
+        tc_fence_after();
+        const float inv_l = 1.f / l_run;
+        uint8_t* o_row = sQ + t * F_QTILE + row * 128;
+        const int sw = row & 7;
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+            uint32_t o[32];
+            tmem_ld_x32(t_o + c * 32, o);
+            tmem_ld_wait();
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2)
+                pk[i >> 1] = Cvt<T>::pack2(__uint_as_float(o[i]) * inv_l, __uint_as_float(o[i + 1]) * inv_l);
+            uint8_t* dst = o_row + (c >> 1) * F_QCHUNK;
+            const int u0 = (c & 1) * 4;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                *reinterpret_cast<uint4*>(dst + (((u0 + u) ^ sw) << 4)) =
+                    make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+        }
+        if (lse != nullptr) lse[((long)blockIdx.x) * S + qrow] = (m_run + log2f(l_run)) * 0.6931471805599453f;
+        fence_proxy_async_smem();
+        named_bar_sync(1 + t, 128);
+        if ((warp & 3) == 0 && lane == 0) {
+            tma_store_4d(&tmO, sQ + t * F_QTILE, 0, h, q0 + t * F_BQ, b);
+            tma_store_4d(&tmO, sQ + t * F_QTILE + F_QCHUNK, 64, h, q0 + t * F_BQ, b);
+            tma_store_commit();
+            tma_store_wait<0>();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
+// ================================================================================================ backward
+// nlse2[bh, s] = -lse * log2(e); ndelta[bh, s] = -scale * sum_d dO[b, s, h, d] * O[b, s, h, d]; one warp per row.
+template <typename T>
+__global__ void __launch_bounds__(256) flash_prep_kernel(const T* __restrict__ dO, const T* __restrict__ O,
+                                                         const float* __restrict__ lse, float* __restrict__ nlse2,
+                                                         float* __restrict__ ndelta, int B, int S, int H, long do_sb,
+                                                         long do_ss, long do_sh, long o_sb, long o_ss, long o_sh,
+                                                         float scale) {
+    const long rows = (long)B * S * H;
+    const int lane = threadIdx.x & 31;
+    for (long r = (long)blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += (long)gridDim.x * 8) {
+        const int h = (int)(r % H);
+        const long t = r / H;
+        const int s = (int)(t % S);
+        const int b = (int)(t / S);
+        const uint2 a = *reinterpret_cast<const uint2*>(dO + b * do_sb + s * do_ss + h * do_sh + lane * 4);
+        const uint2 c = *reinterpret_cast<const uint2*>(O + b * o_sb + s * o_ss + h * o_sh + lane * 4);
+        const float2 a0 = Cvt<T>::unpack2(a.x), a1 = Cvt<T>::unpack2(a.y);
+        const float2 c0 = Cvt<T>::unpack2(c.x), c1 = Cvt<T>::unpack2(c.y);
+        float v = a0.x * c0.x + a0.y * c0.y + a1.x * c1.x + a1.y * c1.y;
+        v = warp_sum(v);
+        if (lane == 0) {
+            const long o = ((long)b * H + h) * S + s;
+            ndelta[o] = -scale * v;
+            nlse2[o] = -1.4426950408889634f * lse[o];
+        }
+    }
+}
+
+constexpr int B_OFF_K = 0;                          // [128 kv x 128 d] 32 KiB (two chunks of 16 KiB)
+constexpr int B_OFF_V = B_OFF_K + 32768;
+constexpr int B_OFF_Q = B_OFF_V + 32768;            // 3 x [64 q x 128 d] 16 KiB (two chunks of 8 KiB)
+constexpr int B_OFF_DO = B_OFF_Q + 3 * 16384;       // 2 x 16 KiB
+constexpr int B_OFF_DS = B_OFF_DO + 2 * 16384;      // 2 x [128 kv x 64 q] 16 KiB
+constexpr int B_OFF_DQ = B_OFF_DS + 2 * 16384;      // fp32 [64 q x 128 d] 32 KiB
+constexpr int B_OFF_LD = B_OFF_DQ + 32768;          // 3 x (64 -lse2 | 64 -delta) fp32
+constexpr int B_OFF_BAR = B_OFF_LD + 3 * 512;
+constexpr int B_SMEM = B_OFF_BAR + 512 + 1024;
+constexpr int TM_ST = 0, TM_DPT = 128, TM_DQT = 192, TM_DV = 256, TM_DK = 384;
+
+template <typename T>
+__global__ void __launch_bounds__(512, 1)
+flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                  const __grid_constant__ CUtensorMap tmdK, const __grid_constant__ CUtensorMap tmdV,
+                  const __grid_constant__ CUtensorMap tmDQ, const float* __restrict__ nlse2,
+                  const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sK = smem + B_OFF_K;
+    uint8_t* sV = smem + B_OFF_V;
+    uint8_t* sQ = smem + B_OFF_Q;
+    uint8_t* sdO = smem + B_OFF_DO;
+    uint8_t* sdS = smem + B_OFF_DS;
+    float* sdQ = reinterpret_cast<float*>(smem + B_OFF_DQ);
+    float* sLD = reinterpret_cast<float*>(smem + B_OFF_LD);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + B_OFF_BAR);
+    uint64_t* kv_full = bars;            // [1]
+    uint64_t* q_full = bars + 1;         // [3] Q tile + its -lse2 / -delta rows
+    uint64_t* q_free = bars + 4;         // [3] dK UMMAs (last readers of the stage) completed
+    uint64_t* do_full = bars + 7;        // [2]
+    uint64_t* do_free = bars + 9;        // [2] dV UMMAs completed
+    uint64_t* s_full = bars + 11;        // [2] S^T in TMEM
+    uint64_t* dp_full = bars + 13;       // [1] dP^T in TMEM
+    uint64_t* dp_free = bars + 14;       // [1] dP^T read into registers (8 warps)
+    uint64_t* p_ready = bars + 15;       // [2] P^T stored in TMEM (8 warps)
+    uint64_t* ds_ready = bars + 17;      // [2] dS^T stored in TMEM and shared memory (8 warps)
+    uint64_t* ds_free = bars + 19;       // [2] dQ^T UMMAs (readers of the shared dS^T buffer) completed
+    uint64_t* dq_full = bars + 21;       // [1] dQ^T in TMEM
+    uint64_t* dq_free = bars + 22;       // [1] dQ^T read into registers (4 warps)
+    uint64_t* fin = bars + 23;           // [1] everything issued has completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+
+    const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+    const int lane = threadIdx.x & 31;
+    const int b = blockIdx.x / H, h = blockIdx.x - b * H;
+    const int jb = blockIdx.y;                       // key block; block 0 walks the most query blocks and starts first
+    const int i0 = causal ? jb * 2 : 0;              // first 64-row query block that sees these keys
+    const int nit = S / 64 - i0;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmK);
+        tma_prefetch_desc(&tmV);
+        tma_prefetch_desc(&tmdO);
+        tma_prefetch_desc(&tmDQ);
+    }
+    if (warp == 1 && lane == 0) {
+        mbar_init(kv_full, 1);
+        for (int i = 0; i < 3; ++i) {
+            mbar_init(&q_full[i], 1);
+            mbar_init(&q_free[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&do_full[i], 1);
+            mbar_init(&do_free[i], 1);
+            mbar_init(&s_full[i], 1);
+            mbar_init(&p_ready[i], 8);
+            mbar_init(&ds_ready[i], 8);
+            mbar_init(&ds_free[i], 1);
+        }
+        mbar_init(dp_full, 1);
+        mbar_init(dp_free, 8);
+        mbar_init(dq_full, 1);
+        mbar_init(dq_free, 4);
+        mbar_init(fin, 1);
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            mbar_arrive_expect_tx(kv_full, 65536);
+            tma_load_4d(sK, &tmK, kv_full, 0, h, jb * 128, b);
+            tma_load_4d(sK + 16384, &tmK, kv_full, 64, h, jb * 128, b);
+            tma_load_4d(sV, &tmV, kv_full, 0, h, jb * 128, b);
+            tma_load_4d(sV + 16384, &tmV, kv_full, 64, h, jb * 128, b);
+            const long bh_off = (long)blockIdx.x * S;
+            for (int it = 0; it < nit; ++it) {
+                const int q0 = (i0 + it) * 64;
+                const int s3 = it % 3, s2 = it & 1;
+                if (it >= 3) mbar_wait(&q_free[s3], ((it / 3) - 1) & 1);
+                mbar_arrive_expect_tx(&q_full[s3], 16384 + 512);
+                tma_load_4d(sQ + s3 * 16384, &tmQ, &q_full[s3], 0, h, q0, b);
+                tma_load_4d(sQ + s3 * 16384 + 8192, &tmQ, &q_full[s3], 64, h, q0, b);
+                bulk_load(sLD + s3 * 128, nlse2 + bh_off + q0, 256, &q_full[s3]);
+                bulk_load(sLD + s3 * 128 + 64, ndelta + bh_off + q0, 256, &q_full[s3]);
+                if (it >= 2) mbar_wait(&do_free[s2], ((it >> 1) - 1) & 1);
+                mbar_arrive_expect_tx(&do_full[s2], 16384);
+                tma_load_4d(sdO + s2 * 16384, &tmdO, &do_full[s2], 0, h, q0, b);
+                tma_load_4d(sdO + s2 * 16384 + 8192, &tmdO, &do_full[s2], 64, h, q0, b);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+            const uint32_t id_st = make_idesc_f16(128, 64, is_bf16, 0, 0);    // K-major x K-major, N = 64 queries
+            const uint32_t id_acc = make_idesc_f16(128, 128, is_bf16, 0, 1);  // A from TMEM, B MN-major, N = 128 (d)
+            const uint32_t id_dq = make_idesc_f16(128, 64, is_bf16, 1, 1);    // both MN-major, N = 64 queries
+            const uint32_t k_km = desc_lo(sK, 16), v_km = desc_lo(sV, 16);
+            const uint32_t k_mn = desc_lo(sK, 16384);
+            auto koff_a = [](int k) { return (uint32_t)((k >> 2) * (16384 >> 4) + (k & 3) * 2); };
+            auto koff_b = [](int k) { return (uint32_t)((k >> 2) * (8192 >> 4) + (k & 3) * 2); };
+            auto issue_st = [&](int it) {   // S^T[kv, q] = K[kv, :] . Q[q, :]
+                const uint32_t q_km = desc_lo(sQ + (it % 3) * 16384, 16);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_f16_lohi(tmem_base + TM_ST + (it & 1) * 64, k_km + koff_a(k), q_km + koff_b(k), DESC_HI, id_st,
+                                  k != 0);
+                umma_commit(&s_full[it & 1]);
+            };
+            auto issue_dpt = [&](int it) {  // dP^T[kv, q] = V[kv, :] . dO[q, :]
+                const uint32_t do_km = desc_lo(sdO + (it & 1) * 16384, 16);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_f16_lohi(tmem_base + TM_DPT, v_km + koff_a(k), do_km + koff_b(k), DESC_HI, id_st, k != 0);
+                umma_commit(dp_full);
+            };
+            // P^T / dS^T of query columns [32 u, 32 u + 32) live in columns 32 u + [0, 16) / 32 u + [16, 32) of the score
+            // buffer (every softmax warp writes only over columns it has read itself); 16 queries = 8 columns per k-step
+            auto issue_dv = [&](int it) {   // dV[kv, d] += P^T[kv, q] dO[q, d]
+                const uint32_t do_mn = desc_lo(sdO + (it & 1) * 16384, 8192);
+                const uint32_t a = tmem_base + TM_ST + (it & 1) * 64;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_ts(tmem_base + TM_DV, a + (k >> 1) * 32 + (k & 1) * 8, do_mn + k * (2048u >> 4), DESC_HI, id_acc,
+                            (it | k) != 0);
+            };
+            auto issue_dk = [&](int it) {   // dK[kv, d] += dS^T[kv, q] Q[q, d]
+                const uint32_t q_mn = desc_lo(sQ + (it % 3) * 16384, 8192);
+                const uint32_t a = tmem_base + TM_ST + (it & 1) * 64 + 16;
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    umma_ts(tmem_base + TM_DK, a + (k >> 1) * 32 + (k & 1) * 8, q_mn + k * (2048u >> 4), DESC_HI, id_acc,
+                            (it | k) != 0);
+            };
+            auto issue_dqt = [&](int it) {  // dQ^T[d, q] = K^T[d, kv] dS^T[kv, q]
+                const uint32_t ds_mn = desc_lo(sdS + (it & 1) * 16384, 8192);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_f16_lohi(tmem_base + TM_DQT, k_mn + k * (2048u >> 4), ds_mn + k * (2048u >> 4), DESC_HI, id_dq,
+                                  k != 0);
+            };
+            mbar_wait(kv_full, 0);
+            mbar_wait(&q_full[0], 0);
+            tc_fence_after();
+            issue_st(0);
+            mbar_wait(&do_full[0], 0);
+            tc_fence_after();
+            issue_dpt(0);
+            for (int it = 0; it < nit; ++it) {
+                if (it + 1 < nit) {
+                    const int n = it + 1;
+                    mbar_wait(&q_full[n % 3], (n / 3) & 1);
+                    tc_fence_after();
+                    issue_st(n);
+                }
+                mbar_wait(&p_ready[it & 1], (it >> 1) & 1);
+                tc_fence_after();
+                issue_dv(it);
+                umma_commit(&do_free[it & 1]);
+                if (it + 1 < nit) {
+                    const int n = it + 1;
+                    mbar_wait(dp_free, it & 1);
+                    mbar_wait(&do_full[n & 1], (n >> 1) & 1);
+                    tc_fence_after();
+                    issue_dpt(n);
+                }
+                mbar_wait(&ds_ready[it & 1], (it >> 1) & 1);
+                tc_fence_after();
+                issue_dk(it);
+                umma_commit(&q_free[it % 3]);
+                if (it > 0) {
+                    mbar_wait(dq_free, (it - 1) & 1);
+                    tc_fence_after();
+                }
+                issue_dqt(it);
+                umma_commit(dq_full);
+                umma_commit(&ds_free[it & 1]);
+            }
+            umma_commit(fin);
+        }
+    } else if (warp >= 4 && warp < 12) {
+        const int qd = warp & 3;
+        const int half = (warp - 4) >> 2;
+        const int row = qd * 32 + lane;                       // key row of the block = TMEM lane
+        const int kvg = jb * 128 + row;
+        const uint32_t lane_field = static_cast<uint32_t>(qd * 32) << 16;
+        const int sw = row & 7;
+        const uint64_t sc2 = pk2(scale_log2, scale_log2);
+        const uint64_t s2 = pk2(scale, scale);
+        for (int it = 0; it < nit; ++it) {
+            const int buf = it & 1;
+            const int q0 = (i0 + it) * 64 + half * 32;        // global query index of this thread's first column
+            mbar_wait(&q_full[it % 3], (it / 3) & 1);         // the -lse2 / -delta rows travel with the Q tile
+            const float4* nl = reinterpret_cast<const float4*>(sLD + (it % 3) * 128 + half * 32);
+            const float4* nd = reinterpret_cast<const float4*>(sLD + (it % 3) * 128 + 64 + half * 32);
+            mbar_wait(&s_full[buf], (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t t_s = tmem_base + lane_field + TM_ST + buf * 64 + half * 32;
+            uint32_t rs[32];
+            tmem_ld_x32(t_s, rs);
+            tmem_ld_wait();
+            float p[32];
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                const float4 l4 = nl[i >> 2];
+                upk2(fma2(pk2u(rs[i], rs[i + 1]), sc2, pk2(l4.x, l4.y)), p[i], p[i + 1]);
+                upk2(fma2(pk2u(rs[i + 2], rs[i + 3]), sc2, pk2(l4.z, l4.w)), p[i + 2], p[i + 3]);
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) p[i] = ex2(p[i]);
+            if (causal && it < 2) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (q0 + i < kvg) p[i] = 0.f;
+            }
+            uint32_t pk[16];
+#pragma unroll
+            for (int i = 0; i < 32; i += 2) pk[i >> 1] = Cvt<T>::pack2(p[i], p[i + 1]);
+            tmem_st_x16(t_s, pk);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_ready[buf]);
+
+            mbar_wait(dp_full, it & 1);
+            tc_fence_after();
+            uint32_t rp[32];
+            tmem_ld_x32(tmem_base + lane_field + TM_DPT + half * 32, rp);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dp_free);
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                const float4 d4 = nd[i >> 2];
+                float a0, a1, b0, b1;
+                upk2(mul2(fma2(pk2u(rp[i], rp[i + 1]), s2, pk2(d4.x, d4.y)), pk2(p[i], p[i + 1])), a0, a1);
+                upk2(mul2(fma2(pk2u(rp[i + 2], rp[i + 3]), s2, pk2(d4.z, d4.w)), pk2(p[i + 2], p[i + 3])), b0, b1);
+                pk[i >> 1] = Cvt<T>::pack2(a0, a1);
+                pk[(i >> 1) + 1] = Cvt<T>::pack2(b0, b1);
+            }
+            tmem_st_x16(t_s + 16, pk);
+            if (it >= 2) mbar_wait(&ds_free[buf], ((it >> 1) - 1) & 1);
+            uint8_t* dst = sdS + buf * 16384 + row * 128;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                *reinterpret_cast<uint4*>(dst + (((half * 4 + u) ^ sw) << 4)) =
+                    make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+            tmem_st_wait();
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ds_ready[buf]);
+        }
+        // dV / dK: TMEM (lane = key row) -> 16 bit -> shared (the K / V tiles are dead) -> TMA store
+        mbar_wait(fin, 0);
+        tc_fence_after();
+#pragma unroll 1
+        for (int which = 0; which < 2; ++which) {
+            uint8_t* stage = (which == 0 ? sK : sV) + half * 16384 + row * 128;
+            const uint32_t t_acc = tmem_base + lane_field + (which == 0 ? TM_DV : TM_DK) + half * 64;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                uint32_t r[32];
+                tmem_ld_x32(t_acc + c * 32, r);
+                tmem_ld_wait();
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    *reinterpret_cast<uint4*>(stage + (((c * 4 + u) ^ sw) << 4)) = make_uint4(
+                        Cvt<T>::pack2(__uint_as_float(r[u * 8]), __uint_as_float(r[u * 8 + 1])),
+                        Cvt<T>::pack2(__uint_as_float(r[u * 8 + 2]), __uint_as_float(r[u * 8 + 3])),
+                        Cvt<T>::pack2(__uint_as_float(r[u * 8 + 4]), __uint_as_float(r[u * 8 + 5])),
+                        Cvt<T>::pack2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7])));
+            }
+        }
+        fence_proxy_async_smem();
+        named_bar_sync(1, 256);
+        if (warp == 4 && lane == 0) {
+            tma_store_4d(&tmdV, sK, 0, h, jb * 128, b);
+            tma_store_4d(&tmdV, sK + 16384, 64, h, jb * 128, b);
+            tma_store_4d(&tmdK, sV, 0, h, jb * 128, b);
+            tma_store_4d(&tmdK, sV + 16384, 64, h, jb * 128, b);
+            tma_store_commit();
+            tma_store_wait<0>();
+        }
+    } else if (warp >= 12) {
+        const int qd = warp & 3;
+        const int d = qd * 32 + lane;                          // head-dim index = TMEM lane of dQ^T
+        const uint32_t lane_field = static_cast<uint32_t>(qd * 32) << 16;
+        for (int it = 0; it < nit; ++it) {
+            const int q0 = (i0 + it) * 64;
+            mbar_wait(dq_full, it & 1);
+            tc_fence_after();
+            uint32_t r[64];
+            tmem_ld_x32(tmem_base + lane_field + TM_DQT, r);
+            tmem_ld_x32(tmem_base + lane_field + TM_DQT + 32, r + 32);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(dq_free);
+            if (it > 0) {   // the previous reduction must have finished reading the staging tile
+                if (warp == 12 && lane == 0) tma_store_wait_read<0>();
+                named_bar_sync(3, 128);
+            }
+#pragma unroll
+            for (int q = 0; q < 64; ++q) sdQ[q * 128 + d] = __uint_as_float(r[q]);
+            fence_proxy_async_smem();
+            named_bar_sync(3, 128);
+            if (warp == 12 && lane == 0) {
+                tma_reduce_add_4d(&tmDQ, sdQ, 0, h, q0, b);
+                tma_store_commit();
+            }
+        }
+        if (warp == 12 && lane == 0) tma_store_wait<0>();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------ host launchers
+int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
+               int B, int S, int H, float scale_log2, int causal, int bf16, cudaStream_t stream) {
+    if (S % 256) return DSB_ERR_SIZE;
+    dim3 grid(B * H, S / 256);
+    cudaError_t e;
+    if (bf16) {
+        auto kern = flash_fwd2_kernel<__nv_bfloat16>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+    } else {
+        auto kern = flash_fwd2_kernel<__half>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+    }
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+int launch_prep(const void* dO, const void* O, const float* lse, float* nlse2, float* ndelta, int B, int S, int H,
+                const long* s_do, const long* s_o, float scale, int bf16, cudaStream_t stream) {
+    const long rows = (long)B * S * H;
+    const int grid = (int)((rows + 7) / 8 < 148L * 16 ? (rows + 7) / 8 : 148L * 16);
+    if (bf16)
+        flash_prep_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((const __nv_bfloat16*)dO, (const __nv_bfloat16*)O, lse,
+                                                                   nlse2, ndelta, B, S, H, s_do[0], s_do[1], s_do[2],
+                                                                   s_o[0], s_o[1], s_o[2], scale);
+    else
+        flash_prep_kernel<__half><<<grid, 256, 0, stream>>>((const __half*)dO, (const __half*)O, lse, nlse2, ndelta, B, S,
+                                                            H, s_do[0], s_do[1], s_do[2], s_o[0], s_o[1], s_o[2], scale);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+               const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* nlse2,
+               const float* ndelta, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
+               cudaStream_t stream) {
+    if (S % 128) return DSB_ERR_SIZE;
+    dim3 grid(B * H, S / 128);
+    cudaError_t e;
+    if (bf16) {
+        auto kern = flash_bwd2_kernel<__nv_bfloat16>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
+                                            causal);
+    } else {
+        auto kern = flash_bwd2_kernel<__half>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
+        if (e != cudaSuccess) return -(int)e;
+        kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
+                                            causal);
+    }
+    e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+}  // namespace fa2
+}  // namespace dsb

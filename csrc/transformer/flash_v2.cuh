@@ -1,0 +1,26 @@
+// Host-side launchers of the second-generation flash-attention kernels (flash_attn_v2.cu); called by the C entry
+// points in flash_attn.cu. Tensor maps are built by the caller (make_map_bshd in flash_attn.cu).
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+namespace dsb {
+namespace fa2 {
+
+// Forward: tq / to with 128-row boxes, tk / tv with 64-row boxes; S must be a multiple of 256.
+int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
+               int B, int S, int H, float scale_log2, int causal, int bf16, cudaStream_t stream);
+
+// lse2[bh, s] = lse * log2(e), delta_s[bh, s] = scale * sum_d dO * O  (both fp32, [B, H, S]).
+int launch_prep(const void* dO, const void* O, const float* lse, float* lse2, float* delta_s, int B, int S, int H,
+                const long* s_do, const long* s_o, float scale, int bf16, cudaStream_t stream);
+
+// Backward: tq / tdo with 64-row boxes, tk / tv / tdk / tdv with 128-row boxes, tdq = fp32 accumulator map with
+// box {128, 1, 64, 1} and no swizzle; S a multiple of 128.
+int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
+               const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* lse2,
+               const float* delta_s, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
+               cudaStream_t stream);
+
+}  // namespace fa2
+}  // namespace dsb

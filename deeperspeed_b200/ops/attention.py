@@ -41,8 +41,17 @@ N.register_sigs({
 _tables = {}
 
 
+def set_flash_bwd_variant(v):
+    """2: transposed backward with P^T / dS^T in tensor memory (default); 1: first-generation kernel."""
+    lib = N.cuda_lib()
+    lib.dsb_flash_attn_bwd_variant.argtypes = [C.c_int]
+    lib.dsb_flash_attn_bwd_variant.restype = C.c_int
+    return lib.dsb_flash_attn_bwd_variant(int(v))
+
+
 def set_flash_fwd_variant(keys_per_step):
-    """64: 64-key blocks, two CTAs per SM (default); 128: 128-key blocks, one CTA per SM. Returns the previous one."""
+    """2: two query tiles per CTA, P kept in tensor memory (default; needs S % 256 == 0, else the 64-key kernel runs);
+    64: 64-key blocks, two CTAs per SM; 128: 128-key blocks, one CTA per SM. Returns the previous one."""
     lib = N.cuda_lib()
     lib.dsb_flash_attn_fwd_variant.argtypes = [C.c_int]
     lib.dsb_flash_attn_fwd_variant.restype = C.c_int
@@ -61,7 +70,7 @@ def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv
     if dv is None:
         dv = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
     dq_acc = torch.zeros(B, S, H, D, dtype=torch.float32, device=q.device)
-    delta = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
+    delta = torch.empty(2, B, H, S, dtype=torch.float32, device=q.device)   # -lse * log2 e | -scale * delta
     ts = (dout, q, k, v, out, dk, dv)
     assert all(t.stride(-1) == 1 and t.shape == q.shape for t in ts)
     strides = (C.c_long * 21)(*[t.stride(i) for t in ts for i in range(3)])

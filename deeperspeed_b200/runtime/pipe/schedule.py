@@ -1,9 +1,19 @@
-"""Pipeline instruction set and schedules (1F1B training, inference, pure data-parallel).
+"""Pipeline instruction set and schedules (1F1B training, forward-only inference, plain gradient accumulation).
 
-Instruction streams are identical to reference deepspeed/runtime/pipe/schedule.py:129-314 (golden table in
-SURVEY C.4); they are generated from closed-form (step, stage) -> micro-batch maps rather than by the reference's
-even/odd helper cascade."""
+The instruction names, their `buffer_id` argument and the per-step streams are the contract of reference
+deepspeed/runtime/pipe/schedule.py:129-474 (golden table in SURVEY C.4; checked in tests/test_pure_logic.py). They
+are produced here from a clock model instead of the reference's even/odd helper cascade:
+
+  tick `t`, stage `p` of `P`:  (t - p) even -> forward slot of micro-batch (t - p) / 2
+                               (t - p) odd  -> backward slot of micro-batch (t + p + 1) / 2 - P
+
+A slot whose micro-batch index falls outside [0, M) is idle (pipeline fill / drain). Activations produced in a
+forward slot travel at the next tick, gradients produced in a backward slot likewise, so every send has its
+matching receive in the same tick of the neighbour stage. The engine does not interpret these lists one by one:
+`executor.compile_plan` fuses the communication of a tick into one bidirectional exchange.
+"""
 from abc import ABC, abstractmethod
+from collections import namedtuple
 
 from ..utils import call_to_str
 
@@ -74,54 +84,47 @@ class RecvGrad(BufferOpInstruction):
     """buffers['gradients'][buffer_id] = recv() from the next stage"""
 
 
+# one slot of the clock model: micro-batch index (possibly out of range = idle) and its direction
+Slot = namedtuple("Slot", ["micro_batch", "forward"])
+
+
 class PipeSchedule(ABC):
-    """Generator of per-step instruction lists for one stage. Every step is barrier-safe: a send on one stage is
-    matched by the receive on its neighbour in the same step."""
+    """Generator of per-tick instruction lists for one stage."""
 
     def __init__(self, micro_batches, stages, stage_id):
         super().__init__()
         self.micro_batches = micro_batches
         self.stages = stages
         self.stage_id = stage_id
-        self.prev_stage = self.stage_id - 1
-        self.next_stage = self.stage_id + 1
+        self.prev_stage = stage_id - 1
+        self.next_stage = stage_id + 1
 
     @abstractmethod
     def steps(self):
-        pass
+        """Yield one list of instructions per tick."""
 
     def num_pipe_buffers(self):
         return self.micro_batches
 
+    # ---- predicates / aliases the reference exposes
     def _valid_micro_batch(self, micro_batch_id):
         return 0 <= micro_batch_id < self.micro_batches
 
     def _valid_stage(self, stage_id):
         return 0 <= stage_id < self.stages
 
-    @property
-    def stage(self):
-        return self.stage_id
-
-    @property
-    def num_stages(self):
-        return self.stages
-
-    @property
-    def num_micro_batches(self):
-        return self.micro_batches
-
-    @property
-    def is_first_stage(self):
-        return self.stage_id == 0
-
-    @property
-    def is_last_stage(self):
-        return self.stage_id == self.stages - 1
+    stage = property(lambda self: self.stage_id)
+    num_stages = property(lambda self: self.stages)
+    num_micro_batches = property(lambda self: self.micro_batches)
+    is_first_stage = property(lambda self: self.stage_id == 0)
+    is_last_stage = property(lambda self: self.stage_id == self.stages - 1)
 
     def _buffer_idx(self, micro_batch_id):
         assert self._valid_micro_batch(micro_batch_id)
         return micro_batch_id % self.num_pipe_buffers()
+
+    def _buf_or_none(self, micro_batch_id):
+        return self._buffer_idx(micro_batch_id) if self._valid_micro_batch(micro_batch_id) else None
 
     def __iter__(self):
         self.it = None
@@ -134,32 +137,26 @@ class PipeSchedule(ABC):
 
 
 class InferenceSchedule(PipeSchedule):
-    """Forward-only pipelining with two alternating buffers."""
+    """Forward-only pipelining over two alternating buffers: stage p works on micro-batch t - p at tick t, ships the
+    previous tick's output and receives this tick's input. Even stages send before they receive, odd stages the
+    other way round, so blocking transports pair up as well."""
 
     def steps(self):
-        total_steps = self.micro_batches + self.stages - 1
-        for step_id in range(total_steps):
+        has_prev, has_next = self.stage_id > 0, self.stage_id < self.stages - 1
+        flip = self.stage_id & 1
+        for tick in range(self.micro_batches + self.stages - 1):
+            mb = tick - self.stage_id
+            work = self._valid_micro_batch(mb)
+            in_buf = (tick + flip) & 1
+            out_buf = in_buf ^ 1
             cmds = []
-            micro_batch_id = step_id - self.stage_id
-            # alternate send/recv buffers; even stages use (step % 2) to receive, odd stages the other one
-            if self.stage_id % 2 == 0:
-                recv_buf, send_buf = step_id % 2, (step_id + 1) % 2
-            else:
-                recv_buf, send_buf = (step_id + 1) % 2, step_id % 2
-
-            if (self.is_first_stage or self.is_last_stage) and self._valid_micro_batch(micro_batch_id):
-                cmds.append(LoadMicroBatch(recv_buf))
-
-            send = SendActivation(send_buf) if (self._valid_stage(self.next_stage)
-                                                and self._valid_micro_batch(micro_batch_id - 1)) else None
-            recv = RecvActivation(recv_buf) if (self._valid_stage(self.prev_stage)
-                                                and self._valid_micro_batch(micro_batch_id)) else None
-            # even stages send first, odd stages receive first (pairs up blocking p2p without deadlock)
-            order = (send, recv) if self.stage_id % 2 == 0 else (recv, send)
-            cmds.extend(c for c in order if c is not None)
-
-            if self._valid_micro_batch(micro_batch_id):
-                cmds.append(ForwardPass(recv_buf))
+            if work and (self.is_first_stage or self.is_last_stage):
+                cmds.append(LoadMicroBatch(in_buf))
+            tx = SendActivation(out_buf) if has_next and self._valid_micro_batch(mb - 1) else None
+            rx = RecvActivation(in_buf) if has_prev and work else None
+            cmds += [c for c in ((rx, tx) if flip else (tx, rx)) if c is not None]
+            if work:
+                cmds.append(ForwardPass(in_buf))
             yield cmds
 
     def num_pipe_buffers(self):
@@ -167,70 +164,65 @@ class InferenceSchedule(PipeSchedule):
 
 
 class TrainSchedule(PipeSchedule):
-    """1F1B: each stage alternates forward and backward steps once the pipeline is full, which bounds the number
-    of live activations by the pipeline depth instead of the number of micro-batches."""
+    """1F1B: once the pipeline is full every stage alternates one forward and one backward slot, so the number of live
+    activations is bounded by the pipeline depth, not by the number of micro-batches."""
+
+    def slot(self, tick):
+        """The clock model of the module docstring."""
+        d = tick - self.stage_id
+        if d % 2 == 0:
+            return Slot(d // 2, True)
+        return Slot((tick + self.stage_id + 1) // 2 - self.stages, False)
 
     def _step_to_micro_batch(self, step_id):
-        """(micro_batch_id, is_forward) for this stage at `step_id` (ids may be out of range = idle slot)."""
-        same_parity = (step_id % 2) == (self.stage_id % 2)
-        if same_parity:
-            # forward slot
-            base = step_id // 2 if step_id % 2 == 0 else (step_id - 1) // 2
-            return base - self.stage_id // 2, True
-        if step_id % 2 == 0:  # even step on an odd stage
-            return step_id // 2 - self.stages + (self.stage_id + 1) // 2, False
-        return (step_id - 1) // 2 - self.stages + 1 + self.stage_id // 2, False
+        s = self.slot(step_id)
+        return s.micro_batch, s.forward
 
     def steps(self):
-        prev_micro_batch_id = -1
-        total_steps = 2 * (self.micro_batches + self.stages - 1)
-        for step_id in range(total_steps):
-            micro_batch_id, is_forward = self._step_to_micro_batch(step_id)
-            prev_buffer = self._buffer_idx(prev_micro_batch_id) if self._valid_micro_batch(prev_micro_batch_id) else None
-            curr_buffer = self._buffer_idx(micro_batch_id) if self._valid_micro_batch(micro_batch_id) else None
+        has_prev, has_next = self.stage_id > 0, self.stage_id < self.stages - 1
+        edge_stage = not (has_prev and has_next)
+        n_ticks = 2 * (self.micro_batches + self.stages - 1)
+        before = None            # buffer worked on in the previous tick (None: idle)
+        for tick in range(n_ticks):
+            slot = self.slot(tick)
+            now = self._buf_or_none(slot.micro_batch)
             cmds = []
-
-            # exchange activations / gradients produced by the previous step with the neighbours
-            if is_forward:
-                if self._valid_micro_batch(micro_batch_id) and self._valid_stage(self.prev_stage):
-                    cmds.append(RecvActivation(curr_buffer))
-                if self._valid_micro_batch(prev_micro_batch_id) and self._valid_stage(self.prev_stage):
-                    cmds.append(SendGrad(prev_buffer))
+            if slot.forward:
+                # input for this forward comes from upstream; the gradient finished last tick goes back upstream
+                if has_prev and now is not None:
+                    cmds.append(RecvActivation(now))
+                if has_prev and before is not None:
+                    cmds.append(SendGrad(before))
+                if edge_stage and now is not None:
+                    cmds.append(LoadMicroBatch(now))
+                if now is not None:
+                    cmds.append(ForwardPass(now))
             else:
-                if self._valid_micro_batch(prev_micro_batch_id) and self._valid_stage(self.next_stage):
-                    cmds.append(SendActivation(prev_buffer))
-                if self._valid_micro_batch(micro_batch_id) and self._valid_stage(self.next_stage):
-                    cmds.append(RecvGrad(curr_buffer))
-
-            if (self.stage_id == 0 or self.stage_id == self.stages - 1) and is_forward \
-                    and self._valid_micro_batch(micro_batch_id):
-                cmds.append(LoadMicroBatch(curr_buffer))
-
-            if self._valid_micro_batch(micro_batch_id):
-                cmds.append(ForwardPass(curr_buffer) if is_forward else BackwardPass(curr_buffer))
-
-            if step_id == total_steps - 1:
-                cmds.append(ReduceTiedGrads())
-                cmds.append(ReduceGrads())
-                cmds.append(OptimizerStep())
-
-            prev_micro_batch_id = micro_batch_id
+                # the activation finished last tick goes downstream; the gradient for this backward comes from there
+                if has_next and before is not None:
+                    cmds.append(SendActivation(before))
+                if has_next and now is not None:
+                    cmds.append(RecvGrad(now))
+                if now is not None:
+                    cmds.append(BackwardPass(now))
+            if tick == n_ticks - 1:
+                cmds += [ReduceTiedGrads(), ReduceGrads(), OptimizerStep()]
+            before = now
             yield cmds
 
     def num_pipe_buffers(self):
         """In-flight micro-batches a stage must hold: deeper for early stages, never fewer than 2."""
-        buffers = min(self.stages - self.stage_id + 1, self.micro_batches)
-        return max(2, buffers)
+        return max(2, min(self.stages - self.stage_id + 1, self.micro_batches))
 
 
 class DataParallelSchedule(PipeSchedule):
     """Plain gradient accumulation expressed in the pipeline ISA (single stage)."""
 
     def steps(self):
-        for step_id in range(self.micro_batches):
+        for mb in range(self.micro_batches):
             cmds = [LoadMicroBatch(buffer_id=0), ForwardPass(buffer_id=0), BackwardPass(buffer_id=0)]
-            if step_id == self.micro_batches - 1:
-                cmds.extend([ReduceGrads(), OptimizerStep()])
+            if mb == self.micro_batches - 1:
+                cmds += [ReduceGrads(), OptimizerStep()]
             yield cmds
 
     def num_pipe_buffers(self):

@@ -106,6 +106,7 @@ int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, f
 /* Forward block shape: 64 = 64-key blocks, two CTAs per SM (default); 128 = 128-key blocks, one CTA per SM. Returns
  * the previous setting; other values only query. */
 int dsb_flash_attn_fwd_variant(int keys_per_step);
+int dsb_flash_attn_bwd_variant(int generation);
 /* Debug aid: when `p` is not NULL, CTA (0, 0) of the following attention launches adds its clock64 phase totals to
  * the 16 int64 at `p` ([0..4] softmax warp, [8..12] MMA thread, [15] blocks walked); NULL switches it off. */
 void dsb_flash_attn_debug_timers(long long* p);
