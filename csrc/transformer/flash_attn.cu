@@ -974,13 +974,17 @@ static int make_map_bshd(CUtensorMap* m, int is_bf16, const void* base, int B, i
 static int g_fa_fwd_variant = 2;
 // Backward variant: 2 = transposed formulation with P^T / dS^T in tensor memory (default); 1 = first generation.
 static int g_fa_bwd_variant = 2;
+extern "C" void dsb_flash_attn_debug_mode(int m) { dsb::fa2::set_debug_mode(m); }
 extern "C" int dsb_flash_attn_bwd_variant(int v) {
     const int prev = g_fa_bwd_variant;
     if (v == 1 || v == 2) g_fa_bwd_variant = v;
     return prev;
 }
 static long long* g_fa_dbg = nullptr;
-extern "C" void dsb_flash_attn_debug_timers(long long* p) { g_fa_dbg = p; }
+extern "C" void dsb_flash_attn_debug_timers(long long* p) {
+    g_fa_dbg = p;
+    dsb::fa2::set_debug_timers(p);
+}
 extern "C" int dsb_flash_attn_fwd_variant(int v) {
     const int prev = g_fa_fwd_variant;
     if (v == 2 || v == 64 || v == 128) g_fa_fwd_variant = v;
@@ -1061,7 +1065,6 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
 // Backward of dsb_flash_attn_fwd. dO / q / k / v / out / dk / dv: [B, S, H, 128] with their own element strides (unit
 // last stride, multiples of 8). lse: [B, H, S] from the forward. delta: [B, H, S] fp32 scratch. dq_acc: [B, S, H, 128]
 // fp32, contiguous, ZEROED by the caller; it receives dQ (key blocks add their contributions with reductions).
-// delta must hold 2 * B * H * S floats (the default backward keeps -lse * log2 e and -scale * delta there).
 extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, const void* v, const void* out,
                                   const float* lse, float* delta, float* dq_acc, void* dk, void* dv, int B, int S,
                                   int H, int D, const long* strides /* 7 x (sb, ss, sh): dO q k v out dk dv */,
@@ -1078,31 +1081,6 @@ extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, 
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     const long* s_do = strides, *s_q = strides + 3, *s_k = strides + 6, *s_v = strides + 9, *s_o = strides + 12,
                *s_dk = strides + 15, *s_dv = strides + 18;
-    if (g_fa_bwd_variant == 2) {
-        float* nlse2 = delta;
-        float* ndelta = delta + (long)B * H * S;
-        int rc2 = dsb::fa2::launch_prep(dO, out, lse, nlse2, ndelta, B, S, H, s_do, s_o, scale, bf, stream);
-        if (rc2) return rc2;
-        CUtensorMap tq, tk, tv, tdo, tdk, tdv, tdq;
-        if ((rc2 = make_map_bshd(&tq, bf, q, B, S, H, D, s_q[0], s_q[1], s_q[2], 64))) return rc2;
-        if ((rc2 = make_map_bshd(&tdo, bf, dO, B, S, H, D, s_do[0], s_do[1], s_do[2], 64))) return rc2;
-        if ((rc2 = make_map_bshd(&tk, bf, k, B, S, H, D, s_k[0], s_k[1], s_k[2]))) return rc2;
-        if ((rc2 = make_map_bshd(&tv, bf, v, B, S, H, D, s_v[0], s_v[1], s_v[2]))) return rc2;
-        if ((rc2 = make_map_bshd(&tdk, bf, dk, B, S, H, D, s_dk[0], s_dk[1], s_dk[2]))) return rc2;
-        if ((rc2 = make_map_bshd(&tdv, bf, dv, B, S, H, D, s_dv[0], s_dv[1], s_dv[2]))) return rc2;
-        EncodeTiledFn enc = get_encode();
-        if (!enc) return -1;
-        cuuint64_t dims[4] = {(cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)S, (cuuint64_t)B};
-        cuuint64_t st[3] = {(cuuint64_t)D * 4, (cuuint64_t)H * D * 4, (cuuint64_t)S * H * D * 4};
-        cuuint32_t box[4] = {128, 1, 64, 1};
-        cuuint32_t estr[4] = {1, 1, 1, 1};
-        CUresult r = enc(&tdq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dq_acc, dims, st, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        if (r != CUDA_SUCCESS) return -(int)r - 1000;
-        return dsb::fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale,
-                                    scale * 1.4426950408889634f, causal, bf, stream);
-    }
     const long rows = (long)B * S * H;
     int grid_d = (int)((rows + 7) / 8 < 148L * 16 ? (rows + 7) / 8 : 148L * 16);
     if (bf)
@@ -1151,4 +1129,53 @@ extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, 
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
+}
+
+// Second-generation backward (flash_attn_v2.cu). Same tensors as dsb_flash_attn_bwd plus the query gradient itself:
+// dq / dk / dv are written in the input dtype. `strides`: 8 x (sb, ss, sh) for dO, q, k, v, out, dq, dk, dv.
+// `scratch`: fp32, (2 + 128) * B * H * S elements: -lse * log2 e, -scale * rowsum(dO * O) and the TRANSPOSED fp32 dQ
+// accumulator [B, H, 128, S]; it is cleared here (stream-ordered memset), nothing is allocated.
+extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H,
+                                   int D, const long* strides, float scale, int causal, int dtype, void* stream_) {
+    using namespace dsb;
+    using namespace dsb::fa;
+    ensure_context_on_this_thread();
+    if (B <= 0 || S <= 0 || H <= 0) return 0;
+    if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
+    if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
+    for (int i = 0; i < 24; ++i)
+        if (strides[i] % 8) return DSB_ERR_ALIGN;
+    const int bf = dtype == DSB_DTYPE_BF16;
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    const long *s_do = strides, *s_q = strides + 3, *s_k = strides + 6, *s_v = strides + 9, *s_o = strides + 12,
+               *s_dq = strides + 15, *s_dk = strides + 18, *s_dv = strides + 21;
+    const long bhs = (long)B * H * S;
+    float* nlse2 = scratch;
+    float* ndelta = scratch + bhs;
+    float* dq_acc = scratch + 2 * bhs;
+    cudaError_t ce = cudaMemsetAsync(dq_acc, 0, sizeof(float) * bhs * HD, stream);
+    if (ce != cudaSuccess) return -(int)ce;
+    int rc = fa2::launch_prep(dO, out, lse, nlse2, ndelta, B, S, H, s_do, s_o, scale, bf, stream);
+    if (rc) return rc;
+    CUtensorMap tq, tk, tv, tdo, tdk, tdv, tdq;
+    if ((rc = make_map_bshd(&tq, bf, q, B, S, H, D, s_q[0], s_q[1], s_q[2], 64))) return rc;
+    if ((rc = make_map_bshd(&tdo, bf, dO, B, S, H, D, s_do[0], s_do[1], s_do[2], 64))) return rc;
+    if ((rc = make_map_bshd(&tk, bf, k, B, S, H, D, s_k[0], s_k[1], s_k[2]))) return rc;
+    if ((rc = make_map_bshd(&tv, bf, v, B, S, H, D, s_v[0], s_v[1], s_v[2]))) return rc;
+    if ((rc = make_map_bshd(&tdk, bf, dk, B, S, H, D, s_dk[0], s_dk[1], s_dk[2]))) return rc;
+    if ((rc = make_map_bshd(&tdv, bf, dv, B, S, H, D, s_dv[0], s_dv[1], s_dv[2]))) return rc;
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return -1;
+    cuuint64_t dims[4] = {(cuuint64_t)S, (cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t st[3] = {(cuuint64_t)S * 4, (cuuint64_t)D * S * 4, (cuuint64_t)H * D * S * 4};
+    cuuint32_t box[4] = {32, 128, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&tdq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dq_acc, dims, st, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return -(int)r - 1000;
+    rc = fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale, scale * 1.4426950408889634f, causal,
+                         bf, stream);
+    if (rc) return rc;
+    return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, stream);
 }

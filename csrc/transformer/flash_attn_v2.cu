@@ -3,8 +3,8 @@
 //
 // Forward (flash_fwd2_kernel): one CTA per 256 query rows of one (batch, head) = two 128-row tiles that share every
 //   K / V tile (one TMA load feeds both), 64 keys per step.
-//     warp 0 / warp 3 : TMA producers (Q tiles + K ring / V ring, 4 stages each)
-//     warp 1          : issues all UMMAs. S_t(j) = Q_t K_j^T goes to one of two TMEM score buffers per tile;
+//     warp 0 / warp 3 : TMA producers (Q tiles + K ring / V ring, 4 stages each); warp 3 also owns the TMEM allocation
+//     warps 1, 2      : UMMA issue for tile 0 / tile 1. S_t(j) = Q_t K_j^T goes to one of two TMEM score buffers per tile;
 //                       O_t += P_t(j) V_j takes its A operand (P, 16 bit) straight from TENSOR MEMORY - the softmax
 //                       warps overwrite the scores they have just read with the packed probabilities, so there is no
 //                       shared-memory round trip, no proxy fence and no bank conflict on that path.
@@ -23,9 +23,10 @@
 //   conflict-free). TMEM: 2 x S^T (64) + dP^T (64) + dQ^T (64) + dV (128) + dK (128) = 512 columns, i.e. dQ has its own
 //   region and S^T is double-buffered, which removes the serial chain of the first-generation kernel.
 //     warp 0: TMA producer (K, V once; Q ring of 3, dO ring of 2, -lse*log2e / -scale*delta rows with the Q tile)
-//     warp 1: UMMA issuer          warp 2: TMEM allocation
+//     warp 1: issues S^T / dP^T    warp 2: issues dV / dK / dQ^T    warp 3: TMEM allocation
 //     warps 4-11 : P^T / dS^T (lane = key row, each warp half of the 64 query columns)
-//     warps 12-15: dQ^T drain: TMEM -> transposed fp32 tile in shared memory -> one TMA reduce-add per block
+//     warps 12-15: dQ^T drain: TMEM -> fp32 tiles in shared memory -> TMA reduce-add into a TRANSPOSED accumulator
+//                  ([B, H, D, S]; flash_dq_finish_kernel transposes and casts it afterwards)
 // Reference for the math: csrc/transformer/ds_transformer_cuda.cpp:186-214 and :340-420 (score, softmax, context and
 // their gradients as separate strided-batch GEMMs and softmax kernels).
 #include "../common/ptx.cuh"
@@ -71,6 +72,49 @@ DSB_DEVICE void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_
         "mov.b64 db, {%2, %3};\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}"
         ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc)
+        : "memory");
+}
+// Warp-uniform issue: every lane of the issuing warp runs the role loop (waits, descriptor arithmetic on the uniform
+// datapath), only the tcgen05 instruction itself is predicated on the elected lane. With the whole loop inside an
+// `if (elected)` branch the descriptors live in per-thread registers and every UMMA pays register -> uniform-register
+// moves: measured 38 cycles per issue, which made the issuing thread - not the tensor pipe - the limit of both kernels.
+DSB_DEVICE void umma_ss_p(uint32_t lead, uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                          uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "setp.ne.b32 q, %6, 0;\n\t"
+        "mov.b64 da, {%1, %3};\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc), "r"(lead)
+        : "memory");
+}
+DSB_DEVICE void umma_ts_p(uint32_t lead, uint32_t d_tmem, uint32_t a_tmem, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                          uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 db;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "setp.ne.b32 q, %6, 0;\n\t"
+        "mov.b64 db, {%2, %3};\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "r"(b_lo), "r"(hi), "r"(idesc), "r"(acc), "r"(lead)
+        : "memory");
+}
+DSB_DEVICE void umma_commit_p(uint32_t lead, uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}"
+        ::"r"(smem_u32(bar)), "r"(lead)
+        : "memory");
+}
+DSB_DEVICE void mbar_arrive_p(uint32_t lead, uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q mbarrier.arrive.shared::cta.b64 _, [%0];\n\t}"
+        ::"r"(smem_u32(bar)), "r"(lead)
         : "memory");
 }
 DSB_DEVICE void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
@@ -143,6 +187,30 @@ DSB_DEVICE uint64_t mul2(uint64_t a, uint64_t b) {
     return r;
 }
 
+DSB_DEVICE uint64_t add2_rm(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("add.rm.ftz.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// 2^x for a packed pair on the FMA / ALU pipes (no MUFU): x = floor(x) + f, 2^f by a cubic fitted on [0, 1) (max relative
+// error 8.7e-5, below the rounding of a 16-bit probability), 2^floor(x) by an add into the exponent field. x in
+// [-125, 126]; callers clamp from below. The MUFU unit does 16 exponentials per clock and SM, which is exactly the
+// tensor pipe's appetite at head dim 128; moving half of them here takes the special-function unit off the critical path.
+DSB_DEVICE void exp2_poly2(uint64_t x, float& lo, float& hi) {
+    const uint64_t magic = pk2(12582912.f, 12582912.f);          // 1.5 * 2^23: the low mantissa bits of x + magic are floor(x)
+    const uint64_t t = add2_rm(x, magic);
+    const uint64_t fl = add2(t, pk2(-12582912.f, -12582912.f));   // floor(x) as a float
+    const uint64_t f = fma2(fl, pk2(-1.f, -1.f), x);             // x - floor(x) in [0, 1)
+    uint64_t pz = fma2(pk2(0.07705804705619812f, 0.07705804705619812f), f, pk2(0.22764557600021362f, 0.22764557600021362f));
+    pz = fma2(pz, f, pk2(0.6951228976249695f, 0.6951228976249695f));
+    pz = fma2(pz, f, pk2(1.f, 1.f));
+    float t0, t1, p0, p1;
+    upk2(t, t0, t1);
+    upk2(pz, p0, p1);
+    lo = __uint_as_float(__float_as_uint(p0) + (__float_as_uint(t0) << 23));
+    hi = __uint_as_float(__float_as_uint(p1) + (__float_as_uint(t1) << 23));
+}
+
 constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);   // SBO 1024 B, descriptor version, 128 B swizzle
 DSB_DEVICE uint32_t desc_lo(const void* p, uint32_t lbo_bytes) {
     return ((smem_u32(p) & 0x3FFFF) >> 4) | ((lbo_bytes >> 4) << 16);
@@ -162,13 +230,14 @@ constexpr int F_OFF_K = F_OFF_Q + 2 * F_QTILE;
 constexpr int F_OFF_V = F_OFF_K + F_NS * F_KVTILE;
 constexpr int F_OFF_BAR = F_OFF_V + F_NS * F_KVTILE;
 constexpr int F_SMEM = F_OFF_BAR + 512 + 1024;
+constexpr bool F_POLY = true;              // half of the exponentials as a polynomial on the FMA pipe
 constexpr float F_TAU = 8.f;               // the running maximum may lag the true one by 2^8
 
 template <typename T>
 __global__ void __launch_bounds__(384, 1)
 flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                  float* __restrict__ lse, int S, int H, float scale_log2, int causal) {
+                  float* __restrict__ lse, int S, int H, float scale_log2, int causal, int dbg, long long* prof) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem + F_OFF_Q;
@@ -193,6 +262,10 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     const int q0 = pr * 2 * F_BQ;
     const int nA = causal ? (q0 + F_BQ) / F_BK : S / F_BK;
     const int nB = causal ? (q0 + 2 * F_BQ) / F_BK : S / F_BK;
+    // phase timers of CTA (0, 0) (the longest one), only when a buffer is registered with dsb_flash_attn_debug_timers
+    const bool tm = prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
+    long long t0 = 0, acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define FA2_TICK(n) if (tm) { const long long t1 = clock64(); acc[n] += t1 - t0; t0 = t1; }
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
@@ -205,9 +278,9 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         mbar_init(&q_full[1], 1);
         for (int i = 0; i < F_NS; ++i) {
             mbar_init(&k_full[i], 1);
-            mbar_init(&k_empty[i], 1);
+            mbar_init(&k_empty[i], 2);   // released by the issuing warps of both tiles
             mbar_init(&v_full[i], 1);
-            mbar_init(&v_empty[i], 1);
+            mbar_init(&v_empty[i], 2);
         }
         for (int i = 0; i < 4; ++i) {
             mbar_init(&s_full[i], 1);
@@ -219,7 +292,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         mbar_init(&o_final[1], 1);
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    if (warp == 3) tmem_alloc<512>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -236,6 +309,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             for (int j = 0; j < nB; ++j) {
                 const int st = j % F_NS;
                 if (j >= F_NS) mbar_wait(&k_empty[st], ((j / F_NS) - 1) & 1);
+                if ((dbg & 32) && j >= F_NS) { mbar_arrive(&k_full[st]); continue; }
                 mbar_arrive_expect_tx(&k_full[st], F_KVTILE);
                 uint8_t* dst = sK + st * F_KVTILE;
                 tma_load_4d(dst, &tmK, &k_full[st], 0, h, j * F_BK, b);
@@ -247,66 +321,82 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             for (int j = 0; j < nB; ++j) {
                 const int st = j % F_NS;
                 if (j >= F_NS) mbar_wait(&v_empty[st], ((j / F_NS) - 1) & 1);
+                if ((dbg & 32) && j >= F_NS) { mbar_arrive(&v_full[st]); continue; }
                 mbar_arrive_expect_tx(&v_full[st], F_KVTILE);
                 uint8_t* dst = sV + st * F_KVTILE;
                 tma_load_4d(dst, &tmV, &v_full[st], 0, h, j * F_BK, b);
                 tma_load_4d(dst + F_KVCHUNK, &tmV, &v_full[st], 64, h, j * F_BK, b);
             }
         }
-    } else if (warp == 1) {
-        if (elect_one()) {
-            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
-            const uint32_t idesc_s = make_idesc_f16(F_BQ, F_BK, is_bf16, 0, 0);
-            const uint32_t idesc_pv = make_idesc_f16(F_BQ, 128, is_bf16, 0, 1);
-            auto issue_s = [&](int t, int j) {
-                const uint32_t q_lo = desc_lo(sQ + t * F_QTILE, 16);
-                const uint32_t k_lo = desc_lo(sK + (j % F_NS) * F_KVTILE, 16);
-                const uint32_t d = tmem_base + t * 128 + (j & 1) * 64;
+    } else if (warp == 1 || warp == 2) {
+        // One issuing warp per query tile: S_t(j + 1) = Q_t K_{j+1}^T, then O_t += P_t(j) V_j. Both warps release every
+        // K / V stage (the empty barriers count two arrivals); the shorter tile keeps arriving for the blocks it skips.
+        const int t = warp - 1;
+        const uint32_t lead = elect_one() ? 1u : 0u;
+        const int n = t ? nB : nA;
+        constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+        const uint32_t idesc_s = make_idesc_f16(F_BQ, (dbg & 16) ? 128 : F_BK, is_bf16, 0, 0);
+        const uint32_t idesc_pv = make_idesc_f16(F_BQ, 128, is_bf16, 0, 1);
+        const uint32_t q_lo = desc_lo(sQ + t * F_QTILE, 16);
+        const uint32_t t_sc = tmem_base + t * 128;
+        const uint32_t t_acc = tmem_base + 256 + t * 128;
+        auto issue_s = [&](int j) {
+            const uint32_t k_lo = desc_lo(sK + (j % F_NS) * F_KVTILE, 16);
+            const uint32_t d = t_sc + (j & 1) * 64;
 #pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_f16_lohi(d, q_lo + (k >> 2) * (F_QCHUNK >> 4) + (k & 3) * 2,
-                                  k_lo + (k >> 2) * (F_KVCHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
-                umma_commit(&s_full[t * 2 + (j & 1)]);
-            };
-            auto issue_pv = [&](int t, int j) {
-                // A = P_t(j) in TMEM (16 keys = 8 columns per k-step); B = V_j read MN-major exactly as TMA delivered it
-                const uint32_t v_lo = desc_lo(sV + (j % F_NS) * F_KVTILE, F_KVCHUNK);
-                const uint32_t a = tmem_base + t * 128 + (j & 1) * 64;
+            for (int k = 0; k < 8; ++k)
+                umma_ss_p(lead, d, q_lo + (k >> 2) * (F_QCHUNK >> 4) + (k & 3) * 2,
+                          k_lo + (k >> 2) * (F_KVCHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
+            umma_commit_p(lead, &s_full[t * 2 + (j & 1)]);
+            umma_commit_p(lead, &k_empty[j % F_NS]);
+        };
+        auto issue_pv = [&](int j) {
+            // A = P_t(j) in TMEM (16 keys = 8 columns per k-step); B = V_j read MN-major exactly as TMA delivered it
+            const uint32_t v_lo = desc_lo(sV + (j % F_NS) * F_KVTILE, F_KVCHUNK);
+            const uint32_t a = t_sc + (j & 1) * 64;
+            if (!(dbg & 4)) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                    umma_ts(tmem_base + 256 + t * 128, a + k * 8, v_lo + k * (2048u >> 4), DESC_HI, idesc_pv,
-                            (j | k) != 0);
-                umma_commit(&pv_done[t]);
-                if (j == (t ? nB : nA) - 1) umma_commit(&o_final[t]);
-            };
-            mbar_wait(&q_full[0], 0);
-            mbar_wait(&k_full[0], 0);
-            tc_fence_after();
-            if (nA > 0) issue_s(0, 0);
-            mbar_wait(&q_full[1], 0);
-            tc_fence_after();
-            issue_s(1, 0);
-            umma_commit(&k_empty[0]);
-            for (int j = 0; j < nB; ++j) {
-                if (j + 1 < nB) {
-                    const int n = j + 1, st = n % F_NS;
-                    mbar_wait(&k_full[st], (n / F_NS) & 1);
-                    tc_fence_after();
-                    if (n < nA) issue_s(0, n);
-                    issue_s(1, n);
-                    umma_commit(&k_empty[st]);
-                }
-                mbar_wait(&v_full[j % F_NS], (j / F_NS) & 1);
-                if (j < nA) {
-                    mbar_wait(&p_ready[(j & 1)], (j >> 1) & 1);
-                    tc_fence_after();
-                    issue_pv(0, j);
-                }
-                mbar_wait(&p_ready[2 + (j & 1)], (j >> 1) & 1);
-                tc_fence_after();
-                issue_pv(1, j);
-                umma_commit(&v_empty[j % F_NS]);
+                    umma_ts_p(lead, t_acc, a + k * 8, v_lo + k * (2048u >> 4), DESC_HI, idesc_pv, (j | k) != 0);
             }
+            umma_commit_p(lead, &pv_done[t]);
+            umma_commit_p(lead, &v_empty[j % F_NS]);
+            if (j == n - 1) umma_commit_p(lead, &o_final[t]);
+        };
+        const bool tmw = tm && lead;
+        mbar_wait(&q_full[t], 0);
+        mbar_wait(&k_full[0], 0);
+        tc_fence_after();
+        issue_s(0);
+        t0 = clock64();
+        const long long t_begin = t0;
+        for (int j = 0; j < n; ++j) {
+            if (j + 1 < n) {
+                const int nx = j + 1;
+                mbar_wait(&k_full[nx % F_NS], (nx / F_NS) & 1);
+                tc_fence_after();
+                FA2_TICK(0)
+                issue_s(nx);
+                FA2_TICK(1)
+            }
+            mbar_wait(&v_full[j % F_NS], (j / F_NS) & 1);
+            FA2_TICK(2)
+            mbar_wait(&p_ready[t * 2 + (j & 1)], (j >> 1) & 1);
+            tc_fence_after();
+            FA2_TICK(3)
+            issue_pv(j);
+            FA2_TICK(4)
+        }
+        if (tmw) {
+            for (int i = 0; i < 5; ++i) prof[16 + t * 6 + i] = acc[i];
+            prof[30 + t] = clock64() - t_begin;
+            prof[28 + t] = n;
+        }
+        for (int j = n; j < nB; ++j) {   // blocks only the other tile works on: keep the two-arrival stage protocol going
+            mbar_wait(&k_full[j % F_NS], (j / F_NS) & 1);
+            mbar_arrive_p(lead, &k_empty[j % F_NS]);
+            mbar_wait(&v_full[j % F_NS], (j / F_NS) & 1);
+            mbar_arrive_p(lead, &v_empty[j % F_NS]);
         }
     } else if (warp >= 4) {
         const int t = (warp - 4) >> 2;
@@ -318,15 +408,35 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const uint32_t t_o = tmem_base + lane_field + 256 + t * 128;
         const uint64_t sc2 = pk2(scale_log2, scale_log2);
         float m_run = -INFINITY, l_run = 0.f;
+        t0 = clock64();
         for (int j = 0; j < n; ++j) {
             const int buf = j & 1;
             mbar_wait(&s_full[t * 2 + buf], (j >> 1) & 1);
             tc_fence_after();
+            FA2_TICK(0)
             const uint32_t t_s = tmem_base + lane_field + t * 128 + buf * 64;
             uint32_t r[64];
-            tmem_ld_x32(t_s, r);
-            tmem_ld_x32(t_s + 32, r + 32);
-            tmem_ld_wait();
+            if (!(dbg & 2)) {
+                tmem_ld_x32(t_s, r);
+                tmem_ld_x32(t_s + 32, r + 32);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) r[i] = 0x3f800000u + i + j;
+            }
+            FA2_TICK(1)
+            if (dbg & 1) {
+                tmem_st_x32(t_s, r);
+                tmem_st_wait();
+                FA2_TICK(4)
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&p_ready[t * 2 + buf]);
+                FA2_TICK(5)
+                l_run = 1.f;
+                m_run = 0.f;
+                continue;
+            }
             if (causal) {
                 const int lim = qrow - j * F_BK;   // columns <= lim of this block are visible to this row
                 if (__any_sync(0xffffffffu, lim < F_BK - 1)) {
@@ -364,6 +474,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 l_run *= alpha;
                 m_run = m_new;
             }
+            FA2_TICK(2)
             const uint64_t nm2 = pk2(-m_run, -m_run);
             uint64_t sa = 0ull, sb = 0ull;
             uint32_t pk[32];
@@ -374,22 +485,31 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 upk2(fma2(pk2u(r[i + 2], r[i + 3]), sc2, nm2), b0, b1);
                 a0 = ex2(a0);
                 a1 = ex2(a1);
-                b0 = ex2(b0);
-                b1 = ex2(b1);
+                if (F_POLY && (i & 4)) {   // every fourth pair on the FMA pipe (balances MUFU time against issue slots)
+                    exp2_poly2(pk2(fmaxf(b0, -125.f), fmaxf(b1, -125.f)), b0, b1);
+                } else {
+                    b0 = ex2(b0);
+                    b1 = ex2(b1);
+                }
                 pk[i >> 1] = Cvt<T>::pack2(a0, a1);
                 pk[(i >> 1) + 1] = Cvt<T>::pack2(b0, b1);
                 sa = add2(sa, pk2(a0, a1));
                 sb = add2(sb, pk2(b0, b1));
             }
+            FA2_TICK(3)
             tmem_st_x32(t_s, pk);
             float s0, s1;
             upk2(add2(sa, sb), s0, s1);
             l_run += s0 + s1;
             tmem_st_wait();
+            FA2_TICK(4)
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&p_ready[t * 2 + buf]);
+            FA2_TICK(5)
         }
+        if (tm && qd == 0 && lane == 0)
+            for (int i = 0; i < 6; ++i) prof[t * 8 + i] = acc[i];
         // epilogue: O / l -> shared (the tile's Q buffer, same swizzled layout) -> TMA store; log-sum-exp for backward
         // (a parity wait on pv_done would be ambiguous here: this thread may be two products behind)
         mbar_wait(&o_final[t], 0);
@@ -426,7 +546,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 2) tmem_dealloc<512>(tmem_base);
+    if (warp == 3) tmem_dealloc<512>(tmem_base);
 }
 
 // ================================================================================================ backward
@@ -458,15 +578,41 @@ __global__ void __launch_bounds__(256) flash_prep_kernel(const T* __restrict__ d
     }
 }
 
+// dq[b, s, h, :] (16 bit, strided) = dq_acc[b, h, :, s] (fp32, transposed accumulator of the backward kernel).
+// One block per (32 queries, batch * head): coalesced 128-byte reads along s, padded shared tile, 256-byte row writes.
+template <typename T>
+__global__ void __launch_bounds__(256) flash_dq_finish_kernel(const float* __restrict__ acc, T* __restrict__ dq, int S,
+                                                              int H, long sb, long ss, long sh) {
+    __shared__ float tile[128][33];
+    const int s0 = blockIdx.x * 32;
+    const int bh = blockIdx.y;
+    const int b = bh / H, h = bh - b * H;
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float* src = acc + (long)bh * 128 * S + s0 + lane;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) tile[w * 16 + i][lane] = src[(long)(w * 16 + i) * S];
+    __syncthreads();
+    T* dst = dq + b * sb + h * sh;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int s = w * 4 + i;
+        uint2 o;
+        o.x = Cvt<T>::pack2(tile[lane * 4][s], tile[lane * 4 + 1][s]);
+        o.y = Cvt<T>::pack2(tile[lane * 4 + 2][s], tile[lane * 4 + 3][s]);
+        *reinterpret_cast<uint2*>(dst + (long)(s0 + s) * ss + lane * 4) = o;
+    }
+}
+
 constexpr int B_OFF_K = 0;                          // [128 kv x 128 d] 32 KiB (two chunks of 16 KiB)
 constexpr int B_OFF_V = B_OFF_K + 32768;
 constexpr int B_OFF_Q = B_OFF_V + 32768;            // 3 x [64 q x 128 d] 16 KiB (two chunks of 8 KiB)
-constexpr int B_OFF_DO = B_OFF_Q + 3 * 16384;       // 2 x 16 KiB
-constexpr int B_OFF_DS = B_OFF_DO + 2 * 16384;      // 2 x [128 kv x 64 q] 16 KiB
-constexpr int B_OFF_DQ = B_OFF_DS + 2 * 16384;      // fp32 [64 q x 128 d] 32 KiB
+constexpr int B_OFF_DO = B_OFF_Q + 3 * 16384;       // 3 x 16 KiB
+constexpr int B_OFF_DS = B_OFF_DO + 3 * 16384;      // [128 kv x 64 q] 16 KiB
+constexpr int B_OFF_DQ = B_OFF_DS + 16384;          // fp32 dQ^T staging: 2 x [128 d x 32 q] 16 KiB, swizzled
 constexpr int B_OFF_LD = B_OFF_DQ + 32768;          // 3 x (64 -lse2 | 64 -delta) fp32
 constexpr int B_OFF_BAR = B_OFF_LD + 3 * 512;
 constexpr int B_SMEM = B_OFF_BAR + 512 + 1024;
+constexpr bool B_POLY = true;   // half of the exponentials as a polynomial on the FMA pipe
 constexpr int TM_ST = 0, TM_DPT = 128, TM_DQT = 192, TM_DV = 256, TM_DK = 384;
 
 template <typename T>
@@ -475,7 +621,8 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
                   const __grid_constant__ CUtensorMap tmdK, const __grid_constant__ CUtensorMap tmdV,
                   const __grid_constant__ CUtensorMap tmDQ, const float* __restrict__ nlse2,
-                  const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal) {
+                  const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal, int dbg,
+                  long long* prof) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + B_OFF_K;
@@ -489,18 +636,18 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     uint64_t* kv_full = bars;            // [1]
     uint64_t* q_full = bars + 1;         // [3] Q tile + its -lse2 / -delta rows
     uint64_t* q_free = bars + 4;         // [3] dK UMMAs (last readers of the stage) completed
-    uint64_t* do_full = bars + 7;        // [2]
-    uint64_t* do_free = bars + 9;        // [2] dV UMMAs completed
-    uint64_t* s_full = bars + 11;        // [2] S^T in TMEM
-    uint64_t* dp_full = bars + 13;       // [1] dP^T in TMEM
-    uint64_t* dp_free = bars + 14;       // [1] dP^T read into registers (8 warps)
-    uint64_t* p_ready = bars + 15;       // [2] P^T stored in TMEM (8 warps)
-    uint64_t* ds_ready = bars + 17;      // [2] dS^T stored in TMEM and shared memory (8 warps)
-    uint64_t* ds_free = bars + 19;       // [2] dQ^T UMMAs (readers of the shared dS^T buffer) completed
-    uint64_t* dq_full = bars + 21;       // [1] dQ^T in TMEM
-    uint64_t* dq_free = bars + 22;       // [1] dQ^T read into registers (4 warps)
-    uint64_t* fin = bars + 23;           // [1] everything issued has completed
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+    uint64_t* do_full = bars + 7;        // [3]
+    uint64_t* do_free = bars + 10;       // [3] dV UMMAs completed
+    uint64_t* s_full = bars + 13;        // [2] S^T in TMEM
+    uint64_t* dp_full = bars + 15;       // [1] dP^T in TMEM
+    uint64_t* dp_free = bars + 16;       // [1] dP^T read into registers (8 warps)
+    uint64_t* pds_ready = bars + 17;     // [2] P^T, dS^T stored in TMEM and dS^T in shared memory (8 warps)
+    uint64_t* ds_free = bars + 19;       // [1] dQ^T UMMAs (readers of the shared dS^T tile) completed
+    uint64_t* dq_full = bars + 20;       // [1] dQ^T in TMEM
+    uint64_t* dq_free = bars + 21;       // [1] dQ^T read into registers (4 warps)
+    uint64_t* fin = bars + 22;           // [1] everything issued has completed
+    uint64_t* st_free = bars + 23;       // [2] dV / dK UMMAs (readers of P^T / dS^T in the score buffer) completed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
 
     const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int lane = threadIdx.x & 31;
@@ -508,6 +655,8 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     const int jb = blockIdx.y;                       // key block; block 0 walks the most query blocks and starts first
     const int i0 = causal ? jb * 2 : 0;              // first 64-row query block that sees these keys
     const int nit = S / 64 - i0;
+    const bool tm = prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
+    long long t0 = 0, acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
@@ -521,15 +670,15 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         for (int i = 0; i < 3; ++i) {
             mbar_init(&q_full[i], 1);
             mbar_init(&q_free[i], 1);
-        }
-        for (int i = 0; i < 2; ++i) {
             mbar_init(&do_full[i], 1);
             mbar_init(&do_free[i], 1);
-            mbar_init(&s_full[i], 1);
-            mbar_init(&p_ready[i], 8);
-            mbar_init(&ds_ready[i], 8);
-            mbar_init(&ds_free[i], 1);
         }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s_full[i], 1);
+            mbar_init(&pds_ready[i], 8);
+            mbar_init(&st_free[i], 1);
+        }
+        mbar_init(ds_free, 1);
         mbar_init(dp_full, 1);
         mbar_init(dp_free, 8);
         mbar_init(dq_full, 1);
@@ -537,7 +686,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         mbar_init(fin, 1);
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc<512>(tmem_slot);
+    if (warp == 3) tmem_alloc<512>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -553,107 +702,113 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             const long bh_off = (long)blockIdx.x * S;
             for (int it = 0; it < nit; ++it) {
                 const int q0 = (i0 + it) * 64;
-                const int s3 = it % 3, s2 = it & 1;
+                const int s3 = it % 3;
                 if (it >= 3) mbar_wait(&q_free[s3], ((it / 3) - 1) & 1);
                 mbar_arrive_expect_tx(&q_full[s3], 16384 + 512);
                 tma_load_4d(sQ + s3 * 16384, &tmQ, &q_full[s3], 0, h, q0, b);
                 tma_load_4d(sQ + s3 * 16384 + 8192, &tmQ, &q_full[s3], 64, h, q0, b);
                 bulk_load(sLD + s3 * 128, nlse2 + bh_off + q0, 256, &q_full[s3]);
                 bulk_load(sLD + s3 * 128 + 64, ndelta + bh_off + q0, 256, &q_full[s3]);
-                if (it >= 2) mbar_wait(&do_free[s2], ((it >> 1) - 1) & 1);
-                mbar_arrive_expect_tx(&do_full[s2], 16384);
-                tma_load_4d(sdO + s2 * 16384, &tmdO, &do_full[s2], 0, h, q0, b);
-                tma_load_4d(sdO + s2 * 16384 + 8192, &tmdO, &do_full[s2], 64, h, q0, b);
+                if (it >= 3) mbar_wait(&do_free[s3], ((it / 3) - 1) & 1);
+                mbar_arrive_expect_tx(&do_full[s3], 16384);
+                tma_load_4d(sdO + s3 * 16384, &tmdO, &do_full[s3], 0, h, q0, b);
+                tma_load_4d(sdO + s3 * 16384 + 8192, &tmdO, &do_full[s3], 64, h, q0, b);
             }
         }
     } else if (warp == 1) {
-        if (elect_one()) {
-            constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
-            const uint32_t id_st = make_idesc_f16(128, 64, is_bf16, 0, 0);    // K-major x K-major, N = 64 queries
-            const uint32_t id_acc = make_idesc_f16(128, 128, is_bf16, 0, 1);  // A from TMEM, B MN-major, N = 128 (d)
-            const uint32_t id_dq = make_idesc_f16(128, 64, is_bf16, 1, 1);    // both MN-major, N = 64 queries
-            const uint32_t k_km = desc_lo(sK, 16), v_km = desc_lo(sV, 16);
-            const uint32_t k_mn = desc_lo(sK, 16384);
-            auto koff_a = [](int k) { return (uint32_t)((k >> 2) * (16384 >> 4) + (k & 3) * 2); };
-            auto koff_b = [](int k) { return (uint32_t)((k >> 2) * (8192 >> 4) + (k & 3) * 2); };
-            auto issue_st = [&](int it) {   // S^T[kv, q] = K[kv, :] . Q[q, :]
-                const uint32_t q_km = desc_lo(sQ + (it % 3) * 16384, 16);
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_f16_lohi(tmem_base + TM_ST + (it & 1) * 64, k_km + koff_a(k), q_km + koff_b(k), DESC_HI, id_st,
-                                  k != 0);
-                umma_commit(&s_full[it & 1]);
-            };
-            auto issue_dpt = [&](int it) {  // dP^T[kv, q] = V[kv, :] . dO[q, :]
-                const uint32_t do_km = desc_lo(sdO + (it & 1) * 16384, 16);
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_f16_lohi(tmem_base + TM_DPT, v_km + koff_a(k), do_km + koff_b(k), DESC_HI, id_st, k != 0);
-                umma_commit(dp_full);
-            };
-            // P^T / dS^T of query columns [32 u, 32 u + 32) live in columns 32 u + [0, 16) / 32 u + [16, 32) of the score
-            // buffer (every softmax warp writes only over columns it has read itself); 16 queries = 8 columns per k-step
-            auto issue_dv = [&](int it) {   // dV[kv, d] += P^T[kv, q] dO[q, d]
-                const uint32_t do_mn = desc_lo(sdO + (it & 1) * 16384, 8192);
-                const uint32_t a = tmem_base + TM_ST + (it & 1) * 64;
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    umma_ts(tmem_base + TM_DV, a + (k >> 1) * 32 + (k & 1) * 8, do_mn + k * (2048u >> 4), DESC_HI, id_acc,
-                            (it | k) != 0);
-            };
-            auto issue_dk = [&](int it) {   // dK[kv, d] += dS^T[kv, q] Q[q, d]
-                const uint32_t q_mn = desc_lo(sQ + (it % 3) * 16384, 8192);
-                const uint32_t a = tmem_base + TM_ST + (it & 1) * 64 + 16;
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    umma_ts(tmem_base + TM_DK, a + (k >> 1) * 32 + (k & 1) * 8, q_mn + k * (2048u >> 4), DESC_HI, id_acc,
-                            (it | k) != 0);
-            };
-            auto issue_dqt = [&](int it) {  // dQ^T[d, q] = K^T[d, kv] dS^T[kv, q]
-                const uint32_t ds_mn = desc_lo(sdS + (it & 1) * 16384, 8192);
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    umma_f16_lohi(tmem_base + TM_DQT, k_mn + k * (2048u >> 4), ds_mn + k * (2048u >> 4), DESC_HI, id_dq,
-                                  k != 0);
-            };
-            mbar_wait(kv_full, 0);
-            mbar_wait(&q_full[0], 0);
+        // Issuing warp A: the two score products of every block, as far ahead as their buffers allow.
+        const uint32_t lead = elect_one() ? 1u : 0u;
+        constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+        const uint32_t id_st = make_idesc_f16(128, 64, is_bf16, 0, 0);    // K-major x K-major, N = 64 queries
+        const uint32_t k_km = desc_lo(sK, 16), v_km = desc_lo(sV, 16);
+        auto koff_a = [](int k) { return (uint32_t)((k >> 2) * (16384 >> 4) + (k & 3) * 2); };
+        auto koff_b = [](int k) { return (uint32_t)((k >> 2) * (8192 >> 4) + (k & 3) * 2); };
+        mbar_wait(kv_full, 0);
+        t0 = clock64();
+        for (int n = 0; n < nit; ++n) {
+            // S^T[kv, q] = K[kv, :] . Q[q, :] into score buffer n & 1 (free once dV / dK of block n - 2 have completed)
+            mbar_wait(&q_full[n % 3], (n / 3) & 1);
+            FA2_TICK(0)
+            if (n >= 2) mbar_wait(&st_free[n & 1], ((n >> 1) - 1) & 1);
             tc_fence_after();
-            issue_st(0);
-            mbar_wait(&do_full[0], 0);
-            tc_fence_after();
-            issue_dpt(0);
-            for (int it = 0; it < nit; ++it) {
-                if (it + 1 < nit) {
-                    const int n = it + 1;
-                    mbar_wait(&q_full[n % 3], (n / 3) & 1);
-                    tc_fence_after();
-                    issue_st(n);
-                }
-                mbar_wait(&p_ready[it & 1], (it >> 1) & 1);
-                tc_fence_after();
-                issue_dv(it);
-                umma_commit(&do_free[it & 1]);
-                if (it + 1 < nit) {
-                    const int n = it + 1;
-                    mbar_wait(dp_free, it & 1);
-                    mbar_wait(&do_full[n & 1], (n >> 1) & 1);
-                    tc_fence_after();
-                    issue_dpt(n);
-                }
-                mbar_wait(&ds_ready[it & 1], (it >> 1) & 1);
-                tc_fence_after();
-                issue_dk(it);
-                umma_commit(&q_free[it % 3]);
-                if (it > 0) {
-                    mbar_wait(dq_free, (it - 1) & 1);
-                    tc_fence_after();
-                }
-                issue_dqt(it);
-                umma_commit(dq_full);
-                umma_commit(&ds_free[it & 1]);
+            FA2_TICK(1)
+            {
+                const uint32_t q_km = desc_lo(sQ + (n % 3) * 16384, 16);
+                const uint32_t d = tmem_base + TM_ST + (n & 1) * 64;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_ss_p(lead, d, k_km + koff_a(k), q_km + koff_b(k), DESC_HI, id_st, k != 0);
+                umma_commit_p(lead, &s_full[n & 1]);
             }
-            umma_commit(fin);
+            FA2_TICK(2)
+            // dP^T[kv, q] = V[kv, :] . dO[q, :]: one buffer, refilled once block n - 1 has been pulled into registers
+            if (n >= 1) mbar_wait(dp_free, (n - 1) & 1);
+            FA2_TICK(3)
+            mbar_wait(&do_full[n % 3], (n / 3) & 1);
+            tc_fence_after();
+            FA2_TICK(4)
+            {
+                const uint32_t do_km = desc_lo(sdO + (n % 3) * 16384, 16);
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    umma_ss_p(lead, tmem_base + TM_DPT, v_km + koff_a(k), do_km + koff_b(k), DESC_HI, id_st, k != 0);
+                umma_commit_p(lead, dp_full);
+            }
+            FA2_TICK(5)
+        }
+        if (tm && lead) for (int i = 0; i < 6; ++i) prof[i] = acc[i];
+    } else if (warp == 2) {
+        // Issuing warp B: the three products that consume P^T / dS^T.
+        // P^T / dS^T of query columns [32 u, 32 u + 32) live in columns 32 u + [0, 16) / 32 u + [16, 32) of the score buffer
+        // (every softmax warp writes only over columns it has read itself); 16 queries = 8 columns per k-step.
+        const uint32_t lead = elect_one() ? 1u : 0u;
+        constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
+        const uint32_t id_acc = make_idesc_f16(128, 128, is_bf16, 0, 1);  // A from TMEM, B MN-major, N = 128 (d)
+        const uint32_t id_dq = make_idesc_f16(128, 64, is_bf16, 1, 1);    // both MN-major, N = 64 queries
+        const uint32_t k_mn = desc_lo(sK, 16384);
+        const uint32_t ds_mn = desc_lo(sdS, 8192);
+        t0 = clock64();
+        const long long t_begin = t0;
+        for (int it = 0; it < nit; ++it) {
+            mbar_wait(&pds_ready[it & 1], (it >> 1) & 1);
+            tc_fence_after();
+            FA2_TICK(0)
+            const uint32_t a = tmem_base + TM_ST + (it & 1) * 64;
+            const uint32_t do_mn = desc_lo(sdO + (it % 3) * 16384, 8192);
+            const uint32_t q_mn = desc_lo(sQ + (it % 3) * 16384, 8192);
+            if (!(dbg & 32))
+#pragma unroll
+            for (int k = 0; k < 4; ++k)   // dV[kv, d] += P^T[kv, q] dO[q, d]
+                umma_ts_p(lead, tmem_base + TM_DV, a + (k >> 1) * 32 + (k & 1) * 8, do_mn + k * (2048u >> 4), DESC_HI,
+                          id_acc, (it | k) != 0);
+            umma_commit_p(lead, &do_free[it % 3]);
+            if (!(dbg & 32))
+#pragma unroll
+            for (int k = 0; k < 4; ++k)   // dK[kv, d] += dS^T[kv, q] Q[q, d]
+                umma_ts_p(lead, tmem_base + TM_DK, a + 16 + (k >> 1) * 32 + (k & 1) * 8, q_mn + k * (2048u >> 4), DESC_HI,
+                          id_acc, (it | k) != 0);
+            umma_commit_p(lead, &q_free[it % 3]);
+            umma_commit_p(lead, &st_free[it & 1]);
+            FA2_TICK(1)
+            if (it > 0) {
+                mbar_wait(dq_free, (it - 1) & 1);
+                tc_fence_after();
+            }
+            FA2_TICK(2)
+            if (!(dbg & 16))
+#pragma unroll
+            for (int k = 0; k < 8; ++k)   // dQ^T[d, q] = K^T[d, kv] dS^T[kv, q]
+                umma_ss_p(lead, tmem_base + TM_DQT, k_mn + k * (2048u >> 4), ds_mn + k * (2048u >> 4), DESC_HI, id_dq,
+                          k != 0);
+            umma_commit_p(lead, dq_full);
+            umma_commit_p(lead, ds_free);
+            FA2_TICK(3)
+        }
+        umma_commit_p(lead, fin);
+        if (tm && lead) {
+            for (int i = 0; i < 4; ++i) prof[8 + i] = acc[i];
+            prof[30] = clock64() - t_begin;
+            prof[31] = nit;
         }
     } else if (warp >= 4 && warp < 12) {
         const int qd = warp & 3;
@@ -667,68 +822,84 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         for (int it = 0; it < nit; ++it) {
             const int buf = it & 1;
             const int q0 = (i0 + it) * 64 + half * 32;        // global query index of this thread's first column
+            if (it == 0) t0 = clock64();
             mbar_wait(&q_full[it % 3], (it / 3) & 1);         // the -lse2 / -delta rows travel with the Q tile
             const float4* nl = reinterpret_cast<const float4*>(sLD + (it % 3) * 128 + half * 32);
             const float4* nd = reinterpret_cast<const float4*>(sLD + (it % 3) * 128 + 64 + half * 32);
             mbar_wait(&s_full[buf], (it >> 1) & 1);
-            tc_fence_after();
-            const uint32_t t_s = tmem_base + lane_field + TM_ST + buf * 64 + half * 32;
-            uint32_t rs[32];
-            tmem_ld_x32(t_s, rs);
-            tmem_ld_wait();
-            float p[32];
-#pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-                const float4 l4 = nl[i >> 2];
-                upk2(fma2(pk2u(rs[i], rs[i + 1]), sc2, pk2(l4.x, l4.y)), p[i], p[i + 1]);
-                upk2(fma2(pk2u(rs[i + 2], rs[i + 3]), sc2, pk2(l4.z, l4.w)), p[i + 2], p[i + 3]);
-            }
-#pragma unroll
-            for (int i = 0; i < 32; ++i) p[i] = ex2(p[i]);
-            if (causal && it < 2) {
-#pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (q0 + i < kvg) p[i] = 0.f;
-            }
-            uint32_t pk[16];
-#pragma unroll
-            for (int i = 0; i < 32; i += 2) pk[i >> 1] = Cvt<T>::pack2(p[i], p[i + 1]);
-            tmem_st_x16(t_s, pk);
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&p_ready[buf]);
-
+            FA2_TICK(0)
             mbar_wait(dp_full, it & 1);
             tc_fence_after();
-            uint32_t rp[32];
-            tmem_ld_x32(tmem_base + lane_field + TM_DPT + half * 32, rp);
-            tmem_ld_wait();
+            FA2_TICK(1)
+            const uint32_t t_s = tmem_base + lane_field + TM_ST + buf * 64 + half * 32;
+            uint32_t rs[32], rp[32];
+            if (!(dbg & 8)) {
+                tmem_ld_x32(t_s, rs);
+                tmem_ld_x32(tmem_base + lane_field + TM_DPT + half * 32, rp);
+                tmem_ld_wait();
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) rs[i] = rp[i] = 0x3c000000u + i + it;
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(dp_free);
+            FA2_TICK(2)
+            const bool diag = causal && it < 2;
+            uint32_t pk[32];   // [0, 16) P^T, [16, 32) dS^T: the 32 columns this warp has just read
+            if (dbg & 1) {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) pk[i] = rs[i] ^ rp[i];
+            } else
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
+                const float4 l4 = nl[i >> 2];
                 const float4 d4 = nd[i >> 2];
+                float p0, p1, p2, p3;
+                upk2(fma2(pk2u(rs[i], rs[i + 1]), sc2, pk2(l4.x, l4.y)), p0, p1);
+                const uint64_t x23 = fma2(pk2u(rs[i + 2], rs[i + 3]), sc2, pk2(l4.z, l4.w));
+                p0 = ex2(p0);
+                p1 = ex2(p1);
+                if (B_POLY) {
+                    float c2, c3;
+                    upk2(x23, c2, c3);
+                    exp2_poly2(pk2(fmaxf(c2, -125.f), fmaxf(c3, -125.f)), p2, p3);
+                } else {
+                    upk2(x23, p2, p3);
+                    p2 = ex2(p2);
+                    p3 = ex2(p3);
+                }
+                if (diag) {
+                    if (q0 + i < kvg) p0 = 0.f;
+                    if (q0 + i + 1 < kvg) p1 = 0.f;
+                    if (q0 + i + 2 < kvg) p2 = 0.f;
+                    if (q0 + i + 3 < kvg) p3 = 0.f;
+                }
                 float a0, a1, b0, b1;
-                upk2(mul2(fma2(pk2u(rp[i], rp[i + 1]), s2, pk2(d4.x, d4.y)), pk2(p[i], p[i + 1])), a0, a1);
-                upk2(mul2(fma2(pk2u(rp[i + 2], rp[i + 3]), s2, pk2(d4.z, d4.w)), pk2(p[i + 2], p[i + 3])), b0, b1);
-                pk[i >> 1] = Cvt<T>::pack2(a0, a1);
-                pk[(i >> 1) + 1] = Cvt<T>::pack2(b0, b1);
+                upk2(mul2(fma2(pk2u(rp[i], rp[i + 1]), s2, pk2(d4.x, d4.y)), pk2(p0, p1)), a0, a1);
+                upk2(mul2(fma2(pk2u(rp[i + 2], rp[i + 3]), s2, pk2(d4.z, d4.w)), pk2(p2, p3)), b0, b1);
+                pk[i >> 1] = Cvt<T>::pack2(p0, p1);
+                pk[(i >> 1) + 1] = Cvt<T>::pack2(p2, p3);
+                pk[16 + (i >> 1)] = Cvt<T>::pack2(a0, a1);
+                pk[17 + (i >> 1)] = Cvt<T>::pack2(b0, b1);
             }
-            tmem_st_x16(t_s + 16, pk);
-            if (it >= 2) mbar_wait(&ds_free[buf], ((it >> 1) - 1) & 1);
-            uint8_t* dst = sdS + buf * 16384 + row * 128;
+            FA2_TICK(3)
+            tmem_st_x32(t_s, pk);
+            if (it >= 1) mbar_wait(ds_free, (it - 1) & 1);   // dQ^T of the previous block has finished reading the tile
+            FA2_TICK(4)
+            uint8_t* dst = sdS + row * 128;
 #pragma unroll
             for (int u = 0; u < 4; ++u)
                 *reinterpret_cast<uint4*>(dst + (((half * 4 + u) ^ sw) << 4)) =
-                    make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+                    make_uint4(pk[16 + u * 4], pk[17 + u * 4], pk[18 + u * 4], pk[19 + u * 4]);
             tmem_st_wait();
             tc_fence_before();
-            fence_proxy_async_smem();
+            if (!(dbg & 64)) fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&ds_ready[buf]);
+            if (lane == 0) mbar_arrive(&pds_ready[buf]);
+            FA2_TICK(5)
         }
+        if (tm && warp == 4 && lane == 0) for (int i = 0; i < 6; ++i) prof[16 + i] = acc[i];
         // dV / dK: TMEM (lane = key row) -> 16 bit -> shared (the K / V tiles are dead) -> TMA store
         mbar_wait(fin, 0);
         tc_fence_after();
@@ -766,8 +937,10 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const uint32_t lane_field = static_cast<uint32_t>(qd * 32) << 16;
         for (int it = 0; it < nit; ++it) {
             const int q0 = (i0 + it) * 64;
+            if (it == 0) t0 = clock64();
             mbar_wait(dq_full, it & 1);
             tc_fence_after();
+            FA2_TICK(0)
             uint32_t r[64];
             tmem_ld_x32(tmem_base + lane_field + TM_DQT, r);
             tmem_ld_x32(tmem_base + lane_field + TM_DQT + 32, r + 32);
@@ -775,28 +948,55 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(dq_free);
+            FA2_TICK(1)
             if (it > 0) {   // the previous reduction must have finished reading the staging tile
                 if (warp == 12 && lane == 0) tma_store_wait_read<0>();
                 named_bar_sync(3, 128);
             }
+            FA2_TICK(2)
+            if (dbg & 2) continue;
+            // The accumulator in global memory is kept TRANSPOSED ([B, H, D, S]) so that this thread's 64 values are
+            // contiguous: 16 vector stores into two 128-byte-swizzled [128 d x 32 q] tiles instead of 64 scalar stores
+            // (the proxy fence that follows costs time in proportion to the stores in flight: ~1000 cycles with 64).
+            {
+                uint8_t* base = reinterpret_cast<uint8_t*>(sdQ) + d * 128;
+                const int sw = d & 7;
 #pragma unroll
-            for (int q = 0; q < 64; ++q) sdQ[q * 128 + d] = __uint_as_float(r[q]);
-            fence_proxy_async_smem();
+                for (int hh = 0; hh < 2; ++hh)
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        *reinterpret_cast<uint4*>(base + hh * 16384 + ((u ^ sw) << 4)) =
+                            make_uint4(r[hh * 32 + u * 4], r[hh * 32 + u * 4 + 1], r[hh * 32 + u * 4 + 2],
+                                       r[hh * 32 + u * 4 + 3]);
+            }
+            if (!(dbg & 64)) fence_proxy_async_smem();
             named_bar_sync(3, 128);
-            if (warp == 12 && lane == 0) {
-                tma_reduce_add_4d(&tmDQ, sdQ, 0, h, q0, b);
+            if (warp == 12 && lane == 0 && !(dbg & 4)) {
+                tma_reduce_add_4d(&tmDQ, sdQ, q0, 0, h, b);
+                tma_reduce_add_4d(&tmDQ, reinterpret_cast<uint8_t*>(sdQ) + 16384, q0 + 32, 0, h, b);
                 tma_store_commit();
             }
+            FA2_TICK(3)
         }
+        if (tm && warp == 12 && lane == 0) for (int i = 0; i < 4; ++i) prof[24 + i] = acc[i];
         if (warp == 12 && lane == 0) tma_store_wait<0>();
     }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (warp == 2) tmem_dealloc<512>(tmem_base);
+    if (warp == 3) tmem_dealloc<512>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------ host launchers
+// Experiment switches (0 in production): the kernels skip parts of their work so that the remaining parts can be timed
+// alone (results are then garbage). Forward: 1 = no softmax arithmetic, 2 = no TMEM score load, 4 = no P V products.
+// (forward, timing only: 16 = score UMMAs issued with N = 128, 32 = K / V tiles not reloaded after the first ring fill)
+// Backward: 1 = no P / dS arithmetic, 2 = dQ drain stops after its TMEM load, 4 = no dQ reduce-add, 8 = no TMEM loads
+// in the softmax warps, 16 = no dQ^T UMMAs, 32 = no dV / dK UMMAs, 64 = no proxy fences.
+static int g_dbg = 0;
+static long long* g_prof = nullptr;
+void set_debug_mode(int m) { g_dbg = m; }
+void set_debug_timers(long long* p) { g_prof = p; }
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
                int B, int S, int H, float scale_log2, int causal, int bf16, cudaStream_t stream) {
     if (S % 256) return DSB_ERR_SIZE;
@@ -806,12 +1006,12 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         auto kern = flash_fwd2_kernel<__nv_bfloat16>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof);
     } else {
         auto kern = flash_fwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal);
+        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
@@ -832,6 +1032,17 @@ int launch_prep(const void* dO, const void* O, const float* lse, float* nlse2, f
     return e == cudaSuccess ? 0 : -(int)e;
 }
 
+int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, cudaStream_t stream) {
+    dim3 grid(S / 32, B * H);
+    if (bf16)
+        flash_dq_finish_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(acc, (__nv_bfloat16*)dq, S, H, s_dq[0], s_dq[1],
+                                                                        s_dq[2]);
+    else
+        flash_dq_finish_kernel<__half><<<grid, 256, 0, stream>>>(acc, (__half*)dq, S, H, s_dq[0], s_dq[1], s_dq[2]);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
 int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* nlse2,
                const float* ndelta, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
@@ -844,13 +1055,13 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal);
+                                            causal, g_dbg, g_prof);
     } else {
         auto kern = flash_bwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal);
+                                            causal, g_dbg, g_prof);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

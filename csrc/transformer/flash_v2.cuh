@@ -15,12 +15,18 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
 int launch_prep(const void* dO, const void* O, const float* lse, float* lse2, float* delta_s, int B, int S, int H,
                 const long* s_do, const long* s_o, float scale, int bf16, cudaStream_t stream);
 
-// Backward: tq / tdo with 64-row boxes, tk / tv / tdk / tdv with 128-row boxes, tdq = fp32 accumulator map with
-// box {128, 1, 64, 1} and no swizzle; S a multiple of 128.
+// Backward: tq / tdo with 64-row boxes, tk / tv / tdk / tdv with 128-row boxes, tdq = map of the TRANSPOSED fp32
+// accumulator [B, H, D, S] (dims S, D, H, B; box {32, 128, 1, 1}, 128-byte swizzle); S a multiple of 128.
 int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* lse2,
                const float* delta_s, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
                cudaStream_t stream);
+
+// dq (16 bit, [B, S, H, 128] with strides s_dq) = transpose of the fp32 accumulator [B, H, 128, S].
+int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, cudaStream_t stream);
+
+void set_debug_mode(int m);
+void set_debug_timers(long long* p);   // 32 int64: phase totals of forward CTA (0, 0)
 
 }  // namespace fa2
 }  // namespace dsb

@@ -6,11 +6,10 @@ backward: attention backward -> inverse rotary written DIRECTLY into the dQKV bu
           no gradient-accumulation adds, no clones).
 
 Two attention back ends, selected with DSB_ATTN (or `set_attention_backend`):
-  "native": the tcgen05 flash-attention kernels of csrc/transformer/flash_attn.cu (forward + backward, V read in place
-            from the fused activation, dV written in place into the dQKV buffer);
-  "sdpa"  : the library flash kernel behind torch SDPA. Default, because it is the faster one today
-            (bench/flash_attn_bench.py: 0.073 / 0.235 ms vs 0.119 / 0.378 ms forward / backward at batch 4 x 16 heads x
-            seq 2048); the native path needs head dim 128 and seq % 128 == 0 and falls back to "sdpa" otherwise.
+  "native": the tcgen05 flash-attention kernels of csrc/transformer/flash_attn_v2.cu (forward + backward, V read in
+            place from the fused activation, dV written in place into the dQKV buffer). Default. Needs head dim 128 and
+            seq % 128 == 0; other shapes run the library path.
+  "sdpa"  : the library flash kernel behind torch SDPA, kept for comparison (bench/flash_attn_bench.py).
 """
 import ctypes as C
 import os
@@ -36,17 +35,19 @@ N.register_sigs({
 
 N.register_sigs({
     "dsb_flash_attn_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p],
+    "dsb_flash_attn_bwd2": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p],
 })
 
 _tables = {}
 
 
 def set_flash_bwd_variant(v):
-    """2: transposed backward with P^T / dS^T in tensor memory (default); 1: first-generation kernel."""
-    lib = N.cuda_lib()
-    lib.dsb_flash_attn_bwd_variant.argtypes = [C.c_int]
-    lib.dsb_flash_attn_bwd_variant.restype = C.c_int
-    return lib.dsb_flash_attn_bwd_variant(int(v))
+    """2: transposed backward with P^T / dS^T in tensor memory (default); 1: first-generation kernel (returns dq as its
+    fp32 accumulator). Returns the previous setting."""
+    global _bwd_gen
+    assert v in (1, 2)
+    prev, _bwd_gen = _bwd_gen, v
+    return prev
 
 
 def set_flash_fwd_variant(keys_per_step):
@@ -58,10 +59,14 @@ def set_flash_fwd_variant(keys_per_step):
     return lib.dsb_flash_attn_fwd_variant(int(keys_per_step))
 
 
-def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv=None):
-    """Backward of `flash_attn_fwd` on the tcgen05 kernel. All tensors [B, S, H, 128] views with unit last stride
-    (dk / dv may be slices of a fused dQKV buffer). Returns (dq fp32 [B, S, H, 128] contiguous, dk, dv): dq is
-    accumulated in fp32 across key blocks and left to the caller to cast (the inverse rotary / cast that follows)."""
+_bwd_gen = 2
+
+
+def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv=None, dq=None):
+    """Backward of `flash_attn_fwd` on the tcgen05 kernels. All tensors [B, S, H, 128] views with unit last stride
+    (dq / dk / dv may be slices of a fused dQKV buffer). Returns (dq, dk, dv). With the default (second-generation)
+    kernel dq comes back in the input dtype; the first-generation kernel (set_flash_bwd_variant(1)) returns its fp32
+    accumulator [B, S, H, 128] and ignores `dq`."""
     B, S, H, D = q.shape
     if scale is None:
         scale = 1.0 / (D ** 0.5)
@@ -69,15 +74,28 @@ def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv
         dk = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
     if dv is None:
         dv = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
+    lib = N.cuda_lib()
+    if _bwd_gen == 2:
+        if dq is None:
+            dq = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
+        scratch = torch.empty((2 + D) * B * H * S, dtype=torch.float32, device=q.device)
+        ts = (dout, q, k, v, out, dq, dk, dv)
+        assert all(t.stride(-1) == 1 and t.shape == q.shape for t in ts)
+        strides = (C.c_long * 24)(*[t.stride(i) for t in ts for i in range(3)])
+        N.check(lib.dsb_flash_attn_bwd2(N.ptr(dout), N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(out), N.ptr(lse),
+                                        N.ptr(scratch), N.ptr(dq), N.ptr(dk), N.ptr(dv), B, S, H, D, strides,
+                                        float(scale), int(causal), N.dtype_code(q.dtype), N.stream_ptr()),
+                "dsb_flash_attn_bwd2")
+        K._count(3)
+        return dq, dk, dv
     dq_acc = torch.zeros(B, S, H, D, dtype=torch.float32, device=q.device)
-    delta = torch.empty(2, B, H, S, dtype=torch.float32, device=q.device)   # -lse * log2 e | -scale * delta
+    delta = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
     ts = (dout, q, k, v, out, dk, dv)
     assert all(t.stride(-1) == 1 and t.shape == q.shape for t in ts)
     strides = (C.c_long * 21)(*[t.stride(i) for t in ts for i in range(3)])
-    N.check(N.cuda_lib().dsb_flash_attn_bwd(N.ptr(dout), N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(out), N.ptr(lse),
-                                            N.ptr(delta), N.ptr(dq_acc), N.ptr(dk), N.ptr(dv), B, S, H, D, strides,
-                                            float(scale), int(causal), N.dtype_code(q.dtype), N.stream_ptr()),
-            "dsb_flash_attn_bwd")
+    N.check(lib.dsb_flash_attn_bwd(N.ptr(dout), N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(out), N.ptr(lse), N.ptr(delta),
+                                   N.ptr(dq_acc), N.ptr(dk), N.ptr(dv), B, S, H, D, strides, float(scale), int(causal),
+                                   N.dtype_code(q.dtype), N.stream_ptr()), "dsb_flash_attn_bwd")
     K._count(2)
     return dq_acc, dk, dv
 
@@ -137,7 +155,7 @@ def rotary_oop(q_in, k_in, q_out, k_out, rot_dim, base, inverse=False, v_in=None
     K._count()
 
 
-_BACKEND = os.environ.get("DSB_ATTN", "sdpa").lower()
+_BACKEND = os.environ.get("DSB_ATTN", "native").lower()
 
 
 def set_attention_backend(name):
@@ -183,15 +201,17 @@ class NativeCausalSelfAttentionFn(torch.autograd.Function):
         dqkv = torch.empty(B, S, 3, H, D, dtype=qkv.dtype, device=qkv.device)
         if rot_dim > 0:
             dk_tmp = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
-            dq32, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dk_tmp,
-                                        dv=dqkv[:, :, 2])
-            dq = torch.empty_like(dk_tmp)
-            K.cast(dq32, dq)
+            dq, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dk_tmp, dv=dqkv[:, :, 2])
+            if dq.dtype != qkv.dtype:   # first-generation kernel: fp32 accumulator
+                dq16 = torch.empty_like(dk_tmp)
+                K.cast(dq, dq16)
+                dq = dq16
             rotary_oop(dq, dk_tmp, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
         else:
-            dq32, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dqkv[:, :, 1],
-                                        dv=dqkv[:, :, 2])
-            dqkv[:, :, 0].copy_(dq32)
+            dq, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dqkv[:, :, 1],
+                                      dv=dqkv[:, :, 2], dq=dqkv[:, :, 0])
+            if dq.dtype != qkv.dtype:
+                dqkv[:, :, 0].copy_(dq)
         return dqkv.view(B, S, 3 * H * D), None, None, None, None
 
 

@@ -103,8 +103,10 @@ int dsb_softmax_bwd(const void* dy, const void* y, void* dx, long rows, int k_le
 int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
                        long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss,
                        long v_sh, long o_sb, long o_ss, long o_sh, float scale, int causal, int dtype, void* stream);
-/* Forward block shape: 64 = 64-key blocks, two CTAs per SM (default); 128 = 128-key blocks, one CTA per SM. Returns
- * the previous setting; other values only query. */
+/* Forward kernel: 2 = two query tiles per CTA with P kept in tensor memory (default, needs S % 256 == 0, otherwise the
+ * 64-key kernel runs); 64 = 64-key blocks, two CTAs per SM; 128 = 128-key blocks, one CTA per SM. Returns the previous
+ * setting; other values only query. dsb_flash_attn_bwd_variant: 2 (default) / 1 selects which backward the Python
+ * wrapper calls (dsb_flash_attn_bwd2 / dsb_flash_attn_bwd). */
 int dsb_flash_attn_fwd_variant(int keys_per_step);
 int dsb_flash_attn_bwd_variant(int generation);
 /* Debug aid: when `p` is not NULL, CTA (0, 0) of the following attention launches adds its clock64 phase totals to
@@ -117,6 +119,15 @@ void dsb_flash_attn_debug_timers(long long* p);
 int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, const void* v, const void* out, const float* lse,
                        float* delta, float* dq_acc, void* dk, void* dv, int B, int S, int H, int D,
                        const long* strides, float scale, int causal, int dtype, void* stream);
+/* Second-generation backward (default): everything is computed transposed (lane = key row) so that P^T and dS^T stay
+ * in tensor memory as UMMA A operands; dq / dk / dv come back in the input dtype. `strides`: 8 x (sb, ss, sh) for dO, q,
+ * k, v, out, dq, dk, dv. `scratch`: (2 + 128) * B * H * S floats (cleared here; nothing is allocated).
+ * Reference: the backward chain of csrc/transformer/ds_transformer_cuda.cpp:340-420. */
+int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out, const float* lse,
+                        float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D, const long* strides,
+                        float scale, int causal, int dtype, void* stream);
+/* Experiment switches of the second-generation kernels (0 = production); see csrc/transformer/flash_attn_v2.cu. */
+void dsb_flash_attn_debug_mode(int mode);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */
 int dsb_bias_gelu_fwd(const void* x, const void* bias, void* y, long rows, int cols, int dtype, void* stream);
 int dsb_bias_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, long rows, int cols, int dtype,

@@ -517,11 +517,11 @@ def test_collective_gemm_variants_single_rank():
         assert ((dw.float() - ref).abs().max() / ref.abs().max()).item() < 3e-3
 
 
-@pytest.mark.parametrize("variant", [64, 128])
+@pytest.mark.parametrize("variant", [2, 64, 128])
 @pytest.mark.parametrize("causal", [True, False])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
 def test_flash_attention_forward(causal, dtype, variant):
-    """tcgen05 flash-attention forward (both block shapes) vs fp32 softmax(QK^T)V, on strided views of a fused QKV
+    """tcgen05 flash-attention forward (all three kernels) vs fp32 softmax(QK^T)V, on strided views of a fused QKV
     buffer."""
     from deeperspeed_b200.ops.attention import flash_attn_fwd, set_flash_fwd_variant
     prev = set_flash_fwd_variant(variant)
@@ -531,9 +531,9 @@ def test_flash_attention_forward(causal, dtype, variant):
         set_flash_fwd_variant(prev)
 
 
-def _check_flash_forward(causal, dtype, flash_attn_fwd):
+def _check_flash_forward(causal, dtype, flash_attn_fwd, B=2, S=768, H=3):
     torch.manual_seed(0)
-    B, S, H, D = 2, 640, 3, 128
+    D = 128
     qkv = torch.randn(B, S, 3, H, D, device="cuda", dtype=dtype)
     q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
     out, lse = flash_attn_fwd(q, k, v, causal=causal, return_lse=True)
@@ -549,13 +549,35 @@ def _check_flash_forward(causal, dtype, flash_attn_fwd):
     assert (lse - torch.logsumexp(scores, -1)).abs().max().item() < 2e-3
 
 
+@pytest.mark.parametrize("S", [2048, 8192])
+def test_flash_attention_long_sequences(S):
+    """The sequence lengths the benchmarks run (several waves of CTAs per head, 32 / 128 key blocks per row block)."""
+    from deeperspeed_b200.ops.attention import flash_attn_fwd
+    _check_flash_forward(True, torch.float16, flash_attn_fwd, B=1, S=S, H=2)
+
+
+def test_flash_attention_forward_odd_block_count_falls_back():
+    """S % 256 == 128: the two-tile kernel does not apply, the 64-key kernel runs instead."""
+    from deeperspeed_b200.ops.attention import flash_attn_fwd
+    _check_flash_forward(True, torch.float16, flash_attn_fwd, B=1, S=640, H=2)
+
+
+@pytest.mark.parametrize("gen,S", [(2, 512), (2, 2048), (1, 512)])
 @pytest.mark.parametrize("causal", [True, False])
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-def test_flash_attention_backward(causal, dtype):
-    """tcgen05 flash-attention backward vs autograd through fp32 softmax(QK^T)V."""
-    from deeperspeed_b200.ops.attention import flash_attn_fwd, flash_attn_bwd
+def test_flash_attention_backward(causal, dtype, gen, S):
+    """tcgen05 flash-attention backward (both generations) vs autograd through fp32 softmax(QK^T)V."""
+    from deeperspeed_b200.ops.attention import flash_attn_fwd, flash_attn_bwd, set_flash_bwd_variant
+    prev = set_flash_bwd_variant(gen)
+    try:
+        _check_flash_backward(causal, dtype, S, flash_attn_fwd, flash_attn_bwd)
+    finally:
+        set_flash_bwd_variant(prev)
+
+
+def _check_flash_backward(causal, dtype, S, flash_attn_fwd, flash_attn_bwd):
     torch.manual_seed(1)
-    B, S, H, D = 2, 512, 3, 128
+    B, H, D = (2, 3, 128) if S <= 512 else (1, 2, 128)
     qkv = torch.randn(B, S, 3, H, D, device="cuda", dtype=dtype)
     q, k, v = qkv[:, :, 0], qkv[:, :, 1], qkv[:, :, 2]
     out, lse = flash_attn_fwd(q, k, v, causal=causal, return_lse=True)
@@ -571,7 +593,7 @@ def test_flash_attention_backward(causal, dtype):
     rq, rk, rv = torch.autograd.grad(ref, (qf, kf, vf), dout.float())
     tol = 2e-2 if dtype == torch.float16 else 8e-2
     for name, got, want in (("dq", dq, rq), ("dk", dk.float(), rk), ("dv", dv.float(), rv)):
-        err = (got - want).abs().max().item()
+        err = (got.float() - want).abs().max().item()
         assert err < tol * max(1.0, want.abs().max().item()), (name, err, want.abs().max().item())
 
 
