@@ -87,6 +87,15 @@ def _attention_backend():
         return "unknown"
 
 
+def _zero_backend(engine):
+    opt = getattr(engine, "optimizer", None)
+    fused = getattr(opt, "_fused", None) or getattr(opt, "fused", None)
+    if fused is not None:
+        return "fused NVLink kernels (fused_rs_norm + fused_adam_ag, ours)"
+    return "NCCL reduce_scatter / all_gather + fused Adam kernel" if getattr(engine, "dp_world_size", 1) > 1 else \
+        "single rank: fused Adam kernel, no collective"
+
+
 def ds_config(n_gpus, pp, dp):
     gas = MICRO_BATCHES_PER_STAGE * pp
     return {
@@ -180,6 +189,9 @@ def run_ours(args):
     torch.manual_seed(1234)
     model = GPTNeoXPipe(cfg, topology=PipeDataParallelTopology(num_pp=pp, num_dp=dp))
     conf = ds_config(n, pp, dp)
+    if pp > 1 and args.edge_split > 1:
+        # our engine's bubble trimming: the first and last micro-batch are fed as slices (same samples, same gradient)
+        conf["pipeline"] = {"edge_split": args.edge_split}
     engine, _, _, _ = deepspeed.initialize(model=model, model_parameters=[p for p in model.parameters() if p.requires_grad],
                                            config_params=conf)
     device = engine.device
@@ -263,7 +275,9 @@ def run_ours(args):
                        "layers": cfg.num_layers, "global_batch": conf["train_batch_size"], "seq_len": SEQ,
                        "micro_batch": MICRO_BATCH, "grad_accum": conf["gradient_accumulation_steps"],
                        "parallelism": f"pp{pp}xdp{dp} zero1", "l2": "working set per step >> 126 MB L2 (no flush needed)",
-                       "params": cfg.num_params(), "attention_backend": _attention_backend()},
+                       "params": cfg.num_params(), "attention_backend": _attention_backend(),
+                       "pipeline_edge_split": getattr(engine, "edge_split", 1),
+                       "zero_step_backend": _zero_backend(engine)},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": float(h2d.item()) / args.steps,
                     "d2h_bytes_per_step": loss_bytes / args.steps, "ms_per_step": ms_e2e / args.steps,
@@ -296,6 +310,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--tiny", action="store_true", help="tiny model (CPU plumbing check only; not a valid bench)")
     ap.add_argument("--layers", type=int, default=0, help="debug override (invalidates the number)")
+    ap.add_argument("--edge-split", dest="edge_split", type=int, default=2,
+                    help="slices of the first / last micro-batch under pipeline parallelism (1 = plain 1F1B)")
     ap.add_argument("--local_rank", type=int, default=0)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -1,194 +1,192 @@
-"""Cartesian process topology and the pipeline/data/model process-group grid (the `mpu` interface).
-Behaviour per reference deepspeed/runtime/pipe/topology.py:13-468; rank maths is plain row-major arithmetic here
-instead of an enumerated namedtuple->rank dictionary."""
+"""Cartesian process topology and the pipeline / data / model process-group grid (the `mpu` interface).
+
+Public behaviour per reference deepspeed/runtime/pipe/topology.py:13-468 (axis names, rank order, group membership,
+the Megatron-style accessors). Mechanism: a topology is a mixed-radix number system. Axis k has stride
+prod(dims[k+1:]), a coordinate is the digit vector of the rank, and every query (rank of a coordinate, the ranks of an
+axis group, a filtered slice) is stride arithmetic; nothing is enumerated up front.
+"""
 from collections import namedtuple
-from itertools import product as cartesian_product
+from itertools import product
 
 import torch.distributed as dist
 
-from ...utils.logging import logger
-
 
 class ProcessTopology:
-    """Maps n-dimensional cartesian coordinates to linear ranks (row-major: last axis varies fastest)."""
+    """n-dimensional cartesian coordinates <-> linear ranks, row-major (the last axis varies fastest)."""
 
     def __init__(self, axes, dims):
         self.axes = list(axes)
         self.dims = list(dims)
         self.ProcessCoord = namedtuple("ProcessCoord", axes)
-        self.mapping = {}
-        for global_rank, coord in enumerate(cartesian_product(*[range(d) for d in dims])):
-            self.mapping[self.ProcessCoord(**dict(zip(axes, coord)))] = global_rank
+        self._strides = [1] * len(self.dims)
+        for k in range(len(self.dims) - 2, -1, -1):
+            self._strides[k] = self._strides[k + 1] * self.dims[k + 1]
+        self._size = self._strides[0] * self.dims[0] if self.dims else 1
+
+    # ---- digits <-> rank
+    def _digits(self, rank):
+        return [(rank // s) % d for s, d in zip(self._strides, self.dims)]
+
+    def _rank_of(self, digits):
+        return sum(x * s for x, s in zip(digits, self._strides))
+
+    def _axis(self, axis):
+        return self.axes.index(axis)
+
+    @property
+    def mapping(self):
+        """{coordinate: rank} for every rank (built on demand; kept because callers print and iterate it)."""
+        return {self.get_coord(r): r for r in range(self._size)}
 
     def get_rank(self, **coord_kwargs):
         if len(coord_kwargs) != len(self.axes):
             raise ValueError("get_rank() does not support slices. Use filter_match())")
-        key = self.ProcessCoord(**coord_kwargs)
-        assert key in self.mapping, f"key {coord_kwargs} invalid"
-        return self.mapping[key]
+        digits = []
+        for axis, dim in zip(self.axes, self.dims):
+            assert axis in coord_kwargs and 0 <= coord_kwargs[axis] < dim, f"key {coord_kwargs} invalid"
+            digits.append(coord_kwargs[axis])
+        return self._rank_of(digits)
 
     def get_axis_names(self):
         return self.axes
 
     def get_rank_repr(self, rank, omit_axes=("data", "pipe"), inner_sep="_", outer_sep="-"):
-        omit_axes = frozenset(omit_axes)
-        axes = [a for a in self.get_axis_names() if a not in omit_axes]
-        names = []
-        for ax in axes:
-            ax_rank = getattr(self.get_coord(rank=rank), ax)
-            names.append(f"{ax}{inner_sep}{ax_rank:02d}")
-        return outer_sep.join(names)
+        """e.g. 'model_00' (checkpoint file names are derived from this)."""
+        digits = self._digits(rank)
+        skip = frozenset(omit_axes)
+        return outer_sep.join(f"{a}{inner_sep}{x:02d}" for a, x in zip(self.axes, digits) if a not in skip)
 
     def get_dim(self, axis):
-        if axis not in self.axes:
-            return 0
-        return self.dims[self.axes.index(axis)]
+        return self.dims[self._axis(axis)] if axis in self.axes else 0
 
     def get_coord(self, rank):
-        for coord, idx in self.mapping.items():
-            if idx == rank:
-                return coord
-        raise ValueError(f"rank {rank} not found in topology.")
+        if not 0 <= rank < self._size:
+            raise ValueError(f"rank {rank} not found in topology.")
+        return self.ProcessCoord(*self._digits(rank))
 
     def get_axis_comm_lists(self, axis):
-        """Lists of ranks that differ only along `axis` (the communicator groups of that axis)."""
+        """Groups of ranks that differ only along `axis`, ordered by their first member."""
         if axis not in self.axes:
             return []
-        other_axes = [a for a in self.axes if a != axis]
-        lists = []
-        for coord in cartesian_product(*[range(self.get_dim(a)) for a in other_axes]):
-            other_keys = dict(zip(other_axes, coord))
-            lists.append([self.mapping[self.ProcessCoord(**other_keys, **{axis: i})]
-                          for i in range(self.get_dim(axis))])
-        return lists
+        k = self._axis(axis)
+        stride, dim = self._strides[k], self.dims[k]
+        firsts = [r for r in range(self._size) if (r // stride) % dim == 0]
+        return [[first + i * stride for i in range(dim)] for first in firsts]
 
     def filter_match(self, **filter_kwargs):
-        def _match(coord):
-            return all(getattr(coord, k) == v for k, v in filter_kwargs.items())
-
-        return [self.mapping[c] for c in filter(_match, self.mapping.keys())]
+        """All ranks whose coordinates agree with the given axis values."""
+        fixed = {self._axis(a): v for a, v in filter_kwargs.items()}
+        free = [range(d) if k not in fixed else (fixed[k],) for k, d in enumerate(self.dims)]
+        return [self._rank_of(digits) for digits in product(*free)]
 
     def get_axis_list(self, axis, idx):
-        axis_num = self.axes.index(axis)
-        return [self.mapping[k] for k in self.mapping.keys() if k[axis_num] == idx]
+        return self.filter_match(**{axis: idx})
 
     def world_size(self):
-        return len(self.mapping)
+        return self._size
 
     def __str__(self):
         return str(self.mapping)
 
 
 def _prime_factors(N):
+    """Prime factors of N in non-decreasing order."""
     if N <= 0:
         raise ValueError("Values must be strictly positive.")
-    primes = []
-    while N != 1:
-        for candidate in range(2, N + 1):
-            if N % candidate == 0:
-                primes.append(candidate)
-                N //= candidate
-                break
-    return primes
+    out, p = [], 2
+    while N > 1:
+        if N % p == 0:
+            out.append(p)
+            N //= p
+        else:
+            p += 1
+    return out
 
 
 class PipeDataParallelTopology(ProcessTopology):
-    """pipe x data: DP ranks of a stage are adjacent (gradient reductions stay on neighbouring GPUs)."""
+    """pipe x data: the data-parallel replicas of a stage have adjacent ranks, so gradient reductions stay among
+    neighbouring GPUs while only activations cross between stages."""
 
     def __init__(self, num_pp, num_dp):
         super().__init__(axes=["pipe", "data"], dims=[num_pp, num_dp])
 
 
 class PipeModelDataParallelTopology(ProcessTopology):
-    """3-D pipe x data x model."""
+    """3-D pipe x data x model (tensor-parallel ranks innermost)."""
 
     def __init__(self, num_pp, num_mp, num_dp):
         super().__init__(axes=["pipe", "data", "model"], dims=[num_pp, num_dp, num_mp])
 
 
 class PipelineParallelGrid:
-    """Builds every process group a pipeline engine needs and implements the Megatron-style `mpu` interface.
+    """Every process group a pipeline engine needs, plus the Megatron-style `mpu` accessors.
 
-    Groups: data-parallel (same pipe/model coords), pipe (same data/model), "ds model" (= all ranks sharing my data
-    coordinate; checkpoint mp_rank is the index inside it), slice (tensor-parallel) and 2-rank p2p neighbours."""
+    Groups: data-parallel (same pipe / model coordinates), pipe (same data / model), "ds model" (all ranks that share
+    my data coordinate; the checkpoint's mp_rank is my index in it) and slice (tensor-parallel). `p2p_groups` lists
+    every rank with its next-stage neighbour (wrapping around); the communicators for those pairs are created by
+    runtime/pipe/p2p.py, one per direction."""
 
     def __init__(self, topology=None, process_group=None):
         self.global_rank = dist.get_rank()
         self.world_size = dist.get_world_size()
-        if topology is not None:
-            self._topo = topology
-        else:
-            num_pp, num_dp = 1, 1
-            for idx, prime in enumerate(_prime_factors(self.world_size)):
-                if idx % 2 == 0:
-                    num_pp *= prime
-                else:
-                    num_dp *= prime
-            self._topo = PipeDataParallelTopology(num_dp=num_dp, num_pp=num_pp)
-        self.data_parallel_size = max(self._topo.get_dim("data"), 1)
-        self.pipe_parallel_size = max(self._topo.get_dim("pipe"), 1)
-        self.model_parallel_size = max(self._topo.get_dim("model"), 1)
+        self._topo = topology if topology is not None else self._default_topology(self.world_size)
+        topo = self._topo
+        self.data_parallel_size = max(topo.get_dim("data"), 1)
+        self.pipe_parallel_size = max(topo.get_dim("pipe"), 1)
+        self.model_parallel_size = max(topo.get_dim("model"), 1)
         self.slice_parallel_size = self.model_parallel_size
         assert self._is_grid_valid(), "Invalid Grid"
 
-        self.stage_id = self.get_stage_id()
-        self.data_parallel_id = self.get_data_parallel_id()
-
-        # "ds model" groups: everything except the data axis
-        self.ds_model_proc_group = None
-        self.ds_model_rank = -1
-        for dp in range(self.data_parallel_size):
-            ranks = sorted(self._topo.get_axis_list(axis="data", idx=dp))
-            proc_group = dist.new_group(ranks=ranks)
-            if self.global_rank in ranks:
-                self.ds_model_proc_group = proc_group
-                self.ds_model_world_size = len(ranks)
-                self.ds_model_rank = ranks.index(self.global_rank)
-        assert self.ds_model_rank > -1 and self.ds_model_proc_group is not None
-
-        self.dp_group = []
-        self.dp_groups = self._topo.get_axis_comm_lists("data")
-        for g in self.dp_groups:
-            proc_group = dist.new_group(ranks=g)
-            if self.global_rank in g:
-                self.dp_group = g
-                self.dp_proc_group = proc_group
-
+        me = topo.get_coord(self.global_rank)
+        self.stage_id = me.pipe
+        self.data_parallel_id = me.data
         self.is_first_stage = self.stage_id == 0
-        self.is_last_stage = self.stage_id == (self.pipe_parallel_size - 1)
+        self.is_last_stage = self.stage_id == self.pipe_parallel_size - 1
+
+        # group creation is collective: every rank walks the same lists in the same order
+        ds_model_lists = [sorted(topo.get_axis_list("data", dp)) for dp in range(self.data_parallel_size)]
+        ranks, self.ds_model_proc_group = self._join(ds_model_lists)
+        self.ds_model_world_size = len(ranks)
+        self.ds_model_rank = ranks.index(self.global_rank)
+
+        self.dp_groups = topo.get_axis_comm_lists("data")
+        self.dp_group, self.dp_proc_group = self._join(self.dp_groups)
 
         self.p2p_groups = self._build_p2p_groups()
 
-        self.pp_group = []
-        self.pp_proc_group = None
-        self.pipe_groups = self._topo.get_axis_comm_lists("pipe")
-        for ranks in self.pipe_groups:
-            proc_group = dist.new_group(ranks=ranks)
-            if self.global_rank in ranks:
-                self.pp_group = ranks
-                self.pp_proc_group = proc_group
-        assert self.pp_proc_group is not None
+        self.pipe_groups = topo.get_axis_comm_lists("pipe")
+        self.pp_group, self.pp_proc_group = self._join(self.pipe_groups)
 
-        # slice (tensor-parallel) groups
-        self.slice_group = None
-        self.slice_proc_group = None
-        if "model" in self._topo.get_axis_names():
-            self.mp_group = []
-            self.model_groups = self._topo.get_axis_comm_lists("model")
-            for g in self.model_groups:
-                proc_group = dist.new_group(ranks=g)
-                if self.global_rank in g:
-                    self.slice_group = g
-                    self.slice_proc_group = proc_group
+        if "model" in topo.get_axis_names():
+            self.model_groups = topo.get_axis_comm_lists("model")
         else:
-            self.slice_group = [self.global_rank]
-            self.slice_proc_group = dist.new_group(ranks=[self.global_rank]) if self.world_size > 1 else None
             self.model_groups = [[r] for r in range(self.world_size)]
-            if self.world_size > 1:
-                # every rank must take part in every new_group call
-                for r in range(self.world_size):
-                    if r != self.global_rank:
-                        dist.new_group(ranks=[r])
+        self.mp_group = []
+        if self.world_size > 1 or "model" in topo.get_axis_names():
+            self.slice_group, self.slice_proc_group = self._join(self.model_groups)
+        else:
+            self.slice_group, self.slice_proc_group = [self.global_rank], None
+
+    @staticmethod
+    def _default_topology(world_size):
+        """No topology given: deal the prime factors of the world size alternately to the pipe and data axes."""
+        num_pp = num_dp = 1
+        for i, prime in enumerate(_prime_factors(world_size)):
+            if i % 2 == 0:
+                num_pp *= prime
+            else:
+                num_dp *= prime
+        return PipeDataParallelTopology(num_dp=num_dp, num_pp=num_pp)
+
+    def _join(self, rank_lists):
+        """Create one process group per list; return (ranks, group) of the list this rank belongs to."""
+        mine = (None, None)
+        for ranks in rank_lists:
+            group = dist.new_group(ranks=ranks)
+            if self.global_rank in ranks:
+                mine = (ranks, group)
+        assert mine[0] is not None
+        return mine
 
     def get_stage_id(self):
         return self._topo.get_coord(rank=self.global_rank).pipe
@@ -197,30 +195,25 @@ class PipelineParallelGrid:
         return self._topo.get_coord(rank=self.global_rank).data
 
     def _build_p2p_groups(self):
-        """[rank, next-stage rank] pairs, including the wrap-around from the last stage to the first."""
-        comm_lists = self._topo.get_axis_comm_lists("pipe")
-        p2p_lists = []
+        """[rank, next-stage rank] for every rank, the last stage wrapping around to the first."""
+        topo = self._topo
+        if "pipe" not in topo.get_axis_names():
+            return [[r, r] for r in range(self.world_size)]
+        k = topo._axis("pipe")
+        stride, dim = topo._strides[k], topo.dims[k]
+        pairs = []
         for rank in range(self.world_size):
-            for l in comm_lists:
-                assert len(l) == self.pipe_parallel_size
-                if rank in l:
-                    idx = l.index(rank)
-                    buddy_rank = l[(idx + 1) % self.pipe_parallel_size]
-                    p2p_lists.append([rank, buddy_rank])
-                    break
-        assert len(p2p_lists) == self.world_size
-        return p2p_lists
+            stage = (rank // stride) % dim
+            pairs.append([rank, rank + (((stage + 1) % dim) - stage) * stride])
+        return pairs
 
     def _is_grid_valid(self):
-        ranks = 1
-        for ax in self._topo.get_axis_names():
-            ranks *= self._topo.get_dim(ax)
-        return ranks == dist.get_world_size()
+        return self._topo.world_size() == dist.get_world_size()
 
     def stage_to_global(self, stage_id, **kwargs):
-        me = self._topo.get_coord(self.global_rank)
-        transform = me._replace(pipe=stage_id, **kwargs)._asdict()
-        return self._topo.get_rank(**transform)
+        """Global rank of the process with my coordinates except pipe = stage_id (and any overrides in kwargs)."""
+        coord = self._topo.get_coord(self.global_rank)._replace(pipe=stage_id, **kwargs)
+        return self._topo.get_rank(**coord._asdict())
 
     def topology(self):
         return self._topo
@@ -260,9 +253,7 @@ class PipelineParallelGrid:
         return self.ds_model_proc_group
 
     def get_slice_parallel_rank(self):
-        if "model" in self._topo.get_axis_names():
-            return self._topo.get_coord(rank=self.global_rank).model
-        return 0
+        return getattr(self._topo.get_coord(self.global_rank), "model", 0)
 
     def get_slice_parallel_world_size(self):
         return self.slice_parallel_size

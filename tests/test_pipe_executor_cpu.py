@@ -1,0 +1,92 @@
+"""The pipeline executor's own pieces: plan compilation, edge-split slot layout and its numerical equivalence with the
+plain schedule (gloo, 2 and 3 stages)."""
+import pytest
+import torch
+import torch.distributed as dist
+
+import deeperspeed_b200 as deepspeed
+from deeperspeed_b200.runtime.pipe import schedule
+from deeperspeed_b200.runtime.pipe.executor import compile_plan, slot_rows, SlotFeed
+from deeperspeed_b200.runtime.pipe.topology import PipeDataParallelTopology, ProcessTopology
+
+from common import distributed_test
+from simple_model import LinearStackPipe, args_from_dict, random_dataset
+
+HID = 16
+
+
+def test_compile_plan_folds_each_tick():
+    plan = compile_plan(schedule.TrainSchedule(micro_batches=4, stages=2, stage_id=0))
+    assert len(plan) == 2 * (4 + 2 - 1)
+    assert plan[0].load == 0 and plan[0].compute == ("fwd", 0) and not plan[0].recvs and not plan[0].sends
+    # tick 3 of stage 0: activation of micro-batch 1 goes down while the gradient of micro-batch 0 comes up
+    assert plan[3].sends == (("act", 1),) and plan[3].recvs == (("grad", 0),) and plan[3].compute == ("bwd", 0)
+    assert plan[-1].tail == ("reduce_tied", "reduce", "step")
+    last = compile_plan(schedule.TrainSchedule(micro_batches=4, stages=2, stage_id=1))
+    assert last[1].recvs == (("act", 0),) and last[1].load == 0 and last[1].compute == ("fwd", 0)
+    # every send of a tick has its receive in the same tick of the neighbour
+    for a, b in zip(plan, last):
+        assert [k for k, _ in a.sends if k == "act"] == [k for k, _ in b.recvs if k == "act"]
+        assert [k for k, _ in b.sends if k == "grad"] == [k for k, _ in a.recvs if k == "grad"]
+
+
+def test_compile_plan_rejects_unknown_instruction():
+    class Bogus(schedule.PipeInstruction):
+        pass
+
+    with pytest.raises(RuntimeError):
+        compile_plan([[Bogus()]])
+
+
+def test_slot_rows_and_feed():
+    assert slot_rows(4, 4, 1) == [4, 4, 4, 4]
+    assert slot_rows(4, 4, 2) == [2, 2, 4, 4, 2, 2]
+    assert slot_rows(1, 4, 2) == [4]                 # a single micro-batch is not split
+    assert slot_rows(4, 3, 2) == [3, 3, 3, 3]        # rows not divisible
+    rows = slot_rows(3, 4, 2)
+    feed = SlotFeed(rows, 4)
+    batches = iter([(torch.arange(4) + 10 * i, torch.arange(4) - 10 * i) for i in range(3)])
+    got = [feed.next(lambda: next(batches)) for _ in rows]
+    assert [g[0].tolist() for g in got] == [[0, 1], [2, 3], [10, 11, 12, 13], [20, 21], [22, 23]]
+    assert got[3][1].tolist() == [-20, -19]
+
+
+def test_topology_is_stride_arithmetic():
+    topo = ProcessTopology(axes=["pipe", "data", "model"], dims=[2, 3, 2])
+    assert topo.world_size() == 12 and topo.get_rank(pipe=1, data=2, model=1) == 11
+    assert topo.get_coord(7) == topo.ProcessCoord(pipe=1, data=0, model=1)
+    assert topo.get_axis_comm_lists("data") == [[0, 2, 4], [1, 3, 5], [6, 8, 10], [7, 9, 11]]
+    assert topo.get_axis_comm_lists("model")[0] == [0, 1] and topo.get_axis_comm_lists("nope") == []
+    assert topo.filter_match(pipe=0, model=1) == [1, 3, 5] and topo.get_axis_list("pipe", 1) == list(range(6, 12))
+    assert topo.get_rank_repr(rank=3) == "model_01" and topo.mapping[topo.ProcessCoord(0, 1, 1)] == 3
+    with pytest.raises(ValueError):
+        topo.get_rank(pipe=0)
+
+
+def _train_losses(tmp_path, stages, edge_split, steps=3):
+    cfg = {"train_batch_size": 16, "train_micro_batch_size_per_gpu": 4, "steps_per_print": 100,
+           "optimizer": {"type": "Adam", "params": {"lr": 0.01}}, "fp16": {"enabled": True, "type": "fp32"},
+           "zero_optimization": {"stage": 1}, "pipeline": {"edge_split": edge_split}}
+    torch.manual_seed(3)
+    pipe = LinearStackPipe(HID, HID, HID, 4, topology=PipeDataParallelTopology(num_pp=stages, num_dp=1),
+                           partition_method="uniform")
+    engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=pipe,
+                                           model_parameters=[p for p in pipe.parameters()])
+    assert engine.edge_split == edge_split
+    it = iter(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(random_dataset(64, HID, seed=11), batch_size=4)))
+    losses = [float(engine.train_batch(it)) for _ in range(steps)]
+    return losses, [p.detach().clone() for p in pipe.parameters()]
+
+
+@pytest.mark.parametrize("stages", [2, 3])
+def test_edge_split_matches_plain_schedule(stages, tmp_path):
+    """Feeding the first and last micro-batch as two half-size slices changes the bubble, not the mathematics."""
+    @distributed_test(world_size=stages)
+    def run():
+        plain, w0 = _train_losses(tmp_path, stages, 1)
+        split, w1 = _train_losses(tmp_path, stages, 2)
+        for a, b in zip(plain, split):
+            assert abs(a - b) < 1e-5, (plain, split)
+        for a, b in zip(w0, w1):
+            assert torch.allclose(a, b, atol=1e-5)
+    run()
