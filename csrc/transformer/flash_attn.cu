@@ -1135,15 +1135,20 @@ extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, 
 // dq / dk / dv are written in the input dtype. `strides`: 8 x (sb, ss, sh) for dO, q, k, v, out, dq, dk, dv.
 // `scratch`: fp32, (2 + 128) * B * H * S elements: -lse * log2 e, -scale * rowsum(dO * O) and the TRANSPOSED fp32 dQ
 // accumulator [B, H, 128, S]; it is cleared here (stream-ordered memset), nothing is allocated.
+// rot_dim > 0 (multiple of 16, tables [S, rot_dim / 2] fp32 from dsb_rotary_table): q and k were rotated before the
+// forward pass, and dq / dk come back as gradients of the UNROTATED tensors (the inverse rotation is applied in the dK
+// epilogue and in the dQ finishing pass, so no separate rotary launch is needed in backward).
 extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out,
                                    const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H,
-                                   int D, const long* strides, float scale, int causal, int dtype, void* stream_) {
+                                   int D, const long* strides, float scale, int causal, int dtype,
+                                   const float* rot_cos, const float* rot_sin, int rot_dim, void* stream_) {
     using namespace dsb;
     using namespace dsb::fa;
     ensure_context_on_this_thread();
     if (B <= 0 || S <= 0 || H <= 0) return 0;
     if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
     if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
+    if (rot_dim > 0 && (rot_cos == nullptr || rot_sin == nullptr)) return DSB_ERR_ARG;
     for (int i = 0; i < 24; ++i)
         if (strides[i] % 8) return DSB_ERR_ALIGN;
     const int bf = dtype == DSB_DTYPE_BF16;
@@ -1175,7 +1180,7 @@ extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return -(int)r - 1000;
     rc = fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale, scale * 1.4426950408889634f, causal,
-                         bf, stream);
+                         bf, rot_cos, rot_sin, rot_dim, stream);
     if (rc) return rc;
-    return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, stream);
+    return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, rot_cos, rot_sin, rot_dim, stream);
 }

@@ -582,7 +582,9 @@ __global__ void __launch_bounds__(256) flash_prep_kernel(const T* __restrict__ d
 // One block per (32 queries, batch * head): coalesced 128-byte reads along s, padded shared tile, 256-byte row writes.
 template <typename T>
 __global__ void __launch_bounds__(256) flash_dq_finish_kernel(const float* __restrict__ acc, T* __restrict__ dq, int S,
-                                                              int H, long sb, long ss, long sh) {
+                                                              int H, long sb, long ss, long sh,
+                                                              const float* __restrict__ rot_cs,
+                                                              const float* __restrict__ rot_sn, int rot) {
     __shared__ float tile[128][33];
     const int s0 = blockIdx.x * 32;
     const int bh = blockIdx.y;
@@ -593,12 +595,25 @@ __global__ void __launch_bounds__(256) flash_dq_finish_kernel(const float* __res
     for (int i = 0; i < 16; ++i) tile[w * 16 + i][lane] = src[(long)(w * 16 + i) * S];
     __syncthreads();
     T* dst = dq + b * sb + h * sh;
+    const int hr = rot >> 1;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int s = w * 4 + i;
+        float v[4];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const int d = lane * 4 + t;
+            float x = tile[d][s];
+            if (d < rot) {   // inverse rotary: the accumulator holds the gradient of the rotated queries
+                const int j = d < hr ? d : d - hr;
+                const float c = rot_cs[(long)(s0 + s) * hr + j], sg = rot_sn[(long)(s0 + s) * hr + j];
+                x = d < hr ? x * c + tile[d + hr][s] * sg : x * c - tile[d - hr][s] * sg;
+            }
+            v[t] = x;
+        }
         uint2 o;
-        o.x = Cvt<T>::pack2(tile[lane * 4][s], tile[lane * 4 + 1][s]);
-        o.y = Cvt<T>::pack2(tile[lane * 4 + 2][s], tile[lane * 4 + 3][s]);
+        o.x = Cvt<T>::pack2(v[0], v[1]);
+        o.y = Cvt<T>::pack2(v[2], v[3]);
         *reinterpret_cast<uint2*>(dst + (long)(s0 + s) * ss + lane * 4) = o;
     }
 }
@@ -622,7 +637,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const __grid_constant__ CUtensorMap tmdK, const __grid_constant__ CUtensorMap tmdV,
                   const __grid_constant__ CUtensorMap tmDQ, const float* __restrict__ nlse2,
                   const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal, int dbg,
-                  long long* prof) {
+                  long long* prof, const float* __restrict__ rot_cs, const float* __restrict__ rot_sn, int rot) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + B_OFF_K;
@@ -921,6 +936,32 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                         Cvt<T>::pack2(__uint_as_float(r[u * 8 + 6]), __uint_as_float(r[u * 8 + 7])));
             }
         }
+        if (rot > 0) {
+            // dK is the gradient of the ROTATED keys: turn it back (inverse rotary, transpose of the forward rotation)
+            // in the staged tile. Pairs (j, j + rot / 2) of a row may sit in different 64-column chunks, hence the
+            // barrier; every thread then rotates whole 8-element units of its own row.
+            named_bar_sync(1, 256);
+            const int hr = rot >> 1;
+            const float* cs = rot_cs + (long)(jb * 128 + row) * hr;
+            const float* sn = rot_sn + (long)(jb * 128 + row) * hr;
+            uint8_t* rowp = sV + row * 128;
+            for (int j = half * 8; j < hr; j += 16) {
+                const int d1 = j + hr;
+                uint4* p0 = reinterpret_cast<uint4*>(rowp + (j >> 6) * 16384 + ((((j & 63) >> 3) ^ sw) << 4));
+                uint4* p1 = reinterpret_cast<uint4*>(rowp + (d1 >> 6) * 16384 + ((((d1 & 63) >> 3) ^ sw) << 4));
+                float x0[8], x1[8], y0[8], y1[8];
+                unpack8<T>(*p0, x0);
+                unpack8<T>(*p1, x1);
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    const float c = cs[j + t], sg = sn[j + t];
+                    y0[t] = x0[t] * c + x1[t] * sg;
+                    y1[t] = x1[t] * c - x0[t] * sg;
+                }
+                *p0 = pack8<T>(y0);
+                *p1 = pack8<T>(y1);
+            }
+        }
         fence_proxy_async_smem();
         named_bar_sync(1, 256);
         if (warp == 4 && lane == 0) {
@@ -1032,13 +1073,15 @@ int launch_prep(const void* dO, const void* O, const float* lse, float* nlse2, f
     return e == cudaSuccess ? 0 : -(int)e;
 }
 
-int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, cudaStream_t stream) {
+int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, const float* rot_cs,
+                     const float* rot_sn, int rot, cudaStream_t stream) {
     dim3 grid(S / 32, B * H);
     if (bf16)
         flash_dq_finish_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(acc, (__nv_bfloat16*)dq, S, H, s_dq[0], s_dq[1],
-                                                                        s_dq[2]);
+                                                                        s_dq[2], rot_cs, rot_sn, rot);
     else
-        flash_dq_finish_kernel<__half><<<grid, 256, 0, stream>>>(acc, (__half*)dq, S, H, s_dq[0], s_dq[1], s_dq[2]);
+        flash_dq_finish_kernel<__half><<<grid, 256, 0, stream>>>(acc, (__half*)dq, S, H, s_dq[0], s_dq[1], s_dq[2],
+                                                                 rot_cs, rot_sn, rot);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
 }
@@ -1046,8 +1089,9 @@ int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long
 int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* nlse2,
                const float* ndelta, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
-               cudaStream_t stream) {
+               const float* rot_cs, const float* rot_sn, int rot, cudaStream_t stream) {
     if (S % 128) return DSB_ERR_SIZE;
+    if (rot < 0 || rot > 128 || (rot % 16)) return DSB_ERR_ARG;
     dim3 grid(B * H, S / 128);
     cudaError_t e;
     if (bf16) {
@@ -1055,13 +1099,13 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot);
     } else {
         auto kern = flash_bwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

@@ -20,10 +20,12 @@ int launch_prep(const void* dO, const void* O, const float* lse, float* lse2, fl
 int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* lse2,
                const float* delta_s, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
-               cudaStream_t stream);
+               const float* rot_cs, const float* rot_sn, int rot, cudaStream_t stream);
 
 // dq (16 bit, [B, S, H, 128] with strides s_dq) = transpose of the fp32 accumulator [B, H, 128, S].
-int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, cudaStream_t stream);
+// rot > 0: apply the inverse rotary embedding (tables [S, rot / 2] fp32) on the way, likewise for dK in launch_bwd.
+int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, const float* rot_cs,
+                     const float* rot_sn, int rot, cudaStream_t stream);
 
 void set_debug_mode(int m);
 void set_debug_timers(long long* p);   // 32 int64: phase totals of forward CTA (0, 0)

@@ -44,6 +44,7 @@ class NeoXConfig:
 
 
 class EmbeddingPipe(nn.Module):
+    pipe_compute_weight = 0      # a row gather: no GEMM work when stages are balanced by compute
     def __init__(self, cfg):
         super().__init__()
         self.word_embeddings = nn.Embedding(cfg.vocab_size, cfg.hidden_size)
@@ -137,7 +138,7 @@ def neox_layer_specs(cfg):
 
 class GPTNeoXPipe(PipelineModule):
     def __init__(self, cfg, num_stages=1, topology=None, activation_checkpoint_interval=0,
-                 partition_method="type:ParallelTransformerLayerPipe", **kwargs):
+                 partition_method="compute", **kwargs):
         self.neox_config = cfg
         super().__init__(layers=neox_layer_specs(cfg), num_stages=num_stages if topology is None else None,
                          topology=topology, loss_fn=neox_loss_fn, partition_method=partition_method,

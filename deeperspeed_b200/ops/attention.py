@@ -35,7 +35,7 @@ N.register_sigs({
 
 N.register_sigs({
     "dsb_flash_attn_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p],
-    "dsb_flash_attn_bwd2": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p],
+    "dsb_flash_attn_bwd2": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _p, _i, _p],
 })
 
 _tables = {}
@@ -62,11 +62,12 @@ def set_flash_fwd_variant(keys_per_step):
 _bwd_gen = 2
 
 
-def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv=None, dq=None):
+def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv=None, dq=None, rotary=None):
     """Backward of `flash_attn_fwd` on the tcgen05 kernels. All tensors [B, S, H, 128] views with unit last stride
     (dq / dk / dv may be slices of a fused dQKV buffer). Returns (dq, dk, dv). With the default (second-generation)
     kernel dq comes back in the input dtype; the first-generation kernel (set_flash_bwd_variant(1)) returns its fp32
-    accumulator [B, S, H, 128] and ignores `dq`."""
+    accumulator [B, S, H, 128] and ignores `dq`. `rotary` = (rot_dim, base): q and k are rotated tensors and dq / dk
+    are wanted for the unrotated ones; the second-generation kernel applies the inverse rotation itself."""
     B, S, H, D = q.shape
     if scale is None:
         scale = 1.0 / (D ** 0.5)
@@ -82,12 +83,18 @@ def flash_attn_bwd(dout, q, k, v, out, lse, causal=True, scale=None, dk=None, dv
         ts = (dout, q, k, v, out, dq, dk, dv)
         assert all(t.stride(-1) == 1 and t.shape == q.shape for t in ts)
         strides = (C.c_long * 24)(*[t.stride(i) for t in ts for i in range(3)])
+        cs = sn = None
+        rot_dim = 0
+        if rotary is not None and rotary[0] > 0:
+            rot_dim = int(rotary[0])
+            cs, sn = rotary_table(S, rot_dim, rotary[1], q.device)
         N.check(lib.dsb_flash_attn_bwd2(N.ptr(dout), N.ptr(q), N.ptr(k), N.ptr(v), N.ptr(out), N.ptr(lse),
                                         N.ptr(scratch), N.ptr(dq), N.ptr(dk), N.ptr(dv), B, S, H, D, strides,
-                                        float(scale), int(causal), N.dtype_code(q.dtype), N.stream_ptr()),
-                "dsb_flash_attn_bwd2")
+                                        float(scale), int(causal), N.dtype_code(q.dtype), N.ptr(cs), N.ptr(sn),
+                                        rot_dim, N.stream_ptr()), "dsb_flash_attn_bwd2")
         K._count(3)
         return dq, dk, dv
+    assert rotary is None, "the first-generation backward does not apply the inverse rotary"
     dq_acc = torch.zeros(B, S, H, D, dtype=torch.float32, device=q.device)
     delta = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
     ts = (dout, q, k, v, out, dk, dv)
@@ -199,14 +206,16 @@ class NativeCausalSelfAttentionFn(torch.autograd.Function):
         if dout.stride(-1) != 1 or any(st % 8 for st in dout.stride()[:3]):
             dout = dout.contiguous()
         dqkv = torch.empty(B, S, 3, H, D, dtype=qkv.dtype, device=qkv.device)
-        if rot_dim > 0:
+        if rot_dim > 0 and _bwd_gen == 2:
+            # inverse rotary fused into the backward kernels: dq / dk / dv land in the dQKV buffer directly
+            flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dq=dqkv[:, :, 0], dk=dqkv[:, :, 1],
+                           dv=dqkv[:, :, 2], rotary=(rot_dim, base))
+        elif rot_dim > 0:
             dk_tmp = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
             dq, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dk_tmp, dv=dqkv[:, :, 2])
-            if dq.dtype != qkv.dtype:   # first-generation kernel: fp32 accumulator
-                dq16 = torch.empty_like(dk_tmp)
-                K.cast(dq, dq16)
-                dq = dq16
-            rotary_oop(dq, dk_tmp, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
+            dq16 = torch.empty_like(dk_tmp)
+            K.cast(dq, dq16)
+            rotary_oop(dq16, dk_tmp, dqkv[:, :, 0], dqkv[:, :, 1], rot_dim, base, inverse=True)
         else:
             dq, _, _ = flash_attn_bwd(dout, q, k, qkv5[:, :, 2], out, lse, causal=True, dk=dqkv[:, :, 1],
                                       dv=dqkv[:, :, 2], dq=dqkv[:, :, 0])

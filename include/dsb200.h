@@ -121,11 +121,13 @@ int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, const void*
                        const long* strides, float scale, int causal, int dtype, void* stream);
 /* Second-generation backward (default): everything is computed transposed (lane = key row) so that P^T and dS^T stay
  * in tensor memory as UMMA A operands; dq / dk / dv come back in the input dtype. `strides`: 8 x (sb, ss, sh) for dO, q,
- * k, v, out, dq, dk, dv. `scratch`: (2 + 128) * B * H * S floats (cleared here; nothing is allocated).
+ * k, v, out, dq, dk, dv. `scratch`: (2 + 128) * B * H * S floats (cleared here; nothing is allocated). rot_dim > 0:
+ * q / k were rotated (dsb_rotary_oop) before the forward; dq / dk are returned for the unrotated tensors.
  * Reference: the backward chain of csrc/transformer/ds_transformer_cuda.cpp:340-420. */
 int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out, const float* lse,
                         float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D, const long* strides,
-                        float scale, int causal, int dtype, void* stream);
+                        float scale, int causal, int dtype, const float* rot_cos, const float* rot_sin, int rot_dim,
+                        void* stream);
 /* Experiment switches of the second-generation kernels (0 = production); see csrc/transformer/flash_attn_v2.cu. */
 void dsb_flash_attn_debug_mode(int mode);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */

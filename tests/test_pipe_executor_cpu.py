@@ -90,3 +90,21 @@ def test_edge_split_matches_plain_schedule(stages, tmp_path):
         for a, b in zip(w0, w1):
             assert torch.allclose(a, b, atol=1e-5)
     run()
+
+
+def test_compute_partitioning_ignores_lookup_tables(tmp_path):
+    """`partition_method="compute"`: an embedding costs nothing, the output projection costs what its weight says, so a
+    decoder with a large vocabulary gets more blocks on its first stage than `parameters` would give it."""
+    @distributed_test(world_size=2)
+    def run():
+        from deeperspeed_b200.models.gpt_neox import GPTNeoXPipe, NeoXConfig
+        cfg = NeoXConfig.tiny()
+        cfg.num_layers, cfg.vocab_size, cfg.hidden_size = 6, 4096, 64
+        topo = PipeDataParallelTopology(num_pp=2, num_dp=1)
+        by_compute = GPTNeoXPipe(cfg, topology=topo, partition_method="compute")
+        by_params = GPTNeoXPipe(cfg, topology=topo, partition_method="parameters")
+        # specs: embedding, 6 blocks, final norm, head. head = 4096 * 64 = 262144 ~ 5.3 blocks of 49k parameters
+        assert by_params.parts[1] < by_compute.parts[1]
+        first, last = by_compute.parts[1] - 1, 6 - (by_compute.parts[1] - 1)
+        assert first > last
+    run()
