@@ -310,8 +310,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--tiny", action="store_true", help="tiny model (CPU plumbing check only; not a valid bench)")
     ap.add_argument("--layers", type=int, default=0, help="debug override (invalidates the number)")
-    ap.add_argument("--edge-split", dest="edge_split", type=int, default=2,
-                    help="slices of the first / last micro-batch under pipeline parallelism (1 = plain 1F1B)")
+    ap.add_argument("--edge-split", dest="edge_split", type=int, default=1,
+                    help="slices of the first / last micro-batch under pipeline parallelism (1 = plain 1F1B, the default: "
+                         "on a power-capped B200 the trimmed bubble is paid back in clocks, profiles/README.md)")
     ap.add_argument("--local_rank", type=int, default=0)
     args = ap.parse_args()
     if args.impl == "reference":
