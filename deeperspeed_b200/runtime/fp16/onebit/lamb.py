@@ -1,20 +1,27 @@
-"""OnebitLamb: LAMB whose (scaled) momentum is communicated with the 1-bit compressed all-reduce after warm-up.
+"""OnebitLamb: LAMB whose momentum travels through the 1-bit compressed all-reduce after a warm-up.
 
-Semantics per reference deepspeed/runtime/fp16/onebit/lamb.py:11-471: warm-up = plain LAMB (per-tensor trust ratio
-`lamb_coeff`, clipped to [min_coeff, max_coeff]) while an EMA of the coefficients (`lamb_coeff_freeze`, coeff_beta) is
-tracked; at `freeze_step` the variance and the coefficients are frozen, per-tensor `scaling_coeff` (mean momentum RMS
-over the tensor's RMS) equalises momentum magnitudes so all tensors can share ONE fused flat buffer, the engine's
-gradient all-reduce is disabled and the flat momentum goes through `compressed_allreduce`. In the compression phase
-the effective coefficient is `lamb_coeff_freeze * clamp(factor, ...)` where factor comes from the ratio of a freshly
-re-estimated variance to the frozen one (factor_min/max, factor_threshold limit its step-to-step change)."""
+Semantics per reference deepspeed/runtime/fp16/onebit/lamb.py:11-471:
+  warm-up      plain LAMB (trust ratio ||w|| / ||update|| clipped to [min_coeff, max_coeff]); an EMA of the ratios
+               (`lamb_coeff_freeze`, rate `coeff_beta`) is tracked for later.
+  freeze_step  variance and ratios freeze. A per-tensor `scaling_coeff` (mean momentum RMS over all tensors divided by
+               this tensor's RMS) equalises momentum magnitudes so every tensor can share ONE flat buffer and one
+               error-feedback scale; the engine's gradient all-reduce is switched off.
+  compression  local gradient -> local momentum -> scale -> `compressed_allreduce` of the flat buffer -> unscale. The
+               step uses `lamb_coeff_freeze * factor`, where factor = max(frozen denom / fresh denom) tracks how the
+               variance would have moved (the gradient is reconstructed from the momentum change), limited to
+               [factor_min, factor_max] and to +-factor_threshold per step.
+
+The momenta of all parameters live in one flat arena from the first step on (views per parameter), so the exchange
+needs no gather / scatter; phases are separate methods.
+"""
+import math
 import types
 
-import numpy as np
 import torch
 import torch.distributed as dist
 
 from ....utils.logging import logger
-from .adam import _gcd
+from .adam import _gcd  # noqa: F401  (kept importable from here)
 
 
 class OnebitLamb(torch.optim.Optimizer):
@@ -24,32 +31,31 @@ class OnebitLamb(torch.optim.Optimizer):
                  factor_min=0.5, factor_threshold=0.1):
         if amsgrad:
             raise RuntimeError("1-bit Lamb does not support the AMSGrad variant.")
-        defaults = dict(lr=lr, bias_correction=bias_correction, betas=betas, eps=eps, weight_decay=weight_decay,
-                        max_grad_norm=max_grad_norm, max_coeff=max_coeff, min_coeff=min_coeff)
-        super().__init__(params, defaults)
-        self.eps_mode = 0 if eps_inside_sqrt else 1
+        super().__init__(params, dict(lr=lr, bias_correction=bias_correction, betas=betas, eps=eps,
+                                      weight_decay=weight_decay, max_grad_norm=max_grad_norm, max_coeff=max_coeff,
+                                      min_coeff=min_coeff))
         assert dist.is_initialized() is True, "Please initialize the torch distributed backend."
+        self.eps_mode = 0 if eps_inside_sqrt else 1
         self.deepspeed = deepspeed
-        self.lamb_freeze_key = False
-        self.initialize = False
         self.freeze_step = freeze_step
+        self.lamb_freeze_key = False      # True in the compression phase
+        self.initialize = False           # the very first call only sets state up
         self.cuda_aware = cuda_aware
         self.coeff_beta = coeff_beta
-        self.factor_max = factor_max
-        self.factor_min = factor_min
-        self.factor_threshold = factor_threshold
-        self.using_pipeline = False
+        self.factor_max, self.factor_min, self.factor_threshold = factor_max, factor_min, factor_threshold
         self.comm_backend_name = comm_backend_name
+        self.using_pipeline = False
         self.comm_backend_handle = None
-        if self.comm_backend_name == "nccl":
+        if comm_backend_name == "nccl":
             from ...comm.nccl import NcclBackend
-            self.using_pipeline = hasattr(self.deepspeed, "pipeline_enable_backward_allreduce")
-            self.comm_backend_handle = NcclBackend(self.deepspeed.mpu if self.deepspeed is not None else None)
-        elif self.comm_backend_name == "mpi":
+            self.using_pipeline = hasattr(deepspeed, "pipeline_enable_backward_allreduce")
+            self.comm_backend_handle = NcclBackend(deepspeed.mpu if deepspeed is not None else None)
+        elif comm_backend_name == "mpi":
             from ...comm.mpi import MpiBackend
             self.comm_backend_handle = MpiBackend(cuda_aware)
         self.size = self.comm_backend_handle.size
-        self.divider = int(self.size * 32 / _gcd(self.size, 32))
+        self.divider = self.size * 32 // math.gcd(self.size, 32)
+        # flat momentum arena(s) and their error-feedback buffers (lists: the reference keeps one entry per arena)
         self.exp_avg_flat = []
         self.dummy_exp_avg = {}
         self.corrected_tensor_sizes = []
@@ -58,229 +64,213 @@ class OnebitLamb(torch.optim.Optimizer):
         self.server_errors = []
         self.lamb_coeffs = []
 
+    # ------------------------------------------------------------------ small helpers
     def _all_params(self):
         for group in self.param_groups:
             for p in group["params"]:
                 yield group, p
 
+    def _engine_reduces_gradients(self, enabled):
+        if self.deepspeed is None:
+            return
+        attr = "pipeline_enable_backward_allreduce" if self.using_pipeline else "enable_backward_allreduce"
+        setattr(self.deepspeed, attr, enabled)
+
+    def _first_state(self):
+        return self.state[self.param_groups[0]["params"][0]]
+
+    def _resolve_grads(self, grads):
+        """[(group, p, grad)] for every parameter that has a gradient this step."""
+        if grads is None:
+            per_group = [None] * len(self.param_groups)
+        elif isinstance(grads, types.GeneratorType) or type(grads[0]) != list:
+            per_group = [grads]
+        else:
+            per_group = grads
+        out = []
+        for group, given in zip(self.param_groups, per_group):
+            given = given if given is not None else [None] * len(group["params"])
+            for p, g in zip(group["params"], given):
+                if g is None:
+                    if p.grad is None:
+                        continue
+                    g = p.grad.data
+                if g.is_sparse:
+                    raise RuntimeError("1-bit Lamb does not support sparse gradients")
+                out.append((group, p, g))
+        return out
+
+    def _ensure_state(self, p):
+        state = self.state[p]
+        if not state or (len(state) == 1 and "scaling_coeff" in state):
+            state["step"] = 0
+            state["lamb_coeff_freeze"] = 0.0
+            state["last_factor"] = 1.0
+            for key in ("exp_avg", "exp_avg_sq", "exp_avg_sq_fresh"):
+                state[key] = torch.zeros_like(p.data)
+        return state
+
+    def _ensure_scaling_coeffs(self):
+        """First compression step: scaling_coeff = (mean RMS of all momenta) / (RMS of this momentum)."""
+        if "scaling_coeff" in self._first_state():
+            return
+        rms = {p: (torch.norm(self.state[p]["exp_avg"]) / math.sqrt(self.state[p]["exp_avg"].numel())).item()
+               for _, p in self._all_params()}
+        mean_rms = sum(rms.values()) / len(rms)
+        for p, r in rms.items():
+            self.state[p]["scaling_coeff"] = mean_rms / max(r, 1e-20)
+
+    def _ensure_flat_momentum(self):
+        """Re-home every exp_avg as a view of one flat fp32 arena (the unit of the compressed exchange)."""
+        if self.exp_avg_flat:
+            return
+        params = [p for _, p in self._all_params()]
+        flat = torch.cat([self.state[p]["exp_avg"].detach().float().view(-1) for p in params])
+        unit = self.size * self.divider
+        padded = -(-flat.numel() // unit) * unit
+        self.corrected_tensor_sizes.append(padded)
+        self.server_chunk_sizes.append(padded // self.size)
+        self.exp_avg_flat.append(flat)
+        offset = 0
+        for p in params:
+            self.state[p]["exp_avg"] = flat.narrow(0, offset, p.numel()).view_as(p.data)
+            offset += p.numel()
+
+    def _ensure_error_buffers(self):
+        if not self.initialize or self.worker_errors:
+            return
+        dev = self.exp_avg_flat[0].device
+        for padded, chunk in zip(self.corrected_tensor_sizes, self.server_chunk_sizes):
+            self.worker_errors.append(torch.zeros(padded, device=dev))
+            self.server_errors.append(torch.zeros(chunk, device=dev))
+
+    # ------------------------------------------------------------------ phases
+    def _warmup_update(self, group, p, state, grad):
+        beta1, beta2 = group["betas"]
+        m, v = state["exp_avg"], state["exp_avg_sq"]
+        m.mul_(beta1).add_(grad, alpha=1 - beta1)
+        v.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
+        if state["step"] == self.freeze_step:
+            state["exp_avg_sq_fresh"].data = v.detach().clone()
+        if not self.initialize:
+            return
+        update = m / (v.sqrt() + group["eps"])
+        if group["weight_decay"] > 0.0:
+            update += group["weight_decay"] * p.data
+        w_norm, u_norm = p.data.pow(2).sum().sqrt(), update.pow(2).sum().sqrt()
+        coeff = 1.0
+        if w_norm != 0 and u_norm != 0:
+            coeff = min(max((w_norm / u_norm).item(), group["min_coeff"]), group["max_coeff"])
+        if coeff != 1.0:
+            state["lamb_coeff_freeze"] = self.coeff_beta * state["lamb_coeff_freeze"] + (1 - self.coeff_beta) * coeff
+        self.lamb_coeffs.append(coeff)
+        with torch.no_grad():
+            p.add_(update, alpha=-group["lr"] * coeff)
+
+    def _exchange_momentum(self):
+        if self.size == 1:
+            return
+        rank = self.deepspeed.local_rank if self.deepspeed else 0
+        for flat, werr, serr in zip(self.exp_avg_flat, self.worker_errors, self.server_errors):
+            averaged = self.comm_backend_handle.compressed_allreduce(flat, werr, serr, rank)
+            if averaged.data_ptr() != flat.data_ptr():
+                flat.copy_(averaged)
+
+    def _compressed_update(self, previous):
+        """Parameter update of the compression phase; `previous[p]` is the momentum before this step."""
+        for group, p in self._all_params():
+            state = self.state[p]
+            beta1, beta2 = group["betas"]
+            m, v, v_fresh = state["exp_avg"], state["exp_avg_sq"], state["exp_avg_sq_fresh"]
+            m.div_(state["scaling_coeff"])
+            mask = group.get("exp_avg_mask")
+            if mask is not None:
+                if mask.device != m.device:
+                    mask = group["exp_avg_mask"] = mask.to(device=m.device)
+                m.mul_(mask)
+            # the averaged gradient is not available any more: recover it from the momentum recursion
+            g_hat = (m - previous[p] * beta1) / (1 - beta1)
+            v_fresh.mul_(beta2).addcmul_(g_hat, g_hat, value=1 - beta2)
+            denom = v.sqrt() + group["eps"]
+            direction = m / denom
+            update = direction + group["weight_decay"] * p.data if group["weight_decay"] > 0.0 else direction
+            factor = (denom / (v_fresh.sqrt() + group["eps"])).max().item()
+            if group["weight_decay"] > 0.0:
+                share = min(1.0, (direction.pow(2).sum().sqrt() / update.pow(2).sum().sqrt()).item())
+                factor = factor * share + (1.0 - share)
+            factor = min(max(factor, self.factor_min), self.factor_max)
+            last = state["last_factor"]
+            factor = max(min(factor, last * (1.0 + self.factor_threshold)), last * (1.0 - self.factor_threshold))
+            state["last_factor"] = factor
+            coeff = state["lamb_coeff_freeze"] * factor
+            self.lamb_coeffs.append(coeff)
+            with torch.no_grad():
+                p.add_(update, alpha=-group["lr"] * coeff)
+
+    # ------------------------------------------------------------------ step
     def step(self, closure=None, grads=None):
         loss = closure() if closure is not None else None
-        if grads is None:
-            grads_group = [None] * len(self.param_groups)
-        elif isinstance(grads, types.GeneratorType):
-            grads_group = [grads]
-        elif type(grads[0]) != list:
-            grads_group = [grads]
-        else:
-            grads_group = grads
+        work = self._resolve_grads(grads)
         del self.lamb_coeffs[:]
+        if not self.initialize:
+            self.lamb_freeze_key = False
+        compressing = self.lamb_freeze_key
+        previous = None
+        if compressing:
+            previous = {p: self.state[p]["exp_avg"].detach().clone() for _, p in self._all_params()}
+            self._ensure_scaling_coeffs()
 
-        if self.lamb_freeze_key:
-            exp_avg_last_step = [[self.state[p]["exp_avg"].detach().clone() for p in group["params"]]
-                                 for group in self.param_groups]
-            if "scaling_coeff" not in self.state[self.param_groups[0]["params"][0]]:
-                # first compression step: per-tensor momentum scaling so tensors share one error-feedback scale
-                momentum_scales = [[(torch.norm(self.state[p]["exp_avg"]) /
-                                     np.sqrt(torch.numel(self.state[p]["exp_avg"]))).item() for p in group["params"]]
-                                   for group in self.param_groups]
-                united_scale = sum(sum(x) for x in momentum_scales) / sum(len(x) for x in momentum_scales)
-                for i, group in enumerate(self.param_groups):
-                    for j, p in enumerate(group["params"]):
-                        self.state[p]["scaling_coeff"] = united_scale / max(momentum_scales[i][j], 1e-20)
+        for group, p, grad in work:
+            state = self._ensure_state(p)
+            state["step"] += 1
+            if not compressing:
+                self._warmup_update(group, p, state, grad)
+            elif self.initialize:
+                beta1 = group["betas"][0]
+                state["exp_avg"].mul_(beta1).add_(grad, alpha=1 - beta1).mul_(state["scaling_coeff"])
 
-        for group, grads_this_group in zip(self.param_groups, grads_group):
-            if grads_this_group is None:
-                grads_this_group = [None] * len(group["params"])
-            for p, grad in zip(group["params"], grads_this_group):
-                if p.grad is None and grad is None:
-                    continue
-                if grad is None:
-                    grad = p.grad.data
-                if grad.is_sparse:
-                    raise RuntimeError("1-bit Lamb does not support sparse gradients")
-                state = self.state[p]
-                if len(state) == 0 or (len(state) == 1 and "scaling_coeff" in state):
-                    state["step"] = 0
-                    state["lamb_coeff_freeze"] = 0.0
-                    state["last_factor"] = 1.0
-                    state["exp_avg"] = torch.zeros_like(p.data)
-                    state["exp_avg_sq"] = torch.zeros_like(p.data)
-                    state["exp_avg_sq_fresh"] = torch.zeros_like(p.data)
-                if not self.initialize:
-                    self.lamb_freeze_key = False
-                exp_avg, exp_avg_sq, exp_avg_sq_fresh = state["exp_avg"], state["exp_avg_sq"], state["exp_avg_sq_fresh"]
-                beta1, beta2 = group["betas"]
-                max_coeff, min_coeff = group["max_coeff"], group["min_coeff"]
-                state["step"] += 1
-                if self.lamb_freeze_key is False:
-                    # warm-up: vanilla LAMB
-                    exp_avg.mul_(beta1).add_(grad, alpha=1 - beta1)
-                    exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
-                    if state["step"] == self.freeze_step:
-                        exp_avg_sq_fresh.data = exp_avg_sq.detach().clone()
-                    grad = None
-                    if self.initialize:
-                        weight_norm = p.data.pow(2).sum().sqrt()
-                        update = exp_avg / (exp_avg_sq.sqrt() + group["eps"])
-                        if group["weight_decay"] > 0.0:
-                            update += group["weight_decay"] * p.data
-                        update_norm = update.pow(2).sum().sqrt()
-                        lamb_coeff = 1.0
-                        if weight_norm != 0 and update_norm != 0:
-                            lamb_coeff = (weight_norm / update_norm).item()
-                            lamb_coeff = min(max(lamb_coeff, min_coeff), max_coeff)
-                        if lamb_coeff != 1.0:
-                            state["lamb_coeff_freeze"] = self.coeff_beta * state["lamb_coeff_freeze"] + \
-                                (1 - self.coeff_beta) * lamb_coeff
-                        self.lamb_coeffs.append(lamb_coeff)
-                        with torch.no_grad():
-                            p.add_(-group["lr"] * lamb_coeff * update)
-                else:
-                    # compression stage: local momentum, scaled so all tensors share one magnitude
-                    if self.initialize:
-                        exp_avg.mul_(beta1).add_(grad, alpha=1 - beta1)
-                        exp_avg.mul_(self.state[p]["scaling_coeff"])
-                    grad = None
-
-        # one-time setup of the fused flat momentum buffer + error-feedback buffers
-        if len(self.exp_avg_flat) == 0:
-            momentum_groups = []
-            tensor_size = 0
-            for group in self.param_groups:
-                for p in group["params"]:
-                    momentum_groups.append(self.state[p]["exp_avg"])
-                    tensor_size += torch.numel(p.data)
-            corrected = tensor_size
-            if tensor_size % (self.size * self.divider) != 0:
-                corrected += (self.size * self.divider) - (tensor_size % (self.size * self.divider))
-            self.corrected_tensor_sizes.append(corrected)
-            self.server_chunk_sizes.append(corrected // self.size)
-            flat = torch.cat([m.detach().float().view(-1) for m in momentum_groups])
-            self.exp_avg_flat.append(flat)
-            off = 0
-            for group in self.param_groups:
-                for p in group["params"]:
-                    n = p.numel()
-                    self.state[p]["exp_avg"] = flat.narrow(0, off, n).view_as(p.data)
-                    off += n
-
-        if self.initialize and len(self.worker_errors) == 0:
-            dev = self.exp_avg_flat[0].device
-            for i in range(len(self.exp_avg_flat)):
-                self.worker_errors.append(torch.zeros(self.corrected_tensor_sizes[i], device=dev))
-                self.server_errors.append(torch.zeros(self.server_chunk_sizes[i], device=dev))
-
-        if self.lamb_freeze_key:
-            if self.size > 1:
-                for i in range(len(self.exp_avg_flat)):
-                    if not self.initialize:
-                        self.exp_avg_flat[i].zero_()
-                        self.worker_errors[i].zero_()
-                        self.server_errors[i].zero_()
-                    res = self.comm_backend_handle.compressed_allreduce(
-                        self.exp_avg_flat[i], self.worker_errors[i], self.server_errors[i],
-                        self.deepspeed.local_rank if self.deepspeed else 0)
-                    if res.data_ptr() != self.exp_avg_flat[i].data_ptr():
-                        self.exp_avg_flat[i].copy_(res)
-
-        if self.lamb_freeze_key and self.initialize:
-            for i, group in enumerate(self.param_groups):
-                bias_correction = 1 if group["bias_correction"] else 0
-                for j, p in enumerate(group["params"]):
-                    state = self.state[p]
-                    exp_avg, exp_avg_sq, exp_avg_sq_fresh = state["exp_avg"], state["exp_avg_sq"], state["exp_avg_sq_fresh"]
-                    beta1, beta2 = group["betas"]
-                    exp_avg.div_(self.state[p]["scaling_coeff"])
-                    # momentum change approximates the averaged gradient -> refresh a "fresh" variance estimate
-                    if "exp_avg_mask" in group:
-                        if exp_avg.device != group["exp_avg_mask"].device:
-                            group["exp_avg_mask"] = group["exp_avg_mask"].to(device=exp_avg.device)
-                        exp_avg.mul_(group["exp_avg_mask"])
-                    grad_reconstruct = ((exp_avg - exp_avg_last_step[i][j] * beta1) / (1 - beta1))
-                    exp_avg_sq_fresh.mul_(beta2).addcmul_(grad_reconstruct, grad_reconstruct, value=1 - beta2)
-                    denom = exp_avg_sq.sqrt() + group["eps"]
-                    update_prelim = exp_avg / denom
-                    if group["weight_decay"] > 0.0:
-                        update = update_prelim + group["weight_decay"] * p.data
-                    else:
-                        update = update_prelim
-                    lamb_coeff = 1.0
-                    update_norm = update.pow(2).sum().sqrt()
-                    denom_real = exp_avg_sq_fresh.sqrt() + group["eps"]
-                    factor = (denom / denom_real).max().item()
-                    if group["weight_decay"] > 0.0:
-                        update_ratio = min(1.0, (update_prelim.pow(2).sum().sqrt() / update_norm).item())
-                        factor = factor * update_ratio + (1.0 - update_ratio)
-                    factor = min(max(factor, self.factor_min), self.factor_max)
-                    factor = min(factor, state["last_factor"] * (1.0 + self.factor_threshold))
-                    factor = max(factor, state["last_factor"] * (1.0 - self.factor_threshold))
-                    state["last_factor"] = factor
-                    lamb_coeff = state["lamb_coeff_freeze"] * factor
-                    self.lamb_coeffs.append(lamb_coeff)
-                    with torch.no_grad():
-                        p.add_(-group["lr"] * lamb_coeff * update)
-            del exp_avg_last_step[:]
-            exp_avg_last_step = None
+        self._ensure_flat_momentum()
+        self._ensure_error_buffers()
+        if compressing:
+            self._exchange_momentum()
+            if self.initialize:
+                self._compressed_update(previous)
 
         if not self.initialize:
             self.lamb_freeze_key = False
             self.initialize = True
             logger.info(f"Finished the initialization step at rank {dist.get_rank()}")
             return loss
-
-        if self.lamb_freeze_key is False:
-            first = self.state[self.param_groups[0]["params"][0]]
-            if first["step"] >= self.freeze_step:
-                logger.info("OnebitLamb - starting compressed communication")
-                self.lamb_freeze_key = True
-                if self.deepspeed is not None:
-                    if self.using_pipeline:
-                        self.deepspeed.pipeline_enable_backward_allreduce = False
-                    else:
-                        self.deepspeed.enable_backward_allreduce = False
+        if not self.lamb_freeze_key and self._first_state()["step"] >= self.freeze_step:
+            logger.info("OnebitLamb - starting compressed communication")
+            self.lamb_freeze_key = True
+            self._engine_reduces_gradients(False)
         return loss
 
     def load_state_dict(self, state_dict):
-        for i, group in enumerate(self.param_groups):
-            if "exp_avg_mask" in group:
-                state_dict["param_groups"][i]["exp_avg_mask"] = group["exp_avg_mask"]
-            elif "exp_avg_mask" in state_dict["param_groups"][i]:
-                state_dict["param_groups"][i].pop("exp_avg_mask")
+        """Restore; the flat arena and the error buffers are rebuilt on the next step, the phase follows `step`."""
+        for live, saved in zip(self.param_groups, state_dict["param_groups"]):
+            if "exp_avg_mask" in live:
+                saved["exp_avg_mask"] = live["exp_avg_mask"]
+            else:
+                saved.pop("exp_avg_mask", None)
         super().load_state_dict(state_dict)
-        # the fused flat buffer and the error buffers are rebuilt on the next step
-        del self.exp_avg_flat[:]
+        for buffers in (self.exp_avg_flat, self.corrected_tensor_sizes, self.server_chunk_sizes, self.worker_errors,
+                        self.server_errors):
+            del buffers[:]
         self.dummy_exp_avg.clear()
-        del self.corrected_tensor_sizes[:]
-        del self.server_chunk_sizes[:]
-        first = self.state[self.param_groups[0]["params"][0]]
-        if first["step"] < self.freeze_step:
-            if dist.get_rank() == 0:
-                logger.info("Checkpoint loaded and OnebitLamb warmup stage starts/continues.")
-            if self.lamb_freeze_key is True:
-                self.lamb_freeze_key = False
-                if self.deepspeed is not None:
-                    if self.using_pipeline:
-                        self.deepspeed.pipeline_enable_backward_allreduce = True
-                    else:
-                        self.deepspeed.enable_backward_allreduce = True
-            for group in self.param_groups:
-                for p in group["params"]:
-                    self.state[p]["lamb_coeff_freeze"] = 0.0
-                    self.state[p]["last_factor"] = 1.0
-                    if "scaling_coeff" in self.state[p]:
-                        self.state[p].pop("scaling_coeff")
-        else:
-            if dist.get_rank() == 0:
-                logger.info("Checkpoint loaded and OnebitLamb compression stage starts/continues.")
-            if self.lamb_freeze_key is False:
-                self.lamb_freeze_key = True
-                if self.deepspeed is not None:
-                    if self.using_pipeline:
-                        self.deepspeed.pipeline_enable_backward_allreduce = False
-                    else:
-                        self.deepspeed.enable_backward_allreduce = False
-        del self.worker_errors[:]
-        del self.server_errors[:]
+        compressing = self._first_state()["step"] >= self.freeze_step
+        if dist.get_rank() == 0:
+            logger.info("Checkpoint loaded and OnebitLamb %s stage starts/continues.",
+                        "compression" if compressing else "warmup")
+        if compressing != self.lamb_freeze_key:
+            self.lamb_freeze_key = compressing
+            self._engine_reduces_gradients(not compressing)
+        if not compressing:
+            for _, p in self._all_params():   # the frozen statistics are re-learned during the rest of the warm-up
+                self.state[p]["lamb_coeff_freeze"] = 0.0
+                self.state[p]["last_factor"] = 1.0
+                self.state[p].pop("scaling_coeff", None)
 
     def get_lamb_coeffs(self):
         return self.lamb_coeffs
