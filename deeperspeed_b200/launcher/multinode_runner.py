@@ -1,5 +1,10 @@
-"""Multi-node command builders: pdsh/ssh, OpenMPI, MVAPICH, Slurm, MosaicML
-(reference deepspeed/launcher/multinode_runner.py:14-292, command shapes in SURVEY C.12)."""
+"""Multi-node transports: how the per-node launcher (or the user script itself) is started on every host.
+
+Command shapes per reference deepspeed/launcher/multinode_runner.py:14-292: pdsh / ssh fan-out,
+OpenMPI `mpirun`, MVAPICH2-GDR `mpirun`, Slurm `srun`, and the MosaicML platform. A transport is described by a few
+class attributes (the binary that proves it is installed, how exported variables are spelled, which runner options it
+cannot honour) plus one `get_cmd`; the argv pieces shared by several transports are built once in the base class.
+"""
 import os
 import shutil
 import subprocess
@@ -14,16 +19,21 @@ LAUNCH_MODULE = "deeperspeed_b200.launcher.launch"
 
 
 class MultiNodeRunner(ABC):
-    def __init__(self, args, world_info_base64):
+    probe = None               # executable whose presence means the transport is installed
+    label = None               # value of `name` (launcher option / log messages)
+    unsupported = ()           # (runner attribute, neutral value): options this transport cannot honour
+
+    def __init__(self, args, world_info_base64, resource_pool=None):
         self.args = args
         self.user_arguments = self.parse_user_args()
         self.user_script = args.user_script
         self.world_info_base64 = world_info_base64
+        self.resource_pool = resource_pool
         self.exports = {}
 
-    @abstractmethod
     def backend_exists(self):
         """Return whether the corresponding backend exists"""
+        return shutil.which(self.probe)
 
     @abstractmethod
     def get_cmd(self, environment, active_resources):
@@ -37,168 +47,136 @@ class MultiNodeRunner(ABC):
 
     @property
     def name(self):
-        return self.__class__.__name__
+        return self.label or self.__class__.__name__
+
+    # ---- shared argv pieces
+    def _reject_unsupported(self):
+        for attr, neutral in self.unsupported:
+            what = {"include": "worker include/exclusion", "exclude": "worker include/exclusion",
+                    "num_nodes": "limiting num nodes", "num_gpus": "limiting num gpus"}[attr]
+            assert getattr(self.args, attr) == neutral, f"{self.name} backend does not support {what}"
+
+    def _total_processes(self):
+        return sum(self.resource_pool.values())
+
+    def _script_argv(self):
+        """python -u <user script> <user args>: transports that start every rank themselves."""
+        return [sys.executable, "-u", self.user_script] + self.user_arguments
+
+    def _launcher_argv(self, node_rank, master_addr=None, master_port=None):
+        """python -u -m <per-node launcher> ...: transports that start one process per node."""
+        return [sys.executable, "-u", "-m", LAUNCH_MODULE, f"--world_info={self.world_info_base64}",
+                f"--node_rank={node_rank}", f"--master_addr={master_addr or self.args.master_addr}",
+                f"--master_port={master_port or self.args.master_port}"]
 
 
 class PDSHRunner(MultiNodeRunner):
-    def backend_exists(self):
-        return shutil.which("pdsh")
-
-    @property
-    def name(self):
-        return "pdsh"
+    probe, label = "pdsh", "pdsh"
 
     def parse_user_args(self):
-        return list(map(lambda x: x if x.startswith("-") else "'{}'".format(x), self.args.user_args))
+        # the command line passes through a remote shell: quote everything that is not an option
+        return [a if a.startswith("-") else f"'{a}'" for a in self.args.user_args]
 
     def get_cmd(self, environment, active_resources):
         environment["PDSH_RCMD_TYPE"] = "ssh"
-        active_workers = ",".join(active_resources.keys())
-        logger.info("Running on the following workers: %s" % active_workers)
-        pdsh_cmd_args = ["pdsh", "-f", str(PDSH_MAX_FAN_OUT), "-w", active_workers]
-        exports = ""
-        for key, val in self.exports.items():
-            exports += "export {}={}; ".format(key, val)
-        deepspeed_launch = [exports, "cd {};".format(os.path.abspath(".")), sys.executable, "-u", "-m", LAUNCH_MODULE,
-                            "--world_info={}".format(self.world_info_base64), "--node_rank=%n",
-                            "--master_addr={}".format(self.args.master_addr),
-                            "--master_port={}".format(self.args.master_port)]
+        workers = ",".join(active_resources.keys())
+        logger.info("Running on the following workers: %s" % workers)
+        exports = "".join(f"export {k}={v}; " for k, v in self.exports.items())
+        remote = [exports, f"cd {os.path.abspath('.')};"] + self._launcher_argv("%n")     # pdsh expands %n per host
         if getattr(self.args, "detect_nvlink_pairs", False):
-            deepspeed_launch.append("--detect_nvlink_pairs")
-        return pdsh_cmd_args + deepspeed_launch + [self.user_script] + self.user_arguments
+            remote.append("--detect_nvlink_pairs")
+        return ["pdsh", "-f", str(PDSH_MAX_FAN_OUT), "-w", workers] + remote + [self.user_script] + self.user_arguments
 
 
-class OpenMPIRunner(MultiNodeRunner):
+class _MpirunRunner(MultiNodeRunner):
+    """Transports where an MPI launcher starts every rank and the user script discovers its rank from MPI."""
+    unsupported = (("include", ""), ("exclude", ""), ("num_nodes", -1), ("num_gpus", -1))
+    export_flag = "-x"
+
+    def _export_argv(self):
+        return [tok for k, v in self.exports.items() for tok in (self.export_flag, f"{k}={v}")]
+
+
+class OpenMPIRunner(_MpirunRunner):
+    probe, label = "ompi_info", "openmpi"
+
     def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
+        super().__init__(args, world_info_base64, resource_pool)
         self.add_export("UCX_TLS", "tcp")
 
-    def backend_exists(self):
-        return shutil.which("ompi_info")
-
-    @property
-    def name(self):
-        return "openmpi"
-
     def get_cmd(self, environment, active_resources):
-        assert self.args.include == "", "openmpi backend does not support worker include/exclusion"
-        assert self.args.exclude == "", "openmpi backend does not support worker include/exclusion"
-        assert self.args.num_nodes == -1, "openmpi backend does not support limiting num nodes"
-        assert self.args.num_gpus == -1, "openmpi backend does not support limiting num gpus"
-        total_process_count = sum(self.resource_pool.values())
-        mpirun_cmd = ["mpirun", "-n", f"{total_process_count}", "-hostfile", f"{self.args.hostfile}", "--mca", "btl",
-                      "^openib", "--mca", "btl_tcp_if_include", "eth0"]
-        export_cmd = []
-        for k, v in self.exports.items():
-            export_cmd += ["-x", f"{k}={v}"]
-        python_exec = [sys.executable, "-u"]
-        return mpirun_cmd + export_cmd + python_exec + [self.user_script] + self.user_arguments
+        self._reject_unsupported()
+        head = ["mpirun", "-n", f"{self._total_processes()}", "-hostfile", f"{self.args.hostfile}",
+                "--mca", "btl", "^openib", "--mca", "btl_tcp_if_include", "eth0"]
+        return head + self._export_argv() + self._script_argv()
 
 
-class MVAPICHRunner(MultiNodeRunner):
+class MVAPICHRunner(_MpirunRunner):
+    label = "mvapich"
+    export_flag = "-env"
+    _ENV = {"MV2_SMP_USE_CMA": "0",             # CMA is unavailable in containers
+            "MV2_DEBUG_SHOW_BACKTRACE": "1", "MV2_USE_CUDA": "1", "MV2_SUPPORT_DL": "1",
+            "MV2_ENABLE_AFFINITY": "0",        # leave thread placement to the framework (OpenMP CPU-Adam)
+            "MV2_INTER_ALLGATHER_TUNING": "5", "MV2_CUDA_USE_NAIVE": "0"}
+
     def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
-        self.add_export("MV2_SMP_USE_CMA", "0")
-        self.add_export("MV2_DEBUG_SHOW_BACKTRACE", "1")
-        self.add_export("MV2_USE_CUDA", "1")
-        self.add_export("MV2_SUPPORT_DL", "1")
-        self.add_export("MV2_ENABLE_AFFINITY", "0")
-        self.add_export("MV2_INTER_ALLGATHER_TUNING", "5")
-        self.add_export("MV2_CUDA_USE_NAIVE", "0")
+        super().__init__(args, world_info_base64, resource_pool)
+        for k, v in self._ENV.items():
+            self.add_export(k, v)
 
     def backend_exists(self):
-        mpiname_exists = shutil.which("mpiname")
-        exists = False
-        if not mpiname_exists:
+        if not shutil.which("mpiname"):
             warnings.warn("mpiname does not exist, mvapich is not installed properly")
-        else:
-            results = subprocess.check_output("mpiname", shell=True)
-            mpiname_results = results.decode("utf-8").strip()
-            if "MVAPICH2-GDR" in mpiname_results:
-                exists = True
-            else:
-                warnings.warn(f"Expected MVAPICH2-GDR as return for mpiname but received {mpiname_results}")
-        return exists
-
-    @property
-    def name(self):
-        return "mvapich"
+            return False
+        flavour = subprocess.check_output("mpiname", shell=True).decode("utf-8").strip()
+        if "MVAPICH2-GDR" not in flavour:
+            warnings.warn(f"Expected MVAPICH2-GDR as return for mpiname but received {flavour}")
+            return False
+        return True
 
     def get_cmd(self, environment, active_resources):
-        assert self.args.include == "", "mvapich backend does not support worker include/exclusion"
-        assert self.args.exclude == "", "mvapich backend does not support worker include/exclusion"
-        assert self.args.num_nodes == -1, "mvapich backend does not support limiting num nodes"
-        assert self.args.num_gpus == -1, "mvapich backend does not support limiting num gpus"
-        devices_per_node = self.resource_pool.values()
-        total_process_count = sum(devices_per_node)
-        process_per_node = list(devices_per_node)[0]
-        assert all([n == process_per_node for n in devices_per_node]), "mvapich requires same number of devices per node"
+        self._reject_unsupported()
+        per_node = list(self.resource_pool.values())
+        assert all(n == per_node[0] for n in per_node), "mvapich requires same number of devices per node"
         with open(MVAPICH_TMP_HOSTFILE, "w") as fd:
-            for host in self.resource_pool.keys():
-                fd.write(f"{host}\n")
-        mpirun_cmd = ["mpirun", "-np", f"{total_process_count}", "-ppn", f"{process_per_node}", "--hostfile",
-                      f"{MVAPICH_TMP_HOSTFILE}"]
-        export_cmd = []
-        for k, v in self.exports.items():
-            export_cmd += ["-env", f"{k}={v}"]
-        python_exec = [sys.executable, "-u"]
-        return mpirun_cmd + export_cmd + python_exec + [self.user_script] + self.user_arguments
+            fd.writelines(f"{host}\n" for host in self.resource_pool)
+        head = ["mpirun", "-np", f"{sum(per_node)}", "-ppn", f"{per_node[0]}", "--hostfile", f"{MVAPICH_TMP_HOSTFILE}"]
+        return head + self._export_argv() + self._script_argv()
 
 
 class SlurmRunner(MultiNodeRunner):
+    probe, label = "sinfo", "slurm"
+
     def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
-
-    def backend_exists(self):
-        return shutil.which("sinfo")
-
-    @property
-    def name(self):
-        return "slurm"
+        super().__init__(args, world_info_base64, resource_pool)
 
     def get_cmd(self, environment, active_resources):
-        assert not getattr(self.args, "detect_nvlink_pairs", False), "slurm backend does not support remapping visible devices"
-        total_process_count = sum(self.resource_pool.values())
-        srun_cmd = ["srun", "-n", f"{total_process_count}"]
-        if getattr(self.args, "comment", ""):
-            srun_cmd += ["--comment", self.args.comment]
-        if self.args.include != "":
-            srun_cmd += ["--include", f"{self.args.include}"]
-        if self.args.exclude != "":
-            srun_cmd += ["--exclude", f"{self.args.exclude}"]
-        if self.args.num_nodes > 0:
-            srun_cmd += ["--nodes", f"{self.args.num_nodes}"]
-        if self.args.num_gpus > 0:
-            srun_cmd += ["--gpus", f"{self.args.num_gpus}"]
-        exports = "--export=ALL"
-        for key, val in self.exports.items():
-            exports += f",{key}={val}"
-        python_exec = [sys.executable, "-u"]
-        return srun_cmd + [exports] + python_exec + [self.user_script] + self.user_arguments
+        assert not getattr(self.args, "detect_nvlink_pairs", False), \
+            "slurm backend does not support remapping visible devices"
+        cmd = ["srun", "-n", f"{self._total_processes()}"]
+        optional = (("--comment", getattr(self.args, "comment", "")), ("--include", self.args.include),
+                    ("--exclude", self.args.exclude),
+                    ("--nodes", self.args.num_nodes if self.args.num_nodes > 0 else ""),
+                    ("--gpus", self.args.num_gpus if self.args.num_gpus > 0 else ""))
+        for flag, value in optional:
+            if value != "":
+                cmd += [flag, f"{value}"]
+        exports = ",".join(["--export=ALL"] + [f"{k}={v}" for k, v in self.exports.items()])
+        return cmd + [exports] + self._script_argv()
 
 
 class MosaicMLRunner(MultiNodeRunner):
-    """MosaicML platform: ranks are started by the platform; NODE_RANK / MASTER_ADDR come from its environment."""
+    """MosaicML platform: the platform starts one container per node and tells it NODE_RANK / MASTER_ADDR / MASTER_PORT
+    through the environment; each node then runs the per-node launcher."""
+    label = "mosaicml"
 
     def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
+        super().__init__(args, world_info_base64, resource_pool)
 
     def backend_exists(self):
         return "NODE_RANK" in os.environ or shutil.which("mcli")
 
-    @property
-    def name(self):
-        return "mosaicml"
-
     def get_cmd(self, environment, active_resources):
-        node_rank = os.environ.get("NODE_RANK", "0")
-        master_addr = os.environ.get("MASTER_ADDR", self.args.master_addr)
-        master_port = os.environ.get("MASTER_PORT", str(self.args.master_port))
-        launch = [sys.executable, "-u", "-m", LAUNCH_MODULE, "--world_info={}".format(self.world_info_base64),
-                  "--node_rank={}".format(node_rank), "--master_addr={}".format(master_addr),
-                  "--master_port={}".format(master_port)]
-        return launch + [self.user_script] + self.user_arguments
+        env = os.environ
+        return self._launcher_argv(env.get("NODE_RANK", "0"), env.get("MASTER_ADDR"), env.get("MASTER_PORT")) + \
+            [self.user_script] + self.user_arguments

@@ -1,124 +1,169 @@
-"""FlopsProfiler: counts MACs/params/latency per module by wrapping torch.nn.functional ops and module hooks; prints the
-annotated module tree and depth-aggregated top-k (API of reference deepspeed/profiling/flops_profiler/profiler.py:11-868)."""
-import time
-from functools import partial
+"""FlopsProfiler: MACs, parameters and forward latency of every module of a model.
 
-import numpy as np
+Interface and report layout per reference deepspeed/profiling/flops_profiler/profiler.py:11-868 (`FlopsProfiler`
+start / stop / reset / end, `get_total_*`, `print_model_profile`, `print_model_aggregated_profile`,
+`get_model_profile`, the `*_to_string` helpers). Own mechanism:
+  * the profiler keeps one record per module in a dictionary (nothing is stored on the modules), with a stack of
+    "currently executing" records that the patched operators charge their MACs to;
+  * operator rules are a table {namespace: {function: MAC formula}} that also covers this framework's fused kernels
+    (`ops.kernels.linear / linear_gelu / linear_residual / mlp_residual`, the flash-attention block), which never pass
+    through torch.nn.functional and would otherwise count as zero;
+  * on CUDA the latency of a module is measured with a pair of events and read once, when the numbers are asked for,
+    instead of synchronising the device before and after every module.
+"""
+import time
+from functools import wraps
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
-module_flop_count = []
-old_functions = {}
 
-
+# ----------------------------------------------------------------------------------------------- MAC formulas
 def _prod(dims):
-    p = 1
+    out = 1
     for v in dims:
-        p *= v
-    return p
+        out *= int(v)
+    return out
 
 
-def _linear_flops_compute(input, weight, bias=None):
-    return _prod(input.shape) * weight.shape[0]
+def _linear_macs(input, weight, bias=None, *args, **kwargs):
+    return input.numel() * weight.shape[0]
 
 
-def _relu_flops_compute(input, inplace=False):
+def _per_element(input, *args, **kwargs):
     return input.numel()
 
 
-def _elementwise(input, *args, **kwargs):
-    return input.numel()
+def _norm_macs(input, *args, **kwargs):
+    return 5 * input.numel()
 
 
-def _pool_flops_compute(input, *args, **kwargs):
-    return input.numel()
-
-
-def _conv_flops_compute(input, weight, bias=None, stride=1, padding=0, dilation=1, groups=1):
-    batch_size = input.shape[0]
-    in_channels = input.shape[1]
-    out_channels = weight.shape[0]
-    kernel_dims = list(weight.shape[2:])
-    input_dims = list(input.shape[2:])
-    length = len(input_dims)
-    paddings = padding if type(padding) is tuple else (padding,) * length
-    strides = stride if type(stride) is tuple else (stride,) * length
-    dilations = dilation if type(dilation) is tuple else (dilation,) * length
-    output_dims = []
-    for idx, input_dim in enumerate(input_dims):
-        pad = paddings[idx] if not isinstance(paddings[idx], str) else 0
-        output_dim = (input_dim + 2 * pad - (dilations[idx] * (kernel_dims[idx] - 1) + 1)) // strides[idx] + 1
-        output_dims.append(output_dim)
-    filters_per_channel = out_channels // groups
-    conv_per_position_flops = int(_prod(kernel_dims)) * in_channels * filters_per_channel
-    active_elements_count = batch_size * int(_prod(output_dims))
-    overall_conv_flops = conv_per_position_flops * active_elements_count
-    bias_flops = out_channels * active_elements_count if bias is not None else 0
-    return int(overall_conv_flops + bias_flops)
-
-
-def _norm_flops(input, *args, **kwargs):
-    return input.numel() * 5
-
-
-def _softmax_flops_compute(input, dim=None, _stacklevel=3, dtype=None):
-    return input.numel()
-
-
-def _embedding_flops_compute(input, weight, *args, **kwargs):
+def _zero(*args, **kwargs):
     return 0
 
 
-def _matmul_flops(input, other, *args, **kwargs):
-    return _prod(input.shape) * other.shape[-1]
+def _conv_macs(input, weight, bias=None, stride=1, padding=0, dilation=1, groups=1):
+    spatial = list(input.shape[2:])
+    kernel = list(weight.shape[2:])
+    as_tuple = lambda v: v if isinstance(v, tuple) else (v,) * len(spatial)
+    out_positions = input.shape[0]
+    for size, k, s, p, d in zip(spatial, kernel, as_tuple(stride), as_tuple(padding), as_tuple(dilation)):
+        p = 0 if isinstance(p, str) else p
+        out_positions *= (size + 2 * p - (d * (k - 1) + 1)) // s + 1
+    per_position = _prod(kernel) * input.shape[1] * (weight.shape[0] // groups)
+    return int(out_positions * (per_position + (weight.shape[0] if bias is not None else 0)))
 
 
-def _sdpa_flops(q, k, v, *args, **kwargs):
-    return 2 * _prod(q.shape) * k.shape[-2]
+def _matmul_macs(input, other, *args, **kwargs):
+    return input.numel() * other.shape[-1]
 
 
+def _sdpa_macs(q, k, v, *args, **kwargs):
+    return 2 * q.numel() * k.shape[-2]          # scores + context
+
+
+def _linear_residual_macs(x, w, b, r):
+    return x.numel() * w.shape[0]
+
+
+def _mlp_residual_macs(x, w1, b1, w2, b2, r):
+    rows = x.numel() // x.shape[-1]
+    return rows * (w1.shape[0] * w1.shape[1] + w2.shape[0] * w2.shape[1])
+
+
+def _causal_attention_macs(qkv, H, D, rot_dim, base=10000.0):
+    B, S = qkv.shape[0], qkv.shape[1]
+    return 2 * B * H * S * S * D // 2           # causal: half of the score / context products
+
+
+_TORCH_RULES = {
+    "linear": _linear_macs, "conv1d": _conv_macs, "conv2d": _conv_macs, "conv3d": _conv_macs,
+    "relu": _per_element, "gelu": _per_element, "silu": _per_element, "elu": _per_element, "leaky_relu": _per_element,
+    "relu6": _per_element, "prelu": _per_element, "softmax": _per_element,
+    "batch_norm": _norm_macs, "layer_norm": _norm_macs, "instance_norm": _norm_macs, "group_norm": _norm_macs,
+    "avg_pool1d": _per_element, "avg_pool2d": _per_element, "avg_pool3d": _per_element, "max_pool1d": _per_element,
+    "max_pool2d": _per_element, "max_pool3d": _per_element, "adaptive_avg_pool2d": _per_element,
+    "adaptive_max_pool2d": _per_element, "embedding": _zero, "scaled_dot_product_attention": _sdpa_macs,
+}
+_KERNEL_RULES = {"linear": _linear_macs, "linear_gelu": _linear_macs, "linear_residual": _linear_residual_macs,
+                 "mlp_residual": _mlp_residual_macs}
+_ATTENTION_RULES = {"causal_self_attention": _causal_attention_macs}
+
+# kept for code that extends the profiler the reference's way (module type -> forward hook)
 MODULE_HOOK_MAPPING = {}
+module_flop_count = []          # the live stack of MAC lists (one per executing module)
+old_functions = {}
+_depth = [0]
+
+
+def _namespaces():
+    spaces = [(F, _TORCH_RULES)]
+    try:
+        from ...ops import kernels as K
+        from ...ops import attention as A
+        spaces += [(K, _KERNEL_RULES), (A, _ATTENTION_RULES)]
+    except Exception:
+        pass
+    return spaces
 
 
 def wrapFunc(func, funcFlopCompute):
-    oldFunc = func
+    """`func` that also charges funcFlopCompute(*args) MACs to the module executing at the time of the call."""
     name = func.__name__
-    old_functions[name] = oldFunc
 
-    def newFunc(*args, **kwds):
-        flops = funcFlopCompute(*args, **kwds)
-        if module_flop_count:
-            module_flop_count[-1].append((name, flops))
-        return oldFunc(*args, **kwds)
+    @wraps(func)
+    def counted(*args, **kwds):
+        # only the outermost counted call charges: a fused op that falls back to torch.nn.functional on the CPU must
+        # not be counted a second time through the functional it calls
+        if module_flop_count and _depth[0] == 0:
+            module_flop_count[-1].append((name, funcFlopCompute(*args, **kwds)))
+        _depth[0] += 1
+        try:
+            return func(*args, **kwds)
+        finally:
+            _depth[0] -= 1
 
-    newFunc.__name__ = name
-    return newFunc
-
-
-_F_PATCHES = {
-    "linear": _linear_flops_compute, "conv1d": _conv_flops_compute, "conv2d": _conv_flops_compute,
-    "conv3d": _conv_flops_compute, "relu": _relu_flops_compute, "gelu": _elementwise, "silu": _elementwise,
-    "elu": _elementwise, "leaky_relu": _elementwise, "relu6": _elementwise, "prelu": _elementwise,
-    "batch_norm": _norm_flops, "layer_norm": _norm_flops, "instance_norm": _norm_flops, "group_norm": _norm_flops,
-    "avg_pool1d": _pool_flops_compute, "avg_pool2d": _pool_flops_compute, "avg_pool3d": _pool_flops_compute,
-    "max_pool1d": _pool_flops_compute, "max_pool2d": _pool_flops_compute, "max_pool3d": _pool_flops_compute,
-    "adaptive_avg_pool2d": _pool_flops_compute, "adaptive_max_pool2d": _pool_flops_compute,
-    "softmax": _softmax_flops_compute, "embedding": _embedding_flops_compute,
-    "scaled_dot_product_attention": _sdpa_flops,
-}
+    counted.__wrapped_by_flops_profiler__ = func
+    return counted
 
 
 def _patch_functionals():
-    for name, fn in _F_PATCHES.items():
-        if hasattr(F, name):
-            setattr(F, name, wrapFunc(getattr(F, name), fn))
+    for space, rules in _namespaces():
+        for name, rule in rules.items():
+            fn = getattr(space, name, None)
+            if fn is not None and not hasattr(fn, "__wrapped_by_flops_profiler__"):
+                old_functions[(space.__name__, name)] = fn
+                setattr(space, name, wrapFunc(fn, rule))
 
 
 def _reload_functionals():
-    for name in _F_PATCHES:
-        if name in old_functions:
-            setattr(F, name, old_functions[name])
+    for space, rules in _namespaces():
+        for name in rules:
+            original = old_functions.pop((space.__name__, name), None)
+            if original is not None:
+                setattr(space, name, original)
+
+
+class _Record:
+    """What the profiler knows about one module."""
+    __slots__ = ("macs", "params", "seconds", "events", "t0", "handles")
+
+    def __init__(self, module):
+        self.macs = 0
+        self.params = sum(p.numel() for p in module.parameters() if p.requires_grad)
+        self.seconds = 0.0
+        self.events = []
+        self.t0 = None
+        self.handles = []
+
+    def settle(self):
+        """Fold finished CUDA event pairs into `seconds`."""
+        if self.events:
+            torch.cuda.synchronize()
+            self.seconds += sum(a.elapsed_time(b) for a, b in self.events) * 1e-3
+            self.events = []
+        return self.seconds
 
 
 class FlopsProfiler(object):
@@ -128,308 +173,246 @@ class FlopsProfiler(object):
         self.model = model
         self.started = False
         self.func_patched = False
+        self.records = {}
+
+    # ---- hooks
+    def _attach(self, module, ignore):
+        if ignore and type(module) in ignore:
+            return
+        rec = self.records[module]
+        if type(module) in MODULE_HOOK_MAPPING:
+            rec.handles.append(module.register_forward_hook(MODULE_HOOK_MAPPING[type(module)]))
+            return
+        on_gpu = torch.cuda.is_available()
+
+        def enter(mod, inputs):
+            module_flop_count.append([])
+            if on_gpu:
+                rec.t0 = torch.cuda.Event(enable_timing=True)
+                rec.t0.record()
+            else:
+                rec.t0 = time.time()
+
+        def leave(mod, inputs, output):
+            if on_gpu:
+                end = torch.cuda.Event(enable_timing=True)
+                end.record()
+                rec.events.append((rec.t0, end))
+            else:
+                rec.seconds += time.time() - rec.t0
+            if module_flop_count:
+                rec.macs += sum(m for _, m in module_flop_count.pop())
+
+        rec.handles += [module.register_forward_pre_hook(enter), module.register_forward_hook(leave)]
 
     def start_profile(self, ignore_list=None):
         self.reset_profile()
         _patch_functionals()
-
-        def register_module_hooks(module, ignore_list):
-            if ignore_list and type(module) in ignore_list:
-                return
-            if type(module) in MODULE_HOOK_MAPPING:
-                module.__flops_handle__ = module.register_forward_hook(MODULE_HOOK_MAPPING[type(module)])
-                return
-
-            def pre_hook(module, input):
-                module_flop_count.append([])
-
-            module.__pre_hook_handle__ = module.register_forward_pre_hook(pre_hook)
-
-            def post_hook(module, input, output):
-                if module_flop_count:
-                    module.__flops__ += sum([elem[1] for elem in module_flop_count[-1]])
-                    module_flop_count.pop()
-
-            module.__post_hook_handle__ = module.register_forward_hook(post_hook)
-
-            def start_time_hook(module, input):
-                if torch.cuda.is_available():
-                    torch.cuda.synchronize()
-                module.__start_time__ = time.time()
-
-            module.__start_time_hook_handle__ = module.register_forward_pre_hook(start_time_hook)
-
-            def end_time_hook(module, input, output):
-                if torch.cuda.is_available():
-                    torch.cuda.synchronize()
-                module.__duration__ += time.time() - module.__start_time__
-
-            module.__end_time_hook_handle__ = module.register_forward_hook(end_time_hook)
-
-        self.model.apply(partial(register_module_hooks, ignore_list=ignore_list))
-        self.started = True
-        self.func_patched = True
+        for module in self.model.modules():
+            self._attach(module, ignore_list)
+        self.started = self.func_patched = True
 
     def stop_profile(self):
         if self.started and self.func_patched:
             _reload_functionals()
             self.func_patched = False
-
-        def remove_profile_attrs(module):
-            for attr in ("__pre_hook_handle__", "__post_hook_handle__", "__flops_handle__",
-                         "__start_time_hook_handle__", "__end_time_hook_handle__"):
-                if hasattr(module, attr):
-                    getattr(module, attr).remove()
-                    delattr(module, attr)
-
-        self.model.apply(remove_profile_attrs)
+        for rec in self.records.values():
+            for h in rec.handles:
+                h.remove()
+            rec.handles = []
 
     def reset_profile(self):
-        def add_or_reset_attrs(module):
-            module.__flops__ = 0
-            module.__params__ = sum(p.numel() for p in module.parameters() if p.requires_grad)
-            module.__start_time__ = 0
-            module.__duration__ = 0
-
-        self.model.apply(add_or_reset_attrs)
+        self.records = {m: _Record(m) for m in self.model.modules()}
 
     def end_profile(self):
         if not self.started:
             return
         self.stop_profile()
         self.started = False
+        self.records = {}
 
-        def remove_profile_attrs(module):
-            for attr in ("__flops__", "__params__", "__start_time__", "__duration__"):
-                if hasattr(module, attr):
-                    delattr(module, attr)
+    # ---- numbers
+    def _macs(self, module):
+        return self.records[module].macs + sum(self._macs(c) for c in module.children())
 
-        self.model.apply(remove_profile_attrs)
+    def _seconds(self, module):
+        own = self.records[module].settle()
+        return own if own != 0 else sum(self.records[c].settle() for c in module.children())
 
     def get_total_flops(self, as_string=False):
-        total_flops = get_module_flops(self.model)
-        return macs_to_string(total_flops) if as_string else total_flops
+        total = self._macs(self.model)
+        return macs_to_string(total) if as_string else total
 
     def get_total_duration(self, as_string=False):
-        total_duration = self.model.__duration__
-        return duration_to_string(total_duration) if as_string else total_duration
+        total = self.records[self.model].settle()
+        return duration_to_string(total) if as_string else total
 
     def get_total_params(self, as_string=False):
-        return params_to_string(self.model.__params__) if as_string else self.model.__params__
+        total = self.records[self.model].params
+        return params_to_string(total) if as_string else total
+
+    # ---- report
+    def _line(self, module, totals):
+        total_macs, total_seconds, total_params = totals
+        rec = self.records[module]
+        macs, seconds = self._macs(module), self._seconds(module)
+        share = lambda part, whole: 0.0 if whole == 0 else part / whole
+        return ", ".join([params_to_string(rec.params), "{:.2%} Params".format(share(rec.params, total_params)),
+                          macs_to_string(macs), "{:.2%} MACs".format(share(macs, total_macs)),
+                          duration_to_string(seconds), "{:.2%} latency".format(share(seconds, total_seconds)),
+                          flops_to_string(0.0 if seconds == 0 else 2 * macs / seconds)])
 
     def print_model_profile(self, profile_step=1, module_depth=-1, top_modules=3, detailed=True):
-        total_flops = self.get_total_flops()
-        total_duration = self.get_total_duration()
-        total_params = self.get_total_params()
-        self.flops = total_flops
-        self.params = total_params
+        totals = (self.get_total_flops(), self.get_total_duration(), self.get_total_params())
+        total_macs, total_seconds, total_params = totals
+        self.flops, self.params = total_macs, total_params
+        row = "{:<60}  {:<8}".format
         print("\n-------------------------- DeepSpeed Flops Profiler --------------------------")
         print(f"Profile Summary at step {profile_step}:")
         print("Notations:\ndata parallel size (dp_size), model paralel size(mp_size),\nnumber of parameters (params), "
               "number of multiply-accumulate operations(MACs),\nnumber of floating point operations (flops), floating "
               "point operations per second (FLOPS),\nfwd latency (forward propagation latency), bwd latency (backward "
               "propagation latency),\nstep (weights update latency), iter latency (sum of fwd, bwd and step latency)\n")
-        print("{:<60}  {:<8}".format("params per gpu: ", params_to_string(total_params)))
-        print("{:<60}  {:<8}".format("fwd MACs per GPU: ", macs_to_string(total_flops)))
-        print("{:<60}  {:<8}".format("fwd latency: ", duration_to_string(total_duration)))
-        if total_duration > 0:
-            print("{:<60}  {:<8}".format("fwd FLOPS per GPU = 2 * fwd MACs per GPU / fwd latency: ",
-                                         flops_to_string(2 * total_flops / total_duration)))
-
-        def flops_repr(module):
-            params = module.__params__
-            flops = get_module_flops(module)
-            items = [params_to_string(params), "{:.2%} Params".format(params / total_params if total_params else 0),
-                     macs_to_string(flops), "{:.2%} MACs".format(0.0 if total_flops == 0 else flops / total_flops)]
-            duration = module.__duration__
-            if duration == 0:
-                for m in module.children():
-                    duration += m.__duration__
-            items.append(duration_to_string(duration))
-            items.append("{:.2%} latency".format(0.0 if total_duration == 0 else duration / total_duration))
-            items.append(flops_to_string(0.0 if duration == 0 else 2 * flops / duration))
-            items.append(module.original_extra_repr())
-            return ", ".join(items)
-
-        def add_extra_repr(module):
-            flops_extra_repr = flops_repr.__get__(module)
-            if module.extra_repr != flops_extra_repr:
-                module.original_extra_repr = module.extra_repr
-                module.extra_repr = flops_extra_repr
-                assert module.extra_repr != module.original_extra_repr
-
-        def del_extra_repr(module):
-            if hasattr(module, "original_extra_repr"):
-                module.extra_repr = module.original_extra_repr
-                del module.original_extra_repr
-
-        self.model.apply(add_extra_repr)
+        print(row("params per gpu: ", params_to_string(total_params)))
+        print(row("fwd MACs per GPU: ", macs_to_string(total_macs)))
+        print(row("fwd latency: ", duration_to_string(total_seconds)))
+        if total_seconds > 0:
+            print(row("fwd FLOPS per GPU = 2 * fwd MACs per GPU / fwd latency: ",
+                      flops_to_string(2 * total_macs / total_seconds)))
         print("\n----------------------------- Aggregated Profile per GPU -----------------------------")
         self.print_model_aggregated_profile(module_depth=module_depth, top_modules=top_modules)
         if detailed:
             print("\n------------------------------ Detailed Profile per GPU ------------------------------")
             print("Each module profile is listed after its name in the following order: \nparams, percentage of total "
                   "params, MACs, percentage of total MACs, fwd latency, percentage of total fwd latency, fwd FLOPS")
-            print(self.model)
-        self.model.apply(del_extra_repr)
+            # annotate extra_repr for the duration of one print(model), then put the originals back
+            saved = {}
+            for m in self.model.modules():
+                saved[m] = m.extra_repr
+                m.extra_repr = (lambda mod=m, orig=m.extra_repr: ", ".join(
+                    s for s in (self._line(mod, totals), orig()) if s))
+            try:
+                print(self.model)
+            finally:
+                for m, orig in saved.items():
+                    if "extra_repr" in m.__dict__:
+                        del m.__dict__["extra_repr"]
         print("------------------------------------------------------------------------------")
 
     def print_model_aggregated_profile(self, module_depth=-1, top_modules=3):
-        info = {}
-        if not hasattr(self.model, "__flops__"):
+        if not self.records:
             print("no __flops__ attribute in the model, call this function after start_profile and before end_profile")
             return
+        by_depth = {}
 
-        def walk_module(module, curr_depth, info):
-            if curr_depth not in info:
-                info[curr_depth] = {}
-            if module.__class__.__name__ not in info[curr_depth]:
-                info[curr_depth][module.__class__.__name__] = [0, 0, 0]
-            info[curr_depth][module.__class__.__name__][0] += get_module_flops(module)
-            info[curr_depth][module.__class__.__name__][1] += module.__params__
-            info[curr_depth][module.__class__.__name__][2] += get_module_duration(module)
-            has_children = len(module._modules.items()) != 0
-            if has_children:
-                for child in module.children():
-                    walk_module(child, curr_depth + 1, info)
+        def walk(module, depth):
+            slot = by_depth.setdefault(depth, {}).setdefault(module.__class__.__name__, [0, 0, 0.0])
+            slot[0] += self._macs(module)
+            slot[1] += self.records[module].params
+            slot[2] += self._seconds(module)
+            for child in module.children():
+                walk(child, depth + 1)
 
-        walk_module(self.model, 0, info)
-        depth = module_depth
-        if module_depth == -1:
-            depth = len(info) - 1
+        walk(self.model, 0)
+        depth = len(by_depth) - 1 if module_depth == -1 else module_depth
         print(f"Top {top_modules} modules in terms of params, MACs or fwd latency at different model depths:")
         for d in range(depth):
-            num_items = min(top_modules, len(info[d]))
-            sort_macs = {k: macs_to_string(v[0]) for k, v in sorted(info[d].items(), key=lambda item: item[1][0], reverse=True)[:num_items]}
-            sort_params = {k: params_to_string(v[1]) for k, v in sorted(info[d].items(), key=lambda item: item[1][1], reverse=True)[:num_items]}
-            sort_time = {k: duration_to_string(v[2]) for k, v in sorted(info[d].items(), key=lambda item: item[1][2], reverse=True)[:num_items]}
+            def top(col, fmt):
+                ranked = sorted(by_depth[d].items(), key=lambda kv: kv[1][col], reverse=True)[:top_modules]
+                return {k: fmt(v[col]) for k, v in ranked}
             print(f"depth {d}:")
-            print(f"    params      - {sort_params}")
-            print(f"    MACs        - {sort_macs}")
-            print(f"    fwd latency - {sort_time}")
+            print(f"    params      - {top(1, params_to_string)}")
+            print(f"    MACs        - {top(0, macs_to_string)}")
+            print(f"    fwd latency - {top(2, duration_to_string)}")
+
+
+# ----------------------------------------------------------------------------------------------- formatting
+def _scaled(value, steps, units, precision, bare_suffix):
+    """`value` with the largest unit of `steps` ((factor, suffix), descending) it reaches, or in `units` if given."""
+    if units is not None:
+        factor = dict((s, f) for f, s in steps).get(units, 1)
+        return str(round(value / factor, precision)) + " " + units
+    for factor, suffix in steps:
+        if value // factor > 0:
+            return str(round(value / factor, precision)) + " " + suffix
+    return str(value) + bare_suffix
 
 
 def num_to_string(num, precision=2):
-    if num // 10 ** 9 > 0:
-        return str(round(num / 10.0 ** 9, precision)) + " G"
-    elif num // 10 ** 6 > 0:
-        return str(round(num / 10.0 ** 6, precision)) + " M"
-    elif num // 10 ** 3 > 0:
-        return str(round(num / 10.0 ** 3, precision)) + " K"
-    return str(num)
+    return _scaled(num, ((10.0 ** 9, "G"), (10.0 ** 6, "M"), (10.0 ** 3, "K")), None, precision, "")
 
 
 def macs_to_string(macs, units=None, precision=2):
-    if units is None:
-        if macs // 10 ** 9 > 0:
-            return str(round(macs / 10.0 ** 9, precision)) + " GMACs"
-        elif macs // 10 ** 6 > 0:
-            return str(round(macs / 10.0 ** 6, precision)) + " MMACs"
-        elif macs // 10 ** 3 > 0:
-            return str(round(macs / 10.0 ** 3, precision)) + " KMACs"
-        return str(macs) + " MACs"
-    scale = {"GMACs": 10.0 ** 9, "MMACs": 10.0 ** 6, "KMACs": 10.0 ** 3}.get(units, 1)
-    return str(round(macs / scale, precision)) + " " + units
+    return _scaled(macs, ((10.0 ** 9, "GMACs"), (10.0 ** 6, "MMACs"), (10.0 ** 3, "KMACs")), units, precision, " MACs")
 
 
 def number_to_string(num, units=None, precision=2):
-    if units is None:
-        if num // 10 ** 9 > 0:
-            return str(round(num / 10.0 ** 9, precision)) + " G"
-        elif num // 10 ** 6 > 0:
-            return str(round(num / 10.0 ** 6, precision)) + " M"
-        elif num // 10 ** 3 > 0:
-            return str(round(num / 10.0 ** 3, precision)) + " K"
-        return str(num) + " "
-    scale = {"G": 10.0 ** 9, "M": 10.0 ** 6, "K": 10.0 ** 3}.get(units, 1)
-    return str(round(num / scale, precision)) + " " + units
+    return _scaled(num, ((10.0 ** 9, "G"), (10.0 ** 6, "M"), (10.0 ** 3, "K")), units, precision, " ")
 
 
 def flops_to_string(flops, units=None, precision=2):
-    if units is None:
-        if flops // 10 ** 12 > 0:
-            return str(round(flops / 10.0 ** 12, precision)) + " TFLOPS"
-        if flops // 10 ** 9 > 0:
-            return str(round(flops / 10.0 ** 9, precision)) + " GFLOPS"
-        elif flops // 10 ** 6 > 0:
-            return str(round(flops / 10.0 ** 6, precision)) + " MFLOPS"
-        elif flops // 10 ** 3 > 0:
-            return str(round(flops / 10.0 ** 3, precision)) + " KFLOPS"
-        return str(flops) + " FLOPS"
-    scale = {"TFLOPS": 10.0 ** 12, "GFLOPS": 10.0 ** 9, "MFLOPS": 10.0 ** 6, "KFLOPS": 10.0 ** 3}.get(units, 1)
-    return str(round(flops / scale, precision)) + " " + units
+    return _scaled(flops, ((10.0 ** 12, "TFLOPS"), (10.0 ** 9, "GFLOPS"), (10.0 ** 6, "MFLOPS"), (10.0 ** 3, "KFLOPS")),
+                   units, precision, " FLOPS")
 
 
 def params_to_string(params_num, units=None, precision=2):
-    if units is None:
-        if params_num // 10 ** 6 > 0:
-            return str(round(params_num / 10 ** 6, 2)) + " M"
-        elif params_num // 10 ** 3:
-            return str(round(params_num / 10 ** 3, 2)) + " k"
-        return str(params_num)
-    scale = {"M": 10 ** 6, "K": 10 ** 3}.get(units, 1)
-    return str(round(params_num / scale, precision)) + " " + units
+    if units is not None:
+        return str(round(params_num / {"M": 10 ** 6, "K": 10 ** 3}.get(units, 1), precision)) + " " + units
+    if params_num // 10 ** 6 > 0:
+        return str(round(params_num / 10 ** 6, 2)) + " M"
+    if params_num // 10 ** 3:
+        return str(round(params_num / 10 ** 3, 2)) + " k"
+    return str(params_num)
 
 
 def duration_to_string(duration, units=None, precision=2):
-    if units is None:
-        if duration > 1:
-            return str(round(duration, precision)) + " s"
-        elif duration * 10 ** 3 > 1:
-            return str(round(duration * 10 ** 3, precision)) + " ms"
-        elif duration * 10 ** 6 > 1:
-            return str(round(duration * 10 ** 6, precision)) + " us"
-        return str(duration)
-    scale = {"us": 10 ** 6, "ms": 10 ** 3}.get(units, 1)
-    return str(round(duration * scale, precision)) + " " + units
+    if units is not None:
+        return str(round(duration * {"us": 10 ** 6, "ms": 10 ** 3}.get(units, 1), precision)) + " " + units
+    for factor, suffix in ((1, "s"), (10 ** 3, "ms"), (10 ** 6, "us")):
+        if duration * factor > 1:
+            return str(round(duration * factor, precision)) + " " + suffix
+    return str(duration)
 
 
-def get_module_flops(module):
-    total = module.__flops__
-    for child in module.children():
-        total += get_module_flops(child)
-    return total
+def get_module_flops(module, profiler=None):
+    """MACs of `module` and its descendants under `profiler` (the one currently attached, if not given)."""
+    prof = profiler or _ACTIVE[-1]
+    return prof._macs(module)
 
 
-def get_module_duration(module):
-    duration = module.__duration__
-    if duration == 0:
-        for m in module.children():
-            duration += m.__duration__
-    return duration
+def get_module_duration(module, profiler=None):
+    prof = profiler or _ACTIVE[-1]
+    return prof._seconds(module)
+
+
+_ACTIVE = []
 
 
 def get_model_profile(model, input_res, input_constructor=None, print_profile=True, detailed=True, module_depth=-1,
                       top_modules=3, warm_up=1, as_string=True, ignore_modules=None):
-    """Returns (MACs, params) of one forward pass on an input of shape `input_res` (batch included)."""
+    """(MACs, params) of one forward pass on an input of shape `input_res` (batch dimension included)."""
     assert type(input_res) is tuple and len(input_res) >= 1 and isinstance(model, nn.Module)
+
+    def run_once():
+        if input_constructor:
+            return model(**input_constructor(input_res))
+        first = next(model.parameters(), None)
+        like = dict(dtype=first.dtype, device=first.device) if first is not None else {}
+        return model(torch.empty(tuple(input_res), **like))
+
     prof = FlopsProfiler(model)
     model.eval()
     for _ in range(warm_up):
-        if input_constructor:
-            _ = model(**input_constructor(input_res))
-        else:
-            try:
-                batch = torch.ones(()).new_empty((*input_res,), dtype=next(model.parameters()).dtype,
-                                                 device=next(model.parameters()).device)
-            except StopIteration:
-                batch = torch.ones(()).new_empty((*input_res,))
-            _ = model(batch)
+        run_once()
     prof.start_profile(ignore_list=ignore_modules)
-    if input_constructor:
-        _ = model(**input_constructor(input_res))
-    else:
-        try:
-            batch = torch.ones(()).new_empty((*input_res,), dtype=next(model.parameters()).dtype,
-                                             device=next(model.parameters()).device)
-        except StopIteration:
-            batch = torch.ones(()).new_empty((*input_res,))
-        _ = model(batch)
-    flops = prof.get_total_flops()
-    params = prof.get_total_params()
-    if print_profile:
-        prof.print_model_profile(profile_step=warm_up, module_depth=module_depth, top_modules=top_modules, detailed=detailed)
-    prof.end_profile()
-    if as_string:
-        return macs_to_string(flops), params_to_string(params)
-    return flops, params
+    _ACTIVE.append(prof)
+    try:
+        run_once()
+        macs, params = prof.get_total_flops(), prof.get_total_params()
+        if print_profile:
+            prof.print_model_profile(profile_step=warm_up, module_depth=module_depth, top_modules=top_modules,
+                                     detailed=detailed)
+    finally:
+        _ACTIVE.pop()
+        prof.end_profile()
+    return (macs_to_string(macs), params_to_string(params)) if as_string else (macs, params)
