@@ -30,6 +30,7 @@ from .fp16.unfused_optimizer import FP16_UnfusedOptimizer
 from .progressive_layer_drop import ProgressiveLayerDrop
 from . import lr_schedules
 from . import utils as ds_utils
+from . import optimizer_factory
 from .engine_train import TrainStepMixin, _get_global_rank, is_zero_supported_optimizer, split_half_float_double_csr
 from .engine_checkpoint import CheckpointMixin
 
@@ -231,25 +232,19 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         return self._config.tensorboard_job_name
 
     def get_summary_writer(self, name="DeepSpeedJobName", base=os.path.join(os.path.expanduser("~"), "tensorboard")):
+        """TensorBoard writer under <output_path>/<job_name>, or (no output path configured)
+        ~/tensorboard/<cluster job id>/logs/<job name>."""
         if _SummaryWriter is None:
             logger.warning("tensorboard is not installed; tensorboard logging disabled")
             self._config.tensorboard_enabled = False
             return None
+        job = self.tensorboard_job_name()
         if self.tensorboard_output_path():
-            base_dir = self.tensorboard_output_path()
-            job_name = self.tensorboard_job_name()
-            log_dir = os.path.join(base_dir, job_name)
+            log_dir = os.path.join(self.tensorboard_output_path(), job)
         else:
-            if self.tensorboard_job_name():
-                name = self.tensorboard_job_name()
-            if "DLWS_JOB_ID" in os.environ:
-                infra_job_id = os.environ["DLWS_JOB_ID"]
-            elif "DLTS_JOB_ID" in os.environ:
-                infra_job_id = os.environ["DLTS_JOB_ID"]
-            else:
-                infra_job_id = "unknown-job-id"
-            summary_writer_dir_name = os.path.join(infra_job_id, "logs")
-            log_dir = os.path.join(base, summary_writer_dir_name, name)
+            cluster_job = next((os.environ[k] for k in ("DLWS_JOB_ID", "DLTS_JOB_ID") if k in os.environ),
+                               "unknown-job-id")
+            log_dir = os.path.join(base, cluster_job, "logs", job or name)
         os.makedirs(log_dir, exist_ok=True)
         return _SummaryWriter(log_dir=log_dir)
 
@@ -476,16 +471,19 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         self._config = DeepSpeedConfig(config_file, mpu, param_dict=self.config_params)
 
     def _do_args_sanity_check(self, args):
-        if hasattr(args, "deepscale_config") and args.deepscale_config is not None:
+        """`--deepscale_config` is the pre-rename spelling of `--deepspeed_config`; without `config_params` a config
+        file must be named and exist."""
+        legacy = getattr(args, "deepscale_config", None)
+        if legacy is not None:
             logger.warning("************ --deepscale_config is deprecated, please use --deepspeed_config ************")
-            if hasattr(args, "deepspeed_config"):
-                assert args.deepspeed_config is None, "Not sure how to proceed, we were given both a deepscale_config and deepspeed_config"
-            args.deepspeed_config = args.deepscale_config
-        if self.config_params is None:
-            assert args is not None and hasattr(args, "deepspeed_config") and args.deepspeed_config is not None, \
-                "DeepSpeed requires --deepspeed_config to specify configuration file"
-            assert os.path.isfile(args.deepspeed_config), \
-                "DeepSpeed configuration file: {} is not an existing file".format(args.deepspeed_config)
+            assert getattr(args, "deepspeed_config", None) is None, \
+                "Not sure how to proceed, we were given both a deepscale_config and deepspeed_config"
+            args.deepspeed_config = legacy
+        if self.config_params is not None:
+            return
+        path = getattr(args, "deepspeed_config", None) if args is not None else None
+        assert path is not None, "DeepSpeed requires --deepspeed_config to specify configuration file"
+        assert os.path.isfile(path), "DeepSpeed configuration file: {} is not an existing file".format(path)
 
     def _is_supported_optimizer(self, optimizer_name):
         return optimizer_name in C.DEEPSPEED_OPTIMIZERS or getattr(torch.optim, optimizer_name, None) is not None
@@ -530,158 +528,47 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         if not self.amp_enabled():
             self._broadcast_model()
 
-    # ------------------------------------------------------------------ optimizer wiring
+    # ------------------------------------------------------------------ optimizer wiring (runtime/optimizer_factory.py)
     def _configure_optimizer(self, client_optimizer, model_parameters):
-        if client_optimizer is not None:
+        """basic optimizer (client's, or built from the config) -> ZeRO stage | reduced-precision wrapper | as is."""
+        if client_optimizer is None:
+            basic = self._configure_basic_optimizer(model_parameters)
+            origin = "DeepSpeed Optimizer param name {}".format(self.optimizer_name())
+        else:
             if callable(client_optimizer) and not isinstance(client_optimizer, torch.optim.Optimizer):
                 client_optimizer = client_optimizer(model_parameters)
-            client_optimizer.param_groups[:] = [pg for pg in client_optimizer.param_groups if len(pg["params"]) != 0]
-            basic_optimizer = client_optimizer
-            if self.global_rank == 0:
-                logger.info("Using client Optimizer as basic optimizer")
-        else:
-            basic_optimizer = self._configure_basic_optimizer(model_parameters)
-            if self.global_rank == 0:
-                logger.info("Using DeepSpeed Optimizer param name {} as basic optimizer".format(self.optimizer_name()))
+            client_optimizer.param_groups[:] = [g for g in client_optimizer.param_groups if len(g["params"]) != 0]
+            basic, origin = client_optimizer, "client Optimizer"
         if self.global_rank == 0:
-            logger.info("DeepSpeed Basic Optimizer = {}".format(basic_optimizer.__class__.__name__))
+            logger.info(f"Using {origin} as basic optimizer")
+            logger.info("DeepSpeed Basic Optimizer = {}".format(basic.__class__.__name__))
 
         if self.zero_optimization():
-            assert not self.amp_enabled(), "Amp and ZeRO are not currently compatible, please use (legacy) fp16 mode which performs similar to amp opt_mode=O2"
-            if not is_zero_supported_optimizer(basic_optimizer):
-                assert self.zero_allow_untested_optimizer(), \
-                    'You are using an untested ZeRO Optimizer. Please add <"zero_allow_untested_optimizer": true> in the configuration file to use it.'
+            assert not self.amp_enabled(), "Amp and ZeRO are not currently compatible, please use (legacy) fp16 mode " \
+                "which performs similar to amp opt_mode=O2"
+            if not is_zero_supported_optimizer(basic):
+                assert self.zero_allow_untested_optimizer(), 'You are using an untested ZeRO Optimizer. Please add ' \
+                    '<"zero_allow_untested_optimizer": true> in the configuration file to use it.'
                 if self.global_rank == 0:
                     logger.warning("**** You are using ZeRO with an untested optimizer, proceed with caution *****")
-            self.optimizer = self._configure_zero_optimizer(basic_optimizer)
+            self.optimizer = self._configure_zero_optimizer(basic)
         elif self.amp_enabled():
             raise RuntimeError("apex AMP is not available in this environment; use the fp16 block (fp16 or bfloat16) "
                                "which gives the O2-style master-weight regime")
         elif self.fp16_enabled() and self.precision() != torch.float32:
-            self.optimizer = self._configure_fp16_optimizer(basic_optimizer)
+            self.optimizer = self._configure_fp16_optimizer(basic)
         else:
-            self.optimizer = basic_optimizer
+            self.optimizer = basic
         log_dist("DeepSpeed Final Optimizer = {}".format(self.optimizer_name()), ranks=[0])
 
     def _configure_basic_optimizer(self, model_parameters):
-        optimizer_parameters = dict(self.optimizer_params() or {})
-        if "max_grad_norm" in optimizer_parameters:
-            raise ValueError("'max_grad_norm' is not supported as an optimizer parameter, please switch to using the "
-                             "deepspeed parameter 'gradient_clipping' see: "
-                             "https://www.deepspeed.ai/docs/config-json/#gradient-clipping for more details")
-        name = self.optimizer_name()
-        if name in (C.ADAM_OPTIMIZER, C.ADAMW_OPTIMIZER):
-            torch_adam = optimizer_parameters.pop(C.TORCH_ADAM_PARAM, False)
-            adam_w_mode = optimizer_parameters.pop(C.ADAM_W_MODE, C.ADAM_W_MODE_DEFAULT)
-            # "adamw" always means decoupled decay; "adam" follows adam_w_mode (default True, as in the reference)
-            effective_adam_w_mode = name == C.ADAMW_OPTIMIZER or adam_w_mode
-            if torch_adam:
-                if not effective_adam_w_mode:
-                    optimizer = torch.optim.Adam(model_parameters, **optimizer_parameters)
-                else:
-                    optimizer = torch.optim.AdamW(model_parameters, **optimizer_parameters)
-            elif self.zero_cpu_offload():
-                from ..ops.adam import DeepSpeedCPUAdam
-                optimizer = DeepSpeedCPUAdam(model_parameters, **optimizer_parameters, adamw_mode=effective_adam_w_mode)
-            else:
-                from ..ops.adam import FusedAdam
-                optimizer = FusedAdam(model_parameters, **optimizer_parameters, adam_w_mode=effective_adam_w_mode)
-        elif name == C.LAMB_OPTIMIZER:
-            from ..ops.lamb import FusedLamb
-            optimizer = FusedLamb(model_parameters, **optimizer_parameters)
-        elif name == C.ONEBIT_ADAM_OPTIMIZER:
-            from .fp16.onebit.adam import OnebitAdam
-            optimizer = OnebitAdam(model_parameters, self, **optimizer_parameters)
-            if not self.fp16_enabled():
-                logger.warning("Currently the convergence of 1-bit Adam is only verified under FP16")
-        elif name == C.ONEBIT_LAMB_OPTIMIZER:
-            from .fp16.onebit.lamb import OnebitLamb
-            optimizer = OnebitLamb(model_parameters, self, **optimizer_parameters)
-            if not self.fp16_enabled():
-                logger.warning("Currently the convergence of 1-bit Lamb is only verified under FP16")
-        else:
-            torch_optimizer = getattr(torch.optim, name)
-            optimizer = torch_optimizer(model_parameters, **optimizer_parameters)
-        return optimizer
+        return optimizer_factory.build_basic_optimizer(self, model_parameters)
 
     def _configure_fp16_optimizer(self, optimizer):
-        initial_dynamic_scale = self.initial_dynamic_scale()
-        dynamic_loss_args = self.dynamic_loss_scale_args()
-        clip_grad = self.gradient_clipping()
-        from ..ops.adam import FusedAdam
-        is_bf16 = self.precision() == torch.bfloat16
-        if isinstance(optimizer, FusedAdam) or self.optimizer_name() == C.ONEBIT_ADAM_OPTIMIZER:
-            if self.dynamic_loss_scale() and not is_bf16:
-                log_dist("Creating fp16 optimizer with dynamic loss scale", ranks=[0])
-                optimizer = FP16_Optimizer(optimizer, dynamic_loss_scale=True, initial_dynamic_scale=initial_dynamic_scale,
-                                           dynamic_loss_args=dynamic_loss_args, mpu=self.mpu, clip_grad=clip_grad,
-                                           fused_adam_legacy=self.optimizer_legacy_fusion(), timers=None,
-                                           dp_process_group=self.data_parallel_group,
-                                           fp32_allreduce=self.allreduce_always_fp32())
-            else:
-                log_dist("Creating fp16 optimizer with static loss scale: {}".format(self.loss_scale()), ranks=[0])
-                optimizer = FP16_Optimizer(optimizer, static_loss_scale=1.0 if is_bf16 else self.loss_scale(),
-                                           mpu=self.mpu, clip_grad=clip_grad,
-                                           fused_adam_legacy=self.optimizer_legacy_fusion(),
-                                           dp_process_group=self.data_parallel_group,
-                                           fp32_allreduce=self.allreduce_always_fp32())
-        else:
-            log_dist("Creating fp16 unfused optimizer with dynamic loss scale", ranks=[0])
-            optimizer = FP16_UnfusedOptimizer(optimizer, static_loss_scale=1.0 if is_bf16 else self.loss_scale(),
-                                              dynamic_loss_scale=self.dynamic_loss_scale() and not is_bf16,
-                                              dynamic_loss_args=dynamic_loss_args, mpu=self.mpu, clip_grad=clip_grad,
-                                              fused_lamb_legacy=self.optimizer_name() == C.LAMB_OPTIMIZER)
-        return optimizer
+        return optimizer_factory.wrap_for_reduced_precision(self, optimizer)
 
     def _configure_zero_optimizer(self, optimizer):
-        zero_stage = self.zero_optimization_stage()
-        log_dist("Creating fp16 ZeRO stage {} optimizer".format(zero_stage), ranks=[0])
-        assert not self.allreduce_always_fp32() or self.precision() == torch.bfloat16 or True
-        common = dict(static_loss_scale=self.loss_scale(), dynamic_loss_scale=self.dynamic_loss_scale(),
-                      dynamic_loss_args=self.dynamic_loss_scale_args(), clip_grad=self.gradient_clipping(),
-                      dp_process_group=self.data_parallel_group, mpu=self.mpu,
-                      elastic_checkpoint=self.zero_elastic_checkpoint(), precision=self.precision(),
-                      postscale_gradients=self.postscale_gradients(),
-                      gradient_predivide_factor=self.gradient_predivide_factor())
-        if zero_stage == C.ZERO_OPTIMIZATION_OPTIMIZER_STATES:
-            assert self.zero_reduce_scatter(), "Stage 1 only supports reduce scatter mode"
-            from .zero.stage1 import FP16_DeepSpeedZeroOptimizer_Stage1
-            optimizer = FP16_DeepSpeedZeroOptimizer_Stage1(
-                optimizer, all_gather_partitions=self.zero_allgather_partitions(),
-                allgather_size=self.zero_allgather_bucket_size(), max_elements_per_comm=self.zero_reduce_bucket_size(),
-                fp32_allreduce=self.allreduce_always_fp32() and self.precision() != torch.bfloat16,
-                fused_nvlink=self.zero_fused_nvlink(), **common)
-        elif zero_stage == C.ZERO_OPTIMIZATION_GRADIENTS:
-            from .zero.stage2 import FP16_DeepSpeedZeroOptimizer
-            off = self.zero_offload_optimizer()
-            optimizer = FP16_DeepSpeedZeroOptimizer(
-                optimizer, timers=self.timers, contiguous_gradients=self.zero_contiguous_gradients(),
-                reduce_bucket_size=self.zero_reduce_bucket_size(), allgather_bucket_size=self.zero_allgather_bucket_size(),
-                reduce_scatter=self.zero_reduce_scatter(), overlap_comm=self.zero_overlap_comm(),
-                cpu_offload=self.zero_cpu_offload(), pin_memory=True if off is None else (off.get("pin_memory", False) or True),
-                allreduce_always_fp32=self.allreduce_always_fp32() and self.precision() != torch.bfloat16,
-                gradient_accumulation_steps=self.gradient_accumulation_steps(),
-                fused_nvlink=self.zero_fused_nvlink(), **common)
-        elif zero_stage == C.ZERO_OPTIMIZATION_WEIGHTS:
-            from .zero.stage3 import FP16_DeepSpeedZeroOptimizer_Stage3
-            optimizer = FP16_DeepSpeedZeroOptimizer_Stage3(
-                self.module, optimizer, timers=self.timers, static_loss_scale=self.loss_scale(),
-                dynamic_loss_scale=self.dynamic_loss_scale(), dynamic_loss_args=self.dynamic_loss_scale_args(),
-                clip_grad=self.gradient_clipping(), contiguous_gradients=self.zero_contiguous_gradients(),
-                reduce_bucket_size=self.zero_reduce_bucket_size(), prefetch_bucket_size=self.zero_prefetch_bucket_size(),
-                max_reuse_distance=self.zero_max_reuse_distance(), max_live_parameters=self.zero_max_live_parameters(),
-                param_persistence_threshold=self.zero_param_persistence_threshold(),
-                dp_process_group=self.data_parallel_group, reduce_scatter=self.zero_reduce_scatter(),
-                overlap_comm=self.zero_overlap_comm(), offload_optimizer_config=self.zero_offload_optimizer(),
-                offload_param_config=self.zero_offload_param(), sub_group_size=self.zero_sub_group_size(),
-                mpu=self.mpu, postscale_gradients=self.postscale_gradients(),
-                gradient_predivide_factor=self.gradient_predivide_factor(),
-                gradient_accumulation_steps=self.gradient_accumulation_steps(), aio_config=self.aio_config(),
-                precision=self.precision(),
-                fused_allgather_gemm=bool(self._config.zero_config.stage3_fused_allgather_gemm) or None)
-        else:
-            raise NotImplementedError("ZeRO stage {} not implemented".format(zero_stage))
-        return optimizer
+        return optimizer_factory.wrap_for_zero(self, optimizer)
 
     def _configure_progressive_layer_drop(self):
         return ProgressiveLayerDrop(theta=self.pld_theta(), gamma=self.pld_gamma())
@@ -689,23 +576,22 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
     # ------------------------------------------------------------------ data
     def deepspeed_io(self, dataset, batch_size=None, route=C.ROUTE_TRAIN, pin_memory=True, data_sampler=None,
                      collate_fn=None, num_local_io_workers=None):
+        """A DeepSpeedDataLoader over `dataset` sharded by data-parallel rank (training), or read sequentially
+        (evaluation / prediction routes); training loaders feed the throughput timer."""
         if not isinstance(dataset, torch.utils.data.Dataset):
             raise ValueError("Training data must be a torch Dataset")
         if data_sampler is None and route in (C.ROUTE_PREDICT, C.ROUTE_EVAL):
             data_sampler = torch.utils.data.SequentialSampler(dataset)
-        if batch_size is None:
-            batch_size = self.train_micro_batch_size_per_gpu()
-        if collate_fn is None:
-            collate_fn = self.collate_fn
-        deepspeed_io_timer = self.tput_timer if route == C.ROUTE_TRAIN else None
         if self.mpu is not None:
-            dp_world, dp_rank = self.mpu.get_data_parallel_world_size(), self.mpu.get_data_parallel_rank()
+            replicas, my_replica = self.mpu.get_data_parallel_world_size(), self.mpu.get_data_parallel_rank()
         else:
-            dp_world, dp_rank = self.dp_world_size, dist.get_rank(group=self.data_parallel_group)
-        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory,
-                                   collate_fn=collate_fn, local_rank=self.local_rank, tput_timer=deepspeed_io_timer,
+            replicas, my_replica = self.dp_world_size, dist.get_rank(group=self.data_parallel_group)
+        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size or self.train_micro_batch_size_per_gpu(),
+                                   pin_memory=pin_memory, collate_fn=collate_fn or self.collate_fn,
+                                   local_rank=self.local_rank,
+                                   tput_timer=self.tput_timer if route == C.ROUTE_TRAIN else None,
                                    num_local_io_workers=num_local_io_workers, data_sampler=data_sampler,
-                                   data_parallel_world_size=dp_world, data_parallel_rank=dp_rank)
+                                   data_parallel_world_size=replicas, data_parallel_rank=my_replica)
 
     def train(self, mode=True):
         self.warn_unscaled_loss = True
@@ -716,18 +602,14 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         self.module.train(False)
 
     def _scale_loss(self, prescaled_loss):
+        """loss / gradient_accumulation_steps for a tensor or every tensor of a tuple / list (other types pass through
+        with one warning)."""
+        gas = self.gradient_accumulation_steps()
         if isinstance(prescaled_loss, torch.Tensor):
-            scaled_loss = prescaled_loss / self.gradient_accumulation_steps()
-        elif isinstance(prescaled_loss, (tuple, list)):
-            scaled_loss = []
-            for l in prescaled_loss:
-                if isinstance(l, torch.Tensor):
-                    scaled_loss.append(l / self.gradient_accumulation_steps())
-                else:
-                    scaled_loss.append(l)
-        else:
-            scaled_loss = prescaled_loss
-            if self.warn_unscaled_loss:
-                logger.warning(f"DeepSpeed unable to scale loss because of type: {type(prescaled_loss)}")
-                self.warn_unscaled_loss = False
-        return scaled_loss
+            return prescaled_loss / gas
+        if isinstance(prescaled_loss, (tuple, list)):
+            return [l / gas if isinstance(l, torch.Tensor) else l for l in prescaled_loss]
+        if self.warn_unscaled_loss:
+            logger.warning(f"DeepSpeed unable to scale loss because of type: {type(prescaled_loss)}")
+            self.warn_unscaled_loss = False
+        return prescaled_loss
