@@ -201,35 +201,11 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
     def get_batch_info(self):
         return self.train_batch_size, self.train_micro_batch_size_per_gpu, self.gradient_accumulation_steps
 
-    def checkpoint_tag_validation_enabled(self):
-        return self._config.checkpoint_tag_validation_enabled
-
-    def checkpoint_tag_validation_fail(self):
-        return self._config.checkpoint_tag_validation_fail
-
-    def elasticity_enabled(self):
-        return self._config.elasticity_enabled
-
-    def pld_enabled(self):
-        return self._config.pld_enabled
-
-    def pld_params(self):
-        return self._config.pld_params
-
     def pld_theta(self):
         return self.pld_params()[C.PLD_THETA]
 
     def pld_gamma(self):
         return self.pld_params()[C.PLD_GAMMA]
-
-    def tensorboard_enabled(self):
-        return self._config.tensorboard_enabled
-
-    def tensorboard_output_path(self):
-        return self._config.tensorboard_output_path
-
-    def tensorboard_job_name(self):
-        return self._config.tensorboard_job_name
 
     def get_summary_writer(self, name="DeepSpeedJobName", base=os.path.join(os.path.expanduser("~"), "tensorboard")):
         """TensorBoard writer under <output_path>/<job_name>, or (no output path configured)
@@ -248,83 +224,11 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         os.makedirs(log_dir, exist_ok=True)
         return _SummaryWriter(log_dir=log_dir)
 
-    def wall_clock_breakdown(self):
-        return self._config.wall_clock_breakdown
-
-    def flops_profiler_enabled(self):
-        return self._config.flops_profiler_config.enabled
-
-    def flops_profiler_profile_step(self):
-        return self._config.flops_profiler_config.profile_step
-
-    def flops_profiler_module_depth(self):
-        return self._config.flops_profiler_config.module_depth
-
-    def flops_profiler_top_modules(self):
-        return self._config.flops_profiler_config.top_modules
-
-    def flops_profiler_detailed(self):
-        return self._config.flops_profiler_config.detailed
-
-    def memory_breakdown(self):
-        return self._config.memory_breakdown
-
-    def sparse_gradients_enabled(self):
-        return self._config.sparse_gradients_enabled
-
-    def train_batch_size(self):
-        return self._config.train_batch_size
-
-    def train_micro_batch_size_per_gpu(self):
-        return self._config.train_micro_batch_size_per_gpu
-
     def optimizer_name(self):
         return self.client_optimizer.__class__.__name__ if self.client_optimizer else self._config.optimizer_name
 
-    def optimizer_params(self):
-        return self._config.optimizer_params
-
-    def optimizer_legacy_fusion(self):
-        return self._config.optimizer_legacy_fusion
-
-    def scheduler_name(self):
-        return self._config.scheduler_name
-
-    def scheduler_params(self):
-        return self._config.scheduler_params
-
-    def zero_optimization(self):
-        return self._config.zero_enabled
-
-    def zero_allow_untested_optimizer(self):
-        return self._config.zero_allow_untested_optimizer
-
-    def zero_reduce_scatter(self):
-        return self._config.zero_config.reduce_scatter
-
-    def zero_overlap_comm(self):
-        return self._config.zero_config.overlap_comm
-
-    def zero_offload_optimizer(self):
-        return self._config.zero_config.offload_optimizer
-
-    def zero_offload_param(self):
-        return self._config.zero_config.offload_param
-
     def zero_cpu_offload(self):
         return self._config.zero_config.offload_optimizer is not None
-
-    def zero_sub_group_size(self):
-        return self._config.zero_config.sub_group_size
-
-    def zero_optimization_stage(self):
-        return self._config.zero_optimization_stage
-
-    def zero_reduce_bucket_size(self):
-        return self._config.zero_config.reduce_bucket_size
-
-    def zero_allgather_bucket_size(self):
-        return self._config.zero_config.allgather_bucket_size
 
     def zero_optimization_partition_gradients(self):
         return self.zero_optimization_stage() >= C.ZERO_OPTIMIZATION_GRADIENTS
@@ -332,86 +236,17 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
     def zero_optimization_partition_weights(self):
         return self.zero_optimization_stage() >= C.ZERO_OPTIMIZATION_WEIGHTS
 
-    def zero_contiguous_gradients(self):
-        return self._config.zero_config.contiguous_gradients
-
-    def zero_load_from_fp32_weights(self):
-        return self._config.zero_config.load_from_fp32_weights
-
-    def zero_elastic_checkpoint(self):
-        return self._config.zero_config.elastic_checkpoint
-
-    def zero_max_live_parameters(self):
-        return self._config.zero_config.max_live_parameters
-
-    def zero_max_reuse_distance(self):
-        return self._config.zero_config.max_reuse_distance
-
-    def zero_prefetch_bucket_size(self):
-        return self._config.zero_config.prefetch_bucket_size
-
-    def zero_param_persistence_threshold(self):
-        return self._config.zero_config.param_persistence_threshold
-
-    def zero_gather_fp16_weights_on_model_save(self):
-        return self._config.zero_config.gather_fp16_weights_on_model_save
-
     def zero_fused_nvlink(self):
         v = self._config.zero_config.fused_nvlink
         if v == "auto":
             return torch.cuda.is_available() and self.dp_world_size > 1 and os.environ.get("DSB_FUSED_NVLINK", "1") != "0"
         return bool(v)
 
-    def fp16_enabled(self):
-        return self._config.fp16_enabled
-
-    def precision(self):
-        return self._config.precision
-
-    def amp_enabled(self):
-        return self._config.amp_enabled
-
-    def amp_params(self):
-        return self._config.amp_params
-
-    def loss_scale(self):
-        return self._config.loss_scale
-
-    def gradient_accumulation_steps(self):
-        return self._config.gradient_accumulation_steps
-
-    def allreduce_always_fp32(self):
-        return self._config.fp32_allreduce
-
     def postscale_gradients(self):
         return not self._config.prescale_gradients
 
-    def gradient_predivide_factor(self):
-        return self._config.gradient_predivide_factor
-
-    def steps_per_print(self):
-        return self._config.steps_per_print
-
-    def zero_allgather_partitions(self):
-        return self._config.zero_config.allgather_partitions
-
-    def dump_state(self):
-        return self._config.dump_state
-
-    def gradient_clipping(self):
-        return self._config.gradient_clipping
-
     def dynamic_loss_scale(self):
         return self._config.loss_scale == 0
-
-    def initial_dynamic_scale(self):
-        return self._config.initial_dynamic_scale
-
-    def dynamic_loss_scale_args(self):
-        return self._config.dynamic_loss_scale_args
-
-    def aio_config(self):
-        return self._config.aio_config
 
     # ------------------------------------------------------------------ setup
     def _configure_lr_scheduler(self, client_lr_scheduler):
@@ -613,3 +448,66 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
             logger.warning(f"DeepSpeed unable to scale loss because of type: {type(prescaled_loss)}")
             self.warn_unscaled_loss = False
         return prescaled_loss
+
+
+# ----------------------------------------------------------------------------------------------- generated accessors
+# The reference exposes one zero-argument method per configuration value (engine.train_batch_size(), ...). Here they are
+# generated from a table: (method name, attribute path below engine._config).
+_CONFIG_ACCESSORS = (
+    ("checkpoint_tag_validation_enabled", "checkpoint_tag_validation_enabled"),
+    ("checkpoint_tag_validation_fail", "checkpoint_tag_validation_fail"),
+    ("elasticity_enabled", "elasticity_enabled"), ("pld_enabled", "pld_enabled"), ("pld_params", "pld_params"),
+    ("tensorboard_enabled", "tensorboard_enabled"), ("tensorboard_output_path", "tensorboard_output_path"),
+    ("tensorboard_job_name", "tensorboard_job_name"), ("wall_clock_breakdown", "wall_clock_breakdown"),
+    ("flops_profiler_enabled", "flops_profiler_config.enabled"),
+    ("flops_profiler_profile_step", "flops_profiler_config.profile_step"),
+    ("flops_profiler_module_depth", "flops_profiler_config.module_depth"),
+    ("flops_profiler_top_modules", "flops_profiler_config.top_modules"),
+    ("flops_profiler_detailed", "flops_profiler_config.detailed"), ("memory_breakdown", "memory_breakdown"),
+    ("sparse_gradients_enabled", "sparse_gradients_enabled"), ("train_batch_size", "train_batch_size"),
+    ("train_micro_batch_size_per_gpu", "train_micro_batch_size_per_gpu"), ("optimizer_params", "optimizer_params"),
+    ("optimizer_legacy_fusion", "optimizer_legacy_fusion"), ("scheduler_name", "scheduler_name"),
+    ("scheduler_params", "scheduler_params"), ("zero_optimization", "zero_enabled"),
+    ("zero_allow_untested_optimizer", "zero_allow_untested_optimizer"),
+    ("zero_reduce_scatter", "zero_config.reduce_scatter"), ("zero_overlap_comm", "zero_config.overlap_comm"),
+    ("zero_offload_optimizer", "zero_config.offload_optimizer"),
+    ("zero_offload_param", "zero_config.offload_param"), ("zero_sub_group_size", "zero_config.sub_group_size"),
+    ("zero_optimization_stage", "zero_optimization_stage"),
+    ("zero_reduce_bucket_size", "zero_config.reduce_bucket_size"),
+    ("zero_allgather_bucket_size", "zero_config.allgather_bucket_size"),
+    ("zero_contiguous_gradients", "zero_config.contiguous_gradients"),
+    ("zero_load_from_fp32_weights", "zero_config.load_from_fp32_weights"),
+    ("zero_elastic_checkpoint", "zero_config.elastic_checkpoint"),
+    ("zero_max_live_parameters", "zero_config.max_live_parameters"),
+    ("zero_max_reuse_distance", "zero_config.max_reuse_distance"),
+    ("zero_prefetch_bucket_size", "zero_config.prefetch_bucket_size"),
+    ("zero_param_persistence_threshold", "zero_config.param_persistence_threshold"),
+    ("zero_gather_fp16_weights_on_model_save", "zero_config.gather_fp16_weights_on_model_save"),
+    ("fp16_enabled", "fp16_enabled"), ("precision", "precision"), ("amp_enabled", "amp_enabled"),
+    ("amp_params", "amp_params"), ("loss_scale", "loss_scale"),
+    ("gradient_accumulation_steps", "gradient_accumulation_steps"), ("allreduce_always_fp32", "fp32_allreduce"),
+    ("gradient_predivide_factor", "gradient_predivide_factor"), ("steps_per_print", "steps_per_print"),
+    ("zero_allgather_partitions", "zero_config.allgather_partitions"), ("dump_state", "dump_state"),
+    ("gradient_clipping", "gradient_clipping"), ("initial_dynamic_scale", "initial_dynamic_scale"),
+    ("dynamic_loss_scale_args", "dynamic_loss_scale_args"), ("aio_config", "aio_config"),
+)
+
+
+def _make_config_accessor(path):
+    parts = path.split(".")
+
+    def accessor(self):
+        value = self._config
+        for part in parts:
+            value = getattr(value, part)
+        return value
+
+    return accessor
+
+
+for _name, _path in _CONFIG_ACCESSORS:
+    _fn = _make_config_accessor(_path)
+    _fn.__name__ = _name
+    _fn.__doc__ = f"Configuration value `{_path}`."
+    setattr(DeepSpeedEngine, _name, _fn)
+del _name, _path, _fn
