@@ -43,26 +43,23 @@ except Exception:  # pragma: no cover
     _SummaryWriter = None
 
 
-def _initialize_parameter_parallel_groups(parameter_parallel_size=None):
-    data_parallel_size = int(dist.get_world_size())
-    if parameter_parallel_size is None:
-        parameter_parallel_size = int(data_parallel_size)
-    assert data_parallel_size % parameter_parallel_size == 0, "world size should be divisible by parameter parallel size"
-    rank = dist.get_rank()
-    my_group = None
-    for i in range(dist.get_world_size() // parameter_parallel_size):
-        ranks = range(i * parameter_parallel_size, (i + 1) * parameter_parallel_size)
-        group = torch.distributed.new_group(ranks)
-        if rank in ranks:
-            my_group = group
-    return my_group
+from .zero.utils import _initialize_parameter_parallel_groups  # noqa: E402  (same helper, one implementation)
 
 
 def print_configuration(args, name):
-    logger.info("{}:".format(name))
-    for arg in sorted(vars(args)):
-        dots = "." * (29 - len(arg))
-        logger.info("  {} {} {}".format(arg, dots, getattr(args, arg)))
+    """Every attribute of `args`, one per line, names padded with dots to a common column."""
+    logger.info(f"{name}:")
+    for key in sorted(vars(args)):
+        logger.info("  {} {} {}".format(key, "." * (29 - len(key)), getattr(args, key)))
+
+
+# what a fresh engine knows before any configuration is read: attribute -> initial value
+_INITIAL_STATE = dict(
+    data_parallel_group=None, global_steps=0, global_samples=0, micro_steps=0, skipped_steps=0, gradient_average=True,
+    warn_unscaled_loss=True, loaded_checkpoint_mp_world_size=None, loaded_checkpoint_dp_world_size=None,
+    enable_backward_allreduce=True, progressive_layer_drop=None, store_gradients=False, store_gradients_cpu=False,
+    stored_gradients=None, optimizer=None, lr_scheduler=None, save_non_zero_checkpoint=False,
+    save_zero_checkpoint=False)
 
 
 class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
@@ -71,79 +68,54 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
     def __init__(self, args, model, optimizer=None, model_parameters=None, training_data=None, lr_scheduler=None,
                  mpu=None, dist_init_required=None, collate_fn=None, config_params=None, dont_change_device=False):
         super().__init__()
-        self.dont_change_device = dont_change_device
-        self.client_optimizer = optimizer
-        self.client_model_parameters = model_parameters
-        self.client_lr_scheduler = lr_scheduler
-        self.training_data = training_data
-        self.collate_fn = collate_fn
-        self.mpu = mpu
-        self.data_parallel_group = None
-        self.global_steps = 0
-        self.global_samples = 0
-        self.micro_steps = 0
-        self.skipped_steps = 0
-        self.gradient_average = True
-        self.warn_unscaled_loss = True
-        self.config_params = config_params
-        self.loaded_checkpoint_mp_world_size = None
-        self.loaded_checkpoint_dp_world_size = None
-        self.enable_backward_allreduce = True
-        self.progressive_layer_drop = None
+        # ---- what the caller handed in
+        self.client_optimizer, self.client_model_parameters = optimizer, model_parameters
+        self.client_lr_scheduler, self.training_data, self.collate_fn = lr_scheduler, training_data, collate_fn
+        self.mpu, self.config_params, self.dont_change_device = mpu, config_params, dont_change_device
+        for attr, value in _INITIAL_STATE.items():
+            setattr(self, attr, value)
+        self.layer_outputs, self._hook_handles = {}, []
         self.dist_backend = "nccl" if torch.cuda.is_available() else "gloo"
-        self.store_gradients = False
-        self.store_gradients_cpu = False
-        self.stored_gradients = None
-        self.layer_outputs = {}
-        self._hook_handles = []
 
+        # ---- process group, configuration, device
         if dist_init_required is None:
             dist_init_required = not dist.is_initialized()
-        if dist_init_required is False:
-            assert dist.is_initialized() is True, "Torch distributed not initialized. Please set dist_init_required to True or initialize before calling deepspeed.initialize()"
-        else:
+        if dist_init_required:
             init_distributed(dist_backend=self.dist_backend)
-
+        else:
+            assert dist.is_initialized() is True, "Torch distributed not initialized. Please set dist_init_required " \
+                "to True or initialize before calling deepspeed.initialize()"
         self._do_args_sanity_check(args)
         self._configure_with_arguments(args, mpu)
         self._do_sanity_check()
         self._set_distributed_vars()
-
         if self.tensorboard_enabled() and self.global_rank == 0:
             self.summary_writer = self.get_summary_writer()
 
+        # ---- model, timers, data
         self._configure_distributed_model(model)
-
         self.timers = SynchronizedWallClockTimer()
         self.tput_timer = ThroughputTimer(batch_size=self.train_micro_batch_size_per_gpu(),
                                           num_workers=self.dp_world_size, steps_per_output=self.steps_per_print(),
                                           monitor_memory=False)
-        if training_data:
-            self.training_dataloader = self.deepspeed_io(training_data)
-        else:
-            self.training_dataloader = None
+        self.training_dataloader = self.deepspeed_io(training_data) if training_data else None
 
-        self.optimizer = None
-        self.lr_scheduler = None
+        # ---- optimizer stack and schedule
         if model_parameters or optimizer:
             self._configure_optimizer(optimizer, model_parameters)
             self._configure_lr_scheduler(lr_scheduler)
             self._report_progress(0)
 
+        # ---- embedding gradients that travel as CSR, checkpoint roles, progressive layer drop
         self.csr_tensor_module_names = set()
         if self.sparse_gradients_enabled():
             for name, module in self.module.named_modules():
                 if isinstance(module, torch.nn.Embedding):
                     self.csr_tensor_module_names.add(name + ".weight")
                     logger.info("Will convert {} to sparse (csr) tensor during training".format(name))
-
-        self.save_non_zero_checkpoint = False
-        self.save_zero_checkpoint = False
         self._configure_checkpointing(dist_init_required)
-
         if self.pld_enabled():
             self.progressive_layer_drop = self._configure_progressive_layer_drop()
-
         if self.global_rank == 0:
             self._config.print("DeepSpeedEngine configuration")
             if self.dump_state():
@@ -250,59 +222,55 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
 
     # ------------------------------------------------------------------ setup
     def _configure_lr_scheduler(self, client_lr_scheduler):
-        lr_scheduler = self._scheduler_from_config(self.optimizer)
-        if lr_scheduler:
-            if self.global_rank == 0:
-                logger.info(f"DeepSpeed using configured LR scheduler = {self.scheduler_name()}")
-            self.lr_scheduler = lr_scheduler
-        else:
-            if self.global_rank == 0:
-                logger.info("DeepSpeed using client LR scheduler")
-            self.lr_scheduler = client_lr_scheduler
+        """The scheduler named in the config wins over the one passed to initialize()."""
+        configured = self._scheduler_from_config(self.optimizer)
+        self.lr_scheduler = configured or client_lr_scheduler
+        if self.global_rank == 0:
+            logger.info(f"DeepSpeed using configured LR scheduler = {self.scheduler_name()}" if configured
+                        else "DeepSpeed using client LR scheduler")
         log_dist(f"DeepSpeed LR Scheduler = {self.lr_scheduler}", ranks=[0])
 
     def _configure_checkpointing(self, dist_init_required):
-        dp_rank = self.global_rank
-        if self.mpu:
-            dp_rank = self.mpu.get_data_parallel_rank()
-        # only the first data-parallel replica writes module states; ZeRO ranks each write their optimizer shard
-        self.save_non_zero_checkpoint = (dp_rank == 0) or self.zero_optimization_partition_weights()
+        """Who writes what: module states come from the first data-parallel replica (every replica under ZeRO-3, where
+        each holds different shards); every ZeRO rank writes its own optimizer shard."""
+        replica = self.mpu.get_data_parallel_rank() if self.mpu else self.global_rank
+        self.save_non_zero_checkpoint = replica == 0 or self.zero_optimization_partition_weights()
         if self.zero_optimization():
-            param_rank = dist.get_rank(group=self.optimizer.dp_process_group) if hasattr(self.optimizer, "dp_process_group") else dp_rank
-            self.save_zero_checkpoint = (param_rank == dp_rank)
+            shard_group = getattr(self.optimizer, "dp_process_group", None)
+            shard_rank = dist.get_rank(group=shard_group) if shard_group is not None else replica
+            self.save_zero_checkpoint = shard_rank == replica
 
     def _scheduler_from_config(self, optimizer):
-        scheduler_name = self.scheduler_name()
-        if scheduler_name is not None:
-            if hasattr(lr_schedules, scheduler_name):
-                scheduler = getattr(lr_schedules, scheduler_name)
-            else:
-                assert hasattr(torch.optim.lr_scheduler, scheduler_name), f"DeepSpeed does not recognize LR scheduler {scheduler_name}"
-                scheduler = getattr(torch.optim.lr_scheduler, scheduler_name)
-                optimizer = lr_schedules.get_torch_optimizer(optimizer)
-            return scheduler(optimizer, **self.scheduler_params())
-        return None
+        """Instantiate `scheduler.type`: one of ours (runtime/lr_schedules.py) or any torch.optim.lr_scheduler class."""
+        kind = self.scheduler_name()
+        if kind is None:
+            return None
+        ours = getattr(lr_schedules, kind, None)
+        if ours is not None:
+            return ours(optimizer, **self.scheduler_params())
+        assert hasattr(torch.optim.lr_scheduler, kind), f"DeepSpeed does not recognize LR scheduler {kind}"
+        # torch schedulers insist on a torch.optim.Optimizer: hand them the innermost one
+        return getattr(torch.optim.lr_scheduler, kind)(lr_schedules.get_torch_optimizer(optimizer),
+                                                       **self.scheduler_params())
 
     def _set_distributed_vars(self):
-        if self.local_rank >= 0 and torch.cuda.is_available():
-            torch.cuda.set_device(self.local_rank)
-            self.device = torch.device("cuda", self.local_rank)
-        elif torch.cuda.is_available():
-            self.device = torch.device("cuda")
+        if torch.cuda.is_available():
+            if self.local_rank >= 0:
+                torch.cuda.set_device(self.local_rank)
+            self.device = torch.device("cuda", self.local_rank) if self.local_rank >= 0 else torch.device("cuda")
         else:
             self.device = torch.device("cpu")
-        self.world_size = dist.get_world_size()
-        self.global_rank = dist.get_rank()
+        self.world_size, self.global_rank = dist.get_world_size(), dist.get_rank()
 
     def _configure_with_arguments(self, args, mpu):
-        self.local_rank = int(os.environ.get("LOCAL_RANK", getattr(args, "local_rank", 0) if args is not None else 0))
+        """LOCAL_RANK from the launcher's environment (falling back to args.local_rank) and the parsed configuration."""
+        fallback = getattr(args, "local_rank", 0) if args is not None else 0
+        self.local_rank = int(os.environ.get("LOCAL_RANK", fallback))
         if hasattr(args, "local_rank"):
             args.local_rank = self.local_rank
         config_file = None
         if args is not None:
-            config_file = getattr(args, "deepspeed_config", None)
-            if config_file is None and getattr(args, "deepscale_config", None) is not None:
-                config_file = args.deepscale_config
+            config_file = getattr(args, "deepspeed_config", None) or getattr(args, "deepscale_config", None)
         self._config = DeepSpeedConfig(config_file, mpu, param_dict=self.config_params)
 
     def _do_args_sanity_check(self, args):
@@ -324,24 +292,21 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         return optimizer_name in C.DEEPSPEED_OPTIMIZERS or getattr(torch.optim, optimizer_name, None) is not None
 
     def _do_sanity_check(self):
-        if not self.client_optimizer:
-            if self.optimizer_name() is not None:
-                assert self._is_supported_optimizer(self.optimizer_name()), \
-                    "{} is not a supported DeepSpeed Optimizer".format(self.optimizer_name())
-        if self.optimizer_name() in (C.LAMB_OPTIMIZER, C.ONEBIT_LAMB_OPTIMIZER):
+        name = self.optimizer_name()
+        if not self.client_optimizer and name is not None:
+            assert self._is_supported_optimizer(name), "{} is not a supported DeepSpeed Optimizer".format(name)
+        if name in (C.LAMB_OPTIMIZER, C.ONEBIT_LAMB_OPTIMIZER):
             assert self.dynamic_loss_scale() or self.precision() != torch.float16, \
-                "DeepSpeed {} optimizer requires dynamic loss scaling".format(self.optimizer_name())
+                "DeepSpeed {} optimizer requires dynamic loss scaling".format(name)
 
     def _broadcast_model(self):
-        def is_replicated(p):
-            if hasattr(p, "ds_status"):
-                from .zero.partition_parameters import ZeroParamStatus
-                if p.ds_status is not ZeroParamStatus.AVAILABLE:
-                    return False
-            return True
-
+        """Every data-parallel replica starts from rank 0's weights (ZeRO-3 shards that are not materialised here
+        are skipped: they were scattered from one source when they were partitioned)."""
+        from .zero.partition_parameters import ZeroParamStatus
         for p in self.module.parameters():
-            if torch.is_tensor(p) and is_replicated(p):
+            if hasattr(p, "ds_status") and p.ds_status is not ZeroParamStatus.AVAILABLE:
+                continue
+            if torch.is_tensor(p):
                 dist.broadcast(p.data, self.broadcast_src_rank, group=self.data_parallel_group)
 
     def _configure_distributed_model(self, model):
@@ -350,16 +315,15 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
             self.module.to(self.precision())
         if not self.dont_change_device:
             self.module.to(self.device)
-        if self.mpu is None:
-            self.data_parallel_group = _initialize_parameter_parallel_groups()
-            self.dp_world_size = dist.get_world_size()
-            self.mp_world_size = 1
-            self.broadcast_src_rank = 0
-        else:
-            self.data_parallel_group = self.mpu.get_data_parallel_group()
+        if self.mpu is not None:
+            group = self.mpu.get_data_parallel_group()
+            self.data_parallel_group = group
             self.dp_world_size = self.mpu.get_data_parallel_world_size()
             self.mp_world_size = self.mpu.get_model_parallel_world_size()
-            self.broadcast_src_rank = _get_global_rank(self.mpu.get_data_parallel_group(), 0)
+            self.broadcast_src_rank = _get_global_rank(group, 0)
+        else:
+            self.data_parallel_group = _initialize_parameter_parallel_groups()
+            self.dp_world_size, self.mp_world_size, self.broadcast_src_rank = dist.get_world_size(), 1, 0
         if not self.amp_enabled():
             self._broadcast_model()
 
