@@ -43,12 +43,15 @@ for S in (2048, 4096, 8192):
         out.sum().backward()
 
     dense_masked.mask = sparse_to_dense(torch.ones(1, int(layout.sum()), block, block), layout, block)[0].bool().cuda()[None]
-    t_s = timeit(sparse)
+    t_s = timeit(sparse)                       # one tcgen05 block-sparse flash kernel per direction
+    SparseSelfAttention.use_fused = False
+    t_u = timeit(sparse)                       # SDD + block-sparse softmax + DSD as separate operators
+    SparseSelfAttention.use_fused = True
     try:
         t_d = timeit(dense_masked)
     except torch.cuda.OutOfMemoryError:
         t_d = None
-    res.append({"seq": S, "density": round(density, 4), "sparse_ms": round(t_s, 3),
+    res.append({"seq": S, "density": round(density, 4), "sparse_ms": round(t_s, 3), "sparse_unfused_ms": round(t_u, 3),
                 "dense_masked_ms": None if t_d is None else round(t_d, 3),
                 "speedup": None if t_d is None else round(t_d / t_s, 2)})
     print(res[-1], flush=True)

@@ -994,10 +994,10 @@ extern "C" int dsb_flash_attn_fwd_variant(int v) {
 // out[b, s, h, :] = softmax(scale * q[b, s, h, :] . k[b, :, h, :]^T (+ causal mask)) v[b, :, h, :]; lse (optional,
 // [B, H, S] fp32) receives the natural-log sum of exponentials of the scaled scores of every row.
 // q / k / v / out: [B, S, H, 128] with element strides (s*b, s*s, s*h, 1); S a multiple of 128.
-extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S,
-                                  int H, int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh,
-                                  long v_sb, long v_ss, long v_sh, long o_sb, long o_ss, long o_sh, float scale,
-                                  int causal, int dtype, void* stream_) {
+static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
+                          long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss,
+                          long v_sh, long o_sb, long o_ss, long o_sh, float scale, int causal, int dtype,
+                          const int* sched, int sched_hstride, int sched_pstride, const float* kpm, void* stream_) {
     using namespace dsb;
     using namespace dsb::fa;
     ensure_context_on_this_thread();
@@ -1024,12 +1024,15 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
     const float scale_log2 = scale * 1.4426950408889634f;
     dim3 grid(S / BQ, B * H);
     cudaError_t e;
-    if (g_fa_fwd_variant == 2 && S % 256 == 0) {
+    const bool extras = sched != nullptr || kpm != nullptr;
+    if (extras && S % 256) return DSB_ERR_SIZE;      // only the two-tile kernel knows schedules and key masks
+    if ((g_fa_fwd_variant == 2 || extras) && S % 256 == 0) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
         if (rc) return rc;
         rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);
         if (rc) return rc;
-        return dsb::fa2::launch_fwd(tq, tk, tv, to, lse, B, S, H, scale_log2, causal, bf, stream);
+        return dsb::fa2::launch_fwd(tq, tk, tv, to, lse, B, S, H, scale_log2, causal, bf, sched, sched_hstride,
+                                    sched_pstride, kpm, stream);
     }
     if (g_fa_fwd_variant != 128) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
@@ -1060,6 +1063,30 @@ extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, v
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int dsb_flash_attn_fwd(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S,
+                                  int H, int D, long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh,
+                                  long v_sb, long v_ss, long v_sh, long o_sb, long o_ss, long o_sh, float scale,
+                                  int causal, int dtype, void* stream_) {
+    return flash_fwd_impl(q, k, v, out, lse, B, S, H, D, q_sb, q_ss, q_sh, k_sb, k_ss, k_sh, v_sb, v_ss, v_sh, o_sb, o_ss,
+                          o_sh, scale, causal, dtype, nullptr, 0, 0, nullptr, stream_);
+}
+
+// Same with a block-sparse schedule and / or an additive key mask (S % 256 == 0):
+//   sched : device int32, per (head, 256-row query block) a record [n, (64-key block index, visibility word of the first
+//           128 rows, of the second 128 rows) * n] at sched + head * sched_hstride + block * sched_pstride
+//           (sched_hstride = 0: one layout for all heads). Bit qgroup * 4 + kgroup of a word = 16-query group qgroup of the
+//           tile sees 16-key group kgroup. `causal` is ignored when a schedule is given (the layout says what is visible).
+//   kpm   : fp32 [B, S], added to the scaled scores of every query; ALREADY multiplied by log2(e).
+// Reference: deepspeed/ops/sparse_attention (SDD matmul + block-sparse softmax + DSD matmul as three Triton kernels).
+extern "C" int dsb_flash_attn_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S,
+                                     int H, int D, const long* strides /* 4 x (sb, ss, sh): q k v out */, float scale,
+                                     int causal, int dtype, const int* sched, int sched_hstride, int sched_pstride,
+                                     const float* kpm, void* stream_) {
+    return flash_fwd_impl(q, k, v, out, lse, B, S, H, D, strides[0], strides[1], strides[2], strides[3], strides[4],
+                          strides[5], strides[6], strides[7], strides[8], strides[9], strides[10], strides[11], scale,
+                          causal, dtype, sched, sched_hstride, sched_pstride, kpm, stream_);
 }
 
 // Backward of dsb_flash_attn_fwd. dO / q / k / v / out / dk / dv: [B, S, H, 128] with their own element strides (unit
@@ -1138,10 +1165,11 @@ extern "C" int dsb_flash_attn_bwd(const void* dO, const void* q, const void* k, 
 // rot_dim > 0 (multiple of 16, tables [S, rot_dim / 2] fp32 from dsb_rotary_table): q and k were rotated before the
 // forward pass, and dq / dk come back as gradients of the UNROTATED tensors (the inverse rotation is applied in the dK
 // epilogue and in the dQ finishing pass, so no separate rotary launch is needed in backward).
-extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out,
-                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H,
-                                   int D, const long* strides, float scale, int causal, int dtype,
-                                   const float* rot_cos, const float* rot_sin, int rot_dim, void* stream_) {
+static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                           const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D,
+                           const long* strides, float scale, int causal, int dtype, const float* rot_cos,
+                           const float* rot_sin, int rot_dim, const int* sched, int sched_hstride, int sched_pstride,
+                           const float* kpm, void* stream_) {
     using namespace dsb;
     using namespace dsb::fa;
     ensure_context_on_this_thread();
@@ -1180,7 +1208,27 @@ extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return -(int)r - 1000;
     rc = fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale, scale * 1.4426950408889634f, causal,
-                         bf, rot_cos, rot_sin, rot_dim, stream);
+                         bf, rot_cos, rot_sin, rot_dim, sched, sched_hstride, sched_pstride, kpm, stream);
     if (rc) return rc;
     return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, rot_cos, rot_sin, rot_dim, stream);
+}
+
+extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                                   const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H,
+                                   int D, const long* strides, float scale, int causal, int dtype,
+                                   const float* rot_cos, const float* rot_sin, int rot_dim, void* stream_) {
+    return flash_bwd2_impl(dO, q, k, v, out, lse, scratch, dq, dk, dv, B, S, H, D, strides, scale, causal, dtype, rot_cos,
+                           rot_sin, rot_dim, nullptr, 0, 0, nullptr, stream_);
+}
+
+// Backward of dsb_flash_attn_fwd_ex. `sched`: per (head, 128-key block) a record [n, (64-row query block index,
+// visibility word) * n]; bit kgroup * 4 + qgroup of a word = 16-key group kgroup of the block is seen by 16-query group
+// qgroup of the tile. `kpm` as in the forward.
+extern "C" int dsb_flash_attn_bwd2_ex(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                                      const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S,
+                                      int H, int D, const long* strides, float scale, int causal, int dtype,
+                                      const int* sched, int sched_hstride, int sched_pstride, const float* kpm,
+                                      void* stream_) {
+    return flash_bwd2_impl(dO, q, k, v, out, lse, scratch, dq, dk, dv, B, S, H, D, strides, scale, causal, dtype, nullptr,
+                           nullptr, 0, sched, sched_hstride, sched_pstride, kpm, stream_);
 }

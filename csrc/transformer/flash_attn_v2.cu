@@ -237,7 +237,9 @@ template <typename T>
 __global__ void __launch_bounds__(384, 1)
 flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
-                  float* __restrict__ lse, int S, int H, float scale_log2, int causal, int dbg, long long* prof) {
+                  float* __restrict__ lse, int S, int H, float scale_log2, int causal, int dbg, long long* prof,
+                  const int* __restrict__ sched, int sched_hstride, int sched_pstride,
+                  const float* __restrict__ kpm) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem + F_OFF_Q;
@@ -260,8 +262,12 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     const int b = blockIdx.x / H, h = blockIdx.x - b * H;
     const int pr = gridDim.y - 1 - blockIdx.y;   // the long (late) row blocks are dispatched first
     const int q0 = pr * 2 * F_BQ;
-    const int nA = causal ? (q0 + F_BQ) / F_BK : S / F_BK;
-    const int nB = causal ? (q0 + 2 * F_BQ) / F_BK : S / F_BK;
+    // Block-sparse mode: `sc` = [n, (key block, visibility word of tile 0, of tile 1) * n] for this (head, row pair). A
+    // visibility word has one bit per (16-row query group, 16-key group) of a 128 x 64 tile: bit = qgroup * 4 + kgroup.
+    const int* sc = sched != nullptr ? sched + (long)h * sched_hstride + (long)pr * sched_pstride : nullptr;
+    const int nA = sc ? sc[0] : (causal ? (q0 + F_BQ) / F_BK : S / F_BK);
+    const int nB = sc ? sc[0] : (causal ? (q0 + 2 * F_BQ) / F_BK : S / F_BK);
+    auto key_block = [&](int j) { return sc ? sc[1 + 3 * j] : j; };
     // phase timers of CTA (0, 0) (the longest one), only when a buffer is registered with dsb_flash_attn_debug_timers
     const bool tm = prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
     long long t0 = 0, acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -312,8 +318,8 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 if ((dbg & 32) && j >= F_NS) { mbar_arrive(&k_full[st]); continue; }
                 mbar_arrive_expect_tx(&k_full[st], F_KVTILE);
                 uint8_t* dst = sK + st * F_KVTILE;
-                tma_load_4d(dst, &tmK, &k_full[st], 0, h, j * F_BK, b);
-                tma_load_4d(dst + F_KVCHUNK, &tmK, &k_full[st], 64, h, j * F_BK, b);
+                tma_load_4d(dst, &tmK, &k_full[st], 0, h, key_block(j) * F_BK, b);
+                tma_load_4d(dst + F_KVCHUNK, &tmK, &k_full[st], 64, h, key_block(j) * F_BK, b);
             }
         }
     } else if (warp == 3) {
@@ -324,8 +330,8 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 if ((dbg & 32) && j >= F_NS) { mbar_arrive(&v_full[st]); continue; }
                 mbar_arrive_expect_tx(&v_full[st], F_KVTILE);
                 uint8_t* dst = sV + st * F_KVTILE;
-                tma_load_4d(dst, &tmV, &v_full[st], 0, h, j * F_BK, b);
-                tma_load_4d(dst + F_KVCHUNK, &tmV, &v_full[st], 64, h, j * F_BK, b);
+                tma_load_4d(dst, &tmV, &v_full[st], 0, h, key_block(j) * F_BK, b);
+                tma_load_4d(dst + F_KVCHUNK, &tmV, &v_full[st], 64, h, key_block(j) * F_BK, b);
             }
         }
     } else if (warp == 1 || warp == 2) {
@@ -406,7 +412,10 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const int n = t ? nB : nA;
         const int qrow = q0 + t * F_BQ + row;
         const uint32_t t_o = tmem_base + lane_field + 256 + t * 128;
-        const uint64_t sc2 = pk2(scale_log2, scale_log2);
+        // with an additive key mask the scores are scaled and biased first, and the rest works on them with scale 1
+        const float sc_eff = kpm != nullptr ? 1.f : scale_log2;
+        const uint64_t sc2 = pk2(sc_eff, sc_eff);
+        const float* kpm_b = kpm != nullptr ? kpm + (long)b * S : nullptr;
         float m_run = -INFINITY, l_run = 0.f;
         t0 = clock64();
         for (int j = 0; j < n; ++j) {
@@ -437,7 +446,28 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 m_run = 0.f;
                 continue;
             }
-            if (causal) {
+            if (kpm_b != nullptr) {
+                const float4* km = reinterpret_cast<const float4*>(kpm_b + key_block(j) * F_BK);
+#pragma unroll
+                for (int i = 0; i < 64; i += 4) {
+                    const float4 k4 = __ldg(km + (i >> 2));
+                    float a0, a1, b0, b1;
+                    upk2(fma2(pk2u(r[i], r[i + 1]), pk2(scale_log2, scale_log2), pk2(k4.x, k4.y)), a0, a1);
+                    upk2(fma2(pk2u(r[i + 2], r[i + 3]), pk2(scale_log2, scale_log2), pk2(k4.z, k4.w)), b0, b1);
+                    r[i] = __float_as_uint(a0);
+                    r[i + 1] = __float_as_uint(a1);
+                    r[i + 2] = __float_as_uint(b0);
+                    r[i + 3] = __float_as_uint(b1);
+                }
+            }
+            if (sc != nullptr) {
+                const uint32_t vis = (static_cast<uint32_t>(sc[2 + 3 * j + t]) >> ((row >> 4) * 4)) & 15u;
+                if (__any_sync(0xffffffffu, vis != 15u)) {
+#pragma unroll
+                    for (int i = 0; i < 64; ++i)
+                        if (!((vis >> (i >> 4)) & 1u)) r[i] = NEG_INF_BITS;
+                }
+            } else if (causal) {
                 const int lim = qrow - j * F_BK;   // columns <= lim of this block are visible to this row
                 if (__any_sync(0xffffffffu, lim < F_BK - 1)) {
 #pragma unroll
@@ -453,7 +483,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 m2 = max3(m2, __uint_as_float(r[i + 4]), __uint_as_float(r[i + 5]));
                 m3 = max3(m3, __uint_as_float(r[i + 6]), __uint_as_float(r[i + 7]));
             }
-            const float m_cand = max3(m0, m1, fmaxf(m2, m3)) * scale_log2;
+            const float m_cand = max3(m0, m1, fmaxf(m2, m3)) * sc_eff;
             const bool grow = m_cand > m_run + F_TAU;   // always true for the first block (m_run = -inf)
             if (__any_sync(0xffffffffu, grow)) {
                 const float m_new = grow ? m_cand : m_run;
@@ -475,7 +505,8 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 m_run = m_new;
             }
             FA2_TICK(2)
-            const uint64_t nm2 = pk2(-m_run, -m_run);
+            const float m_use = m_run == -INFINITY ? 0.f : m_run;   // a row with nothing visible yet: exp2(-inf - 0) = 0
+            const uint64_t nm2 = pk2(-m_use, -m_use);
             uint64_t sa = 0ull, sb = 0ull;
             uint32_t pk[32];
 #pragma unroll
@@ -514,7 +545,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         // (a parity wait on pv_done would be ambiguous here: this thread may be two products behind)
         mbar_wait(&o_final[t], 0);
         tc_fence_after();
-        const float inv_l = 1.f / l_run;
+        const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
         uint8_t* o_row = sQ + t * F_QTILE + row * 128;
         const int sw = row & 7;
 #pragma unroll 1
@@ -637,7 +668,9 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const __grid_constant__ CUtensorMap tmdK, const __grid_constant__ CUtensorMap tmdV,
                   const __grid_constant__ CUtensorMap tmDQ, const float* __restrict__ nlse2,
                   const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal, int dbg,
-                  long long* prof, const float* __restrict__ rot_cs, const float* __restrict__ rot_sn, int rot) {
+                  long long* prof, const float* __restrict__ rot_cs, const float* __restrict__ rot_sn, int rot,
+                  const int* __restrict__ sched, int sched_hstride, int sched_pstride,
+                  const float* __restrict__ kpm) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + B_OFF_K;
@@ -668,8 +701,12 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     const int lane = threadIdx.x & 31;
     const int b = blockIdx.x / H, h = blockIdx.x - b * H;
     const int jb = blockIdx.y;                       // key block; block 0 walks the most query blocks and starts first
+    // Block-sparse mode: `sc` = [n, (64-row query block, visibility word) * n] for this (head, key block); bit
+    // kgroup * 4 + qgroup of a word says whether 16-key group kgroup sees 16-query group qgroup of the 128 x 64 tile.
+    const int* sc = sched != nullptr ? sched + (long)h * sched_hstride + (long)jb * sched_pstride : nullptr;
     const int i0 = causal ? jb * 2 : 0;              // first 64-row query block that sees these keys
-    const int nit = S / 64 - i0;
+    const int nit = sc ? sc[0] : S / 64 - i0;
+    auto q_block = [&](int it) { return sc ? sc[1 + 2 * it] : i0 + it; };
     const bool tm = prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
     long long t0 = 0, acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 
@@ -716,7 +753,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             tma_load_4d(sV + 16384, &tmV, kv_full, 64, h, jb * 128, b);
             const long bh_off = (long)blockIdx.x * S;
             for (int it = 0; it < nit; ++it) {
-                const int q0 = (i0 + it) * 64;
+                const int q0 = q_block(it) * 64;
                 const int s3 = it % 3;
                 if (it >= 3) mbar_wait(&q_free[s3], ((it / 3) - 1) & 1);
                 mbar_arrive_expect_tx(&q_full[s3], 16384 + 512);
@@ -834,9 +871,10 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const int sw = row & 7;
         const uint64_t sc2 = pk2(scale_log2, scale_log2);
         const uint64_t s2 = pk2(scale, scale);
+        const float kp_row = kpm != nullptr ? kpm[(long)b * S + kvg] : 0.f;   // additive key mask (already in log2 units)
         for (int it = 0; it < nit; ++it) {
             const int buf = it & 1;
-            const int q0 = (i0 + it) * 64 + half * 32;        // global query index of this thread's first column
+            const int q0 = q_block(it) * 64 + half * 32;      // global query index of this thread's first column
             if (it == 0) t0 = clock64();
             mbar_wait(&q_full[it % 3], (it / 3) & 1);         // the -lse2 / -delta rows travel with the Q tile
             const float4* nl = reinterpret_cast<const float4*>(sLD + (it % 3) * 128 + half * 32);
@@ -860,7 +898,9 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             __syncwarp();
             if (lane == 0) mbar_arrive(dp_free);
             FA2_TICK(2)
-            const bool diag = causal && it < 2;
+            const bool diag = causal && it < 2 && sc == nullptr;
+            // this thread's two 16-query groups of the tile: visible or not (block-sparse mode)
+            const uint32_t vis = sc ? (static_cast<uint32_t>(sc[2 + 2 * it]) >> ((row >> 4) * 4 + half * 2)) & 3u : 3u;
             uint32_t pk[32];   // [0, 16) P^T, [16, 32) dS^T: the 32 columns this warp has just read
             if (dbg & 1) {
 #pragma unroll
@@ -871,8 +911,8 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 const float4 l4 = nl[i >> 2];
                 const float4 d4 = nd[i >> 2];
                 float p0, p1, p2, p3;
-                upk2(fma2(pk2u(rs[i], rs[i + 1]), sc2, pk2(l4.x, l4.y)), p0, p1);
-                const uint64_t x23 = fma2(pk2u(rs[i + 2], rs[i + 3]), sc2, pk2(l4.z, l4.w));
+                upk2(fma2(pk2u(rs[i], rs[i + 1]), sc2, pk2(l4.x + kp_row, l4.y + kp_row)), p0, p1);
+                const uint64_t x23 = fma2(pk2u(rs[i + 2], rs[i + 3]), sc2, pk2(l4.z + kp_row, l4.w + kp_row));
                 p0 = ex2(p0);
                 p1 = ex2(p1);
                 if (B_POLY) {
@@ -884,6 +924,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                     p2 = ex2(p2);
                     p3 = ex2(p3);
                 }
+                if (!((vis >> (i >> 4)) & 1u)) p0 = p1 = p2 = p3 = 0.f;
                 if (diag) {
                     if (q0 + i < kvg) p0 = 0.f;
                     if (q0 + i + 1 < kvg) p1 = 0.f;
@@ -977,7 +1018,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const int d = qd * 32 + lane;                          // head-dim index = TMEM lane of dQ^T
         const uint32_t lane_field = static_cast<uint32_t>(qd * 32) << 16;
         for (int it = 0; it < nit; ++it) {
-            const int q0 = (i0 + it) * 64;
+            const int q0 = q_block(it) * 64;
             if (it == 0) t0 = clock64();
             mbar_wait(dq_full, it & 1);
             tc_fence_after();
@@ -1039,7 +1080,8 @@ static long long* g_prof = nullptr;
 void set_debug_mode(int m) { g_dbg = m; }
 void set_debug_timers(long long* p) { g_prof = p; }
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
-               int B, int S, int H, float scale_log2, int causal, int bf16, cudaStream_t stream) {
+               int B, int S, int H, float scale_log2, int causal, int bf16, const int* sched, int sched_hstride,
+               int sched_pstride, const float* kpm, cudaStream_t stream) {
     if (S % 256) return DSB_ERR_SIZE;
     dim3 grid(B * H, S / 256);
     cudaError_t e;
@@ -1047,12 +1089,14 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         auto kern = flash_fwd2_kernel<__nv_bfloat16>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof);
+        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof, sched, sched_hstride,
+                                            sched_pstride, kpm);
     } else {
         auto kern = flash_fwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
-        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof);
+        kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof, sched, sched_hstride,
+                                            sched_pstride, kpm);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
@@ -1089,7 +1133,8 @@ int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long
 int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* nlse2,
                const float* ndelta, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
-               const float* rot_cs, const float* rot_sn, int rot, cudaStream_t stream) {
+               const float* rot_cs, const float* rot_sn, int rot, const int* sched, int sched_hstride, int sched_pstride,
+               const float* kpm, cudaStream_t stream) {
     if (S % 128) return DSB_ERR_SIZE;
     if (rot < 0 || rot > 128 || (rot % 16)) return DSB_ERR_ARG;
     dim3 grid(B * H, S / 128);
@@ -1099,13 +1144,13 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm);
     } else {
         auto kern = flash_bwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

@@ -8,8 +8,11 @@ namespace dsb {
 namespace fa2 {
 
 // Forward: tq / to with 128-row boxes, tk / tv with 64-row boxes; S must be a multiple of 256.
+// sched (optional, device int32): block-sparse schedule, see flash_attn_v2.cu; kpm (optional): additive key mask
+// [B, S] fp32, already multiplied by log2(e).
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
-               int B, int S, int H, float scale_log2, int causal, int bf16, cudaStream_t stream);
+               int B, int S, int H, float scale_log2, int causal, int bf16, const int* sched, int sched_hstride,
+               int sched_pstride, const float* kpm, cudaStream_t stream);
 
 // lse2[bh, s] = lse * log2(e), delta_s[bh, s] = scale * sum_d dO * O  (both fp32, [B, H, S]).
 int launch_prep(const void* dO, const void* O, const float* lse, float* lse2, float* delta_s, int B, int S, int H,
@@ -20,7 +23,8 @@ int launch_prep(const void* dO, const void* O, const float* lse, float* lse2, fl
 int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& tdo,
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* lse2,
                const float* delta_s, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
-               const float* rot_cs, const float* rot_sn, int rot, cudaStream_t stream);
+               const float* rot_cs, const float* rot_sn, int rot, const int* sched, int sched_hstride, int sched_pstride,
+               const float* kpm, cudaStream_t stream);
 
 // dq (16 bit, [B, S, H, 128] with strides s_dq) = transpose of the fp32 accumulator [B, H, 128, S].
 // rot > 0: apply the inverse rotary embedding (tables [S, rot / 2] fp32) on the way, likewise for dK in launch_bwd.

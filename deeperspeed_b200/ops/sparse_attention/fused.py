@@ -1,0 +1,144 @@
+"""Block-sparse attention as ONE tcgen05 flash kernel per direction.
+
+The reference computes sparse attention as three Triton kernels (SDD Q K^T on the layout's blocks, block-sparse softmax,
+DSD P V; deepspeed/ops/sparse_attention/matmul.py:98-501, softmax.py, trsrc/*.tr) and materialises the sparse score
+matrix between them. Here the layout is compiled into a *schedule* - per (head, 256-row query block) the list of 64-key
+blocks that contain anything visible, with one 32-bit visibility word per 128 x 64 tile at 16 x 16 granularity - and the
+flash-attention kernels of csrc/transformer/flash_attn_v2.cu walk that list: tiles that are not listed are never loaded
+or multiplied, listed tiles run on the tensor cores (tcgen05.mma, operands by TMA, P kept in tensor memory), and the 16 x
+16 blocks inside a tile that the layout leaves out are masked in the softmax. The backward uses the transposed schedule
+(per 128-key block, the 64-row query blocks that see it). Key-padding masks ride along as an additive per-key bias.
+
+Supported: fp16 / bf16, sequence length a multiple of 256, head dim <= 128 (smaller head dims are zero-padded to the
+kernel's 128), layout blocks of 16 / 32 / 64 / 128, key-padding mask in "add" or "mul" mode. Relative position
+embeddings and dense attention masks go through the unfused operators (`SparseSelfAttention` falls back by itself).
+"""
+import ctypes as C
+
+import torch
+
+from .. import kernels as K
+from .. import native as N
+
+_LOG2E = 1.4426950408889634
+_p, _i, _f = C.c_void_p, C.c_int, C.c_float
+N.register_sigs({
+    "dsb_flash_attn_fwd_ex": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _i, _i, _p, _p],
+    "dsb_flash_attn_bwd2_ex": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _i, _i, _p,
+                               _p],
+})
+
+
+def _records(words, index_dim_size):
+    """words: int64 [Hs, G, T] (G groups, T candidate tiles, 0 = nothing visible). Returns int32 [Hs, G, 1 + w * maxn]
+    records [n, (tile index, word...) * n] where `words` may carry several words per tile in a trailing dim."""
+    if words.dim() == 3:
+        words = words.unsqueeze(-1)
+    Hs, G, T, W = words.shape
+    live = (words != 0).any(-1)                                   # [Hs, G, T]
+    counts = live.sum(-1)
+    maxn = max(int(counts.max()), 1)
+    rec = torch.zeros(Hs, G, 1 + (1 + W) * maxn, dtype=torch.int64)
+    rec[..., 0] = counts
+    order = torch.argsort((~live).to(torch.int8), dim=-1, stable=True)[..., :maxn]      # live tiles first, in order
+    picked = torch.gather(words, 2, order.unsqueeze(-1).expand(-1, -1, -1, W))         # [Hs, G, maxn, W]
+    body = torch.cat([order.unsqueeze(-1), picked], dim=-1)                             # [Hs, G, maxn, 1 + W]
+    valid = (torch.arange(maxn).view(1, 1, -1) < counts.unsqueeze(-1)).unsqueeze(-1)
+    rec[..., 1:] = (body * valid).reshape(Hs, G, -1)
+    # visibility words use all 32 bits: store their two's complement in int32
+    rec = torch.where(rec >= 2 ** 31, rec - 2 ** 32, rec)
+    return rec.to(torch.int32).contiguous()
+
+
+def build_schedules(layout, block, seq_len):
+    """(forward schedule, backward schedule) as CPU int32 tensors for a [heads, nb, nb] 0/1 layout with `block`-sized
+    blocks over `seq_len` tokens. Heads with identical layouts share one record set (first dim 1)."""
+    assert block % 16 == 0, "layout blocks must be multiples of 16"
+    assert seq_len % 256 == 0
+    nb = seq_len // block
+    lay = layout[:, :nb, :nb].to(torch.int64)
+    if bool((lay == lay[:1]).all()):
+        lay = lay[:1]
+    rep = block // 16
+    sub = lay.repeat_interleave(rep, 1).repeat_interleave(rep, 2)       # [Hs, S / 16, S / 16]
+    Hs, n16 = sub.shape[0], sub.shape[1]
+    P, KB = seq_len // 256, seq_len // 64
+    # forward: bit = qgroup * 4 + kgroup inside a (128 query rows) x (64 keys) tile; two tiles per 256-row block
+    f = sub.view(Hs, P, 2, 8, KB, 4).permute(0, 1, 4, 2, 3, 5)         # [Hs, P, KB, tile, qg, kg]
+    wf = (f * (2 ** (torch.arange(8).view(8, 1) * 4 + torch.arange(4).view(1, 4)))).sum((-1, -2))     # [Hs, P, KB, 2]
+    # backward: bit = kgroup * 4 + qgroup inside a (128 keys) x (64 query rows) tile
+    JB, QB = seq_len // 128, seq_len // 64
+    g = sub.view(Hs, QB, 4, JB, 8).permute(0, 3, 1, 4, 2)              # [Hs, JB, QB, kg, qg]
+    wb = (g * (2 ** (torch.arange(8).view(8, 1) * 4 + torch.arange(4).view(1, 4)))).sum((-1, -2))     # [Hs, JB, QB]
+    return _records(wf, KB), _records(wb, QB)
+
+
+def _as_bshd128(x):
+    """[B, H, S, D] -> a [B, S, H, 128] view (D == 128) or zero-padded copy (D < 128) with unit last stride."""
+    B, H, S, D = x.shape
+    if D == 128:
+        v = x.transpose(1, 2)
+        if v.stride(-1) == 1 and all(st % 8 == 0 for st in v.stride()[:3]):
+            return v
+        return v.contiguous()
+    out = torch.zeros(B, S, H, 128, dtype=x.dtype, device=x.device)
+    out[..., :D] = x.transpose(1, 2)
+    return out
+
+
+def _strides(*tensors):
+    return (C.c_long * (3 * len(tensors)))(*[t.stride(i) for t in tensors for i in range(3)])
+
+
+class BlockSparseFlashFn(torch.autograd.Function):
+    """context = softmax(scale * Q K^T restricted to the layout (+ key mask)) V for [B, H, S, D] operands."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, sched_f, sched_b, kpm, scale):
+        B, H, S, D = q.shape
+        q4, k4, v4 = _as_bshd128(q), _as_bshd128(k), _as_bshd128(v)
+        out = torch.empty(B, S, H, 128, dtype=q.dtype, device=q.device)
+        lse = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
+        hs = sched_f.stride(0) if sched_f.shape[0] > 1 else 0
+        N.check(N.cuda_lib().dsb_flash_attn_fwd_ex(
+            N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), B, S, H, 128, _strides(q4, k4, v4, out),
+            float(scale), 0, N.dtype_code(q.dtype), N.ptr(sched_f), hs, sched_f.stride(1), N.ptr(kpm), N.stream_ptr()),
+            "dsb_flash_attn_fwd_ex")
+        K._count()
+        ctx.save_for_backward(q4, k4, v4, out, lse, sched_b, kpm)
+        ctx.meta = (D, float(scale))
+        return out[..., :D].transpose(1, 2)
+
+    @staticmethod
+    def backward(ctx, dctx):
+        q4, k4, v4, out, lse, sched_b, kpm = ctx.saved_tensors
+        D, scale = ctx.meta
+        B, S, H, _ = q4.shape
+        do4 = _as_bshd128(dctx)
+        dq, dk, dv = (torch.empty(B, S, H, 128, dtype=q4.dtype, device=q4.device) for _ in range(3))
+        scratch = torch.empty((2 + 128) * B * H * S, dtype=torch.float32, device=q4.device)
+        hs = sched_b.stride(0) if sched_b.shape[0] > 1 else 0
+        N.check(N.cuda_lib().dsb_flash_attn_bwd2_ex(
+            N.ptr(do4), N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), N.ptr(scratch), N.ptr(dq), N.ptr(dk),
+            N.ptr(dv), B, S, H, 128, _strides(do4, q4, k4, v4, out, dq, dk, dv), scale, 0, N.dtype_code(q4.dtype),
+            N.ptr(sched_b), hs, sched_b.stride(1), N.ptr(kpm), N.stream_ptr()), "dsb_flash_attn_bwd2_ex")
+        K._count(3)
+        cut = lambda t: t[..., :D].transpose(1, 2)
+        return cut(dq), cut(dk), cut(dv), None, None, None, None
+
+
+def key_mask_bias(key_padding_mask, mode, batch, seq_len):
+    """fp32 [B, S] additive bias in log2 units from a key-padding mask ("add": the mask values themselves, "mul":
+    0 where the mask is non-zero and -inf where it is zero)."""
+    if key_padding_mask is None:
+        return None
+    m = key_padding_mask.reshape(batch, seq_len).float()
+    if mode == "mul":
+        return torch.where(m == 0, torch.full_like(m, float("-inf")), torch.zeros_like(m)).contiguous()
+    return (m * _LOG2E).contiguous()
+
+
+def supported(query, block, rpe, attn_mask):
+    B, H, S, D = query.shape
+    return (query.is_cuda and query.dtype in (torch.float16, torch.bfloat16) and rpe is None and attn_mask is None
+            and S % 256 == 0 and D <= 128 and D % 8 == 0 and block % 16 == 0)

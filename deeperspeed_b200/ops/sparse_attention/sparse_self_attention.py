@@ -2,11 +2,14 @@
 embedding, key-padding and attention masks), context = DSD(P V).
 API per reference deepspeed/ops/sparse_attention/sparse_self_attention.py:14-174 (constructor arguments, `get_layout`,
 `get_ops`, mask handling, [batch, heads, seq, head_dim] operands). Unlike the reference, the per-length operator cache
-is keyed by the layout as well, so modules with different sparsity configs never pick up each other's operators."""
+is keyed by the layout as well, so modules with different sparsity configs never pick up each other's operators.
+Calls without rpe / dense attention mask on sequences that are multiples of 256 run as ONE block-sparse flash kernel per
+direction on the tensor cores (fused.py); everything else uses the three separate operators."""
 import torch
 import torch.distributed as dist
 import torch.nn as nn
 
+from . import fused
 from .matmul import MatMul
 from .softmax import Softmax
 from .sparsity_config import SparsityConfig
@@ -14,6 +17,8 @@ from .sparsity_config import SparsityConfig
 
 class SparseSelfAttention(nn.Module):
     ops = dict()      # (seq_len, block, layout fingerprint) -> (sdd, dsd, softmax)
+    schedules = dict()  # (seq_len, block, layout fingerprint, device) -> (forward, backward) schedules of the fused kernel
+    use_fused = True  # one tcgen05 flash kernel per direction when the call qualifies (ops/sparse_attention/fused.py)
 
     def __init__(self, sparsity_config=SparsityConfig(num_heads=4), key_padding_mask_mode="add", attn_mask_mode="mul",
                  max_seq_length=2048):
@@ -46,6 +51,13 @@ class SparseSelfAttention(nn.Module):
         return self.master_layout[..., :n, :n].cpu()
 
     def get_ops(self, H, L):
+        memo = self.__dict__.setdefault("_ops_memo", {})
+        if L in memo:           # the layout of a module never changes after its one-time synchronisation: skip the
+            return memo[L]      # copy + fingerprint of the (possibly tens of MB) layout on every call
+        memo[L] = self._get_ops_uncached(H, L)
+        return memo[L]
+
+    def _get_ops_uncached(self, H, L):
         layout = self.get_layout(L)
         block = self.sparsity_config.block
         key = (L, block, hash(layout.numpy().tobytes()))
@@ -55,6 +67,22 @@ class SparseSelfAttention(nn.Module):
                       MatMul(layout, block, "dsd", trans_a=False, trans_b=False),     # sparse P, dense V -> context
                       Softmax(layout, block))
             SparseSelfAttention.ops[key] = cached
+        return cached
+
+    def get_schedules(self, L, device):
+        memo = self.__dict__.setdefault("_sched_memo", {})
+        if (L, str(device)) not in memo:
+            memo[(L, str(device))] = self._get_schedules_uncached(L, device)
+        return memo[(L, str(device))]
+
+    def _get_schedules_uncached(self, L, device):
+        layout = self.get_layout(L)
+        block = self.sparsity_config.block
+        key = (L, block, hash(layout.numpy().tobytes()), str(device))
+        cached = SparseSelfAttention.schedules.get(key)
+        if cached is None:
+            fwd, bwd = fused.build_schedules(layout, block, L)
+            cached = SparseSelfAttention.schedules[key] = (fwd.to(device), bwd.to(device))
         return cached
 
     # ---- operand helpers
@@ -83,6 +111,10 @@ class SparseSelfAttention(nn.Module):
             key_padding_mask = self.transpose_mask_for_sparse(query.dtype, key_padding_mask, is_key_padding_mask=True)
         if attn_mask is not None:
             attn_mask = self.transpose_mask_for_sparse(query.dtype, attn_mask)
+        if self.use_fused and fused.supported(query, self.sparsity_config.block, rpe, attn_mask):
+            sched_f, sched_b = self.get_schedules(seq, query.device)
+            bias = fused.key_mask_bias(key_padding_mask, self.key_padding_mask_mode, query.shape[0], seq)
+            return fused.BlockSparseFlashFn.apply(query, key, value, sched_f, sched_b, bias, float(head_dim) ** -0.5)
         scores_op, context_op, softmax_op = self.get_ops(heads, seq)
         probs = softmax_op(scores_op(query, key), scale=float(head_dim) ** -0.5, rpe=rpe,
                            key_padding_mask=key_padding_mask, attn_mask=attn_mask,

@@ -128,6 +128,19 @@ int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void
                         float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D, const long* strides,
                         float scale, int causal, int dtype, const float* rot_cos, const float* rot_sin, int rot_dim,
                         void* stream);
+/* Block-sparse / masked variants (S a multiple of 256): `sched` is a device int32 schedule of the visible 64-key blocks
+ * per (head, 256-row query block) with one 32-bit visibility word per 128 x 64 tile (16 x 16 granularity); `kpm` an
+ * additive key mask [B, S] in log2 units. The backward takes the transposed schedule (per 128-key block, the 64-row
+ * query blocks that see it). Record layouts: csrc/transformer/flash_attn.cu. The kernels skip every tile that is not
+ * listed, so time scales with the layout's density.
+ * Reference: deepspeed/ops/sparse_attention/{matmul,softmax}.py + trsrc/*.tr (SDD + softmax + DSD as separate kernels). */
+int dsb_flash_attn_fwd_ex(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
+                          const long* strides, float scale, int causal, int dtype, const int* sched, int sched_hstride,
+                          int sched_pstride, const float* kpm, void* stream);
+int dsb_flash_attn_bwd2_ex(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                           const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D,
+                           const long* strides, float scale, int causal, int dtype, const int* sched, int sched_hstride,
+                           int sched_pstride, const float* kpm, void* stream);
 /* Experiment switches of the second-generation kernels (0 = production); see csrc/transformer/flash_attn_v2.cu. */
 void dsb_flash_attn_debug_mode(int mode);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */

@@ -167,3 +167,100 @@ def test_sparse_self_attention_cpu():
 @pytest.mark.gpu
 def test_sparse_self_attention_gpu():
     _attn_case("cuda", torch.float16)
+
+
+# ----------------------------------------------------------------------------------------------- fused flash path
+def test_fused_schedules_cover_exactly_the_layout():
+    """Every visible 16 x 16 block of the layout has its bit in exactly one listed tile, forward and backward."""
+    from deeperspeed_b200.ops.sparse_attention.fused import build_schedules
+    torch.manual_seed(3)
+    S, block, H = 512, 32, 3
+    nb = S // block
+    layout = (torch.rand(H, nb, nb) < 0.25).long()
+    layout[:, torch.arange(nb), torch.arange(nb)] = 1
+    sub = layout.repeat_interleave(block // 16, 1).repeat_interleave(block // 16, 2)     # 16-granular visibility
+    fwd, bwd = build_schedules(layout, block, S)
+    assert fwd.shape[:2] == (H, S // 256) and bwd.shape[:2] == (H, S // 128)
+    seen_f, seen_b = torch.zeros_like(sub), torch.zeros_like(sub)
+    for h in range(H):
+        for p in range(S // 256):
+            rec = fwd[h, p].tolist()
+            for e in range(rec[0]):
+                kb, words = rec[1 + 3 * e], rec[2 + 3 * e:4 + 3 * e]
+                for t, w in enumerate(words):
+                    for bit in range(32):
+                        if (w >> bit) & 1:
+                            seen_f[h, p * 16 + t * 8 + bit // 4, kb * 4 + bit % 4] += 1
+        for jb in range(S // 128):
+            rec = bwd[h, jb].tolist()
+            for e in range(rec[0]):
+                qb, w = rec[1 + 2 * e], rec[2 + 2 * e]
+                for bit in range(32):
+                    if (w >> bit) & 1:
+                        seen_b[h, qb * 4 + bit % 4, jb * 8 + bit // 4] += 1
+    assert torch.equal(seen_f, sub) and torch.equal(seen_b, sub)
+    # identical layouts on every head collapse to one record set
+    f1, b1 = build_schedules(layout[:1].expand(H, -1, -1).contiguous(), block, S)
+    assert f1.shape[0] == 1 and b1.shape[0] == 1
+
+
+def _fused_case(S, D, block, per_head, key_mask, dtype=torch.float16):
+    from deeperspeed_b200.ops.sparse_attention import VariableSparsityConfig
+    torch.manual_seed(4)
+    Bz, H = 2, 4
+    if per_head:
+        cfg = VariableSparsityConfig(num_heads=H, block=block, different_layout_per_head=True, num_random_blocks=2,
+                                     local_window_blocks=[2], global_block_indices=[0])
+    else:
+        cfg = FixedSparsityConfig(num_heads=H, block=block, num_local_blocks=4, num_global_blocks=1,
+                                  attention="unidirectional")
+    SparseSelfAttention.ops.clear()
+    SparseSelfAttention.schedules.clear()
+    attn = SparseSelfAttention(cfg, max_seq_length=S).cuda()
+    q, k, v = ((torch.randn(Bz, H, S, D, device="cuda") * 0.7).to(dtype).requires_grad_() for _ in range(3))
+    kpm = None
+    if key_mask:
+        kpm = torch.zeros(Bz, S, device="cuda", dtype=dtype)
+        kpm[:, -37:] = -10000.0
+    out = attn(q, k, v, key_padding_mask=kpm)
+    assert "BlockSparseFlashFn" in type(out.grad_fn).__name__ or "Transpose" in type(out.grad_fn).__name__
+    g = torch.randn_like(out)
+    out.backward(g)
+    layout = attn.get_layout(S)
+    vis = sparse_to_dense(torch.ones(1, int(layout.sum()), block, block), layout, block)[0].bool().cuda()
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    sc = (qf @ kf.transpose(-1, -2)) * D ** -0.5
+    if kpm is not None:
+        sc = sc + kpm.float()[:, None, None, :]
+    sc = sc.masked_fill(~vis[None], float("-inf"))
+    ref = torch.softmax(sc, -1) @ vf
+    ref.backward(g.float())
+    assert (out.float() - ref).abs().max() < 3e-3
+    for got, want in ((q.grad, qf.grad), (k.grad, kf.grad), (v.grad, vf.grad)):
+        assert (got.float() - want).abs().max() < 2e-2 * max(1.0, want.abs().max().item())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("S,D,block", [(256, 64, 16), (512, 64, 32), (768, 128, 16), (1024, 32, 64)])
+@pytest.mark.parametrize("per_head", [False, True])
+@pytest.mark.parametrize("key_mask", [False, True])
+def test_fused_block_sparse_attention(S, D, block, per_head, key_mask):
+    """The tcgen05 block-sparse flash path (forward + backward) against dense masked fp32 attention."""
+    _fused_case(S, D, block, per_head, key_mask)
+
+
+@pytest.mark.gpu
+def test_fused_block_sparse_attention_falls_back_for_rpe():
+    """Relative position embeddings are not part of the fused kernel: the three separate operators run."""
+    torch.manual_seed(5)
+    cfg = FixedSparsityConfig(num_heads=2, block=16, num_local_blocks=4, num_global_blocks=1)
+    attn = SparseSelfAttention(cfg, max_seq_length=256).cuda()
+    q, k, v = ((torch.randn(1, 2, 256, 64, device="cuda") * 0.5).half() for _ in range(3))
+    rpe = (torch.randn(2, 256, 256, device="cuda") * 0.1).half()
+    a = attn(q, k, v, rpe=rpe)
+    SparseSelfAttention.use_fused = False
+    try:
+        b = attn(q, k, v, rpe=rpe)
+    finally:
+        SparseSelfAttention.use_fused = True
+    assert torch.equal(a, b)
