@@ -1025,8 +1025,8 @@ static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out
     dim3 grid(S / BQ, B * H);
     cudaError_t e;
     const bool extras = sched != nullptr || kpm != nullptr;
-    if (extras && S % 256) return DSB_ERR_SIZE;      // only the two-tile kernel knows schedules and key masks
-    if ((g_fa_fwd_variant == 2 || extras) && S % 256 == 0) {
+    if (sched != nullptr && S % 256) return DSB_ERR_SIZE;   // schedules are per 256-row query block
+    if (g_fa_fwd_variant == 2 || extras) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
         if (rc) return rc;
         rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);

@@ -266,7 +266,9 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
     // visibility word has one bit per (16-row query group, 16-key group) of a 128 x 64 tile: bit = qgroup * 4 + kgroup.
     const int* sc = sched != nullptr ? sched + (long)h * sched_hstride + (long)pr * sched_pstride : nullptr;
     const int nA = sc ? sc[0] : (causal ? (q0 + F_BQ) / F_BK : S / F_BK);
-    const int nB = sc ? sc[0] : (causal ? (q0 + 2 * F_BQ) / F_BK : S / F_BK);
+    const bool tileB = q0 + F_BQ < S;             // S % 256 == 128: the last CTA has only its first tile
+    const int nB = !tileB ? 0 : (sc ? sc[0] : (causal ? (q0 + 2 * F_BQ) / F_BK : S / F_BK));
+    const int nmax = nA > nB ? nA : nB;
     auto key_block = [&](int j) { return sc ? sc[1 + 3 * j] : j; };
     // phase timers of CTA (0, 0) (the longest one), only when a buffer is registered with dsb_flash_attn_debug_timers
     const bool tm = prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
@@ -307,12 +309,12 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
 
     if (warp == 0) {
         if (elect_one()) {
-            for (int t = 0; t < 2; ++t) {
+            for (int t = 0; t < (tileB ? 2 : 1); ++t) {
                 mbar_arrive_expect_tx(&q_full[t], F_QTILE);
                 tma_load_4d(sQ + t * F_QTILE, &tmQ, &q_full[t], 0, h, q0 + t * F_BQ, b);
                 tma_load_4d(sQ + t * F_QTILE + F_QCHUNK, &tmQ, &q_full[t], 64, h, q0 + t * F_BQ, b);
             }
-            for (int j = 0; j < nB; ++j) {
+            for (int j = 0; j < nmax; ++j) {
                 const int st = j % F_NS;
                 if (j >= F_NS) mbar_wait(&k_empty[st], ((j / F_NS) - 1) & 1);
                 if ((dbg & 32) && j >= F_NS) { mbar_arrive(&k_full[st]); continue; }
@@ -324,7 +326,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         }
     } else if (warp == 3) {
         if (elect_one()) {
-            for (int j = 0; j < nB; ++j) {
+            for (int j = 0; j < nmax; ++j) {
                 const int st = j % F_NS;
                 if (j >= F_NS) mbar_wait(&v_empty[st], ((j / F_NS) - 1) & 1);
                 if ((dbg & 32) && j >= F_NS) { mbar_arrive(&v_full[st]); continue; }
@@ -370,10 +372,12 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             if (j == n - 1) umma_commit_p(lead, &o_final[t]);
         };
         const bool tmw = tm && lead;
-        mbar_wait(&q_full[t], 0);
-        mbar_wait(&k_full[0], 0);
-        tc_fence_after();
-        issue_s(0);
+        if (n > 0) {
+            mbar_wait(&q_full[t], 0);
+            mbar_wait(&k_full[0], 0);
+            tc_fence_after();
+            issue_s(0);
+        }
         t0 = clock64();
         const long long t_begin = t0;
         for (int j = 0; j < n; ++j) {
@@ -398,7 +402,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             prof[30 + t] = clock64() - t_begin;
             prof[28 + t] = n;
         }
-        for (int j = n; j < nB; ++j) {   // blocks only the other tile works on: keep the two-arrival stage protocol going
+        for (int j = n; j < nmax; ++j) {   // blocks only the other tile works on: keep the two-arrival stage protocol going
             mbar_wait(&k_full[j % F_NS], (j / F_NS) & 1);
             mbar_arrive_p(lead, &k_empty[j % F_NS]);
             mbar_wait(&v_full[j % F_NS], (j / F_NS) & 1);
@@ -543,6 +547,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             for (int i = 0; i < 6; ++i) prof[t * 8 + i] = acc[i];
         // epilogue: O / l -> shared (the tile's Q buffer, same swizzled layout) -> TMA store; log-sum-exp for backward
         // (a parity wait on pv_done would be ambiguous here: this thread may be two products behind)
+        if (n > 0) {
         mbar_wait(&o_final[t], 0);
         tc_fence_after();
         const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
@@ -573,6 +578,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             tma_store_commit();
             tma_store_wait<0>();
         }
+        }   // n > 0
     }
     tc_fence_before();
     __syncthreads();
@@ -1082,8 +1088,8 @@ void set_debug_timers(long long* p) { g_prof = p; }
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
                int B, int S, int H, float scale_log2, int causal, int bf16, const int* sched, int sched_hstride,
                int sched_pstride, const float* kpm, cudaStream_t stream) {
-    if (S % 256) return DSB_ERR_SIZE;
-    dim3 grid(B * H, S / 256);
+    if (S % 128) return DSB_ERR_SIZE;
+    dim3 grid(B * H, (S + 255) / 256);
     cudaError_t e;
     if (bf16) {
         auto kern = flash_fwd2_kernel<__nv_bfloat16>;

@@ -163,20 +163,25 @@ template <typename T, int ITERS, int R>
 __global__ void __launch_bounds__(LN_THREADS, ITERS == 1 ? 2 : 1)
 ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean,
               const float* __restrict__ rstd, const T* __restrict__ gamma, const T* __restrict__ dres,
-              T* __restrict__ dx, float* __restrict__ part_g, float* __restrict__ part_b, long rows, int hidden) {
+              T* __restrict__ dx, float* __restrict__ part_g, float* __restrict__ part_b, long rows, int hidden,
+              const T* __restrict__ beta_inv) {
+    // beta_inv != nullptr: "invertible" mode. `x` then holds the layer's OUTPUT y and the normalised input is recovered
+    // as (y - beta) / gamma, so the forward pass does not have to keep its input (mean is unused, rstd still needed).
     __shared__ float sh[2 * LN_WARPS * 2 * R];
     int flip = 0;
     const int nvec = hidden >> 3;
     const float inv_h = 1.f / hidden;
     const long stride = (long)gridDim.x * R;
     float accg[ITERS][8], accb[ITERS][8];
-    uint4 graw[ITERS];
+    uint4 graw[ITERS], braw[ITERS];
+    const bool inv = beta_inv != nullptr;
 #pragma unroll
     for (int it = 0; it < ITERS; ++it) {
         const int i = threadIdx.x + it * LN_THREADS;
 #pragma unroll
         for (int k = 0; k < 8; ++k) { accg[it][k] = 0.f; accb[it][k] = 0.f; }
         graw[it] = i < nvec ? __ldg(reinterpret_cast<const uint4*>(gamma) + i) : make_uint4(0, 0, 0, 0);
+        braw[it] = (inv && i < nvec) ? __ldg(reinterpret_cast<const uint4*>(beta_inv) + i) : make_uint4(0, 0, 0, 0);
     }
     uint4 cx[R][ITERS], cdy[R][ITERS], cdr[R][ITERS];
     float cmu[R], crs[R];
@@ -211,14 +216,15 @@ ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __
             float s1 = 0.f, s2 = 0.f;
 #pragma unroll
             for (int it = 0; it < ITERS; ++it) {
-                float xv[8], dyv[8], g8[8];
+                float xv[8], dyv[8], g8[8], b8[8];
                 unpack8<T>(cx[r][it], xv);
                 unpack8<T>(cdy[r][it], dyv);
                 unpack8<T>(graw[it], g8);
+                unpack8<T>(braw[it], b8);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
                     // rows past the end have rs = 0 and dy = 0 -> contribute nothing
-                    const float xh = (xv[k] - cmu[r]) * crs[r];
+                    const float xh = inv ? (g8[k] != 0.f ? (xv[k] - b8[k]) / g8[k] : 0.f) : (xv[k] - cmu[r]) * crs[r];
                     accg[it][k] += dyv[k] * xh;
                     accb[it][k] += dyv[k];
                     const float dg = dyv[k] * g8[k];
@@ -239,13 +245,15 @@ ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __
                 for (int it = 0; it < ITERS; ++it) {
                     const int i = threadIdx.x + it * LN_THREADS;
                     if (i < nvec) {
-                        float xv[8], dyv[8], g8[8], o[8];
+                        float xv[8], dyv[8], g8[8], b8[8], o[8];
                         unpack8<T>(cx[r][it], xv);
                         unpack8<T>(cdy[r][it], dyv);
                         unpack8<T>(graw[it], g8);
+                        unpack8<T>(braw[it], b8);
 #pragma unroll
                         for (int k = 0; k < 8; ++k) {
-                            const float xh = (xv[k] - cmu[r]) * crs[r];
+                            const float xh = inv ? (g8[k] != 0.f ? (xv[k] - b8[k]) / g8[k] : 0.f)
+                                                 : (xv[k] - cmu[r]) * crs[r];
                             o[k] = (dyv[k] * g8[k] - s1 - xh * s2) * crs[r];
                         }
                         if (dres) {
@@ -345,9 +353,9 @@ extern "C" int dsb_layernorm_fwd(const void* x, const void* residual, const void
 extern "C" long dsb_layernorm_bwd_scratch_bytes(int hidden) { return 2L * LN_BWD_BLOCKS * hidden * sizeof(float); }
 
 // accumulate != 0: dgamma/dbeta += (they point at the parameters' gradient buffers) instead of being overwritten.
-extern "C" int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float* mean, const float* rstd,
-                                     const void* gamma, const void* dres, void* dx, void* dgamma, void* dbeta,
-                                     long rows, int hidden, int dtype, int accumulate, void* scratch, void* stream) {
+static int ln_bwd_impl(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
+                       const void* beta_inv, const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden,
+                       int dtype, int accumulate, void* scratch, void* stream) {
     if (rows <= 0) return 0;
     if (hidden % 8 || hidden > LN_THREADS * 8 * LN_MAX_ITERS) return DSB_ERR_SIZE;
     if (!scratch) return DSB_ERR_ARG;
@@ -359,7 +367,7 @@ extern "C" int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float*
     const int grid = (int)(groups < cap ? groups : cap);
     float* pg = reinterpret_cast<float*>(scratch);
     float* pb = pg + (long)LN_BWD_BLOCKS * hidden;
-#define LNB(T, I, RR) ln_bwd_kernel<T, I, RR><<<grid, LN_THREADS, 0, s>>>((const T*)dy, (const T*)x, mean, rstd, (const T*)gamma, (const T*)dres, (T*)dx, pg, pb, rows, hidden)
+#define LNB(T, I, RR) ln_bwd_kernel<T, I, RR><<<grid, LN_THREADS, 0, s>>>((const T*)dy, (const T*)x, mean, rstd, (const T*)gamma, (const T*)dres, (T*)dx, pg, pb, rows, hidden, (const T*)beta_inv)
 #define LNB_D(T) do { if (iters <= 1) LNB(T, 1, 2); else if (iters <= 2) LNB(T, 2, 1); else LNB(T, 4, 1); \
         ln_bwd_finalize<T><<<(hidden + 31) / 32, 32 * FIN_SLICES, 0, s>>>(pg, pb, grid, hidden, (T*)dgamma, (T*)dbeta, accumulate); } while (0)
     if (dtype == DSB_DTYPE_F16) LNB_D(__half);
@@ -369,6 +377,23 @@ extern "C" int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float*
 #undef LNB
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float* mean, const float* rstd,
+                                     const void* gamma, const void* dres, void* dx, void* dgamma, void* dbeta,
+                                     long rows, int hidden, int dtype, int accumulate, void* scratch, void* stream) {
+    return ln_bwd_impl(dy, x, mean, rstd, gamma, nullptr, dres, dx, dgamma, dbeta, rows, hidden, dtype, accumulate,
+                       scratch, stream);
+}
+
+// Invertible variant: takes the layer's OUTPUT y (plus gamma, beta, rstd) instead of its input; the forward pass can
+// drop the input. Reference: the *_invertible kernels of csrc/transformer/normalize_kernels.cu:602-672,1056-1348.
+extern "C" int dsb_layernorm_bwd_inv(const void* dy, const void* y, const float* rstd, const void* gamma,
+                                     const void* beta, const void* dres, void* dx, void* dgamma, void* dbeta, long rows,
+                                     int hidden, int dtype, int accumulate, void* scratch, void* stream) {
+    if (!beta) return DSB_ERR_ARG;
+    return ln_bwd_impl(dy, y, rstd /* unused mean */, rstd, gamma, beta, dres, dx, dgamma, dbeta, rows, hidden, dtype,
+                       accumulate, scratch, stream);
 }
 
 extern "C" int dsb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,

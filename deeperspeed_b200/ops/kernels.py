@@ -378,6 +378,50 @@ class LayerNormFn(torch.autograd.Function):
         return dx, (dx if ctx.has_res else None), dgamma, dbeta, None
 
 
+class LayerNormInvertibleFn(torch.autograd.Function):
+    """y = LN(x) keeping only y (and rstd) for backward: the kernel recovers x-hat = (y - beta) / gamma. Saves the
+    activation-sized input tensor per LayerNorm (DeepSpeedTransformerConfig.normalize_invertible)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        hidden = x.shape[-1]
+        x2 = x.reshape(-1, hidden)
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        N.check(N.cuda_lib().dsb_layernorm_fwd(N.ptr(x2), 0, N.ptr(gamma), N.ptr(beta), N.ptr(y), 0, N.ptr(mean),
+                                               N.ptr(rstd), rows, hidden, float(eps), N.dtype_code(x.dtype),
+                                               N.stream_ptr()), "dsb_layernorm_fwd")
+        _count()
+        ctx.save_for_backward(y, rstd, gamma, beta)
+        ctx.shape = x.shape
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        y, rstd, gamma, beta = ctx.saved_tensors
+        rows, hidden = y.shape
+        dy2 = dy.reshape(-1, hidden).contiguous()
+        dx = torch.empty_like(y)
+        dgamma, dbeta = torch.empty_like(gamma), torch.empty_like(gamma)
+        lib = N.cuda_lib()
+        sc = N.scratch(lib.dsb_layernorm_bwd_scratch_bytes(hidden), y.device, "ln_bwd")
+        N.check(lib.dsb_layernorm_bwd_inv(N.ptr(dy2), N.ptr(y), N.ptr(rstd), N.ptr(gamma), N.ptr(beta), 0, N.ptr(dx),
+                                          N.ptr(dgamma), N.ptr(dbeta), rows, hidden, N.dtype_code(y.dtype), 0,
+                                          N.ptr(sc), N.stream_ptr()), "dsb_layernorm_bwd_inv")
+        _count(2)
+        return dx.view(ctx.shape), dgamma, dbeta, None
+
+
+def layer_norm_invertible(x, gamma, beta, eps=1e-5):
+    """LayerNorm whose backward needs only its output (see LayerNormInvertibleFn); plain LN where the kernel is absent."""
+    if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16) and x.shape[-1] % 8 == 0 and x.shape[-1] <= 8192:
+        N.cuda_lib()
+        return LayerNormInvertibleFn.apply(x, gamma, beta, eps)
+    return F.layer_norm(x, (x.shape[-1],), gamma, beta, eps)
+
+
 def layer_norm(x, gamma, beta, eps=1e-5, residual=None):
     """Returns (LN(x + residual), x + residual). With residual=None the second output is an alias of x: use it (not
     x) as the residual stream downstream so the stream's gradient is folded into the LN backward kernel."""

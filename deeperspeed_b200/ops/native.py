@@ -37,6 +37,7 @@ _CUDA_SIGS = {
     "dsb_layernorm_fwd": [_p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _f, _i, _p],
     "dsb_layernorm_bwd": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _p, _p],
     "dsb_layernorm_bwd_acc": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _i, _p, _p],
+    "dsb_layernorm_bwd_inv": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _i, _i, _i, _p, _p],
     "dsb_softmax_fwd": [_p, _p, _p, _i, _i, _i, _i, _f, _i, _i, _p],
     "dsb_softmax_bwd": [_p, _p, _p, _l, _i, _f, _i, _p],
     "dsb_bias_gelu_fwd": [_p, _p, _p, _l, _i, _i, _p],

@@ -90,8 +90,17 @@ def _strides(*tensors):
     return (C.c_long * (3 * len(tensors)))(*[t.stride(i) for t in tensors for i in range(3)])
 
 
+def _sched_strides(sched):
+    """(head stride, block stride) of a schedule tensor in int32 elements; (0, 0) without a schedule (dense attention),
+    head stride 0 when all heads share one layout."""
+    if sched is None:
+        return 0, 0
+    return (sched.stride(0) if sched.shape[0] > 1 else 0), sched.stride(1)
+
+
 class BlockSparseFlashFn(torch.autograd.Function):
-    """context = softmax(scale * Q K^T restricted to the layout (+ key mask)) V for [B, H, S, D] operands."""
+    """context = softmax(scale * Q K^T restricted to the layout (+ key mask)) V for [B, H, S, D] operands. Without
+    schedules it is plain (non-causal) attention with an optional additive key mask."""
 
     @staticmethod
     def forward(ctx, q, k, v, sched_f, sched_b, kpm, scale):
@@ -99,10 +108,10 @@ class BlockSparseFlashFn(torch.autograd.Function):
         q4, k4, v4 = _as_bshd128(q), _as_bshd128(k), _as_bshd128(v)
         out = torch.empty(B, S, H, 128, dtype=q.dtype, device=q.device)
         lse = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
-        hs = sched_f.stride(0) if sched_f.shape[0] > 1 else 0
+        hs, ps = _sched_strides(sched_f)
         N.check(N.cuda_lib().dsb_flash_attn_fwd_ex(
             N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), B, S, H, 128, _strides(q4, k4, v4, out),
-            float(scale), 0, N.dtype_code(q.dtype), N.ptr(sched_f), hs, sched_f.stride(1), N.ptr(kpm), N.stream_ptr()),
+            float(scale), 0, N.dtype_code(q.dtype), N.ptr(sched_f), hs, ps, N.ptr(kpm), N.stream_ptr()),
             "dsb_flash_attn_fwd_ex")
         K._count()
         ctx.save_for_backward(q4, k4, v4, out, lse, sched_b, kpm)
@@ -117,11 +126,11 @@ class BlockSparseFlashFn(torch.autograd.Function):
         do4 = _as_bshd128(dctx)
         dq, dk, dv = (torch.empty(B, S, H, 128, dtype=q4.dtype, device=q4.device) for _ in range(3))
         scratch = torch.empty((2 + 128) * B * H * S, dtype=torch.float32, device=q4.device)
-        hs = sched_b.stride(0) if sched_b.shape[0] > 1 else 0
+        hs, ps = _sched_strides(sched_b)
         N.check(N.cuda_lib().dsb_flash_attn_bwd2_ex(
             N.ptr(do4), N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), N.ptr(scratch), N.ptr(dq), N.ptr(dk),
             N.ptr(dv), B, S, H, 128, _strides(do4, q4, k4, v4, out, dq, dk, dv), scale, 0, N.dtype_code(q4.dtype),
-            N.ptr(sched_b), hs, sched_b.stride(1), N.ptr(kpm), N.stream_ptr()), "dsb_flash_attn_bwd2_ex")
+            N.ptr(sched_b), hs, ps, N.ptr(kpm), N.stream_ptr()), "dsb_flash_attn_bwd2_ex")
         K._count(3)
         cut = lambda t: t[..., :D].transpose(1, 2)
         return cut(dq), cut(dk), cut(dv), None, None, None, None

@@ -9,8 +9,19 @@ cuBLAS handles and a workspace, the layer is a composition of fused autograd ops
   -> tcgen05 GEMM (out-proj) -> bias+dropout+residual kernel -> LN kernel -> tcgen05 GEMM with bias+GeLU epilogue
   -> tcgen05 GEMM (FF2) -> bias+dropout+residual kernel.
 
-Memory flags: `gelu_checkpoint`, `attn_dropout_checkpoint` and `normalize_invertible` are honoured by recomputing the
-corresponding segment in backward (activation recompute) rather than by special-cased kernels."""
+Attention core: when attention dropout is inactive (ratio 0 or eval) the scores / softmax / context chain is ONE
+tcgen05 flash-attention kernel per direction (csrc/transformer/flash_attn_v2.cu): q / k / v are read from the fused QKV
+activation, the additive attention mask rides along as a per-key bias, head dims below 128 are zero-padded. With
+attention dropout active the chain runs as batched GEMM + masked softmax + Philox dropout + batched GEMM.
+
+Memory flags: `gelu_checkpoint` and `attn_dropout_checkpoint` recompute their segment in backward;
+`normalize_invertible` uses the LayerNorm whose backward kernel recovers the normalised input from the OUTPUT
+(`K.layer_norm_invertible`), so the LayerNorm inputs are not kept (pre-LN layers; post-LN layers need the sum for the
+residual stream anyway). `stochastic_mode` selects the reference's relaxed-synchronisation kernel build (about 2 %
+faster, non-deterministic); every kernel here is already launched asynchronously on one stream without host
+synchronisation, there is nothing to relax, so the flag is accepted and changes nothing (a warning says so once).
+fp32 layers: the GEMMs and fused kernels are 16-bit; an fp32 layer runs on torch's fp32 ops (TF32 is not enabled
+behind the user's back), which is what the reference's fp32 instantiation computes."""
 import json
 import math
 
@@ -177,6 +188,7 @@ class DeepSpeedTransformerLayer(nn.Module):
         initial_weights / initial_biases: optional [q, k, v, attn_out, attn_norm, inter, output, norm] tensors
             (used by module injection and by the unit tests to start from a reference BERT layer)."""
     layer_id = 0
+    _warned_stochastic = False
 
     def __init__(self, config, initial_weights=None, initial_biases=None):
         super().__init__()
@@ -215,6 +227,11 @@ class DeepSpeedTransformerLayer(nn.Module):
             self.norm_b = initial_biases[7]
         if torch.cuda.is_available():
             N.cuda_lib()   # fail loudly at construction time if the kernel library is missing on a GPU box
+        if config.stochastic_mode and not DeepSpeedTransformerLayer._warned_stochastic:
+            DeepSpeedTransformerLayer._warned_stochastic = True
+            from ...utils.logging import logger
+            logger.warning("DeepSpeedTransformerLayer: stochastic_mode has no separate kernel build here (all kernels "
+                           "already run asynchronously on one stream); the flag is accepted and ignored")
 
     def init_transformer_weights(self, adjust_init_range=False):
         num_layers = self.config.num_hidden_layers
@@ -237,9 +254,22 @@ class DeepSpeedTransformerLayer(nn.Module):
         self.norm_b.data.zero_()
 
     # ---- segments (each may be recomputed in backward when the matching *_checkpoint flag is set)
+    def _flash_ok(self, x):
+        cfg = self.config
+        D = cfg.hidden_size // cfg.heads
+        no_dropout = not (self.training and cfg.attn_dropout_ratio > 0.0)
+        return no_dropout and _gemm_ok(x) and D <= 128 and D % 8 == 0
+
     def _attention(self, xn, mask2d, B, S):
         cfg = self.config
         H, D = cfg.heads, cfg.hidden_size // cfg.heads
+        if self._flash_ok(xn) and S % 128 == 0:
+            from ..sparse_attention import fused
+            qkv = K.linear(xn, self.attn_qkvw, self.attn_qkvb).view(B, S, 3, H, D)      # bias in the GEMM epilogue
+            q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))                  # [B, H, S, D] views
+            bias = fused.key_mask_bias(mask2d, "add", B, S)
+            ctx = fused.BlockSparseFlashFn.apply(q, k, v, None, None, bias, 1.0 / math.sqrt(D))
+            return K.linear(ctx.transpose(1, 2).reshape(B, S, H * D), self.attn_ow, None)
         qkv = K.linear(xn, self.attn_qkvw, None)                                   # [B,S,3h]
         q, k, v = _split_heads(qkv, self.attn_qkvb, B, S, H, D)                    # [B,H,S,D]
         scores = matmul(q.reshape(B * H, S, D), k.reshape(B * H, S, D), trans_b=True, alpha=1.0 / math.sqrt(D))
@@ -262,8 +292,9 @@ class DeepSpeedTransformerLayer(nn.Module):
         cfg = self.config
         x = hidden_states
         B, S, h = x.shape
-        # pad the sequence to a multiple of 16 (tensor-core friendly), masking the padded keys out
-        pad = (-S) % 16 if x.is_cuda else 0
+        # pad the sequence to the kernels' granularity (128 rows for the flash-attention path, 16 otherwise) and mask the
+        # padded keys out
+        pad = ((-S) % (128 if self._flash_ok(x) else 16)) if x.is_cuda else 0
         mask2d = None
         if attention_mask is not None:
             mask2d = attention_mask.reshape(B, -1)[:, -S:].to(x.dtype).contiguous()
@@ -275,10 +306,14 @@ class DeepSpeedTransformerLayer(nn.Module):
         eps = cfg.layer_norm_eps
         ck = _maybe_checkpoint
         if cfg.pre_layer_norm:
-            xn, _ = K.layer_norm(x, self.norm_w, self.norm_b, eps)
+            if cfg.normalize_invertible:
+                norm = lambda t, w, bb: K.layer_norm_invertible(t, w, bb, eps)
+            else:
+                norm = lambda t, w, bb: K.layer_norm(t, w, bb, eps)[0]
+            xn = norm(x, self.norm_w, self.norm_b)
             a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, xn, mask2d, B, S)
             r1 = bias_dropout_residual(a, self.attn_ob, x, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
-            y, _ = K.layer_norm(r1, self.attn_nw, self.attn_nb, eps)
+            y = norm(r1, self.attn_nw, self.attn_nb)
             o = ck(cfg.gelu_checkpoint and self.training, self._ffn, y)
             out = bias_dropout_residual(o, self.output_b, r1, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
         else:

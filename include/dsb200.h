@@ -83,6 +83,12 @@ long dsb_layernorm_bwd_scratch_bytes(int hidden);
 int dsb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
                       const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden, int dtype,
                       void* scratch, void* stream);
+/* "Invertible" LayerNorm backward: the normalised input is recovered from the OUTPUT y as (y - beta) / gamma, so the
+ * forward pass does not keep its input (DeepSpeedTransformerConfig.normalize_invertible). gamma entries equal to zero
+ * contribute a zero x-hat. Reference: csrc/transformer/normalize_kernels.cu:602-672,1056-1348. */
+int dsb_layernorm_bwd_inv(const void* dy, const void* y, const float* rstd, const void* gamma, const void* beta,
+                          const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden, int dtype,
+                          int accumulate, void* scratch, void* stream);
 /* Same; accumulate != 0 adds the gamma/beta gradients into dgamma/dbeta (the parameters' .grad storage). */
 int dsb_layernorm_bwd_acc(const void* dy, const void* x, const float* mean, const float* rstd, const void* gamma,
                           const void* dres, void* dx, void* dgamma, void* dbeta, long rows, int hidden, int dtype,

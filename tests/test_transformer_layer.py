@@ -7,7 +7,7 @@ from deeperspeed_b200.models.bert import BertConfig, BertLayer, BertLayerPreLN
 from deeperspeed_b200.module_inject import replace_transformer_layer, revert_transformer_layer
 
 
-def _case(batch, hidden, seq, heads, preln, device, dtype, atol):
+def _case(batch, hidden, seq, heads, preln, device, dtype, atol, invertible=False, attn_dropout=0.0):
     torch.manual_seed(0)
     cfg = BertConfig(hidden_size=hidden, num_hidden_layers=2, num_attention_heads=heads, hidden_dropout_prob=0.0,
                      attention_probs_dropout_prob=0.0)
@@ -19,6 +19,10 @@ def _case(batch, hidden, seq, heads, preln, device, dtype, atol):
                                       preln=preln, fp16=dtype == torch.float16)
     ds_layer = model[0]
     assert type(ds_layer).__name__ == "DeepSpeedTransformerLayer"
+    ds_layer.config.normalize_invertible = invertible
+    # a non-zero ratio routes attention through the GEMM + softmax + dropout chain; the Philox kernel is then told to
+    # keep everything so that the result stays comparable with the dropout-free reference
+    ds_layer.config.attn_dropout_ratio = attn_dropout
     x = (torch.randn(batch, seq, hidden, device=device) * 0.5)
     mask = torch.zeros(batch, 1, 1, seq, device=device)
     mask[:, :, :, -3:] = -10000.0
@@ -57,12 +61,52 @@ def test_layer_cpu(preln):
     _case(2, 64, 24, 4, preln, "cpu", torch.float32, 2e-4)
 
 
+# shapes of reference tests/unit/test_cuda_forward.py:200-235 / test_cuda_backward.py:259-270 (odd sequence lengths,
+# small batches, head dims 64 / 80 / 128, hidden up to 8192)
+_SHAPES = [(8, 1024, 128, 16, True), (8, 1024, 128, 16, False), (3, 1024, 119, 16, True), (8, 1600, 128, 25, True),
+           (8, 160, 128, 2, False), (2, 2048, 512, 16, True), (8, 256, 52, 4, True), (3, 1024, 51, 16, True),
+           (3, 1024, 54, 16, False), (8, 1024, 381, 16, True), (8, 1024, 384, 16, False), (8, 1024, 119, 16, True),
+           (8, 1024, 509, 16, True), (3, 1024, 511, 16, False), (1, 1536, 128, 24, True), (1, 2560, 128, 40, False),
+           (1, 128, 2048, 2, True), (1, 8192, 128, 64, True), (64, 1024, 56, 16, False), (64, 1024, 21, 16, True)]
+
+
 @pytest.mark.gpu
-@pytest.mark.parametrize("batch,hidden,seq,heads,preln", [(8, 1024, 128, 16, True), (8, 1024, 128, 16, False),
-                                                         (3, 1024, 119, 16, True), (8, 1600, 128, 25, True),
-                                                         (8, 160, 128, 2, False), (2, 2048, 512, 16, True)])
+@pytest.mark.parametrize("batch,hidden,seq,heads,preln", _SHAPES)
 def test_layer_gpu(batch, hidden, seq, heads, preln):
+    """Attention on the tcgen05 flash kernel (mask as key bias, head dims padded to 128, sequences padded to 128)."""
     _case(batch, hidden, seq, heads, preln, "cuda", torch.float16, 2e-2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,hidden,seq,heads,preln", [(8, 1024, 128, 16, True), (3, 1024, 119, 16, False),
+                                                         (2, 2048, 512, 16, True)])
+def test_layer_gpu_unfused_attention_chain(batch, hidden, seq, heads, preln):
+    """The GEMM + masked softmax + dropout chain that serves attention dropout (keep-probability 1 - 1e-7 ~ identity)."""
+    _case(batch, hidden, seq, heads, preln, "cuda", torch.float16, 2e-2, attn_dropout=1e-7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch,hidden,seq,heads", [(8, 1024, 128, 16), (3, 1024, 119, 16), (2, 2048, 512, 16)])
+def test_layer_gpu_invertible_layernorm(batch, hidden, seq, heads):
+    """normalize_invertible: LayerNorm backward from the layer OUTPUT; same gradients as the regular layer."""
+    _case(batch, hidden, seq, heads, True, "cuda", torch.float16, 2e-2, invertible=True)
+
+
+@pytest.mark.gpu
+def test_layernorm_invertible_kernel_vs_fp32():
+    from deeperspeed_b200.ops import kernels as K
+    torch.manual_seed(3)
+    x = torch.randn(300, 1024, device="cuda").half().requires_grad_()
+    g = (torch.rand(1024, device="cuda") + 0.5).half().requires_grad_()
+    b = (torch.randn(1024, device="cuda") * 0.1).half().requires_grad_()
+    y = K.layer_norm_invertible(x, g, b, 1e-5)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xf, gf, bf = (t.detach().float().requires_grad_() for t in (x, g, b))
+    yf = torch.nn.functional.layer_norm(xf, (1024,), gf, bf, 1e-5)
+    yf.backward(dy.float())
+    rel = lambda a, r: ((a.float() - r).abs().max() / r.abs().max()).item()
+    assert rel(y, yf) < 2e-3 and rel(x.grad, xf.grad) < 1e-2 and rel(g.grad, gf.grad) < 1e-2 and rel(b.grad, bf.grad) < 1e-2
 
 
 @pytest.mark.gpu
