@@ -264,6 +264,34 @@ def run_ours(args):
     if dist.get_world_size() > 1:
         dist.all_reduce(h2d)
     sync()
+
+    # ---- exposed communication: the same device-timed steps with the bulk transfers skipped (utils/comm_stub.py);
+    # real - stubbed = transfer time (and the waiting it causes) the real step does not hide behind compute
+    exposed = None
+    if dist.get_world_size() > 1 and not args.no_exposed_comm:
+        from deeperspeed_b200.utils import comm_stub
+        comm_stub.set_enabled(True)
+        for _ in range(max(1, min(args.warmup, 2))):
+            engine.train_batch(dev_iter)
+        sync()
+        if torch.cuda.is_available():
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        t0 = time.time()
+        for _ in range(args.steps):
+            engine.train_batch(dev_iter)
+        if torch.cuda.is_available():
+            e1.record()
+            torch.cuda.synchronize()
+            ms_stub = e0.elapsed_time(e1)
+        else:
+            ms_stub = (time.time() - t0) * 1e3
+        comm_stub.set_enabled(False)
+        sync()
+        ms_stub = _max_over_ranks(ms_stub, device) / args.steps
+        exposed = {"ms_per_step": ms_per_step - ms_stub, "stubbed_ms_per_step": ms_stub,
+                   "how": "device-timed step minus the same step with pipeline p2p and ZeRO reduce-scatter / "
+                          "all-gather skipped (max over ranks both)"}
     if rank == 0:
         value = tokens_per_step / (ms_per_step / 1e3)
         e2e_value = tokens_per_step / (ms_e2e / args.steps / 1e3)
@@ -283,6 +311,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": loss_bytes / args.steps, "ms_per_step": ms_e2e / args.steps,
                     "last_loss": lv},
             "gpu_launches": launches,
+            "exposed_comm": exposed,
         }
         print(json.dumps(out), flush=True)
     dist.barrier()
@@ -305,6 +334,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--no-exposed-comm", dest="no_exposed_comm", action="store_true",
+                    help="skip the extra stubbed-communication pass that measures exposed comm per step (N > 1)")
     ap.add_argument("--no-autotune", dest="no_autotune", action="store_true", help="skip the GEMM variant autotune")
     ap.add_argument("--verbose", action="store_true")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])

@@ -7,6 +7,7 @@
 // `dsb_gemm_auto` is the entry point the framework calls: tuned problems use their recorded variant, everything else
 // a static rule.
 #include <cuda_runtime.h>
+#include <atomic>
 #include <mutex>
 #include <unordered_map>
 #include <cstdint>
@@ -40,6 +41,7 @@ struct KeyHash {
 };
 std::unordered_map<Key, int, KeyHash> g_table;
 std::mutex g_mu;
+std::atomic<bool> g_nonempty{false};      // read without the lock on the dispatch path
 
 int run_variant(int variant, const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb,
                 long ldd, long sA, long sB, long sD, int a_mn, int b_mn, int dtype, int epi, float alpha,
@@ -116,6 +118,7 @@ extern "C" int dsb_gemm_tune(int M, int N, int K, int batch, int a_mn, int b_mn,
     {
         std::lock_guard<std::mutex> lk(g_mu);
         g_table[Key{M, N, K, batch, a_mn * 2 + b_mn, dtype}] = best;
+        g_nonempty.store(true, std::memory_order_release);
     }
     return best;
 }
@@ -130,6 +133,7 @@ extern "C" int dsb_gemm_tuned_variant(int M, int N, int K, int batch, int a_mn, 
 extern "C" void dsb_gemm_tune_clear(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     g_table.clear();
+    g_nonempty.store(false, std::memory_order_release);
 }
 
 // Same contract as dsb_gemm; picks the kernel variant (tuned table first, static rule otherwise).
@@ -138,7 +142,7 @@ extern "C" int dsb_gemm_auto(const void* A, const void* B, void* D, int M, int N
                              int dtype, int epilogue, float alpha, const void* bias, const void* aux, long ldaux,
                              long stride_aux, void* aux_out, long ldaux_out, long stride_aux_out, void* stream) {
     int variant = -1;
-    if (!g_table.empty()) {
+    if (g_nonempty.load(std::memory_order_acquire)) {
         std::lock_guard<std::mutex> lk(g_mu);
         auto it = g_table.find(Key{M, N, K, batch, a_mn_major * 2 + b_mn_major, dtype});
         if (it != g_table.end()) variant = it->second;

@@ -617,6 +617,16 @@ static int launch(const CUtensorMap& a, const BMapSet<NMAPS>& b, const CUtensorM
     const int m_blocks = (p.M + BM - 1) / BM, n_blocks = (p.N + BN - 1) / BN;
     const long tiles = (long)m_blocks * n_blocks * p.batch;
     const int grid = (int)(tiles < sms ? tiles : sms);
+    if (p.ag_overlap) {
+        // the TMA producers wait for panels copied by OTHER CTAs of this grid: every CTA must be resident. A
+        // cooperative launch guarantees that or fails (cudaErrorCooperativeLaunchTooLarge) instead of hanging when
+        // SMs are held by another kernel's context limit.
+        void* args[] = {const_cast<CUtensorMap*>(&a), const_cast<BMapSet<NMAPS>*>(&b), const_cast<CUtensorMap*>(&d),
+                        const_cast<GemmParams*>(&p)};
+        cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(NUM_THREADS), args,
+                                                    Cfg::SMEM_BYTES, stream);
+        return e == cudaSuccess ? 0 : -(int)e;
+    }
     kern<<<grid, NUM_THREADS, Cfg::SMEM_BYTES, stream>>>(a, b, d, p);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

@@ -137,9 +137,11 @@ long do_aio(int fd, bool read, bool direct, char* buf, long nbytes, long offset,
                     break;
                 }
                 for (int i = 0; i < got; ++i) {
-                    if ((long)events[i].res < 0) failed = true;
+                    const int slot = (int)events[i].data;
+                    // a short transfer (EOF, ENOSPC part way) is a failure of the block, not a success with fewer bytes
+                    if ((long)events[i].res < 0 || (uint64_t)events[i].res != cbs[slot].aio_nbytes) failed = true;
                     else moved += events[i].res;
-                    free_slots.push_back((int)events[i].data);
+                    free_slots.push_back(slot);
                 }
                 inflight -= got;
                 completed += got;
@@ -171,6 +173,7 @@ long do_aio(int fd, bool read, bool direct, char* buf, long nbytes, long offset,
         if (r < 0) return r;
         moved += r;
     }
+    if (moved != nbytes) return -EIO;       // never report a partial transfer as done
     return moved;
 }
 

@@ -204,7 +204,7 @@ class FusedZeroStep:
                 K._count()
         self._mark("rs_norm")
         o._sumsq[1] = o._flag[0].float()
-        o._mp_owned_correction()
+        o._mp_owned_correction(reduced=reds)      # the arena still holds raw local gradients here
         norm, bad = o._global_scalars()
         self._mark("scalars")
         if self.is_lamb:

@@ -23,6 +23,7 @@ import torch
 import torch.distributed as dist
 
 from ...ops import kernels as K
+from ...utils import comm_stub
 from ...utils.logging import logger
 from ..flat import FlatArena
 
@@ -160,7 +161,7 @@ class FlatMixedPrecisionOptimizer:
 
     def reduce_bucket(self, gi, k):
         """In-place reduce-scatter (sharded) or all-reduce of bucket k of group gi, averaging over dp."""
-        if self.dp_world == 1:
+        if self.dp_world == 1 or comm_stub.enabled():
             return
         arena = self.arenas[gi]
         buck = self._bucket(arena.grad, gi, k)
@@ -219,9 +220,11 @@ class FlatMixedPrecisionOptimizer:
                 K.sumsq(g, out=acc, flag=self._flag, accumulate=True)
         self._sumsq[1] = self._flag[0].float()
 
-    def _mp_owned_correction(self):
+    def _mp_owned_correction(self, reduced=None):
         """With model parallelism replicated (non-MP) params must be counted once; the arena mixes both kinds, so
-        subtract the replicated segments on MP ranks > 0."""
+        subtract the replicated segments on MP ranks > 0. `reduced` maps (group, bucket) to the fp32 tensor holding
+        this rank's reduced slice when the reduction did not happen in place in the gradient arena (fused NVLink
+        step): the sum of squares was taken over those values, so the correction must read them too."""
         if self.mpu is None or self.mpu.get_model_parallel_world_size() == 1:
             return
         if self.mpu.get_model_parallel_rank() == 0:
@@ -235,7 +238,10 @@ class FlatMixedPrecisionOptimizer:
                     span = self.sub_size[gi] if self.shard else self.partition_count * self.sub_size[gi]
                     lo, hi = max(base, s.offset), min(base + span, s.offset + s.numel)
                     if lo < hi:
-                        seg = arena.grad.narrow(0, lo, hi - lo).float()
+                        if reduced is None:
+                            seg = arena.grad.narrow(0, lo, hi - lo).float()
+                        else:
+                            seg = reduced[(gi, k)].narrow(0, lo - base, hi - lo).float()
                         self._sumsq[0] -= (seg * seg).sum()
 
     def _global_scalars(self):
@@ -287,7 +293,7 @@ class FlatMixedPrecisionOptimizer:
             K.cast(self._master_slice(master.data, gi, k), dst)
 
     def all_gather_params(self):
-        if not self.shard or self.dp_world == 1:
+        if not self.shard or self.dp_world == 1 or comm_stub.enabled():
             return
         for gi, arena in enumerate(self.arenas):
             for k in range(self.num_buckets[gi]):

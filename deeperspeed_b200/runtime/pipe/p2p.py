@@ -15,6 +15,8 @@ module-level functions (`init_process_groups`, `send`, `recv`, `barrier`) are ke
 import torch
 import torch.distributed as dist
 
+from ...utils import comm_stub
+
 _grid = None
 _links = None
 
@@ -29,6 +31,8 @@ class Link:
 
     def post(self, tensor):
         """Start the transfer of `tensor` (send) or into `tensor` (receive); returns the work handle."""
+        if comm_stub.enabled():
+            return comm_stub.DONE
         if self.sends:
             return dist.isend(tensor, dst=self.peer, group=self.group)
         return dist.irecv(tensor, src=self.peer, group=self.group)

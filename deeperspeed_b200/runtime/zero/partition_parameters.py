@@ -511,3 +511,12 @@ class GatheredParameters:
             p.partition(has_been_updated=True)
             if getattr(p, "ds_persist", False):
                 p.all_gather()
+        # fused all-gather + GEMM layers read the peers' shards directly from the symmetric heap: publish the edit there
+        # (the optimizer re-homes ds_tensor into its flat buffer, so the heap copy is a separate tensor) and make sure
+        # every rank has done so before anyone's next forward
+        edited = [p for p in self.params if getattr(p, "ds_fused_ag", False)]
+        for p in edited:
+            if p.ds_heap_shard.data_ptr() != p.ds_tensor.data_ptr():
+                p.ds_heap_shard.copy_(p.ds_tensor.view(-1)[:p.ds_heap_shard.numel()])
+        if edited and dist.get_world_size(group=edited[0].ds_process_group) > 1:
+            dist.barrier(group=edited[0].ds_process_group)

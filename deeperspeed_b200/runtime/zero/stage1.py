@@ -9,6 +9,7 @@ the single fused peer-memory kernel from deeperspeed_b200.parallel.fused_zero.
 import torch
 import torch.distributed as dist
 
+from ...utils import comm_stub
 from ...utils.logging import logger
 from ..fp16.flat_optimizer import FlatMixedPrecisionOptimizer
 from ..fp16.loss_scaler import LossScaler, DynamicLossScaler
@@ -94,6 +95,8 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
 
     def _use_fused(self):
         fused = getattr(self, "fused", None)
+        if comm_stub.enabled():       # measurement mode: the NCCL path, whose collectives are skipped
+            return False
         return fused is not None and (self.fused_inner or fused.is_lamb)
 
     def reduce_gradients(self):

@@ -219,7 +219,10 @@ int dsb_gemm_pair_ex(const void* A, const void* B, void* D, int M, int N, int K,
 int dsb_gemm_pair_force_bn(int bn);
 int dsb_gemm_pair_force_split(int split);
 /* Dispatcher (tuned table, else static rule) and the autotuner that fills the table: variant 0 = single-CTA,
- * 1..4 = pair with that split, 5 = pair choosing its split. Reference: csrc/includes/gemm_test.h:27-293. */
+ * 1..4 = pair with that split, 5 = pair choosing its split. Reference: csrc/includes/gemm_test.h:27-293.
+ * dsb_gemm_tune ALLOCATES device memory (cudaMalloc / cudaFree), records events and synchronises `stream`: call it at
+ * set-up time only, never while a stream is being captured into a CUDA graph. dsb_gemm_auto is capture-safe; it may be
+ * called from any thread while another thread tunes (table under a mutex, empty check on an atomic flag). */
 int dsb_gemm_auto(const void* A, const void* B, void* D, int M, int N, int K, int batch, long lda, long ldb, long ldd,
                   long strideA, long strideB, long strideD, int a_mn_major, int b_mn_major, int dtype, int epilogue,
                   float alpha, const void* bias, const void* aux, long ldaux, long stride_aux, void* aux_out,

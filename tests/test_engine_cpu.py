@@ -408,3 +408,35 @@ def test_gpt2_model_trains_under_zero3_on_cpu(tmp_path):
                 losses.append(loss.item())
             assert all(l == l for l in losses) and losses[-1] < losses[0], (sparse, losses)
     run()
+
+
+def test_model_parallel_norm_correction_reads_the_reduced_slices():
+    """Fused NVLink step (parallel/fused_zero.py): the gradient arena still holds raw local gradients when the norm is
+    corrected for replicated parameters, so the correction must use the reduced fp32 slices it is given."""
+    from types import SimpleNamespace
+    from deeperspeed_b200.runtime.fp16.flat_optimizer import FlatMixedPrecisionOptimizer
+
+    class FakeMpu:
+        def get_model_parallel_world_size(self):
+            return 2
+
+        def get_model_parallel_rank(self):
+            return 1
+
+    sub, parts, me = 8, 2, 1
+    replicated = SimpleNamespace(param=SimpleNamespace(model_parallel=False), offset=6, numel=6)    # [6, 12)
+    sharded = SimpleNamespace(param=SimpleNamespace(model_parallel=True), offset=12, numel=4)
+    raw = torch.full((sub * parts,), 100.0)                      # what an un-reduced arena would hold
+    opt = object.__new__(FlatMixedPrecisionOptimizer)
+    opt.mpu, opt.shard, opt.dp_rank, opt.partition_count = FakeMpu(), True, me, parts
+    opt.arenas = [SimpleNamespace(segments=[replicated, sharded], grad=raw)]
+    opt.num_buckets, opt.sub_size = [1], [sub]
+    reduced = torch.arange(sub, dtype=torch.float32)             # this rank's slice = arena[8:16]
+    opt._sumsq = torch.tensor([float((reduced * reduced).sum()), 0.0])
+    opt._mp_owned_correction(reduced={(0, 0): reduced})
+    keep = reduced[4:]                                           # arena [12, 16): the replicated [8, 12) part is removed
+    assert torch.allclose(opt._sumsq[0], (keep * keep).sum())
+    # the in-place path reads the arena itself
+    opt._sumsq = torch.tensor([1e6, 0.0])
+    opt._mp_owned_correction()
+    assert torch.allclose(opt._sumsq[0], torch.tensor(1e6 - 4 * 100.0 ** 2))
