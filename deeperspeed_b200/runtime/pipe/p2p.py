@@ -33,9 +33,10 @@ class Link:
         """Start the transfer of `tensor` (send) or into `tensor` (receive); returns the work handle."""
         if comm_stub.enabled():
             return comm_stub.DONE
-        if self.sends:
-            return dist.isend(tensor, dst=self.peer, group=self.group)
-        return dist.irecv(tensor, src=self.peer, group=self.group)
+        # issued as a one-element batch: NCCL then runs it as a grouped point-to-point operation of this link's own
+        # communicator instead of an "independent collective" of an eagerly initialised group
+        op = dist.P2POp(dist.isend if self.sends else dist.irecv, tensor, self.peer, self.group)
+        return dist.batch_isend_irecv([op])[-1]
 
 
 class StageLinks:

@@ -106,3 +106,94 @@ def _onebit_opt_worker(kind):
 @pytest.mark.parametrize("kind", ["OneBitAdam", "OneBitLamb"])
 def test_onebit_optimizers_cpu(kind):
     run_distributed(_onebit_opt_worker, world_size=2, use_cuda=False, args=(kind,))
+
+
+class _ThreadComm:
+    """In-process stand-in for an MPI communicator: `size` ranks run as threads and meet at a barrier. Accepts numpy
+    arrays (host-staged transport) and torch tensors (what a CUDA-aware MPI is handed)."""
+
+    class _Shared:
+        def __init__(self, size):
+            import threading
+            self.size = size
+            self.barrier = threading.Barrier(size)
+            self.slots = [None] * size
+
+    def __init__(self, shared, rank):
+        self.shared, self.rank = shared, rank
+        self.calls = []
+
+    def Get_rank(self):
+        return self.rank
+
+    def Get_size(self):
+        return self.shared.size
+
+    @staticmethod
+    def _view(buf):
+        return buf if isinstance(buf, torch.Tensor) else torch.from_numpy(buf)
+
+    def _meet(self, send):
+        sh = self.shared
+        sh.slots[self.rank] = self._view(send).clone()
+        sh.barrier.wait()
+        everyone = list(sh.slots)
+        sh.barrier.wait()
+        return everyone
+
+    def Alltoall(self, send, recv):
+        self.calls.append(("Alltoall", type(send).__name__))
+        everyone = self._meet(send)
+        n = everyone[0].numel() // self.shared.size
+        out = self._view(recv)
+        for r, src in enumerate(everyone):
+            out[r * n:(r + 1) * n] = src[self.rank * n:(self.rank + 1) * n]
+
+    def Allgather(self, send, recv):
+        self.calls.append(("Allgather", type(send).__name__))
+        everyone = self._meet(send)
+        self._view(recv).copy_(torch.cat([e.view(-1) for e in everyone]))
+
+
+@pytest.mark.parametrize("cuda_aware", [False, True])
+def test_mpi_backend_both_transports(cuda_aware):
+    """MpiBackend (reference runtime/comm/mpi.py): device-buffer and host-staged transports give the dense two-phase
+    result; the CUDA-aware one hands the tensors themselves to MPI, the other numpy views of pinned staging buffers."""
+    import threading
+    from deeperspeed_b200.runtime.comm.mpi import MpiBackend
+    world = 2
+    n = 64 * world * 4
+    inputs = []
+    for rank in range(world):
+        torch.manual_seed(10 + rank)
+        inputs.append((torch.rand(n) - 0.5) + 0.01 * rank)
+    # dense oracle
+    quant = [a.norm() / n ** 0.5 * ((a >= 0).float() * 2 - 1) for a in inputs]
+    avg = torch.stack(quant).mean(0)
+    c = n // world
+    want = torch.cat([avg[k * c:(k + 1) * c].norm() / c ** 0.5 * ((avg[k * c:(k + 1) * c] >= 0).float() * 2 - 1)
+                      for k in range(world)])
+    shared = _ThreadComm._Shared(world)
+    results, comms, errors = [None] * world, [None] * world, []
+
+    def run(rank):
+        try:
+            comms[rank] = _ThreadComm(shared, rank)
+            backend = MpiBackend(cuda_aware, comm=comms[rank])
+            werr, serr = torch.zeros(n), torch.zeros(n // world)
+            results[rank] = backend.compressed_allreduce(inputs[rank].clone(), werr, serr, rank)
+            assert werr.abs().sum() > 0 and serr.abs().sum() > 0
+            short = torch.rand(n - 5) - 0.5          # padded input is cut back to its own length
+            assert backend.compressed_allreduce(short, torch.zeros(n), torch.zeros(n // world), rank).numel() == n - 5
+        except Exception as e:  # pragma: no cover
+            errors.append(e)
+            shared.barrier.abort()
+
+    threads = [threading.Thread(target=run, args=(r,)) for r in range(world)]
+    [t.start() for t in threads]
+    [t.join(60) for t in threads]
+    assert not errors, errors
+    for got in results:
+        assert torch.allclose(got, want, atol=1e-6)
+    kinds = {kind for _, kind in comms[0].calls}
+    assert kinds == ({"Tensor"} if cuda_aware else {"ndarray"})
