@@ -119,6 +119,10 @@ ZERO_DEFAULTS = {
     "stage3_gather_fp16_weights_on_model_save": False,
     # B200-native extension: fuse reduce-scatter + cast + Adam + all-gather over NVSwitch peer memory
     "fused_nvlink": "auto",
+    # Stage 2 gradient memory: "sharded" keeps only this rank's reduced slices (the reference's behaviour: gradient
+    # bytes / dp), "full" keeps a whole gradient arena that autograd accumulates into in place (fastest; fine while
+    # the arena is small next to 180 GB of HBM), "auto" = sharded once the arena would exceed 8 GiB per rank
+    "gradient_memory": "auto",
     # B200-native extension (stage 3): Linear forwards run the weight all-gather inside the GEMM kernel; shards of
     # eligible weights live on a peer-mapped heap (zero/partition_parameters.py, parallel/ag_gemm.py)
     "stage3_fused_allgather_gemm": False,

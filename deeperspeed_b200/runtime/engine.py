@@ -214,6 +214,16 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
             return torch.cuda.is_available() and self.dp_world_size > 1 and os.environ.get("DSB_FUSED_NVLINK", "1") != "0"
         return bool(v)
 
+    def zero_shard_gradient_memory(self):
+        """Stage 2: keep only the owned gradient slices (see ZERO_DEFAULTS["gradient_memory"])."""
+        mode = str(self._config.zero_config.gradient_memory).lower()
+        if mode not in ("auto", "full", "sharded"):
+            raise ValueError(f"zero_optimization.gradient_memory must be auto, full or sharded, got {mode!r}")
+        if mode != "auto":
+            return mode == "sharded"
+        arena_bytes = sum(p.numel() * p.element_size() for p in self.module.parameters() if p.requires_grad)
+        return self.dp_world_size > 1 and arena_bytes > (8 << 30)
+
     def postscale_gradients(self):
         return not self._config.prescale_gradients
 

@@ -72,6 +72,8 @@ class FlatArena:
 
     def absorb_stray_grads(self):
         """If user code replaced a .grad (e.g. set_to_none), fold it back into the arena."""
+        if self.grad is None:       # gradients are not kept whole (ZeRO-2 sharded gradient memory)
+            return
         for s in self.segments:
             g = s.param.grad
             view = self.grad.narrow(0, s.offset, s.numel).view(s.shape)

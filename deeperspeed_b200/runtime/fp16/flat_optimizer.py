@@ -35,8 +35,12 @@ def _dist_ready():
 class FlatMixedPrecisionOptimizer:
     def __init__(self, init_optimizer, dp_process_group=None, shard=False, mpu=None, clip_grad=0.0,
                  max_elements_per_comm=int(5e8), fp32_allreduce=False, overlap_comm=False, allocator=None,
-                 gradient_predivide_factor=1.0, postscale_gradients=True, verbose=False):
+                 gradient_predivide_factor=1.0, postscale_gradients=True, verbose=False, shard_gradients=False):
         self.optimizer = init_optimizer
+        # shard_gradients (ZeRO-2 memory mode): no full-size gradient arena; only this rank's reduced slices persist
+        # (`grad_shards`), gradients pass through pooled bucket-sized staging buffers (runtime/zero/stage2.py)
+        self.shard_gradients = bool(shard_gradients) and shard
+        self.grad_shards = []
         self.mpu = mpu
         self.clip_grad = clip_grad
         self.verbose = verbose
@@ -79,7 +83,10 @@ class FlatMixedPrecisionOptimizer:
             arena = FlatArena(params, shard_count=pc * count, allocator=allocator, shard_align=8)
             # FlatArena pads to pc*count*8; recompute sub from the final size
             sub = arena.numel // (pc * count)
-            arena.allocate_grads()
+            if self.shard_gradients:
+                self.grad_shards.append(torch.zeros(sub * count, dtype=arena.dtype, device=arena.device))
+            else:
+                arena.allocate_grads()
             self.arenas.append(arena)
             self.sub_size.append(sub)
             self.num_buckets.append(count)
@@ -109,6 +116,14 @@ class FlatMixedPrecisionOptimizer:
     def _master_slice(self, t, gi, k):
         return t.narrow(0, k * self.sub_size[gi], self.sub_size[gi])
 
+    def _owned_grad(self, gi, k):
+        """The gradient the optimizer consumes for bucket k of group gi: this rank's slice (sharded) or the whole
+        bucket (replicated) of the gradient arena, or the persistent owned shard when gradients are not kept whole."""
+        if self.shard_gradients:
+            return self._master_slice(self.grad_shards[gi], gi, k)
+        grad = self.arenas[gi].grad
+        return self._slice(grad, gi, k) if self.shard else self._bucket(grad, gi, k)
+
     def _init_inner_state(self):
         """Allocate optimizer state up front (the reference does a dummy step for the same reason)."""
         if self.fused_inner:
@@ -136,12 +151,14 @@ class FlatMixedPrecisionOptimizer:
         self.optimizer.state = value
 
     def flat_grad_buffers(self):
-        return [a.grad for a in self.arenas]
+        return list(self.grad_shards) if self.shard_gradients else [a.grad for a in self.arenas]
 
     # ------------------------------------------------------------------ gradients
     def zero_grad(self, set_grads_to_None=True):
         for a in self.arenas:
             a.zero_grads()
+        for g in self.grad_shards:
+            g.zero_()
         self._reduced = False
 
     def _loss_scale(self):
@@ -216,8 +233,7 @@ class FlatMixedPrecisionOptimizer:
         acc = self._sumsq.narrow(0, 0, 1)
         for gi, arena in enumerate(self.arenas):
             for k in range(self.num_buckets[gi]):
-                g = self._slice(arena.grad, gi, k) if self.shard else self._bucket(arena.grad, gi, k)
-                K.sumsq(g, out=acc, flag=self._flag, accumulate=True)
+                K.sumsq(self._owned_grad(gi, k), out=acc, flag=self._flag, accumulate=True)
         self._sumsq[1] = self._flag[0].float()
 
     def _mp_owned_correction(self, reduced=None):
@@ -238,7 +254,9 @@ class FlatMixedPrecisionOptimizer:
                     span = self.sub_size[gi] if self.shard else self.partition_count * self.sub_size[gi]
                     lo, hi = max(base, s.offset), min(base + span, s.offset + s.numel)
                     if lo < hi:
-                        if reduced is None:
+                        if reduced is None and self.shard_gradients:
+                            seg = self._owned_grad(gi, k).narrow(0, lo - base, hi - lo).float()
+                        elif reduced is None:
                             seg = arena.grad.narrow(0, lo, hi - lo).float()
                         else:
                             seg = reduced[(gi, k)].narrow(0, lo - base, hi - lo).float()
@@ -275,13 +293,12 @@ class FlatMixedPrecisionOptimizer:
                 self.optimizer.step_flat(group, self._master_slice(master.data, gi, k),
                                          self._master_slice(st["exp_avg"], gi, k),
                                          self._master_slice(st["exp_avg_sq"], gi, k),
-                                         self._slice(arena.grad, gi, k) if self.shard else self._bucket(arena.grad, gi, k),
+                                         self._owned_grad(gi, k),
                                          lp=self._slice(arena.data, gi, k) if self.shard else self._bucket(arena.data, gi, k),
                                          inv_scale_dev=self._inv_scale, skip_dev=self._skip)
             return
         # generic inner optimizer: materialise fp32 grads, step, copy back
-        g32 = torch.cat([(self._slice(arena.grad, gi, k) if self.shard else self._bucket(arena.grad, gi, k)).float()
-                         for k in range(self.num_buckets[gi])])
+        g32 = torch.cat([self._owned_grad(gi, k).float() for k in range(self.num_buckets[gi])])
         g32.mul_(self._inv_scale)
         master.grad = g32
 

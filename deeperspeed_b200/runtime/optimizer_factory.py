@@ -116,7 +116,8 @@ def _zero2(e, optimizer):
         reduce_scatter=e.zero_reduce_scatter(), overlap_comm=e.zero_overlap_comm(), cpu_offload=e.zero_cpu_offload(),
         pin_memory=True, allreduce_always_fp32=_fp32_reduce(e),
         gradient_accumulation_steps=e.gradient_accumulation_steps(), fused_nvlink=e.zero_fused_nvlink(),
-        elastic_checkpoint=e.zero_elastic_checkpoint(), **_scaling_and_groups(e))
+        elastic_checkpoint=e.zero_elastic_checkpoint(), shard_gradients=e.zero_shard_gradient_memory(),
+        **_scaling_and_groups(e))
 
 
 def _zero3(e, optimizer):

@@ -36,7 +36,7 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
                  verbose=True, dp_process_group=None, partition_size=None, mpu=None, all_gather_partitions=True,
                  allgather_size=int(5e8), clip_grad=0.0, max_elements_per_comm=int(5e8), elastic_checkpoint=True,
                  fp32_allreduce=False, overlap_comm=False, precision=torch.float16, allocator=None,
-                 gradient_predivide_factor=1.0, postscale_gradients=True, fused_nvlink=False):
+                 gradient_predivide_factor=1.0, postscale_gradients=True, fused_nvlink=False, shard_gradients=False):
         if dynamic_loss_scale and precision == torch.float16:
             self.loss_scaler = DynamicLossScaler() if dynamic_loss_args is None else DynamicLossScaler(**dynamic_loss_args)
             self.dynamic_loss_scale = True
@@ -60,7 +60,7 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
                          max_elements_per_comm=max_elements_per_comm, fp32_allreduce=fp32_allreduce,
                          overlap_comm=overlap_comm, allocator=allocator,
                          gradient_predivide_factor=gradient_predivide_factor,
-                         postscale_gradients=postscale_gradients, verbose=verbose)
+                         postscale_gradients=postscale_gradients, verbose=verbose, shard_gradients=shard_gradients)
         # reference attribute names
         self.fp16_groups = self.group_params
         self.fp16_groups_flat = [a.data for a in self.arenas]

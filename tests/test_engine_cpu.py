@@ -429,6 +429,7 @@ def test_model_parallel_norm_correction_reads_the_reduced_slices():
     raw = torch.full((sub * parts,), 100.0)                      # what an un-reduced arena would hold
     opt = object.__new__(FlatMixedPrecisionOptimizer)
     opt.mpu, opt.shard, opt.dp_rank, opt.partition_count = FakeMpu(), True, me, parts
+    opt.shard_gradients = False
     opt.arenas = [SimpleNamespace(segments=[replicated, sharded], grad=raw)]
     opt.num_buckets, opt.sub_size = [1], [sub]
     reduced = torch.arange(sub, dtype=torch.float32)             # this rank's slice = arena[8:16]
@@ -440,3 +441,38 @@ def test_model_parallel_norm_correction_reads_the_reduced_slices():
     opt._sumsq = torch.tensor([1e6, 0.0])
     opt._mp_owned_correction()
     assert torch.allclose(opt._sumsq[0], torch.tensor(1e6 - 4 * 100.0 ** 2))
+
+
+def test_zero2_sharded_gradient_memory_world2(tmp_path):
+    """Stage 2 with `gradient_memory: sharded`: no whole gradient arena exists, only the owned slices plus pooled
+    bucket staging; results equal plain AdamW on the global batch (with several buckets, gradient accumulation, an
+    offloaded optimizer, and parameters that get no gradient on one rank)."""
+    @distributed_test(world_size=2)
+    def run():
+        for extra in ({}, {"reduce_bucket_size": 96}, {"cpu_offload": True, "reduce_bucket_size": 96}):
+            torch.manual_seed(42)
+            model = SimpleModel(HID)
+            cfg = _cfg(2)
+            cfg["zero_optimization"].update(extra, gradient_memory="sharded")
+            engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                   model_parameters=model.parameters())
+            opt = engine.optimizer
+            assert opt.shard_gradients and all(a.grad is None for a in opt.arenas)
+            _train(engine, 3)
+            assert all(p.grad is None for p in engine.module.parameters())      # freed as soon as they were staged
+            ref = _reference_run(3, 2, 2)
+            for p, r in zip(engine.module.parameters(), ref):
+                assert torch.allclose(p.detach(), r, atol=3e-5), (extra, (p - r).abs().max())
+            own, staged = opt.gradient_memory_bytes()
+            total = sum(a.numel * 4 for a in opt.arenas)
+            assert own == total // 2
+            if "reduce_bucket_size" in extra:
+                assert sum(opt.num_buckets) > 1 and staged < total      # staging is a few buckets, not the arena
+        model = SimpleModel(HID, empty_grad=True, rank=dist.get_rank())
+        cfg = _cfg(2)
+        cfg["zero_optimization"]["gradient_memory"] = "sharded"
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        losses = _train(engine, 2)
+        assert all(l == l for l in losses)
+    run()
