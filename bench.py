@@ -91,7 +91,8 @@ def _zero_backend(engine):
     opt = getattr(engine, "optimizer", None)
     fused = getattr(opt, "_fused", None) or getattr(opt, "fused", None)
     if fused is not None:
-        return "fused NVLink kernels (fused_rs_norm + fused_adam_ag, ours)"
+        how = "NVLS multimem.ld_reduce / multimem.st" if getattr(fused, "use_multicast", False) else "peer loads / stores"
+        return f"fused_zero_step kernel (ours): reduce-scatter + norm + Adam + all-gather over the symmetric heap, {how}"
     return "NCCL reduce_scatter / all_gather + fused Adam kernel" if getattr(engine, "dp_world_size", 1) > 1 else \
         "single rank: fused Adam kernel, no collective"
 
@@ -311,6 +312,7 @@ def run_ours(args):
                     "d2h_bytes_per_step": loss_bytes / args.steps, "ms_per_step": ms_e2e / args.steps,
                     "last_loss": lv},
             "gpu_launches": launches,
+            "zero_step_launches": dict(getattr(getattr(engine.optimizer, "fused", None), "launches", {}) or {}),
             "exposed_comm": exposed,
         }
         print(json.dumps(out), flush=True)

@@ -18,7 +18,13 @@ torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
 N = int(os.environ.get("NUMEL", 700_000_000)) // (world * 8) * (world * 8)
 LAMB = os.environ.get("OPT", "adam").lower() == "lamb"
 res = {}
-for name, fused in (("nccl", False), ("fused", True)):
+variants = [("nccl", False, None), ("fused", True, "1")]
+if not LAMB:
+    variants.append(("fused_unicast", True, "0"))      # same kernel, peer loads / stores instead of NVLS multimem
+heap_info = {}
+for name, fused, mc in variants:
+    if mc is not None:
+        os.environ["DSB_FUSED_ZERO_MULTICAST"] = mc
     if LAMB:
         n_each = N // 96 // 8 * 8
         N = n_each * 96
@@ -40,6 +46,11 @@ for name, fused in (("nccl", False), ("fused", True)):
         if it >= 3:
             ts.append(t.item())
     res[name] = round(sorted(ts)[len(ts) // 2], 3)
+    if fused and opt.fused is not None:
+        heap_info[name] = {"heap": opt.fused.heap.backend, "multicast": bool(getattr(opt.fused, "use_multicast", False)),
+                           "launches": dict(getattr(opt.fused, "launches", {}))}
+        if not LAMB:
+            heap_info[name]["phase_ms_last_step"] = opt.fused.phase_times_ms()
     del opt, ps, inner
     torch.cuda.empty_cache()
 if rank == 0:
@@ -56,7 +67,8 @@ if rank == 0:
            "speedup": round(res["nccl"] / res["fused"], 2), "roofline_ms": round(roof_ms, 3),
            "fused_fraction_of_roofline": round(roof_ms / res["fused"], 3),
            "two_phase_bound_ms": round(pull_ms + upd_ms, 3),
-           "fused_fraction_of_two_phase_bound": round((pull_ms + upd_ms) / res["fused"], 3)}
+           "fused_fraction_of_two_phase_bound": round((pull_ms + upd_ms) / res["fused"], 3),
+           "fused_unicast_ms": res.get("fused_unicast"), "variants": heap_info}
     print(json.dumps(out))
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(out, open(f"gpurun_out/fused_zero{'_lamb' if LAMB else ''}_bench_w{world}.json", "w"))

@@ -16,33 +16,13 @@
 // ld.acquire.sys; grids are launched cooperatively (all CTAs resident) because CTAs wait on CTA 0.
 // Replaces reference engine.allreduce_bucket + zero/stage1.reduce_scatter_gradients + stage1.step all_gather
 // (deepspeed/runtime/engine.py:1323-1395, zero/stage1.py:629-783).
-#include "../common/ptx.cuh"
+#include "xgpu.cuh"
 #include "../../include/dsb200.h"
 #include <cooperative_groups.h>
 
 namespace cg = cooperative_groups;
 
 namespace dsb {
-
-constexpr int MAX_RANKS = 16;
-struct PeerPtrs {
-    void* p[MAX_RANKS];
-};
-struct FlagPtrs {
-    uint32_t* p[MAX_RANKS];
-};
-
-// All ranks arrive at `slot` with value `epoch`; returns when every rank has arrived. Called by one CTA.
-DSB_DEVICE void xgpu_barrier(const FlagPtrs& flags, int R, int me, int slot, uint32_t epoch) {
-    __syncthreads();
-    if (threadIdx.x < R) {
-        __threadfence_system();
-        st_release_sys(flags.p[threadIdx.x] + slot * MAX_RANKS + me, epoch);
-        const uint32_t* mine = flags.p[me] + slot * MAX_RANKS + threadIdx.x;
-        while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {}
-    }
-    __syncthreads();
-}
 
 struct AdamH {
     float lr, beta1, beta2, eps, wd, bc1, bc2;

@@ -1,5 +1,12 @@
-"""Fused ZeRO step over NVLink peer memory: reduce-scatter + fp16->fp32 cast + average + norm/overflow in one kernel,
-Adam + cast + all-gather (peer stores) in a second one. See csrc/comm/fused_zero.cu."""
+"""Fused ZeRO step over NVLink / NVSwitch peer memory.
+
+Adam: ONE cooperative kernel per bucket (csrc/comm/fused_zero_step.cu) does reduce-scatter (in the switch through the
+heap's multicast address when there is one - NVLS - else peer loads) + average + norm / overflow, trades the norm terms
+with the peers through mailboxes in the heap, derives the unscale / clip factor on the device, runs Adam on the fp32
+master, casts, all-gathers by (multicast) stores into every rank's parameter arena and zeroes the gradient bucket.
+With a model-parallel / pipeline group the norm also has to be reduced over that group, so the kernel is launched
+twice (reduce, then update) around the host-side scalar all-reduce.
+LAMB: reduce kernel + the three-phase LAMB kernel of csrc/comm/fused_zero.cu."""
 import ctypes as C
 import os
 
@@ -21,6 +28,11 @@ N.register_sigs({
                           _i, _i, _i, _p, _p, _p, _u, _p],
 })
 N.register_sigs({"dsb_fused_zero_scratch_bytes": []}, restype=_l)
+N.register_sigs({
+    "dsb_fused_zero_step": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _i, _p, _p, _p, _p, _f, _f, _f, _f, _f,
+                            _i, _i, _i, _f, _f, _p, _p, _p, _p, _p, _u, _p],
+})
+PH_REDUCE, PH_UPDATE, PH_EXCHANGE = 1, 2, 4
 
 
 def _ptr_array(ptrs):
@@ -74,18 +86,27 @@ class FusedZeroStep:
         self.lib = N.cuda_lib()
         self._prof = [] if os.environ.get("DSB_FUSED_ZERO_PROFILE") == "1" else None
         self.scratch = torch.zeros(self.lib.dsb_fused_zero_scratch_bytes(), dtype=torch.uint8, device=opt._dev)
-        self.red32 = [torch.empty(opt.sub_size[gi], dtype=torch.float32, device=opt._dev)
-                      for gi in range(len(opt.arenas))]
         self.flag_ptrs = _ptr_array(heap.flag_ptrs())
-        self.grad_ptrs, self.param_ptrs = [], []
+        self.grad_ptrs, self.param_ptrs, self.mc_grads, self.mc_params = [], [], [], []
         for a in opt.arenas:
-            self.grad_ptrs.append(_ptr_array(heap.peer_ptrs(heap.offsets[a.grad.data_ptr()])))
-            self.param_ptrs.append(_ptr_array(heap.peer_ptrs(heap.offsets[a.data.data_ptr()])))
+            g_off, p_off = heap.offsets[a.grad.data_ptr()], heap.offsets[a.data.data_ptr()]
+            self.grad_ptrs.append(_ptr_array(heap.peer_ptrs(g_off)))
+            self.param_ptrs.append(_ptr_array(heap.peer_ptrs(p_off)))
+            self.mc_grads.append(heap.mc_ptr(g_off))
+            self.mc_params.append(heap.mc_ptr(p_off))
+        # NVLS reduce (multimem.ld_reduce) is opt-in: a reduce-SCATTER through the switch sends every byte of the local
+        # arena out (the switch fetches this rank's own contribution over NVLink too), W / (W - 1) times the bytes of
+        # peer loads; measured 2.07 ms vs 1.12 ms for the reduce phase at W = 2 (profiles/fused_zero_bench_w2.json)
+        self.use_multicast = bool(heap.mc_base) and os.environ.get("DSB_FUSED_ZERO_MULTICAST", "0") == "1"
+        self.host_out = torch.zeros(2, dtype=torch.float32, device=opt._dev)
+        self._reds = {}
+        self.launches = {"reduce": 0, "update": 0, "whole_step": 0}      # per-kernel launch counts (bench / tests)
         self.is_lamb = bool(getattr(opt.optimizer, "supports_fused_zero_lamb", False))
         if self.is_lamb:
             self._init_lamb()
         logger.info(f"[fused-zero] rank {opt.dp_rank}/{opt.dp_world}: NVLink peer-memory ZeRO step enabled "
-                    f"({sum(a.numel for a in opt.arenas)} elements, {'LAMB' if self.is_lamb else 'Adam'})")
+                    f"({sum(a.numel for a in opt.arenas)} elements, {'LAMB' if self.is_lamb else 'Adam'}, heap "
+                    f"{heap.backend}, {'NVLS multimem' if self.use_multicast else 'peer loads / stores'})")
 
     # ---- LAMB: per-tensor segment tables of the owned slices + norm tables in the symmetric heap
     @staticmethod
@@ -176,58 +197,86 @@ class FusedZeroStep:
             logger.info("[fused-zero] " + " ".join(parts))
         self._prof = []
 
+    # ---- Adam: the one-kernel step ----------------------------------------------------------------------------
+    def _launch(self, gi, k, phases, s, epoch=None):
+        o = self.opt
+        arena = o.arenas[gi]
+        group = o.optimizer.param_groups[gi]
+        master = o.fp32_masters[gi]
+        st = o.optimizer.state[master]
+        R, me, sub = o.dp_world, o.dp_rank, o.sub_size[gi]
+        beta1, beta2 = group["betas"]
+        mc = self.use_multicast
+        N.check(self.lib.dsb_fused_zero_step(
+            self.grad_ptrs[gi], self.param_ptrs[gi], self.flag_ptrs, self.mc_grads[gi] if mc else None,
+            self.mc_params[gi] if mc else None, R, me, phases, 1, (k * R + me) * sub, k * R * sub, R * sub, sub,
+            N.dtype_code(arena.dtype), N.ptr(self._red(gi, k)), N.ptr(o._master_slice(master.data, gi, k)),
+            N.ptr(o._master_slice(st["exp_avg"], gi, k)), N.ptr(o._master_slice(st["exp_avg_sq"], gi, k)),
+            float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), float(group["weight_decay"]),
+            int(o.optimizer.adam_w_mode), int(group["bias_correction"]), int(group["step"]), float(o._loss_scale()),
+            float(o.clip_grad), N.ptr(o._sumsq), N.ptr(o._inv_scale), N.ptr(o._skip), N.ptr(self.host_out),
+            N.ptr(self.scratch), self.heap.next_epoch(), s), "dsb_fused_zero_step")
+        K._count()
+        self.launches["whole_step" if phases == 7 else "reduce" if phases & PH_REDUCE else "update"] += 1
+
+    def phase_times_ms(self):
+        """Phase durations of the LAST fused_zero_step launch from its in-kernel %globaltimer stamps: barrier wait,
+        reduce, norm fold + exchange, update (+ all-gather + gradient zeroing), closing barrier."""
+        torch.cuda.synchronize()
+        t = self.scratch[2560:2560 + 48].view(torch.int64).tolist()
+        names = ["entry_barrier", "reduce", "fold_exchange", "update", "closing_barrier"]
+        return {n: round((t[i + 1] - t[i]) / 1e6, 4) for i, n in enumerate(names)}
+
+    def _red(self, gi, k):
+        """Scratch for the reduced slice of bucket k in the arena dtype (None: the kernel reduces in place in the
+        gradient arena; DSB_FUSED_ZERO_INPLACE=1)."""
+        if os.environ.get("DSB_FUSED_ZERO_INPLACE", "0") == "1":
+            return None
+        key = (gi, k)
+        if key not in self._reds:
+            o = self.opt
+            self._reds[key] = torch.empty(o.sub_size[gi], dtype=o.arenas[gi].dtype, device=o._dev)
+        return self._reds[key]
+
+    def _adam_step(self, s):
+        """Returns (norm, overflow flag) as a 2-element device tensor."""
+        o = self.opt
+        buckets = [(gi, k) for gi in range(len(o.arenas)) for k in range(o.num_buckets[gi])]
+        for group in o.optimizer.param_groups:
+            group["step"] = group.get("step", 0) + 1
+        o._sumsq.zero_()
+        mp = o.mpu is not None and o.mpu.get_model_parallel_world_size() > 1
+        if not mp:
+            # the norm lives inside the data-parallel group: the last bucket's launch trades it through the heap
+            for gi, k in buckets[:-1]:
+                self._launch(gi, k, PH_REDUCE, s)
+            self._launch(*buckets[-1], PH_REDUCE | PH_EXCHANGE | PH_UPDATE, s)
+            self._mark("reduce+exchange+update")
+            for gi, k in buckets[:-1]:
+                self._launch(gi, k, PH_UPDATE, s)
+            return self.host_out
+        for gi, k in buckets:
+            self._launch(gi, k, PH_REDUCE, s)
+        self._mark("reduce")
+        o._mp_owned_correction(reduced=self._reds or None)      # the arena itself still holds raw local gradients
+        norm, bad = o._global_scalars()                    # all-reduce over dp and the model-parallel group
+        self._mark("scalars")
+        for gi, k in buckets:
+            self._launch(gi, k, PH_UPDATE, s)
+        self._mark("update")
+        return torch.stack([norm, bad.float()])
+
     def step(self):
         o = self.opt
         self._mark("start")
         for a in o.arenas:
             a.absorb_stray_grads()
-        R, me = o.dp_world, o.dp_rank
         s = N.stream_ptr()
-        o._sumsq.zero_()
-        o._flag.zero_()
-        sumsq = o._sumsq.narrow(0, 0, 1)
-        # With several buckets the reduced slices are kept per bucket; the common case is one bucket per group.
-        reds = {}
-        for gi, arena in enumerate(o.arenas):
-            sub = o.sub_size[gi]
-            for k in range(o.num_buckets[gi]):
-                if self.is_lamb:
-                    red = self.lamb_red[gi].narrow(0, k * sub, sub)
-                else:
-                    red = self.red32[gi] if k == 0 else torch.empty(sub, dtype=torch.float32, device=o._dev)
-                reds[(gi, k)] = red
-                off = (k * o.partition_count + me) * sub
-                N.check(self.lib.dsb_fused_rs_norm(self.grad_ptrs[gi], self.flag_ptrs, R, me, off, sub,
-                                                   N.dtype_code(arena.dtype), 1.0 / R, N.ptr(red), N.ptr(sumsq),
-                                                   N.ptr(o._flag), N.ptr(self.scratch), self.heap.next_epoch(), s),
-                        "dsb_fused_rs_norm")
-                K._count()
-        self._mark("rs_norm")
-        o._sumsq[1] = o._flag[0].float()
-        o._mp_owned_correction(reduced=reds)      # the arena still holds raw local gradients here
-        norm, bad = o._global_scalars()
-        self._mark("scalars")
         if self.is_lamb:
-            self._lamb_update(s)
-        for gi, arena in enumerate(() if self.is_lamb else o.arenas):
-            group = o.optimizer.param_groups[gi]
-            master = o.fp32_masters[gi]
-            st = o.optimizer.state[master]
-            group["step"] = group.get("step", 0) + 1
-            beta1, beta2 = group["betas"]
-            sub = o.sub_size[gi]
-            for k in range(o.num_buckets[gi]):
-                off = (k * o.partition_count + me) * sub
-                N.check(self.lib.dsb_fused_adam_ag(
-                    N.ptr(reds[(gi, k)]), N.ptr(o._master_slice(master.data, gi, k)),
-                    N.ptr(o._master_slice(st["exp_avg"], gi, k)), N.ptr(o._master_slice(st["exp_avg_sq"], gi, k)),
-                    self.param_ptrs[gi], self.flag_ptrs, R, me, off, sub, N.dtype_code(arena.dtype),
-                    float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), float(group["weight_decay"]),
-                    int(o.optimizer.adam_w_mode), int(group["bias_correction"]), int(group["step"]),
-                    N.ptr(o._inv_scale), N.ptr(o._skip), self.heap.next_epoch(), s), "dsb_fused_adam_ag")
-                K._count()
-        self._mark("update_ag")
-        host = torch.stack([norm, bad.float()]).tolist()
+            scalars = self._lamb_step(s)
+        else:
+            scalars = self._adam_step(s)
+        host = scalars.tolist()                                # the only device -> host read of the step
         self._report()
         overflow = bool(host[1])
         o.overflow = overflow
@@ -244,5 +293,33 @@ class FusedZeroStep:
                     group["step"] = max(group.get("step", 1) - 1, 0)
             logger.info("[deepspeed] OVERFLOW! Rank {} Skipping step. Attempted loss scale: {}, reducing to {}".format(
                 dist.get_rank(), prev, o._loss_scale()))
+        o._grads_already_zero = not self.is_lamb               # the update phase zeroed every gradient bucket
         o.zero_grad()
         return overflow
+
+    def _lamb_step(self, s):
+        o = self.opt
+        R, me = o.dp_world, o.dp_rank
+        o._sumsq.zero_()
+        o._flag.zero_()
+        sumsq = o._sumsq.narrow(0, 0, 1)
+        reds = {}
+        for gi, arena in enumerate(o.arenas):
+            sub = o.sub_size[gi]
+            for k in range(o.num_buckets[gi]):
+                red = self.lamb_red[gi].narrow(0, k * sub, sub)
+                reds[(gi, k)] = red
+                off = (k * o.partition_count + me) * sub
+                N.check(self.lib.dsb_fused_rs_norm(self.grad_ptrs[gi], self.flag_ptrs, R, me, off, sub,
+                                                   N.dtype_code(arena.dtype), 1.0 / R, N.ptr(red), N.ptr(sumsq),
+                                                   N.ptr(o._flag), N.ptr(self.scratch), self.heap.next_epoch(), s),
+                        "dsb_fused_rs_norm")
+                K._count()
+        self._mark("rs_norm")
+        o._sumsq[1] = o._flag[0].float()
+        o._mp_owned_correction(reduced=reds)      # the arena still holds raw local gradients here
+        norm, bad = o._global_scalars()
+        self._mark("scalars")
+        self._lamb_update(s)
+        self._mark("update_ag")
+        return torch.stack([norm, bad.float()])

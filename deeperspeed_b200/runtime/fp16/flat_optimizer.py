@@ -155,8 +155,12 @@ class FlatMixedPrecisionOptimizer:
 
     # ------------------------------------------------------------------ gradients
     def zero_grad(self, set_grads_to_None=True):
+        already_zero, self._grads_already_zero = getattr(self, "_grads_already_zero", False), False
         for a in self.arenas:
-            a.zero_grads()
+            if already_zero and a.grad is not None:
+                a.bind_grads()      # a fused step cleared the arena inside its kernel
+            else:
+                a.zero_grads()
         for g in self.grad_shards:
             g.zero_()
         self._reduced = False

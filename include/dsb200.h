@@ -281,6 +281,18 @@ int dsb_fused_adam_ag(const float* red32, float* p32, float* m, float* v, void* 
                       void* const* flag_ptrs, int R, int me, long slice_off, long n, int dtype, float lr, float beta1,
                       float beta2, float eps, float weight_decay, int adamw_mode, int bias_correction, int step,
                       const float* inv_scale_dev, const int* skip_dev, unsigned int epoch, void* stream);
+/* The whole ZeRO-1/2 step of one gradient bucket as one cooperative kernel (csrc/comm/fused_zero_step.cu). `phases`:
+ * 1 = reduce this rank's slice over all ranks (+ local norm terms into sumsq2), 2 = Adam + cast + all-gather + zero the
+ * local gradient bucket, 4 = trade the norm terms with the peers inside the kernel and derive inv_scale / skip /
+ * host_out2 = {norm, overflow} on the device (only together with 2). mc_grads / mc_params: multicast addresses of the
+ * gradient / parameter arenas (NVLS: multimem.ld_reduce / multimem.st), NULL = unicast peer loads / stores.
+ * slice_off, bucket_off, bucket_n, n in elements (multiples of 8); scratch: dsb_fused_zero_scratch_bytes(). */
+int dsb_fused_zero_step(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs, const void* mc_grads,
+                        void* mc_params, int R, int me, int phases, int zero_grads, long slice_off, long bucket_off,
+                        long bucket_n, long n, int dtype, void* red, float* p32, float* m, float* v, float lr,
+                        float beta1, float beta2, float eps, float weight_decay, int adamw_mode, int bias_correction,
+                        int step, float loss_scale, float clip, float* sumsq2, float* inv_scale, int* skip,
+                        float* host_out2, void* scratch, unsigned int epoch, void* stream);
 /* LAMB counterpart of dsb_fused_adam_ag, one launch per parameter group over all `n / sub` bucket slices this rank
  * owns. `upd32` holds the reduced fp32 gradients on entry (it is overwritten with the update). The owned range is
  * described by `nseg` segments: seg_start[i] .. seg_start[i+1] (local element offsets, multiples of 8,

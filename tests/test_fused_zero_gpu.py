@@ -304,3 +304,39 @@ def _zero3_fused_ag_worker(tmp):
 
 def test_zero3_fused_allgather_gemm_2gpu(tmp_path):
     run_distributed(_zero3_fused_ag_worker, world_size=2, use_cuda=True, args=(str(tmp_path),))
+
+
+def _zero2_sharded_worker():
+    """Stage 2 on 2 GPUs: sharded gradient memory (side-stream reduce-scatter per bucket, pooled staging) must give
+    the same parameters as the full gradient arena on the NCCL path."""
+    results = []
+    for mode, overlap in (("full", False), ("sharded", True), ("sharded", False)):
+        torch.manual_seed(5)
+        model = Net()
+        cfg = {"train_batch_size": 16, "train_micro_batch_size_per_gpu": 4, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-3, "weight_decay": 0.01}},
+               "fp16": {"enabled": True, "initial_scale_power": 8}, "gradient_clipping": 1.0,
+               "zero_optimization": {"stage": 2, "fused_nvlink": False, "gradient_memory": mode,
+                                     "overlap_comm": overlap, "reduce_bucket_size": 200000}}
+        engine, opt, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        assert opt.shard_gradients == (mode == "sharded")
+        g = torch.Generator().manual_seed(100 + dist.get_rank())
+        for _ in range(4 * engine.gradient_accumulation_steps()):
+            x = torch.randn(4, 256, generator=g).half().cuda()
+            y = torch.randint(0, 256, (4,), generator=g).cuda()
+            engine.backward(engine(x, y))
+            engine.step()
+        torch.cuda.synchronize()
+        results.append(torch.cat([p.detach().float().view(-1) for p in model.parameters()]))
+        if mode == "sharded":
+            own, staged = opt.gradient_memory_bytes()
+            total = sum(a.numel * 2 for a in opt.arenas)
+            assert sum(opt.num_buckets) > 1 and own == total // 2 and staged < total
+    for got in results[1:]:
+        d = (got - results[0]).abs()
+        # per-micro-batch reduction rounds differently from one reduction of the accumulated arena (fp16)
+        assert d.max().item() <= 2 * 1e-3 * 4 + 1e-3 and (d > 2e-3).float().mean().item() < 0.02, d.max().item()
+
+
+def test_zero2_sharded_gradient_memory_2gpu():
+    run_distributed(_zero2_sharded_worker, world_size=2, use_cuda=True)
