@@ -13,7 +13,7 @@ from ..ops.sparse_attention import SparseSelfAttention
 
 class GPT2Config:
     def __init__(self, vocab_size=50304, n_positions=1024, n_embd=768, n_layer=12, n_head=12, layer_norm_eps=1e-5,
-                 init_std=0.02, sparsity_config=None):
+                 init_std=0.02, sparsity_config=None, attention_impl="flash", checkpoint_blocks=False):
         self.vocab_size = vocab_size
         self.n_positions = n_positions
         self.n_embd = n_embd
@@ -22,6 +22,10 @@ class GPT2Config:
         self.layer_norm_eps = layer_norm_eps
         self.init_std = init_std
         self.sparsity_config = sparsity_config
+        # dense attention: "flash" (fused causal kernel) or "masked" (scores materialised, -inf mask, softmax: what the
+        # reference's dense layers do and the stand-in its sparse-attention numbers are quoted against)
+        self.attention_impl = attention_impl
+        self.checkpoint_blocks = checkpoint_blocks      # recompute each block in backward (activation checkpointing)
 
     @staticmethod
     def medium(**kw):
@@ -68,7 +72,11 @@ class GPT2Block(nn.Module):
         qkv = K.linear(xn, self.c_attn_w, self.c_attn_b).view(B, S, 3, H, D)
         q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))       # [B,H,S,D]
         if self.sparse_attn is not None:
-            ctx = self.sparse_attn(q.contiguous(), k.contiguous(), v.contiguous())
+            ctx = self.sparse_attn(q, k, v)
+        elif self.cfg.attention_impl == "masked":
+            scores = torch.matmul(q, k.transpose(-1, -2)) * (D ** -0.5)
+            causal = torch.ones(S, S, dtype=torch.bool, device=xn.device).tril_()
+            ctx = torch.matmul(torch.softmax(scores.masked_fill(~causal, float("-inf")), -1), v)
         else:
             ctx = F.scaled_dot_product_attention(q, k, v, is_causal=True)
         return ctx.transpose(1, 2).reshape(B, S, h)
@@ -97,7 +105,11 @@ class GPT2Model(nn.Module):
         pos = torch.arange(S, device=tokens.device)
         x = self.wte(tokens) + self.wpe(pos)[None]
         for blk in self.h:
-            x = blk(x)
+            if self.cfg.checkpoint_blocks and torch.is_grad_enabled():
+                from torch.utils.checkpoint import checkpoint
+                x = checkpoint(blk, x, use_reentrant=False)
+            else:
+                x = blk(x)
         x, _ = K.layer_norm(x, self.ln_f_w, self.ln_f_b, self.cfg.layer_norm_eps)
         logits = K.linear(x, self.wte.weight, None)      # tied LM head
         if labels is None:
