@@ -188,7 +188,18 @@ def run_ours(args):
     if args.layers:
         cfg.num_layers = args.layers
     torch.manual_seed(1234)
-    model = GPTNeoXPipe(cfg, topology=PipeDataParallelTopology(num_pp=pp, num_dp=dp))
+    if args.impl == "engine-ref-model":
+        # OUR engine (pipeline executor, ZeRO-1 arenas, fused step) around the reference arm's eager PyTorch model
+        # (baseline/ref_model.py): separates the engine's share of the speed-up from the model kernels'
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import ref_model
+        from deeperspeed_b200.pipe import PipelineModule, LayerSpec
+        vocab, hidden, heads = (1024, 256, 4) if args.tiny else (cfg.vocab_size, 2048, 16)
+        model = PipelineModule(layers=ref_model.build_specs(LayerSpec, vocab, hidden, cfg.num_layers, heads),
+                               topology=PipeDataParallelTopology(num_pp=pp, num_dp=dp), loss_fn=ref_model.ref_loss_fn,
+                               partition_method="type:ParallelTransformerLayerPipe")
+    else:
+        model = GPTNeoXPipe(cfg, topology=PipeDataParallelTopology(num_pp=pp, num_dp=dp))
     conf = ds_config(n, pp, dp)
     if pp > 1 and args.edge_split > 1:
         # our engine's bubble trimming: the first and last micro-batch are fed as slices (same samples, same gradient)
@@ -299,12 +310,13 @@ def run_ours(args):
         out = {
             "metric": METRIC, "value": value, "unit": "tokens/s", "n_gpus": n, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "fp16", "data": "synthetic tokens, random-init weights", "impl": "ours",
+            "vs_baseline": None, "dtype": "fp16", "data": "synthetic tokens, random-init weights", "impl": args.impl,
             "config": {"model": "GPT-NeoX-1.3B (24L d2048 h16 seq2048 vocab50432)" if not args.tiny else "tiny",
                        "layers": cfg.num_layers, "global_batch": conf["train_batch_size"], "seq_len": SEQ,
                        "micro_batch": MICRO_BATCH, "grad_accum": conf["gradient_accumulation_steps"],
                        "parallelism": f"pp{pp}xdp{dp} zero1", "l2": "working set per step >> 126 MB L2 (no flush needed)",
-                       "params": cfg.num_params(), "attention_backend": _attention_backend(),
+                       "params": cfg.num_params(), "attention_backend": _attention_backend() if args.impl == "ours" else
+                       "baseline/ref_model.py: eager PyTorch layers, library SDPA",
                        "pipeline_edge_split": getattr(engine, "edge_split", 1),
                        "zero_step_backend": _zero_backend(engine)},
             "clocks": clocks,
@@ -340,7 +352,8 @@ def main():
                     help="skip the extra stubbed-communication pass that measures exposed comm per step (N > 1)")
     ap.add_argument("--no-autotune", dest="no_autotune", action="store_true", help="skip the GEMM variant autotune")
     ap.add_argument("--verbose", action="store_true")
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "engine-ref-model"],
+                    help="ours; the unmodified reference; or our engine around the reference arm's eager model")
     ap.add_argument("--tiny", action="store_true", help="tiny model (CPU plumbing check only; not a valid bench)")
     ap.add_argument("--layers", type=int, default=0, help="debug override (invalidates the number)")
     ap.add_argument("--edge-split", dest="edge_split", type=int, default=1,

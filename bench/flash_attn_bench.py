@@ -29,20 +29,25 @@ for (B, S, H, D) in ((4, 2048, 16, 128), (1, 8192, 16, 128)):
     A.set_flash_fwd_variant(128)
     t_128 = timed(lambda: A.flash_attn_fwd(q, k, v, causal=True, return_lse=True))
     A.set_flash_fwd_variant(64)
+    t_64 = timed(lambda: A.flash_attn_fwd(q, k, v, causal=True, return_lse=True))
+    A.set_flash_fwd_variant(2)            # the default: two query tiles per CTA, P kept in tensor memory
     t_ours = timed(lambda: A.flash_attn_fwd(q, k, v, causal=True, return_lse=True))
     qt, kt, vt = (t.transpose(1, 2) for t in (q, k, v))
     t_lib = timed(lambda: F.scaled_dot_product_attention(qt, kt, vt, is_causal=True))
-    row = {"B": B, "S": S, "H": H, "D": D, "fwd_ours_ms": round(t_ours, 4), "fwd_ours_128key_1cta_ms": round(t_128, 4), "fwd_sdpa_ms": round(t_lib, 4),
+    row = {"B": B, "S": S, "H": H, "D": D, "fwd_ours_ms": round(t_ours, 4), "fwd_gen1_64key_ms": round(t_64, 4), "fwd_gen1_128key_ms": round(t_128, 4), "fwd_sdpa_ms": round(t_lib, 4),
            "fwd_ours_tflops": round(fl / t_ours / 1e9, 1), "fwd_sdpa_tflops": round(fl / t_lib / 1e9, 1)}
     if hasattr(A, "flash_attn_bwd"):
         out, lse = A.flash_attn_fwd(q, k, v, causal=True, return_lse=True)
         do = torch.randn_like(out)
-        t_b = timed(lambda: A.flash_attn_bwd(do, q, k, v, out, lse, causal=True))
+        t_b = timed(lambda: A.flash_attn_bwd(do, q, k, v, out, lse, causal=True))     # incl. prep + dQ finish kernels
+        A.set_flash_bwd_variant(1)
+        t_b1 = timed(lambda: A.flash_attn_bwd(do, q, k, v, out, lse, causal=True))
+        A.set_flash_bwd_variant(2)
         ql, kl, vl = (t.detach().clone().requires_grad_() for t in (qt, kt, vt))
         o = F.scaled_dot_product_attention(ql, kl, vl, is_causal=True)
         dot = do.transpose(1, 2)
         t_lb = timed(lambda: torch.autograd.grad(o, (ql, kl, vl), dot, retain_graph=True))
-        row.update({"bwd_ours_ms": round(t_b, 4), "bwd_sdpa_ms": round(t_lb, 4),
+        row.update({"bwd_ours_ms": round(t_b, 4), "bwd_gen1_ms": round(t_b1, 4), "bwd_sdpa_ms": round(t_lb, 4),
                     "bwd_ours_tflops": round(2.5 * fl / t_b / 1e9, 1), "bwd_sdpa_tflops": round(2.5 * fl / t_lb / 1e9, 1)})
     res.append(row)
     print(row)

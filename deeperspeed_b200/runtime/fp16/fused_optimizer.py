@@ -8,29 +8,26 @@ from .flat_optimizer import FlatMixedPrecisionOptimizer
 from .loss_scaler import INITIAL_LOSS_SCALE, SCALE_WINDOW, MIN_LOSS_SCALE
 
 
+# loss-scale attributes that travel in the state dict (the last three only with a dynamic scale)
+_SCALE_KEYS = ("dynamic_loss_scale", "cur_scale", "cur_iter")
+_DYNAMIC_KEYS = ("last_overflow_iter", "scale_factor", "scale_window")
+
+
 class FP16_Optimizer(FlatMixedPrecisionOptimizer):
     def __init__(self, init_optimizer, static_loss_scale=1.0, dynamic_loss_scale=False, initial_dynamic_scale=2 ** 32,
                  dynamic_loss_args=None, verbose=True, mpu=None, clip_grad=0.0, fused_adam_legacy=False, timers=None,
                  dp_process_group=None, fp32_allreduce=False):
         self.fused_adam_legacy = fused_adam_legacy
         self.timers = timers
-        if dynamic_loss_scale:
-            self.dynamic_loss_scale = True
-            self.cur_iter = 0
-            self.last_overflow_iter = -1
-            self.scale_factor = 2
-            if dynamic_loss_args is None:
-                self.cur_scale = initial_dynamic_scale
-                self.scale_window = 1000
-                self.min_loss_scale = 1
-            else:
-                self.cur_scale = dynamic_loss_args[INITIAL_LOSS_SCALE]
-                self.scale_window = dynamic_loss_args[SCALE_WINDOW]
-                self.min_loss_scale = dynamic_loss_args[MIN_LOSS_SCALE]
-        else:
-            self.dynamic_loss_scale = False
-            self.cur_iter = 0
-            self.cur_scale = static_loss_scale
+        self.dynamic_loss_scale = bool(dynamic_loss_scale)
+        self.cur_iter = 0
+        self.cur_scale = static_loss_scale
+        if self.dynamic_loss_scale:
+            knobs = dynamic_loss_args or {INITIAL_LOSS_SCALE: initial_dynamic_scale, SCALE_WINDOW: 1000,
+                                          MIN_LOSS_SCALE: 1}
+            self.cur_scale = knobs[INITIAL_LOSS_SCALE]
+            self.scale_window, self.min_loss_scale = knobs[SCALE_WINDOW], knobs[MIN_LOSS_SCALE]
+            self.scale_factor, self.last_overflow_iter = 2, -1
         super().__init__(init_optimizer, dp_process_group=dp_process_group, shard=False, mpu=mpu, clip_grad=clip_grad,
                          fp32_allreduce=fp32_allreduce, verbose=verbose)
         # reference attribute names
@@ -49,25 +46,24 @@ class FP16_Optimizer(FlatMixedPrecisionOptimizer):
         self._update_scale(overflow)
 
     def _update_scale(self, skip):
-        if self.dynamic_loss_scale:
-            prev_scale = self.cur_scale
-            if skip:
-                self.cur_scale = max(self.cur_scale / self.scale_factor, self.min_loss_scale)
-                self.last_overflow_iter = self.cur_iter
-                if self.verbose:
-                    logger.info(f"\nGrad overflow on iteration {self.cur_iter}")
-                    logger.info(f"Reducing dynamic loss scale from {prev_scale} to {self.cur_scale}")
-            else:
-                stable_interval = (self.cur_iter - self.last_overflow_iter) - 1
-                if (stable_interval > 0) and (stable_interval % self.scale_window == 0):
-                    self.cur_scale *= self.scale_factor
-                    if self.verbose:
-                        logger.info(f"No Grad overflow for {self.scale_window} iterations")
-                        logger.info(f"Increasing dynamic loss scale from {prev_scale} to {self.cur_scale}")
-        else:
+        """FP16_Optimizer rule (no hysteresis): halve on overflow, double after `scale_window` clean iterations."""
+        say = logger.info if self.verbose else (lambda *a: None)
+        before = self.cur_scale
+        if not self.dynamic_loss_scale:
             if skip:
                 logger.info("Grad overflow on iteration: %s", self.cur_iter)
                 logger.info("Using static loss scale of: %s", self.cur_scale)
+        elif skip:
+            self.cur_scale = max(before / self.scale_factor, self.min_loss_scale)
+            self.last_overflow_iter = self.cur_iter
+            say(f"\nGrad overflow on iteration {self.cur_iter}")
+            say(f"Reducing dynamic loss scale from {before} to {self.cur_scale}")
+        else:
+            clean = self.cur_iter - self.last_overflow_iter - 1
+            if clean > 0 and clean % self.scale_window == 0:
+                self.cur_scale = before * self.scale_factor
+                say(f"No Grad overflow for {self.scale_window} iterations")
+                say(f"Increasing dynamic loss scale from {before} to {self.cur_scale}")
         self.cur_iter += 1
 
     def step_fused_adam(self, closure=None):
@@ -86,17 +82,13 @@ class FP16_Optimizer(FlatMixedPrecisionOptimizer):
                 grad.data.mul_(1.0 / combined_scale)
         return combined_scale
 
+    def _scale_keys(self, dynamic):
+        return _SCALE_KEYS + (_DYNAMIC_KEYS if dynamic else ())
+
     def state_dict(self):
-        sd = {
-            "dynamic_loss_scale": self.dynamic_loss_scale,
-            "cur_scale": self.cur_scale,
-            "cur_iter": self.cur_iter,
-        }
-        if self.dynamic_loss_scale:
-            sd["last_overflow_iter"] = self.last_overflow_iter
-            sd["scale_factor"] = self.scale_factor
-            sd["scale_window"] = self.scale_window
+        sd = {key: getattr(self, key) for key in self._scale_keys(self.dynamic_loss_scale)}
         sd["optimizer_state_dict"] = self.optimizer.state_dict()
+        # masters are saved without the arena's alignment padding, so the file does not depend on the layout
         sd["fp32_groups_flat"] = [a.to_unpadded(m.data) if a.numel_used != a.numel_unpadded else
                                   m.data.narrow(0, 0, a.numel_unpadded).clone()
                                   for a, m in zip(self.arenas, self.fp32_masters)]
@@ -107,22 +99,17 @@ class FP16_Optimizer(FlatMixedPrecisionOptimizer):
         super().refresh_fp32_params()
 
     def load_state_dict(self, state_dict, load_optimizer_states=True):
-        self.dynamic_loss_scale = state_dict["dynamic_loss_scale"]
-        self.cur_scale = state_dict["cur_scale"]
-        self.cur_iter = state_dict["cur_iter"]
-        if state_dict["dynamic_loss_scale"]:
-            self.last_overflow_iter = state_dict["last_overflow_iter"]
-            self.scale_factor = state_dict["scale_factor"]
-            self.scale_window = state_dict["scale_window"]
+        for key in self._scale_keys(state_dict["dynamic_loss_scale"]):
+            setattr(self, key, state_dict[key])
+        self.clip_grad = state_dict["clip_grad"]
         if load_optimizer_states:
             self._load_inner_state(state_dict["optimizer_state_dict"])
-        self.clip_grad = state_dict["clip_grad"]
-        for a, cur, saved in zip(self.arenas, self.fp32_masters, state_dict["fp32_groups_flat"]):
-            saved = saved.to(cur.device)
-            if saved.numel() == cur.numel():
-                cur.data.copy_(saved)
+        for arena, master, saved in zip(self.arenas, self.fp32_masters, state_dict["fp32_groups_flat"]):
+            saved = saved.to(master.device)
+            if saved.numel() == master.numel():
+                master.data.copy_(saved)
             else:
-                a.from_unpadded(saved.float(), out=cur.data)
+                arena.from_unpadded(saved.float(), out=master.data)
 
     def _load_inner_state(self, osd):
         """Inner state tensors are saved unpadded-flat per group; pad them to the arena layout on load."""

@@ -3,7 +3,7 @@ import collections, os, re, subprocess, sys
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 lib = os.path.join(root, "deeperspeed_b200", "lib", "libdsb200.so")
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
-pat = re.compile(r"\b(UTC[A-Z0-9]*MMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UBLKCP|HMMA|SYNCS|LDGSTS|RED|ATOM)\b")
+pat = re.compile(r"\b(UTC[A-Z0-9]*MMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UTMAREDG|UBLKCP|UBLKRED|LDGMC|HMMA|SYNCS|LDGSTS|RED|ATOM)\b")
 cur, counts = None, collections.OrderedDict()
 for line in out.splitlines():
     m = re.search(r"Function : (\S+)", line)
