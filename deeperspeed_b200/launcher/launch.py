@@ -10,7 +10,6 @@ import subprocess
 import sys
 import time
 from argparse import ArgumentParser, REMAINDER
-from collections import defaultdict
 
 from ..runtime.constants import TORCH_DISTRIBUTED_DEFAULT_PORT
 from ..utils.logging import logger
@@ -34,92 +33,76 @@ def decode_world_info(encoded):
 
 
 def build_rank_env(world_info, node_rank, master_addr, master_port, detect_nvlink_pairs=False):
-    """Returns (list of per-process env dicts, world size) for this node. Global ranks are host-major in dict order."""
-    node_list = list(world_info.keys())
-    local_node = node_list[node_rank]
-    local_gpu_ids = list(world_info[local_node])
+    """Returns (list of per-process env dicts, world size) for this node. Global ranks are host-major in dict order:
+    the first rank of a node is the number of GPUs listed on the nodes before it."""
+    hosts = list(world_info)
+    gpus = list(world_info[hosts[node_rank]])
     if detect_nvlink_pairs:
         from .gpu_topology import detect_nvlink_pairs as _detect
-        order = [g for g in _detect() if g in local_gpu_ids]
-        if len(order) == len(local_gpu_ids):
-            local_gpu_ids = order
-    global_rank_mapping = defaultdict(list)
-    curr_global_rank = 0
-    dist_world_size = 0
-    for node_id in node_list:
-        gids = world_info[node_id]
-        dist_world_size += len(gids)
-        for _ in gids:
-            global_rank_mapping[node_id].append(curr_global_rank)
-            curr_global_rank += 1
-    envs = []
-    for local_rank in range(len(local_gpu_ids)):
-        env = {
-            "CUDA_VISIBLE_DEVICES": ",".join(map(str, local_gpu_ids)),
-            "MASTER_ADDR": str(master_addr),
-            "MASTER_PORT": str(master_port),
-            "WORLD_SIZE": str(dist_world_size),
-            "RANK": str(global_rank_mapping[local_node][local_rank]),
-            "LOCAL_RANK": str(local_rank),
-        }
-        envs.append(env)
-    return envs, dist_world_size
+        paired = [g for g in _detect() if g in gpus]
+        if len(paired) == len(gpus):
+            gpus = paired
+    first_rank = sum(len(world_info[h]) for h in hosts[:node_rank])
+    world_size = sum(len(world_info[h]) for h in hosts)
+    shared = {"CUDA_VISIBLE_DEVICES": ",".join(str(g) for g in gpus), "MASTER_ADDR": str(master_addr),
+              "MASTER_PORT": str(master_port), "WORLD_SIZE": str(world_size)}
+    return [dict(shared, RANK=str(first_rank + local), LOCAL_RANK=str(local)) for local in range(len(gpus))], world_size
+
+
+class _Children:
+    """The training processes of this node: started together, and brought down together - on a signal to the launcher
+    or as soon as one of them fails (its exit code becomes the launcher's; the reference exits 1 whatever failed)."""
+
+    def __init__(self, commands_and_envs):
+        self.procs = [(subprocess.Popen(cmd, env=env), cmd) for cmd, env in commands_and_envs]
+        for sig in (signal.SIGINT, signal.SIGTERM):
+            signal.signal(sig, self._on_signal)
+
+    def kill_all(self):
+        for proc, _ in self.procs:
+            logger.info(f"Killing subprocess {proc.pid}")
+            try:
+                proc.kill()
+            except Exception:
+                pass
+
+    def _on_signal(self, signum, frame):
+        self.kill_all()
+        logger.info(f"Main process received {signal.Signals(signum).name}, exiting")
+        sys.exit(1)
+
+    def wait(self, poll_s=1.0):
+        running = list(self.procs)
+        while running:
+            for proc, cmd in list(running):
+                code = proc.poll()
+                if code is None:
+                    continue
+                if code != 0:
+                    self.kill_all()
+                    logger.error(f"{cmd} exited with code {code}; siblings killed")
+                    sys.exit(code if 0 < code < 256 else 1)
+                running.remove((proc, cmd))
+            if running:
+                time.sleep(poll_s)
 
 
 def main(args=None):
     args = parse_args(args)
-    current_env = os.environ.copy()
-    for k in current_env.keys():
-        if "NCCL" in k:
-            logger.info("%s %s %s", args.node_rank, k, current_env[k])
+    for name, value in os.environ.items():
+        if "NCCL" in name:
+            logger.info("%s %s %s", args.node_rank, name, value)
     assert args.world_info != "None", "must provide world info dict"
     world_info = decode_world_info(args.world_info)
     logger.info("WORLD INFO DICT: {}".format(world_info))
     envs, world = build_rank_env(world_info, args.node_rank, args.master_addr, args.master_port, args.detect_nvlink_pairs)
     logger.info("nnodes={}, num_local_procs={}, node_rank={}, dist_world_size={}".format(len(world_info), len(envs),
                                                                                         args.node_rank, world))
-    processes = []
+    launches = []
     for env in envs:
-        e = dict(current_env)
-        e.update(env)
-        cmd = [sys.executable, "-u", args.training_script, "--local_rank={}".format(env["LOCAL_RANK"])] + args.training_script_args
-        processes.append(subprocess.Popen(cmd, env=e))
-
-    sig_names = {2: "SIGINT", 15: "SIGTERM"}
-    last_return_code = None
-
-    def sigkill_handler(signum, frame):
-        for process in processes:
-            logger.info(f"Killing subprocess {process.pid}")
-            try:
-                process.kill()
-            except Exception:
-                pass
-        if last_return_code is not None:
-            # the reference raises CalledProcessError here, which makes the launcher itself exit with 1; handing the
-            # failed rank's own code to the caller (runner / scheduler) is more useful
-            logger.error(f"{cmd} exited with code {last_return_code}; siblings killed")
-            sys.exit(last_return_code if 0 < last_return_code < 256 else 1)
-        if signum in sig_names:
-            logger.info(f"Main process received {sig_names[signum]}, exiting")
-        sys.exit(1)
-
-    signal.signal(signal.SIGINT, sigkill_handler)
-    signal.signal(signal.SIGTERM, sigkill_handler)
-
-    alive_processes = set(processes)
-    while len(alive_processes):
-        finished_processes = []
-        for process in alive_processes:
-            if process.poll() is None:
-                continue
-            if process.returncode != 0:
-                last_return_code = process.returncode   # first failure kills the siblings
-                sigkill_handler(signal.SIGTERM, None)
-            else:
-                finished_processes.append(process)
-        alive_processes = set(alive_processes) - set(finished_processes)
-        time.sleep(1)
+        cmd = [sys.executable, "-u", args.training_script, "--local_rank={}".format(env["LOCAL_RANK"])]
+        launches.append((cmd + args.training_script_args, dict(os.environ, **env)))
+    _Children(launches).wait()
 
 
 if __name__ == "__main__":

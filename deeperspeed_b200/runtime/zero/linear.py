@@ -1,55 +1,53 @@
 """Memory-efficient linear for ZeRO-3: the autograd function keeps a *reference to the Parameter object*, not to
 its (gathered) storage, so the weight can be released between forward and backward and re-gathered by the ZeRO-3
 hooks (reference deepspeed/runtime/zero/linear.py:29-168). On CUDA the products run on the tcgen05 GEMM kernels."""
-import math
-
 import torch
 from torch import Tensor
-from torch.nn import init
-from torch.nn.modules.module import Module
-from torch.nn.parameter import Parameter
 
 from ...ops import kernels as K
 
-tensor_map = {}
+tensor_map = {}     # kept for code that imported it; this implementation does not need a registry
+
+
+def _tensor_core_ok(x2, out_features):
+    return x2.is_cuda and x2.dtype in (torch.float16, torch.bfloat16) and x2.shape[-1] % 8 == 0 and out_features % 8 == 0
 
 
 class LinearFunctionForZeroStage3(torch.autograd.Function):
+    """y = x W^T + b. Only the INPUT goes through save_for_backward; weight and bias are remembered as the Parameter
+    objects themselves (plain attributes of ctx), so autograd pins no gathered storage: between forward and backward
+    ZeRO-3 may shrink `weight.data` to its placeholder, and by the time backward reads `ctx.weight.data` the
+    pre-backward hook has gathered it again."""
+
     @staticmethod
     def forward(ctx, input, weight, bias=None):
-        weight_id = id(weight)
-        bias_id = id(bias)
-        tensor_map[weight_id] = weight
-        tensor_map[bias_id] = bias
-        ctx.save_for_backward(input, torch.tensor(weight_id), torch.tensor(bias_id))
-        if input.is_cuda and input.dtype in (torch.float16, torch.bfloat16) and input.shape[-1] % 8 == 0 \
-                and weight.shape[0] % 8 == 0:
-            x2 = input.reshape(-1, input.shape[-1])
-            out = K.gemm(x2, weight, trans_b=True, epilogue=1 if bias is not None else 0, bias=bias)
-            return out.view(*input.shape[:-1], weight.shape[0])
-        if input.dim() == 2 and bias is not None:
-            return torch.addmm(bias, input, weight.t())
-        output = input.matmul(weight.t())
-        if bias is not None:
-            output = output + bias
-        return output
+        ctx.save_for_backward(input)
+        ctx.weight, ctx.bias = weight, bias
+        x2 = input.reshape(-1, input.shape[-1])
+        if _tensor_core_ok(x2, weight.shape[0]):
+            y = K.gemm(x2, weight, trans_b=True, epilogue=1 if bias is not None else 0, bias=bias)
+        elif bias is not None:
+            y = torch.addmm(bias, x2, weight.t())
+        else:
+            y = x2.matmul(weight.t())
+        return y.view(*input.shape[:-1], weight.shape[0])
 
     @staticmethod
     def backward(ctx, grad_output):
-        input, weight_id, bias_id = ctx.saved_tensors
-        weight = tensor_map[weight_id.item()]
-        bias = tensor_map[bias_id.item()]
+        (input,) = ctx.saved_tensors
+        weight, bias = ctx.weight, ctx.bias
+        want_x, want_w, want_b = ctx.needs_input_grad
+        g2 = grad_output.reshape(-1, grad_output.shape[-1])
+        x2 = input.reshape(-1, input.shape[-1])
+        fast = _tensor_core_ok(g2, weight.shape[1]) and g2.shape[0] % 8 == 0 and g2.is_contiguous()
         grad_input = grad_weight = grad_bias = None
-        if ctx.needs_input_grad[0]:
-            grad_input = grad_output.matmul(weight)
-        if ctx.needs_input_grad[1]:
-            dim = grad_output.dim()
-            if dim > 2:
-                grad_weight = grad_output.reshape(-1, grad_output.shape[-1]).t().matmul(input.reshape(-1, input.shape[-1]))
-            else:
-                grad_weight = grad_output.t().matmul(input)
-        if bias is not None and ctx.needs_input_grad[2]:
-            grad_bias = grad_output.reshape(-1, grad_output.shape[-1]).sum(0)
+        if want_x:
+            gx = K.gemm(g2, weight.data, trans_b=False) if fast else g2.matmul(weight)
+            grad_input = gx.view(input.shape)
+        if want_w:
+            grad_weight = K.gemm(g2, x2.contiguous(), trans_a=True, trans_b=False) if fast else g2.t().matmul(x2)
+        if bias is not None and want_b:
+            grad_bias = g2.sum(0)
         return grad_input, grad_weight, grad_bias
 
     @staticmethod
@@ -118,30 +116,8 @@ class FusedAGLinearFunction(torch.autograd.Function):
         return grad_input, grad_bias, None, None
 
 
-class LinearModuleForZeroStage3(Module):
-    """nn.Linear twin built on LinearFunctionForZeroStage3."""
-    __constants__ = ["in_features", "out_features"]
-
-    def __init__(self, in_features: int, out_features: int, bias: bool = True) -> None:
-        super().__init__()
-        self.in_features = in_features
-        self.out_features = out_features
-        self.weight = Parameter(torch.Tensor(out_features, in_features))
-        if bias:
-            self.bias = Parameter(torch.Tensor(out_features))
-        else:
-            self.register_parameter("bias", None)
-        self.reset_parameters()
-
-    def reset_parameters(self) -> None:
-        init.kaiming_uniform_(self.weight, a=math.sqrt(5))
-        if self.bias is not None:
-            fan_in, _ = init._calculate_fan_in_and_fan_out(self.weight)
-            bound = 1 / math.sqrt(fan_in)
-            init.uniform_(self.bias, -bound, bound)
+class LinearModuleForZeroStage3(torch.nn.Linear):
+    """nn.Linear (same parameters, same initialisation) whose forward is LinearFunctionForZeroStage3."""
 
     def forward(self, input: Tensor) -> Tensor:
         return LinearFunctionForZeroStage3.apply(input, self.weight, self.bias)
-
-    def extra_repr(self) -> str:
-        return "in_features={}, out_features={}, bias={}".format(self.in_features, self.out_features, self.bias is not None)
