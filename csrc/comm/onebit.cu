@@ -57,44 +57,55 @@ DSB_DEVICE uint32_t pack_nibbles(uint32_t nib, int lane) {
 }
 DSB_DEVICE float sgn_sel(uint32_t bits, int t, float s) { return ((bits >> t) & 1u) ? s : -s; }
 
+// Optional fusion with 1-bit Adam's compression stage (reference runtime/fp16/onebit/adam.py:200-260): with `g` the
+// momentum is formed on the way in (m <- beta1 * m + (1 - beta1) * g), with `p` the parameter update runs on the way
+// out (p <- p - lr * (m / (sqrt(v) + eps) + wd * p)) - the averaged momentum is decompressed straight into the update
+// instead of being written, re-read and combined by separate elementwise passes.
+struct ObAdam {
+    const float* g;      // local gradient (nullptr: m already holds the momentum to exchange)
+    float* p;            // fp32 parameters to update (nullptr: exchange only)
+    const float* v;      // frozen second moment
+    float beta1, lr, eps, wd;
+};
+
 // All element loops run on float4 (16-byte accesses, two independent iterations in flight per thread in the pure
 // streaming phases): the first version used 4-byte accesses and reached ~1/6 of HBM bandwidth
-// (profiles/onebit_bench_w*.json history).
+// (profiles/onebit_bench_w*.json history). `m` holds n_real <= n elements (n = padded size of the error buffers); the
+// compensated values live in the error buffers between the phases (x in e_w, y in e_s), so m is read once and
+// written once.
 __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict__ m, float* __restrict__ e_w,
-                                                               float* __restrict__ e_s, long n, int W, int me,
-                                                               ObPtrs P, float* __restrict__ partials, uint32_t epoch) {
+                                                               float* __restrict__ e_s, long n, long n_real, int W,
+                                                               int me, ObPtrs P, ObAdam A,
+                                                               float* __restrict__ partials, uint32_t epoch) {
     cg::grid_group grid = cg::this_grid();
     __shared__ float sh[33];
     __shared__ float ssc[OB_MAX_RANKS];
     const long c = n / W;
     const long cwords = c >> 5;
-    const long n4 = n >> 2, c4 = c >> 2;
+    const long n4 = n >> 2, c4 = c >> 2, r4 = n_real >> 2;
     const long gtid = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const long gstride = (long)gridDim.x * blockDim.x;
     const int lane = threadIdx.x & 31;
     float4* m4 = reinterpret_cast<float4*>(m);
     float4* ew4 = reinterpret_cast<float4*>(e_w);
     float4* es4 = reinterpret_cast<float4*>(e_s);
+    const float4* g4 = reinterpret_cast<const float4*>(A.g);
 
-    // ---- phase A: x = m + e_w (kept in m), partial sum of squares
+    // ---- phase A: x = momentum + e_w (kept in e_w), partial sum of squares
     float acc = 0.f;
-    {
-        long i = gtid;
-        for (; i + gstride < n4; i += 2 * gstride) {
-            float4 a0 = m4[i], b0 = ew4[i], a1 = m4[i + gstride], b1 = ew4[i + gstride];
-            a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
-            a1.x += b1.x; a1.y += b1.y; a1.z += b1.z; a1.w += b1.w;
-            m4[i] = a0;
-            m4[i + gstride] = a1;
-            acc += a0.x * a0.x + a0.y * a0.y + a0.z * a0.z + a0.w * a0.w;
-            acc += a1.x * a1.x + a1.y * a1.y + a1.z * a1.z + a1.w * a1.w;
+    for (long i = gtid; i < n4; i += gstride) {
+        float4 x = ew4[i];
+        if (i < r4) {
+            float4 a = m4[i];
+            if (g4 != nullptr) {
+                const float4 g = g4[i];
+                const float b1 = A.beta1, b2 = 1.f - A.beta1;
+                a.x = b1 * a.x + b2 * g.x; a.y = b1 * a.y + b2 * g.y; a.z = b1 * a.z + b2 * g.z; a.w = b1 * a.w + b2 * g.w;
+            }
+            x.x += a.x; x.y += a.y; x.z += a.z; x.w += a.w;
         }
-        if (i < n4) {
-            float4 a0 = m4[i], b0 = ew4[i];
-            a0.x += b0.x; a0.y += b0.y; a0.z += b0.z; a0.w += b0.w;
-            m4[i] = a0;
-            acc += a0.x * a0.x + a0.y * a0.y + a0.z * a0.z + a0.w * a0.w;
-        }
+        ew4[i] = x;
+        acc += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
     }
     acc = block_sum(acc, sh);
     if (threadIdx.x == 0) partials[blockIdx.x] = acc;
@@ -108,7 +119,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
         const bool valid = i < n4;
         uint32_t nib = 0;
         if (valid) {
-            const float4 x = m4[i];
+            const float4 x = ew4[i];
             nib = (x.x >= 0.f ? 1u : 0u) | (x.y >= 0.f ? 2u : 0u) | (x.z >= 0.f ? 4u : 0u) | (x.w >= 0.f ? 8u : 0u);
             float4 e;
             e.x = x.x - sgn_sel(nib, 0, s_w); e.y = x.y - sgn_sel(nib, 1, s_w);
@@ -128,8 +139,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     if (blockIdx.x == 0) ob_barrier(P, W, me, 0, epoch);
     grid.sync();
 
-    // ---- phase C: server average of my chunk + server error feedback (y kept in m[me*c ..])
-    float4* y4 = reinterpret_cast<float4*>(m + (long)me * c);
+    // ---- phase C: server average of my chunk + server error feedback (y kept in e_s)
     const uint32_t* rs = P.recv_signs[me];
     if (threadIdx.x < W) ssc[threadIdx.x] = __ldcg(P.recv_scales[me] + threadIdx.x);
     __syncthreads();
@@ -146,7 +156,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
         }
         const float4 e = es4[j];
         y.x = y.x * inv_w + e.x; y.y = y.y * inv_w + e.y; y.z = y.z * inv_w + e.z; y.w = y.w * inv_w + e.w;
-        y4[j] = y;
+        es4[j] = y;
         acc += y.x * y.x + y.y * y.y + y.z * y.z + y.w * y.w;
     }
     acc = block_sum(acc, sh);
@@ -160,7 +170,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
         const bool valid = j < c4;
         uint32_t nib = 0;
         if (valid) {
-            const float4 y = y4[j];
+            const float4 y = es4[j];
             nib = (y.x >= 0.f ? 1u : 0u) | (y.y >= 0.f ? 2u : 0u) | (y.z >= 0.f ? 4u : 0u) | (y.w >= 0.f ? 8u : 0u);
             float4 e;
             e.x = y.x - sgn_sel(nib, 0, s_s); e.y = y.y - sgn_sel(nib, 1, s_s);
@@ -179,24 +189,25 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     if (blockIdx.x == 0) ob_barrier(P, W, me, 1, epoch);
     grid.sync();
 
-    // ---- phase E: decompress everything into m
+    // ---- phase E: decompress the averaged momentum into m (and, fused, apply the parameter update)
     const uint32_t* gs = P.gath_signs[me];
     if (threadIdx.x < W) ssc[threadIdx.x] = __ldcg(P.gath_scales[me] + threadIdx.x);
     __syncthreads();
-    {
-        long i = gtid;
-        for (; i + gstride < n4; i += 2 * gstride) {
-            const long i1 = i + gstride;
-            const uint32_t b0 = __ldcg(gs + (i >> 3)) >> ((int)(i & 7) * 4);
-            const uint32_t b1 = __ldcg(gs + (i1 >> 3)) >> ((int)(i1 & 7) * 4);
-            const float s0 = ssc[(int)(i / c4)], s1 = ssc[(int)(i1 / c4)];
-            m4[i] = make_float4(sgn_sel(b0, 0, s0), sgn_sel(b0, 1, s0), sgn_sel(b0, 2, s0), sgn_sel(b0, 3, s0));
-            m4[i1] = make_float4(sgn_sel(b1, 0, s1), sgn_sel(b1, 1, s1), sgn_sel(b1, 2, s1), sgn_sel(b1, 3, s1));
-        }
-        if (i < n4) {
-            const uint32_t b0 = __ldcg(gs + (i >> 3)) >> ((int)(i & 7) * 4);
-            const float s0 = ssc[(int)(i / c4)];
-            m4[i] = make_float4(sgn_sel(b0, 0, s0), sgn_sel(b0, 1, s0), sgn_sel(b0, 2, s0), sgn_sel(b0, 3, s0));
+    float4* p4 = reinterpret_cast<float4*>(A.p);
+    const float4* v4 = reinterpret_cast<const float4*>(A.v);
+    for (long i = gtid; i < r4; i += gstride) {
+        const uint32_t b0 = __ldcg(gs + (i >> 3)) >> ((int)(i & 7) * 4);
+        const float s0 = ssc[(int)(i / c4)];
+        const float4 mm = make_float4(sgn_sel(b0, 0, s0), sgn_sel(b0, 1, s0), sgn_sel(b0, 2, s0), sgn_sel(b0, 3, s0));
+        m4[i] = mm;
+        if (p4 != nullptr) {
+            const float4 v = v4[i];
+            float4 p = p4[i];
+            p.x -= A.lr * (mm.x / (sqrtf(v.x) + A.eps) + A.wd * p.x);
+            p.y -= A.lr * (mm.y / (sqrtf(v.y) + A.eps) + A.wd * p.y);
+            p.z -= A.lr * (mm.z / (sqrtf(v.z) + A.eps) + A.wd * p.z);
+            p.w -= A.lr * (mm.w / (sqrtf(v.w) + A.eps) + A.wd * p.w);
+            p4[i] = p;
         }
     }
 }
@@ -211,10 +222,11 @@ extern "C" long dsb_onebit_heap_bytes(long n, int W) {
     return 2 * (words * 4 + 256) + 2 * 256;
 }
 
-extern "C" int dsb_onebit_allreduce(float* m, float* e_w, float* e_s, long n, int W, int me, void* const* heap_bases,
-                                    long region_off, void* const* flag_bases, void* scratch, unsigned int epoch,
-                                    void* stream) {
-    if (W < 1 || W > OB_MAX_RANKS || n <= 0 || (n % (32L * W)) || !scratch) return DSB_ERR_ARG;
+static int onebit_launch(float* m, float* e_w, float* e_s, long n, long n_real, int W, int me,
+                         void* const* heap_bases, long region_off, void* const* flag_bases, void* scratch,
+                         unsigned int epoch, const ObAdam& adam, void* stream) {
+    if (W < 1 || W > OB_MAX_RANKS || n <= 0 || (n % (32L * W)) || n_real <= 0 || n_real > n || (n_real % 4) || !scratch)
+        return DSB_ERR_ARG;
     const long words = n / 32;
     const long sign_bytes = words * 4 + 256;
     ObPtrs P;
@@ -233,8 +245,27 @@ extern "C" int dsb_onebit_allreduce(float* m, float* e_w, float* e_s, long n, in
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, onebit_allreduce_kernel, 512, 0);
     if (per_sm < 1) per_sm = 1;
     if (per_sm > 2) per_sm = 2;
-    void* args[] = {&m, &e_w, &e_s, &n, &W, &me, &P, &partials, &epoch};
+    ObAdam A = adam;
+    void* args[] = {&m, &e_w, &e_s, &n, &n_real, &W, &me, &P, &A, &partials, &epoch};
     cudaError_t e = cudaLaunchCooperativeKernel((const void*)onebit_allreduce_kernel, dim3(sms * per_sm), dim3(512),
                                                 args, 0, reinterpret_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int dsb_onebit_allreduce(float* m, float* e_w, float* e_s, long n, int W, int me, void* const* heap_bases,
+                                    long region_off, void* const* flag_bases, void* scratch, unsigned int epoch,
+                                    void* stream) {
+    ObAdam none = {nullptr, nullptr, nullptr, 0.f, 0.f, 0.f, 0.f};
+    return onebit_launch(m, e_w, e_s, n, n, W, me, heap_bases, region_off, flag_bases, scratch, epoch, none, stream);
+}
+
+// 1-bit Adam compression-stage step in one kernel: momentum from the local gradient, compressed exchange, parameter
+// update. m / g / p / v hold n_real elements (multiple of 4), the error buffers the padded n.
+extern "C" int dsb_onebit_adam_step(float* m, const float* g, float* p, const float* v, float* e_w, float* e_s, long n,
+                                    long n_real, int W, int me, void* const* heap_bases, long region_off,
+                                    void* const* flag_bases, void* scratch, unsigned int epoch, float beta1, float lr,
+                                    float eps, float weight_decay, void* stream) {
+    if (!g || !p || !v) return DSB_ERR_ARG;
+    ObAdam a = {g, p, v, beta1, lr, eps, weight_decay};
+    return onebit_launch(m, e_w, e_s, n, n_real, W, me, heap_bases, region_off, flag_bases, scratch, epoch, a, stream);
 }

@@ -994,16 +994,30 @@ extern "C" int dsb_flash_attn_fwd_variant(int v) {
 // out[b, s, h, :] = softmax(scale * q[b, s, h, :] . k[b, :, h, :]^T (+ causal mask)) v[b, :, h, :]; lse (optional,
 // [B, H, S] fp32) receives the natural-log sum of exponentials of the scaled scores of every row.
 // q / k / v / out: [B, S, H, 128] with element strides (s*b, s*s, s*h, 1); S a multiple of 128.
+// dropout probability -> the kernels' 16-bit threshold form (fa2::Dropout); p is quantised to 1 / 65536
+static dsb::fa2::Dropout make_dropout(float p, unsigned seed) {
+    dsb::fa2::Dropout d = {0u, 1.f, seed};
+    if (p > 0.f) {
+        unsigned thr = (unsigned)(p * 65536.f + 0.5f);
+        if (thr > 65535u) thr = 65535u;
+        d.thr16 = thr;
+        d.inv_keep = 65536.f / (float)(65536u - thr);
+    }
+    return d;
+}
+
 static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H, int D,
                           long q_sb, long q_ss, long q_sh, long k_sb, long k_ss, long k_sh, long v_sb, long v_ss,
                           long v_sh, long o_sb, long o_ss, long o_sh, float scale, int causal, int dtype,
-                          const int* sched, int sched_hstride, int sched_pstride, const float* kpm, void* stream_) {
+                          const int* sched, int sched_hstride, int sched_pstride, const float* kpm, void* stream_,
+                          float dropout_p = 0.f, unsigned dropout_seed = 0) {
     using namespace dsb;
     using namespace dsb::fa;
     ensure_context_on_this_thread();
     if (B <= 0 || S <= 0 || H <= 0) return 0;
     if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
     if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
+    if (dropout_p < 0.f || dropout_p >= 1.f) return DSB_ERR_ARG;
     const long strides[12] = {q_sb, q_ss, q_sh, k_sb, k_ss, k_sh, v_sb, v_ss, v_sh, o_sb, o_ss, o_sh};
     for (int i = 0; i < 12; ++i)
         if (strides[i] % 8) return DSB_ERR_ALIGN;
@@ -1024,7 +1038,7 @@ static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out
     const float scale_log2 = scale * 1.4426950408889634f;
     dim3 grid(S / BQ, B * H);
     cudaError_t e;
-    const bool extras = sched != nullptr || kpm != nullptr;
+    const bool extras = sched != nullptr || kpm != nullptr || dropout_p > 0.f;
     if (sched != nullptr && S % 256) return DSB_ERR_SIZE;   // schedules are per 256-row query block
     if (g_fa_fwd_variant == 2 || extras) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
@@ -1032,7 +1046,7 @@ static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out
         rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);
         if (rc) return rc;
         return dsb::fa2::launch_fwd(tq, tk, tv, to, lse, B, S, H, scale_log2, causal, bf, sched, sched_hstride,
-                                    sched_pstride, kpm, stream);
+                                    sched_pstride, kpm, make_dropout(dropout_p, dropout_seed), stream);
     }
     if (g_fa_fwd_variant != 128) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
@@ -1087,6 +1101,20 @@ extern "C" int dsb_flash_attn_fwd_ex(const void* q, const void* k, const void* v
     return flash_fwd_impl(q, k, v, out, lse, B, S, H, D, strides[0], strides[1], strides[2], strides[3], strides[4],
                           strides[5], strides[6], strides[7], strides[8], strides[9], strides[10], strides[11], scale,
                           causal, dtype, sched, sched_hstride, sched_pstride, kpm, stream_);
+}
+
+// dsb_flash_attn_fwd_ex with attention dropout inside the kernel: every probability is dropped with probability
+// `dropout_p` (quantised to 1 / 65536) and the kept ones are scaled by 1 / (1 - p), as torch.nn.functional.dropout does
+// on the softmax output. The keep bits are a hash of (seed, batch, head, query, key): pass the same `dropout_seed` to
+// dsb_flash_attn_bwd2_drop. Reference: the attention-probability dropout of csrc/transformer/dropout_kernels.cu as used
+// by ds_transformer_cuda.cpp:225-236.
+extern "C" int dsb_flash_attn_fwd_drop(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S,
+                                       int H, int D, const long* strides, float scale, int causal, int dtype,
+                                       const int* sched, int sched_hstride, int sched_pstride, const float* kpm,
+                                       float dropout_p, unsigned dropout_seed, void* stream_) {
+    return flash_fwd_impl(q, k, v, out, lse, B, S, H, D, strides[0], strides[1], strides[2], strides[3], strides[4],
+                          strides[5], strides[6], strides[7], strides[8], strides[9], strides[10], strides[11], scale,
+                          causal, dtype, sched, sched_hstride, sched_pstride, kpm, stream_, dropout_p, dropout_seed);
 }
 
 // Backward of dsb_flash_attn_fwd. dO / q / k / v / out / dk / dv: [B, S, H, 128] with their own element strides (unit
@@ -1169,13 +1197,14 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
                            const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D,
                            const long* strides, float scale, int causal, int dtype, const float* rot_cos,
                            const float* rot_sin, int rot_dim, const int* sched, int sched_hstride, int sched_pstride,
-                           const float* kpm, void* stream_) {
+                           const float* kpm, void* stream_, float dropout_p = 0.f, unsigned dropout_seed = 0) {
     using namespace dsb;
     using namespace dsb::fa;
     ensure_context_on_this_thread();
     if (B <= 0 || S <= 0 || H <= 0) return 0;
     if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
     if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
+    if (dropout_p < 0.f || dropout_p >= 1.f) return DSB_ERR_ARG;
     if (rot_dim > 0 && (rot_cos == nullptr || rot_sin == nullptr)) return DSB_ERR_ARG;
     for (int i = 0; i < 24; ++i)
         if (strides[i] % 8) return DSB_ERR_ALIGN;
@@ -1208,7 +1237,8 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return -(int)r - 1000;
     rc = fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale, scale * 1.4426950408889634f, causal,
-                         bf, rot_cos, rot_sin, rot_dim, sched, sched_hstride, sched_pstride, kpm, stream);
+                         bf, rot_cos, rot_sin, rot_dim, sched, sched_hstride, sched_pstride, kpm,
+                         make_dropout(dropout_p, dropout_seed), stream);
     if (rc) return rc;
     return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, rot_cos, rot_sin, rot_dim, stream);
 }
@@ -1231,4 +1261,14 @@ extern "C" int dsb_flash_attn_bwd2_ex(const void* dO, const void* q, const void*
                                       void* stream_) {
     return flash_bwd2_impl(dO, q, k, v, out, lse, scratch, dq, dk, dv, B, S, H, D, strides, scale, causal, dtype, nullptr,
                            nullptr, 0, sched, sched_hstride, sched_pstride, kpm, stream_);
+}
+
+// Backward of dsb_flash_attn_fwd_drop (same dropout_p / dropout_seed).
+extern "C" int dsb_flash_attn_bwd2_drop(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                                        const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S,
+                                        int H, int D, const long* strides, float scale, int causal, int dtype,
+                                        const int* sched, int sched_hstride, int sched_pstride, const float* kpm,
+                                        float dropout_p, unsigned dropout_seed, void* stream_) {
+    return flash_bwd2_impl(dO, q, k, v, out, lse, scratch, dq, dk, dv, B, S, H, D, strides, scale, causal, dtype, nullptr,
+                           nullptr, 0, sched, sched_hstride, sched_pstride, kpm, stream_, dropout_p, dropout_seed);
 }

@@ -217,6 +217,14 @@ DSB_DEVICE uint32_t desc_lo(const void* p, uint32_t lbo_bytes) {
 }
 constexpr uint32_t NEG_INF_BITS = 0xff800000u;
 
+// ---- dropout bits (see fa2::Dropout): one 32-bit hash serves the two keys of an even / odd pair
+constexpr uint32_t DROP_C1 = 0x9E3779B1u, DROP_C2 = 0x85EBCA77u;
+__device__ __forceinline__ uint32_t lowbias32(uint32_t x) {
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+__device__ __forceinline__ uint32_t drop_seed_bh(uint32_t seed, uint32_t bh) { return lowbias32(seed ^ (bh * 0x27d4eb2fu)); }
+
 // ================================================================================================ forward
 constexpr int F_BQ = 128;                  // rows per query tile
 constexpr int F_BK = 64;                   // keys per step
@@ -239,7 +247,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                   float* __restrict__ lse, int S, int H, float scale_log2, int causal, int dbg, long long* prof,
                   const int* __restrict__ sched, int sched_hstride, int sched_pstride,
-                  const float* __restrict__ kpm) {
+                  const float* __restrict__ kpm, const Dropout drop) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem + F_OFF_Q;
@@ -421,6 +429,9 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const uint64_t sc2 = pk2(sc_eff, sc_eff);
         const float* kpm_b = kpm != nullptr ? kpm + (long)b * S : nullptr;
         float m_run = -INFINITY, l_run = 0.f;
+        // dropout: this row's hash base; the row sum l keeps ALL probabilities, only the P handed to P V is thinned,
+        // and the 1 / keep factor is applied once, with 1 / l, in the epilogue
+        const uint32_t drop_row = drop_seed_bh(drop.seed, blockIdx.x) + static_cast<uint32_t>(qrow) * DROP_C1;
         t0 = clock64();
         for (int j = 0; j < n; ++j) {
             const int buf = j & 1;
@@ -526,10 +537,19 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                     b0 = ex2(b0);
                     b1 = ex2(b1);
                 }
-                pk[i >> 1] = Cvt<T>::pack2(a0, a1);
-                pk[(i >> 1) + 1] = Cvt<T>::pack2(b0, b1);
                 sa = add2(sa, pk2(a0, a1));
                 sb = add2(sb, pk2(b0, b1));
+                if (drop.thr16) {
+                    const uint32_t kp = static_cast<uint32_t>(key_block(j) * F_BK + i) >> 1;      // key pair index
+                    const uint32_t h0 = lowbias32(drop_row + kp * DROP_C2);
+                    const uint32_t h1 = lowbias32(drop_row + (kp + 1) * DROP_C2);
+                    if ((h0 & 0xffffu) < drop.thr16) a0 = 0.f;
+                    if ((h0 >> 16) < drop.thr16) a1 = 0.f;
+                    if ((h1 & 0xffffu) < drop.thr16) b0 = 0.f;
+                    if ((h1 >> 16) < drop.thr16) b1 = 0.f;
+                }
+                pk[i >> 1] = Cvt<T>::pack2(a0, a1);
+                pk[(i >> 1) + 1] = Cvt<T>::pack2(b0, b1);
             }
             FA2_TICK(3)
             tmem_st_x32(t_s, pk);
@@ -550,7 +570,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         if (n > 0) {
         mbar_wait(&o_final[t], 0);
         tc_fence_after();
-        const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
+        const float inv_l = l_run > 0.f ? drop.inv_keep / l_run : 0.f;
         uint8_t* o_row = sQ + t * F_QTILE + row * 128;
         const int sw = row & 7;
 #pragma unroll 1
@@ -676,7 +696,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal, int dbg,
                   long long* prof, const float* __restrict__ rot_cs, const float* __restrict__ rot_sn, int rot,
                   const int* __restrict__ sched, int sched_hstride, int sched_pstride,
-                  const float* __restrict__ kpm) {
+                  const float* __restrict__ kpm, const Dropout drop) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + B_OFF_K;
@@ -878,6 +898,10 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const uint64_t sc2 = pk2(scale_log2, scale_log2);
         const uint64_t s2 = pk2(scale, scale);
         const float kp_row = kpm != nullptr ? kpm[(long)b * S + kvg] : 0.f;   // additive key mask (already in log2 units)
+        // dropout: the forward's bits again. This thread's key selects the half of the pair hash; the query varies
+        const uint32_t drop_key = drop_seed_bh(drop.seed, blockIdx.x) + (static_cast<uint32_t>(kvg) >> 1) * DROP_C2;
+        const int drop_sh = (kvg & 1) * 16;
+        const uint64_t ik2 = pk2(drop.inv_keep, drop.inv_keep);
         for (int it = 0; it < nit; ++it) {
             const int buf = it & 1;
             const int q0 = q_block(it) * 64 + half * 32;      // global query index of this thread's first column
@@ -938,8 +962,27 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                     if (q0 + i + 3 < kvg) p3 = 0.f;
                 }
                 float a0, a1, b0, b1;
+                if (drop.thr16) {
+                    // dropped elements: no contribution to dV (P^T operand) and no gradient through dP; kept ones carry
+                    // the 1 / keep factor on both
+                    float g0, g1, g2, g3;
+                    upk2(mul2(pk2u(rp[i], rp[i + 1]), ik2), g0, g1);
+                    upk2(mul2(pk2u(rp[i + 2], rp[i + 3]), ik2), g2, g3);
+                    const uint32_t qb = static_cast<uint32_t>(q0 + i) * DROP_C1 + drop_key;
+                    const bool k0 = ((lowbias32(qb) >> drop_sh) & 0xffffu) >= drop.thr16;
+                    const bool k1 = ((lowbias32(qb + DROP_C1) >> drop_sh) & 0xffffu) >= drop.thr16;
+                    const bool k2 = ((lowbias32(qb + 2 * DROP_C1) >> drop_sh) & 0xffffu) >= drop.thr16;
+                    const bool k3 = ((lowbias32(qb + 3 * DROP_C1) >> drop_sh) & 0xffffu) >= drop.thr16;
+                    upk2(mul2(fma2(pk2(k0 ? g0 : 0.f, k1 ? g1 : 0.f), s2, pk2(d4.x, d4.y)), pk2(p0, p1)), a0, a1);
+                    upk2(mul2(fma2(pk2(k2 ? g2 : 0.f, k3 ? g3 : 0.f), s2, pk2(d4.z, d4.w)), pk2(p2, p3)), b0, b1);
+                    p0 = k0 ? p0 * drop.inv_keep : 0.f;
+                    p1 = k1 ? p1 * drop.inv_keep : 0.f;
+                    p2 = k2 ? p2 * drop.inv_keep : 0.f;
+                    p3 = k3 ? p3 * drop.inv_keep : 0.f;
+                } else {
                 upk2(mul2(fma2(pk2u(rp[i], rp[i + 1]), s2, pk2(d4.x, d4.y)), pk2(p0, p1)), a0, a1);
                 upk2(mul2(fma2(pk2u(rp[i + 2], rp[i + 3]), s2, pk2(d4.z, d4.w)), pk2(p2, p3)), b0, b1);
+                }
                 pk[i >> 1] = Cvt<T>::pack2(p0, p1);
                 pk[(i >> 1) + 1] = Cvt<T>::pack2(p2, p3);
                 pk[16 + (i >> 1)] = Cvt<T>::pack2(a0, a1);
@@ -1087,7 +1130,7 @@ void set_debug_mode(int m) { g_dbg = m; }
 void set_debug_timers(long long* p) { g_prof = p; }
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
                int B, int S, int H, float scale_log2, int causal, int bf16, const int* sched, int sched_hstride,
-               int sched_pstride, const float* kpm, cudaStream_t stream) {
+               int sched_pstride, const float* kpm, Dropout drop, cudaStream_t stream) {
     if (S % 128) return DSB_ERR_SIZE;
     dim3 grid(B * H, (S + 255) / 256);
     cudaError_t e;
@@ -1096,13 +1139,13 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof, sched, sched_hstride,
-                                            sched_pstride, kpm);
+                                            sched_pstride, kpm, drop);
     } else {
         auto kern = flash_fwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof, sched, sched_hstride,
-                                            sched_pstride, kpm);
+                                            sched_pstride, kpm, drop);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
@@ -1140,7 +1183,7 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* nlse2,
                const float* ndelta, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
                const float* rot_cs, const float* rot_sn, int rot, const int* sched, int sched_hstride, int sched_pstride,
-               const float* kpm, cudaStream_t stream) {
+               const float* kpm, Dropout drop, cudaStream_t stream) {
     if (S % 128) return DSB_ERR_SIZE;
     if (rot < 0 || rot > 128 || (rot % 16)) return DSB_ERR_ARG;
     dim3 grid(B * H, S / 128);
@@ -1150,13 +1193,13 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm, drop);
     } else {
         auto kern = flash_bwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm, drop);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

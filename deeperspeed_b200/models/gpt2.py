@@ -8,6 +8,7 @@ import torch.nn as nn
 import torch.nn.functional as F
 
 from ..ops import kernels as K
+from ..ops.attention import causal_self_attention
 from ..ops.sparse_attention import SparseSelfAttention
 
 
@@ -69,7 +70,11 @@ class GPT2Block(nn.Module):
     def _attention(self, xn):
         B, S, h = xn.shape
         H, D = self.heads, self.head_dim
-        qkv = K.linear(xn, self.c_attn_w, self.c_attn_b).view(B, S, 3, H, D)
+        fused = K.linear(xn, self.c_attn_w, self.c_attn_b)
+        if self.sparse_attn is None and self.cfg.attention_impl == "flash":
+            # our tcgen05 flash kernels for head dim 128 (reads q / k / v in place out of the fused activation)
+            return causal_self_attention(fused, H, D, 0)
+        qkv = fused.view(B, S, 3, H, D)
         q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))       # [B,H,S,D]
         if self.sparse_attn is not None:
             ctx = self.sparse_attn(q, k, v)
@@ -89,14 +94,27 @@ class GPT2Block(nn.Module):
         return K.mlp_residual(yn, self.c_fc_w, self.c_fc_b, self.mlp_proj_w, self.mlp_proj_b, r1)
 
 
+def _init_normal(param, std):
+    """N(0, std) initialisation that also works for a parameter `zero.Init` has already partitioned (nn.Embedding is
+    partitioned the moment its own constructor returns): gather it, let rank 0 draw, broadcast on the way out."""
+    if hasattr(param, "ds_id"):
+        import torch.distributed as dist
+        from ..runtime.zero.partition_parameters import GatheredParameters
+        with GatheredParameters(param, modifier_rank=0):
+            if dist.get_rank() == 0:
+                nn.init.normal_(param, std=std)
+    else:
+        nn.init.normal_(param, std=std)
+
+
 class GPT2Model(nn.Module):
     def __init__(self, cfg):
         super().__init__()
         self.cfg = cfg
         self.wte = nn.Embedding(cfg.vocab_size, cfg.n_embd)
         self.wpe = nn.Embedding(cfg.n_positions, cfg.n_embd)
-        nn.init.normal_(self.wte.weight, std=cfg.init_std)
-        nn.init.normal_(self.wpe.weight, std=cfg.init_std)
+        _init_normal(self.wte.weight, cfg.init_std)
+        _init_normal(self.wpe.weight, cfg.init_std)
         self.h = nn.ModuleList([GPT2Block(cfg) for _ in range(cfg.n_layer)])
         self.ln_f_w, self.ln_f_b = nn.Parameter(torch.ones(cfg.n_embd)), nn.Parameter(torch.zeros(cfg.n_embd))
 

@@ -26,6 +26,9 @@ N.register_sigs({
     "dsb_flash_attn_fwd_ex": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _i, _i, _p, _p],
     "dsb_flash_attn_bwd2_ex": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _i, _i, _p,
                                _p],
+    "dsb_flash_attn_fwd_drop": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _i, _i, _p, _f, C.c_uint, _p],
+    "dsb_flash_attn_bwd2_drop": [_p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p, _f, _i, _i, _p, _i, _i, _p,
+                                 _f, C.c_uint, _p],
 })
 
 
@@ -99,41 +102,66 @@ def _sched_strides(sched):
 
 
 class BlockSparseFlashFn(torch.autograd.Function):
-    """context = softmax(scale * Q K^T restricted to the layout (+ key mask)) V for [B, H, S, D] operands. Without
-    schedules it is plain (non-causal) attention with an optional additive key mask."""
+    """context = dropout(softmax(scale * Q K^T restricted to the layout (+ key mask))) V for [B, H, S, D] operands.
+    Without schedules it is plain (non-causal) attention with an optional additive key mask. `dropout` = (p, seed) or
+    None: the keep mask is a hash inside the kernels (csrc/transformer/flash_v2.cuh), regenerated in backward."""
 
     @staticmethod
-    def forward(ctx, q, k, v, sched_f, sched_b, kpm, scale):
+    def forward(ctx, q, k, v, sched_f, sched_b, kpm, scale, dropout=None):
         B, H, S, D = q.shape
         q4, k4, v4 = _as_bshd128(q), _as_bshd128(k), _as_bshd128(v)
         out = torch.empty(B, S, H, 128, dtype=q.dtype, device=q.device)
         lse = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
         hs, ps = _sched_strides(sched_f)
-        N.check(N.cuda_lib().dsb_flash_attn_fwd_ex(
+        p_drop, seed = dropout if dropout is not None else (0.0, 0)
+        N.check(N.cuda_lib().dsb_flash_attn_fwd_drop(
             N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), B, S, H, 128, _strides(q4, k4, v4, out),
-            float(scale), 0, N.dtype_code(q.dtype), N.ptr(sched_f), hs, ps, N.ptr(kpm), N.stream_ptr()),
-            "dsb_flash_attn_fwd_ex")
+            float(scale), 0, N.dtype_code(q.dtype), N.ptr(sched_f), hs, ps, N.ptr(kpm), float(p_drop),
+            int(seed) & 0xffffffff, N.stream_ptr()), "dsb_flash_attn_fwd_drop")
         K._count()
         ctx.save_for_backward(q4, k4, v4, out, lse, sched_b, kpm)
-        ctx.meta = (D, float(scale))
+        ctx.meta = (D, float(scale), float(p_drop), int(seed) & 0xffffffff)
         return out[..., :D].transpose(1, 2)
 
     @staticmethod
     def backward(ctx, dctx):
         q4, k4, v4, out, lse, sched_b, kpm = ctx.saved_tensors
-        D, scale = ctx.meta
+        D, scale, p_drop, seed = ctx.meta
         B, S, H, _ = q4.shape
         do4 = _as_bshd128(dctx)
         dq, dk, dv = (torch.empty(B, S, H, 128, dtype=q4.dtype, device=q4.device) for _ in range(3))
         scratch = torch.empty((2 + 128) * B * H * S, dtype=torch.float32, device=q4.device)
         hs, ps = _sched_strides(sched_b)
-        N.check(N.cuda_lib().dsb_flash_attn_bwd2_ex(
+        N.check(N.cuda_lib().dsb_flash_attn_bwd2_drop(
             N.ptr(do4), N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), N.ptr(scratch), N.ptr(dq), N.ptr(dk),
             N.ptr(dv), B, S, H, 128, _strides(do4, q4, k4, v4, out, dq, dk, dv), scale, 0, N.dtype_code(q4.dtype),
-            N.ptr(sched_b), hs, ps, N.ptr(kpm), N.stream_ptr()), "dsb_flash_attn_bwd2_ex")
+            N.ptr(sched_b), hs, ps, N.ptr(kpm), p_drop, seed, N.stream_ptr()), "dsb_flash_attn_bwd2_drop")
         K._count(3)
         cut = lambda t: t[..., :D].transpose(1, 2)
-        return cut(dq), cut(dk), cut(dv), None, None, None, None
+        return cut(dq), cut(dk), cut(dv), None, None, None, None, None
+
+
+def dropout_keep_mask(B, H, S, p, seed, device="cpu"):
+    """The [B, H, S, S] keep mask (bool) the kernels derive for dropout probability `p` and `seed` - a restatement of
+    the device hash for tests and debugging; returns (mask, 1 / keep probability as the kernels quantise it)."""
+    thr = min(int(p * 65536.0 + 0.5), 65535)
+    M = 0xffffffff
+
+    def lowbias32(x):
+        x = x ^ (x >> 16)
+        x = (x * 0x7feb352d) & M
+        x = x ^ (x >> 15)
+        x = (x * 0x846ca68b) & M
+        return x ^ (x >> 16)
+
+    bh = torch.arange(B * H, dtype=torch.int64, device=device)
+    seed_bh = lowbias32((int(seed) & M) ^ ((bh * 0x27d4eb2f) & M))                          # [BH]
+    q = (torch.arange(S, dtype=torch.int64, device=device) * 0x9E3779B1) & M                # [S]
+    key = torch.arange(S, dtype=torch.int64, device=device)
+    kp = ((key >> 1) * 0x85EBCA77) & M                                                      # [S]
+    h = lowbias32((seed_bh.view(-1, 1, 1) + q.view(1, -1, 1) + kp.view(1, 1, -1)) & M)      # [BH, S, S]
+    bits = (h >> ((key & 1) * 16).view(1, 1, -1)) & 0xffff
+    return (bits >= thr).view(B, H, S, S), 65536.0 / (65536 - thr)
 
 
 def key_mask_bias(key_padding_mask, mode, batch, seq_len):

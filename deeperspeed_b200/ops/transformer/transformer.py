@@ -188,6 +188,7 @@ class DeepSpeedTransformerLayer(nn.Module):
         initial_weights / initial_biases: optional [q, k, v, attn_out, attn_norm, inter, output, norm] tensors
             (used by module injection and by the unit tests to start from a reference BERT layer)."""
     layer_id = 0
+    use_flash = True      # False: attention as separate GEMM / masked-softmax / dropout kernels (also the fp32 route)
     _warned_stochastic = False
 
     def __init__(self, config, initial_weights=None, initial_biases=None):
@@ -257,10 +258,16 @@ class DeepSpeedTransformerLayer(nn.Module):
     def _flash_ok(self, x):
         cfg = self.config
         D = cfg.hidden_size // cfg.heads
-        no_dropout = not (self.training and cfg.attn_dropout_ratio > 0.0)
-        return no_dropout and _gemm_ok(x) and D <= 128 and D % 8 == 0
+        return self.use_flash and _gemm_ok(x) and D <= 128 and D % 8 == 0
 
-    def _attention(self, xn, mask2d, B, S):
+    def _next_drop_seed(self):
+        """A fresh dropout seed per forward call (config seed, layer id and a call counter mixed into 32 bits); it is an
+        ARGUMENT of `_attention`, so a checkpointed recomputation repeats the same mask."""
+        self._drop_calls = getattr(self, "_drop_calls", 0) + 1
+        return (max(self.config.seed, 0) * 0x9E3779B1 + self.config.layer_id * 0x85EBCA77 + self._drop_calls * 0xC2B2AE3D) \
+            & 0xffffffff
+
+    def _attention(self, xn, mask2d, B, S, drop_seed=0):
         cfg = self.config
         H, D = cfg.heads, cfg.hidden_size // cfg.heads
         if self._flash_ok(xn) and S % 128 == 0:
@@ -268,7 +275,9 @@ class DeepSpeedTransformerLayer(nn.Module):
             qkv = K.linear(xn, self.attn_qkvw, self.attn_qkvb).view(B, S, 3, H, D)      # bias in the GEMM epilogue
             q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))                  # [B, H, S, D] views
             bias = fused.key_mask_bias(mask2d, "add", B, S)
-            ctx = fused.BlockSparseFlashFn.apply(q, k, v, None, None, bias, 1.0 / math.sqrt(D))
+            # attention-probability dropout happens inside the flash kernels (hash of seed / batch / head / query / key)
+            drop = (cfg.attn_dropout_ratio, drop_seed) if (self.training and cfg.attn_dropout_ratio > 0.0) else None
+            ctx = fused.BlockSparseFlashFn.apply(q, k, v, None, None, bias, 1.0 / math.sqrt(D), drop)
             return K.linear(ctx.transpose(1, 2).reshape(B, S, H * D), self.attn_ow, None)
         qkv = K.linear(xn, self.attn_qkvw, None)                                   # [B,S,3h]
         q, k, v = _split_heads(qkv, self.attn_qkvb, B, S, H, D)                    # [B,H,S,D]
@@ -311,13 +320,13 @@ class DeepSpeedTransformerLayer(nn.Module):
             else:
                 norm = lambda t, w, bb: K.layer_norm(t, w, bb, eps)[0]
             xn = norm(x, self.norm_w, self.norm_b)
-            a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, xn, mask2d, B, S)
+            a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, xn, mask2d, B, S, self._next_drop_seed())
             r1 = bias_dropout_residual(a, self.attn_ob, x, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
             y = norm(r1, self.attn_nw, self.attn_nb)
             o = ck(cfg.gelu_checkpoint and self.training, self._ffn, y)
             out = bias_dropout_residual(o, self.output_b, r1, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
         else:
-            a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, x, mask2d, B, S)
+            a = ck(cfg.attn_dropout_checkpoint and self.training, self._attention, x, mask2d, B, S, self._next_drop_seed())
             s1 = bias_dropout_residual(a, self.attn_ob, x, cfg.hidden_dropout_ratio, self.training, max(cfg.seed, 0))
             r1, _ = K.layer_norm(s1, self.attn_nw, self.attn_nb, eps)
             o = ck(cfg.gelu_checkpoint and self.training, self._ffn, r1)

@@ -15,6 +15,8 @@ from ..compression.cupy import packbits, unpackbits
 _p, _i, _l, _u = C.c_void_p, C.c_int, C.c_long, C.c_uint
 N.register_sigs({"dsb_onebit_allreduce": [_p, _p, _p, _l, _i, _i, _p, _l, _p, _p, _u, _p]})
 N.register_sigs({"dsb_onebit_heap_bytes": [_l, _i]}, restype=_l)
+_f = C.c_float
+N.register_sigs({"dsb_onebit_adam_step": [_p, _p, _p, _p, _p, _p, _l, _l, _i, _i, _p, _l, _p, _p, _u, _f, _f, _f, _f, _p]})
 
 
 class NcclBackend:
@@ -81,6 +83,34 @@ class NcclBackend:
         from ...ops import kernels as K
         K._count()
         return buffer_m
+
+    def fused_adam_supported(self, momentum, worker_error):
+        """Can `compressed_adam_step` run for this momentum tensor (fp32 on a GPU, length a multiple of 4, error buffers
+        padded to whole sign words per server chunk)?"""
+        n = worker_error.numel()
+        return (self.use_fused and momentum.is_cuda and momentum.dtype == torch.float32 and 1 < self.size <= 16
+                and momentum.is_contiguous() and momentum.numel() % 4 == 0 and momentum.numel() <= n
+                and n % (32 * self.size) == 0)
+
+    def compressed_adam_step(self, momentum, grad, param, variance, worker_error, server_error, beta1, lr, eps,
+                             weight_decay):
+        """1-bit Adam's compression-stage step as ONE kernel (csrc/comm/onebit.cu): momentum <- beta1 * momentum +
+        (1 - beta1) * grad, error-compensated 1-bit average over the group, param <- param - lr * (momentum /
+        (sqrt(variance) + eps) + weight_decay * param). All tensors fp32 and flat."""
+        from ...parallel.symm import FLAG_BYTES
+        n = worker_error.numel()
+        heap = self._heap_for(n)
+        lib = N.cuda_lib()
+        if self._scratch is None:
+            self._scratch = torch.zeros(4096, dtype=torch.float32, device=momentum.device)
+        bases = (C.c_void_p * self.size)(*heap.peer_base)
+        rc = lib.dsb_onebit_adam_step(N.ptr(momentum), N.ptr(grad), N.ptr(param), N.ptr(variance), N.ptr(worker_error),
+                                      N.ptr(server_error), n, momentum.numel(), self.size, self.rank, bases, FLAG_BYTES,
+                                      bases, N.ptr(self._scratch), heap.next_epoch(), float(beta1), float(lr),
+                                      float(eps), float(weight_decay), N.stream_ptr())
+        N.check(rc, "dsb_onebit_adam_step")
+        from ...ops import kernels as K
+        K._count()
 
     # ------------------------------------------------------------------ torch.distributed restatement
     def _compressed_allreduce_torch(self, buffer_m, worker_error, server_error):

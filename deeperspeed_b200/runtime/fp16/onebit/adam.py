@@ -119,6 +119,19 @@ class OnebitAdam(torch.optim.Optimizer):
                 mask = group["exp_avg_mask"] = mask.to(device=m.device)
             m.mul_(mask)
 
+    def _fused_step(self, p, grad, state, group, beta1):
+        """Compression-stage step of one tensor inside the 1-bit all-reduce kernel, when the backend offers it and the
+        tensors qualify (flat fp32 on a GPU, no momentum mask). Returns False to fall back to the separate passes."""
+        backend = self.comm_backend_handle
+        fused = getattr(backend, "fused_adam_supported", None)
+        if (fused is None or self.size == 1 or group.get("exp_avg_mask") is not None or self.eps_mode != 1
+                or p.data.dtype != torch.float32 or grad.dtype != torch.float32 or not p.data.is_contiguous()
+                or not grad.is_contiguous() or not fused(state["exp_avg"], state["worker_error"])):
+            return False
+        backend.compressed_adam_step(state["exp_avg"], grad, p.data, state["exp_avg_sq"], state["worker_error"],
+                                     state["server_error"], beta1, group["lr"], group["eps"], group["weight_decay"])
+        return True
+
     def step(self, closure=None, grads=None):
         loss = closure() if closure is not None else None
         for group, given in zip(self.param_groups, self._grads_per_group(grads, len(self.param_groups))):
@@ -140,6 +153,8 @@ class OnebitAdam(torch.optim.Optimizer):
                     dist.all_reduce(grad)
                     grad.mul_(1 / dist.get_world_size())
                     self._exact_moments(state, grad, beta1, beta2)
+                elif self._fused_step(p, grad, state, group, beta1):
+                    continue      # momentum, exchange and parameter update ran as one kernel
                 else:
                     self._compressed_momentum(state, grad, beta1, group)
                 update = state["exp_avg"] / (state["exp_avg_sq"].sqrt() + group["eps"])

@@ -147,6 +147,18 @@ int dsb_flash_attn_bwd2_ex(const void* dO, const void* q, const void* k, const v
                            const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D,
                            const long* strides, float scale, int causal, int dtype, const int* sched, int sched_hstride,
                            int sched_pstride, const float* kpm, void* stream);
+/* The same with attention dropout inside the kernels: probabilities are dropped with probability dropout_p (quantised
+ * to 1 / 65536) and the kept ones scaled by 1 / (1 - p); the keep bits are a hash of (dropout_seed, batch, head, query,
+ * key), so the backward call reproduces the forward's mask from the same seed - no mask tensor exists. */
+int dsb_flash_attn_fwd_drop(const void* q, const void* k, const void* v, void* out, float* lse, int B, int S, int H,
+                            int D, const long* strides, float scale, int causal, int dtype, const int* sched,
+                            int sched_hstride, int sched_pstride, const float* kpm, float dropout_p,
+                            unsigned dropout_seed, void* stream);
+int dsb_flash_attn_bwd2_drop(const void* dO, const void* q, const void* k, const void* v, const void* out,
+                             const float* lse, float* scratch, void* dq, void* dk, void* dv, int B, int S, int H, int D,
+                             const long* strides, float scale, int causal, int dtype, const int* sched,
+                             int sched_hstride, int sched_pstride, const float* kpm, float dropout_p,
+                             unsigned dropout_seed, void* stream);
 /* Experiment switches of the second-generation kernels (0 = production); see csrc/transformer/flash_attn_v2.cu. */
 void dsb_flash_attn_debug_mode(int mode);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */
@@ -311,6 +323,13 @@ int dsb_fused_lamb_ag(float* upd32, float* p32, float* m, float* v, void* const*
 long dsb_onebit_heap_bytes(long n, int W);
 int dsb_onebit_allreduce(float* m, float* e_w, float* e_s, long n, int W, int me, void* const* heap_bases,
                          long region_off, void* const* flag_bases, void* scratch, unsigned int epoch, void* stream);
+/* The compression-stage step of 1-bit Adam in the same kernel: m <- beta1 m + (1 - beta1) g on the way in, the
+ * averaged momentum is decompressed straight into p <- p - lr (m / (sqrt(v) + eps) + wd p) on the way out.
+ * m, g, p, v: n_real fp32 elements (multiple of 4); e_w: n, e_s: n / W elements (n = n_real padded to 32 W). */
+int dsb_onebit_adam_step(float* m, const float* g, float* p, const float* v, float* e_w, float* e_s, long n,
+                         long n_real, int W, int me, void* const* heap_bases, long region_off,
+                         void* const* flag_bases, void* scratch, unsigned int epoch, float beta1, float lr, float eps,
+                         float weight_decay, void* stream);
 
 /* ---- block-sparse attention (csrc/sparse_attn) -------------------------------------------------------------- */
 /* Host LUT builders: layout [H, nb, nb] (0/1) -> block list (h, i, j), row CSR, column CSC; super-block packing. */

@@ -264,3 +264,37 @@ def test_fused_block_sparse_attention_falls_back_for_rpe():
     finally:
         SparseSelfAttention.use_fused = True
     assert torch.equal(a, b)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D,dtype,p", [(128, torch.float16, 0.1), (64, torch.bfloat16, 0.25)])
+def test_flash_attention_dropout_matches_masked_reference(D, dtype, p):
+    """Attention dropout inside the flash kernels: the keep mask is a hash of (seed, batch, head, query, key) that
+    forward and backward both derive; `dropout_keep_mask` restates it, so the result can be checked EXACTLY against
+    softmax -> mask / keep -> matmul in fp32, gradients included (a wrong or inconsistent mask fails loudly)."""
+    from deeperspeed_b200.ops.sparse_attention import fused
+    torch.manual_seed(0)
+    B, H, S = 2, 3, 384
+    seed = 0xC0FFEE
+    q, k, v = (torch.randn(B, H, S, D, device="cuda", dtype=dtype).requires_grad_() for _ in range(3))
+    scale = D ** -0.5
+    out = fused.BlockSparseFlashFn.apply(q, k, v, None, None, None, scale, (p, seed))
+    dout = torch.randn_like(out)
+    dq, dk, dv = torch.autograd.grad(out, (q, k, v), dout)
+    keep, inv_keep = fused.dropout_keep_mask(B, H, S, p, seed, device="cuda")
+    assert abs(keep.float().mean().item() - (1 - p)) < 0.01
+    assert abs(inv_keep - 1 / (1 - p)) < 1e-3
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    probs = torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) * keep * inv_keep
+    ref = probs @ vf
+    rq, rk, rv = torch.autograd.grad(ref, (qf, kf, vf), dout.float())
+    tol = 2e-2 if dtype == torch.float16 else 6e-2
+    for got, want, name in ((out, ref, "out"), (dq, rq, "dq"), (dk, rk, "dk"), (dv, rv, "dv")):
+        err = (got.float() - want).abs().max().item() / (want.abs().max().item() + 1e-6)
+        assert err < tol, (name, err)
+    # a different seed gives a different mask; p = 0 is the plain kernel
+    other = fused.BlockSparseFlashFn.apply(q, k, v, None, None, None, scale, (p, seed + 1))
+    assert (other - out).abs().max().item() > 1e-3
+    plain = fused.BlockSparseFlashFn.apply(q, k, v, None, None, None, scale, None)
+    ref0 = torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf
+    assert (plain.float() - ref0).abs().max().item() / ref0.abs().max().item() < tol

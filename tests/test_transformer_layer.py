@@ -20,9 +20,11 @@ def _case(batch, hidden, seq, heads, preln, device, dtype, atol, invertible=Fals
     ds_layer = model[0]
     assert type(ds_layer).__name__ == "DeepSpeedTransformerLayer"
     ds_layer.config.normalize_invertible = invertible
-    # a non-zero ratio routes attention through the GEMM + softmax + dropout chain; the Philox kernel is then told to
+    # `use_flash = False` routes attention through the GEMM + softmax + dropout chain; the Philox kernel is then told to
     # keep everything so that the result stays comparable with the dropout-free reference
     ds_layer.config.attn_dropout_ratio = attn_dropout
+    if attn_dropout > 0.0:
+        ds_layer.use_flash = False
     x = (torch.randn(batch, seq, hidden, device=device) * 0.5)
     mask = torch.zeros(batch, 1, 1, seq, device=device)
     mask[:, :, :, -3:] = -10000.0
