@@ -327,13 +327,16 @@ static int step_grid(const void* kern) {
 
 using namespace dsb;
 
-extern "C" int dsb_fused_zero_step(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs,
-                                   const void* mc_grads, void* mc_params, int R, int me, int phases, int zero_grads,
-                                   long slice_off, long bucket_off, long bucket_n, long n, int dtype, void* red,
-                                   float* p32, float* m, float* v, float lr, float beta1, float beta2, float eps,
-                                   float weight_decay, int adamw_mode, int bias_correction, int step, float loss_scale,
-                                   float clip, float* sumsq2, float* inv_scale, int* skip, float* host_out2,
-                                   void* scratch, unsigned int epoch, void* stream) {
+// `max_ctas` caps the grid (0 = fill the GPU): a reduce phase launched on a side stream while backward is still
+// running should leave most SMs to the GEMMs - it is NVLink-bound and may sit in its entry barrier for a while.
+extern "C" int dsb_fused_zero_step_grid(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs,
+                                        const void* mc_grads, void* mc_params, int R, int me, int phases,
+                                        int zero_grads, long slice_off, long bucket_off, long bucket_n, long n,
+                                        int dtype, void* red, float* p32, float* m, float* v, float lr, float beta1,
+                                        float beta2, float eps, float weight_decay, int adamw_mode,
+                                        int bias_correction, int step, float loss_scale, float clip, float* sumsq2,
+                                        float* inv_scale, int* skip, float* host_out2, void* scratch,
+                                        unsigned int epoch, int max_ctas, void* stream) {
     if (R < 1 || R > MAX_RANKS || me < 0 || me >= R || (n % 8) || (slice_off % 8) || (bucket_off % 8) ||
         (bucket_n % 8) || !scratch || !(phases & 7))
         return DSB_ERR_ARG;
@@ -366,7 +369,22 @@ extern "C" int dsb_fused_zero_step(void* const* grad_ptrs, void* const* param_pt
     else
         kern = mc ? (const void*)fused_zero_step_kernel<__half, true> : (const void*)fused_zero_step_kernel<__half, false>;
     void* args[] = {&a};
-    cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(step_grid(kern)), dim3(512), args, 0,
+    int grid = step_grid(kern);
+    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+    cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(512), args, 0,
                                                 reinterpret_cast<cudaStream_t>(stream));
     return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int dsb_fused_zero_step(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs,
+                                   const void* mc_grads, void* mc_params, int R, int me, int phases, int zero_grads,
+                                   long slice_off, long bucket_off, long bucket_n, long n, int dtype, void* red,
+                                   float* p32, float* m, float* v, float lr, float beta1, float beta2, float eps,
+                                   float weight_decay, int adamw_mode, int bias_correction, int step, float loss_scale,
+                                   float clip, float* sumsq2, float* inv_scale, int* skip, float* host_out2,
+                                   void* scratch, unsigned int epoch, void* stream) {
+    return dsb_fused_zero_step_grid(grad_ptrs, param_ptrs, flag_ptrs, mc_grads, mc_params, R, me, phases, zero_grads,
+                                    slice_off, bucket_off, bucket_n, n, dtype, red, p32, m, v, lr, beta1, beta2, eps,
+                                    weight_decay, adamw_mode, bias_correction, step, loss_scale, clip, sumsq2, inv_scale,
+                                    skip, host_out2, scratch, epoch, 0, stream);
 }

@@ -31,7 +31,10 @@ N.register_sigs({"dsb_fused_zero_scratch_bytes": []}, restype=_l)
 N.register_sigs({
     "dsb_fused_zero_step": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _i, _p, _p, _p, _p, _f, _f, _f, _f, _f,
                             _i, _i, _i, _f, _f, _p, _p, _p, _p, _p, _u, _p],
+    "dsb_fused_zero_step_grid": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _l, _l, _l, _l, _i, _p, _p, _p, _p, _f, _f, _f, _f,
+                                 _f, _i, _i, _i, _f, _f, _p, _p, _p, _p, _p, _u, _i, _p],
 })
+EARLY_REDUCE_CTAS = 32     # grid of a reduce phase overlapped with backward (NVLink-bound; leaves the SMs to the GEMMs)
 PH_REDUCE, PH_UPDATE, PH_EXCHANGE = 1, 2, 4
 
 
@@ -100,7 +103,8 @@ class FusedZeroStep:
         self.use_multicast = bool(heap.mc_base) and os.environ.get("DSB_FUSED_ZERO_MULTICAST", "0") == "1"
         self.host_out = torch.zeros(2, dtype=torch.float32, device=opt._dev)
         self._reds = {}
-        self.launches = {"reduce": 0, "update": 0, "whole_step": 0}      # per-kernel launch counts (bench / tests)
+        self.launches = {"reduce": 0, "reduce_early": 0, "update": 0, "whole_step": 0}      # launch counts
+        self._early = set()          # buckets whose reduce phase already ran under this step's backward
         self.is_lamb = bool(getattr(opt.optimizer, "supports_fused_zero_lamb", False))
         if self.is_lamb:
             self._init_lamb()
@@ -198,7 +202,19 @@ class FusedZeroStep:
         self._prof = []
 
     # ---- Adam: the one-kernel step ----------------------------------------------------------------------------
-    def _launch(self, gi, k, phases, s, epoch=None):
+    def reduce_early(self, gi, k):
+        """Reduce phase of one bucket on the CURRENT stream with a small grid, as soon as its gradients are final
+        (called from ZeRO-2's per-bucket hooks on the reduction stream while backward is still running). Every rank
+        calls it for the same buckets in the same order; the step then skips the reduce of these buckets."""
+        if self.is_lamb or (gi, k) in self._early:
+            return False
+        self._launch(gi, k, PH_REDUCE, N.stream_ptr(), max_ctas=EARLY_REDUCE_CTAS)
+        self._early.add((gi, k))
+        self.launches["reduce_early"] += 1
+        self.launches["reduce"] -= 1
+        return True
+
+    def _launch(self, gi, k, phases, s, epoch=None, max_ctas=0):
         o = self.opt
         arena = o.arenas[gi]
         group = o.optimizer.param_groups[gi]
@@ -207,15 +223,15 @@ class FusedZeroStep:
         R, me, sub = o.dp_world, o.dp_rank, o.sub_size[gi]
         beta1, beta2 = group["betas"]
         mc = self.use_multicast
-        N.check(self.lib.dsb_fused_zero_step(
+        N.check(self.lib.dsb_fused_zero_step_grid(
             self.grad_ptrs[gi], self.param_ptrs[gi], self.flag_ptrs, self.mc_grads[gi] if mc else None,
             self.mc_params[gi] if mc else None, R, me, phases, 1, (k * R + me) * sub, k * R * sub, R * sub, sub,
             N.dtype_code(arena.dtype), N.ptr(self._red(gi, k)), N.ptr(o._master_slice(master.data, gi, k)),
             N.ptr(o._master_slice(st["exp_avg"], gi, k)), N.ptr(o._master_slice(st["exp_avg_sq"], gi, k)),
             float(group["lr"]), float(beta1), float(beta2), float(group["eps"]), float(group["weight_decay"]),
-            int(o.optimizer.adam_w_mode), int(group["bias_correction"]), int(group["step"]), float(o._loss_scale()),
+            int(o.optimizer.adam_w_mode), int(group["bias_correction"]), int(group.get("step", 1)), float(o._loss_scale()),
             float(o.clip_grad), N.ptr(o._sumsq), N.ptr(o._inv_scale), N.ptr(o._skip), N.ptr(self.host_out),
-            N.ptr(self.scratch), self.heap.next_epoch(), s), "dsb_fused_zero_step")
+            N.ptr(self.scratch), self.heap.next_epoch(), int(max_ctas), s), "dsb_fused_zero_step_grid")
         K._count()
         self.launches["whole_step" if phases == 7 else "reduce" if phases & PH_REDUCE else "update"] += 1
 
@@ -244,27 +260,33 @@ class FusedZeroStep:
         buckets = [(gi, k) for gi in range(len(o.arenas)) for k in range(o.num_buckets[gi])]
         for group in o.optimizer.param_groups:
             group["step"] = group.get("step", 0) + 1
-        o._sumsq.zero_()
+        # o._sumsq was cleared at the end of the previous step: reduce phases that ran under backward have added to it
+        todo = [b for b in buckets if b not in self._early]
         mp = o.mpu is not None and o.mpu.get_model_parallel_world_size() > 1
         if not mp:
             # the norm lives inside the data-parallel group: the last bucket's launch trades it through the heap
-            for gi, k in buckets[:-1]:
-                self._launch(gi, k, PH_REDUCE, s)
-            self._launch(*buckets[-1], PH_REDUCE | PH_EXCHANGE | PH_UPDATE, s)
+            last = buckets[-1]
+            for gi, k in todo:
+                if (gi, k) != last:
+                    self._launch(gi, k, PH_REDUCE, s)
+            self._launch(*last, (PH_REDUCE if last in todo else 0) | PH_EXCHANGE | PH_UPDATE, s)
             self._mark("reduce+exchange+update")
             for gi, k in buckets[:-1]:
                 self._launch(gi, k, PH_UPDATE, s)
-            return self.host_out
-        for gi, k in buckets:
-            self._launch(gi, k, PH_REDUCE, s)
-        self._mark("reduce")
-        o._mp_owned_correction(reduced=self._reds or None)      # the arena itself still holds raw local gradients
-        norm, bad = o._global_scalars()                    # all-reduce over dp and the model-parallel group
-        self._mark("scalars")
-        for gi, k in buckets:
-            self._launch(gi, k, PH_UPDATE, s)
-        self._mark("update")
-        return torch.stack([norm, bad.float()])
+            scalars = self.host_out
+        else:
+            for gi, k in todo:
+                self._launch(gi, k, PH_REDUCE, s)
+            self._mark("reduce")
+            o._mp_owned_correction(reduced=self._reds or None)      # the arena itself still holds raw local gradients
+            norm, bad = o._global_scalars()                    # all-reduce over dp and the model-parallel group
+            self._mark("scalars")
+            for gi, k in buckets:
+                self._launch(gi, k, PH_UPDATE, s)
+            self._mark("update")
+            scalars = torch.stack([norm, bad.float()])
+        self._early = set()
+        return scalars
 
     def step(self):
         o = self.opt
@@ -277,6 +299,8 @@ class FusedZeroStep:
         else:
             scalars = self._adam_step(s)
         host = scalars.tolist()                                # the only device -> host read of the step
+        if not self.is_lamb:
+            o._sumsq.zero_()                                   # ready for reduce phases launched under the next backward
         self._report()
         overflow = bool(host[1])
         o.overflow = overflow

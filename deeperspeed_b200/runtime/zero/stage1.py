@@ -108,6 +108,10 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
 
     def reduce_bucket(self, gi, k):
         if self._use_fused():
+            # Called per bucket while backward is still running (ZeRO-2 overlap_comm hooks, on the reduction stream):
+            # run the fused kernel's reduce phase for this bucket now, with a small grid; the step skips it later.
+            if self.overlap_comm:
+                self.fused.reduce_early(gi, k)
             return
         super().reduce_bucket(gi, k)
 

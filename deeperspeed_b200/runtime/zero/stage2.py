@@ -306,10 +306,11 @@ class FP16_DeepSpeedZeroOptimizer(ZeroShardedOptimizer):
             return
         for a in self.arenas:
             a.absorb_stray_grads()
-        for gi in range(len(self.arenas)):
-            for k in range(self.num_buckets[gi]):
-                if (gi, k) not in self._bucket_done:
-                    self.reduce_bucket(gi, k)
+        if not self._use_fused():      # the fused step reduces what is left itself, with the whole GPU
+            for gi in range(len(self.arenas)):
+                for k in range(self.num_buckets[gi]):
+                    if (gi, k) not in self._bucket_done:
+                        self.reduce_bucket(gi, k)
         if self._side_stream is not None:
             torch.cuda.current_stream().wait_stream(self._side_stream)
         self._reduced = True

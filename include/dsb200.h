@@ -305,6 +305,14 @@ int dsb_fused_zero_step(void* const* grad_ptrs, void* const* param_ptrs, void* c
                         float beta1, float beta2, float eps, float weight_decay, int adamw_mode, int bias_correction,
                         int step, float loss_scale, float clip, float* sumsq2, float* inv_scale, int* skip,
                         float* host_out2, void* scratch, unsigned int epoch, void* stream);
+/* ... with at most max_ctas CTAs (0 = fill the GPU): for a reduce phase overlapped with backward on a side stream. */
+int dsb_fused_zero_step_grid(void* const* grad_ptrs, void* const* param_ptrs, void* const* flag_ptrs,
+                             const void* mc_grads, void* mc_params, int R, int me, int phases, int zero_grads,
+                             long slice_off, long bucket_off, long bucket_n, long n, int dtype, void* red, float* p32,
+                             float* m, float* v, float lr, float beta1, float beta2, float eps, float weight_decay,
+                             int adamw_mode, int bias_correction, int step, float loss_scale, float clip,
+                             float* sumsq2, float* inv_scale, int* skip, float* host_out2, void* scratch,
+                             unsigned int epoch, int max_ctas, void* stream);
 /* LAMB counterpart of dsb_fused_adam_ag, one launch per parameter group over all `n / sub` bucket slices this rank
  * owns. `upd32` holds the reduced fp32 gradients on entry (it is overwritten with the update). The owned range is
  * described by `nseg` segments: seg_start[i] .. seg_start[i+1] (local element offsets, multiples of 8,

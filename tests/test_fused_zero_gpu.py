@@ -340,3 +340,38 @@ def _zero2_sharded_worker():
 
 def test_zero2_sharded_gradient_memory_2gpu():
     run_distributed(_zero2_sharded_worker, world_size=2, use_cuda=True)
+
+
+def _zero2_fused_overlap_worker():
+    """ZeRO-2 with overlap_comm on the fused path: the reduce phase of every bucket is launched from the bucket hooks
+    on the reduction stream while backward is still running (small grid), the step then runs exchange + update only.
+    Must match the NCCL path."""
+    results = []
+    for fused in (False, True):
+        torch.manual_seed(5)
+        model = Net()
+        cfg = {"train_batch_size": 8, "train_micro_batch_size_per_gpu": 4, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-3, "weight_decay": 0.01}},
+               "fp16": {"enabled": True, "initial_scale_power": 8}, "gradient_clipping": 1.0,
+               "zero_optimization": {"stage": 2, "fused_nvlink": fused, "overlap_comm": True,
+                                     "reduce_bucket_size": 200000}}
+        engine, opt, _, _ = deepspeed.initialize(model=model, model_parameters=model.parameters(), config_params=cfg)
+        assert (opt.fused is not None) == fused and sum(opt.num_buckets) > 1
+        g = torch.Generator().manual_seed(100 + dist.get_rank())
+        for _ in range(5):
+            x = torch.randn(4, 256, generator=g).half().cuda()
+            y = torch.randint(0, 256, (4,), generator=g).cuda()
+            engine.backward(engine(x, y))
+            engine.step()
+        torch.cuda.synchronize()
+        results.append(torch.cat([p.detach().float().view(-1) for p in model.parameters()]))
+        if fused:
+            n = opt.fused.launches
+            assert n["reduce_early"] >= 5 * (sum(opt.num_buckets) - 1), n      # buckets were reduced under backward
+            assert n["reduce"] <= 5, n
+    d = (results[1] - results[0]).abs()
+    assert d.max().item() <= 2 * 1e-3 * 5 + 1e-3 and (d > 2e-3).float().mean().item() < 0.02, d.max().item()
+
+
+def test_zero2_fused_reduce_overlaps_backward_2gpu():
+    run_distributed(_zero2_fused_overlap_worker, world_size=2, use_cuda=True)
