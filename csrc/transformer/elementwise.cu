@@ -479,6 +479,74 @@ extern "C" int dsb_cross_entropy_bwd(void* logits, const long* targets, const fl
     DSB_RET();
 }
 
+// ------------------------------------------------------------------------------------------- embedding
+// out[t, :] = table[ids[t], :] and its gradient dtable[ids[t], :] += dout[t, :]. The backward adds with packed 16-bit
+// atomics straight into the caller's gradient buffer (the flat gradient arena), so there is no dense [vocab, dim]
+// temporary, no sort and no separate accumulate pass (torch's embedding_dense_backward: sort + segmented sum into a
+// fresh tensor, then AccumulateGrad adds it: 1.3 ms per 8192 x 2048 micro-batch against 50432 rows). Tokens that
+// repeat add in arbitrary order (16-bit rounding may differ in the last bit between runs).
+namespace dsb {
+template <typename T>
+__global__ void __launch_bounds__(256) embedding_fwd_kernel(const T* __restrict__ table, const long* __restrict__ ids,
+                                                            T* __restrict__ out, long ntok, int dim, long vocab) {
+    const int vec = dim >> 3;
+    for (long t = blockIdx.x; t < ntok; t += gridDim.x) {
+        const long row = ids[t];
+        if (row < 0 || row >= vocab) continue;      // out-of-range ids read as zeros would hide bugs: leave untouched
+        const uint4* src = reinterpret_cast<const uint4*>(table + row * dim);
+        uint4* dst = reinterpret_cast<uint4*>(out + t * dim);
+        for (int i = threadIdx.x; i < vec; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+}
+
+template <typename T2>
+__global__ void __launch_bounds__(256) embedding_bwd_kernel(const T2* __restrict__ dout, const long* __restrict__ ids,
+                                                            T2* __restrict__ dtable, long ntok, int dim2, long vocab) {
+    for (long t = blockIdx.x; t < ntok; t += gridDim.x) {
+        const long row = ids[t];
+        if (row < 0 || row >= vocab) continue;
+        const T2* src = dout + t * dim2;
+        T2* dst = dtable + row * dim2;
+        for (int i = threadIdx.x; i < dim2; i += blockDim.x) atomicAdd(dst + i, src[i]);
+    }
+}
+}  // namespace dsb
+
+extern "C" int dsb_embedding_fwd(const void* table, const long* ids, void* out, long ntok, int dim, long vocab,
+                                 int dtype, void* stream) {
+    if (dim % 8) return DSB_ERR_SIZE;
+    if (ntok <= 0) return 0;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const unsigned grid = (unsigned)(ntok < (long)ew_sms() * 16 ? ntok : (long)ew_sms() * 16);
+    if (dtype == DSB_DTYPE_F16)
+        dsb::embedding_fwd_kernel<__half><<<grid, 256, 0, s>>>((const __half*)table, ids, (__half*)out, ntok, dim, vocab);
+    else if (dtype == DSB_DTYPE_BF16)
+        dsb::embedding_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>((const __nv_bfloat16*)table, ids,
+                                                                     (__nv_bfloat16*)out, ntok, dim, vocab);
+    else
+        return DSB_ERR_DTYPE;
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
+extern "C" int dsb_embedding_bwd_acc(const void* dout, const long* ids, void* dtable, long ntok, int dim, long vocab,
+                                     int dtype, void* stream) {
+    if (dim % 2) return DSB_ERR_SIZE;
+    if (ntok <= 0) return 0;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    const unsigned grid = (unsigned)(ntok < (long)ew_sms() * 16 ? ntok : (long)ew_sms() * 16);
+    if (dtype == DSB_DTYPE_F16)
+        dsb::embedding_bwd_kernel<__half2><<<grid, 256, 0, s>>>((const __half2*)dout, ids, (__half2*)dtable, ntok,
+                                                                dim / 2, vocab);
+    else if (dtype == DSB_DTYPE_BF16)
+        dsb::embedding_bwd_kernel<__nv_bfloat162><<<grid, 256, 0, s>>>((const __nv_bfloat162*)dout, ids,
+                                                                       (__nv_bfloat162*)dtable, ntok, dim / 2, vocab);
+    else
+        return DSB_ERR_DTYPE;
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : -(int)e;
+}
+
 // ------------------------------------------------------------------------------------------- allocation-free column sum
 // Same reduction as dsb_column_sum, for callers that cannot hand over (or obtain) scratch memory: a plug-in or host
 // callback that is not allowed to touch the CUDA allocation API, or a process whose HBM has been given wholesale to

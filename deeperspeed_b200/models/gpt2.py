@@ -121,7 +121,7 @@ class GPT2Model(nn.Module):
     def forward(self, tokens, labels=None):
         B, S = tokens.shape
         pos = torch.arange(S, device=tokens.device)
-        x = self.wte(tokens) + self.wpe(pos)[None]
+        x = K.embedding(tokens, self.wte.weight) + self.wpe(pos)[None]
         for blk in self.h:
             if self.cfg.checkpoint_blocks and torch.is_grad_enabled():
                 from torch.utils.checkpoint import checkpoint

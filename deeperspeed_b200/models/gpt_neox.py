@@ -51,7 +51,7 @@ class EmbeddingPipe(nn.Module):
         nn.init.normal_(self.word_embeddings.weight, std=cfg.init_std)
 
     def forward(self, tokens):
-        return self.word_embeddings(tokens)
+        return K.embedding(tokens, self.word_embeddings.weight)
 
 
 class ParallelTransformerLayerPipe(nn.Module):

@@ -548,6 +548,50 @@ def transpose_0213(x):
 
 
 # ------------------------------------------------------------------------------------------------ cross entropy
+class EmbeddingFn(torch.autograd.Function):
+    """Row gather whose backward adds the output gradient straight into the table's existing `.grad` (a view of the
+    flat gradient arena) with packed 16-bit atomics: no dense [vocab, dim] temporary, no sort, no AccumulateGrad pass
+    (csrc/transformer/elementwise.cu). Falls back to torch where that does not apply."""
+
+    @staticmethod
+    def forward(ctx, ids, table):
+        ids_c = ids.contiguous()
+        out = torch.empty(*ids.shape, table.shape[1], dtype=table.dtype, device=table.device)
+        N.check(N.cuda_lib().dsb_embedding_fwd(N.ptr(table), N.ptr(ids_c), N.ptr(out), ids_c.numel(), table.shape[1],
+                                               table.shape[0], N.dtype_code(table.dtype), N.stream_ptr()),
+                "dsb_embedding_fwd")
+        _count()
+        ctx.save_for_backward(ids_c)
+        ctx.table = table
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (ids,) = ctx.saved_tensors
+        table = ctx.table
+        g = table.grad
+        into_arena = (ACCUMULATE_INTO_GRAD and g is not None and g.dtype == dout.dtype and g.is_contiguous()
+                      and g.shape == table.shape)
+        if not into_arena:
+            g = torch.zeros_like(table)
+        d2 = dout.reshape(-1, table.shape[1])
+        if not d2.is_contiguous():
+            d2 = d2.contiguous()
+        N.check(N.cuda_lib().dsb_embedding_bwd_acc(N.ptr(d2), N.ptr(ids), N.ptr(g), ids.numel(), table.shape[1],
+                                                   table.shape[0], N.dtype_code(table.dtype), N.stream_ptr()),
+                "dsb_embedding_bwd_acc")
+        _count()
+        return None, (None if into_arena else g)
+
+
+def embedding(ids, table):
+    """table[ids]; on CUDA in fp16 / bf16 with a 16-byte-aligned row size our gather / scatter-add kernels."""
+    if (table.is_cuda and table.dtype in (torch.float16, torch.bfloat16) and table.dim() == 2 and table.shape[1] % 8 == 0
+            and table.is_contiguous() and ids.dtype == torch.int64):
+        return EmbeddingFn.apply(ids, table)
+    return torch.nn.functional.embedding(ids, table)
+
+
 class CrossEntropyFn(torch.autograd.Function):
     """Mean token cross entropy over a [tokens, vocab] half/bf16 logits matrix. Backward overwrites the logits
     buffer with the gradient (no second [tokens, vocab] allocation, no fp32 copy of the logits)."""

@@ -47,6 +47,8 @@ _CUDA_SIGS = {
     "dsb_qkv_bias_split_transpose": [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p],
     "dsb_transpose_0213": [_p, _p, _i, _i, _i, _i, _i, _p],
     "dsb_column_sum": [_p, _p, _l, _i, _i, _i, _p, _p],
+    "dsb_embedding_fwd": [_p, _p, _p, _l, _i, _l, _i, _p],
+    "dsb_embedding_bwd_acc": [_p, _p, _p, _l, _i, _l, _i, _p],
     "dsb_fused_add": [_p, _p, _p, _p, _p, _l, _i, _p],
     "dsb_cross_entropy_fwd": [_p, _p, _p, _p, _l, _i, _l, _l, _i, _p],
     "dsb_cross_entropy_bwd": [_p, _p, _p, _p, _f, _l, _i, _l, _l, _i, _p],

@@ -161,6 +161,13 @@ int dsb_flash_attn_bwd2_drop(const void* dO, const void* q, const void* k, const
                              unsigned dropout_seed, void* stream);
 /* Experiment switches of the second-generation kernels (0 = production); see csrc/transformer/flash_attn_v2.cu. */
 void dsb_flash_attn_debug_mode(int mode);
+/* Embedding lookup out[t] = table[ids[t]] (ids int64, dim % 8 == 0) and its gradient dtable[ids[t]] += dout[t], added
+ * with packed 16-bit atomics straight into the caller's (pre-existing, e.g. arena) gradient buffer: no dense temporary,
+ * no sort, no separate accumulate pass. */
+int dsb_embedding_fwd(const void* table, const long* ids, void* out, long ntok, int dim, long vocab, int dtype,
+                      void* stream);
+int dsb_embedding_bwd_acc(const void* dout, const long* ids, void* dtable, long ntok, int dim, long vocab, int dtype,
+                          void* stream);
 /* y = gelu(x + bias); dx = dy * gelu'(x + bias). Reference: csrc/transformer/gelu_kernels.cu:38-330. */
 int dsb_bias_gelu_fwd(const void* x, const void* bias, void* y, long rows, int cols, int dtype, void* stream);
 int dsb_bias_gelu_bwd(const void* dy, const void* x, const void* bias, void* dx, long rows, int cols, int dtype,

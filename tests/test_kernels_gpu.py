@@ -649,3 +649,30 @@ def test_causal_self_attention_op_native_backend(rot):
     ref.backward(g.float().cpu())
     assert _rel(out.cpu(), ref) < 5e-3
     assert _rel(qkv.grad.cpu(), ref_in.grad) < 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_embedding_gather_and_scatter_add(dtype):
+    """K.embedding: gather forward; backward adds into the table's EXISTING .grad (arena view) with packed atomics,
+    or returns a fresh gradient when there is none. Oracle: torch.nn.functional.embedding in fp32, repeated ids."""
+    torch.manual_seed(0)
+    vocab, dim = 1000, 264
+    table = (torch.randn(vocab, dim, device="cuda") * 0.5).to(dtype).requires_grad_()
+    ids = torch.randint(0, 50, (4, 96), device="cuda")          # few distinct rows: many repeats per row
+    dout = (torch.randn(4, 96, dim, device="cuda") * 0.1).to(dtype)
+    ref_t = table.detach().float().requires_grad_()
+    ref = torch.nn.functional.embedding(ids, ref_t)
+    ref.backward(dout.float())
+    out = K.embedding(ids, table)
+    assert torch.equal(out, table.detach()[ids])
+    out.backward(dout)                                           # no .grad yet: autograd receives the gradient
+    assert (table.grad.float() - ref_t.grad).abs().max().item() < (2e-2 if dtype == torch.float16 else 1e-1)
+    # with a gradient buffer in place the kernel accumulates into it and autograd gets None
+    base = table.grad.detach().clone()
+    keep_ptr = table.grad.data_ptr()
+    K.embedding(ids, table).backward(dout)
+    assert table.grad.data_ptr() == keep_ptr
+    assert (table.grad.float() - 2 * base.float()).abs().max().item() < (4e-2 if dtype == torch.float16 else 2e-1)
+    # untouched rows stay exactly zero
+    assert float(table.grad[50:].abs().max()) == 0.0
