@@ -57,148 +57,121 @@ def _counts_for_norm(p, mpu):
     return mpu is None or is_model_parallel_parameter(p) or _mp_rank(mpu) == 0
 
 
+def _flat(groups):
+    return [p for group in groups for p in group]
+
+
+def _agree(flag, group=None, device="cpu"):
+    """True if `flag` is true on any rank of `group` (MAX all-reduce of one float)."""
+    t = torch.tensor([float(flag)], device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return bool(t[0].item())
+
+
 class CheckOverflow:
     """Checks for inf/nan over model gradients, agreeing across MP / DP ranks with a MAX all-reduce."""
 
     def __init__(self, param_groups=None, mpu=None, zero_reduce_scatter=False):
         self.mpu = mpu
-        self.params = [] if param_groups else None
+        self.params = _flat(param_groups) if param_groups else None
         self.zero_reduce_scatter = zero_reduce_scatter
-        if param_groups:
-            for group in param_groups:
-                for param in group:
-                    self.params.append(param)
+
+    def _mp_group(self):
+        return self.mpu.get_model_parallel_group() if self.mpu is not None else None
 
     def check_using_norm(self, norm_group, reduce_overflow=True):
+        """A norm of -1 marks an overflowed group (see get_grad_norm)."""
         overflow = -1 in norm_group
-        if self.mpu is not None or reduce_overflow:
-            dev = "cuda" if torch.cuda.is_available() and dist.get_backend() == "nccl" else "cpu"
-            t = torch.tensor([float(overflow)], device=dev)
-            if self.mpu is not None:
-                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.mpu.get_model_parallel_group())
-            elif reduce_overflow:
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            overflow = t[0].item()
-        return bool(overflow)
+        if self.mpu is None and not reduce_overflow:
+            return bool(overflow)
+        on_gpu = torch.cuda.is_available() and dist.get_backend() == "nccl"
+        return _agree(overflow, self._mp_group(), "cuda" if on_gpu else "cpu")
 
     def check(self, param_groups=None):
-        params = []
-        if param_groups is None:
-            params = self.params
-        else:
-            assert param_groups is not None, "self.params and param_groups both cannot be none"
-            for group in param_groups:
-                for param in group:
-                    params.append(param)
-        return self.has_overflow(params)
+        return self.has_overflow(self.params if param_groups is None else _flat(param_groups))
 
     def has_overflow_serial(self, params):
+        """One fused sum-of-squares + non-finite-flag kernel per gradient; a single host read at the end."""
         grads = [p.grad for p in params if p.grad is not None]
         if not grads:
             return False
-        flag = torch.zeros(1, dtype=torch.int32, device=grads[0].device)
-        out = torch.zeros(1, dtype=torch.float32, device=grads[0].device)
+        dev = grads[0].device
+        flag, total = torch.zeros(1, dtype=torch.int32, device=dev), torch.zeros(1, dtype=torch.float32, device=dev)
         for g in grads:
-            if g.is_contiguous():
-                K.sumsq(g.view(-1), out=out, flag=flag, accumulate=True)
-            else:
-                K.sumsq(g.contiguous().view(-1), out=out, flag=flag, accumulate=True)
-        return bool(flag.item()) or not math.isfinite(out.item())
+            K.sumsq((g if g.is_contiguous() else g.contiguous()).view(-1), out=total, flag=flag, accumulate=True)
+        return bool(flag.item()) or not math.isfinite(total.item())
 
     def has_overflow(self, params):
         overflow = self.has_overflow_serial(params)
         if not (dist.is_available() and dist.is_initialized()):
             return overflow
-        dev = params[0].device if params else torch.device("cpu")
-        t = torch.tensor([float(overflow)], device=dev)
-        if self.zero_reduce_scatter:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=dist.group.WORLD)
-        elif self.mpu is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.mpu.get_model_parallel_group())
-        return bool(t[0].item())
+        if not (self.zero_reduce_scatter or self.mpu is not None):
+            return bool(overflow)
+        group = dist.group.WORLD if self.zero_reduce_scatter else self._mp_group()
+        return _agree(overflow, group, params[0].device if params else "cpu")
 
     @staticmethod
     def _has_inf_or_nan(x, i=None):
-        s = float(x.float().sum())
-        return s in (float("inf"), -float("inf")) or s != s
+        return not math.isfinite(float(x.float().sum()))
 
 
 def _has_inf_or_nan(x):
     return CheckOverflow._has_inf_or_nan(x)
 
 
-def get_grad_norm(parameters, norm_type=2, mpu=None):
-    """Global gradient norm across model-parallel ranks; returns -1 for inf/nan (treated as overflow upstream)."""
-    if isinstance(parameters, torch.Tensor):
-        parameters = [parameters]
-    parameters = [p for p in parameters if p.grad is not None]
-    if not parameters:
+def _global_norm(tensors, counted, norm_type, mpu, fused=True):
+    """Norm of the concatenation of `tensors` over the model-parallel group; `counted[i]` says whether tensor i is
+    this rank's to count (replicated tensors count on MP rank 0 only). Returns -1 for inf / nan: callers treat that as
+    a gradient overflow."""
+    if not tensors:
         return 0.0
-    dev = parameters[0].device
+    group = mpu.get_model_parallel_group() if mpu is not None else None
     norm_type = float(norm_type)
     if norm_type == inf:
-        total = torch.stack([p.grad.detach().abs().max().float() for p in parameters]).max().reshape(1)
-        if mpu is not None:
-            dist.all_reduce(total, op=dist.ReduceOp.MAX, group=mpu.get_model_parallel_group())
-        total_norm = total[0].item()
+        acc = torch.stack([t.abs().max().float() for t in tensors]).max().reshape(1)
+        op, root = dist.ReduceOp.MAX, 1.0
     else:
-        if norm_type == 2.0:
-            acc = torch.zeros(1, dtype=torch.float32, device=dev)
-            for p in parameters:
-                if _counts_for_norm(p, mpu):
-                    g = p.grad.detach()
-                    K.sumsq(g.view(-1) if g.is_contiguous() else g.contiguous().view(-1), out=acc, accumulate=True)
-        else:
-            acc = torch.zeros(1, dtype=torch.float32, device=dev)
-            for p in parameters:
-                if _counts_for_norm(p, mpu):
-                    acc += p.grad.detach().float().norm(norm_type) ** norm_type
-        if mpu is not None:
-            dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=mpu.get_model_parallel_group())
-        total_norm = acc[0].item() ** (1.0 / norm_type)
-    if total_norm == float("inf") or total_norm == -float("inf") or total_norm != total_norm:
-        total_norm = -1
-    return total_norm
+        acc = torch.zeros(1, dtype=torch.float32, device=tensors[0].device)
+        for t, mine in zip(tensors, counted):
+            if not mine:
+                continue
+            if fused and norm_type == 2.0:      # fused kernel, result stays on the device
+                K.sumsq((t if t.is_contiguous() else t.contiguous()).view(-1), out=acc, accumulate=True)
+            else:
+                acc += t.float().norm(norm_type) ** norm_type
+        op, root = dist.ReduceOp.SUM, 1.0 / norm_type
+    if group is not None:
+        dist.all_reduce(acc, op=op, group=group)
+    value = acc[0].item() ** root
+    return value if math.isfinite(value) else -1
+
+
+def _as_list(parameters):
+    return [parameters] if isinstance(parameters, torch.Tensor) else list(parameters)
+
+
+def get_grad_norm(parameters, norm_type=2, mpu=None):
+    """Global gradient norm across model-parallel ranks; returns -1 for inf/nan (treated as overflow upstream)."""
+    params = [p for p in _as_list(parameters) if p.grad is not None]
+    return _global_norm([p.grad.detach() for p in params], [_counts_for_norm(p, mpu) for p in params], norm_type, mpu)
 
 
 def get_weight_norm(parameters, norm_type=2, mpu=None):
-    if isinstance(parameters, torch.Tensor):
-        parameters = [parameters]
-    parameters = list(parameters)
-    if not parameters:
-        return 0.0
-    dev = parameters[0].device
-    norm_type = float(norm_type)
-    if norm_type == inf:
-        total = torch.stack([p.detach().abs().max().float() for p in parameters]).max().reshape(1)
-        if mpu is not None:
-            dist.all_reduce(total, op=dist.ReduceOp.MAX, group=mpu.get_model_parallel_group())
-        total_norm = total[0].item()
-    else:
-        acc = torch.zeros(1, dtype=torch.float32, device=dev)
-        for p in parameters:
-            if _counts_for_norm(p, mpu):
-                acc += p.detach().float().norm(norm_type) ** norm_type
-        if mpu is not None:
-            dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=mpu.get_model_parallel_group())
-        total_norm = acc[0].item() ** (1.0 / norm_type)
-    if total_norm == float("inf") or total_norm == -float("inf") or total_norm != total_norm:
-        total_norm = -1
-    return total_norm
+    params = _as_list(parameters)
+    return _global_norm([p.detach() for p in params], [_counts_for_norm(p, mpu) for p in params], norm_type, mpu,
+                        fused=False)
 
 
 def clip_grad_norm_(parameters, max_norm, norm_type=2, mpu=None):
-    """MP-aware clip (fp32 / AMP path)."""
-    if isinstance(parameters, torch.Tensor):
-        parameters = [parameters]
-    parameters = [p for p in parameters if p.grad is not None]
-    total_norm = get_grad_norm(parameters, norm_type, mpu)
-    if total_norm in (-1,):
+    """MP-aware clip (fp32 / AMP path): scales every gradient by max_norm / (norm + 1e-6) when that is below 1."""
+    params = [p for p in _as_list(parameters) if p.grad is not None]
+    total_norm = get_grad_norm(params, norm_type, mpu)
+    if total_norm == -1:
         return total_norm
-    clip_coef = float(max_norm) / (total_norm + 1e-6)
-    if clip_coef < 1:
-        for p in parameters:
-            p.grad.detach().mul_(clip_coef)
+    scale = float(max_norm) / (total_norm + 1e-6)
+    if scale < 1:
+        for p in params:
+            p.grad.detach().mul_(scale)
     return total_norm
 
 
@@ -221,69 +194,56 @@ def prime_factors(n):
 
 def prefix_sum_inc(weights):
     """Inclusive prefix sum."""
-    out = list(weights)
-    for i in range(1, len(out)):
-        out[i] += out[i - 1]
+    out, running = [], 0
+    for w in weights:
+        running += w
+        out.append(running)
     return out
 
 
 def partition_uniform(num_items, num_parts):
-    parts = [0] * (num_parts + 1)
+    """Boundaries [b_0 .. b_num_parts] of num_parts consecutive parts of floor(num_items / num_parts) items, the last
+    part taking the remainder; with fewer items than parts the first parts get one item each."""
     if num_items <= num_parts:
-        for p in range(num_parts + 1):
-            parts[p] = min(p, num_items)
-        return parts
-    chunksize = math.floor(num_items / num_parts)
-    for p in range(num_parts):
-        parts[p] = min(chunksize * p, num_items)
-    parts[num_parts] = num_items
-    return parts
+        return [min(p, num_items) for p in range(num_parts + 1)]
+    size = num_items // num_parts
+    return [min(size * p, num_items) for p in range(num_parts)] + [num_items]
 
 
 def _lprobe(weights, num_parts, bottleneck):
-    """Greedy feasibility probe: can prefix-summed `weights` be split into num_parts parts of weight <= bottleneck?"""
-    num_items = len(weights)
-    total_weight = weights[-1]
-    parts = [0] * (num_parts + 1)
-    for p in range(1, num_parts + 1):
-        parts[p] = num_items
-    bsum = bottleneck
-    chunksize = num_items // num_parts
-    step = chunksize
+    """Greedy feasibility probe on inclusive prefix sums: every part takes items while its weight stays BELOW
+    `bottleneck`. Returns (boundaries, feasible)."""
+    n, total = len(weights), weights[-1]
+    parts = [0] + [n] * num_parts
+    limit = bottleneck
     for p in range(1, num_parts):
-        while step < num_items and weights[step] < bsum:
-            step += chunksize
-        parts[p] = bisect_left(weights, bsum, lo=step - chunksize, hi=min(step, num_items))
-        if parts[p] == num_items:
-            part_size = weights[-1] - weights[parts[p - 1]]
-            return parts, part_size < bottleneck
-        bsum = weights[parts[p] - 1] + bottleneck
-    return parts, bsum >= total_weight
+        cut = bisect_left(weights, limit)          # first item whose prefix reaches the limit starts the next part
+        parts[p] = cut
+        if cut == n:                                # everything is placed: is what the last cut left light enough?
+            return parts, total - weights[parts[p - 1]] < bottleneck
+        limit = weights[cut - 1] + bottleneck
+    return parts, limit >= total
 
 
 def _rb_partition_balanced(weights, num_parts, eps):
-    total_weight = weights[-1]
-    lower = total_weight / num_parts
-    upper = total_weight
-    while upper > lower + eps:
-        mid = lower + (upper - lower) / 2
-        parts, success = _lprobe(weights, num_parts, mid)
-        if success:
-            upper = mid
+    """Smallest feasible bottleneck (within eps) by bisection between the ideal share and the total."""
+    low, high = weights[-1] / num_parts, weights[-1]
+    while high > low + eps:
+        mid = low + (high - low) / 2
+        if _lprobe(weights, num_parts, mid)[1]:
+            high = mid
         else:
-            lower = mid + eps
-    return upper
+            low = mid + eps
+    return high
 
 
 def partition_balanced(weights, num_parts, eps=1e-3):
     """Minimise the heaviest part (binary search on the bottleneck; reference utils.py:333-414)."""
-    num_items = len(weights)
-    if num_items <= num_parts:
-        return partition_uniform(num_items, num_parts)
-    weights_ = prefix_sum_inc(weights)
-    bottleneck = _rb_partition_balanced(weights_, num_parts, eps=eps)
-    parts, success = _lprobe(weights_, num_parts, bottleneck)
-    assert success
+    if len(weights) <= num_parts:
+        return partition_uniform(len(weights), num_parts)
+    prefix = prefix_sum_inc(weights)
+    parts, feasible = _lprobe(prefix, num_parts, _rb_partition_balanced(prefix, num_parts, eps=eps))
+    assert feasible
     return parts
 
 
@@ -292,58 +252,51 @@ class PartitionedTensor:
     receiver of a pipeline send can rebuild it (meta = [ndims, *shape, num_parts, rank, *partition_offsets])."""
 
     def __init__(self, tensor, group, partition_meta=None):
-        super().__init__()
         self.group = group
-        self.num_parts = dist.get_world_size(group=self.group)
-        self.rank = dist.get_rank(group=self.group)
+        self.num_parts = dist.get_world_size(group=group)
+        self.rank = dist.get_rank(group=group)
         self.orig_size = list(tensor.size())
         self.orig_device = tensor.device
         self.local_data, self.partition = self._partition_tensor(tensor)
 
     @classmethod
     def from_meta(cls, meta, local_part, group, device=None):
+        """Rebuild the receiver's view from a meta vector and the local part that came with it."""
         assert meta.dtype == torch.long
-        dummy = torch.ones(dist.get_world_size(group=group))
-        part_obj = cls(tensor=dummy, group=group)
-        meta = meta.tolist()
-        part_obj.orig_size = meta[1:(1 + meta[0])]
-        meta = meta[1 + meta[0]:]
-        part_obj.orig_device = device if device is not None else local_part.device
-        part_obj.local_data = local_part.detach()
-        part_obj.group = group
-        assert part_obj.num_parts == meta[0]
-        assert part_obj.rank == meta[1]
-        part_obj.partition = meta[2:]
-        return part_obj
+        fields = meta.tolist()
+        ndims = fields[0]
+        obj = cls.__new__(cls)
+        obj.group = group
+        obj.num_parts, obj.rank = dist.get_world_size(group=group), dist.get_rank(group=group)
+        obj.orig_size = fields[1:1 + ndims]
+        obj.orig_device = device if device is not None else local_part.device
+        obj.local_data = local_part.detach()
+        assert (obj.num_parts, obj.rank) == tuple(fields[1 + ndims:3 + ndims])
+        obj.partition = fields[3 + ndims:]
+        return obj
+
+    def _bounds(self, part):
+        return self.partition[part], self.partition[part + 1] - self.partition[part]
 
     def _partition_tensor(self, tensor):
-        partition = partition_uniform(num_items=tensor.numel(), num_parts=self.num_parts)
-        start = partition[self.rank]
-        length = partition[self.rank + 1] - start
-        tensor_part = tensor.detach().contiguous().view(-1).narrow(0, start=start, length=length).clone()
-        return tensor_part, partition
+        self.partition = partition_uniform(num_items=tensor.numel(), num_parts=self.num_parts)
+        start, length = self._bounds(self.rank)
+        return tensor.detach().contiguous().view(-1).narrow(0, start, length).clone(), self.partition
 
     def full(self, device=None):
-        if device is None:
-            device = self.orig_device
-        full_numel = math.prod(self.full_size())
-        flat_tensor = torch.zeros([full_numel], dtype=self.local_data.dtype, device=device)
-        partition_tensors = []
-        for part_id in range(self.num_parts):
-            part_size = self.partition[part_id + 1] - self.partition[part_id]
-            buf = flat_tensor.narrow(0, start=self.partition[part_id], length=part_size)
-            if part_id == self.rank:
-                buf.copy_(self.local_data)
-            partition_tensors.append(buf)
-        # parts may be uneven, so exchange through equally-sized padded buffers
-        max_len = max(t.numel() for t in partition_tensors)
-        padded = [torch.zeros(max_len, dtype=flat_tensor.dtype, device=device) for _ in range(self.num_parts)]
-        mine = torch.zeros(max_len, dtype=flat_tensor.dtype, device=device)
+        """All-gather the parts (through equally sized padded buffers: parts may be uneven) into the full tensor."""
+        device = self.orig_device if device is None else device
+        dtype = self.local_data.dtype
+        longest = max(self._bounds(part)[1] for part in range(self.num_parts))
+        mine = torch.zeros(longest, dtype=dtype, device=device)
         mine[:self.local_data.numel()].copy_(self.local_data)
+        padded = [torch.zeros(longest, dtype=dtype, device=device) for _ in range(self.num_parts)]
         dist.all_gather(padded, mine, group=self.group)
-        for part_id, buf in enumerate(partition_tensors):
-            buf.copy_(padded[part_id][:buf.numel()])
-        return flat_tensor.view(self.full_size()).clone().detach()
+        flat = torch.zeros(math.prod(self.full_size()), dtype=dtype, device=device)
+        for part, buf in enumerate(padded):
+            start, length = self._bounds(part)
+            flat.narrow(0, start, length).copy_(buf[:length])
+        return flat.view(self.full_size()).clone().detach()
 
     def to_meta(self):
         meta = [len(self.orig_size)] + list(self.orig_size) + [self.num_parts, self.rank] + list(self.partition)
