@@ -1015,7 +1015,7 @@ static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out
     using namespace dsb::fa;
     ensure_context_on_this_thread();
     if (B <= 0 || S <= 0 || H <= 0) return 0;
-    if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
+    if (D < 8 || D > HD || (D % 8) || (S % BQ)) return DSB_ERR_SIZE;      // D < 128: see flash_v2.cuh
     if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
     if (dropout_p < 0.f || dropout_p >= 1.f) return DSB_ERR_ARG;
     const long strides[12] = {q_sb, q_ss, q_sh, k_sb, k_ss, k_sh, v_sb, v_ss, v_sh, o_sb, o_ss, o_sh};
@@ -1038,7 +1038,7 @@ static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out
     const float scale_log2 = scale * 1.4426950408889634f;
     dim3 grid(S / BQ, B * H);
     cudaError_t e;
-    const bool extras = sched != nullptr || kpm != nullptr || dropout_p > 0.f;
+    const bool extras = sched != nullptr || kpm != nullptr || dropout_p > 0.f || D != HD;
     if (sched != nullptr && S % 256) return DSB_ERR_SIZE;   // schedules are per 256-row query block
     if (g_fa_fwd_variant == 2 || extras) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
@@ -1202,7 +1202,7 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
     using namespace dsb::fa;
     ensure_context_on_this_thread();
     if (B <= 0 || S <= 0 || H <= 0) return 0;
-    if (D != HD || (S % BQ)) return DSB_ERR_SIZE;
+    if (D < 8 || D > HD || (D % 8) || (S % BQ)) return DSB_ERR_SIZE;      // D < 128: see flash_v2.cuh
     if (dtype != DSB_DTYPE_F16 && dtype != DSB_DTYPE_BF16) return DSB_ERR_DTYPE;
     if (dropout_p < 0.f || dropout_p >= 1.f) return DSB_ERR_ARG;
     if (rot_dim > 0 && (rot_cos == nullptr || rot_sin == nullptr)) return DSB_ERR_ARG;
@@ -1218,7 +1218,7 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
     float* dq_acc = scratch + 2 * bhs;
     cudaError_t ce = cudaMemsetAsync(dq_acc, 0, sizeof(float) * bhs * HD, stream);
     if (ce != cudaSuccess) return -(int)ce;
-    int rc = fa2::launch_prep(dO, out, lse, nlse2, ndelta, B, S, H, s_do, s_o, scale, bf, stream);
+    int rc = fa2::launch_prep(dO, out, lse, nlse2, ndelta, B, S, H, s_do, s_o, scale, bf, stream, D);
     if (rc) return rc;
     CUtensorMap tq, tk, tv, tdo, tdk, tdv, tdq;
     if ((rc = make_map_bshd(&tq, bf, q, B, S, H, D, s_q[0], s_q[1], s_q[2], 64))) return rc;
@@ -1229,8 +1229,9 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
     if ((rc = make_map_bshd(&tdv, bf, dv, B, S, H, D, s_dv[0], s_dv[1], s_dv[2]))) return rc;
     EncodeTiledFn enc = get_encode();
     if (!enc) return -1;
-    cuuint64_t dims[4] = {(cuuint64_t)S, (cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)B};
-    cuuint64_t st[3] = {(cuuint64_t)S * 4, (cuuint64_t)D * S * 4, (cuuint64_t)H * D * S * 4};
+    // the accumulator always has 128 rows per head (rows >= D stay zero), whatever the head dim
+    cuuint64_t dims[4] = {(cuuint64_t)S, (cuuint64_t)HD, (cuuint64_t)H, (cuuint64_t)B};
+    cuuint64_t st[3] = {(cuuint64_t)S * 4, (cuuint64_t)HD * S * 4, (cuuint64_t)H * HD * S * 4};
     cuuint32_t box[4] = {32, 128, 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(&tdq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dq_acc, dims, st, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -1240,7 +1241,7 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
                          bf, rot_cos, rot_sin, rot_dim, sched, sched_hstride, sched_pstride, kpm,
                          make_dropout(dropout_p, dropout_seed), stream);
     if (rc) return rc;
-    return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, rot_cos, rot_sin, rot_dim, stream);
+    return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, rot_cos, rot_sin, rot_dim, stream, D);
 }
 
 extern "C" int dsb_flash_attn_bwd2(const void* dO, const void* q, const void* k, const void* v, const void* out,

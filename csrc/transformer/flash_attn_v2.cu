@@ -613,7 +613,7 @@ __global__ void __launch_bounds__(256) flash_prep_kernel(const T* __restrict__ d
                                                          const float* __restrict__ lse, float* __restrict__ nlse2,
                                                          float* __restrict__ ndelta, int B, int S, int H, long do_sb,
                                                          long do_ss, long do_sh, long o_sb, long o_ss, long o_sh,
-                                                         float scale) {
+                                                         float scale, int D) {
     const long rows = (long)B * S * H;
     const int lane = threadIdx.x & 31;
     for (long r = (long)blockIdx.x * 8 + (threadIdx.x >> 5); r < rows; r += (long)gridDim.x * 8) {
@@ -621,11 +621,14 @@ __global__ void __launch_bounds__(256) flash_prep_kernel(const T* __restrict__ d
         const long t = r / H;
         const int s = (int)(t % S);
         const int b = (int)(t / S);
-        const uint2 a = *reinterpret_cast<const uint2*>(dO + b * do_sb + s * do_ss + h * do_sh + lane * 4);
-        const uint2 c = *reinterpret_cast<const uint2*>(O + b * o_sb + s * o_ss + h * o_sh + lane * 4);
-        const float2 a0 = Cvt<T>::unpack2(a.x), a1 = Cvt<T>::unpack2(a.y);
-        const float2 c0 = Cvt<T>::unpack2(c.x), c1 = Cvt<T>::unpack2(c.y);
-        float v = a0.x * c0.x + a0.y * c0.y + a1.x * c1.x + a1.y * c1.y;
+        float v = 0.f;
+        if (lane * 4 < D) {      // head dims below 128: the rows are only D wide
+            const uint2 a = *reinterpret_cast<const uint2*>(dO + b * do_sb + s * do_ss + h * do_sh + lane * 4);
+            const uint2 c = *reinterpret_cast<const uint2*>(O + b * o_sb + s * o_ss + h * o_sh + lane * 4);
+            const float2 a0 = Cvt<T>::unpack2(a.x), a1 = Cvt<T>::unpack2(a.y);
+            const float2 c0 = Cvt<T>::unpack2(c.x), c1 = Cvt<T>::unpack2(c.y);
+            v = a0.x * c0.x + a0.y * c0.y + a1.x * c1.x + a1.y * c1.y;
+        }
         v = warp_sum(v);
         if (lane == 0) {
             const long o = ((long)b * H + h) * S + s;
@@ -641,7 +644,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) flash_dq_finish_kernel(const float* __restrict__ acc, T* __restrict__ dq, int S,
                                                               int H, long sb, long ss, long sh,
                                                               const float* __restrict__ rot_cs,
-                                                              const float* __restrict__ rot_sn, int rot) {
+                                                              const float* __restrict__ rot_sn, int rot, int D) {
     __shared__ float tile[128][33];
     const int s0 = blockIdx.x * 32;
     const int bh = blockIdx.y;
@@ -671,7 +674,7 @@ __global__ void __launch_bounds__(256) flash_dq_finish_kernel(const float* __res
         uint2 o;
         o.x = Cvt<T>::pack2(v[0], v[1]);
         o.y = Cvt<T>::pack2(v[2], v[3]);
-        *reinterpret_cast<uint2*>(dst + (long)(s0 + s) * ss + lane * 4) = o;
+        if (lane * 4 < D) *reinterpret_cast<uint2*>(dst + (long)(s0 + s) * ss + lane * 4) = o;
     }
 }
 
@@ -1152,29 +1155,29 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
 }
 
 int launch_prep(const void* dO, const void* O, const float* lse, float* nlse2, float* ndelta, int B, int S, int H,
-                const long* s_do, const long* s_o, float scale, int bf16, cudaStream_t stream) {
+                const long* s_do, const long* s_o, float scale, int bf16, cudaStream_t stream, int D) {
     const long rows = (long)B * S * H;
     const int grid = (int)((rows + 7) / 8 < 148L * 16 ? (rows + 7) / 8 : 148L * 16);
     if (bf16)
         flash_prep_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((const __nv_bfloat16*)dO, (const __nv_bfloat16*)O, lse,
                                                                    nlse2, ndelta, B, S, H, s_do[0], s_do[1], s_do[2],
-                                                                   s_o[0], s_o[1], s_o[2], scale);
+                                                                   s_o[0], s_o[1], s_o[2], scale, D);
     else
         flash_prep_kernel<__half><<<grid, 256, 0, stream>>>((const __half*)dO, (const __half*)O, lse, nlse2, ndelta, B, S,
-                                                            H, s_do[0], s_do[1], s_do[2], s_o[0], s_o[1], s_o[2], scale);
+                                                            H, s_do[0], s_do[1], s_do[2], s_o[0], s_o[1], s_o[2], scale, D);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
 }
 
 int launch_dq_finish(const float* acc, void* dq, int B, int S, int H, const long* s_dq, int bf16, const float* rot_cs,
-                     const float* rot_sn, int rot, cudaStream_t stream) {
+                     const float* rot_sn, int rot, cudaStream_t stream, int D) {
     dim3 grid(S / 32, B * H);
     if (bf16)
         flash_dq_finish_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(acc, (__nv_bfloat16*)dq, S, H, s_dq[0], s_dq[1],
-                                                                        s_dq[2], rot_cs, rot_sn, rot);
+                                                                        s_dq[2], rot_cs, rot_sn, rot, D);
     else
         flash_dq_finish_kernel<__half><<<grid, 256, 0, stream>>>(acc, (__half*)dq, S, H, s_dq[0], s_dq[1], s_dq[2],
-                                                                 rot_cs, rot_sn, rot);
+                                                                 rot_cs, rot_sn, rot, D);
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
 }

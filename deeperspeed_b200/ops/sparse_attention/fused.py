@@ -10,7 +10,7 @@ or multiplied, listed tiles run on the tensor cores (tcgen05.mma, operands by TM
 (per 128-key block, the 64-row query blocks that see it). Key-padding masks ride along as an additive per-key bias.
 
 Supported: fp16 / bf16, sequence length a multiple of 256, head dim <= 128 (smaller head dims are zero-padded to the
-kernel's 128), layout blocks of 16 / 32 / 64 / 128, key-padding mask in "add" or "mul" mode. Relative position
+kernel's 128 by TMA itself, without copies), layout blocks of 16 / 32 / 64 / 128, key-padding mask in "add" or "mul" mode. Relative position
 embeddings and dense attention masks go through the unfused operators (`SparseSelfAttention` falls back by itself).
 """
 import ctypes as C
@@ -76,17 +76,13 @@ def build_schedules(layout, block, seq_len):
     return _records(wf, KB), _records(wb, QB)
 
 
-def _as_bshd128(x):
-    """[B, H, S, D] -> a [B, S, H, 128] view (D == 128) or zero-padded copy (D < 128) with unit last stride."""
-    B, H, S, D = x.shape
-    if D == 128:
-        v = x.transpose(1, 2)
-        if v.stride(-1) == 1 and all(st % 8 == 0 for st in v.stride()[:3]):
-            return v
-        return v.contiguous()
-    out = torch.zeros(B, S, H, 128, dtype=x.dtype, device=x.device)
-    out[..., :D] = x.transpose(1, 2)
-    return out
+def _as_bshd(x):
+    """[B, H, S, D] -> a [B, S, H, D] view with unit last stride and 16-byte-aligned strides (a copy only if needed).
+    Head dims below 128 need no padding: the kernels' tensor maps carry the true D and TMA zero-fills the rest."""
+    v = x.transpose(1, 2)
+    if v.stride(-1) == 1 and all(st % 8 == 0 for st in v.stride()[:3]) and v.data_ptr() % 16 == 0:
+        return v
+    return v.contiguous()
 
 
 def _strides(*tensors):
@@ -109,36 +105,35 @@ class BlockSparseFlashFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, q, k, v, sched_f, sched_b, kpm, scale, dropout=None):
         B, H, S, D = q.shape
-        q4, k4, v4 = _as_bshd128(q), _as_bshd128(k), _as_bshd128(v)
-        out = torch.empty(B, S, H, 128, dtype=q.dtype, device=q.device)
+        q4, k4, v4 = _as_bshd(q), _as_bshd(k), _as_bshd(v)
+        out = torch.empty(B, S, H, D, dtype=q.dtype, device=q.device)
         lse = torch.empty(B, H, S, dtype=torch.float32, device=q.device)
         hs, ps = _sched_strides(sched_f)
         p_drop, seed = dropout if dropout is not None else (0.0, 0)
         N.check(N.cuda_lib().dsb_flash_attn_fwd_drop(
-            N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), B, S, H, 128, _strides(q4, k4, v4, out),
+            N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), B, S, H, D, _strides(q4, k4, v4, out),
             float(scale), 0, N.dtype_code(q.dtype), N.ptr(sched_f), hs, ps, N.ptr(kpm), float(p_drop),
             int(seed) & 0xffffffff, N.stream_ptr()), "dsb_flash_attn_fwd_drop")
         K._count()
         ctx.save_for_backward(q4, k4, v4, out, lse, sched_b, kpm)
         ctx.meta = (D, float(scale), float(p_drop), int(seed) & 0xffffffff)
-        return out[..., :D].transpose(1, 2)
+        return out.transpose(1, 2)
 
     @staticmethod
     def backward(ctx, dctx):
         q4, k4, v4, out, lse, sched_b, kpm = ctx.saved_tensors
         D, scale, p_drop, seed = ctx.meta
         B, S, H, _ = q4.shape
-        do4 = _as_bshd128(dctx)
-        dq, dk, dv = (torch.empty(B, S, H, 128, dtype=q4.dtype, device=q4.device) for _ in range(3))
+        do4 = _as_bshd(dctx)
+        dq, dk, dv = (torch.empty(B, S, H, D, dtype=q4.dtype, device=q4.device) for _ in range(3))
         scratch = torch.empty((2 + 128) * B * H * S, dtype=torch.float32, device=q4.device)
         hs, ps = _sched_strides(sched_b)
         N.check(N.cuda_lib().dsb_flash_attn_bwd2_drop(
             N.ptr(do4), N.ptr(q4), N.ptr(k4), N.ptr(v4), N.ptr(out), N.ptr(lse), N.ptr(scratch), N.ptr(dq), N.ptr(dk),
-            N.ptr(dv), B, S, H, 128, _strides(do4, q4, k4, v4, out, dq, dk, dv), scale, 0, N.dtype_code(q4.dtype),
+            N.ptr(dv), B, S, H, D, _strides(do4, q4, k4, v4, out, dq, dk, dv), scale, 0, N.dtype_code(q4.dtype),
             N.ptr(sched_b), hs, ps, N.ptr(kpm), p_drop, seed, N.stream_ptr()), "dsb_flash_attn_bwd2_drop")
         K._count(3)
-        cut = lambda t: t[..., :D].transpose(1, 2)
-        return cut(dq), cut(dk), cut(dv), None, None, None, None, None
+        return dq.transpose(1, 2), dk.transpose(1, 2), dv.transpose(1, 2), None, None, None, None, None
 
 
 def dropout_keep_mask(B, H, S, p, seed, device="cpu"):
