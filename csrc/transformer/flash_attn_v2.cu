@@ -502,7 +502,8 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             const bool grow = m_cand > m_run + F_TAU;   // always true for the first block (m_run = -inf)
             if (__any_sync(0xffffffffu, grow)) {
                 const float m_new = grow ? m_cand : m_run;
-                const float alpha = ex2(m_run - m_new);
+                // rows that do not grow keep their state (also rows that have seen nothing yet: -inf - -inf is not 0)
+                const float alpha = grow ? ex2(m_run - m_new) : 1.f;
                 if (j > 0) {
                     mbar_wait(&pv_done[t], (j - 1) & 1);   // O_t is quiescent: P V of the previous block has completed
                     tc_fence_after();

@@ -18,7 +18,8 @@ from .sparsity_config import SparsityConfig
 class SparseSelfAttention(nn.Module):
     ops = dict()      # (seq_len, block, layout fingerprint) -> (sdd, dsd, softmax)
     schedules = dict()  # (seq_len, block, layout fingerprint, device) -> (forward, backward) schedules of the fused kernel
-    use_fused = True  # one tcgen05 flash kernel per direction when the call qualifies (ops/sparse_attention/fused.py)
+    use_fused = True          # one tcgen05 flash kernel per direction when the call qualifies (ops/sparse_attention/fused.py)
+    reorder_keys = True       # fused path: visit keys in the order planned by fused.plan_key_order
 
     def __init__(self, sparsity_config=SparsityConfig(num_heads=4), key_padding_mask_mode="add", attn_mask_mode="mul",
                  max_seq_length=2048):
@@ -78,11 +79,17 @@ class SparseSelfAttention(nn.Module):
     def _get_schedules_uncached(self, L, device):
         layout = self.get_layout(L)
         block = self.sparsity_config.block
-        key = (L, block, hash(layout.numpy().tobytes()), str(device))
+        key = (L, block, hash(layout.numpy().tobytes()), str(device), bool(self.reorder_keys))
         cached = SparseSelfAttention.schedules.get(key)
         if cached is None:
-            fwd, bwd = fused.build_schedules(layout, block, L)
-            cached = SparseSelfAttention.schedules[key] = (fwd.to(device), bwd.to(device))
+            # keys are visited in an order that packs widely seen ("global") columns into dense tiles when that pays
+            order, planned = fused.plan_key_order(layout, block, L) if self.reorder_keys else (None, layout)
+            fwd, bwd = fused.build_schedules(planned, block, L)
+            if order is not None:      # (order, inverse order) as device index tensors
+                inverse = torch.empty_like(order)
+                inverse[order] = torch.arange(order.numel())
+                order = (order.to(device), inverse.to(device))
+            cached = SparseSelfAttention.schedules[key] = (fwd.to(device), bwd.to(device), order)
         return cached
 
     # ---- operand helpers
@@ -112,8 +119,12 @@ class SparseSelfAttention(nn.Module):
         if attn_mask is not None:
             attn_mask = self.transpose_mask_for_sparse(query.dtype, attn_mask)
         if self.use_fused and fused.supported(query, self.sparsity_config.block, rpe, attn_mask):
-            sched_f, sched_b = self.get_schedules(seq, query.device)
+            sched_f, sched_b, key_order = self.get_schedules(seq, query.device)
             bias = fused.key_mask_bias(key_padding_mask, self.key_padding_mask_mode, query.shape[0], seq)
+            if key_order is not None:      # the schedules were built for this key order (autograd undoes the gathers)
+                key = fused.PermuteKeysFn.apply(key, *key_order)
+                value = fused.PermuteKeysFn.apply(value, *key_order)
+                bias = None if bias is None else bias.index_select(1, key_order[0]).contiguous()
             return fused.BlockSparseFlashFn.apply(query, key, value, sched_f, sched_b, bias, float(head_dim) ** -0.5)
         scores_op, context_op, softmax_op = self.get_ops(heads, seq)
         probs = softmax_op(scores_op(query, key), scale=float(head_dim) ** -0.5, rpe=rpe,

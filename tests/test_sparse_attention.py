@@ -298,3 +298,99 @@ def test_flash_attention_dropout_matches_masked_reference(D, dtype, p):
     plain = fused.BlockSparseFlashFn.apply(q, k, v, None, None, None, scale, None)
     ref0 = torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf
     assert (plain.float() - ref0).abs().max().item() / ref0.abs().max().item() < tol
+
+
+def test_key_order_plan_is_a_permutation_that_cuts_tile_work():
+    """fused.plan_key_order: the fixed pattern's global columns (one 16-key block per window) are moved to the front,
+    in index order; the result is a permutation, the permuted layout is the layout with its columns reordered, and the
+    schedules need far fewer tiles. Layouts that gain nothing (or differ per head) keep their order."""
+    from deeperspeed_b200.ops.sparse_attention import fused, BigBirdSparsityConfig, VariableSparsityConfig
+    S, block = 4096, 16
+    cfg = FixedSparsityConfig(num_heads=4, block=block, num_local_blocks=8, num_global_blocks=1, attention="unidirectional")
+    layout = cfg.make_layout(S)
+    order, planned = fused.plan_key_order(layout, block, S)
+    assert order is not None and sorted(order.tolist()) == list(range(S))
+    assert fused.plan_key_order(cfg.make_layout(1024), block, 1024)[0] is None      # too little to gain at 1k tokens
+    blocks = order.view(-1, block)[:, 0] // block
+    assert torch.equal(planned, layout[:, :, blocks])
+    # whole blocks move, tokens inside a block keep their order
+    assert torch.equal(order.view(-1, block), blocks.view(-1, 1) * block + torch.arange(block))
+    work = lambda lay: fused._tile_work(*fused.build_schedules(lay, block, S))
+    assert work(planned) < 0.5 * work(layout)
+    # the moved columns are the widely seen ones, still ascending (a causal prefix of them stays a prefix)
+    moved = blocks[:int((blocks[:-1] > blocks[1:]).nonzero()[0]) + 1]
+    assert torch.equal(moved, moved.sort().values) and bool((moved % 8 == 7).all())
+    bb = BigBirdSparsityConfig(num_heads=2, block=block, num_random_blocks=1, num_global_blocks=2).make_layout(S)
+    assert fused.plan_key_order(bb, block, S)[0] is None          # global blocks already sit together at the front
+    var = VariableSparsityConfig(num_heads=2, block=block, different_layout_per_head=True, num_random_blocks=2).make_layout(S)
+    assert fused.plan_key_order(var, block, S)[0] is None         # per-head layouts: one shared order does not exist
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("key_mask", [False, True])
+def test_fused_block_sparse_attention_with_reordered_keys(key_mask):
+    """Long fixed layout: the module visits the keys in the planned order (gathers K, V and the key mask) - same result
+    as dense masked attention, gradients included, and the same as with the reordering switched off."""
+    from deeperspeed_b200.ops.sparse_attention import fused
+    torch.manual_seed(6)
+    Bz, H, S, D, block = 1, 4, 4096, 64, 16
+    cfg = FixedSparsityConfig(num_heads=H, block=block, num_local_blocks=8, num_global_blocks=1, attention="unidirectional")
+    SparseSelfAttention.schedules.clear()
+    attn = SparseSelfAttention(cfg, max_seq_length=S).cuda()
+    assert attn.get_schedules(S, torch.device("cuda", 0))[2] is not None
+    q, k, v = ((torch.randn(Bz, H, S, D, device="cuda") * 0.7).half().requires_grad_() for _ in range(3))
+    kpm = None
+    if key_mask:
+        kpm = torch.zeros(Bz, S, device="cuda", dtype=torch.float16)
+        kpm[:, 100:180] = -10000.0
+    out = attn(q, k, v, key_padding_mask=kpm)
+    g = torch.randn_like(out)
+    grads = torch.autograd.grad(out, (q, k, v), g)
+    plain = SparseSelfAttention(cfg, max_seq_length=S).cuda()
+    plain.reorder_keys = False
+    assert plain.get_schedules(S, torch.device("cuda", 0))[2] is None
+    out0 = plain(q, k, v, key_padding_mask=kpm)
+    grads0 = torch.autograd.grad(out0, (q, k, v), g)
+    assert (out.float() - out0.float()).abs().max() < 2e-3
+    for a, b in zip(grads, grads0):
+        assert (a.float() - b.float()).abs().max() < 1e-2 * max(1.0, b.float().abs().max().item())
+    layout = attn.get_layout(S)
+    vis = sparse_to_dense(torch.ones(1, int(layout.sum()), block, block), layout, block)[0].bool().cuda()
+    sc = (q.float() @ k.float().transpose(-1, -2)) * D ** -0.5
+    if kpm is not None:
+        sc = sc + kpm.float()[:, None, None, :]
+    ref = torch.softmax(sc.masked_fill(~vis[None], float("-inf")), -1) @ v.float()
+    assert (out.float() - ref).abs().max() < 3e-3
+
+
+@pytest.mark.gpu
+def test_fused_rows_that_see_nothing_in_their_first_tile():
+    """Regression: a query row whose first live key tile holds nothing visible FOR IT (other rows of its warp do see
+    keys there) used to pick up a NaN rescale factor (-inf - -inf) and come out as zeros."""
+    from deeperspeed_b200.ops.sparse_attention import SparsityConfig
+
+    class Crossed(SparsityConfig):
+        def make_layout(self, seq_len):
+            layout = self.setup_layout(seq_len)
+            nb = layout.shape[1]
+            for i in range(nb):
+                layout[:, i, (nb // 2 + i) % nb if i % 2 == 0 else i // 2] = 1      # even rows look far ahead, odd rows back
+                layout[:, i, i] = 1
+            return layout
+
+    torch.manual_seed(8)
+    S, D, H, block = 512, 128, 2, 16
+    SparseSelfAttention.schedules.clear()
+    attn = SparseSelfAttention(Crossed(num_heads=H, block=block), max_seq_length=S).cuda()
+    q, k, v = ((torch.randn(1, H, S, D, device="cuda") * 0.7).half().requires_grad_() for _ in range(3))
+    out = attn(q, k, v)
+    g = torch.randn_like(out)
+    grads = torch.autograd.grad(out, (q, k, v), g)
+    layout = attn.get_layout(S)
+    vis = sparse_to_dense(torch.ones(1, int(layout.sum()), block, block), layout, block)[0].bool().cuda()
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    ref = torch.softmax(((qf @ kf.transpose(-1, -2)) * D ** -0.5).masked_fill(~vis[None], float("-inf")), -1) @ vf
+    refg = torch.autograd.grad(ref, (qf, kf, vf), g.float())
+    assert torch.isfinite(out).all() and (out.float() - ref).abs().max() < 3e-3
+    for a, b in zip(grads, refg):
+        assert (a.float() - b).abs().max() < 2e-2 * max(1.0, b.abs().max().item())
