@@ -362,8 +362,13 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
                     logger.warning("**** You are using ZeRO with an untested optimizer, proceed with caution *****")
             self.optimizer = self._configure_zero_optimizer(basic)
         elif self.amp_enabled():
-            raise RuntimeError("apex AMP is not available in this environment; use the fp16 block (fp16 or bfloat16) "
-                               "which gives the O2-style master-weight regime")
+            assert not (self.fp16_enabled() and self.precision() != torch.float32), \
+                "Cannot enable both amp with (legacy) fp16 mode"
+            from .amp import NativeAmp
+            self.amp = NativeAmp(self.amp_params(), self.device)      # torch.autocast + GradScaler (no apex needed)
+            logger.info(f"Initializing AMP with these params: {self.amp_params()}")
+            self.optimizer = basic
+            self._broadcast_model()      # deferred in _configure_distributed_model when amp is on, as in the reference
         elif self.fp16_enabled() and self.precision() != torch.float32:
             self.optimizer = self._configure_fp16_optimizer(basic)
         else:

@@ -83,7 +83,12 @@ class TrainStepMixin:
         if self.training_dataloader is None:
             self.tput_timer.start()
         with self._timed("forward_microstep", "forward"):
-            loss = self.module(*inputs, **kwargs)
+            amp = getattr(self, "amp", None)
+            if amp is not None:
+                with amp.autocast():
+                    loss = self.module(*inputs, **kwargs)
+            else:
+                loss = self.module(*inputs, **kwargs)
         if zero3:
             if not torch._C.is_grad_enabled():
                 self.optimizer.param_coordinator.reset_step()      # no backward will come to close the trace
@@ -132,7 +137,9 @@ class TrainStepMixin:
             with self._timed("backward_inner_microstep", "backward_inner"):
                 if hasattr(self.optimizer, "is_gradient_accumulation_boundary"):
                     self.optimizer.is_gradient_accumulation_boundary = boundary
-                if self.zero_optimization() or hasattr(self.optimizer, "backward"):
+                if getattr(self, "amp", None) is not None:
+                    self.amp.backward(loss)            # GradScaler's loss scale
+                elif self.zero_optimization() or hasattr(self.optimizer, "backward"):
                     self.optimizer.backward(loss)      # applies the loss scale
                 else:
                     loss.backward()
@@ -157,18 +164,23 @@ class TrainStepMixin:
     def _take_model_step(self, lr_kwargs):
         """One optimizer step plus its bookkeeping (skipped steps, LR schedule, counters)."""
         wrapped = self.zero_optimization() or (self.fp16_enabled() and self.precision() != torch.float32)
-        if self.gradient_clipping() > 0.0 and not wrapped:
+        amp = getattr(self, "amp", None)
+        if self.gradient_clipping() > 0.0 and not wrapped and amp is None:
             self.clip_fp32_gradients()      # the fp16 / ZeRO wrappers clip inside their own step
         if self.store_gradients:
             keep = (lambda g: g.clone().cpu()) if self.store_gradients_cpu else (lambda g: g.clone())
             self.stored_gradients = [keep(p.grad) for p in self.module.parameters() if p.grad is not None]
-        self.optimizer.step()
+        if amp is not None:                 # unscale -> clip -> step (skipped on overflow) -> new scale
+            amp.step(self.optimizer, [p for p in self.module.parameters() if p.grad is not None],
+                     self.gradient_clipping())
+        else:
+            self.optimizer.step()
         if not wrapped:
             self.zero_grad()                # a client optimizer's own zero_grad is not relied upon
         elif not hasattr(self.optimizer, "arenas"):
             self.optimizer.zero_grad()      # arena optimizers clear their gradient arena inside step()
 
-        if getattr(self.optimizer, "overflow", False):
+        if getattr(self.optimizer, "overflow", False) or (amp is not None and amp.skipped):
             self.skipped_steps += 1
         elif self.lr_scheduler is not None:
             self.lr_scheduler.step(**(lr_kwargs or {}))

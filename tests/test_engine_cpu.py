@@ -476,3 +476,46 @@ def test_zero2_sharded_gradient_memory_world2(tmp_path):
         losses = _train(engine, 2)
         assert all(l == l for l in losses)
     run()
+
+
+def test_amp_block_runs_on_native_autocast_world2(tmp_path):
+    """`"amp": {"enabled": true}`: autocast forward + GradScaler instead of apex; fp32 weights, gradients averaged over
+    the ranks, replicas stay identical, the loss goes down, and amp + fp16 / amp + ZeRO are refused like the reference."""
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(3 + dist.get_rank())          # different initial weights: the deferred broadcast must fix that
+        model = SimpleModel(HID)
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.01}}, "gradient_clipping": 1.0,
+               "amp": {"enabled": True, "opt_level": "O1"}}
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        assert engine.amp is not None and all(p.dtype == torch.float32 for p in model.parameters())
+        start = [p.detach().clone() for p in model.parameters()]      # rank 0's weights after the broadcast
+        _train(engine, 4)
+        flat = torch.cat([p.detach().view(-1) for p in model.parameters()])
+        other = flat.clone()
+        dist.broadcast(other, src=0)
+        assert torch.allclose(flat, other, atol=1e-6)
+        # the same four steps by hand: autocast forward on both ranks' batches, averaged gradients, clip, Adam
+        ref = SimpleModel(HID)
+        for p, s0 in zip(ref.parameters(), start):
+            p.data.copy_(s0)
+        opt = torch.optim.Adam(ref.parameters(), lr=0.01)
+        its = [iter(torch.utils.data.DataLoader(random_dataset(64, HID, seed=r), batch_size=2)) for r in range(2)]
+        for _ in range(4):
+            opt.zero_grad()
+            for it in its:
+                x, y = next(it)
+                with torch.autocast("cpu", dtype=torch.bfloat16):
+                    loss = ref(x, y)
+                (loss / 2).backward()
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+            opt.step()
+        for p, r in zip(model.parameters(), ref.parameters()):
+            assert torch.allclose(p.detach(), r.detach(), atol=2e-3), (p - r).abs().max()
+        with pytest.raises(AssertionError):
+            bad = dict(cfg, zero_optimization={"stage": 1}, fp16={"enabled": True})
+            deepspeed.initialize(args=args_from_dict(tmp_path, bad), model=SimpleModel(HID),
+                                 model_parameters=model.parameters())
+    run()
