@@ -519,3 +519,48 @@ def test_amp_block_runs_on_native_autocast_world2(tmp_path):
             deepspeed.initialize(args=args_from_dict(tmp_path, bad), model=SimpleModel(HID),
                                  model_parameters=model.parameters())
     run()
+
+
+def _scalar_tags(log_dir):
+    from tensorboard.backend.event_processing.event_accumulator import EventAccumulator
+    tags = set()
+    for root, _, files in os.walk(log_dir):
+        if any(f.startswith("events.out") for f in files):
+            acc = EventAccumulator(root)
+            acc.Reload()
+            tags.update(acc.Tags()["scalars"])
+    return tags
+
+
+def test_tensorboard_scalars_from_both_engines(tmp_path):
+    """`"tensorboard": {"enabled": true}`: rank 0 of the plain engine and of the PIPELINE engine write the reference's
+    scalar tags (Train/Samples/train_loss, lr, loss_scale; per-phase times with wall_clock_breakdown)."""
+    pytest.importorskip("tensorboard")
+
+    @distributed_test(world_size=2)
+    def run():
+        tb = lambda name: {"enabled": True, "output_path": str(tmp_path / name), "job_name": "job"}
+        cfg = _cfg(0, tensorboard=tb("plain"), wall_clock_breakdown=True)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        _train(engine, 2)
+        dist.barrier()
+        if dist.get_rank() == 0:
+            tags = _scalar_tags(str(tmp_path / "plain"))
+            assert {"Train/Samples/train_loss", "Train/Samples/lr"} <= tags, tags
+            assert any(t.startswith("Train/Samples/elapsed_time_ms_") for t in tags), tags
+        pcfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+                "optimizer": {"type": "Adam", "params": {"lr": 0.01}}, "tensorboard": tb("pipe")}
+        net = LinearStackPipe(HID, HID, HID, 2, num_stages=2)
+        pengine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, pcfg), model=net,
+                                                model_parameters=[p for p in net.parameters()])
+        ds = random_dataset(32, HID, seed=3)
+        it = iter(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(ds, batch_size=2)))
+        for _ in range(3):
+            pengine.train_batch(it)
+        dist.barrier()
+        if dist.get_rank() == 0:
+            tags = _scalar_tags(str(tmp_path / "pipe"))
+            assert "Train/Samples/train_loss" in tags and "Train/Samples/lr" in tags, tags
+    run()
