@@ -260,7 +260,10 @@ class FusedZeroStep:
         buckets = [(gi, k) for gi in range(len(o.arenas)) for k in range(o.num_buckets[gi])]
         for group in o.optimizer.param_groups:
             group["step"] = group.get("step", 0) + 1
-        # o._sumsq was cleared at the end of the previous step: reduce phases that ran under backward have added to it
+        # o._sumsq was cleared at the end of the previous step and reduce phases that ran under backward have added to
+        # it since; without any of those, clear it here as well (another code path may have used it in between)
+        if not self._early:
+            o._sumsq.zero_()
         todo = [b for b in buckets if b not in self._early]
         mp = o.mpu is not None and o.mpu.get_model_parallel_world_size() > 1
         if not mp:
