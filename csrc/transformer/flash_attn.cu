@@ -1046,7 +1046,7 @@ static int flash_fwd_impl(const void* q, const void* k, const void* v, void* out
         rc = make_map_bshd(&tv, bf, v, B, S, H, D, v_sb, v_ss, v_sh, K64);
         if (rc) return rc;
         return dsb::fa2::launch_fwd(tq, tk, tv, to, lse, B, S, H, scale_log2, causal, bf, sched, sched_hstride,
-                                    sched_pstride, kpm, make_dropout(dropout_p, dropout_seed), stream);
+                                    sched_pstride, kpm, make_dropout(dropout_p, dropout_seed), stream, D);
     }
     if (g_fa_fwd_variant != 128) {
         rc = make_map_bshd(&tk, bf, k, B, S, H, D, k_sb, k_ss, k_sh, K64);
@@ -1229,8 +1229,9 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
     if ((rc = make_map_bshd(&tdv, bf, dv, B, S, H, D, s_dv[0], s_dv[1], s_dv[2]))) return rc;
     EncodeTiledFn enc = get_encode();
     if (!enc) return -1;
-    // the accumulator always has 128 rows per head (rows >= D stay zero), whatever the head dim
-    cuuint64_t dims[4] = {(cuuint64_t)S, (cuuint64_t)HD, (cuuint64_t)H, (cuuint64_t)B};
+    // the accumulator always has 128 rows per head (see the strides), whatever the head dim; the map exposes only the
+    // first D of them, so the reduce-adds of the rows beyond (all zeros) are clipped instead of travelling to L2
+    cuuint64_t dims[4] = {(cuuint64_t)S, (cuuint64_t)D, (cuuint64_t)H, (cuuint64_t)B};
     cuuint64_t st[3] = {(cuuint64_t)S * 4, (cuuint64_t)HD * S * 4, (cuuint64_t)H * HD * S * 4};
     cuuint32_t box[4] = {32, 128, 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
@@ -1239,7 +1240,7 @@ static int flash_bwd2_impl(const void* dO, const void* q, const void* k, const v
     if (r != CUDA_SUCCESS) return -(int)r - 1000;
     rc = fa2::launch_bwd(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, B, S, H, scale, scale * 1.4426950408889634f, causal,
                          bf, rot_cos, rot_sin, rot_dim, sched, sched_hstride, sched_pstride, kpm,
-                         make_dropout(dropout_p, dropout_seed), stream);
+                         make_dropout(dropout_p, dropout_seed), stream, D);
     if (rc) return rc;
     return fa2::launch_dq_finish(dq_acc, dq, B, S, H, s_dq, bf, rot_cos, rot_sin, rot_dim, stream, D);
 }

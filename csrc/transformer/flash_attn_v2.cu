@@ -247,7 +247,7 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
                   float* __restrict__ lse, int S, int H, float scale_log2, int causal, int dbg, long long* prof,
                   const int* __restrict__ sched, int sched_hstride, int sched_pstride,
-                  const float* __restrict__ kpm, const Dropout drop) {
+                  const float* __restrict__ kpm, const Dropout drop, const int D) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sQ = smem + F_OFF_Q;
@@ -352,7 +352,10 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const int n = t ? nB : nA;
         constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
         const uint32_t idesc_s = make_idesc_f16(F_BQ, (dbg & 16) ? 128 : F_BK, is_bf16, 0, 0);
-        const uint32_t idesc_pv = make_idesc_f16(F_BQ, 128, is_bf16, 0, 1);
+        // head dims below 128: TMA zero-filled the columns beyond D, so the products skip them - S = Q K^T runs D / 16
+        // k-steps and O += P V is D columns wide (the accumulator columns beyond are never written nor stored)
+        const int ksteps = (D + 15) >> 4;
+        const uint32_t idesc_pv = make_idesc_f16(F_BQ, ksteps * 16, is_bf16, 0, 1);
         const uint32_t q_lo = desc_lo(sQ + t * F_QTILE, 16);
         const uint32_t t_sc = tmem_base + t * 128;
         const uint32_t t_acc = tmem_base + 256 + t * 128;
@@ -361,8 +364,9 @@ flash_fwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
             const uint32_t d = t_sc + (j & 1) * 64;
 #pragma unroll
             for (int k = 0; k < 8; ++k)
-                umma_ss_p(lead, d, q_lo + (k >> 2) * (F_QCHUNK >> 4) + (k & 3) * 2,
-                          k_lo + (k >> 2) * (F_KVCHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
+                if (k < ksteps)
+                    umma_ss_p(lead, d, q_lo + (k >> 2) * (F_QCHUNK >> 4) + (k & 3) * 2,
+                              k_lo + (k >> 2) * (F_KVCHUNK >> 4) + (k & 3) * 2, DESC_HI, idesc_s, k != 0);
             umma_commit_p(lead, &s_full[t * 2 + (j & 1)]);
             umma_commit_p(lead, &k_empty[j % F_NS]);
         };
@@ -700,7 +704,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                   const float* __restrict__ ndelta, int S, int H, float scale, float scale_log2, int causal, int dbg,
                   long long* prof, const float* __restrict__ rot_cs, const float* __restrict__ rot_sn, int rot,
                   const int* __restrict__ sched, int sched_hstride, int sched_pstride,
-                  const float* __restrict__ kpm, const Dropout drop) {
+                  const float* __restrict__ kpm, const Dropout drop, const int D) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sK = smem + B_OFF_K;
@@ -802,6 +806,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         const uint32_t lead = elect_one() ? 1u : 0u;
         constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
         const uint32_t id_st = make_idesc_f16(128, 64, is_bf16, 0, 0);    // K-major x K-major, N = 64 queries
+        const int ksteps = (D + 15) >> 4;    // head dims below 128: the zero-filled columns are skipped
         const uint32_t k_km = desc_lo(sK, 16), v_km = desc_lo(sV, 16);
         auto koff_a = [](int k) { return (uint32_t)((k >> 2) * (16384 >> 4) + (k & 3) * 2); };
         auto koff_b = [](int k) { return (uint32_t)((k >> 2) * (8192 >> 4) + (k & 3) * 2); };
@@ -819,7 +824,7 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 const uint32_t d = tmem_base + TM_ST + (n & 1) * 64;
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
-                    umma_ss_p(lead, d, k_km + koff_a(k), q_km + koff_b(k), DESC_HI, id_st, k != 0);
+                    if (k < ksteps) umma_ss_p(lead, d, k_km + koff_a(k), q_km + koff_b(k), DESC_HI, id_st, k != 0);
                 umma_commit_p(lead, &s_full[n & 1]);
             }
             FA2_TICK(2)
@@ -833,7 +838,8 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
                 const uint32_t do_km = desc_lo(sdO + (n % 3) * 16384, 16);
 #pragma unroll
                 for (int k = 0; k < 8; ++k)
-                    umma_ss_p(lead, tmem_base + TM_DPT, v_km + koff_a(k), do_km + koff_b(k), DESC_HI, id_st, k != 0);
+                    if (k < ksteps)
+                        umma_ss_p(lead, tmem_base + TM_DPT, v_km + koff_a(k), do_km + koff_b(k), DESC_HI, id_st, k != 0);
                 umma_commit_p(lead, dp_full);
             }
             FA2_TICK(5)
@@ -845,7 +851,8 @@ flash_bwd2_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant
         // (every softmax warp writes only over columns it has read itself); 16 queries = 8 columns per k-step.
         const uint32_t lead = elect_one() ? 1u : 0u;
         constexpr int is_bf16 = std::is_same<T, __nv_bfloat16>::value ? 1 : 0;
-        const uint32_t id_acc = make_idesc_f16(128, 128, is_bf16, 0, 1);  // A from TMEM, B MN-major, N = 128 (d)
+        // A from TMEM, B MN-major, N = head dim (rounded up to 16; the accumulator columns beyond are never stored)
+        const uint32_t id_acc = make_idesc_f16(128, ((D + 15) >> 4) * 16, is_bf16, 0, 1);
         const uint32_t id_dq = make_idesc_f16(128, 64, is_bf16, 1, 1);    // both MN-major, N = 64 queries
         const uint32_t k_mn = desc_lo(sK, 16384);
         const uint32_t ds_mn = desc_lo(sdS, 8192);
@@ -1134,7 +1141,7 @@ void set_debug_mode(int m) { g_dbg = m; }
 void set_debug_timers(long long* p) { g_prof = p; }
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
                int B, int S, int H, float scale_log2, int causal, int bf16, const int* sched, int sched_hstride,
-               int sched_pstride, const float* kpm, Dropout drop, cudaStream_t stream) {
+               int sched_pstride, const float* kpm, Dropout drop, cudaStream_t stream, int D) {
     if (S % 128) return DSB_ERR_SIZE;
     dim3 grid(B * H, (S + 255) / 256);
     cudaError_t e;
@@ -1143,13 +1150,13 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof, sched, sched_hstride,
-                                            sched_pstride, kpm, drop);
+                                            sched_pstride, kpm, drop, D);
     } else {
         auto kern = flash_fwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, F_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 384, F_SMEM, stream>>>(tq, tk, tv, to, lse, S, H, scale_log2, causal, g_dbg, g_prof, sched, sched_hstride,
-                                            sched_pstride, kpm, drop);
+                                            sched_pstride, kpm, drop, D);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
@@ -1187,7 +1194,7 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* nlse2,
                const float* ndelta, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
                const float* rot_cs, const float* rot_sn, int rot, const int* sched, int sched_hstride, int sched_pstride,
-               const float* kpm, Dropout drop, cudaStream_t stream) {
+               const float* kpm, Dropout drop, cudaStream_t stream, int D) {
     if (S % 128) return DSB_ERR_SIZE;
     if (rot < 0 || rot > 128 || (rot % 16)) return DSB_ERR_ARG;
     dim3 grid(B * H, S / 128);
@@ -1197,13 +1204,13 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm, drop);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm, drop, D);
     } else {
         auto kern = flash_bwd2_kernel<__half>;
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, B_SMEM);
         if (e != cudaSuccess) return -(int)e;
         kern<<<grid, 512, B_SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, tdq, nlse2, ndelta, S, H, scale, scale_log2,
-                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm, drop);
+                                            causal, g_dbg, g_prof, rot_cs, rot_sn, rot, sched, sched_hstride, sched_pstride, kpm, drop, D);
     }
     e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;

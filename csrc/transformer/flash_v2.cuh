@@ -24,7 +24,7 @@ struct Dropout {
 // [B, S] fp32, already multiplied by log2(e).
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& tv, const CUtensorMap& to, float* lse,
                int B, int S, int H, float scale_log2, int causal, int bf16, const int* sched, int sched_hstride,
-               int sched_pstride, const float* kpm, Dropout drop, cudaStream_t stream);
+               int sched_pstride, const float* kpm, Dropout drop, cudaStream_t stream, int D = 128);
 
 // lse2[bh, s] = lse * log2(e), delta_s[bh, s] = scale * sum_d dO * O  (both fp32, [B, H, S]).
 int launch_prep(const void* dO, const void* O, const float* lse, float* lse2, float* delta_s, int B, int S, int H,
@@ -36,7 +36,7 @@ int launch_bwd(const CUtensorMap& tq, const CUtensorMap& tk, const CUtensorMap& 
                const CUtensorMap& tdk, const CUtensorMap& tdv, const CUtensorMap& tdq, const float* lse2,
                const float* delta_s, int B, int S, int H, float scale, float scale_log2, int causal, int bf16,
                const float* rot_cs, const float* rot_sn, int rot, const int* sched, int sched_hstride, int sched_pstride,
-               const float* kpm, Dropout drop, cudaStream_t stream);
+               const float* kpm, Dropout drop, cudaStream_t stream, int D = 128);
 
 // dq (16 bit, [B, S, H, 128] with strides s_dq) = transpose of the fp32 accumulator [B, H, 128, S].
 // rot > 0: apply the inverse rotary embedding (tables [S, rot / 2] fp32) on the way, likewise for dK in launch_bwd.
