@@ -157,9 +157,95 @@ ln_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, const T* __res
     }
 }
 
+// ------------------------------------------------------------------------------------------- forward, one warp per row
+// For rows of 256 * VEC elements (VEC <= 16: up to 4096) a warp owns a whole row: lane l holds the 16-byte vectors
+// l, l + 32, ... (coalesced 512-byte requests), the two row statistics are warp shuffles, and no block barrier exists,
+// so the eight warps of a CTA stream independently. gamma / beta are staged
+// once per CTA in shared memory. The block-cooperative kernel above (two barriers per row group) reached 50 % (plain) /
+// 80 % (with residual) of the copy bandwidth on 8192 x 2048 (profiles/bench_ops_v4.json); this one removes the
+// barriers from the streaming loop.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(LN_THREADS, VEC <= 4 ? 4 : (VEC <= 8 ? 2 : 1))
+ln_fwd_warp_kernel(const T* __restrict__ x, const T* __restrict__ res, const T* __restrict__ gamma,
+                   const T* __restrict__ beta, T* __restrict__ y, T* __restrict__ sum_out, float* __restrict__ mean_out,
+                   float* __restrict__ rstd_out, long rows, float eps) {
+    constexpr int HIDDEN = 256 * VEC;
+    __shared__ uint4 sg[32 * VEC], sb[32 * VEC];
+    for (int i = threadIdx.x; i < 32 * VEC; i += LN_THREADS) {
+        sg[i] = __ldg(reinterpret_cast<const uint4*>(gamma) + i);
+        sb[i] = __ldg(reinterpret_cast<const uint4*>(beta) + i);
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const long warp_id = (long)blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+    const long nwarps = (long)gridDim.x * LN_WARPS;
+    const float inv_h = 1.f / HIDDEN;
+    uint4 cx[VEC], cr[VEC];
+    auto load_row = [&](uint4 (&dx)[VEC], uint4 (&dr)[VEC], long row) {
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            dx[i] = make_uint4(0, 0, 0, 0);
+            dr[i] = make_uint4(0, 0, 0, 0);
+            if (row < rows) {
+                dx[i] = ld_nc_v4(reinterpret_cast<const uint4*>(x + row * HIDDEN) + lane + 32 * i);
+                if (res != nullptr) dr[i] = ld_nc_v4(reinterpret_cast<const uint4*>(res + row * HIDDEN) + lane + 32 * i);
+            }
+        }
+    };
+    // no register prefetch of the next row: 24 - 32 resident warps per SM, each with its whole row in flight, already
+    // keep several hundred KB outstanding per SM
+    for (long row = warp_id; row < rows; row += nwarps) {
+        load_row(cx, cr, row);
+        float sum = 0.f;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            float v[8];
+            unpack8<T>(cx[i], v);
+            if (res != nullptr) {
+                float r8[8];
+                unpack8<T>(cr[i], r8);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] += r8[k];
+                cx[i] = pack8<T>(v);      // round through the storage dtype: backward sees exactly what is stored
+                if (sum_out != nullptr) reinterpret_cast<uint4*>(sum_out + row * HIDDEN)[lane + 32 * i] = cx[i];
+                unpack8<T>(cx[i], v);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; ++k) sum += v[k];
+        }
+        const float mu = warp_sum(sum) * inv_h;
+        float var = 0.f;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            float v[8];
+            unpack8<T>(cx[i], v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const float d = v[k] - mu;
+                var += d * d;
+            }
+        }
+        const float rstd = rsqrtf(warp_sum(var) * inv_h + eps);
+        if (lane == 0) {
+            if (mean_out != nullptr) mean_out[row] = mu;
+            if (rstd_out != nullptr) rstd_out[row] = rstd;
+        }
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            float v[8], g8[8], b8[8], o[8];
+            unpack8<T>(cx[i], v);
+            unpack8<T>(sg[lane + 32 * i], g8);
+            unpack8<T>(sb[lane + 32 * i], b8);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) o[k] = (v[k] - mu) * rstd * g8[k] + b8[k];
+            reinterpret_cast<uint4*>(y + row * HIDDEN)[lane + 32 * i] = pack8<T>(o);
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------- backward
 // dx = rstd * (dy*gamma - mean_h(dy*gamma) - xhat * mean_h(dy*gamma*xhat)) (+ dres); dgamma += dy*xhat; dbeta += dy.
-template <typename T, int ITERS, int R>
+template <typename T, int ITERS, int R, bool INV>
 __global__ void __launch_bounds__(LN_THREADS, ITERS == 1 ? 2 : 1)
 ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __restrict__ mean,
               const float* __restrict__ rstd, const T* __restrict__ gamma, const T* __restrict__ dres,
@@ -174,14 +260,15 @@ ln_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const float* __
     const long stride = (long)gridDim.x * R;
     float accg[ITERS][8], accb[ITERS][8];
     uint4 graw[ITERS], braw[ITERS];
-    const bool inv = beta_inv != nullptr;
+    constexpr bool inv = INV;      // compile-time: the common (non-invertible) path carries no beta registers / divisions
 #pragma unroll
     for (int it = 0; it < ITERS; ++it) {
         const int i = threadIdx.x + it * LN_THREADS;
 #pragma unroll
         for (int k = 0; k < 8; ++k) { accg[it][k] = 0.f; accb[it][k] = 0.f; }
         graw[it] = i < nvec ? __ldg(reinterpret_cast<const uint4*>(gamma) + i) : make_uint4(0, 0, 0, 0);
-        braw[it] = (inv && i < nvec) ? __ldg(reinterpret_cast<const uint4*>(beta_inv) + i) : make_uint4(0, 0, 0, 0);
+        braw[it] = make_uint4(0, 0, 0, 0);
+        if (inv && i < nvec) braw[it] = __ldg(reinterpret_cast<const uint4*>(beta_inv) + i);
     }
     uint4 cx[R][ITERS], cdy[R][ITERS], cdr[R][ITERS];
     float cmu[R], crs[R];
@@ -334,6 +421,23 @@ extern "C" int dsb_layernorm_fwd(const void* x, const void* residual, const void
     if (rows <= 0) return 0;
     if (hidden % 8 || hidden > LN_THREADS * 8 * LN_MAX_ITERS) return DSB_ERR_SIZE;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (hidden % 256 == 0 && hidden <= 4096 && (hidden / 256 == 1 || hidden / 256 == 2 || hidden / 256 == 3 ||
+                                                  hidden / 256 == 4 || hidden / 256 == 6 || hidden / 256 == 8 ||
+                                                  hidden / 256 == 16)) {
+        // one warp per row (no block barriers in the streaming loop)
+        const long want = (rows + LN_WARPS - 1) / LN_WARPS;
+        const unsigned g = (unsigned)(want < 148L * 4 ? want : 148L * 4);
+#define LNW(T, V) ln_fwd_warp_kernel<T, V><<<g, LN_THREADS, 0, s>>>((const T*)x, (const T*)residual, (const T*)gamma, (const T*)beta, (T*)y, (T*)sum_out, mean, rstd, rows, eps)
+#define LNW_D(T) do { switch (hidden / 256) { case 1: LNW(T, 1); break; case 2: LNW(T, 2); break; case 3: LNW(T, 3); break; \
+        case 4: LNW(T, 4); break; case 6: LNW(T, 6); break; case 8: LNW(T, 8); break; default: LNW(T, 16); break; } } while (0)
+        if (dtype == DSB_DTYPE_F16) LNW_D(__half);
+        else if (dtype == DSB_DTYPE_BF16) LNW_D(__nv_bfloat16);
+        else return DSB_ERR_DTYPE;
+#undef LNW_D
+#undef LNW
+        cudaError_t we = cudaGetLastError();
+        return we == cudaSuccess ? 0 : -(int)we;
+    }
     const int iters = ((hidden >> 3) + LN_THREADS - 1) / LN_THREADS;
     const int R = iters <= 1 ? 4 : (iters <= 2 ? 2 : 1);
     const long groups = (rows + R - 1) / R;
@@ -367,7 +471,8 @@ static int ln_bwd_impl(const void* dy, const void* x, const float* mean, const f
     const int grid = (int)(groups < cap ? groups : cap);
     float* pg = reinterpret_cast<float*>(scratch);
     float* pb = pg + (long)LN_BWD_BLOCKS * hidden;
-#define LNB(T, I, RR) ln_bwd_kernel<T, I, RR><<<grid, LN_THREADS, 0, s>>>((const T*)dy, (const T*)x, mean, rstd, (const T*)gamma, (const T*)dres, (T*)dx, pg, pb, rows, hidden, (const T*)beta_inv)
+#define LNB1(T, I, RR, V) ln_bwd_kernel<T, I, RR, V><<<grid, LN_THREADS, 0, s>>>((const T*)dy, (const T*)x, mean, rstd, (const T*)gamma, (const T*)dres, (T*)dx, pg, pb, rows, hidden, (const T*)beta_inv)
+#define LNB(T, I, RR) do { if (beta_inv != nullptr) LNB1(T, I, RR, true); else LNB1(T, I, RR, false); } while (0)
 #define LNB_D(T) do { if (iters <= 1) LNB(T, 1, 2); else if (iters <= 2) LNB(T, 2, 1); else LNB(T, 4, 1); \
         ln_bwd_finalize<T><<<(hidden + 31) / 32, 32 * FIN_SLICES, 0, s>>>(pg, pb, grid, hidden, (T*)dgamma, (T*)dbeta, accumulate); } while (0)
     if (dtype == DSB_DTYPE_F16) LNB_D(__half);
@@ -375,6 +480,7 @@ static int ln_bwd_impl(const void* dy, const void* x, const float* mean, const f
     else return DSB_ERR_DTYPE;
 #undef LNB_D
 #undef LNB
+#undef LNB1
     cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? 0 : -(int)e;
 }
