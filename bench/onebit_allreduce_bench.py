@@ -28,6 +28,8 @@ for name, fused in (("fused", True), ("nccl_restatement", False)):
             ts.append(t.item())
     ms = sorted(ts)[len(ts) // 2]
     res[name] = {"ms": round(ms, 3), "algo_GBps": round(n * 4 / ms / 1e6, 1)}
+    if fused:
+        res[name]["phase_ms_last_call"] = be.phase_times_ms()
 if rank == 0:
     res["speedup"] = round(res["nccl_restatement"]["ms"] / res["fused"]["ms"], 2)
     res["world"], res["numel"] = world, n

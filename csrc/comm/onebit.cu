@@ -57,6 +57,15 @@ DSB_DEVICE uint32_t pack_nibbles(uint32_t nib, int lane) {
 }
 DSB_DEVICE float sgn_sel(uint32_t bits, int t, float s) { return ((bits >> t) & 1u) ? s : -s; }
 
+// phase timestamps (ns) for benches: CTA 0 writes %globaltimer at the phase boundaries behind the partial sums
+DSB_DEVICE void ob_stamp(float* partials, int slot) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        reinterpret_cast<unsigned long long*>(partials + 1024)[slot] = t;
+    }
+}
+
 // Optional fusion with 1-bit Adam's compression stage (reference runtime/fp16/onebit/adam.py:200-260): with `g` the
 // momentum is formed on the way in (m <- beta1 * m + (1 - beta1) * g), with `p` the parameter update runs on the way
 // out (p <- p - lr * (m / (sqrt(v) + eps) + wd * p)) - the averaged momentum is decompressed straight into the update
@@ -91,6 +100,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     float4* es4 = reinterpret_cast<float4*>(e_s);
     const float4* g4 = reinterpret_cast<const float4*>(A.g);
 
+    ob_stamp(partials, 0);
     // ---- phase A: x = momentum + e_w (kept in e_w), partial sum of squares
     float acc = 0.f;
     for (long i = gtid; i < n4; i += gstride) {
@@ -112,6 +122,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     grid.sync();
     const float s_w = sqrtf(fold_partials(partials, gridDim.x, sh) / (float)n);
     grid.sync();   // partials are reused below
+    ob_stamp(partials, 1);
 
     // ---- phase B: worker error, sign packing, scatter chunk r to rank r (whole warps stay together: n % 32 == 0)
     for (long base = gtid - lane; base < n4; base += gstride) {
@@ -136,8 +147,10 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     if (blockIdx.x == 0 && threadIdx.x < W) P.recv_scales[threadIdx.x][me] = s_w;
     __threadfence_system();
     grid.sync();
+    ob_stamp(partials, 2);
     if (blockIdx.x == 0) ob_barrier(P, W, me, 0, epoch);
     grid.sync();
+    ob_stamp(partials, 3);
 
     // ---- phase C: server average of my chunk + server error feedback (y kept in e_s)
     const uint32_t* rs = P.recv_signs[me];
@@ -186,8 +199,10 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     if (blockIdx.x == 0 && threadIdx.x < W) P.gath_scales[threadIdx.x][me] = s_s;
     __threadfence_system();
     grid.sync();
+    ob_stamp(partials, 4);
     if (blockIdx.x == 0) ob_barrier(P, W, me, 1, epoch);
     grid.sync();
+    ob_stamp(partials, 5);
 
     // ---- phase E: decompress the averaged momentum into m (and, fused, apply the parameter update)
     const uint32_t* gs = P.gath_signs[me];
@@ -195,9 +210,9 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     __syncthreads();
     float4* p4 = reinterpret_cast<float4*>(A.p);
     const float4* v4 = reinterpret_cast<const float4*>(A.v);
-    for (long i = gtid; i < r4; i += gstride) {
+    // chunk by chunk (one scale per chunk: no 64-bit division per vector), two vectors in flight per thread
+    auto emit = [&](long i, float s0) {
         const uint32_t b0 = __ldcg(gs + (i >> 3)) >> ((int)(i & 7) * 4);
-        const float s0 = ssc[(int)(i / c4)];
         const float4 mm = make_float4(sgn_sel(b0, 0, s0), sgn_sel(b0, 1, s0), sgn_sel(b0, 2, s0), sgn_sel(b0, 3, s0));
         m4[i] = mm;
         if (p4 != nullptr) {
@@ -209,7 +224,19 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
             p.w -= A.lr * (mm.w / (sqrtf(v.w) + A.eps) + A.wd * p.w);
             p4[i] = p;
         }
+    };
+    for (int k = 0; k < W; ++k) {
+        const float s0 = ssc[k];
+        const long base = (long)k * c4;
+        const long stop = base + c4 < r4 ? base + c4 : r4;      // m may be shorter than the padded error buffers
+        long i = base + gtid;
+        for (; i + gstride < stop; i += 2 * gstride) {
+            emit(i, s0);
+            emit(i + gstride, s0);
+        }
+        if (i < stop) emit(i, s0);
     }
+    ob_stamp(partials, 6);
 }
 
 }  // namespace dsb

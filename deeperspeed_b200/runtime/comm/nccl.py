@@ -84,6 +84,14 @@ class NcclBackend:
         K._count()
         return buffer_m
 
+    def phase_times_ms(self):
+        """Phase durations of the last fused launch from its in-kernel timestamps: A (compensate + norm), B (quantise +
+        scatter), wait for the peers, C + D (server average, requantise, broadcast), wait, E (decompress / update)."""
+        torch.cuda.synchronize()
+        t = self._scratch[1024:1024 + 14].view(torch.int64).tolist()
+        names = ["A_norm", "B_pack_scatter", "barrier_1", "CD_server", "barrier_2", "E_unpack"]
+        return {n: round((t[i + 1] - t[i]) / 1e6, 4) for i, n in enumerate(names)}
+
     def fused_adam_supported(self, momentum, worker_error):
         """Can `compressed_adam_step` run for this momentum tensor (fp32 on a GPU, length a multiple of 4, error buffers
         padded to whole sign words per server chunk)?"""
