@@ -91,6 +91,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     __shared__ float ssc[OB_MAX_RANKS];
     const long c = n / W;
     const long cwords = c >> 5;
+    const bool vec4 = (cwords & 3) == 0;      // four consecutive sign words never straddle two servers' chunks
     const long n4 = n >> 2, c4 = c >> 2, r4 = n_real >> 2;
     const long gtid = (long)blockIdx.x * blockDim.x + threadIdx.x;
     const long gstride = (long)gridDim.x * blockDim.x;
@@ -124,13 +125,11 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     grid.sync();   // partials are reused below
     ob_stamp(partials, 1);
 
-    // ---- phase B: worker error, sign packing, scatter chunk r to rank r (whole warps stay together: n % 32 == 0)
-    for (long base = gtid - lane; base < n4; base += gstride) {
-        const long i = base + lane;
-        const bool valid = i < n4;
+    // ---- phase B: worker error, sign packing, scatter chunk r to rank r (whole warps stay together: n % 32 == 0).
+    // Two vectors per thread and trip, both loads issued before anything is stored (the loop is latency-bound otherwise).
+    auto quantise_w = [&](long i, bool valid, const float4& x) {
         uint32_t nib = 0;
         if (valid) {
-            const float4 x = ew4[i];
             nib = (x.x >= 0.f ? 1u : 0u) | (x.y >= 0.f ? 2u : 0u) | (x.z >= 0.f ? 4u : 0u) | (x.w >= 0.f ? 8u : 0u);
             float4 e;
             e.x = x.x - sgn_sel(nib, 0, s_w); e.y = x.y - sgn_sel(nib, 1, s_w);
@@ -138,11 +137,21 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
             ew4[i] = e;
         }
         const uint32_t word = pack_nibbles(nib, lane);
+        // (per-word stores here: gathering the four words into one 16-byte store measured slower in this phase)
         if (valid && (lane & 7) == 0) {
             const long w = i >> 3;
             const int dst = (int)(w / cwords);
             P.recv_signs[dst][(long)me * cwords + (w - (long)dst * cwords)] = word;
         }
+    };
+    for (long base = gtid - lane; base < n4; base += 2 * gstride) {
+        const long i0 = base + lane, i1 = i0 + gstride;
+        const bool v0 = i0 < n4, v1 = i1 < n4;
+        const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 x0 = v0 ? ew4[i0] : zero4;
+        const float4 x1 = v1 ? ew4[i1] : zero4;
+        quantise_w(i0, v0, x0);
+        quantise_w(i1, v1, x1);
     }
     if (blockIdx.x == 0 && threadIdx.x < W) P.recv_scales[threadIdx.x][me] = s_w;
     __threadfence_system();
@@ -158,7 +167,7 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
     __syncthreads();
     const float inv_w = 1.f / (float)W;
     acc = 0.f;
-    for (long j = gtid; j < c4; j += gstride) {
+    auto average = [&](long j, const float4& e) {
         float4 y = make_float4(0.f, 0.f, 0.f, 0.f);
         const int sh4 = (int)(j & 7) * 4;
         for (int w = 0; w < W; ++w) {
@@ -167,23 +176,28 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
             y.x += sgn_sel(bits, 0, s); y.y += sgn_sel(bits, 1, s);
             y.z += sgn_sel(bits, 2, s); y.w += sgn_sel(bits, 3, s);
         }
-        const float4 e = es4[j];
         y.x = y.x * inv_w + e.x; y.y = y.y * inv_w + e.y; y.z = y.z * inv_w + e.z; y.w = y.w * inv_w + e.w;
         es4[j] = y;
         acc += y.x * y.x + y.y * y.y + y.z * y.z + y.w * y.w;
+    };
+    {
+        long j = gtid;
+        for (; j + gstride < c4; j += 2 * gstride) {
+            const float4 e0 = es4[j], e1 = es4[j + gstride];
+            average(j, e0);
+            average(j + gstride, e1);
+        }
+        if (j < c4) average(j, es4[j]);
     }
     acc = block_sum(acc, sh);
     if (threadIdx.x == 0) partials[blockIdx.x] = acc;
     grid.sync();
     const float s_s = sqrtf(fold_partials(partials, gridDim.x, sh) / (float)c);
 
-    // ---- phase D: server error, pack, broadcast my chunk's signs + scale to every rank
-    for (long base = gtid - lane; base < c4; base += gstride) {
-        const long j = base + lane;
-        const bool valid = j < c4;
+    // ---- phase D: server error, pack, broadcast my chunk's signs + scale to every rank (two vectors per trip)
+    auto quantise_s = [&](long j, bool valid, const float4& y, long jw, bool valid_warp) {
         uint32_t nib = 0;
         if (valid) {
-            const float4 y = es4[j];
             nib = (y.x >= 0.f ? 1u : 0u) | (y.y >= 0.f ? 2u : 0u) | (y.z >= 0.f ? 4u : 0u) | (y.w >= 0.f ? 8u : 0u);
             float4 e;
             e.x = y.x - sgn_sel(nib, 0, s_s); e.y = y.y - sgn_sel(nib, 1, s_s);
@@ -191,10 +205,29 @@ __global__ void __launch_bounds__(512) onebit_allreduce_kernel(float* __restrict
             es4[j] = e;
         }
         const uint32_t word = pack_nibbles(nib, lane);
-        if (valid && (lane & 7) == 0) {
+        if (vec4) {
+            uint4 wv;
+            wv.x = __shfl_sync(0xffffffffu, word, 0);
+            wv.y = __shfl_sync(0xffffffffu, word, 8);
+            wv.z = __shfl_sync(0xffffffffu, word, 16);
+            wv.w = __shfl_sync(0xffffffffu, word, 24);
+            if (lane < W && valid_warp) {      // one lane per destination rank
+                const long w = (long)me * cwords + (jw >> 3);
+                *reinterpret_cast<uint4*>(P.gath_signs[(me + lane) % W] + w) = wv;
+            }
+        } else if (valid && (lane & 7) == 0) {
             const long w = (long)me * cwords + (j >> 3);
             for (int r = 0; r < W; ++r) P.gath_signs[(me + r) % W][w] = word;
         }
+    };
+    for (long base = gtid - lane; base < c4; base += 2 * gstride) {
+        const long j0 = base + lane, j1 = j0 + gstride;
+        const bool v0 = j0 < c4, v1 = j1 < c4;
+        const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const float4 y0 = v0 ? es4[j0] : zero4;
+        const float4 y1 = v1 ? es4[j1] : zero4;
+        quantise_s(j0, v0, y0, base, base < c4);
+        quantise_s(j1, v1, y1, base + gstride, base + gstride < c4);
     }
     if (blockIdx.x == 0 && threadIdx.x < W) P.gath_scales[threadIdx.x][me] = s_s;
     __threadfence_system();
