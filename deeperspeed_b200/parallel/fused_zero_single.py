@@ -75,3 +75,21 @@ class SingleRankFusedZero:
                                            betas[1], eps, wd, max_coeff, min_coeff, 0, 1, step, N.ptr(self.inv),
                                            N.ptr(self.skip), N.ptr(self.coeff), self._next(), N.stream_ptr()),
                 "dsb_fused_lamb_ag")
+
+    def whole_step(self, lr, betas, eps, wd, adamw, step, loss_scale=1.0, clip=0.0, phases=7):
+        """The one-kernel step (csrc/comm/fused_zero_step.cu) with this GPU as its only peer: reduce (here: average of
+        one copy) + norm, in-kernel scalar exchange -> unscale / clip factor + skip flag, Adam + cast + gather + clearing
+        of the gradient bucket. Returns the device tensor [norm, overflow] the kernel wrote for the host."""
+        if not hasattr(self, "sumsq2"):
+            self.sumsq2 = torch.zeros(2, dtype=torch.float32, device=self.dev)
+            self.host_out = torch.zeros(2, dtype=torch.float32, device=self.dev)
+            self.red16 = torch.empty(self.n, dtype=self.dtype, device=self.dev)
+        self.sumsq2.zero_()
+        N.check(self.lib.dsb_fused_zero_step(
+            self._arr(self.grad), self._arr(self.param), self._arr(self.flags), None, None, 1, 0, int(phases), 1, 0, 0,
+            self.n, self.n, N.dtype_code(self.dtype), N.ptr(self.red16), N.ptr(self.master), N.ptr(self.m),
+            N.ptr(self.v), float(lr), float(betas[0]), float(betas[1]), float(eps), float(wd), int(adamw), 1, int(step),
+            float(loss_scale), float(clip), N.ptr(self.sumsq2), N.ptr(self.inv), N.ptr(self.skip), N.ptr(self.host_out),
+            N.ptr(self.scratch), self._next(), N.stream_ptr()), "dsb_fused_zero_step")
+        return self.host_out
+

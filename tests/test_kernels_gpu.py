@@ -676,3 +676,43 @@ def test_embedding_gather_and_scatter_add(dtype):
     assert (table.grad.float() - 2 * base.float()).abs().max().item() < (4e-2 if dtype == torch.float16 else 2e-1)
     # untouched rows stay exactly zero
     assert float(table.grad[50:].abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_fused_zero_one_kernel_step_single_rank(dtype):
+    """dsb_fused_zero_step with R = 1 (this GPU is its own peer): reduce + norm, in-kernel exchange (unscale / clip
+    factor, overflow skip), AdamW on the fp32 master, cast + bulk-copy gather, clearing of the gradient bucket - against
+    plain fp32 PyTorch. The multi-GPU behaviour is in tests/test_fused_zero_gpu.py / test_xgpu_protocol_gpu.py."""
+    from deeperspeed_b200.parallel.fused_zero_single import SingleRankFusedZero
+    torch.manual_seed(1)
+    n = 8 * (512 * 37 + 5)              # not a multiple of the 512-vector CTA tile: ragged tails in both phases
+    z = SingleRankFusedZero(n, dtype=dtype)
+    lr, betas, eps, wd, scale, clip = 1e-2, (0.9, 0.95), 1e-8, 0.01, 64.0, 0.5
+    w = torch.randn(n, device="cuda") * 0.5
+    z.master.copy_(w)
+    m, v = torch.zeros_like(w), torch.zeros_like(w)
+    for step in (1, 2, 3):
+        g16 = (torch.randn(n, device="cuda") * 0.05 * scale).to(dtype)
+        z.grad.copy_(g16)
+        out = z.whole_step(lr, betas, eps, wd, True, step, loss_scale=scale, clip=clip)
+        g = g16.float()
+        norm = g.norm()
+        combined = scale * max(1.0, (float(norm) / scale + 1e-6) / clip)
+        gu = g / combined
+        m = betas[0] * m + (1 - betas[0]) * gu
+        v = betas[1] * v + (1 - betas[1]) * gu * gu
+        w = w - lr * ((m / (1 - betas[0] ** step)) / ((v / (1 - betas[1] ** step)).sqrt() + eps) + wd * w)
+        torch.cuda.synchronize()
+        assert abs(out[0].item() - float(norm)) < 1e-3 * float(norm) and out[1].item() == 0.0
+        torch.testing.assert_close(z.master, w, rtol=2e-5, atol=2e-6)
+        torch.testing.assert_close(z.param.float(), w.to(dtype).float(), rtol=0, atol=1e-2)
+        assert float(z.grad.float().abs().max()) == 0.0          # the kernel cleared the gradient bucket
+    # overflow: nothing is updated, the flag reaches the host slot, the gradients are still cleared
+    z.grad.copy_((torch.randn(n, device="cuda") * 0.05).to(dtype))
+    z.grad[11] = float("inf")
+    before = z.master.clone()
+    out = z.whole_step(lr, betas, eps, wd, True, 4, loss_scale=scale, clip=clip)
+    torch.cuda.synchronize()
+    assert out[1].item() == 1.0 and torch.equal(before, z.master) and float(z.grad.float().abs().max()) == 0.0
+
