@@ -391,3 +391,15 @@ class _TransposeFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         return K.transpose_0213(dy.contiguous())
+
+
+class DeepSpeedTransformerFunction:
+    """The reference drives its layer through an autograd Function of this name whose `apply` takes the input, the
+    mask, the layer, the gradient-capture list, the layer id and then every weight (ops/transformer/transformer.py:
+    150-420 there). Here the layer's forward is ordinary differentiable code over our kernels' own autograd
+    functions, so this is only the call surface: `apply` forwards to the layer."""
+
+    @staticmethod
+    def apply(input, input_mask, self, grads=None, layer_id=None, *weights_and_config):
+        return self(input, input_mask, grads=grads)
+

@@ -27,3 +27,39 @@ def compressed_all_reduce(tensor, group=None, op=dist.ReduceOp.SUM, async_op=Fal
     out = tensor_ldexp(mant.float(), exp.to(torch.int32)).to(original_dtype)
     tensor.data.copy_(out)
     return tensor
+
+
+# ---- the reference module's own entry points (its cupy variant needs no cupy here: torch.frexp / ldexp run on the GPU)
+def decompose(t):
+    """fp32 value -> (fp16 mantissa in [0.5, 1), int8 exponent)."""
+    mant, exp = tensor_frexp(t)
+    return mant.half(), exp.to(torch.int8)
+
+
+def reconstruct(mantissa, exponent, original_dtype=torch.bfloat16):
+    return tensor_ldexp(mantissa.float(), exponent.to(torch.int32)).to(original_dtype)
+
+
+def compressed_all_reduce_torch(tensor, op=dist.ReduceOp.SUM, group=None, async_op=False):
+    """Returns a new tensor (the reference's behaviour); `compressed_all_reduce` above also writes it back in place."""
+    mant, exp = decompose(tensor)
+    handles = [dist.all_reduce(mant, op=op, group=group, async_op=async_op),
+               dist.all_reduce(exp, op=op, group=group, async_op=async_op)]
+    if async_op:
+        for h in handles:
+            h.wait()
+    return reconstruct(mant, exp, tensor.dtype)
+
+
+compressed_all_reduce_cupy = compressed_all_reduce_torch
+decompose_cupy = decompose
+
+
+def torch2cupy(tensor):
+    """No cupy in this framework: tensors stay torch tensors (see runtime/compression/cupy.py)."""
+    return tensor
+
+
+def cupy2torch(cupy_tensor):
+    return cupy_tensor
+

@@ -32,3 +32,46 @@ def pipeline_visualizer(num_stages, num_micro_batches, schedule_cls=schedule.Tra
     total = sum(len(r) for r in rows)
     print_fn(f"bubble fraction: {1 - busy / total:.3f}")
     return rows
+
+
+# short labels of the reference's table (runtime/pipe/pipe_visualizer.py:33-44)
+reprs = {schedule.ForwardPass: "fwd", schedule.BackwardPass: "bwd", schedule.RecvActivation: "recv_act",
+         schedule.SendActivation: "send_act", schedule.RecvGrad: "recv_grad", schedule.SendGrad: "send_grad",
+         schedule.LoadMicroBatch: "load_batch", schedule.ReduceGrads: "reduce_grads",
+         schedule.ReduceTiedGrads: "reduce_tied_grads", schedule.OptimizerStep: "step"}
+
+
+def expand(steps, include_all=False):
+    """Instruction lists of one stage -> one label per step ("fwd_3 / send_act_3", None for an idle step). Without
+    `include_all` only forward / backward passes are shown. Buffer ids are printed 1-based, as in the reference."""
+    shown = tuple(reprs) if include_all else (schedule.ForwardPass, schedule.BackwardPass)
+    out = []
+    for cmds in steps:
+        labels = []
+        for cmd in cmds or ():
+            if isinstance(cmd, shown):
+                label = reprs[type(cmd)]
+                if hasattr(cmd, "buffer_id"):
+                    label += f"_{cmd.buffer_id + 1}"
+                labels.append(label)
+        out.append(" / ".join(labels) if labels else None)
+    return out
+
+
+def pipeline_table(num_stages, num_microbatches, include_all=False):
+    """Markdown table of the 1F1B schedule (one row per stage) followed by the idle / busy step counts: the string the
+    reference's `pipeline_visualizer` returns, built without pytablewriter."""
+    rows = [expand(list(schedule.TrainSchedule(micro_batches=num_microbatches, stages=num_stages, stage_id=s).steps()),
+                   include_all) for s in range(num_stages)]
+    steps = max(len(r) for r in rows)
+    header = ["GPU ID"] + [str(i) for i in range(steps)]
+    lines = ["# Pipe Schedule", "", "|" + "|".join(header) + "|", "|" + "|".join("---" for _ in header) + "|"]
+    for s, row in enumerate(rows):
+        cells = [f"GPU {s}"] + [c or "" for c in row + [None] * (steps - len(row))]
+        lines.append("|" + "|".join(cells) + "|")
+    idle = sum(c is None for r in rows for c in r)
+    busy = sum(c is not None for r in rows for c in r)
+    lines += ["", f"Num Devices: {num_stages}", f"Num Microbatches: {num_microbatches} ", f"Idle Time: {idle}",
+              f"Non Idle Time: {busy}"]
+    return "\n".join(lines)
+

@@ -71,6 +71,29 @@ def _take_params(flat, param_shapes, state_dict, aligned):
     return off
 
 
+_FP32_KEY = {1: "local_sub_partitions_of_fp32_groups", 2: "single_partition_of_fp32_groups", 3: "fp32_flat_groups"}
+
+
+def parse_optim_states(files):
+    """(zero stage, world size, param shapes, this checkpoint's fp32 groups per rank) from the per-rank optimizer
+    files (reference utils/zero_to_fp32.py:36-60; stage 1 is understood here as well)."""
+    sds = [_load(f) for f in files]
+    first = sds[0]["optimizer_state_dict"]
+    if "zero_stage" not in first:
+        raise ValueError("non zero checkpoint")
+    stage = first["zero_stage"]
+    if stage not in _FP32_KEY:
+        raise ValueError(f"unknown zero stage {stage}")
+    groups = [sd["optimizer_state_dict"][_FP32_KEY[stage]] for sd in sds]
+    return stage, first["partition_count"], sds[0]["param_shapes"], groups
+
+
+def zero3_partitioned_param_info(unpartitioned_numel, world_size):
+    """(elements of a parameter's shard when the parameter divides evenly, padding of the last shard otherwise)."""
+    remainder = unpartitioned_numel % world_size
+    return unpartitioned_numel // world_size, (world_size - remainder) if remainder else 0
+
+
 def convert_zero_chkpt_to_fp32_consolid_state_dict(checkpoint_dir, output_file=None):
     files = get_optim_files(checkpoint_dir)
     sds = [_load(f) for f in files]

@@ -325,3 +325,25 @@ def test_deepspeed_cli_single_node_end_to_end(tmp_path):
                         str(script), "--steps", "3"], env=env, cwd=str(tmp_path), capture_output=True, timeout=300)
     assert r.returncode == 0, r.stderr.decode()[-3000:]
     assert (tmp_path / "done0").exists() and (tmp_path / "done1").exists()
+
+
+def test_reference_helper_names_behave():
+    """Small public helpers the reference exposes: the 24-bit all-reduce's decompose / reconstruct, the pipeline
+    visualiser's `expand` and table, zero_to_fp32's shard arithmetic."""
+    from deeperspeed_b200.runtime.comm import compressed_ar as car
+    from deeperspeed_b200.runtime.pipe import pipe_visualizer as pv, schedule
+    from deeperspeed_b200.utils.zero_to_fp32 import zero3_partitioned_param_info
+    x = torch.tensor([0.75, -3.0, 1e-3, 120.0])
+    mant, exp = car.decompose(x)
+    assert mant.dtype == torch.float16 and exp.dtype == torch.int8
+    assert torch.allclose(car.reconstruct(mant, exp, torch.float32), x, rtol=1e-3)
+    assert car.torch2cupy(x) is x and car.compressed_all_reduce_cupy is car.compressed_all_reduce_torch
+    steps = list(schedule.TrainSchedule(micro_batches=4, stages=2, stage_id=0).steps())
+    labels = pv.expand(steps)
+    assert labels[0] == "fwd_1" and sum(l is not None for l in labels) == 8          # 4 forward + 4 backward passes
+    assert any(l and l.startswith("bwd_") for l in labels)
+    full = pv.expand(steps, include_all=True)
+    assert "load_batch_1" in full[0] and full[-1].endswith("step")
+    table = pv.pipeline_table(2, 4)
+    assert "GPU 1" in table and "Num Microbatches: 4" in table and "Non Idle Time: 16" in table
+    assert zero3_partitioned_param_info(10, 4) == (2, 2) and zero3_partitioned_param_info(8, 4) == (2, 0)
