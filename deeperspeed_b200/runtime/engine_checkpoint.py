@@ -23,7 +23,7 @@ from ..utils.logging import logger, log_dist
 
 # keys of the model-states file that belong to the engine; everything else is the caller's `client_state`
 _ENGINE_KEYS = ("module", "optimizer", "lr_scheduler", "csr_tensor_module_names", "skipped_steps", "global_steps",
-                "dp_world_size", "mp_world_size")
+                "dp_world_size", "mp_world_size", "amp")
 
 
 def _torch_load(path, map_location=None):
@@ -125,6 +125,8 @@ class CheckpointMixin:
         if with_scheduler and self.lr_scheduler is not None and ckpt.get("lr_scheduler") is not None:
             self.lr_scheduler.load_state_dict(ckpt["lr_scheduler"])
 
+        if getattr(self, "amp", None) is not None:
+            self.amp.load_state_dict(ckpt.get("amp"))      # the GradScaler's scale and growth tracker
         self.csr_tensor_module_names = ckpt["csr_tensor_module_names"]
         self.global_steps = ckpt["global_steps"]
         self.global_samples = ckpt.get("global_samples", self.global_steps * self.train_batch_size())
@@ -211,6 +213,8 @@ class CheckpointMixin:
             "dp_world_size": self.dp_world_size,
             "mp_world_size": self.mp_world_size,
         }
+        if getattr(self, "amp", None) is not None:
+            state["amp"] = self.amp.state_dict()
         state.update(client_state)
         log_dist(message=f"Saving model checkpoint: {path}", ranks=[0])
         torch.save(state, path)
