@@ -1,3 +1,7 @@
+// This file holds (1) the C entry points of ALL flash-attention kernels (tensor maps, argument checks, variant
+// dispatch; the default kernels are the second generation in flash_attn_v2.cu) and (2) the FIRST-generation kernels,
+// kept selectable for comparison (dsb_flash_attn_fwd_variant 64 / 128, dsb_flash_attn_bwd_variant 1):
+//
 // Causal / full flash-attention forward on tcgen05 (head dim 128, fp16 / bf16), one CTA per 128 query rows of one
 // (batch, head).
 //

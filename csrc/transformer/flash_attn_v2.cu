@@ -27,6 +27,12 @@
 //     warps 4-11 : P^T / dS^T (lane = key row, each warp half of the 64 query columns)
 //     warps 12-15: dQ^T drain: TMEM -> fp32 tiles in shared memory -> TMA reduce-add into a TRANSPOSED accumulator
 //                  ([B, H, D, S]; flash_dq_finish_kernel transposes and casts it afterwards)
+// Arguments of both directions beyond plain causal / full attention:
+//   * `sched`: block-sparse schedules (lists of live key tiles / query blocks with 16 x 16 visibility words);
+//   * `kpm`: additive key mask in log2 units; `drop`: attention dropout from a hash of (seed, b, h, query, key), the
+//     same bits in forward and backward, no mask tensor;
+//   * `D`: head dims below 128 - the tensor maps carry the true D (TMA zero-fills / clips the rest) and the products
+//     skip the zero columns (D / 16 k-steps, D-wide accumulators, dQ reduce-adds clipped to D rows).
 // Reference for the math: csrc/transformer/ds_transformer_cuda.cpp:186-214 and :340-420 (score, softmax, context and
 // their gradients as separate strided-batch GEMMs and softmax kernels).
 #include "../common/ptx.cuh"

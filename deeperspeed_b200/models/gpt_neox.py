@@ -2,9 +2,9 @@
 reference deepspeed/runtime/pipe/engine.py:185, pipe/module.py:585-587 — so the flagship model lives here).
 
 Layer math on the sm_100a kernel stack: fused LayerNorm(+residual) kernels, tcgen05 GEMMs with bias / bias+GeLU /
-bias+residual epilogues, in-place rotary kernel, fused cross-entropy (in-place gradient). Causal attention uses
-the attention block op of ops/attention.py (library flash kernel by default, our tcgen05 flash-attention kernels with
-DSB_ATTN=native). 1.3B preset: 24 layers, d_model 2048, 16 heads, seq 2048, vocab 50432."""
+bias+residual epilogues, rotary kernel, our embedding gather / scatter-add, fused cross-entropy (in-place gradient).
+Causal attention is the attention block op of ops/attention.py: our tcgen05 flash-attention kernels (the library
+kernel only with DSB_ATTN=sdpa, for comparison). 1.3B preset: 24 layers, d_model 2048, 16 heads, seq 2048, vocab 50432."""
 import math
 
 import torch
