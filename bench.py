@@ -361,6 +361,10 @@ def main():
                          "on a power-capped B200 the trimmed bubble is paid back in clocks, profiles/README.md)")
     ap.add_argument("--local_rank", type=int, default=0)
     args = ap.parse_args()
+    if args.tiny and os.environ.get("DSB_BENCH_TINY_SEQ"):
+        # CPU plumbing runs only (tests/test_bench_contract_cpu.py): a shorter sequence for the tiny model
+        global SEQ
+        SEQ = int(os.environ["DSB_BENCH_TINY_SEQ"])
     if args.impl == "reference":
         run_reference(args)
     else:
