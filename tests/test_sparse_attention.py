@@ -394,3 +394,30 @@ def test_fused_rows_that_see_nothing_in_their_first_tile():
     assert torch.isfinite(out).all() and (out.float() - ref).abs().max() < 3e-3
     for a, b in zip(grads, refg):
         assert (a.float() - b).abs().max() < 2e-2 * max(1.0, b.abs().max().item())
+
+
+def test_permute_keys_gradient_and_dropout_mask_restatement_cpu():
+    """CPU checks of the fused path's Python helpers: the key permutation's backward is the inverse gather, and the
+    restated dropout hash is deterministic, seed-dependent and keeps the requested fraction."""
+    from deeperspeed_b200.ops.sparse_attention import fused
+    torch.manual_seed(0)
+    x = torch.randn(2, 3, 8, 4, requires_grad=True)
+    order = torch.randperm(8)
+    inverse = torch.empty_like(order)
+    inverse[order] = torch.arange(8)
+    y = fused.PermuteKeysFn.apply(x, order, inverse)
+    assert torch.equal(y, x[:, :, order])
+    w = torch.randn_like(y)
+    (y * w).sum().backward()
+    expect = torch.zeros_like(x)
+    expect[:, :, order] = w
+    assert torch.equal(x.grad, expect)
+    keep, inv_keep = fused.dropout_keep_mask(2, 3, 256, 0.25, seed=7)
+    again, _ = fused.dropout_keep_mask(2, 3, 256, 0.25, seed=7)
+    other, _ = fused.dropout_keep_mask(2, 3, 256, 0.25, seed=8)
+    assert torch.equal(keep, again) and not torch.equal(keep, other)
+    assert abs(keep.float().mean().item() - 0.75) < 0.01 and abs(inv_keep - 1 / 0.75) < 1e-3
+    # heads and batches get different masks
+    assert not torch.equal(keep[0, 0], keep[0, 1]) and not torch.equal(keep[0, 0], keep[1, 0])
+    none, one = fused.dropout_keep_mask(1, 1, 64, 0.0, seed=1)
+    assert bool(none.all()) and one == 1.0
