@@ -562,23 +562,25 @@ class EmbeddingFn(torch.autograd.Function):
                 "dsb_embedding_fwd")
         _count()
         ctx.save_for_backward(ids_c)
-        ctx.table = table
+        # the table's shape is remembered, not re-read in backward: under ZeRO-3 the parameter may be back to its
+        # partitioned placeholder by then (its gradient is then returned whole and the ZeRO hooks scatter it)
+        ctx.table, ctx.table_shape = table, tuple(table.shape)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         (ids,) = ctx.saved_tensors
-        table = ctx.table
-        g = table.grad
+        vocab, dim = ctx.table_shape
+        g = ctx.table.grad
         into_arena = (ACCUMULATE_INTO_GRAD and g is not None and g.dtype == dout.dtype and g.is_contiguous()
-                      and g.shape == table.shape)
+                      and tuple(g.shape) == (vocab, dim))
         if not into_arena:
-            g = torch.zeros_like(table)
-        d2 = dout.reshape(-1, table.shape[1])
+            g = torch.zeros(vocab, dim, dtype=dout.dtype, device=dout.device)
+        d2 = dout.reshape(-1, dim)
         if not d2.is_contiguous():
             d2 = d2.contiguous()
-        N.check(N.cuda_lib().dsb_embedding_bwd_acc(N.ptr(d2), N.ptr(ids), N.ptr(g), ids.numel(), table.shape[1],
-                                                   table.shape[0], N.dtype_code(table.dtype), N.stream_ptr()),
+        N.check(N.cuda_lib().dsb_embedding_bwd_acc(N.ptr(d2), N.ptr(ids), N.ptr(g), ids.numel(), dim, vocab,
+                                                   N.dtype_code(dout.dtype), N.stream_ptr()),
                 "dsb_embedding_bwd_acc")
         _count()
         return None, (None if into_arena else g)
