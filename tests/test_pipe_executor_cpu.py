@@ -108,3 +108,45 @@ def test_compute_partitioning_ignores_lookup_tables(tmp_path):
         first, last = by_compute.parts[1] - 1, 6 - (by_compute.parts[1] - 1)
         assert first > last
     run()
+
+
+def test_comm_stub_skips_transfers_without_desynchronising(tmp_path):
+    """utils/comm_stub (the bench's exposed-communication measurement): with the stub on, a pipeline step runs to the
+    end without any activation / gradient transfer and without the ZeRO collectives; switching it off again leaves the
+    ranks in step (same number of steps everywhere), and training goes on."""
+    @distributed_test(world_size=2)
+    def run():
+        from deeperspeed_b200.utils import comm_stub
+        from deeperspeed_b200.runtime.pipe import p2p
+        cfg = {"train_batch_size": 16, "train_micro_batch_size_per_gpu": 4, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.01}}, "fp16": {"enabled": True, "type": "fp32"},
+               "zero_optimization": {"stage": 1}}
+        torch.manual_seed(3)
+        pipe = LinearStackPipe(HID, HID, HID, 4, topology=PipeDataParallelTopology(num_pp=2, num_dp=1),
+                               partition_method="uniform")
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=pipe,
+                                               model_parameters=[p for p in pipe.parameters()])
+        it = iter(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(random_dataset(64, HID, seed=11), batch_size=4)))
+        first = float(engine.train_batch(it))                    # real step: meta handshake and buffers are set up
+        posted = []
+        real_post = p2p.Link.post
+        p2p.Link.post = lambda self, tensor: posted.append(comm_stub.enabled()) or real_post(self, tensor)
+        try:
+            assert comm_stub.set_enabled(True) is False
+            for _ in range(2):
+                engine.train_batch(it)                           # must not hang although nothing is exchanged
+            assert posted and all(posted)                        # every post happened under the stub ...
+            links = p2p.links()
+            link = links.act_out or links.act_in
+            assert link.post(torch.zeros(1)) is comm_stub.DONE   # ... and a post under the stub transfers nothing
+            assert comm_stub.set_enabled(False) is True
+        finally:
+            p2p.Link.post = real_post
+            comm_stub.set_enabled(False)
+        dist.barrier()
+        after = float(engine.train_batch(it))                    # transfers are back and both stages still agree
+        assert after == after and first == first
+        t = torch.tensor([engine.global_steps], dtype=torch.float32)
+        dist.all_reduce(t)
+        assert int(t.item()) == 2 * engine.global_steps == 8
+    run()
