@@ -374,7 +374,11 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
 
     @property
     def _fused_dgrad(self):
-        return os.environ.get("DSB_ZERO3_FUSED_DGRAD", "1") == "1"
+        # measured (profiles/ag_gemm_bench_*): the K-sharded kernel beats all-gather + GEMM between two GPUs and
+        # trails it (0.86 - 0.98 x) from four on, where every k-panel waits on a different peer; an explicit
+        # DSB_ZERO3_FUSED_DGRAD=1 / 0 overrides the choice
+        choice = os.environ.get("DSB_ZERO3_FUSED_DGRAD")
+        return self.partition_count <= 2 if choice is None else choice == "1"
 
     def _setup_fused_wgrad_reduce_scatter(self):
         """Weights on the fused all-gather + GEMM path also get their gradient reduce-scattered INSIDE the wgrad GEMM

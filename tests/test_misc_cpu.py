@@ -347,3 +347,24 @@ def test_reference_helper_names_behave():
     table = pv.pipeline_table(2, 4)
     assert "GPU 1" in table and "Num Microbatches: 4" in table and "Non Idle Time: 16" in table
     assert zero3_partitioned_param_info(10, 4) == (2, 2) and zero3_partitioned_param_info(8, 4) == (2, 0)
+
+
+def test_zero3_fused_dgrad_choice_follows_world_size(monkeypatch):
+    """Unset, the K-sharded input-gradient kernel is used between two GPUs and NCCL gathers from four on; the env
+    switch overrides either way."""
+    from deeperspeed_b200.runtime.zero.stage3 import FP16_DeepSpeedZeroOptimizer_Stage3 as Z3
+
+    class Probe:
+        _fused_dgrad = Z3._fused_dgrad
+
+    monkeypatch.delenv("DSB_ZERO3_FUSED_DGRAD", raising=False)
+    for world, want in ((1, True), (2, True), (4, False), (8, False)):
+        p = Probe()
+        p.partition_count = world
+        assert p._fused_dgrad is want
+    p.partition_count = 8
+    monkeypatch.setenv("DSB_ZERO3_FUSED_DGRAD", "1")
+    assert p._fused_dgrad is True
+    p.partition_count = 2
+    monkeypatch.setenv("DSB_ZERO3_FUSED_DGRAD", "0")
+    assert p._fused_dgrad is False
