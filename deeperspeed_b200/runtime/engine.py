@@ -351,6 +351,7 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
         if self.global_rank == 0:
             logger.info(f"Using {origin} as basic optimizer")
             logger.info("DeepSpeed Basic Optimizer = {}".format(basic.__class__.__name__))
+        self.basic_optimizer = basic      # the inner optimizer, whatever wrapper ends up in self.optimizer
 
         if self.zero_optimization():
             assert not self.amp_enabled(), "Amp and ZeRO are not currently compatible, please use (legacy) fp16 mode " \
