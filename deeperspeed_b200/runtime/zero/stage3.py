@@ -20,11 +20,28 @@ from ...ops import kernels as K
 from ...utils.logging import logger
 from ..fp16.loss_scaler import LossScaler, DynamicLossScaler
 from .partition_parameters import (Init, ZeroParamStatus, ZeROOrderedDict, FWD_MODULE_STACK, inject_parameters,
-                                   is_zero_param, _init_external_params)
+                                   is_zero_param, _init_external_params, register_external_parameter,
+                                   unregister_external_parameter)
 
 
 def _dist_ready():
     return dist.is_available() and dist.is_initialized()
+
+
+def _zero_params_in(output):
+    """Partitioned parameters that a module handed back in its output: the output itself, the members of a list /
+    tuple / dict, or the tensor attributes of a plain result object."""
+    if torch.is_tensor(output):
+        members = (output,)
+    elif isinstance(output, (list, tuple)):
+        members = output
+    elif isinstance(output, dict):
+        members = output.values()
+    elif hasattr(output, "__dict__"):
+        members = (v for k, v in vars(output).items() if not k.startswith("__"))
+    else:
+        return []
+    return [m for m in members if torch.is_tensor(m) and is_zero_param(m)]
 
 
 class PrefetchCoordinator:
@@ -111,14 +128,18 @@ class PartitionedParameterCoordinator:
         self.prefetch_coordinator.increment_step(sub_module)
 
     def _wait(self, p):
-        for (params, handles) in list(self.in_flight_handles):
-            if any(q is p for q in params):
-                for h in handles:
-                    if h is not None:
-                        h.wait()
-                for q in params:
-                    q.ds_status = ZeroParamStatus.AVAILABLE
-                self.in_flight_handles.remove((params, handles))
+        still_in_flight = []
+        for entry in self.in_flight_handles:
+            params, handles = entry
+            if not any(q is p for q in params):
+                still_in_flight.append(entry)
+                continue
+            for h in handles:
+                if h is not None:
+                    h.wait()
+            for q in params:
+                q.ds_status = ZeroParamStatus.AVAILABLE
+        self.in_flight_handles = still_in_flight      # (list.remove would compare the tensors element-wise)
         if p.ds_status == ZeroParamStatus.INFLIGHT:
             p.ds_status = ZeroParamStatus.AVAILABLE
 
@@ -348,7 +369,46 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
     def _post_forward(self, module, inputs, output):
         if FWD_MODULE_STACK and FWD_MODULE_STACK[-1] is module:
             FWD_MODULE_STACK.pop()
+        self._hand_returned_params_to_caller(module, output)
+        self._watch_opaque_output(module, output)
         self.param_coordinator.release_sub_module(module)
+
+    def _watch_opaque_output(self, module, output):
+        """torch's module backward hooks only see outputs that are a tensor or a tuple / list of tensors. For a dict
+        or a plain result object the tensors inside get a gradient hook each, so the module's parameters are gathered
+        again before its backward runs (they are released from their own gradient hooks, as always)."""
+        if not torch.is_grad_enabled() or torch.is_tensor(output) or isinstance(output, (list, tuple)):
+            return
+        if isinstance(output, dict):
+            members = output.values()
+        elif hasattr(output, "__dict__"):
+            members = vars(output).values()
+        else:
+            return
+        for t in members:
+            if torch.is_tensor(t) and t.requires_grad and t.grad_fn is not None:
+                t.register_hook(lambda grad, m=module: self._pre_backward(m, None))
+
+    def _hand_returned_params_to_caller(self, module, output):
+        """A module that returns one of its parameters (`return out, self.bias`, the skip-bias-add idiom) leaves the
+        caller holding a tensor this module is about to release. The parameter becomes an external parameter of the
+        calling module instead - registered there once, so from the next iteration on the caller gathers it itself -
+        and takes a hold on it that the caller's own release drops; a hold the returning module had on it as ITS
+        external parameter moves up with it (reference stage3.py:1413-1446, same outcome)."""
+        if not FWD_MODULE_STACK:
+            return                      # returned by the root module: nobody above needs it kept
+        caller = FWD_MODULE_STACK[-1]
+        for p in _zero_params_in(output):
+            if any(id(p) in getattr(m, "_external_params", ()) for m in FWD_MODULE_STACK):
+                continue                # an enclosing module already looks after it
+            register_external_parameter(caller, p)
+            p.ds_active_sub_modules += 1
+            if id(p) in getattr(module, "_external_params", ()):
+                unregister_external_parameter(module, p)
+                p.ds_active_sub_modules = max(p.ds_active_sub_modules - 1, 0)
+            if p.ds_status == ZeroParamStatus.NOT_AVAILABLE:
+                p.all_gather()
+                self.param_coordinator.total_available_parameter_numel += p.ds_numel
 
     def _pre_backward(self, module, grad_output):
         # weights on the fused path stay partitioned in backward as well (K-sharded all-gather + GEMM for the input

@@ -126,3 +126,103 @@ def test_stage3_nvme_offload_matches_adamw(pipeline, sub_group, tmp_path):
         swapped = [os.path.join(dp, f) for dp, _, fs in os.walk(nvme) for f in fs]
         assert len(swapped) > 0 and sum(os.path.getsize(f) for f in swapped) > 0, swapped
     run()
+
+
+class _ReturnsBias(torch.nn.Linear):
+    """The skip-bias-add idiom: the caller adds the bias itself."""
+
+    def forward(self, x):
+        return super().forward(x), self.bias
+
+
+class _Result:
+    def __init__(self, out, bias):
+        self.out, self.bias = out, bias
+
+
+class _ReturnsBiasInObject(_ReturnsBias):
+    def forward(self, x):
+        return _Result(*super().forward(x))
+
+
+class _ReturnsBiasInDict(_ReturnsBias):
+    def forward(self, x):
+        out, bias = super().forward(x)
+        return {"out": out, "bias": bias}
+
+
+class _Middle(torch.nn.Linear):
+    """Passes the inner module's bias further up, so the parameter must end up external two levels above its owner."""
+
+    def __init__(self, dim, as_object):
+        super().__init__(dim, dim)
+        kinds = {False: _ReturnsBias, True: _ReturnsBiasInObject, "dict": _ReturnsBiasInDict}
+        self.inner = kinds[as_object](dim, dim)
+        self.as_object = as_object
+
+    def forward(self, x):
+        got = self.inner(super().forward(x))
+        if self.as_object == "dict":
+            return got["out"], got["bias"]
+        return (got.out, got.bias) if self.as_object else got
+
+
+class _Outer(torch.nn.Module):
+    def __init__(self, dim, as_object):
+        super().__init__()
+        self.first = torch.nn.Linear(dim, dim)
+        self.middle = _Middle(dim, as_object)
+
+    def forward(self, x):
+        out, bias = self.middle(self.first(x))
+        assert bias.numel() == self.first.in_features          # still whole although its owner has finished
+        return (out + bias).pow(2).sum()
+
+
+class _Root(torch.nn.Module):
+    def __init__(self, dim=HID, as_object=False):
+        super().__init__()
+        self.outer = _Outer(dim, as_object)
+
+    def forward(self, x):
+        return self.outer(x)
+
+
+@pytest.mark.parametrize("as_object", [False, True, "dict"])
+def test_stage3_parameter_returned_by_a_module_stays_gathered_for_the_caller(as_object):
+    """Reference tests/unit/test_zero_context.py test_ext_param_return(obj): a parameter handed back in a module's
+    output is registered as external to the module that receives it (at the right level of the call stack, once),
+    survives its owner's release, trains like the unpartitioned model, and everything is released again afterwards.
+    Also under no_grad, where nothing but this bookkeeping keeps the tensor alive."""
+    import copy
+
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(0)
+        net = _Root(as_object=as_object)
+        plain = copy.deepcopy(net)
+        plain_opt = torch.optim.Adam(plain.parameters(), lr=1e-2)
+        cfg = {"train_batch_size": 2, "train_micro_batch_size_per_gpu": 1, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-2, "adam_w_mode": False}},
+               "fp16": {"enabled": True, "type": "fp32"},
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+        engine, _, _, _ = deepspeed.initialize(model=net, model_parameters=net.parameters(), config_params=cfg)
+        g = torch.Generator().manual_seed(1)
+        xs = [torch.randn(2, HID, generator=g) for _ in range(4)]      # row r belongs to rank r
+        with torch.no_grad():
+            assert torch.allclose(engine(xs[0][dist.get_rank()]), plain(xs[0][dist.get_rank()]), atol=1e-5)
+        for x in xs:
+            loss = engine(x[dist.get_rank()])
+            engine.backward(loss)
+            engine.step()
+            plain_opt.zero_grad()
+            (0.5 * (plain(x[0]) + plain(x[1]))).backward()
+            plain_opt.step()
+            held = {name: len(getattr(m, "_external_params", {})) for name, m in net.named_modules()}
+            assert held["outer"] == 1 and sum(held.values()) == 1, held
+        for (name, p), q in zip(net.named_parameters(), plain.parameters()):
+            assert p.ds_status == ZeroParamStatus.NOT_AVAILABLE and p.ds_active_sub_modules == 0, name
+            with deepspeed.zero.GatheredParameters(p):
+                assert torch.allclose(p.detach(), q.detach(), atol=1e-5), (name, (p - q).abs().max())
+
+    run()
