@@ -368,3 +368,44 @@ def test_zero3_fused_dgrad_choice_follows_world_size(monkeypatch):
     p.partition_count = 2
     monkeypatch.setenv("DSB_ZERO3_FUSED_DGRAD", "0")
     assert p._fused_dgrad is False
+
+
+def test_version_and_checkout_attributes():
+    """reference tests/unit/test_config.py test_check_version; the hash is the checkout's when there is one."""
+    import re
+    import subprocess
+    for name in ("__git_hash__", "__git_branch__", "__version__", "__version_major__", "__version_minor__",
+                 "__version_patch__"):
+        assert hasattr(deepspeed, name), name
+    assert deepspeed.__version__ == f"{deepspeed.__version_major__}.{deepspeed.__version_minor__}.{deepspeed.__version_patch__}"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(deepspeed.__file__)))
+    if os.path.isdir(os.path.join(root, ".git")):
+        head = subprocess.run(["git", "-C", root, "rev-parse", "--short=7", "HEAD"], capture_output=True, text=True)
+        if head.returncode == 0:
+            assert deepspeed.__git_hash__ == head.stdout.strip()
+    else:
+        assert deepspeed.__git_branch__ == "[snapshot]"
+    from deeperspeed_b200 import git_version_info as info
+    assert info.version == deepspeed.__version__ and re.match(r"\d+\.\d+$", info.torch_info["version"])
+    assert set(info.installed_ops) == set(info.compatible_ops) and info.installed_ops
+
+
+@pytest.mark.parametrize("argv, enabled, config", [
+    ([], False, None),                                               # parser extended, flags absent
+    (["--deepspeed_config", "foo.json"], False, "foo.json"),         # config without the enable flag
+    (["--deepspeed"], True, None),                                   # enable flag without a config
+    (["--deepspeed", "--deepspeed_config", "foo.json"], True, "foo.json"),
+])
+def test_config_argument_combinations(argv, enabled, config):
+    """reference tests/unit/test_ds_arguments.py: every combination of the two core flags next to a user flag."""
+    plain = argparse.ArgumentParser()
+    plain.add_argument("--num_epochs", type=int)
+    ns = plain.parse_args(["--num_epochs", "2"])
+    assert not hasattr(ns, "deepspeed") and not hasattr(ns, "deepspeed_config")
+    with pytest.raises(SystemExit):
+        plain.parse_args(["--num_epochs", "2", "--deepspeed"])      # unknown without add_config_arguments
+    parser = deepspeed.add_config_arguments(plain)
+    ns = parser.parse_args(["--num_epochs", "2"] + argv)
+    assert ns.num_epochs == 2
+    assert type(ns.deepspeed) is bool and ns.deepspeed == enabled
+    assert ns.deepspeed_config == config
