@@ -1,0 +1,136 @@
+"""Checkpoint save -> fresh engine -> load, over the optimizer wrappers of the reference's tests/unit/test_checkpointing.py
+that the other files do not reach: plain fp32 optimizer, reduced-precision fused (Adam) and unfused (LAMB) wrappers,
+ZeRO-3 with and without optimizer offload, `load_optimizer_states=False`, and the tag-validation modes.
+
+The check is behavioural: the restored engine holds the same weights and, fed the same batches, produces the same
+losses and the same weights as the engine that kept running - which only holds when master weights, moments, step
+counts and loss-scale state all came back. CPU / gloo, two ranks."""
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+
+import deeperspeed_b200 as deepspeed
+from common import distributed_test
+from simple_model import SimpleModel, random_dataloader, args_from_dict
+
+HID = 16
+
+
+def _steps(engine, n, seed):
+    out = []
+    dtype = engine.precision() if engine.fp16_enabled() else torch.float32
+    for i, (x, y) in enumerate(random_dataloader(engine, 64, HID, engine.device, dtype=dtype,
+                                                 seed=seed + dist.get_rank())):
+        if i == n:
+            break
+        loss = engine(x, y)
+        engine.backward(loss)
+        engine.step()
+        out.append(float(loss))
+    return out
+
+
+def _weights(engine):
+    if engine.zero_optimization_stage() == 3:
+        with deepspeed.zero.GatheredParameters(list(engine.module.parameters())):
+            return [p.detach().float().clone() for p in engine.module.parameters()]
+    return [p.detach().float().clone() for p in engine.module.parameters()]
+
+
+def _fresh(conf, tmp_path, seed):
+    torch.manual_seed(seed)
+    model = SimpleModel(HID)
+    engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, conf), model=model,
+                                           model_parameters=model.parameters())
+    return engine
+
+
+def _save_load_continue(conf, tmp_path, **load_kwargs):
+    """Returns (losses of the running engine, losses of the restored one, their weights) after the same 3 extra steps."""
+    a = _fresh(conf, tmp_path, seed=3)
+    _steps(a, 4, seed=0)
+    a.save_checkpoint(str(tmp_path), tag="ckpt", client_state={"epoch": 5})
+    dist.barrier()
+    b = _fresh(conf, tmp_path, seed=99)                      # different initial weights on purpose
+    path, client = b.load_checkpoint(str(tmp_path), tag="ckpt", **load_kwargs)
+    assert path is not None and client["epoch"] == 5
+    assert b.global_steps == a.global_steps
+    for wa, wb in zip(_weights(a), _weights(b)):
+        assert torch.equal(wa, wb)
+    la, lb = _steps(a, 3, seed=7), _steps(b, 3, seed=7)
+    return la, lb, _weights(a), _weights(b)
+
+
+def _conf(optimizer="Adam", precision=None, zero=None, **extra):
+    c = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+         "optimizer": {"type": optimizer, "params": {"lr": 1e-2}}}
+    if precision is not None:
+        c["fp16"] = {"enabled": True, "type": precision, "initial_scale_power": 8}
+    if zero is not None:
+        c["zero_optimization"] = zero
+    c.update(extra)
+    return c
+
+
+CASES = {
+    "fp32_adam": _conf(),                                                                    # no wrapper at all
+    "fp32_lamb_clipped": _conf("Lamb", gradient_clipping=1.0),
+    "bf16_fused_adam": _conf(precision="bf16"),                                              # FP16_Optimizer
+    "bf16_unfused_lamb": _conf("Lamb", precision="bf16"),                                    # FP16_UnfusedOptimizer
+    "zero3": _conf(precision="fp32", zero={"stage": 3, "stage3_param_persistence_threshold": 0}),
+    "zero3_offload": _conf(precision="fp32", zero={"stage": 3, "stage3_param_persistence_threshold": 0,
+                                                   "offload_optimizer": {"device": "cpu"}}),
+    "zero2_offload": _conf(precision="fp32", zero={"stage": 2, "cpu_offload": True}),
+}
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_restored_engine_continues_exactly(case, tmp_path):
+    @distributed_test(world_size=2)
+    def run():
+        la, lb, wa, wb = _save_load_continue(CASES[case], tmp_path)
+        assert la == lb, (la, lb)
+        for x, y in zip(wa, wb):
+            assert torch.equal(x, y)
+
+    run()
+
+
+@pytest.mark.parametrize("case", ["bf16_fused_adam", "zero3", "zero2_offload"])
+def test_load_without_optimizer_states_restores_weights_only(case, tmp_path):
+    """`load_optimizer_states=False` (reference test_checkpoint_zero_no_optimizer): the weights come back, the
+    moments do not - so the continuation differs from the engine that kept its optimizer state."""
+    @distributed_test(world_size=2)
+    def run():
+        la, lb, wa, wb = _save_load_continue(CASES[case], tmp_path, load_optimizer_states=False)
+        assert la[0] == pytest.approx(lb[0], rel=1e-3)       # same weights at the first step after the load ...
+        assert any(not torch.equal(x, y) for x, y in zip(wa, wb))      # ... but fresh moments from there on
+
+    run()
+
+
+@pytest.mark.parametrize("mode", ["FAIL", "WARN", "IGNORE"])
+def test_tag_validation_modes_with_diverging_tags(mode, tmp_path):
+    """Ranks that pass different tags: FAIL raises on every rank before anything is written, WARN and IGNORE save
+    (reference test_checkpoint_unique_tag); an unknown mode is rejected when the config is read
+    (test_checkpoint_unknown_tag_validation)."""
+    @distributed_test(world_size=2)
+    def run():
+        conf = _conf(precision="fp32", checkpoint={"tag_validation": mode})
+        engine = _fresh(conf, tmp_path, seed=1)
+        _steps(engine, 1, seed=0)
+        where = os.path.join(str(tmp_path), mode)
+        if mode == "FAIL":
+            with pytest.raises(AssertionError):
+                engine.save_checkpoint(where, tag=f"tag-{dist.get_rank()}")
+        else:
+            engine.save_checkpoint(where, tag=f"tag-{dist.get_rank()}")
+        engine.save_checkpoint(where, tag="same")              # identical tags always pass
+        dist.barrier()
+        assert os.path.isdir(os.path.join(where, "same"))
+        with pytest.raises(Exception):
+            _fresh(_conf(precision="fp32", checkpoint={"tag_validation": "foo"}), tmp_path, seed=1)
+
+    run()
