@@ -226,3 +226,72 @@ def test_stage3_parameter_returned_by_a_module_stays_gathered_for_the_caller(as_
                 assert torch.allclose(p.detach(), q.detach(), atol=1e-5), (name, (p - q).abs().max())
 
     run()
+
+
+# ------------------------------------------------------------------------------------------------- TiledLinear grid
+def _tile_slices(tiled, row, col):
+    return (slice(tiled.out_parts[row], tiled.out_parts[row + 1]), slice(tiled.in_parts[col], tiled.in_parts[col + 1]))
+
+
+@pytest.mark.parametrize("splits", [1, 2, 5, 32])
+def test_tiled_linear_tiles_are_the_blocks_of_the_full_weight(splits):
+    """reference tests/unit/test_zero_tiled.py test_tiled_init / test_tiled_baddim."""
+    import copy
+    from deeperspeed_b200.runtime.zero.tiling import TiledLinear
+    base = torch.nn.Linear(32, 40)
+    tiled = TiledLinear(32, 40, bias=True, init_linear=copy.deepcopy(base), out_splits=splits, in_splits=splits)
+    for row in range(splits):
+        for col in range(splits):
+            tile = tiled.linears[row][col]
+            assert isinstance(tile, torch.nn.Linear)
+            assert torch.equal(tile.weight.data, base.weight.data[_tile_slices(tiled, row, col)])
+            if col == splits - 1:             # the bias of an output slice lives in its last tile only
+                assert torch.equal(tile.bias.data, base.bias.data[_tile_slices(tiled, row, col)[0]])
+            else:
+                assert tile.bias is None
+    for bad in (0, 33):
+        with pytest.raises(RuntimeError):
+            TiledLinear(32, 32, out_splits=bad, in_splits=bad)
+
+
+class _LinearReturningBias(torch.nn.Linear):
+    def forward(self, x):
+        return super().forward(x), self.bias
+
+
+@pytest.mark.parametrize("bias", [False, True])
+@pytest.mark.parametrize("splits", [1, 2, 3])
+@pytest.mark.parametrize("in_f, out_f", [(32, 32), (23, 29), (29, 23)])
+@pytest.mark.parametrize("return_bias", [False, True])
+def test_tiled_linear_forward_backward_grid(bias, splits, in_f, out_f, return_bias):
+    """reference test_tiled_forward / test_tiled_backward / test_tiled_returnbias_backward: outputs and every tile's
+    gradients equal the matching block of the full layer's, for uneven feature counts too."""
+    import copy
+    from deeperspeed_b200.runtime.zero.tiling import TiledLinear, TiledLinearReturnBias
+    torch.manual_seed(in_f * out_f + splits)
+    if return_bias:
+        base = _LinearReturningBias(in_f, out_f, bias=bias)
+        tiled = TiledLinearReturnBias(in_f, out_f, bias=bias, linear_cls=_LinearReturningBias,
+                                      init_linear=copy.deepcopy(base), out_splits=splits, in_splits=splits)
+    else:
+        base = torch.nn.Linear(in_f, out_f, bias=bias)
+        tiled = TiledLinear(in_f, out_f, bias=bias, init_linear=copy.deepcopy(base), out_splits=splits,
+                            in_splits=splits)
+    x = torch.rand(3, in_f)
+    want, got = base(x.clone()), tiled(x.clone())
+    if return_bias:
+        (want, want_b), (got, got_b) = want, got
+        assert (want_b is None) == (got_b is None) == (not bias)
+        if bias:
+            assert torch.allclose(want_b, got_b, atol=1e-6)
+            want, got = want + want_b, got + got_b
+    assert torch.allclose(want, got, atol=1e-5)
+    want.sum().backward()
+    got.sum().backward()
+    for row in range(splits):
+        for col in range(splits):
+            tile = tiled.linears[row][col]
+            rows, cols = _tile_slices(tiled, row, col)
+            assert torch.allclose(base.weight.grad[rows, cols], tile.weight.grad, atol=1e-5)
+            if tile.bias is not None:
+                assert torch.allclose(base.bias.grad[rows], tile.bias.grad, atol=1e-5)
