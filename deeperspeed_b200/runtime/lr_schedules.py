@@ -213,6 +213,10 @@ class OneCycle(_Schedule):
         return (x - 1) / (self.step_ratio - 1)
 
     def _decay_interval(self):
+        # decay_step_size 0 is documented as "no decay" (the reference divides by it, lr_schedules.py:609,619): the
+        # schedule then rests at cycle_min_lr / cycle_max_mom once the cycle is over
+        if not self.decay_step_size:
+            return 0.0
         return (self.last_batch_iteration - self.total_size + 1) / self.decay_step_size
 
     def _in_cycle(self):
