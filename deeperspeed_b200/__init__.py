@@ -9,7 +9,7 @@ import types
 
 from .version import __version__, __version_major__, __version_minor__, __version_patch__, git_hash, git_branch
 __git_hash__, __git_branch__ = git_hash, git_branch
-from . import ops
+from . import ops, elasticity, profiling, module_inject, constants      # reachable as attributes after a bare import
 from .runtime.engine import DeepSpeedEngine
 from .runtime.engine import ADAM_OPTIMIZER, LAMB_OPTIMIZER  # noqa: F401
 from .runtime.pipe.engine import PipelineEngine

@@ -1,6 +1,7 @@
 """The public symbols users and checkpoints of the reference touch resolve through the `deepspeed`
 alias to this package."""
 import importlib
+import os
 
 import deeperspeed_b200 as deepspeed
 
@@ -170,3 +171,19 @@ def test_config_free_getters_agree_with_the_config_object():
     assert c.get_pld_enabled(d) is False and c.get_amp_enabled(d) is False and c.get_sparse_gradients_enabled(d) is False
     assert c.get_sparse_fixed_config({"block": 32})["block"] == 32
     assert c.get_sparse_bigbird_config({})["num_sliding_window_blocks"] == 3
+
+
+def test_subpackages_reachable_after_a_bare_import():
+    """`import deepspeed; deepspeed.elasticity.compute_elastic_config(...)` works in the reference without importing
+    the sub-package first (its engine / config modules pull them in); the same must hold here."""
+    import subprocess
+    import sys
+    code = ("import deeperspeed_b200 as d\n"
+            "d.elasticity.compute_elastic_config; d.elasticity.config.ElasticityError\n"
+            "d.profiling.flops_profiler.FlopsProfiler; d.module_inject.replace_module\n"
+            "d.ops.adam.FusedAdam; d.ops.sparse_attention.SparseSelfAttention; d.runtime.zero.Init\n"
+            "d.pipe.LayerSpec; d.checkpointing.checkpoint; d.git_version_info.version; d.constants.TORCH_DISTRIBUTED_DEFAULT_PORT\n"
+            "d.utils.logger; d.runtime.lr_schedules.OneCycle; d.runtime.pipe.schedule.TrainSchedule\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    done = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True)
+    assert done.returncode == 0, done.stderr[-800:]
