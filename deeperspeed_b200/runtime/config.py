@@ -10,6 +10,9 @@ import os
 import torch
 
 from . import constants as C
+from .constants import (ADAM_OPTIMIZER, ADAMW_OPTIMIZER, LAMB_OPTIMIZER, ONEBIT_ADAM_OPTIMIZER,  # noqa: F401
+                        ONEBIT_LAMB_OPTIMIZER, DEEPSPEED_OPTIMIZERS, TORCH_ADAM_PARAM, ADAM_W_MODE,
+                        ADAM_W_MODE_DEFAULT)      # the reference defines the optimizer names in this module
 from ..utils.logging import logger
 
 

@@ -127,9 +127,21 @@ class FP16_Optimizer(FlatMixedPrecisionOptimizer):
         return repr(self.optimizer)
 
 
+def _fused_supported_classes():
+    from ...ops.adam import FusedAdam
+    return [FusedAdam, torch.optim.Adam, torch.optim.AdamW]
+
+
+def __getattr__(name):
+    # FP16_FUSED_SUPPORTED_OPTIMIZERS (reference fp16/fused_optimizer.py:22): resolved on first use, because
+    # ops.adam imports this package's siblings
+    if name == "FP16_FUSED_SUPPORTED_OPTIMIZERS":
+        return _fused_supported_classes()
+    raise AttributeError(name)
+
+
 def is_fp16_fused_supported_optimizer(optimizer):
     """Is `optimizer` one FP16_Optimizer drives through its fused path (reference fp16/fused_optimizer.py:35-51)?"""
-    from ...ops.adam import FusedAdam
-    if isinstance(optimizer, (FusedAdam, torch.optim.Adam, torch.optim.AdamW)):
+    if isinstance(optimizer, tuple(_fused_supported_classes())):
         return True
     return optimizer.__class__.__name__.lower() == "onebitadam"

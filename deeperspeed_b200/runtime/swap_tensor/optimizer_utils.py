@@ -12,6 +12,7 @@ import torch.distributed as dist
 
 from ...ops.aio import aio_handle
 from . import constants as SC
+from .utils import SwapBufferManager, get_sized_buffer, get_sized_buffers  # noqa: F401
 
 # a piece of a flat gradient partition kept in its own file
 FlattenedTensorSwapInfo = namedtuple("FlattenedTensorSwapInfo", ["path", "length", "offset"])

@@ -8,6 +8,7 @@ from typing import List, Optional
 import torch
 
 from ...utils.logging import logger
+from .constants import AIO_ALIGNED_BYTES, MIN_AIO_BYTES  # noqa: F401
 
 
 def swap_in_tensors(swap_handle, tensor_buffers, swap_paths):

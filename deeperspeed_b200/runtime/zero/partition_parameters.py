@@ -21,6 +21,7 @@ from ...utils.distributed import init_distributed
 
 param_count = 0
 _orig_inits = {}
+partitioned_param_data_shape = [1]      # what `param.data` looks like while the parameter is partitioned
 
 
 class ZeroParamType(Enum):
@@ -396,7 +397,7 @@ class Init(InsertPostInitMethodToModuleSubClasses):
             return
         if param.ds_tensor is not None and not has_been_updated:
             # shard is current: just drop the gathered copy
-            param.data = torch.ones(1, dtype=param.dtype, device=self.local_device).data
+            param.data = torch.ones(partitioned_param_data_shape, dtype=param.dtype, device=self.local_device).data
             return
         part = self._partitioned_size(param)
         start = part * self.rank
@@ -422,7 +423,7 @@ class Init(InsertPostInitMethodToModuleSubClasses):
         end = min(start + part, param.ds_numel)
         if start < param.ds_numel:
             param.ds_tensor.narrow(0, 0, end - start).copy_(one_dim.narrow(0, start, end - start))
-        param.data = torch.ones(1, dtype=param.dtype, device=self.local_device).data
+        param.data = torch.ones(partitioned_param_data_shape, dtype=param.dtype, device=self.local_device).data
 
     # ---- gradients
     def _reduce_scatter_gradients(self, param_list):
