@@ -42,7 +42,7 @@ setup(
     packages=find_packages(include=["deeperspeed_b200", "deeperspeed_b200.*"]),
     package_data={"deeperspeed_b200": ["lib/*.so"]},
     include_package_data=True,
-    scripts=["bin/deepspeed", "bin/ds", "bin/ds_ssh", "bin/ds_report", "bin/ds_elastic"],
+    scripts=["bin/deepspeed", "bin/deepspeed.pt", "bin/ds", "bin/ds_ssh", "bin/ds_report", "bin/ds_elastic"],
     install_requires=requirements("requirements.txt"),
     extras_require={"dev": requirements("requirements-dev.txt"), "1bit_mpi": requirements("requirements-1bit-mpi.txt")},
     python_requires=">=3.10",

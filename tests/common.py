@@ -32,6 +32,10 @@ def _worker(rank, world, port, fn, args, kwargs, errq, use_cuda):
         # threaded op such as a conv): one thread => parallel regions run inline
         torch.set_num_threads(2 if use_cuda else 1)
         import deeperspeed_b200 as deepspeed
+        # a test that initialised torch.distributed in the parent process leaves a group behind that fork copies;
+        # its sockets and threads do not exist here, so it can neither be used nor torn down
+        assert not dist.is_initialized(), "the parent process holds an initialised process group: run tests that " \
+            "call init_distributed() in-process after the fork-based ones (or in their own pytest process)"
         deepspeed.init_distributed(dist_backend="nccl" if use_cuda else "gloo", verbose=False)
         if use_cuda:
             torch.cuda.set_device(rank)

@@ -91,7 +91,7 @@ def test_reference_symbol_surface():
 def test_cli_entry_points_exist():
     import os
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    for exe in ("deepspeed", "ds", "ds_report", "ds_elastic", "ds_ssh"):
+    for exe in ("deepspeed", "deepspeed.pt", "ds", "ds_report", "ds_elastic", "ds_ssh"):
         path = os.path.join(root, "bin", exe)
         assert os.path.isfile(path) and os.access(path, os.X_OK), path
 
