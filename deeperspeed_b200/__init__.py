@@ -9,12 +9,13 @@ import types
 
 from .version import __version__, __version_major__, __version_minor__, __version_patch__, git_hash, git_branch
 __git_hash__, __git_branch__ = git_hash, git_branch
-from . import ops, elasticity, profiling, module_inject, constants      # reachable as attributes after a bare import
+version = __version__
+from . import ops, elasticity, profiling, module_inject, constants, pt  # reachable as attributes after a bare import
 from .runtime.engine import DeepSpeedEngine
 from .runtime.engine import ADAM_OPTIMIZER, LAMB_OPTIMIZER  # noqa: F401
 from .runtime.pipe.engine import PipelineEngine
 from .runtime.lr_schedules import add_tuning_arguments
-from .runtime.config import DeepSpeedConfig
+from .runtime.config import DeepSpeedConfig, DeepSpeedConfigError
 from .runtime.activation_checkpointing import checkpointing
 from .ops.transformer import DeepSpeedTransformerLayer, DeepSpeedTransformerConfig
 from .utils import log_dist, logger
