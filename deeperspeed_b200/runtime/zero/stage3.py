@@ -6,8 +6,10 @@ and backward), with look-ahead prefetch along the recorded execution trace, `max
 `max_reuse_distance` and `param_persistence_threshold`; gradients are reduce-scattered to the owning rank as soon as
 they are produced; the optimizer steps sub-group by sub-group so fp32 state can live on CPU / NVMe.
 
-Mechanism (torch 2.x): module forward pre/post hooks + full backward pre/post hooks (no autograd-function wrapping of
-outputs as in stage3.py:1364-1559) and post-accumulate-grad hooks for the gradient reduce-scatter. Each sub-group's
+Mechanism (torch 2.x): module forward pre/post hooks; for the backward side, gradient hooks on the tensors each
+forward call received and produced (`_BackwardOfOneCall` - no autograd-function wrapping of outputs as in
+stage3.py:1364-1559 and none of torch's module backward hooks, so in-place updates of a sub-module's output work and a
+returned parameter stays a parameter); post-accumulate-grad hooks for the gradient reduce-scatter. Each sub-group's
 shards live in one flat low-precision arena + one flat gradient-shard arena, so the step is the same fused device
 sequence as stages 1/2 (fused norm/overflow kernel, fused Adam with low-precision write-back)."""
 import os
@@ -28,20 +30,54 @@ def _dist_ready():
     return dist.is_available() and dist.is_initialized()
 
 
-def _zero_params_in(output):
-    """Partitioned parameters that a module handed back in its output: the output itself, the members of a list /
-    tuple / dict, or the tensor attributes of a plain result object."""
-    if torch.is_tensor(output):
-        members = (output,)
-    elif isinstance(output, (list, tuple)):
-        members = output
-    elif isinstance(output, dict):
-        members = output.values()
-    elif hasattr(output, "__dict__"):
-        members = (v for k, v in vars(output).items() if not k.startswith("__"))
+def _tensors_in(value, depth=2):
+    """Tensors a module received or handed back: the value itself, the members of (nested) lists / tuples / dicts, or
+    the tensor attributes of a plain result object."""
+    if torch.is_tensor(value):
+        return [value]
+    if depth == 0:
+        return []
+    if isinstance(value, (list, tuple)):
+        members = value
+    elif isinstance(value, dict):
+        members = value.values()
+    elif hasattr(value, "__dict__") and not isinstance(value, (torch.nn.Module, type)):
+        members = [v for k, v in vars(value).items() if not k.startswith("__")]
     else:
         return []
-    return [m for m in members if torch.is_tensor(m) and is_zero_param(m)]
+    found = []
+    for m in members:
+        found.extend(_tensors_in(m, depth - 1))
+    return found
+
+
+def _zero_params_in(output):
+    """Partitioned parameters that a module handed back in its output."""
+    return [t for t in _tensors_in(output) if is_zero_param(t)]
+
+
+class _BackwardOfOneCall:
+    """Backward-side bookkeeping of ONE forward call of a sub-module, driven by gradient hooks on the tensors that
+    went in and came out (nothing is wrapped: outputs stay the tensors the module produced, so callers may modify them
+    in place and a returned parameter is still that parameter). `before` runs when the first gradient arrives at an
+    output - ahead of every autograd node recorded inside the module - and gathers the module's parameters; `after`
+    runs when the gradient of an input is complete, i.e. the module's own nodes are done."""
+
+    __slots__ = ("owner", "module", "started", "finished")
+
+    def __init__(self, owner, module):
+        self.owner, self.module = owner, module
+        self.started = self.finished = False
+
+    def before(self, grad):
+        if not self.started:
+            self.started = True
+            self.owner._pre_backward(self.module)
+
+    def after(self, grad):
+        if self.started and not self.finished:
+            self.finished = True
+            self.owner._post_backward(self.module)
 
 
 class PrefetchCoordinator:
@@ -350,8 +386,6 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 module.forward = types.MethodType(_fused_linear_forward, module)
             self.hook_handles.append(module.register_forward_pre_hook(self._pre_forward))
             self.hook_handles.append(module.register_forward_hook(self._post_forward))
-            self.hook_handles.append(module.register_full_backward_pre_hook(self._pre_backward))
-            self.hook_handles.append(module.register_full_backward_hook(self._post_backward))
             for child in module.children():
                 register(child)
 
@@ -370,24 +404,25 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         if FWD_MODULE_STACK and FWD_MODULE_STACK[-1] is module:
             FWD_MODULE_STACK.pop()
         self._hand_returned_params_to_caller(module, output)
-        self._watch_opaque_output(module, output)
+        self._arm_backward(module, inputs, output)
         self.param_coordinator.release_sub_module(module)
 
-    def _watch_opaque_output(self, module, output):
-        """torch's module backward hooks only see outputs that are a tensor or a tuple / list of tensors. For a dict
-        or a plain result object the tensors inside get a gradient hook each, so the module's parameters are gathered
-        again before its backward runs (they are released from their own gradient hooks, as always)."""
-        if not torch.is_grad_enabled() or torch.is_tensor(output) or isinstance(output, (list, tuple)):
+    def _arm_backward(self, module, inputs, output):
+        """Gradient hooks for this forward call (see _BackwardOfOneCall). torch's module backward hooks are not used:
+        they re-wrap every output in an autograd function, which forbids in-place updates of a sub-module's output
+        (`h += x`, ReLU(inplace=True)), strips the ds attributes from a returned parameter and does not see outputs
+        that are dicts or result objects. Reference: stage3.py:1448-1497 wraps outputs in Pre/PostBackwardFunction."""
+        if not torch.is_grad_enabled():
             return
-        if isinstance(output, dict):
-            members = output.values()
-        elif hasattr(output, "__dict__"):
-            members = vars(output).values()
-        else:
+        outs = [t for t in _tensors_in(output) if t.requires_grad and t.grad_fn is not None]
+        if not outs:
             return
-        for t in members:
-            if torch.is_tensor(t) and t.requires_grad and t.grad_fn is not None:
-                t.register_hook(lambda grad, m=module: self._pre_backward(m, None))
+        call = _BackwardOfOneCall(self, module)
+        for t in outs:
+            t.register_hook(call.before)
+        for t in _tensors_in(inputs):
+            if t.requires_grad and not is_zero_param(t):
+                t.register_hook(call.after)
 
     def _hand_returned_params_to_caller(self, module, output):
         """A module that returns one of its parameters (`return out, self.bias`, the skip-bias-add idiom) leaves the
@@ -410,14 +445,15 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 p.all_gather()
                 self.param_coordinator.total_available_parameter_numel += p.ds_numel
 
-    def _pre_backward(self, module, grad_output):
+    def _pre_backward(self, module):
         # weights on the fused path stay partitioned in backward as well (K-sharded all-gather + GEMM for the input
         # gradient, GEMM + reduce-scatter for the weight gradient); DSB_ZERO3_FUSED_DGRAD=0 gathers them with NCCL
         self.param_coordinator.fetch_sub_module(module, forward=self._fused_dgrad)
 
-    def _post_backward(self, module, grad_input, grad_output):
-        # parameters are released from their own post-accumulate-grad hook: AccumulateGrad may run after this hook
-        # and needs the parameter at full shape
+    def _post_backward(self, module):
+        # trainable parameters are released from their own post-accumulate-grad hook (AccumulateGrad needs them at
+        # full shape and may run after this); modules without a differentiable input never get here - whatever they
+        # leave gathered goes back at the end of backward()
         for p in self.param_coordinator._params_of(module):
             p.ds_active_sub_modules = max(p.ds_active_sub_modules - 1, 0)
             if not p.requires_grad:
