@@ -387,3 +387,62 @@ def test_stage3_returned_parameter_is_still_the_parameter():
         assert seen == [(True, ZeroParamStatus.AVAILABLE, HID)] * 2, seen
 
     run()
+
+
+@pytest.mark.parametrize("family", ["gpt2", "bert"])
+def test_stage3_trains_a_transformers_model_like_plain_adam(family):
+    """A model this package did not write: Hugging Face GPT-2 (tied input / output embeddings, Conv1D projections,
+    ModelOutput results) and BERT (tuple-returning blocks, LayerNorm everywhere) built from a config, wrapped by a
+    stage-3 engine on two ranks, follow plain Adam on the global batch step for step."""
+    transformers = pytest.importorskip("transformers")
+    import copy
+
+    def build():
+        torch.manual_seed(0)
+        if family == "gpt2":
+            cfg = transformers.GPT2Config(n_layer=2, n_head=2, n_embd=32, vocab_size=128, n_positions=32,
+                                          resid_pdrop=0.0, embd_pdrop=0.0, attn_pdrop=0.0)
+            return transformers.GPT2LMHeadModel(cfg)
+        cfg = transformers.BertConfig(num_hidden_layers=2, num_attention_heads=2, hidden_size=32, intermediate_size=64,
+                                      vocab_size=128, max_position_embeddings=32, hidden_dropout_prob=0.0,
+                                      attention_probs_dropout_prob=0.0)
+        return transformers.BertForMaskedLM(cfg)
+
+    class LossOnly(torch.nn.Module):
+        def __init__(self, inner):
+            super().__init__()
+            self.inner = inner
+
+        def forward(self, ids):
+            return self.inner(input_ids=ids, labels=ids).loss
+
+    @distributed_test(world_size=2)
+    def run():
+        model = build()
+        plain = copy.deepcopy(model)
+        plain_opt = torch.optim.Adam(plain.parameters(), lr=1e-3)
+        conf = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+                "optimizer": {"type": "Adam", "params": {"lr": 1e-3, "adam_w_mode": False}},
+                "fp16": {"enabled": True, "type": "fp32"},
+                "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+        engine, _, _, _ = deepspeed.initialize(model=LossOnly(model), model_parameters=model.parameters(),
+                                               config_params=conf)
+        g = torch.Generator().manual_seed(1)
+        for _ in range(3):
+            ids = torch.randint(0, 128, (4, 16), generator=g)
+            mine = ids[2 * dist.get_rank():2 * dist.get_rank() + 2]
+            loss = engine(mine)
+            engine.backward(loss)
+            engine.step()
+            plain_opt.zero_grad()
+            want = 0.5 * (plain(input_ids=ids[:2], labels=ids[:2]).loss + plain(input_ids=ids[2:], labels=ids[2:]).loss)
+            want.backward()
+            plain_opt.step()
+            mean = loss.detach().clone()
+            dist.all_reduce(mean)
+            assert float(mean) / 2 == pytest.approx(float(want), rel=1e-5)
+        for (name, p), q in zip(model.named_parameters(), plain.parameters()):
+            with deepspeed.zero.GatheredParameters(p):
+                assert torch.allclose(p.detach(), q.detach(), atol=2e-5), (name, (p - q).abs().max())
+
+    run()

@@ -51,6 +51,17 @@ def main():
         # the reference's fixture asserts world_size <= torch.cuda.device_count() (one GPU per rank); on a CPU-only
         # machine the ranks are gloo processes, so that count is meaningless - let the assertion pass
         torch.cuda.device_count = lambda: 64
+        # ... and `.cuda()` / `.to("cuda")` in the test bodies keep the tensor / module where it is, so the logic
+        # under test (activation checkpointing, PartitionedTensor, grids, pipeline modules) runs on CPU tensors
+        def _is_cuda_target(args, kwargs):
+            dev = kwargs.get("device", args[0] if args else None)
+            return isinstance(dev, (str, torch.device)) and str(dev).startswith("cuda")
+
+        tensor_to, module_to = torch.Tensor.to, torch.nn.Module.to
+        torch.Tensor.cuda = lambda self, *a, **k: self
+        torch.nn.Module.cuda = lambda self, *a, **k: self
+        torch.Tensor.to = lambda self, *a, **k: self if _is_cuda_target(a, k) else tensor_to(self, *a, **k)
+        torch.nn.Module.to = lambda self, *a, **k: self if _is_cuda_target(a, k) else module_to(self, *a, **k)
     os.chdir(args.ref)
     import inspect
     import pytest
