@@ -375,8 +375,24 @@ class Init(InsertPostInitMethodToModuleSubClasses):
         return t
 
     def _allgather_param(self, param, async_op=False):
+        swap = getattr(param, "ds_swap", None)      # shard on NVMe (ZeRO-3 optimizer's arena swapper): bring it in
+        if swap is None:
+            return self._allgather_resident(param, async_op)
+        swapper, arena = swap
+        swapper.acquire(arena)
+        try:
+            shard = self._shard_on_device(param)
+            if shard.device.type == "cpu":
+                # stays in host memory (CPU run): the pool buffer may be recycled before an asynchronous gather ends
+                shard = shard.clone()
+            return self._allgather_resident(param, async_op, shard)
+        finally:
+            swapper.release(arena)      # device copies out of the buffer are fenced by the swapper's events
+
+    def _allgather_resident(self, param, async_op=False, shard=None):
         part = self._partitioned_size(param)
-        shard = self._shard_on_device(param)
+        if shard is None:
+            shard = self._shard_on_device(param)
         flat = torch.empty(part * self.world_size, dtype=shard.dtype, device=self.local_device)
         handle = None
         if self.world_size > 1:
@@ -399,6 +415,19 @@ class Init(InsertPostInitMethodToModuleSubClasses):
             # shard is current: just drop the gathered copy
             param.data = torch.ones(partitioned_param_data_shape, dtype=param.dtype, device=self.local_device).data
             return
+        swap = getattr(param, "ds_swap", None)
+        if swap is not None:            # shard on NVMe: bring its arena in, update it below, store it again
+            swap[0].acquire(swap[1])
+        try:
+            self._write_shard(param)
+        finally:
+            if swap is not None:
+                swap[0].write_back(swap[1])
+                swap[0].release(swap[1])
+        param.data = torch.ones(partitioned_param_data_shape, dtype=param.dtype, device=self.local_device).data
+
+    def _write_shard(self, param):
+        """Copy this rank's slice of the gathered `param.data` into its shard (created on first use)."""
         part = self._partitioned_size(param)
         start = part * self.rank
         one_dim = param.data.contiguous().view(-1)
@@ -423,7 +452,6 @@ class Init(InsertPostInitMethodToModuleSubClasses):
         end = min(start + part, param.ds_numel)
         if start < param.ds_numel:
             param.ds_tensor.narrow(0, 0, end - start).copy_(one_dim.narrow(0, start, end - start))
-        param.data = torch.ones(partitioned_param_data_shape, dtype=param.dtype, device=self.local_device).data
 
     # ---- gradients
     def _reduce_scatter_gradients(self, param_list):

@@ -193,6 +193,8 @@ class PartitionedParameterCoordinator:
             cost = sum(p.ds_numel for p in params)
             if not params:
                 continue
+            for swapper, arena in {getattr(p, "ds_swap", None) for p in params} - {None}:
+                swapper.prefetch(arena)        # shards on NVMe: start the file read now
             if cost > budget or self.total_available_parameter_numel + cost > self.max_available_parameters_in_numel:
                 break
             handles = []
@@ -261,6 +263,8 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         self.offload_param = offload_param_config is not None
         self.swap_optimizer = self.offload_optimizer and self.offload_optimizer_device == "nvme"
         self.optimizer_swapper = None
+        self.swap_params = self.offload_param and offload_param_config.get("device") == "nvme"
+        self.param_swapper = None
 
         # ---- make sure every parameter is a (partitioned) ds param
         if any(not is_zero_param(p) for p in module.parameters()):
@@ -278,6 +282,15 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
             comm_stream=torch.cuda.Stream() if (overlap_comm and torch.cuda.is_available()) else None,
             max_reuse_distance_in_numel=int(max_reuse_distance), max_available_parameters_in_numel=int(max_live_parameters))
         self._setup_module_hooks()
+
+        if self.swap_params:
+            # ZeRO-Infinity: the low-precision shard arenas live in files, a pool of pinned buffers caches the ones in
+            # use (swap_tensor/arena_swapper.py); a sub-group must fit one buffer
+            from ..swap_tensor.arena_swapper import ArenaSwapper
+            self.param_swapper = ArenaSwapper(offload_param_config["nvme_path"], next(module.parameters()).dtype,
+                                              offload_param_config.get("buffer_count", 5),
+                                              offload_param_config.get("buffer_size", int(1e8)), aio_config or {})
+            self.sub_group_size = min(self.sub_group_size, self.param_swapper.largest_arena())
 
         # ---- sub-groups: flat low-precision shard arena + flat grad-shard arena + fp32 master per sub-group
         self.fp16_groups = []
@@ -315,16 +328,20 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         self._install_grad_hooks()
         self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._sumsq = torch.zeros(2, dtype=torch.float32, device=self.device)
-        self.fused_inner = bool(getattr(self.optimizer, "supports_flat_fused", False)) and not self.offload_optimizer
+        self.fused_inner = (bool(getattr(self.optimizer, "supports_flat_fused", False)) and not self.offload_optimizer
+                            and not self.offload_param)      # the fused kernel writes the low-precision arena on the device
 
     # ------------------------------------------------------------------ construction helpers
     def _add_sub_group(self, params, gid):
         idx = len(self.sub_groups)
         total = sum(p.ds_tensor.numel() for p in params)
         lp_dev = params[0].ds_tensor.device
-        flat = torch.zeros(total, dtype=params[0].dtype, device=lp_dev)
-        if lp_dev.type == "cpu" and torch.cuda.is_available() and self.offload_param:
-            flat = flat.pin_memory()
+        if self.swap_params:
+            flat = self._register_swapped_arena(idx, params, total)
+        else:
+            flat = torch.zeros(total, dtype=params[0].dtype, device=lp_dev)
+            if lp_dev.type == "cpu" and torch.cuda.is_available() and self.offload_param:
+                flat = flat.pin_memory()
         gflat = torch.zeros(total, dtype=params[0].dtype, device=self.device)
         off = 0
         for p in params:
@@ -338,11 +355,56 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         if master_dev.type == "cpu" and self.offload_optimizer_pin and torch.cuda.is_available():
             master = master.pin_memory()
         master.requires_grad = True
+        if self.swap_params:
+            self.param_swapper.write_back(idx)
+            self.param_swapper.release(idx)
+            flat = None                 # lives in its file; `_lp_arena(idx)` brings it in
         self.sub_groups.append(params)
         self.fp16_partitioned_groups_flat.append(flat)
         self.grad_partitions_flat.append(gflat)
         self.fp32_partitioned_groups_flat.append(master)
         self.sub_group_to_group_id[idx] = gid
+
+    def _register_swapped_arena(self, idx, params, total):
+        """Sub-group `idx` gets a file instead of a permanent arena. Returns the (held) buffer to fill."""
+        sizes = [p.ds_tensor.numel() for p in params]
+        placeholder = torch.zeros(0, dtype=params[0].dtype)
+
+        def attach(view):
+            off = 0
+            for p, n in zip(params, sizes):
+                p.ds_tensor.data = placeholder if view is None else view.narrow(0, off, n)
+                off += n
+
+        for p in params:
+            p.ds_swap = (self.param_swapper, idx)
+        # the attach callback must not fire before the shards have been copied: register with a no-op first
+        self.param_swapper.register(idx, total, lambda view: None)
+        flat = self.param_swapper.acquire(idx, load=False)
+        self.param_swapper.attach[idx] = attach
+        return flat
+
+    class _HeldArena:
+        def __init__(self, owner, idx, load, dirty):
+            self.owner, self.idx, self.load, self.dirty = owner, idx, load, dirty
+
+        def __enter__(self):
+            o = self.owner
+            if o.param_swapper is None:
+                return o.fp16_partitioned_groups_flat[self.idx]
+            return o.param_swapper.acquire(self.idx, load=self.load)
+
+        def __exit__(self, *exc):
+            o = self.owner
+            if o.param_swapper is not None:
+                if self.dirty and exc[0] is None:
+                    o.param_swapper.write_back(self.idx)
+                o.param_swapper.release(self.idx)
+
+    def _lp_arena(self, idx, load=False, dirty=True):
+        """`with self._lp_arena(idx) as lp:` - the low-precision shard arena of sub-group `idx`, brought in from its
+        file when parameters are swapped to NVMe (and written back on exit when `dirty`)."""
+        return self._HeldArena(self, idx, load, dirty)
 
     def _rebuild_inner_param_groups(self):
         """The inner optimizer sees one flat fp32 parameter per sub-group (hyper-parameters copied from its group)."""
@@ -515,7 +577,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 return
             world = self.partition_count
             idx, off = self._param_slot[param]
-            part = param.ds_tensor.numel()
+            part = param.ds_tensor.ds_numel       # (numel() is 0 while the shard is swapped out)
             dst = self.grad_partitions_flat[idx].narrow(0, off, part)
             g = p.grad
             if g.numel() != param.ds_numel:
@@ -600,9 +662,12 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         return combined
 
     def _optimizer_step(self, idx, inv):
+        with self._lp_arena(idx) as lp:        # every element is rewritten from the master: no read needed
+            self._optimizer_step_into(idx, inv, lp)
+
+    def _optimizer_step_into(self, idx, inv, lp):
         master = self.fp32_partitioned_groups_flat[idx]
         group = self.optimizer.param_groups[idx]
-        lp = self.fp16_partitioned_groups_flat[idx]
         g = self.grad_partitions_flat[idx]
         if self.fused_inner:
             st = self.optimizer.state[master]
@@ -715,10 +780,10 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         self.overflow = sd["overflow"]
         if load_optimizer_states:
             self.optimizer.load_state_dict(sd["optimizer_state_dict"])
-        for cur, saved, lp in zip(self.fp32_partitioned_groups_flat, sd["fp32_flat_groups"],
-                                  self.fp16_partitioned_groups_flat):
+        for idx, (cur, saved) in enumerate(zip(self.fp32_partitioned_groups_flat, sd["fp32_flat_groups"])):
             cur.data.copy_(saved.data)
-            lp.copy_(cur.data)
+            with self._lp_arena(idx) as lp:
+                lp.copy_(cur.data)
         for p in self.module.parameters():
             if p.ds_persist:
                 p.ds_status = ZeroParamStatus.NOT_AVAILABLE

@@ -446,3 +446,90 @@ def test_stage3_trains_a_transformers_model_like_plain_adam(family):
                 assert torch.allclose(p.detach(), q.detach(), atol=2e-5), (name, (p - q).abs().max())
 
     run()
+
+
+def test_stage3_parameter_shards_live_in_files_and_rotate_through_the_buffer_pool(tmp_path):
+    """offload_param nvme: every sub-group's low-precision shard arena is a file under
+    <nvme>/zero_stage_3/*params/rank<R>/, at most `buffer_count` of them are in host memory at once (the others have
+    empty `ds_tensor`s), arenas are read back for gathers and rewritten by the optimizer step, a modification made
+    under GatheredParameters reaches the file, a checkpoint round trip restores them - and training equals AdamW."""
+    import copy
+    from simple_model import LinearStack
+
+    @distributed_test(world_size=2)
+    def run():
+        nvme = os.path.join(str(tmp_path), "nvme")
+        os.makedirs(nvme, exist_ok=True)
+        dim, layers = 24, 5
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 0.01, "weight_decay": 0.01}},
+               "fp16": {"enabled": True, "type": "fp32"},
+               "aio": {"block_size": 65536, "queue_depth": 4, "thread_count": 1},
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "sub_group_size": 300,
+                                     "offload_optimizer": {"device": "cpu"},
+                                     "offload_param": {"device": "nvme", "nvme_path": nvme, "buffer_count": 2,
+                                                       "buffer_size": 1024}}}
+        torch.manual_seed(7)
+        model = LinearStack(dim, dim, dim, num_layers=layers)
+        ref = LinearStack(dim, dim, dim, num_layers=layers)
+        ref.load_state_dict(model.state_dict())
+        engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                 model_parameters=model.parameters())
+        swapper = opt.param_swapper
+        arenas = len(opt.sub_groups)
+        assert swapper is not None and arenas >= 5 and all(a is None for a in opt.fp16_partitioned_groups_flat)
+        folder = swapper.folder
+        assert sorted(os.listdir(folder)) == sorted(f"arena_{i}.swp" for i in range(arenas))
+        assert f"rank{dist.get_rank()}" in folder and "zero_stage_3" in folder
+
+        def resident_params():
+            return sum(p.ds_tensor.numel() > 0 for p in model.parameters())
+
+        ropt = torch.optim.AdamW(ref.parameters(), lr=0.01, weight_decay=0.01)
+        g = torch.Generator().manual_seed(3)
+        for _ in range(3):
+            x = torch.randn(4, dim, generator=g)
+            y = torch.randint(0, dim, (4,), generator=g)
+            mine = slice(2 * dist.get_rank(), 2 * dist.get_rank() + 2)
+            loss = engine(x[mine], y[mine]); engine.backward(loss); engine.step()
+            assert len(swapper.resident_arenas()) <= 2 and all(h == 0 for h in swapper.holders.values())
+            assert resident_params() < len(list(model.parameters()))
+            ropt.zero_grad()
+            (0.5 * (ref(x[:2], y[:2]) + ref(x[2:], y[2:]))).backward()
+            ropt.step()
+        assert swapper.stats["evictions"] > 0 and swapper.stats["reads"] > 0 and swapper.stats["writes"] >= 4 * arenas
+
+        def check_against(reference):
+            for (name, p), r in zip(model.named_parameters(), reference.parameters()):
+                with deepspeed.zero.GatheredParameters(p):
+                    assert torch.allclose(p.detach(), r.detach(), atol=3e-5), (name, (p - r).abs().max())
+
+        check_against(ref)
+        # checkpoint round trip into a fresh engine that swaps to its own folder
+        engine.save_checkpoint(os.path.join(str(tmp_path), "ckpt"), tag="t")
+        dist.barrier()
+        cfg2 = copy.deepcopy(cfg)
+        cfg2["zero_optimization"]["offload_param"]["nvme_path"] = os.path.join(str(tmp_path), "nvme2")
+        torch.manual_seed(99)
+        model2 = LinearStack(dim, dim, dim, num_layers=layers)
+        engine2, opt2, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg2), model=model2,
+                                                   model_parameters=model2.parameters())
+        path, _ = engine2.load_checkpoint(os.path.join(str(tmp_path), "ckpt"), tag="t")
+        assert path is not None
+        for p2, r in zip(model2.parameters(), ref.parameters()):
+            with deepspeed.zero.GatheredParameters(p2):
+                assert torch.allclose(p2.detach(), r.detach(), atol=3e-5)
+        assert opt2.param_swapper.folder != swapper.folder and opt2.param_swapper.stats["writes"] >= 2 * arenas
+        # a modification through GatheredParameters lands in the file (the arena is evicted and read again below)
+        first = next(model.parameters())
+        with deepspeed.zero.GatheredParameters(first, modifier_rank=0):
+            if dist.get_rank() == 0:
+                with torch.no_grad():
+                    first.fill_(0.125)
+        for p in list(model.parameters())[1:]:
+            with deepspeed.zero.GatheredParameters(p):
+                pass
+        with deepspeed.zero.GatheredParameters(first):
+            assert torch.all(first == 0.125)
+
+    run()
