@@ -23,10 +23,14 @@ from .optimizer_utils import make_aio_handle
 
 
 class ArenaSwapper:
+    _instances = {}       # folder -> swappers created on it in this process (a second engine gets its own files)
+
     def __init__(self, nvme_path, dtype, buffer_count, buffer_size, aio_config=None):
         rank = dist.get_rank() if dist.is_initialized() else 0
         kind = "fp32" if dtype == torch.float32 else "fp16"
-        self.folder = os.path.join(nvme_path, "zero_stage_3", f"{kind}params", f"rank{rank}")
+        base = os.path.join(nvme_path, "zero_stage_3", f"{kind}params", f"rank{rank}")
+        nth = ArenaSwapper._instances[base] = ArenaSwapper._instances.get(base, -1) + 1
+        self.folder = base if nth == 0 else f"{base}_engine{nth}"
         os.makedirs(self.folder, exist_ok=True)
         self.dtype = dtype
         element = torch.tensor([], dtype=dtype).element_size()

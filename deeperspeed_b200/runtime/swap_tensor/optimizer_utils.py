@@ -151,6 +151,21 @@ class OptimizerSwapper:
                 info.add_state_tensors(state)
         return info
 
+    # ---- checkpoints
+    def release_optimizer_state(self, parameter):
+        """Drop the resident copy of a state that was swapped in and NOT modified (its files are current)."""
+        if id(parameter) in getattr(self, "_on_disk", ()):
+            self._get_param_swap_info(parameter).release_memory()
+            getattr(self, "_resident", {}).pop(id(parameter), None)
+
+    def forget(self, parameter):
+        """Forget the swap record of `parameter` (its tensors were replaced, e.g. by load_state_dict): the next
+        swap-out tracks the new tensors and rewrites the files."""
+        self.swap_params_info.pop(id(parameter), None)
+        getattr(self, "_on_disk", set()).discard(id(parameter))
+        getattr(self, "_resident", {}).pop(id(parameter), None)
+        getattr(self, "_prefetched", {}).pop(id(parameter), None)
+
     # ---- hooks of the ZeRO-3 step and timers
     def pre_backward(self):
         self.init_timers()

@@ -759,16 +759,40 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
 
     def state_dict(self):
         if self.optimizer_swapper is not None:
-            raise NotImplementedError("ZeRO-3 does not yet support checkpointing with NVMe offloading, please disable for now.")
+            masters, inner = self._swapped_state_for_checkpoint()
+        else:
+            masters, inner = [m.data.clone() for m in self.fp32_partitioned_groups_flat], self.optimizer.state_dict()
         return {
             "zero_stage": 3,
             "loss_scaler": self.loss_scaler,
             "dynamic_loss_scale": self.dynamic_loss_scale,
             "overflow": self.overflow,
             "partition_count": self.partition_count,
-            "optimizer_state_dict": self.optimizer.state_dict(),
-            "fp32_flat_groups": [m.data.clone() for m in self.fp32_partitioned_groups_flat],
+            "optimizer_state_dict": inner,
+            "fp32_flat_groups": masters,
         }
+
+    def _swapped_state_for_checkpoint(self):
+        """Optimizer state on NVMe (the reference refuses to checkpoint then, stage3.py:3030): one sub-group at a time
+        is read in, copied into ordinary host memory for the checkpoint and dropped again; its files stay as they
+        are."""
+        position, n = {}, 0
+        for group in self.optimizer.param_groups:
+            for p in group["params"]:
+                position[id(p)] = n
+                n += 1
+        masters, states = [], {}
+        for master in self.fp32_partitioned_groups_flat:
+            self.optimizer_swapper.swap_in_optimizer_state(parameter=master)
+            masters.append(master.data.clone())
+            kept = {k: (v.detach().clone() if torch.is_tensor(v) else v)
+                    for k, v in self.optimizer.state.get(master, {}).items()}
+            if kept:
+                states[position[id(master)]] = kept
+            self.optimizer_swapper.release_optimizer_state(parameter=master)
+        inner = self.optimizer.state_dict()
+        inner["state"] = states
+        return masters, inner
 
     def load_state_dict(self, state_dict_list, load_optimizer_states=True, load_from_fp32_weights=False):
         if isinstance(state_dict_list, dict):
@@ -778,12 +802,24 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         self.loss_scaler = sd["loss_scaler"]
         self.dynamic_loss_scale = sd["dynamic_loss_scale"]
         self.overflow = sd["overflow"]
+        swapper = self.optimizer_swapper
+        if swapper is not None:
+            for master in self.fp32_partitioned_groups_flat:
+                if load_optimizer_states:
+                    swapper.forget(master)          # the loaded state tensors replace the tracked ones
+                else:
+                    swapper.swap_in_optimizer_state(parameter=master)    # keep the moments, replace the master
         if load_optimizer_states:
             self.optimizer.load_state_dict(sd["optimizer_state_dict"])
         for idx, (cur, saved) in enumerate(zip(self.fp32_partitioned_groups_flat, sd["fp32_flat_groups"])):
-            cur.data.copy_(saved.data)
+            if cur.data.numel() == saved.numel():
+                cur.data.copy_(saved.data)
+            else:                                   # swapped out: no storage behind it at the moment
+                cur.data = saved.data.to(torch.float32).clone()
             with self._lp_arena(idx) as lp:
                 lp.copy_(cur.data)
+            if swapper is not None:
+                swapper.swap_out_optimizer_state(parameter=cur)
         for p in self.module.parameters():
             if p.ds_persist:
                 p.ds_status = ZeroParamStatus.NOT_AVAILABLE

@@ -5,6 +5,7 @@ ZeRO-3 with and without optimizer offload, `load_optimizer_states=False`, and th
 The check is behavioural: the restored engine holds the same weights and, fed the same batches, produces the same
 losses and the same weights as the engine that kept running - which only holds when master weights, moments, step
 counts and loss-scale state all came back. CPU / gloo, two ranks."""
+import json
 import os
 
 import pytest
@@ -83,14 +84,30 @@ CASES = {
     "zero3_offload": _conf(precision="fp32", zero={"stage": 3, "stage3_param_persistence_threshold": 0,
                                                    "offload_optimizer": {"device": "cpu"}}),
     "zero2_offload": _conf(precision="fp32", zero={"stage": 2, "cpu_offload": True}),
+    # optimizer state AND parameter shards on NVMe (the reference cannot checkpoint this: stage3.py:3030)
+    "zero3_nvme": _conf(precision="fp32", aio={"block_size": 65536, "queue_depth": 4, "thread_count": 1},
+                        zero={"stage": 3, "stage3_param_persistence_threshold": 0, "sub_group_size": 100,
+                              "offload_optimizer": {"device": "nvme", "nvme_path": "<tmp>", "buffer_count": 4},
+                              "offload_param": {"device": "nvme", "nvme_path": "<tmp>", "buffer_count": 2,
+                                                "buffer_size": 1024}}),
+    "zero3_nvme_pipelined": _conf(precision="fp32", aio={"block_size": 65536, "queue_depth": 4, "thread_count": 1},
+                                  zero={"stage": 3, "stage3_param_persistence_threshold": 0, "sub_group_size": 100,
+                                        "offload_optimizer": {"device": "nvme", "nvme_path": "<tmp>", "buffer_count": 4,
+                                                              "pipeline_read": True, "pipeline_write": True}}),
 }
+
+
+def _with_tmp(conf, tmp_path):
+    """Replace the "<tmp>" nvme_path markers by a folder under this test's tmp_path."""
+    text = json.dumps(conf).replace("<tmp>", os.path.join(str(tmp_path), "nvme"))
+    return json.loads(text)
 
 
 @pytest.mark.parametrize("case", sorted(CASES))
 def test_restored_engine_continues_exactly(case, tmp_path):
     @distributed_test(world_size=2)
     def run():
-        la, lb, wa, wb = _save_load_continue(CASES[case], tmp_path)
+        la, lb, wa, wb = _save_load_continue(_with_tmp(CASES[case], tmp_path), tmp_path)
         assert la == lb, (la, lb)
         for x, y in zip(wa, wb):
             assert torch.equal(x, y)
@@ -98,13 +115,13 @@ def test_restored_engine_continues_exactly(case, tmp_path):
     run()
 
 
-@pytest.mark.parametrize("case", ["bf16_fused_adam", "zero3", "zero2_offload"])
+@pytest.mark.parametrize("case", ["bf16_fused_adam", "zero3", "zero2_offload", "zero3_nvme"])
 def test_load_without_optimizer_states_restores_weights_only(case, tmp_path):
     """`load_optimizer_states=False` (reference test_checkpoint_zero_no_optimizer): the weights come back, the
     moments do not - so the continuation differs from the engine that kept its optimizer state."""
     @distributed_test(world_size=2)
     def run():
-        la, lb, wa, wb = _save_load_continue(CASES[case], tmp_path, load_optimizer_states=False)
+        la, lb, wa, wb = _save_load_continue(_with_tmp(CASES[case], tmp_path), tmp_path, load_optimizer_states=False)
         assert la[0] == pytest.approx(lb[0], rel=1e-3)       # same weights at the first step after the load ...
         assert any(not torch.equal(x, y) for x, y in zip(wa, wb))      # ... but fresh moments from there on
 
