@@ -420,6 +420,9 @@ class Init(InsertPostInitMethodToModuleSubClasses):
             swap[0].acquire(swap[1])
         try:
             self._write_shard(param)
+            refreshed = getattr(param, "ds_shard_updated", None)
+            if refreshed is not None:       # the ZeRO-3 optimizer keeps an fp32 master of this shard
+                refreshed(param)
         finally:
             if swap is not None:
                 swap[0].write_back(swap[1])

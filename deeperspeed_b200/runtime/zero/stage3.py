@@ -326,6 +326,9 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                                          largest_numel=max(t.numel() for t in self.fp32_partitioned_groups_flat),
                                          device=self.device, dtype=torch.float32, timers=timers)
         self._install_grad_hooks()
+        for params in self.sub_groups:
+            for p in params:
+                p.ds_shard_updated = self._master_follows_shard
         self._flag = torch.zeros(1, dtype=torch.int32, device=self.device)
         self._sumsq = torch.zeros(2, dtype=torch.float32, device=self.device)
         self.fused_inner = (bool(getattr(self.optimizer, "supports_flat_fused", False)) and not self.offload_optimizer
@@ -405,6 +408,31 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         """`with self._lp_arena(idx) as lp:` - the low-precision shard arena of sub-group `idx`, brought in from its
         file when parameters are swapped to NVMe (and written back on exit when `dirty`)."""
         return self._HeldArena(self, idx, load, dirty)
+
+    def _master_follows_shard(self, param):
+        """A shard was rewritten from outside the optimizer (`GatheredParameters(modifier_rank=...)`, weights loaded
+        after `initialize`): its slice of the fp32 master takes the new values, otherwise the next step would undo the
+        edit (the reference leaves the master stale, partition_parameters.py:700-745)."""
+        idx, off = self._param_slot[param]
+        master = self.fp32_partitioned_groups_flat[idx]
+        swapped = self.optimizer_swapper is not None and master.data.numel() == 0
+        if swapped:
+            self.optimizer_swapper.swap_in_optimizer_state(parameter=master)
+        n = param.ds_tensor.ds_numel
+        master.data.narrow(0, off, n).copy_(param.ds_tensor.data.view(-1)[:n])
+        if swapped:
+            self.optimizer_swapper.swap_out_optimizer_state(parameter=master)
+
+    def refresh_fp32_params(self):
+        """fp32 masters <- current low-precision shards, every sub-group (reference stage3.py:3106)."""
+        for idx, master in enumerate(self.fp32_partitioned_groups_flat):
+            swapped = self.optimizer_swapper is not None and master.data.numel() == 0
+            if swapped:
+                self.optimizer_swapper.swap_in_optimizer_state(parameter=master)
+            with self._lp_arena(idx, load=True, dirty=False) as lp:
+                master.data.copy_(lp)
+            if swapped:
+                self.optimizer_swapper.swap_out_optimizer_state(parameter=master)
 
     def _rebuild_inner_param_groups(self):
         """The inner optimizer sees one flat fp32 parameter per sub-group (hyper-parameters copied from its group)."""

@@ -533,3 +533,45 @@ def test_stage3_parameter_shards_live_in_files_and_rotate_through_the_buffer_poo
             assert torch.all(first == 0.125)
 
     run()
+
+
+@pytest.mark.parametrize("offload", [None, "cpu", "nvme"])
+def test_stage3_weight_edit_after_initialize_survives_the_next_step(offload, tmp_path):
+    """Weights written through GatheredParameters AFTER the engine exists (loading pretrained weights, re-initialising
+    a head) are taken over by the fp32 master - also when it lives in host memory or in a swap file -, so the next
+    optimizer step starts from them instead of undoing the edit."""
+    @distributed_test(world_size=2)
+    def run():
+        zero = {"stage": 3, "stage3_param_persistence_threshold": 0, "sub_group_size": 200}
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-3, "adam_w_mode": False}},
+               "fp16": {"enabled": True, "type": "fp32"}, "zero_optimization": zero}
+        if offload == "cpu":
+            zero["offload_optimizer"] = {"device": "cpu"}
+        elif offload == "nvme":
+            cfg["aio"] = {"block_size": 65536, "queue_depth": 4, "thread_count": 1}
+            zero["offload_optimizer"] = {"device": "nvme", "nvme_path": str(tmp_path), "buffer_count": 4}
+        torch.manual_seed(0)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        torch.manual_seed(5)
+        new_weight = torch.randn(HID, HID)              # same on both ranks
+        with deepspeed.zero.GatheredParameters(model.linear.weight, modifier_rank=0):
+            if dist.get_rank() == 0:
+                with torch.no_grad():
+                    model.linear.weight.copy_(new_weight)
+        x, y = next(iter(torch.utils.data.DataLoader(random_dataset(8, HID, seed=dist.get_rank()), batch_size=2)))
+        loss = engine(x, y)
+        engine.backward(loss)
+        engine.step()
+        with deepspeed.zero.GatheredParameters(model.linear.weight):
+            drift = (model.linear.weight.detach() - new_weight).abs().max()
+        assert 0 < drift <= 1.01e-3, drift           # one Adam step of size lr away from the EDITED weights
+        # the explicit refresh (reference API) is a no-op now: masters already equal the shards
+        before = [m.data.clone() if m.data.numel() else None for m in engine.optimizer.fp32_partitioned_groups_flat]
+        engine.optimizer.refresh_fp32_params()
+        for m, b in zip(engine.optimizer.fp32_partitioned_groups_flat, before):
+            assert b is None or torch.equal(m.data, b)
+
+    run()
