@@ -295,7 +295,9 @@ class DeepSpeedTransformerLayer(nn.Module):
 
     def forward(self, hidden_states, attention_mask=None, head_mask=None, layer_head_mask=None,
                 encoder_hidden_states=None, encoder_attention_mask=None, past_key_value=None,
-                output_attentions=False, grads=None):
+                output_attentions=False, grads=None, **unused):
+        # `unused`: whatever else the surrounding encoder hands its layers (past_key_values, cache_position, ... in
+        # recent Hugging Face releases); an encoder-only layer has no use for them
         self.config.training = self.training
         self.config.is_grad_enabled = torch.is_grad_enabled()
         cfg = self.config
@@ -306,7 +308,10 @@ class DeepSpeedTransformerLayer(nn.Module):
         pad = ((-S) % (128 if self._flash_ok(x) else 16)) if x.is_cuda else 0
         mask2d = None
         if attention_mask is not None:
-            mask2d = attention_mask.reshape(B, -1)[:, -S:].to(x.dtype).contiguous()
+            keys = attention_mask.reshape(B, -1)[:, -S:]        # [B, 1, 1, S] or the last row of [B, 1, S, S]
+            if keys.dtype == torch.bool:                        # recent Hugging Face: True = attend
+                keys = torch.zeros_like(keys, dtype=x.dtype).masked_fill_(~keys, -10000.0)
+            mask2d = keys.to(x.dtype).contiguous()
         if pad:
             x = torch.cat((x, torch.zeros(B, pad, h, dtype=x.dtype, device=x.device)), 1)
             m = mask2d if mask2d is not None else torch.zeros(B, S, dtype=x.dtype, device=x.device)

@@ -179,3 +179,31 @@ def test_module_injection_replace_and_revert_cpu(preln):
     for k, v in model.state_dict().items():
         assert torch.equal(v, original[k]), k
     assert (model.eval()(x, mask) - want).abs().max().item() < 1e-6
+
+
+def test_module_injection_into_a_hugging_face_bert_cpu():
+    """A BERT built by the `transformers` package in this image: every BertLayer becomes a DeepSpeedTransformerLayer
+    with the same weights; hidden states agree on the attended positions although that encoder hands its layers a
+    BOOLEAN [B, 1, S, S] mask and extra keyword arguments (`past_key_values`, ...); reverting restores the original."""
+    transformers = pytest.importorskip("transformers")
+    import copy
+    from transformers.models.bert.modeling_bert import BertLayer
+    from deeperspeed_b200.module_inject import replace_transformer_layer, revert_transformer_layer
+    from deeperspeed_b200.ops.transformer import DeepSpeedTransformerLayer
+    torch.manual_seed(0)
+    cfg = transformers.BertConfig(num_hidden_layers=2, num_attention_heads=2, hidden_size=32, intermediate_size=64,
+                                  vocab_size=128, max_position_embeddings=32, hidden_dropout_prob=0.0,
+                                  attention_probs_dropout_prob=0.0)
+    model = transformers.BertModel(cfg).eval()
+    ids = torch.randint(0, 128, (2, 16))
+    keep = torch.ones(2, 16, dtype=torch.long)
+    keep[1, 10:] = 0                                    # second sequence is padded
+    want = model(input_ids=ids, attention_mask=keep).last_hidden_state
+    swapped = replace_transformer_layer(BertLayer, copy.deepcopy(model), micro_batch_size=2, bert_config=cfg, seed=1,
+                                        max_seq_length=16, preln=False, fp16=False, huggingface=False)
+    assert all(isinstance(layer, DeepSpeedTransformerLayer) for layer in swapped.encoder.layer)
+    got = swapped(input_ids=ids, attention_mask=keep).last_hidden_state
+    assert torch.allclose(got[0], want[0], atol=1e-5) and torch.allclose(got[1, :10], want[1, :10], atol=1e-5)
+    back = revert_transformer_layer(BertLayer, swapped, cfg, preln=False)
+    assert all(isinstance(layer, BertLayer) for layer in back.encoder.layer)
+    assert torch.allclose(back(input_ids=ids, attention_mask=keep).last_hidden_state, want, atol=1e-6)
