@@ -564,3 +564,57 @@ def test_tensorboard_scalars_from_both_engines(tmp_path):
             tags = _scalar_tags(str(tmp_path / "pipe"))
             assert "Train/Samples/train_loss" in tags and "Train/Samples/lr" in tags, tags
     run()
+
+
+def test_training_data_loader_shards_by_rank_and_feeds_the_engine(tmp_path):
+    """`initialize(training_data=...)`: the returned loader hands every data-parallel rank its own, disjoint share of
+    the dataset in micro-batches, applies the collate function, starts the throughput timer per batch and drives a
+    normal training loop; `deepspeed_io` builds evaluation loaders that read sequentially; `RepeatingLoader` never runs
+    dry (reference runtime/dataloader.py:10-101, engine.py:890-957)."""
+    from deeperspeed_b200.runtime.dataloader import DeepSpeedDataLoader, RepeatingLoader
+
+    @distributed_test(world_size=2)
+    def run():
+        n = 24
+        xs = torch.arange(n, dtype=torch.float32).unsqueeze(1).repeat(1, HID)        # sample i is all i's
+        ys = torch.arange(n) % HID
+        dataset = torch.utils.data.TensorDataset(xs, ys)
+        tagged = []
+
+        def collate(samples):
+            x = torch.stack([s[0] for s in samples])
+            y = torch.stack([s[1] for s in samples])
+            tagged.append(len(samples))
+            return x, y
+
+        model = SimpleModel(HID)
+        engine, _, loader, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(1)), model=model,
+                                                    model_parameters=model.parameters(), training_data=dataset,
+                                                    collate_fn=collate)
+        assert isinstance(loader, DeepSpeedDataLoader) and loader is engine.training_dataloader
+        assert len(loader) == n // 2                                   # samples of this rank
+        seen = []
+        for x, y in loader:
+            assert x.shape == (engine.train_micro_batch_size_per_gpu(), HID)
+            seen.extend(int(v) for v in x[:, 0])
+            loss = engine(x / n, y)
+            engine.backward(loss)
+            engine.step()
+        assert tagged and all(t == 2 for t in tagged)                  # the collate function was used
+        assert engine.global_steps == len(seen) // (2 * engine.gradient_accumulation_steps())
+        assert engine.tput_timer.total_step_count > 0                  # the loader started the timer
+        gathered = [None, None]
+        dist.all_gather_object(gathered, seen)
+        assert sorted(gathered[0] + gathered[1]) == list(range(n)) and not set(gathered[0]) & set(gathered[1])
+
+        evaluation = engine.deepspeed_io(dataset, batch_size=4, route="eval")
+        order = [int(v) for x, _ in evaluation for v in x[:, 0]]
+        assert order == list(range(n))                                 # sequential, every sample, no sharding
+        with pytest.raises(ValueError):
+            engine.deepspeed_io([1, 2, 3])
+
+        endless = RepeatingLoader(engine.deepspeed_io(dataset, batch_size=4, route="eval"))
+        drawn = [next(endless)[0][0, 0].item() for _ in range(2 * (n // 4) + 1)]
+        assert drawn[0] == drawn[n // 4] == drawn[2 * (n // 4)] == 0.0
+
+    run()
