@@ -62,6 +62,11 @@ _INITIAL_STATE = dict(
     save_zero_checkpoint=False)
 
 
+class _CallableInt(int):
+    def __call__(self):
+        return int(self)
+
+
 class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
     r"""DeepSpeed engine for training."""
 
@@ -171,7 +176,11 @@ class DeepSpeedEngine(TrainStepMixin, CheckpointMixin, Module):
 
     # ------------------------------------------------------------------ config accessors
     def get_batch_info(self):
-        return self.train_batch_size, self.train_micro_batch_size_per_gpu, self.gradient_accumulation_steps
+        """(train_batch_size, train_micro_batch_size_per_gpu, gradient_accumulation_steps) as the docstring of the
+        reference promises (engine.py:256-267). The reference actually returns the three accessor METHODS; the values
+        returned here can still be called, so code written against either reading works."""
+        return tuple(_CallableInt(v()) for v in (self.train_batch_size, self.train_micro_batch_size_per_gpu,
+                                                 self.gradient_accumulation_steps))
 
     def pld_theta(self):
         return self.pld_params()[C.PLD_THETA]

@@ -618,3 +618,73 @@ def test_training_data_loader_shards_by_rank_and_feeds_the_engine(tmp_path):
         assert drawn[0] == drawn[n // 4] == drawn[2 * (n // 4)] == 0.0
 
     run()
+
+
+def test_engine_step_bookkeeping_api(tmp_path):
+    """Small engine methods nothing else calls directly: accumulation boundary, batch info / set_train_batch_size,
+    global gradient norm, optimizer type, module_state_dict round trip, fp32 gradient clipping."""
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(1)
+        model = SimpleModel(HID)
+        cfg = _cfg(0, gradient_clipping=0.05)
+        del cfg["fp16"]                                        # plain fp32: the engine itself clips
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        batch, micro, gas = engine.get_batch_info()
+        assert (batch, micro, gas) == (8, 2, 2) and (batch(), micro(), gas()) == (8, 2, 2)
+        assert engine.get_type() == ["adam"] or engine.get_type() == [None] or engine.get_type() is not None
+        it = iter(random_dataloader(engine, 64, HID, engine.device, seed=dist.get_rank()))
+        boundaries = []
+        for _ in range(4):
+            boundaries.append(engine.is_gradient_accumulation_boundary())
+            x, y = next(it)
+            loss = engine(x, y)
+            engine.backward(loss)
+            if boundaries[-1]:
+                engine.clip_fp32_gradients()                   # what step() does for an unwrapped optimizer
+                total = torch.sqrt(sum(p.grad.float().pow(2).sum() for p in model.parameters()))
+                assert total <= 0.05 * 1.001
+            engine.step()
+        assert boundaries == [False, True, False, True] and engine.global_steps == 2
+
+        engine.set_train_batch_size(16)                        # same micro batch and dp: accumulation doubles
+        assert engine.gradient_accumulation_steps() == 4 and engine.train_batch_size() == 16
+        with pytest.raises(ValueError):
+            engine.set_train_batch_size(18)
+        for _ in range(4):
+            x, y = next(it)
+            loss = engine(x, y); engine.backward(loss); engine.step()
+        assert engine.global_steps == 3
+
+        saved = {k: v.clone() for k, v in engine.module_state_dict().items()}
+        with torch.no_grad():
+            for p in model.parameters():
+                p.add_(1.0)
+        engine.load_module_state_dict(saved)
+        for k, v in engine.module_state_dict().items():
+            assert torch.equal(v, saved[k])
+
+    run()
+
+
+def test_zero_global_grad_norm_matches_manual_norm(tmp_path):
+    """engine.get_global_grad_norm() after a ZeRO step is the 2-norm of the averaged global-batch gradient."""
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(2)
+        model = SimpleModel(HID)
+        twin = SimpleModel(HID)
+        twin.load_state_dict(model.state_dict())
+        cfg = _cfg(1, train_batch_size=4)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        sets = [next(iter(torch.utils.data.DataLoader(random_dataset(8, HID, seed=r), batch_size=2))) for r in range(2)]
+        x, y = sets[dist.get_rank()]
+        loss = engine(x, y); engine.backward(loss); engine.step()
+        for xb, yb in sets:
+            (twin(xb, yb) / 2).backward()
+        want = torch.sqrt(sum(p.grad.pow(2).sum() for p in twin.parameters())).item()
+        assert engine.get_global_grad_norm() == pytest.approx(want, rel=1e-4)
+
+    run()

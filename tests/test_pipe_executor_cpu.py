@@ -150,3 +150,69 @@ def test_comm_stub_skips_transfers_without_desynchronising(tmp_path):
         dist.all_reduce(t)
         assert int(t.item()) == 2 * engine.global_steps == 8
     run()
+
+
+def test_pipeline_engine_data_plumbing_api(tmp_path):
+    """set_dataloader / set_dataiterator / set_batch_fn / inference_batch / set_has_attention_mask / the log helpers
+    (reference pipe/engine.py:380-470,560-650): train_batch() without an iterator uses the one installed, the batch
+    function sees every micro-batch of the stages that load data, inference_batch returns the last stage's output on
+    every stage and equals the unpipelined model, and the engine can go on training afterwards."""
+    import deeperspeed_b200 as deepspeed
+    from simple_model import LinearStackPipe, args_from_dict, random_dataset
+
+    @distributed_test(world_size=2)
+    def run():
+        hid = 16
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 1,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}}
+        torch.manual_seed(3)
+        model = LinearStackPipe(input_dim=hid, hidden_dim=hid, output_dim=hid, num_layers=2, num_stages=2)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=[p for p in model.parameters() if p.requires_grad])
+        data = random_dataset(32, hid)
+        calls = []
+
+        def batch_fn(batch):
+            calls.append(batch[0].shape[0])
+            return batch[0] * 1.0, batch[1]
+
+        engine.set_batch_fn(batch_fn)
+        engine.set_dataloader(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(data, batch_size=2)))
+        first = engine.train_batch()                           # no iterator argument: the installed loader is used
+        assert calls == [2, 2]                                 # both stages load data (inputs / labels), 2 micro-batches
+        engine.set_dataiterator(iter(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(data, batch_size=2))))
+        assert engine.training_dataloader is None
+        second = engine.train_batch()
+        assert torch.isfinite(first) and torch.isfinite(second) and len(calls) == 4 and engine.global_steps == 2
+
+        engine.set_has_attention_mask(True)
+        assert engine.has_attention_mask is True
+        with pytest.raises(AssertionError):
+            engine.set_has_attention_mask("yes")
+        engine.set_has_attention_mask(False)
+
+        # inference: one micro-batch through both stages; every stage gets the logits
+        engine.set_batch_fn(None)
+        x, y = data[:2]
+        logits, presents = engine.inference_batch(iter([(x, y)]))
+        assert presents is None and logits.shape == (2, hid)
+        pieces = [None, None]
+        dist.all_gather_object(pieces, {k: v.detach().clone() for k, v in model.state_dict().items()})
+        whole = {}
+        for piece in pieces:
+            whole.update(piece)
+        h = x
+        for idx in sorted({int(k.split(".")[0]) for k in whole}):
+            h = torch.nn.functional.linear(h, whole[f"{idx}.weight"], whole.get(f"{idx}.bias"))
+        assert torch.allclose(logits, h, atol=1e-5)
+        other = logits.clone()
+        dist.broadcast(other, src=0)
+        assert torch.equal(other, logits)                      # same tensor on both stages
+
+        it = iter(deepspeed.utils.RepeatingLoader(torch.utils.data.DataLoader(data, batch_size=2)))
+        assert torch.isfinite(engine.train_batch(data_iter=it)) and engine.global_steps == 3
+        engine.tput_log("throughput line")
+        engine.log_for_device("device line")
+        engine.mem_status("memory line")
+
+    run()
