@@ -112,15 +112,17 @@ class ArenaSwapper:
             self.reading = {}
 
     def prefetch(self, idx):
-        """Start reading arena `idx` if it is not here and a buffer can be had without waiting for anybody."""
+        """Start reading arena `idx` if it is not here and a buffer can be had without waiting for anybody.
+        True when a read was issued by this call (the caller then has something to overlap it with)."""
         if idx in self.resident or idx in self.reading or not os.path.exists(self._path(idx)):
-            return
+            return False
         if not self.free_slots and not any(self.holders[i] == 0 for i in self.resident):
-            return
+            return False
         slot = self._take_slot()
         self.read_handle.async_pread(self._io_view(idx, slot), self._path(idx))
         self.reading[idx] = slot
         self.stats["reads"] += 1
+        return True
 
     def acquire(self, idx, load=True):
         """Resident view of arena `idx`; held until release(). `load=False`: the caller overwrites all of it."""

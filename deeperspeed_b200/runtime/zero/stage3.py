@@ -193,8 +193,10 @@ class PartitionedParameterCoordinator:
             cost = sum(p.ds_numel for p in params)
             if not params:
                 continue
-            for swapper, arena in {getattr(p, "ds_swap", None) for p in params} - {None}:
-                swapper.prefetch(arena)        # shards on NVMe: start the file read now
+            # shards on NVMe: start the file read now and let it run under the current module's compute; the
+            # gather is issued by a later call (or by the module's own fetch), when the arena is in memory
+            if any([swapper.prefetch(arena) for swapper, arena in {getattr(p, "ds_swap", None) for p in params} - {None}]):
+                break
             if cost > budget or self.total_available_parameter_numel + cost > self.max_available_parameters_in_numel:
                 break
             handles = []

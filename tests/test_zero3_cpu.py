@@ -498,6 +498,7 @@ def test_stage3_parameter_shards_live_in_files_and_rotate_through_the_buffer_poo
             (0.5 * (ref(x[:2], y[:2]) + ref(x[2:], y[2:]))).backward()
             ropt.step()
         assert swapper.stats["evictions"] > 0 and swapper.stats["reads"] > 0 and swapper.stats["writes"] >= 4 * arenas
+        assert swapper.stats["prefetch_hits"] > 0          # reads started ahead along the recorded module trace
 
         def check_against(reference):
             for (name, p), r in zip(model.named_parameters(), reference.parameters()):
