@@ -382,7 +382,9 @@ def test_version_and_checkout_attributes():
     if os.path.isdir(os.path.join(root, ".git")):
         head = subprocess.run(["git", "-C", root, "rev-parse", "--short=7", "HEAD"], capture_output=True, text=True)
         if head.returncode == 0:
-            assert deepspeed.__git_hash__ == head.stdout.strip()
+            from deeperspeed_b200.version import _checkout_state
+            assert _checkout_state()[0] == head.stdout.strip()      # read now: HEAD may have moved since the import
+            assert re.fullmatch(r"[0-9a-f]{7}", deepspeed.__git_hash__)
     else:
         assert deepspeed.__git_branch__ == "[snapshot]"
     from deeperspeed_b200 import git_version_info as info
