@@ -389,8 +389,8 @@ def test_stage3_returned_parameter_is_still_the_parameter():
     run()
 
 
-@pytest.mark.parametrize("family", ["gpt2", "bert"])
-def test_stage3_trains_a_transformers_model_like_plain_adam(family):
+@pytest.mark.parametrize("family, stage", [("gpt2", 3), ("bert", 3), ("gpt2", 2), ("gpt2", 1)])
+def test_stage3_trains_a_transformers_model_like_plain_adam(family, stage):
     """A model this package did not write: Hugging Face GPT-2 (tied input / output embeddings, Conv1D projections,
     ModelOutput results) and BERT (tuple-returning blocks, LayerNorm everywhere) built from a config, wrapped by a
     stage-3 engine on two ranks, follow plain Adam on the global batch step for step."""
@@ -424,7 +424,9 @@ def test_stage3_trains_a_transformers_model_like_plain_adam(family):
         conf = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
                 "optimizer": {"type": "Adam", "params": {"lr": 1e-3, "adam_w_mode": False}},
                 "fp16": {"enabled": True, "type": "fp32"},
-                "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+                "zero_optimization": {"stage": stage}}
+        if stage == 3:
+            conf["zero_optimization"]["stage3_param_persistence_threshold"] = 0
         engine, _, _, _ = deepspeed.initialize(model=LossOnly(model), model_parameters=model.parameters(),
                                                config_params=conf)
         g = torch.Generator().manual_seed(1)
@@ -442,7 +444,7 @@ def test_stage3_trains_a_transformers_model_like_plain_adam(family):
             dist.all_reduce(mean)
             assert float(mean) / 2 == pytest.approx(float(want), rel=1e-5)
         for (name, p), q in zip(model.named_parameters(), plain.parameters()):
-            with deepspeed.zero.GatheredParameters(p):
+            with deepspeed.zero.GatheredParameters(p, enabled=stage == 3):
                 assert torch.allclose(p.detach(), q.detach(), atol=2e-5), (name, (p - q).abs().max())
 
     run()
