@@ -80,40 +80,64 @@ class _BackwardOfOneCall:
             self.owner._post_backward(self.module)
 
 
-class PrefetchCoordinator:
-    """Records the order in which sub-modules run in the first step and replays it to know what comes next."""
+class ExecutionTrace:
+    """The order in which sub-modules fetch their parameters during ONE whole iteration - forward and backward -,
+    recorded while the first iteration runs and replayed afterwards: it tells the coordinator what to gather ahead
+    (also in backward, where the reference looks ahead as well, stage3.py:365-440) and how soon a module runs again
+    (`max_reuse_distance`: the last layers of the forward pass are the first of the backward pass and are not worth
+    releasing in between). A step that leaves the recorded order (data-dependent control flow, an evaluation pass of a
+    different shape) truncates the trace at that point and records the rest again."""
 
     def __init__(self):
-        self.sub_module_trace = []
-        self.step_id = 0
-        self.most_recent_sub_module_step = {}
-        self.in_forward = True
+        self.order = []              # module ids, one entry per fetch
+        self.recording = True
+        self.position = -1           # index in `order` of the latest fetch
+        self.fetched_at = {}         # module id -> position of its latest fetch
+        self._next_use = []          # per position: position of the next fetch of the same module (None: never again)
+        self._before = []            # per position: elements fetched by all earlier positions (prefix sum)
 
-    def reset_step(self):
-        self.step_id = 0
+    @property
+    def ready(self):
+        return not self.recording and bool(self.order)
 
-    def record_trace(self, sub_module):
-        self.sub_module_trace.append(sub_module.id)
+    def begin_pass(self):
+        """The root module starts a forward pass."""
+        self.position = -1
 
-    def trace_completed(self):
-        return len(self.sub_module_trace) > 0 and self.step_id > 0
+    def advance(self, module_id):
+        self.position += 1
+        if not self.recording:
+            if self.position < len(self.order) and self.order[self.position] == module_id:
+                self.fetched_at[module_id] = self.position
+                return
+            del self.order[self.position:]          # off the recorded path: record the rest of this iteration anew
+            self.recording = True
+        self.order.append(module_id)
+        self.fetched_at[module_id] = self.position
 
-    def increment_step(self, sub_module):
-        self.most_recent_sub_module_step[sub_module.id] = self.step_id
-        self.step_id += 1
+    def end_iteration(self, numel_of):
+        """The backward pass is over. `numel_of(module_id)` sizes the entries of a freshly recorded trace."""
+        if self.recording and self.order:
+            self.recording = False
+            sizes = [numel_of(mid) for mid in self.order]
+            self._before = [0] * (len(sizes) + 1)
+            for i, n in enumerate(sizes):
+                self._before[i + 1] = self._before[i] + n
+            self._next_use, later = [None] * len(self.order), {}
+            for i in range(len(self.order) - 1, -1, -1):
+                self._next_use[i] = later.get(self.order[i])
+                later[self.order[i]] = i
+        self.position = -1
 
-    def get_reuse_distance_in_numel(self, sub_module, sub_module_step_id=None):
-        """Elements touched before `sub_module` runs again (inf when it does not recur in the trace)."""
-        if sub_module_step_id is None:
-            sub_module_step_id = self.most_recent_sub_module_step.get(sub_module.id, 0)
-        start = sub_module_step_id + 1
-        if sub_module.id not in self.sub_module_trace[start:]:
+    def upcoming(self, count):
+        return self.order[self.position + 1:self.position + 1 + count] if self.ready else []
+
+    def reuse_distance(self, module_id):
+        """Elements other modules fetch before `module_id` fetches again (inf: not again in this iteration)."""
+        at = self.fetched_at.get(module_id)
+        if not self.ready or at is None or at >= len(self._next_use) or self._next_use[at] is None:
             return float("inf")
-        end = self.sub_module_trace.index(sub_module.id, start)
-        return (start, end)
-
-    def next_modules(self, count):
-        return self.sub_module_trace[self.step_id + 1:self.step_id + 1 + count]
+        return self._before[self._next_use[at]] - self._before[at + 1]
 
 
 class PartitionedParameterCoordinator:
@@ -121,7 +145,7 @@ class PartitionedParameterCoordinator:
         self.in_flight_handles = []
         self.params_in_flight = []
         self.comm_stream = comm_stream
-        self.prefetch_coordinator = PrefetchCoordinator()
+        self.trace = ExecutionTrace()
         self.hierarchy = 0
         self.total_available_parameter_numel = 0
         self.max_available_parameters_in_numel = max_available_parameters_in_numel
@@ -129,16 +153,14 @@ class PartitionedParameterCoordinator:
         self.module_by_id = {}
 
     def reset_step(self):
-        self.prefetch_coordinator.reset_step()
+        """End of an iteration (after backward, or after a forward pass that will have none)."""
+        self.trace.end_iteration(lambda mid: sum(p.ds_numel for p in self._params_of(self.module_by_id[mid])))
 
     def _params_of(self, sub_module):
         params = [p for p in sub_module.parameters(recurse=False) if is_zero_param(p)]
         if hasattr(sub_module, "ds_external_parameters"):
             params += [p for _, p in sub_module.ds_external_parameters() if is_zero_param(p)]
         return params
-
-    def record_trace(self, sub_module):
-        self.prefetch_coordinator.record_trace(sub_module)
 
     @staticmethod
     def _fused_forward_weight(sub_module, p):
@@ -161,7 +183,7 @@ class PartitionedParameterCoordinator:
         for p in params:
             if p.ds_status == ZeroParamStatus.INFLIGHT:
                 self._wait(p)
-        self.prefetch_coordinator.increment_step(sub_module)
+        self.trace.advance(sub_module.id)
 
     def _wait(self, p):
         still_in_flight = []
@@ -181,10 +203,8 @@ class PartitionedParameterCoordinator:
 
     def prefetch_next_sub_modules(self, sub_module, numel=5000000):
         """Issue asynchronous all-gathers for the next sub-modules of the recorded trace, up to `numel` elements."""
-        if not self.prefetch_coordinator.trace_completed():
-            return
         budget = numel
-        for mid in self.prefetch_coordinator.next_modules(8):
+        for mid in self.trace.upcoming(8):
             mod = self.module_by_id.get(mid)
             if mod is None:
                 continue
@@ -207,10 +227,14 @@ class PartitionedParameterCoordinator:
             budget -= cost
 
     def release_sub_module(self, sub_module):
+        # a module that fetches again soon (the tail of the forward pass at the turn into backward) keeps its
+        # parameters, as long as the live-parameter budget holds
+        soon = (self.trace.reuse_distance(sub_module.id) < self.max_reuse_distance_in_numel
+                and self.total_available_parameter_numel <= self.max_available_parameters_in_numel)
         for p in self._params_of(sub_module):
             p.ds_active_sub_modules = max(p.ds_active_sub_modules - 1, 0)
-            if p.ds_active_sub_modules == 0 and not p.ds_persist and p.ds_status == ZeroParamStatus.AVAILABLE:
-                # keep alive when the module runs again soon (reuse distance below the threshold)
+            if (p.ds_active_sub_modules == 0 and not p.ds_persist and p.ds_status == ZeroParamStatus.AVAILABLE
+                    and not soon):
                 p.partition()
                 self.total_available_parameter_numel -= p.ds_numel
 
@@ -486,9 +510,8 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
     def _pre_forward(self, module, *args):
         FWD_MODULE_STACK.append(module)
         pc = self.param_coordinator
-        if not pc.prefetch_coordinator.trace_completed() or len(pc.prefetch_coordinator.sub_module_trace) <= module.id:
-            if module.id not in pc.prefetch_coordinator.sub_module_trace:
-                pc.record_trace(module)
+        if module is self.module:
+            pc.trace.begin_pass()
         pc.fetch_sub_module(module, forward=True)
         pc.prefetch_next_sub_modules(module, numel=self.prefetch_elements)
 
@@ -541,6 +564,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         # weights on the fused path stay partitioned in backward as well (K-sharded all-gather + GEMM for the input
         # gradient, GEMM + reduce-scatter for the weight gradient); DSB_ZERO3_FUSED_DGRAD=0 gathers them with NCCL
         self.param_coordinator.fetch_sub_module(module, forward=self._fused_dgrad)
+        self.param_coordinator.prefetch_next_sub_modules(module, numel=self.prefetch_elements)    # backward looks ahead too
 
     def _post_backward(self, module):
         # trainable parameters are released from their own post-accumulate-grad hook (AccumulateGrad needs them at
@@ -656,7 +680,6 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
 
     def backward(self, loss, retain_graph=False):
         self.micro_step_id += 1
-        self.param_coordinator.prefetch_coordinator.in_forward = False
         scaled = loss.float() * self.loss_scale
         scaled.backward(retain_graph=retain_graph)
         for p in self.module.parameters():   # anything still gathered (unused in this backward) goes back to shards

@@ -578,3 +578,125 @@ def test_stage3_weight_edit_after_initialize_survives_the_next_step(offload, tmp
             assert b is None or torch.equal(m.data, b)
 
     run()
+
+
+def test_execution_trace_replay_reuse_distance_and_rerecording():
+    """ExecutionTrace alone: records one iteration, answers look-ahead and reuse-distance queries on replay, and
+    re-records from the point where a later iteration leaves the recorded order."""
+    from deeperspeed_b200.runtime.zero.stage3 import ExecutionTrace
+    sizes = {0: 0, 1: 10, 2: 20, 3: 30}
+    trace = ExecutionTrace()
+    first = [0, 1, 2, 3, 3, 2, 1, 0]                   # forward 0..3, backward 3..0
+    trace.begin_pass()
+    for mid in first:
+        assert trace.upcoming(4) == [] and trace.reuse_distance(mid) == float("inf")      # nothing known yet
+        trace.advance(mid)
+    trace.end_iteration(sizes.__getitem__)
+    assert trace.ready and trace.order == first
+    trace.begin_pass()
+    trace.advance(0)
+    assert trace.upcoming(3) == [1, 2, 3]
+    trace.advance(1); trace.advance(2); trace.advance(3)
+    assert trace.upcoming(8) == [3, 2, 1, 0]           # the look-ahead runs into the backward pass
+    assert trace.reuse_distance(3) == 0                # runs again immediately
+    assert trace.reuse_distance(2) == 30 + 30          # both fetches of module 3 lie in between
+    assert trace.reuse_distance(1) == 20 + 30 + 30 + 20
+    for mid in (3, 2, 1, 0):
+        trace.advance(mid)
+    assert trace.reuse_distance(0) == float("inf")     # last use of the iteration
+    trace.end_iteration(sizes.__getitem__)
+    # an iteration that skips module 2 on the way back: truncated at the deviation and recorded again
+    trace.begin_pass()
+    for mid in (0, 1, 2, 3, 3):
+        trace.advance(mid)
+    assert trace.ready
+    trace.advance(1)
+    assert not trace.ready and trace.order == [0, 1, 2, 3, 3, 1]
+    trace.advance(0)
+    trace.end_iteration(sizes.__getitem__)
+    assert trace.ready and trace.order == [0, 1, 2, 3, 3, 1, 0]
+
+
+def test_stage3_keeps_the_forward_tail_for_backward_and_prefetches_in_backward(tmp_path):
+    """From the second iteration on (the first records the trace): the last layer is still gathered when the forward
+    pass ends, because its backward comes first (`stage3_max_reuse_distance`); with a reuse distance of 0 it is
+    released like every other layer. Backward issues asynchronous gathers ahead of the module it is in. Either way
+    the result equals plain Adam."""
+    import copy
+    from simple_model import LinearStack
+
+    @distributed_test(world_size=2)
+    def run():
+        dim = 16
+        torch.manual_seed(0)
+        base = LinearStack(dim, dim, dim, num_layers=3)
+
+        def train(reuse):
+            model = copy.deepcopy(base)
+            cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+                   "optimizer": {"type": "Adam", "params": {"lr": 1e-2, "adam_w_mode": False}},
+                   "fp16": {"enabled": True, "type": "fp32"},
+                   "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0,
+                                         "stage3_max_reuse_distance": reuse, "stage3_prefetch_bucket_size": 10 ** 6}}
+            engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                     model_parameters=model.parameters())
+            pc = opt.param_coordinator
+            from deeperspeed_b200.runtime.zero.partition_parameters import Init
+            gathers = []                                  # (iteration, "forward" | "backward", asynchronous?)
+            where = {"iteration": 0, "phase": "forward"}
+            plain_gather = Init._all_gather
+
+            def counting(init, param_list, async_op=False, hierarchy=None):
+                needed = [p for p in param_list if p.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+                if needed:
+                    gathers.append((where["iteration"], where["phase"], bool(async_op)))
+                return plain_gather(init, param_list, async_op=async_op, hierarchy=hierarchy)
+
+            Init._all_gather = counting
+            g = torch.Generator().manual_seed(4)
+            gathered_after_forward = []
+            for _ in range(3):
+                x = torch.randn(4, dim, generator=g)
+                y = torch.randint(0, dim, (4,), generator=g)
+                mine = slice(2 * dist.get_rank(), 2 * dist.get_rank() + 2)
+                where["phase"] = "forward"
+                loss = engine(x[mine], y[mine])
+                gathered_after_forward.append(sorted(n for n, p in model.named_parameters()
+                                                     if p.ds_status == ZeroParamStatus.AVAILABLE))
+                where["phase"] = "backward"
+                engine.backward(loss)
+                where["phase"] = "step"
+                engine.step()
+                where["iteration"] += 1
+            Init._all_gather = plain_gather
+            return model, gathered_after_forward, gathers, pc.trace
+
+        kept, after_fwd, _, trace = train(reuse=10 ** 9)
+        half = len(trace.order) // 2                                    # every module that ran: forward, then backward
+        assert trace.ready and half >= 6 and sorted(trace.order[:half]) == sorted(trace.order[half:])
+        assert after_fwd[0] == []                                       # first iteration: nothing known, all released
+        assert "output_layer.weight" in after_fwd[1] and "output_layer.weight" in after_fwd[2]
+        strict, after_fwd0, gathers, _ = train(reuse=0)
+        assert after_fwd0 == [[], [], []]
+        # first iteration: every gather is synchronous, in forward and again in backward; once the trace is known the
+        # look-ahead (which runs across the turn into backward) leaves only the very first gather synchronous
+        first = [g for g in gathers if g[0] == 0]
+        assert {g[1] for g in first} == {"forward", "backward"} and not any(g[2] for g in first)
+        later = [g for g in gathers if g[0] == 2]
+        assert sum(not g[2] for g in later) <= 1 and sum(g[2] for g in later) >= 2
+        assert not [g for g in later if g[1] == "backward" and not g[2]]
+        plain = copy.deepcopy(base)
+        popt = torch.optim.Adam(plain.parameters(), lr=1e-2)
+        g = torch.Generator().manual_seed(4)
+        for _ in range(3):
+            x = torch.randn(4, dim, generator=g)
+            y = torch.randint(0, dim, (4,), generator=g)
+            popt.zero_grad()
+            (0.5 * (plain(x[:2], y[:2]) + plain(x[2:], y[2:]))).backward()
+            popt.step()
+        for model in (kept, strict):
+            for (name, p), q in zip(model.named_parameters(), plain.parameters()):
+                with deepspeed.zero.GatheredParameters(p):
+                    assert torch.allclose(p.detach(), q.detach(), atol=1e-5), name
+
+    run()
