@@ -700,3 +700,43 @@ def test_stage3_keeps_the_forward_tail_for_backward_and_prefetches_in_backward(t
                     assert torch.allclose(p.detach(), q.detach(), atol=1e-5), name
 
     run()
+
+
+def test_stage3_gradient_accumulation_matches_adam_on_the_global_batch(tmp_path):
+    """Two micro-batches per step on each of two ranks (every micro-batch is one pass of the execution trace, the
+    gradient shards accumulate across them) equal one Adam step on the four micro-batches together."""
+    import copy
+    from simple_model import LinearStack
+
+    @distributed_test(world_size=2)
+    def run():
+        dim = 16
+        torch.manual_seed(0)
+        model = LinearStack(dim, dim, dim, num_layers=2)
+        plain = copy.deepcopy(model)
+        popt = torch.optim.Adam(plain.parameters(), lr=1e-2)
+        cfg = {"train_batch_size": 8, "train_micro_batch_size_per_gpu": 2, "gradient_accumulation_steps": 2,
+               "steps_per_print": 100, "optimizer": {"type": "Adam", "params": {"lr": 1e-2, "adam_w_mode": False}},
+               "fp16": {"enabled": True, "type": "fp32"}, "gradient_clipping": 1.0,
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                               model_parameters=model.parameters())
+        g = torch.Generator().manual_seed(9)
+        for _ in range(3):
+            x = torch.randn(8, dim, generator=g)
+            y = torch.randint(0, dim, (8,), generator=g)
+            for micro in range(2):                       # rank r takes micro-batches 2r and 2r + 1
+                lo = 4 * dist.get_rank() + 2 * micro
+                loss = engine(x[lo:lo + 2], y[lo:lo + 2])
+                engine.backward(loss)
+                engine.step()
+            popt.zero_grad()
+            sum(plain(x[i:i + 2], y[i:i + 2]) for i in range(0, 8, 2)).div(4).backward()
+            torch.nn.utils.clip_grad_norm_(plain.parameters(), 1.0)
+            popt.step()
+        assert engine.global_steps == 3
+        for (name, p), q in zip(model.named_parameters(), plain.parameters()):
+            with deepspeed.zero.GatheredParameters(p):
+                assert torch.allclose(p.detach(), q.detach(), atol=2e-5), (name, (p - q).abs().max())
+
+    run()
