@@ -91,7 +91,7 @@ class TrainStepMixin:
                 loss = self.module(*inputs, **kwargs)
         if zero3:
             if not torch._C.is_grad_enabled():
-                self.optimizer.param_coordinator.reset_step()      # no backward will come to close the trace
+                self.optimizer.end_of_pass()      # no backward will come to release the kept tail and close the trace
             for m in self.module.modules():
                 m._parameters._in_forward = False
 

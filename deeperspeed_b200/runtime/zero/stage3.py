@@ -682,7 +682,12 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         self.micro_step_id += 1
         scaled = loss.float() * self.loss_scale
         scaled.backward(retain_graph=retain_graph)
-        for p in self.module.parameters():   # anything still gathered (unused in this backward) goes back to shards
+        self.end_of_pass()
+
+    def end_of_pass(self):
+        """After backward (or after a forward pass that will have no backward): whatever is still gathered - unused
+        in this backward, or kept for a backward that is not coming - goes back to shards; the trace starts over."""
+        for p in self.module.parameters():
             if not p.ds_persist and p.ds_status != ZeroParamStatus.NOT_AVAILABLE:
                 self.param_coordinator.release_and_reset_parameter(p)
         self.param_coordinator.reset_step()

@@ -740,3 +740,32 @@ def test_stage3_gradient_accumulation_matches_adam_on_the_global_batch(tmp_path)
                 assert torch.allclose(p.detach(), q.detach(), atol=2e-5), (name, (p - q).abs().max())
 
     run()
+
+
+def test_stage3_evaluation_pass_between_training_steps_releases_everything(tmp_path):
+    """A no-grad forward pass in the middle of training follows the forward part of the recorded trace, leaves no
+    parameter gathered (the tail kept for a backward that is not coming is released) and does not disturb training."""
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(0)
+        model = SimpleModel(HID)
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-2}}, "fp16": {"enabled": True, "type": "fp32"},
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+        engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg), model=model,
+                                                 model_parameters=model.parameters())
+        data = list(torch.utils.data.DataLoader(random_dataset(16, HID, seed=dist.get_rank()), batch_size=2))
+        losses = []
+        for i, (x, y) in enumerate(data[:4]):
+            loss = engine(x, y); engine.backward(loss); engine.step()
+            losses.append(float(loss))
+            engine.eval()
+            with torch.no_grad():
+                first = float(engine(*data[5]))
+                assert all(p.ds_status == ZeroParamStatus.NOT_AVAILABLE for p in model.parameters())
+                assert float(engine(*data[5])) == first            # twice in a row, same answer
+            engine.train()
+            assert opt.param_coordinator.trace.ready and opt.param_coordinator.trace.position == -1
+        assert all(l == l for l in losses)
+
+    run()
