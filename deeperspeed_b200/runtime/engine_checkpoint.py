@@ -105,6 +105,10 @@ class CheckpointMixin:
 
     def _load_model_states(self, layout, strict, with_optimizer, with_scheduler):
         path = self._get_ckpt_name(layout.root, layout.tag)
+        if not os.path.exists(path) and self.zero_optimization_partition_weights():
+            # ZeRO-3 writes one model-states file per data-parallel rank; a run with MORE ranks than the saved one
+            # reads rank 0's (counters and client state are the same in all of them, the weights come from the shards)
+            path = layout.model_states(self._mp_rank(), 0)
         if not os.path.exists(path):
             logger.warning("Client provided checkpoint load path: {} does not exist ... skip checkpoint load".format(path))
             return None, None

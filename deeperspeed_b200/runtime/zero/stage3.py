@@ -828,6 +828,8 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
             "partition_count": self.partition_count,
             "optimizer_state_dict": inner,
             "fp32_flat_groups": masters,
+            # what a loader with a different data-parallel degree needs to cut the arenas apart again
+            "sub_group_numels": [[p.ds_numel for p in params] for params in self.sub_groups],
         }
 
     def _swapped_state_for_checkpoint(self):
@@ -855,8 +857,10 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
     def load_state_dict(self, state_dict_list, load_optimizer_states=True, load_from_fp32_weights=False):
         if isinstance(state_dict_list, dict):
             state_dict_list = [state_dict_list]
-        sd = state_dict_list[min(self.dp_rank, len(state_dict_list) - 1)]
-        assert sd["partition_count"] == self.partition_count, "ZeRO-3 checkpoints are rigid: same DP degree required"
+        if state_dict_list[0]["partition_count"] != self.partition_count:
+            sd = self._reshard_for_this_rank(state_dict_list)
+        else:
+            sd = state_dict_list[min(self.dp_rank, len(state_dict_list) - 1)]
         self.loss_scaler = sd["loss_scaler"]
         self.dynamic_loss_scale = sd["dynamic_loss_scale"]
         self.overflow = sd["overflow"]
@@ -883,6 +887,73 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
                 p.ds_status = ZeroParamStatus.NOT_AVAILABLE
                 p.all_gather()
         self._peer_shard_fence()
+
+    def _reshard_for_this_rank(self, shards):
+        """A checkpoint written with another data-parallel degree (the reference's ZeRO-3 checkpoints are rigid,
+        stage3.py:3072): every saved arena is cut back into its parameters' shards, the shards of all saved ranks are
+        joined into the full fp32 vectors (master and every per-element optimizer state), and those are cut again
+        for this rank's arenas. Returns a state dict in the layout `load_state_dict` expects from a same-degree save."""
+        saved_world = shards[0]["partition_count"]
+        assert len(shards) == saved_world, f"need all {saved_world} ZeRO shards of the checkpoint, got {len(shards)}"
+        layout = shards[0].get("sub_group_numels")
+        assert layout is not None, "this ZeRO-3 checkpoint predates re-shardable saves: load it with the same DP degree"
+        saved_numels = [n for group in layout for n in group]
+        mine = [p.ds_numel for params in self.sub_groups for p in params]
+        assert saved_numels == mine, "the checkpoint belongs to a different model (parameter sizes differ)"
+
+        def tensors_of(shard):
+            """Per saved sub-group: {name: flat tensor} of the master and the per-element optimizer states."""
+            out = []
+            for g, master in enumerate(shard["fp32_flat_groups"]):
+                state = shard["optimizer_state_dict"]["state"].get(g, {})
+                per = {"": master}
+                per.update({k: v for k, v in state.items() if torch.is_tensor(v) and v.numel() == master.numel()})
+                out.append(per)
+            return out
+
+        per_rank = [tensors_of(shard) for shard in shards]
+        names = sorted(set().union(*[set(g) for g in per_rank[0]]))
+        full = {name: [] for name in names}          # name -> full vectors, one per parameter, in parameter order
+        for g, numels in enumerate(layout):
+            offset = 0
+            for n in numels:
+                part = -(-n // saved_world)
+                for name in names:
+                    if name in per_rank[0][g]:
+                        pieces = [per_rank[r][g][name].narrow(0, offset, part) for r in range(saved_world)]
+                        full[name].append(torch.cat(pieces)[:n].float())
+                    else:
+                        full[name].append(None)
+                offset += part
+        world, rank = self.partition_count, self.dp_rank
+        masters, states, k = [], {}, 0
+        scalars = shards[0]["optimizer_state_dict"]["state"]
+        for g, params in enumerate(self.sub_groups):
+            arenas = {name: [] for name in names}
+            for p in params:
+                part = -(-p.ds_numel // world)
+                for name in names:
+                    vec = full[name][k]
+                    if vec is None:
+                        continue
+                    padded = torch.zeros(part * world, dtype=torch.float32)
+                    padded[:p.ds_numel] = vec
+                    arenas[name].append(padded.narrow(0, rank * part, part))
+                k += 1
+            masters.append(torch.cat(arenas[""]))
+            state = {name: torch.cat(parts) for name, parts in arenas.items() if name and parts}
+            if state:
+                # scalar entries (the step count) are the same in every saved sub-group
+                state.update({key: v for key, v in next(iter(scalars.values())).items() if not torch.is_tensor(v)
+                              or v.numel() == 1})
+                states[g] = state
+        inner = {"state": states, "param_groups": self.optimizer.state_dict()["param_groups"]}
+        saved_groups = shards[0]["optimizer_state_dict"]["param_groups"]
+        for group in inner["param_groups"]:          # hyper-parameters (lr after scheduling, betas, ...) as saved
+            group.update({key: v for key, v in saved_groups[0].items() if key != "params"})
+        out = dict(shards[0])
+        out.update(partition_count=world, fp32_flat_groups=masters, optimizer_state_dict=inner)
+        return out
 
     def __repr__(self):
         return repr(self.optimizer)

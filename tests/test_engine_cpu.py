@@ -291,15 +291,24 @@ def test_zero_to_fp32_script_runs_standalone_from_checkpoint_dir(tmp_path):
         assert torch.allclose(got[k].float(), want[k], atol=1e-6), k
 
 
-@pytest.mark.parametrize("stage", [1, 2])
+def _whole_parameters(engine):
+    params = list(engine.module.parameters())
+    with deepspeed.zero.GatheredParameters(params, enabled=engine.zero_optimization_stage() == 3):
+        return [p.detach().clone() for p in params]
+
+
+@pytest.mark.parametrize("stage", [1, 2, 3])
 def test_elastic_reload_world3_to_world2_continues_identically(stage, tmp_path):
     """Elastic ZeRO checkpoints (padding-free shards, reference stage1.py:924-1098 / stage2.py:1685-1823): a run saved
     on 3 ranks and resumed on 2 has the same master weights and Adam moments, i.e. the same next update as the run
-    that was never interrupted (same global batch, same data)."""
+    that was never interrupted (same global batch, same data). Stage 3 as well - the reference's stage-3 checkpoints
+    are rigid (stage3.py:3072) - with sub-groups that fall differently for the two world sizes."""
     def cfg_for(world):
         c = _cfg(stage)
         c["train_batch_size"] = 12
         c["train_micro_batch_size_per_gpu"] = 2
+        if stage == 3:
+            c["zero_optimization"].update({"stage3_param_persistence_threshold": 0, "sub_group_size": 100})
         return c          # gas = 2 on 3 ranks, 3 on 2 ranks
 
     data = torch.utils.data.TensorDataset(*random_dataset(48, HID, seed=99).tensors)
@@ -328,8 +337,9 @@ def test_elastic_reload_world3_to_world2_continues_identically(stage, tmp_path):
         run_steps(engine, 3, 2, 0)
         engine.save_checkpoint(str(tmp_path), tag="w3")
         run_steps(engine, 3, 1, 2)            # the uninterrupted run goes one step further
+        whole = _whole_parameters(engine)
         if dist.get_rank() == 0:
-            torch.save([p.detach().clone() for p in engine.module.parameters()], os.path.join(str(tmp_path), "w3_step3.pt"))
+            torch.save(whole, os.path.join(str(tmp_path), "w3_step3.pt"))
     save()
 
     @distributed_test(world_size=2)
@@ -341,8 +351,53 @@ def test_elastic_reload_world3_to_world2_continues_identically(stage, tmp_path):
         assert path is not None and engine.global_steps == 2
         run_steps(engine, 2, 1, 2)
         want = torch.load(os.path.join(str(tmp_path), "w3_step3.pt"))
-        for p, w in zip(engine.module.parameters(), want):
-            assert torch.allclose(p.detach(), w, atol=2e-6), (p.detach() - w).abs().max()
+        for p, w in zip(_whole_parameters(engine), want):
+            assert torch.allclose(p, w, atol=2e-6), (p - w).abs().max()
+    resume()
+
+
+def test_zero3_checkpoint_resumes_on_more_ranks(tmp_path):
+    """The other direction for stage 3: saved on 2 ranks, resumed on 4 (ranks 2 and 3 have no model-states file of
+    their own and read rank 0's); the next step equals the uninterrupted run's."""
+    def cfg():
+        c = _cfg(3, train_batch_size=8)
+        c["zero_optimization"].update({"stage3_param_persistence_threshold": 0, "sub_group_size": 150})
+        return c
+
+    data = random_dataset(32, HID, seed=5).tensors
+
+    def step(engine, world, index):
+        per_rank = 8 // world
+        lo = index * 8 + dist.get_rank() * per_rank
+        for i in range(0, per_rank, 2):
+            loss = engine(data[0][lo + i:lo + i + 2], data[1][lo + i:lo + i + 2])
+            engine.backward(loss)
+            engine.step()
+
+    @distributed_test(world_size=2)
+    def save():
+        torch.manual_seed(3)
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg()), model=model,
+                                               model_parameters=model.parameters())
+        step(engine, 2, 0)
+        engine.save_checkpoint(str(tmp_path), tag="w2")
+        step(engine, 2, 1)
+        whole = _whole_parameters(engine)
+        if dist.get_rank() == 0:
+            torch.save(whole, os.path.join(str(tmp_path), "w2_next.pt"))
+    save()
+
+    @distributed_test(world_size=4)
+    def resume():
+        model = SimpleModel(HID)
+        engine, _, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, cfg()), model=model,
+                                               model_parameters=model.parameters())
+        path, _ = engine.load_checkpoint(str(tmp_path), tag="w2")
+        assert path is not None and engine.global_steps == 1
+        step(engine, 4, 1)
+        for p, w in zip(_whole_parameters(engine), torch.load(os.path.join(str(tmp_path), "w2_next.pt"))):
+            assert torch.allclose(p, w, atol=2e-6), (p - w).abs().max()
     resume()
 
 
