@@ -146,6 +146,9 @@ class PartitionedParameterCoordinator:
         self.params_in_flight = []
         self.comm_stream = comm_stream
         self.trace = ExecutionTrace()
+        # weights served by the fused all-gather + GEMM kernels are not worth gathering ahead; the optimizer clears
+        # this in backward when the input-gradient kernel is not in use (then backward gathers them like any other)
+        self.fused_weights_stay_partitioned = True
         self.hierarchy = 0
         self.total_available_parameter_numel = 0
         self.max_available_parameters_in_numel = max_available_parameters_in_numel
@@ -209,7 +212,7 @@ class PartitionedParameterCoordinator:
             if mod is None:
                 continue
             params = [p for p in self._params_of(mod) if p.ds_status == ZeroParamStatus.NOT_AVAILABLE
-                      and not getattr(p, "ds_fused_ag", False)]
+                      and not (self.fused_weights_stay_partitioned and getattr(p, "ds_fused_ag", False))]
             cost = sum(p.ds_numel for p in params)
             if not params:
                 continue
@@ -512,6 +515,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         pc = self.param_coordinator
         if module is self.module:
             pc.trace.begin_pass()
+        pc.fused_weights_stay_partitioned = True
         pc.fetch_sub_module(module, forward=True)
         pc.prefetch_next_sub_modules(module, numel=self.prefetch_elements)
 
@@ -563,6 +567,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
     def _pre_backward(self, module):
         # weights on the fused path stay partitioned in backward as well (K-sharded all-gather + GEMM for the input
         # gradient, GEMM + reduce-scatter for the weight gradient); DSB_ZERO3_FUSED_DGRAD=0 gathers them with NCCL
+        self.param_coordinator.fused_weights_stay_partitioned = self._fused_dgrad
         self.param_coordinator.fetch_sub_module(module, forward=self._fused_dgrad)
         self.param_coordinator.prefetch_next_sub_modules(module, numel=self.prefetch_elements)    # backward looks ahead too
 
