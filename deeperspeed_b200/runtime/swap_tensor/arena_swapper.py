@@ -47,6 +47,7 @@ class ArenaSwapper:
         self.holders = {}                    # arena -> number of acquire() calls not yet released
         self.reading = {}                    # arena -> slot of a read that was issued and not waited for
         self.writes_in_flight = False
+        self.being_written = set()           # arenas whose buffer an asynchronous write is still reading
         self.last_use = {}                   # slot -> CUDA event after the last device copy out of / into it
         self.stats = {"reads": 0, "writes": 0, "evictions": 0, "prefetch_hits": 0}
 
@@ -80,6 +81,7 @@ class ArenaSwapper:
         if self.writes_in_flight:
             self.write_handle.wait()
             self.writes_in_flight = False
+            self.being_written.clear()
 
     def _wait_device(self, slot):
         event = self.last_use.pop(slot, None)
@@ -119,6 +121,8 @@ class ArenaSwapper:
         if not self.free_slots and not any(self.holders[i] == 0 for i in self.resident):
             return False
         slot = self._take_slot()
+        if idx in self.being_written:
+            self._drain_writes()                         # do not read a file that is still being written
         self.read_handle.async_pread(self._io_view(idx, slot), self._path(idx))
         self.reading[idx] = slot
         self.stats["reads"] += 1
@@ -129,6 +133,8 @@ class ArenaSwapper:
         if idx in self.reading:
             self._finish_reads()
             self.stats["prefetch_hits"] += 1
+        if idx in self.being_written:
+            self._drain_writes()                         # the caller may modify the buffer
         if idx in self.resident:
             self.resident.move_to_end(idx)
         else:
@@ -158,6 +164,7 @@ class ArenaSwapper:
         self._drain_writes()
         self.write_handle.async_pwrite(self._io_view(idx, slot), self._path(idx))
         self.writes_in_flight = True
+        self.being_written.add(idx)
         self.stats["writes"] += 1
         if not async_op:
             self._drain_writes()

@@ -417,8 +417,8 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         return flat
 
     class _HeldArena:
-        def __init__(self, owner, idx, load, dirty):
-            self.owner, self.idx, self.load, self.dirty = owner, idx, load, dirty
+        def __init__(self, owner, idx, load, dirty, async_write=False):
+            self.owner, self.idx, self.load, self.dirty, self.async_write = owner, idx, load, dirty, async_write
 
         def __enter__(self):
             o = self.owner
@@ -430,13 +430,13 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
             o = self.owner
             if o.param_swapper is not None:
                 if self.dirty and exc[0] is None:
-                    o.param_swapper.write_back(self.idx)
+                    o.param_swapper.write_back(self.idx, async_op=self.async_write)
                 o.param_swapper.release(self.idx)
 
-    def _lp_arena(self, idx, load=False, dirty=True):
+    def _lp_arena(self, idx, load=False, dirty=True, async_write=False):
         """`with self._lp_arena(idx) as lp:` - the low-precision shard arena of sub-group `idx`, brought in from its
         file when parameters are swapped to NVMe (and written back on exit when `dirty`)."""
-        return self._HeldArena(self, idx, load, dirty)
+        return self._HeldArena(self, idx, load, dirty, async_write)
 
     def _master_follows_shard(self, param):
         """A shard was rewritten from outside the optimizer (`GatheredParameters(modifier_rank=...)`, weights loaded
@@ -725,7 +725,9 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
         return combined
 
     def _optimizer_step(self, idx, inv):
-        with self._lp_arena(idx) as lp:        # every element is rewritten from the master: no read needed
+        # every element is rewritten from the master: no read needed; the file write of this sub-group runs under the
+        # next sub-group's step (the swapper waits for it before the buffer is reused or the file is read)
+        with self._lp_arena(idx, async_write=True) as lp:
             self._optimizer_step_into(idx, inv, lp)
 
     def _optimizer_step_into(self, idx, inv, lp):
@@ -774,6 +776,8 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
             self._optimizer_step(idx, inv)
             if self.optimizer_swapper is not None:
                 self.optimizer_swapper.swap_out_optimizer_state(parameter=self.fp32_partitioned_groups_flat[idx])
+        if self.param_swapper is not None:
+            self.param_swapper.flush()          # the last sub-group's file write
         self.loss_scaler.update_scale(False)
         self.zero_grad()
         # persistent (always-gathered) params must see their updated values
