@@ -769,3 +769,40 @@ def test_stage3_evaluation_pass_between_training_steps_releases_everything(tmp_p
         assert all(l == l for l in losses)
 
     run()
+
+
+def test_arena_swapper_alone(tmp_path):
+    """ArenaSwapper without an engine: contents survive eviction, the least recently used free arena goes first, held
+    arenas are never evicted (a clear error when every buffer is held), oversized arenas are refused, a prefetch is
+    picked up by the next acquire, and an asynchronous write is finished before its file is read back."""
+    from deeperspeed_b200.runtime.swap_tensor.arena_swapper import ArenaSwapper
+    sw = ArenaSwapper(str(tmp_path), torch.float32, buffer_count=2, buffer_size=1000,
+                      aio_config={"block_size": 65536, "queue_depth": 4, "thread_count": 1})
+    seen = {}
+    for idx in range(3):
+        sw.register(idx, 700 + idx, lambda view, idx=idx: seen.__setitem__(idx, view))
+        buf = sw.acquire(idx, load=False)
+        buf.fill_(float(idx + 1))
+        sw.write_back(idx, async_op=(idx == 2))          # the last one is still on its way out
+        sw.release(idx)
+    assert sw.resident_arenas() == [1, 2] and seen[0] is None and seen[2].numel() == 702
+    with pytest.raises(ValueError):
+        sw.register(9, 5000, lambda view: None)
+    back = sw.acquire(0)                                 # evicts 1 (least recently used), reads the file
+    assert torch.all(back == 1.0) and back.numel() == 700 and sw.resident_arenas() == [2, 0]
+    held_too = sw.acquire(2)
+    assert torch.all(held_too == 3.0)
+    with pytest.raises(RuntimeError):
+        sw.acquire(1)                                    # both buffers are held
+    sw.release(2)
+    assert sw.prefetch(1) and not sw.prefetch(1)         # takes over arena 2's buffer; a second call has nothing to do
+    one = sw.acquire(1)
+    assert torch.all(one == 2.0) and sw.stats["prefetch_hits"] == 1
+    sw.release(1)
+    sw.release(0)
+    again = sw.acquire(2)                                # written asynchronously above, evicted since
+    assert torch.all(again == 3.0)
+    sw.release(2)
+    sw.flush()
+    assert all(h == 0 for h in sw.holders.values())
+    assert sorted(os.listdir(sw.folder)) == ["arena_0.swp", "arena_1.swp", "arena_2.swp"]
