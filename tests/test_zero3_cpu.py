@@ -806,3 +806,65 @@ def test_arena_swapper_alone(tmp_path):
     sw.flush()
     assert all(h == 0 for h in sw.holders.values())
     assert sorted(os.listdir(sw.folder)) == ["arena_0.swp", "arena_1.swp", "arena_2.swp"]
+
+
+class _Branchy(torch.nn.Module):
+    """Takes a different path through its layers from one step to the next."""
+
+    def __init__(self, dim=HID):
+        super().__init__()
+        self.first, self.detour, self.last = (torch.nn.Linear(dim, dim) for _ in range(3))
+        self.calls = 0
+
+    def forward(self, x):
+        self.calls += 1
+        h = torch.tanh(self.first(x))
+        if self.calls % 2 == 0:
+            h = torch.tanh(self.detour(h)) + h
+        return self.last(h).pow(2).mean()
+
+
+def test_stage3_follows_control_flow_that_changes_between_steps():
+    """The recorded execution trace is a hint, not a contract: a model whose path changes from step to step (one layer
+    is skipped every other step, so it has no gradient then) trains exactly like plain Adam; the trace is cut at the
+    first deviation and recorded again."""
+    import copy
+
+    @distributed_test(world_size=2)
+    def run():
+        torch.manual_seed(0)
+        net = _Branchy()
+        plain = copy.deepcopy(net)
+        popt = torch.optim.Adam(plain.parameters(), lr=1e-2)
+        cfg = {"train_batch_size": 4, "train_micro_batch_size_per_gpu": 2, "steps_per_print": 100,
+               "optimizer": {"type": "Adam", "params": {"lr": 1e-2, "adam_w_mode": False}},
+               "fp16": {"enabled": True, "type": "fp32"},
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+        engine, opt, _, _ = deepspeed.initialize(model=net, model_parameters=net.parameters(), config_params=cfg)
+        g = torch.Generator().manual_seed(6)
+        lengths = []
+        for _ in range(5):
+            x = torch.randn(4, HID, generator=g)
+            loss = engine(x[2 * dist.get_rank():2 * dist.get_rank() + 2])
+            engine.backward(loss)
+            engine.step()
+            lengths.append(len(opt.param_coordinator.trace.order))
+            popt.zero_grad()
+            plain.calls += 1
+            took_detour = plain.calls % 2 == 0
+            plain.calls -= 1                                  # both halves of the global batch take the same path
+            a = plain(x[:2])
+            plain.calls -= 1
+            b = plain(x[2:])
+            (0.5 * (a + b)).backward()
+            if not took_detour:                               # the engine's Adam sees a zero gradient there, not None
+                for p in plain.detour.parameters():
+                    p.grad = torch.zeros_like(p)
+            popt.step()
+        assert len(set(lengths)) == 2, lengths                # the trace was re-recorded as the path changed
+        for (name, p), q in zip(net.named_parameters(), plain.parameters()):
+            assert p.ds_status == ZeroParamStatus.NOT_AVAILABLE
+            with deepspeed.zero.GatheredParameters(p):
+                assert torch.allclose(p.detach(), q.detach(), atol=1e-5), (name, (p - q).abs().max())
+
+    run()
