@@ -812,7 +812,7 @@ class FP16_DeepSpeedZeroOptimizer_Stage3:
     def state(self):
         return self.optimizer.state
 
-    # ------------------------------------------------------------------ checkpoints (same-degree loads take the saved arenas as they are; another degree re-shards)
+    # ------------------------------------------------------------------ checkpoints (another DP degree re-shards on load)
     def save_checkpoint_prologue(self):
         for p in self.module.parameters():
             self.param_coordinator.release_and_reset_parameter(p)
