@@ -1,6 +1,10 @@
 """AsyncPartitionedParameterSwapper: low-precision parameter shards <-> NVMe with a pinned buffer pool
 (`buffer_count` x `buffer_size` elements) and separate read / write aio handles. Files live under
-<nvme_path>/zero_stage_3/fp16params/rank<R>/ (reference deepspeed/runtime/swap_tensor/partitioned_param_swapper.py:36-308)."""
+<nvme_path>/zero_stage_3/fp16params/rank<R>/ (reference deepspeed/runtime/swap_tensor/partitioned_param_swapper.py:36-308).
+
+This is the reference's per-PARAMETER interface, kept for code that drives a swapper itself. The ZeRO-3 optimizer of
+this package does not use it: it swaps whole sub-group arenas through `arena_swapper.ArenaSwapper` (one file and one
+sequential transfer per sub-group)."""
 import os
 from enum import Enum
 
