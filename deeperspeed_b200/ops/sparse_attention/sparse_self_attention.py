@@ -22,8 +22,10 @@ class SparseSelfAttention(nn.Module):
     reorder_keys = True       # fused path: visit keys in the order planned by fused.plan_key_order
 
     def __init__(self, sparsity_config=SparsityConfig(num_heads=4), key_padding_mask_mode="add", attn_mask_mode="mul",
-                 max_seq_length=2048):
+                 max_seq_length=2048, mpu=None):
         super().__init__()
+        self.mpu = mpu          # kept for the reference's signature (sparse_self_attention.py:28); the layout is a pure
+                                # function of the configuration, so there is nothing to synchronise over its groups
         self.sparsity_config = sparsity_config
         self.max_seq_length = max_seq_length
         self.key_padding_mask_mode = key_padding_mask_mode

@@ -316,6 +316,16 @@ class FlatMixedPrecisionOptimizer:
     def all_gather_params(self):
         if not self.shard or self.dp_world == 1 or comm_stub.enabled():
             return
+        timer = getattr(self, "_comms_timer", None)
+        if timer is not None:
+            timer.start()
+        try:
+            self._all_gather_buckets()
+        finally:
+            if timer is not None:
+                timer.stop()
+
+    def _all_gather_buckets(self):
         for gi, arena in enumerate(self.arenas):
             for k in range(self.num_buckets[gi]):
                 buck = self._bucket(arena.data, gi, k)

@@ -16,7 +16,8 @@ _DYNAMIC_KEYS = ("last_overflow_iter", "scale_factor", "scale_window")
 class FP16_Optimizer(FlatMixedPrecisionOptimizer):
     def __init__(self, init_optimizer, static_loss_scale=1.0, dynamic_loss_scale=False, initial_dynamic_scale=2 ** 32,
                  dynamic_loss_args=None, verbose=True, mpu=None, clip_grad=0.0, fused_adam_legacy=False, timers=None,
-                 dp_process_group=None, fp32_allreduce=False):
+                 dp_process_group=None, fp32_allreduce=False, deepspeed=None):
+        self.deepspeed = deepspeed          # the engine, when it builds the wrapper (reference fused_optimizer.py:61)
         self.fused_adam_legacy = fused_adam_legacy
         self.timers = timers
         self.dynamic_loss_scale = bool(dynamic_loss_scale)

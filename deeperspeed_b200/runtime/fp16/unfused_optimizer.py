@@ -18,7 +18,8 @@ from .loss_scaler import INITIAL_LOSS_SCALE, SCALE_WINDOW, MIN_LOSS_SCALE
 
 class FP16_UnfusedOptimizer:
     def __init__(self, init_optimizer, static_loss_scale=1.0, dynamic_loss_scale=False, dynamic_loss_args=None,
-                 verbose=True, mpu=None, clip_grad=0.0, fused_lamb_legacy=False):
+                 verbose=True, mpu=None, clip_grad=0.0, fused_lamb_legacy=False, deepspeed=None):
+        self.deepspeed = deepspeed          # the engine, when it builds the wrapper (reference unfused_optimizer.py:31)
         self.fused_lamb_legacy = fused_lamb_legacy
         self.optimizer = init_optimizer
         self.verbose, self.clip_grad, self.mpu = verbose, clip_grad, mpu

@@ -115,10 +115,16 @@ class ZeroShardedOptimizer(FlatMixedPrecisionOptimizer):
             return
         super().reduce_bucket(gi, k)
 
-    def step(self, closure=None):
-        if self._use_fused():
-            return self.fused.step()
-        return super().step(closure)
+    def step(self, closure=None, comms_timer=None):
+        """`comms_timer` (reference stage1.py:688,759-775): a timer object that is started / stopped around the
+        parameter all-gather, so a caller can report the communication share of the step."""
+        self._comms_timer = comms_timer
+        try:
+            if self._use_fused():
+                return self.fused.step()      # one kernel: there is no separate all-gather to time
+            return super().step(closure)
+        finally:
+            self._comms_timer = None
 
     # ---- checkpoints -------------------------------------------------------------------------------------
     def _inner_state_stripped(self):

@@ -743,3 +743,47 @@ def test_zero_global_grad_norm_matches_manual_norm(tmp_path):
         assert engine.get_global_grad_norm() == pytest.approx(want, rel=1e-4)
 
     run()
+
+
+def test_reference_keyword_arguments_of_optimizers_and_stage1_comms_timer(tmp_path):
+    """Keyword arguments callers written against the reference pass: `deepspeed=` of the precision wrappers, `mpu=` of
+    SparseSelfAttention, and `comms_timer=` of the ZeRO-1 step, which is started and stopped around the parameter
+    all-gather (reference stage1.py:688,759-775)."""
+    from deeperspeed_b200.ops.adam import FusedAdam
+    from deeperspeed_b200.ops.sparse_attention import SparseSelfAttention, FixedSparsityConfig
+    from deeperspeed_b200.runtime.fp16.fused_optimizer import FP16_Optimizer
+    from deeperspeed_b200.runtime.fp16.unfused_optimizer import FP16_UnfusedOptimizer
+    marker = object()
+    for cls in (FP16_Optimizer, FP16_UnfusedOptimizer):
+        model = SimpleModel(HID).bfloat16()
+        wrapped = cls(FusedAdam(model.parameters(), lr=1e-3), static_loss_scale=1.0, deepspeed=marker)
+        assert wrapped.deepspeed is marker
+    attention = SparseSelfAttention(FixedSparsityConfig(num_heads=2, block=16), max_seq_length=64, mpu=marker)
+    assert attention.mpu is marker
+
+    class Stopwatch:
+        def __init__(self):
+            self.events = []
+
+        def start(self):
+            self.events.append("start")
+
+        def stop(self):
+            self.events.append("stop")
+
+    @distributed_test(world_size=2)
+    def run():
+        model = SimpleModel(HID)
+        engine, opt, _, _ = deepspeed.initialize(args=args_from_dict(tmp_path, _cfg(1, train_batch_size=4)),
+                                                 model=model, model_parameters=model.parameters())
+        x, y = next(iter(random_dataloader(engine, 8, HID, engine.device, seed=dist.get_rank())))
+        loss = engine(x, y)
+        engine.backward(loss)
+        watch = Stopwatch()
+        before = [p.detach().clone() for p in model.parameters()]
+        opt.step(comms_timer=watch)
+        assert watch.events == ["start", "stop"]
+        assert any(not torch.equal(a, b.detach()) for a, b in zip(before, model.parameters()))
+        assert opt._comms_timer is None
+
+    run()
