@@ -13,20 +13,34 @@ def _attr(obj, path):
     return obj
 
 
-def replace_transformer_layer(orig_layer_impl, model, micro_batch_size, bert_config, seed, max_seq_length,
-                              preln=False, fp16=True, huggingface=False, local_rank=-1):
-    """Replace every `orig_layer_impl` instance in `model` by a DeepSpeedTransformerLayer carrying the same weights."""
+def replace_transformer_layer(orig_layer_impl, model, micro_batch_size, bert_config, seed=-1, preln=True, fp16=True,
+                              training=True, huggingface=False, local_rank=-1, max_seq_length=None):
+    """Replace every `orig_layer_impl` instance in `model` by a DeepSpeedTransformerLayer carrying the same weights.
+    Argument order and defaults of the reference (module_inject/replace_module.py:6-15); `max_seq_length` (an addition,
+    keyword) defaults to the model's `max_position_embeddings`."""
+    if max_seq_length is None:
+        max_seq_length = getattr(bert_config, "max_position_embeddings", 512)
+    cfg = DeepSpeedTransformerConfig(batch_size=micro_batch_size, max_seq_length=max_seq_length,
+                                     hidden_size=bert_config.hidden_size, heads=bert_config.num_attention_heads,
+                                     intermediate_size=getattr(bert_config, "intermediate_size", 4 * bert_config.hidden_size),
+                                     attn_dropout_ratio=bert_config.attention_probs_dropout_prob,
+                                     hidden_dropout_ratio=bert_config.hidden_dropout_prob,
+                                     num_hidden_layers=bert_config.num_hidden_layers,
+                                     initializer_range=bert_config.initializer_range, seed=seed, fp16=fp16,
+                                     pre_layer_norm=preln, huggingface=huggingface, local_rank=local_rank,
+                                     layer_norm_eps=getattr(bert_config, "layer_norm_eps", 1e-12))
+    cfg.training = training
+    return replace_layers_with_config(orig_layer_impl, model, cfg)
+
+
+def replace_layers_with_config(orig_layer_impl, model, transformer_config):
+    """The same replacement driven by a ready DeepSpeedTransformerConfig (what `deepspeed.ops.replace_module` takes,
+    reference ops/module_inject.py:8-88)."""
+    import copy
+    preln = bool(transformer_config.pre_layer_norm)
 
     def replace_fn(child):
-        cfg = DeepSpeedTransformerConfig(batch_size=micro_batch_size, max_seq_length=max_seq_length,
-                                         hidden_size=bert_config.hidden_size, heads=bert_config.num_attention_heads,
-                                         intermediate_size=getattr(bert_config, "intermediate_size", 4 * bert_config.hidden_size),
-                                         attn_dropout_ratio=bert_config.attention_probs_dropout_prob,
-                                         hidden_dropout_ratio=bert_config.hidden_dropout_prob,
-                                         num_hidden_layers=bert_config.num_hidden_layers,
-                                         initializer_range=bert_config.initializer_range, seed=seed, fp16=fp16,
-                                         pre_layer_norm=preln, huggingface=huggingface, local_rank=local_rank,
-                                         layer_norm_eps=getattr(bert_config, "layer_norm_eps", 1e-12))
+        cfg = copy.copy(transformer_config)          # every layer gets its own config object (it carries a layer id)
         new_module = DeepSpeedTransformerLayer(cfg)
         qw, qb = child.attention.self.query.weight, child.attention.self.query.bias
         kw, kb = child.attention.self.key.weight, child.attention.self.key.bias

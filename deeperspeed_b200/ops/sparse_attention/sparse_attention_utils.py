@@ -75,9 +75,11 @@ class SparseAttentionUtils:
 
     @staticmethod
     def pad_to_block_size(block_size, input_ids, attention_mask, token_type_ids, position_ids, inputs_embeds,
-                          pad_token_id, model_embeddings):
+                          pad_token_id, model_mbeddings):
         """Right-pad the sequence dimension to a multiple of `block_size` (padding is masked out of attention).
-        Returns (pad_len, input_ids, attention_mask, token_type_ids, position_ids, inputs_embeds)."""
+        Returns (pad_len, input_ids, attention_mask, token_type_ids, position_ids, inputs_embeds).
+        `model_mbeddings` is the reference's spelling of the keyword (sparse_attention_utils.py:158)."""
+        model_embeddings = model_mbeddings
         batch, seq_len = (input_ids.shape if input_ids is not None else inputs_embeds.shape[:-1])
         pad_len = -seq_len % block_size
         if pad_len == 0:
@@ -91,8 +93,8 @@ class SparseAttentionUtils:
             inputs_embeds = torch.cat([inputs_embeds, model_embeddings(filler)], dim=-2)
         input_ids = right_pad(input_ids, pad_token_id)
         position_ids = right_pad(position_ids, pad_token_id)
-        attention_mask = F.pad(attention_mask, (0, pad_len), value=False)
-        token_type_ids = F.pad(token_type_ids, (0, pad_len), value=0)
+        attention_mask = right_pad(attention_mask, False)
+        token_type_ids = right_pad(token_type_ids, 0)
         return pad_len, input_ids, attention_mask, token_type_ids, position_ids, inputs_embeds
 
     @staticmethod

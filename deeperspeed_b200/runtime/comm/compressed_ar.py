@@ -52,7 +52,10 @@ def compressed_all_reduce_torch(tensor, op=dist.ReduceOp.SUM, group=None, async_
 
 
 compressed_all_reduce_cupy = compressed_all_reduce_torch
-decompose_cupy = decompose
+
+
+def decompose_cupy(tensor):
+    return decompose(tensor)
 
 
 def torch2cupy(tensor):

@@ -33,8 +33,8 @@ def dict_raise_error_on_duplicate_keys(ordered_pairs):
     return d
 
 
-def get_scalar_param(d, name, default):
-    return d.get(name, default)
+def get_scalar_param(param_dict, param_name, param_default_value):
+    return param_dict.get(param_name, param_default_value)
 
 
 class ScientificNotationEncoder(json.JSONEncoder):

@@ -32,8 +32,9 @@ class CSRTensor:
         dense = self.values.new_zeros(self.dense_size)
         return dense.index_add_(0, self.indices, self.values)
 
-    def add(self, other):
+    def add(self, b):
         """Concatenate another sparse gradient of the same dense shape (summation happens in `to_dense`)."""
+        other = b
         assert self.dense_size == other.dense_size, "both operands must describe the same dense tensor"
         self.indices = torch.cat((self.indices, other.indices))
         self.values = torch.cat((self.values, other.values))

@@ -23,7 +23,19 @@ def schedule_grid(num_stages, num_micro_batches, schedule_cls=schedule.TrainSche
     return rows
 
 
-def pipeline_visualizer(num_stages, num_micro_batches, schedule_cls=schedule.TrainSchedule, print_fn=print):
+def pipeline_visualizer(num_stages, num_microbatches=None, include_all=False, *, num_micro_batches=None,
+                        schedule_cls=None, print_fn=None):
+    """The reference's call (pipe_visualizer.py:44): `pipeline_visualizer(num_stages, num_microbatches, include_all)`
+    returns the schedule as a markdown table plus idle / busy counts. With `schedule_cls` or `print_fn` it prints this
+    package's compact grid (any schedule class) and returns its rows."""
+    if num_microbatches is None:
+        num_microbatches = num_micro_batches
+    if schedule_cls is None and print_fn is None:
+        return pipeline_table(num_stages, num_microbatches, include_all)
+    return print_schedule_grid(num_stages, num_microbatches, schedule_cls or schedule.TrainSchedule, print_fn or print)
+
+
+def print_schedule_grid(num_stages, num_micro_batches, schedule_cls=schedule.TrainSchedule, print_fn=print):
     rows = schedule_grid(num_stages, num_micro_batches, schedule_cls)
     width = max(len(c) for r in rows for c in r) + 1
     for stage, cells in enumerate(rows):

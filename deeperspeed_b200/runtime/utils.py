@@ -71,8 +71,9 @@ def _agree(flag, group=None, device="cpu"):
 class CheckOverflow:
     """Checks for inf/nan over model gradients, agreeing across MP / DP ranks with a MAX all-reduce."""
 
-    def __init__(self, param_groups=None, mpu=None, zero_reduce_scatter=False):
+    def __init__(self, param_groups=None, mpu=None, zero_reduce_scatter=False, deepspeed=None):
         self.mpu = mpu
+        self.deepspeed = deepspeed
         self.params = _flat(param_groups) if param_groups else None
         self.zero_reduce_scatter = zero_reduce_scatter
 

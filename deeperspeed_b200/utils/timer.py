@@ -160,15 +160,21 @@ class SynchronizedWallClockTimer:
                                                        torch.cuda.memory_reserved() / gb,
                                                        torch.cuda.max_memory_reserved() / gb)
 
-    def log(self, names, normalizer=1.0, reset=True, memory_breakdown=False, ranks=None):
+    def log(self, names, normalizer=1.0, reset=True, memory_breakdown=False, ranks=None, return_values=True):
+        """Log a group of timers; returns {name: elapsed ms / normalizer} (reference utils/timer.py:84-102) unless
+        `return_values` is false."""
         assert normalizer > 0.0
-        s = "time (ms)"
+        s, values = "time (ms)", {}
         for name in names:
             if name in self.timers:
-                s += " | {}: {:.2f}".format(name, self.timers[name].elapsed(reset=reset) * 1000.0 / normalizer)
+                values[name] = self.timers[name].elapsed(reset=reset) * 1000.0 / normalizer
+                s += " | {}: {:.2f}".format(name, values[name])
+            else:
+                log_dist(f"logging failed for timer {name}", ranks=[0])
         if memory_breakdown:
             s += self.memory_usage()
         log_dist(s, ranks=ranks or [0])
+        return values if return_values else None
 
 
 class ThroughputTimer:

@@ -411,3 +411,77 @@ def test_config_argument_combinations(argv, enabled, config):
     assert ns.num_epochs == 2
     assert type(ns.deepspeed) is bool and ns.deepspeed == enabled
     assert ns.deepspeed_config == config
+
+
+def test_batch_size_scheduler_reference_contract():
+    """BatchSizeScheduler with the reference's constructor (bs_schedules.py:12-18): goldens produced by running the
+    reference class itself - schedule keys / values and the value at selected iterations."""
+    from deeperspeed_b200.runtime.bs_schedules import BatchSizeScheduler
+    s = BatchSizeScheduler(final_batch_size=16, num_intervals=8, warmup_num_steps=10000)
+    assert s.schedule == {0: 1, 1428: 3, 2857: 5, 4285: 7, 5714: 9, 7142: 11, 8571: 13, 10000: 16}
+    assert BatchSizeScheduler(final_batch_size=1024).schedule == {0: 11, 333: 348, 666: 686, 1000: 1024}
+    s = BatchSizeScheduler(final_batch_size=512, min_batch_size_multiplier=0.1, warmup_num_steps=300, num_intervals=7)
+    assert s.schedule == {0: 52, 50: 128, 100: 205, 150: 282, 200: 358, 250: 435, 300: 512}
+    seen = {}
+    for it in range(320):
+        seen[it] = s.step()
+        assert s.current_batch_size == seen[it]
+    assert (seen[0], seen[49], seen[50], seen[299], seen[300], seen[319]) == (52, 52, 128, 435, 512, 512)
+    assert BatchSizeScheduler(final_batch_size=3, num_intervals=4, warmup_num_steps=10).schedule == {0: 1, 6: 2, 10: 3}
+    restored = BatchSizeScheduler(final_batch_size=512, min_batch_size_multiplier=0.1, warmup_num_steps=300, num_intervals=7)
+    restored.load_state_dict({"last_batch_iteration": 149})
+    assert restored.step() == 282
+
+    class Engine:
+        sizes = []
+
+        def set_train_batch_size(self, size):
+            self.sizes.append(size)
+
+    driven = BatchSizeScheduler(final_batch_size=8, min_batch_size_multiplier=0.5, warmup_num_steps=4, num_intervals=3,
+                                deepspeed=Engine())
+    for _ in range(8):
+        driven.step()
+    assert Engine.sizes == [4, 6, 8]                      # told once per change
+
+
+def test_reference_argument_names_of_small_helpers():
+    """Keyword names callers of the reference use: `model_mbeddings` (sic) of pad_to_block_size, `b` of CSRTensor.add,
+    `deepspeed` of CheckOverflow, the three names of get_scalar_param, `tensor` of decompose_cupy, `return_values` of
+    SynchronizedWallClockTimer.log, `num_microbatches` / `include_all` of pipeline_visualizer, and the argument order
+    of `deepspeed.ops.replace_module`."""
+    import inspect
+    from deeperspeed_b200.ops.sparse_attention import SparseAttentionUtils
+    from deeperspeed_b200.runtime.csr_tensor import CSRTensor
+    from deeperspeed_b200.runtime.utils import CheckOverflow
+    from deeperspeed_b200.runtime.config_utils import get_scalar_param
+    from deeperspeed_b200.runtime.comm.compressed_ar import decompose_cupy
+    from deeperspeed_b200.runtime.pipe.pipe_visualizer import pipeline_visualizer
+    from deeperspeed_b200.utils.timer import SynchronizedWallClockTimer
+    from deeperspeed_b200.module_inject import replace_transformer_layer
+
+    def names(fn):
+        return list(inspect.signature(fn).parameters)
+
+    assert names(SparseAttentionUtils.pad_to_block_size)[-1] == "model_mbeddings"
+    emb = torch.nn.Embedding(10, 4)
+    ids = torch.randint(0, 10, (2, 5))
+    pad, ids2, mask2, *_ = SparseAttentionUtils.pad_to_block_size(block_size=4, input_ids=ids,
+                                                                 attention_mask=torch.ones(2, 5), token_type_ids=None,
+                                                                 position_ids=None, inputs_embeds=None, pad_token_id=0,
+                                                                 model_mbeddings=emb)
+    assert pad == 3 and ids2.shape == (2, 8) and mask2.shape == (2, 8)
+    assert names(CSRTensor.add) == ["self", "b"]
+    assert CheckOverflow(deepspeed="engine").deepspeed == "engine"
+    assert get_scalar_param(param_dict={"a": 1}, param_name="a", param_default_value=0) == 1
+    mantissa, exponent = decompose_cupy(tensor=torch.tensor([0.5, 8.0]))
+    assert mantissa.shape == exponent.shape == (2,)
+    timers = SynchronizedWallClockTimer()
+    timers("x").start(); timers("x").stop()
+    values = timers.log(["x", "never_started"], return_values=True)
+    assert set(values) == {"x"} and values["x"] >= 0 and timers.log(["x"], return_values=False) is None
+    text = pipeline_visualizer(num_stages=2, num_microbatches=2, include_all=False)
+    assert "Idle Time: 4" in text and "Non Idle Time: 8" in text
+    assert names(deepspeed.ops.replace_module) == ["orig_module_impl", "model", "replacement_module_config"]
+    assert names(replace_transformer_layer)[:10] == ["orig_layer_impl", "model", "micro_batch_size", "bert_config", "seed",
+                                                     "preln", "fp16", "training", "huggingface", "local_rank"]
